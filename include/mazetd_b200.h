@@ -1,0 +1,143 @@
+/*
+ * mazetd_b200.h -- C ABI of libmazetd_b200.so: the B200-native (sm_100a) replacement for mazetd's
+ * flow-field hot path. Plain pointers and sizes only; no C++ or torch types cross this boundary.
+ *
+ * Each entry point names the reference interface it replaces (paths relative to the mazetd tree).
+ * The reference has no plugin registry: the seam is link-time substitution of the bodies of
+ * sources/map/paths.cpp, sources/map/grid.cpp and the elevation part of sources/map/procedural.cpp
+ * (SURVEY.md 8b). mazetd_b200/host/ holds those replacement bodies (thin adapters onto this ABI);
+ * INTEGRATION.md shows how a maintainer links them.
+ *
+ * Conventions
+ *   - tile index idx = y * W + x (sources/map/grid.cpp:105); MTD_M = 0xFFFFFFFF is cage's `m`.
+ *   - distances are uint32 "24.8" fixed point with 255 units per world unit (sources/common.h:15-29).
+ *   - flags are mazetd TileFlags bits (sources/grid.h:15-28); pathing reads Invalid|Building only
+ *     (sources/map/paths.cpp:65).
+ *   - every call returns 0 on success, a negative MTD_ERR_* otherwise; mtd_last_error() has the text.
+ *     No C++ exception crosses the boundary (the adapter turns codes into cage::Exception).
+ *   - "host" entry points take caller-owned HOST pointers and are synchronous (results are complete on
+ *     return, like the reference's update()). "_dev" entry points take DEVICE pointers, enqueue on the
+ *     context's stream and do not synchronise: they are what bench.py times for the HBM-resident metric.
+ *   - there is no CPU fallback: without a CUDA device mtd_create() fails with MTD_ERR_CUDA.
+ */
+#ifndef MAZETD_B200_H
+#define MAZETD_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MTD_M 0xFFFFFFFFu
+#define MTD_MAX_WAYPOINTS 32 /* visited bits are a uint32 (sources/map/paths.cpp:147) */
+
+enum
+{
+	MTD_OK = 0,
+	MTD_ERR_ARG = -1,      /* bad argument (null pointer, size, tile out of range) */
+	MTD_ERR_CUDA = -2,     /* CUDA runtime error, no device, or kernel fault */
+	MTD_ERR_STATE = -3,    /* call order (e.g. update before grid upload) */
+	MTD_ERR_CAPACITY = -4, /* map does not fit the selected path / buffer too small */
+	MTD_ERR_OVERFLOW = -5, /* a distance reached the uint32 guard band (reference would wrap) */
+	MTD_ERR_NOMEM = -6
+};
+
+typedef struct mtd_ctx mtd_ctx;
+
+/* ---- lifecycle ------------------------------------------------------------------------------- */
+/* device: CUDA ordinal. stream: a cudaStream_t to enqueue on (e.g. torch's current stream), or NULL to let
+ * the context create its own non-blocking stream. */
+int mtd_create(mtd_ctx **out, int device, void *stream);
+void mtd_destroy(mtd_ctx *ctx);
+const char *mtd_last_error(const mtd_ctx *ctx);
+int mtd_version(void);
+/* blocks until everything enqueued by this context has finished; returns deferred kernel status */
+int mtd_synchronize(mtd_ctx *ctx);
+/* number of kernels this context has launched since creation (bench.py's gpu_launches) */
+uint64_t mtd_launch_count(const mtd_ctx *ctx);
+
+/* ---- Grid (replaces the data side of struct Grid, sources/grid.h:38-53) ------------------------ */
+/* Upload a grid; builds the device-side derived data (packed edge weights = Grid::neighborDistance for the
+ * right/down edge of every tile, sources/map/grid.cpp:141-145, and the Invalid|Building blocking mask). */
+int mtd_grid_upload(mtd_ctx *ctx, int32_t W, int32_t H, int32_t ox, int32_t oy, const int16_t *elev, const uint16_t *flags);
+int mtd_grid_upload_dev(mtd_ctx *ctx, int32_t W, int32_t H, int32_t ox, int32_t oy, const int16_t *d_elev, const uint16_t *d_flags);
+/* placeStructure / clearStructure flag flip (sources/player/buildingsPlacement.cpp:120-130, 143-164):
+ * overwrite the flags word of one tile on the device mirror. */
+int mtd_grid_set_flags(mtd_ctx *ctx, uint32_t tile, uint16_t flags);
+/* Grid::neighborDistance for arbitrary adjacent pairs, computed on the device (parity probe for G4). */
+int mtd_neighbor_distances(mtd_ctx *ctx, const uint32_t *a, const uint32_t *b, int32_t n, uint32_t *out);
+/* right/down edge weights of every tile as the kernels see them (0 where there is no such neighbour) */
+int mtd_edge_weights(mtd_ctx *ctx, uint32_t *right, uint32_t *down);
+
+/* ---- Directions::update (sources/map/paths.cpp:24-78) ----------------------------------------- */
+/* nsrc == 1 is the reference; nsrc > 1 seeds every source at distance 0 (synthetic multi-source config).
+ * extra_blocked != MTD_M treats that tile as Building without touching the grid -- the trial of
+ * placingBuildingBlocksMonsters (sources/player/buildingsPlacement.cpp:18-29). Outputs may be NULL. */
+int mtd_directions_update(mtd_ctx *ctx, const uint32_t *sources, int32_t nsrc, uint32_t extra_blocked, uint32_t *tiles_out, uint32_t *dist_out);
+int mtd_directions_update_dev(mtd_ctx *ctx, const uint32_t *sources /* host */, int32_t nsrc, uint32_t extra_blocked, uint32_t *d_tiles, uint32_t *d_dist);
+
+/* ---- Waypoints::update (sources/map/paths.cpp:82-139) ------------------------------------------ */
+/* n Dijkstra layers + n full-path walks + aggregates, one call.
+ *   tiles_out, dist_out : [n][W*H]            (may be NULL)
+ *   fullpath_buf        : [n][fullpath_cap]   tiles of Waypoint::fullPath, MTD_M padded (may be NULL)
+ *   fullpath_len        : [n]  true path lengths (may exceed cap; only cap entries are written)
+ *   full_distance       : [n]  Waypoint::fullDistance
+ *   agg3                : avgFullDistance, minFullDistance, minDistanceSpawner
+ * The layers stay resident on the device for mtd_waypoints_find_dev / monsters / placing_blocks. */
+int mtd_waypoints_update(mtd_ctx *ctx, const uint32_t *wp_tiles, int32_t n, uint32_t *tiles_out, uint32_t *dist_out, uint32_t *fullpath_buf, uint32_t fullpath_cap, uint32_t *fullpath_len, uint32_t *full_distance, uint32_t *agg3);
+int mtd_waypoints_update_dev(mtd_ctx *ctx, const uint32_t *wp_tiles /* host */, int32_t n);
+/* Waypoints::find (sources/map/paths.cpp:141-169) evaluated on the device for a batch of queries
+ * (host arrays in/out). The adapter keeps the per-call host version on host mirrors, as SURVEY.md 8b asks. */
+int mtd_waypoints_find(mtd_ctx *ctx, const uint32_t *pos, const uint32_t *bits, int32_t nq, uint32_t *tile_out, uint32_t *dist_out);
+/* device pointers of the resident layers ([n][W*H] each); valid until the next update/upload */
+int mtd_waypoints_layers_dev(mtd_ctx *ctx, uint32_t **d_tiles, uint32_t **d_dist);
+
+/* ---- placingBuildingBlocksMonsters (sources/player/buildingsPlacement.cpp:18-42) ---------------- */
+/* One trial Dijkstra from waypoint 0 with `candidate` blocked; *blocked_out = 1 if any waypoint tile or any
+ * live resident monster (mtd_monsters_upload) becomes unreachable. */
+int mtd_placing_blocks(mtd_ctx *ctx, uint32_t candidate, int32_t *blocked_out);
+
+/* ---- procedural generator (sources/map/procedural.cpp:13-70, sources/map/grid.cpp:147-198,
+ *      sources/map/paths.cpp:173-201) ------------------------------------------------------------- */
+typedef struct mtd_mapgen_params
+{
+	int32_t W, H;     /* reference: 101, 101 (grid.cpp:150) */
+	int32_t ox, oy;   /* reference: 50, 50   (grid.cpp:151) */
+	int32_t radius;   /* reference: 45       (grid.cpp:179); < 0 disables the radius test */
+	int32_t nwp;      /* reference: 4        (paths.cpp:190) */
+	uint32_t fullpath_cap;
+} mtd_mapgen_params;
+
+/* Generate maps k = first .. first+nmaps-1 from RNG seed (s1 + k, s2): newProcedural -> newGrid ->
+ * newWaypoints (incl. Waypoints::update). All outputs are optional host arrays, map-major:
+ *   elev [nmaps][T] int16, flags [nmaps][T] uint16, wp_tiles [nmaps][nwp],
+ *   tiles/dist [nmaps][nwp][T], fullpath [nmaps][nwp][cap], fullpath_len/full_distance [nmaps][nwp],
+ *   agg [nmaps][3]. */
+int mtd_mapgen_batch(mtd_ctx *ctx, const mtd_mapgen_params *p, uint64_t s1, uint64_t s2, int32_t first, int32_t nmaps, int16_t *elev, uint16_t *flags, uint32_t *wp_tiles, uint32_t *tiles, uint32_t *dist, uint32_t *fullpath, uint32_t *fullpath_len, uint32_t *full_distance, uint32_t *agg);
+/* same with DEVICE output pointers (all required except tiles/dist/fullpath, which may be NULL); asynchronous */
+int mtd_mapgen_batch_dev(mtd_ctx *ctx, const mtd_mapgen_params *p, uint64_t s1, uint64_t s2, int32_t first, int32_t nmaps, int16_t *d_elev, uint16_t *d_flags, uint32_t *d_wp_tiles, uint32_t *d_tiles, uint32_t *d_dist, uint32_t *d_fullpath, uint32_t *d_fullpath_len, uint32_t *d_full_distance, uint32_t *d_agg);
+/* raw float32 ProceduralImpl::elevation samples (procedural.cpp:65-70) for seed (s1, s2): parity probe */
+int mtd_elevation_samples(mtd_ctx *ctx, uint64_t s1, uint64_t s2, const float *xy, int32_t n, float *out);
+
+/* ---- monster steering (sources/game/monsters.cpp:55-99, sources/game/game.cpp:15-21) ------------ */
+/* SoA mirror of PositionComponent / MovementComponent / MonsterComponent fields the tick touches
+ * (sources/game.h:154-186). dotflags: bit0 = affected(Fire), bit1 = affected(Water); NULL = none.
+ * damage NULL = 0. alive NULL = all alive. */
+int mtd_monsters_upload(mtd_ctx *ctx, int32_t n, const uint32_t *tile, const uint32_t *tileStart, const uint32_t *tileEnd, const uint32_t *timeStart, const uint32_t *timeEnd, const uint32_t *bits, const uint32_t *timeToArrive, const uint8_t *dotflags, const uint32_t *damage, const uint8_t *alive);
+int mtd_monsters_download(mtd_ctx *ctx, uint32_t *tile, uint32_t *tileStart, uint32_t *tileEnd, uint32_t *timeStart, uint32_t *timeEnd, uint32_t *bits, uint8_t *alive);
+/* one "move monsters" tick at gameTime against the resident waypoint layers. Asynchronous. */
+int mtd_monsters_tick_dev(mtd_ctx *ctx, uint32_t gameTime);
+/* synchronous variant returning the damage dealt to the player this tick and the number of live monsters */
+int mtd_monsters_tick(mtd_ctx *ctx, uint32_t gameTime, int64_t *damage_out, uint32_t *alive_out);
+/* MovementComponent::position() for every monster -> [n][3] float32 (device or host output) */
+int mtd_monsters_positions_dev(mtd_ctx *ctx, uint32_t gameTime, float *d_out3n);
+int mtd_monsters_positions(mtd_ctx *ctx, uint32_t gameTime, float *out3n);
+/* SpawningGroup::spawnOne steering state (sources/game/monsterSpawning.cpp:205-216): out3 = tile, bits, timeToArrive */
+int mtd_monster_spawn(mtd_ctx *ctx, uint32_t gameTime, float speed, uint32_t *out3);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif

@@ -1,0 +1,267 @@
+"""ctypes binding of libmazetd_b200.so (include/mazetd_b200.h). No torch here: plain pointers and sizes.
+
+The library is the product; this module only loads it and fails loudly when it is missing or when the
+CUDA device is absent (there is no CPU fallback by design)."""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libmazetd_b200.so")
+
+M = 0xFFFFFFFF
+
+EXPORTS = [
+    "mtd_create", "mtd_destroy", "mtd_last_error", "mtd_version", "mtd_synchronize", "mtd_launch_count",
+    "mtd_grid_upload", "mtd_grid_upload_dev", "mtd_grid_set_flags", "mtd_neighbor_distances", "mtd_edge_weights",
+    "mtd_directions_update", "mtd_directions_update_dev",
+    "mtd_waypoints_update", "mtd_waypoints_update_dev", "mtd_waypoints_find", "mtd_waypoints_layers_dev",
+    "mtd_placing_blocks",
+    "mtd_mapgen_batch", "mtd_mapgen_batch_dev", "mtd_elevation_samples",
+    "mtd_monsters_upload", "mtd_monsters_download", "mtd_monsters_tick_dev", "mtd_monsters_tick",
+    "mtd_monsters_positions_dev", "mtd_monsters_positions", "mtd_monster_spawn",
+]
+
+
+class MtdError(RuntimeError):
+    def __init__(self, code, text):
+        super().__init__(f"libmazetd_b200 error {code}: {text}")
+        self.code = code
+
+
+class MapgenParams(C.Structure):
+    _fields_ = [("W", C.c_int32), ("H", C.c_int32), ("ox", C.c_int32), ("oy", C.c_int32), ("radius", C.c_int32), ("nwp", C.c_int32), ("fullpath_cap", C.c_uint32)]
+
+
+_lib = None
+
+
+def load():
+    """dlopen the in-tree library (built by mazetd_b200/build.py); raises if absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise FileNotFoundError(f"{LIB_PATH} is missing: run `python -m mazetd_b200.build` (needs nvcc). There is no CPU fallback.")
+    L = C.CDLL(LIB_PATH)
+    vp, i32, u32, u64, f32 = C.c_void_p, C.c_int32, C.c_uint32, C.c_uint64, C.c_float
+    L.mtd_create.argtypes = [C.POINTER(vp), C.c_int, vp]
+    L.mtd_destroy.argtypes = [vp]
+    L.mtd_destroy.restype = None
+    L.mtd_last_error.argtypes = [vp]
+    L.mtd_last_error.restype = C.c_char_p
+    L.mtd_synchronize.argtypes = [vp]
+    L.mtd_launch_count.argtypes = [vp]
+    L.mtd_launch_count.restype = u64
+    L.mtd_grid_upload.argtypes = [vp, i32, i32, i32, i32, vp, vp]
+    L.mtd_grid_upload_dev.argtypes = [vp, i32, i32, i32, i32, vp, vp]
+    L.mtd_grid_set_flags.argtypes = [vp, u32, C.c_uint16]
+    L.mtd_neighbor_distances.argtypes = [vp, vp, vp, i32, vp]
+    L.mtd_edge_weights.argtypes = [vp, vp, vp]
+    L.mtd_directions_update.argtypes = [vp, vp, i32, u32, vp, vp]
+    L.mtd_directions_update_dev.argtypes = [vp, vp, i32, u32, vp, vp]
+    L.mtd_waypoints_update.argtypes = [vp, vp, i32, vp, vp, vp, u32, vp, vp, vp]
+    L.mtd_waypoints_update_dev.argtypes = [vp, vp, i32]
+    L.mtd_waypoints_find.argtypes = [vp, vp, vp, i32, vp, vp]
+    L.mtd_waypoints_layers_dev.argtypes = [vp, C.POINTER(vp), C.POINTER(vp)]
+    L.mtd_placing_blocks.argtypes = [vp, u32, C.POINTER(i32)]
+    L.mtd_mapgen_batch.argtypes = [vp, C.POINTER(MapgenParams), u64, u64, i32, i32] + [vp] * 9
+    L.mtd_mapgen_batch_dev.argtypes = [vp, C.POINTER(MapgenParams), u64, u64, i32, i32] + [vp] * 9
+    L.mtd_elevation_samples.argtypes = [vp, u64, u64, vp, i32, vp]
+    L.mtd_monsters_upload.argtypes = [vp, i32] + [vp] * 10
+    L.mtd_monsters_download.argtypes = [vp] + [vp] * 7
+    L.mtd_monsters_tick_dev.argtypes = [vp, u32]
+    L.mtd_monsters_tick.argtypes = [vp, u32, C.POINTER(C.c_int64), C.POINTER(u32)]
+    L.mtd_monsters_positions_dev.argtypes = [vp, u32, vp]
+    L.mtd_monsters_positions.argtypes = [vp, u32, vp]
+    L.mtd_monster_spawn.argtypes = [vp, u32, f32, vp]
+    _lib = L
+    return L
+
+
+def _p(a):
+    """host numpy array (or None, or raw int device pointer) -> void*"""
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return C.c_void_p(a)
+    assert a.flags["C_CONTIGUOUS"], "arrays crossing the C ABI must be contiguous"
+    return C.c_void_p(a.ctypes.data)
+
+
+class Context:
+    """One mtd_ctx: a device, a stream, and the device-resident grid / layers / monsters."""
+
+    def __init__(self, device=0, stream=None):
+        self.L = load()
+        h = C.c_void_p()
+        rc = self.L.mtd_create(C.byref(h), int(device), C.c_void_p(stream) if stream else None)
+        if rc != 0:
+            raise MtdError(rc, "mtd_create failed (no CUDA device? the library has no CPU fallback)")
+        self.h = h
+        self.W = self.H = self.T = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.mtd_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise MtdError(rc, self.L.mtd_last_error(self.h).decode())
+
+    def synchronize(self):
+        self._ck(self.L.mtd_synchronize(self.h))
+
+    @property
+    def launches(self):
+        return int(self.L.mtd_launch_count(self.h))
+
+    # ---- grid ----
+    def grid_upload(self, W, H, elev, flags, ox=0, oy=0):
+        elev = np.ascontiguousarray(elev, np.int16)
+        flags = np.ascontiguousarray(flags, np.uint16)
+        assert elev.size == W * H and flags.size == W * H
+        self._ck(self.L.mtd_grid_upload(self.h, W, H, ox, oy, _p(elev), _p(flags)))
+        self.W, self.H, self.T = W, H, W * H
+
+    def grid_upload_dev(self, W, H, d_elev, d_flags, ox=0, oy=0):
+        self._ck(self.L.mtd_grid_upload_dev(self.h, W, H, ox, oy, _p(d_elev), _p(d_flags)))
+        self.W, self.H, self.T = W, H, W * H
+
+    def grid_set_flags(self, tile, flags):
+        self._ck(self.L.mtd_grid_set_flags(self.h, int(tile), int(flags)))
+
+    def neighbor_distances(self, a, b):
+        a = np.ascontiguousarray(a, np.uint32)
+        b = np.ascontiguousarray(b, np.uint32)
+        out = np.empty(len(a), np.uint32)
+        self._ck(self.L.mtd_neighbor_distances(self.h, _p(a), _p(b), len(a), _p(out)))
+        return out
+
+    def edge_weights(self):
+        r = np.empty(self.T, np.uint32)
+        d = np.empty(self.T, np.uint32)
+        self._ck(self.L.mtd_edge_weights(self.h, _p(r), _p(d)))
+        return r, d
+
+    # ---- Directions::update ----
+    def directions_update(self, sources, extra_blocked=M, want_tiles=True):
+        src = np.ascontiguousarray(np.atleast_1d(sources), np.uint32)
+        tiles = np.empty(self.T, np.uint32) if want_tiles else None
+        dist = np.empty(self.T, np.uint32)
+        self._ck(self.L.mtd_directions_update(self.h, _p(src), len(src), int(extra_blocked), _p(tiles), _p(dist)))
+        return tiles, dist
+
+    def directions_update_dev(self, sources, d_tiles, d_dist, extra_blocked=M):
+        src = np.ascontiguousarray(np.atleast_1d(sources), np.uint32)
+        self._ck(self.L.mtd_directions_update_dev(self.h, _p(src), len(src), int(extra_blocked), _p(d_tiles), _p(d_dist)))
+
+    # ---- Waypoints::update ----
+    def waypoints_update(self, wp_tiles, cap=None, want_layers=True):
+        wp = np.ascontiguousarray(wp_tiles, np.uint32)
+        n = len(wp)
+        cap = self.T if cap is None else cap
+        out = dict(
+            tiles=np.empty((n, self.T), np.uint32) if want_layers else None,
+            dist=np.empty((n, self.T), np.uint32) if want_layers else None,
+            fullpath=np.full((n, cap), M, np.uint32) if cap else None,
+            fullpath_len=np.zeros(n, np.uint32),
+            full_distance=np.zeros(n, np.uint32),
+            agg=np.zeros(3, np.uint32),
+        )
+        self._ck(self.L.mtd_waypoints_update(self.h, _p(wp), n, _p(out["tiles"]), _p(out["dist"]), _p(out["fullpath"]), cap, _p(out["fullpath_len"]), _p(out["full_distance"]), _p(out["agg"])))
+        return out
+
+    def waypoints_update_dev(self, wp_tiles):
+        wp = np.ascontiguousarray(wp_tiles, np.uint32)
+        self._ck(self.L.mtd_waypoints_update_dev(self.h, _p(wp), len(wp)))
+
+    def waypoints_find(self, pos, bits):
+        pos = np.ascontiguousarray(np.atleast_1d(pos), np.uint32)
+        bits = np.ascontiguousarray(np.atleast_1d(bits), np.uint32)
+        t = np.empty(len(pos), np.uint32)
+        d = np.empty(len(pos), np.uint32)
+        self._ck(self.L.mtd_waypoints_find(self.h, _p(pos), _p(bits), len(pos), _p(t), _p(d)))
+        return t, d
+
+    def layers_dev(self):
+        a, b = C.c_void_p(), C.c_void_p()
+        self._ck(self.L.mtd_waypoints_layers_dev(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def placing_blocks(self, candidate):
+        out = C.c_int32(0)
+        self._ck(self.L.mtd_placing_blocks(self.h, int(candidate), C.byref(out)))
+        return bool(out.value)
+
+    # ---- generator ----
+    def mapgen_batch(self, s1, s2, first, nmaps, W=101, H=101, ox=50, oy=50, radius=45, nwp=4, cap=1024, want_layers=True):
+        T = W * H
+        p = MapgenParams(W, H, ox, oy, radius, nwp, cap)
+        out = dict(
+            elev=np.empty((nmaps, T), np.int16),
+            flags=np.empty((nmaps, T), np.uint16),
+            wp_tiles=np.empty((nmaps, nwp), np.uint32),
+            tiles=np.empty((nmaps, nwp, T), np.uint32) if want_layers else None,
+            dist=np.empty((nmaps, nwp, T), np.uint32) if want_layers else None,
+            fullpath=np.empty((nmaps, nwp, cap), np.uint32) if cap else None,
+            fullpath_len=np.zeros((nmaps, nwp), np.uint32),
+            full_distance=np.zeros((nmaps, nwp), np.uint32),
+            agg=np.zeros((nmaps, 3), np.uint32),
+        )
+        self._ck(self.L.mtd_mapgen_batch(self.h, C.byref(p), s1, s2, first, nmaps, *[_p(out[k]) for k in ("elev", "flags", "wp_tiles", "tiles", "dist", "fullpath", "fullpath_len", "full_distance", "agg")]))
+        return out
+
+    def mapgen_batch_dev(self, s1, s2, first, nmaps, ptrs, W=101, H=101, ox=50, oy=50, radius=45, nwp=4, cap=1024):
+        """ptrs: dict of raw device pointers (ints) for elev, flags, wp_tiles, tiles, dist, fullpath, fullpath_len, full_distance, agg"""
+        p = MapgenParams(W, H, ox, oy, radius, nwp, cap)
+        self._ck(self.L.mtd_mapgen_batch_dev(self.h, C.byref(p), s1, s2, first, nmaps, *[_p(ptrs.get(k)) for k in ("elev", "flags", "wp_tiles", "tiles", "dist", "fullpath", "fullpath_len", "full_distance", "agg")]))
+
+    def elevation_samples(self, s1, s2, xy):
+        xy = np.ascontiguousarray(xy, np.float32)
+        out = np.empty(len(xy), np.float32)
+        self._ck(self.L.mtd_elevation_samples(self.h, s1, s2, _p(xy), len(xy), _p(out)))
+        return out
+
+    # ---- monsters ----
+    def monsters_upload(self, a):
+        n = len(a["tile"])
+        g = lambda k: _p(a[k]) if a.get(k) is not None else None
+        self._ck(self.L.mtd_monsters_upload(self.h, n, g("tile"), g("tileStart"), g("tileEnd"), g("timeStart"), g("timeEnd"), g("bits"), g("timeToArrive"), g("dotflags"), g("damage"), g("alive")))
+        self.nmon = n
+
+    def monsters_download(self):
+        n = self.nmon
+        a = {k: np.empty(n, np.uint32) for k in ("tile", "tileStart", "tileEnd", "timeStart", "timeEnd", "bits")}
+        a["alive"] = np.empty(n, np.uint8)
+        self._ck(self.L.mtd_monsters_download(self.h, *[_p(a[k]) for k in ("tile", "tileStart", "tileEnd", "timeStart", "timeEnd", "bits", "alive")]))
+        return a
+
+    def monsters_tick(self, game_time):
+        dmg, alive = C.c_int64(0), C.c_uint32(0)
+        self._ck(self.L.mtd_monsters_tick(self.h, int(game_time), C.byref(dmg), C.byref(alive)))
+        return dmg.value, alive.value
+
+    def monsters_tick_dev(self, game_time):
+        self._ck(self.L.mtd_monsters_tick_dev(self.h, int(game_time)))
+
+    def monsters_positions(self, game_time):
+        out = np.empty((self.nmon, 3), np.float32)
+        self._ck(self.L.mtd_monsters_positions(self.h, int(game_time), _p(out)))
+        return out
+
+    def monsters_positions_dev(self, game_time, d_out):
+        self._ck(self.L.mtd_monsters_positions_dev(self.h, int(game_time), _p(d_out)))
+
+    def monster_spawn(self, game_time, speed):
+        out = np.zeros(3, np.uint32)
+        self._ck(self.L.mtd_monster_spawn(self.h, int(game_time), float(speed), _p(out)))
+        return out

@@ -1,0 +1,1240 @@
+// capi.cu -- C ABI of libmazetd_b200.so (include/mazetd_b200.h): context, device buffers, kernel launches.
+// Single translation unit: all kernels are header-only templates included below.
+//
+// Build (see mazetd_b200/build.py):
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -fmad=false -shared -Xcompiler -fPIC
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "../../include/mazetd_b200.h"
+#include "big_grid.cuh"
+#include "common.cuh"
+#include "monsters.cuh"
+#include "noise.cuh"
+#include "small_maps.cuh"
+#include "sssp_warp.cuh"
+
+using namespace mtd;
+
+namespace
+{
+	constexpr size_t MAX_SMEM = 227 * 1024;
+	constexpr int BIG_TS = 64;
+	constexpr int BIG_WARPS = 2;
+
+	template<class T>
+	struct DevBuf
+	{
+		T *p = nullptr;
+		size_t cap = 0; // elements
+		cudaError_t reserve(size_t n)
+		{
+			if (n <= cap)
+				return cudaSuccess;
+			if (p)
+				cudaFree(p);
+			p = nullptr;
+			cap = 0;
+			cudaError_t e = cudaMalloc((void **)&p, n * sizeof(T));
+			if (e == cudaSuccess)
+				cap = n;
+			return e;
+		}
+		void release()
+		{
+			if (p)
+				cudaFree(p);
+			p = nullptr;
+			cap = 0;
+		}
+	};
+
+	struct HostFlags
+	{
+		int status;            // OR of ST_* bits written by kernels (copied back on demand)
+		uint32_t next_count;   // work-list size published by k_round_advance
+		int trial_blocked;
+		uint32_t alive;
+		unsigned long long damage;
+		uint32_t spawn[3];
+	};
+}
+
+struct mtd_ctx
+{
+	int device = 0;
+	int sms = 148;
+	cudaStream_t stream = nullptr;
+	bool own_stream = false;
+	char err[512] = { 0 };
+	uint64_t launches = 0;
+	std::mutex mu;
+
+	// grid
+	int W = 0, H = 0, ox = 0, oy = 0;
+	size_t T = 0;
+	bool have_grid = false;
+	bool small = false;
+	DevBuf<int16_t> elev;
+	DevBuf<uint16_t> flags;
+	// big path derived data
+	DevBuf<uint32_t> wpack;
+	DevBuf<uint8_t> blocked;
+	DevBuf<uint32_t> list0, list1, stamp, counters; // counters: count[2], cursor, total_active
+	DevBuf<uint32_t> sources;
+	int tilesX = 0, tilesY = 0;
+	uint32_t last_rounds = 0;
+
+	// resident layers
+	int nlayers = 0;
+	DevBuf<uint32_t> ltiles, ldist, lwp, dtab;
+	DevBuf<uint32_t> fp_buf, fp_len, fp_dist, agg;
+	uint32_t fp_cap = 0;
+	DevBuf<uint32_t> trial_dist;
+
+	// monsters
+	int nmon = 0;
+	DevBuf<uint32_t> m_tile, m_tileStart, m_tileEnd, m_timeStart, m_timeEnd, m_bits, m_tta, m_damage;
+	DevBuf<uint8_t> m_dot, m_alive;
+	bool m_has_dot = false, m_has_damage = false;
+	DevBuf<float> m_pos;
+
+	// scratch
+	DevBuf<uint32_t> scratch_u32a, scratch_u32b, scratch_u32c, scratch_u32d;
+	DevBuf<float> scratch_f;
+	DevBuf<int> d_status;
+	DevBuf<unsigned long long> d_damage;
+	DevBuf<uint32_t> d_small; // alive count, spawn out ...
+	DevBuf<int> d_trial;
+	HostFlags *hflags = nullptr; // pinned
+};
+
+namespace
+{
+	int fail(mtd_ctx *c, int code, const char *fmt, ...)
+	{
+		if (c)
+		{
+			va_list ap;
+			va_start(ap, fmt);
+			vsnprintf(c->err, sizeof(c->err), fmt, ap);
+			va_end(ap);
+		}
+		return code;
+	}
+
+#define CU(call)                                                                                          \
+	do                                                                                                    \
+	{                                                                                                     \
+		cudaError_t e__ = (call);                                                                         \
+		if (e__ != cudaSuccess)                                                                           \
+			return fail(ctx, e__ == cudaErrorMemoryAllocation ? MTD_ERR_NOMEM : MTD_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e__)); \
+	} while (0)
+
+#define LAUNCHED()                                                  \
+	do                                                              \
+	{                                                               \
+		ctx->launches++;                                            \
+		CU(cudaGetLastError());                                     \
+	} while (0)
+
+	struct DeviceGuard
+	{
+		int prev = -1;
+		explicit DeviceGuard(int dev)
+		{
+			cudaGetDevice(&prev);
+			if (prev != dev)
+				cudaSetDevice(dev);
+			else
+				prev = -1;
+		}
+		~DeviceGuard()
+		{
+			if (prev >= 0)
+				cudaSetDevice(prev);
+		}
+	};
+
+	int status_to_error(mtd_ctx *ctx, int st)
+	{
+		if (st & ST_GUARD)
+			return fail(ctx, MTD_ERR_OVERFLOW, "a distance reached the uint32 guard band (the reference's uint32 arithmetic would wrap)");
+		if (st & ST_NO_VALID)
+			return fail(ctx, MTD_ERR_STATE, "a generated map has no valid tile (the reference would never return from findSpawnPoint)");
+		if (st & ST_PATH_TRUNC)
+			return fail(ctx, MTD_ERR_CAPACITY, "a full path is longer than fullpath_cap (lengths are exact, tiles were truncated)");
+		return MTD_OK;
+	}
+
+	int sync_and_status(mtd_ctx *ctx)
+	{
+		CU(cudaMemcpyAsync(&ctx->hflags->status, ctx->d_status.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+		CU(cudaStreamSynchronize(ctx->stream));
+		const int st = ctx->hflags->status;
+		if (st)
+		{
+			CU(cudaMemsetAsync(ctx->d_status.p, 0, sizeof(int), ctx->stream));
+			return status_to_error(ctx, st);
+		}
+		return MTD_OK;
+	}
+
+	bool small_fits(int W, int H, int n)
+	{
+		if (W > 256 || H > 256)
+			return false;
+		const size_t T = (size_t)W * H;
+		if (T >= 65536)
+			return false;
+		const int R = n < SMALL_MAX_RESIDENT ? n : SMALL_MAX_RESIDENT;
+		// prefer full residency for n <= 4; fall back to fewer resident layers is not implemented -> big path
+		return waypoints_small_smem((int)T, R) <= MAX_SMEM;
+	}
+
+	int grid_blocks(mtd_ctx *ctx, size_t n, int threads, int per_sm = 8)
+	{
+		size_t b = (n + threads - 1) / threads;
+		const size_t cap = (size_t)ctx->sms * per_sm;
+		return (int)(b < cap ? (b ? b : 1) : cap);
+	}
+
+	// ---- small path launcher -------------------------------------------------------------------------
+	int launch_waypoints_small(mtd_ctx *ctx, WaypointsSmallParams P)
+	{
+		const int T = P.W * P.H;
+		const int R = P.n < SMALL_MAX_RESIDENT ? P.n : SMALL_MAX_RESIDENT;
+		const size_t smem = waypoints_small_smem(T, R);
+		if (smem > MAX_SMEM)
+			return fail(ctx, MTD_ERR_CAPACITY, "map of %d tiles with %d layers does not fit shared memory", T, P.n);
+		static size_t configured = 0;
+		if (smem > configured)
+		{
+			CU(cudaFuncSetAttribute(k_waypoints_small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MAX_SMEM));
+			configured = MAX_SMEM;
+		}
+		const int blocks = P.nmaps < ctx->sms * (smem * 2 <= MAX_SMEM ? 2 : 1) ? P.nmaps : ctx->sms * (smem * 2 <= MAX_SMEM ? 2 : 1);
+		k_waypoints_small<<<blocks, SMALL_THREADS, smem, ctx->stream>>>(P);
+		LAUNCHED();
+		return MTD_OK;
+	}
+
+	// ---- big path -----------------------------------------------------------------------------------
+	int big_prepare(mtd_ctx *ctx)
+	{
+		// derived data for the tiled path: packed edge weights + blocking mask + work-lists
+		CU(ctx->wpack.reserve(ctx->T));
+		CU(ctx->blocked.reserve(ctx->T));
+		ctx->tilesX = (ctx->W + BIG_TS - 1) / BIG_TS;
+		ctx->tilesY = (ctx->H + BIG_TS - 1) / BIG_TS;
+		const size_t nt = (size_t)ctx->tilesX * ctx->tilesY;
+		CU(ctx->list0.reserve(nt));
+		CU(ctx->list1.reserve(nt));
+		CU(ctx->stamp.reserve(nt));
+		CU(ctx->counters.reserve(8));
+		k_edge_weights<<<grid_blocks(ctx, ctx->T, 256), 256, 0, ctx->stream>>>(ctx->W, ctx->H, ctx->elev.p, nullptr, ctx->flags.p, ctx->wpack.p, ctx->blocked.p);
+		LAUNCHED();
+		return MTD_OK;
+	}
+
+	int big_directions(mtd_ctx *ctx, const uint32_t *h_sources, int nsrc, uint32_t extra_blocked, uint32_t *d_tiles, uint32_t *d_dist)
+	{
+		using TSm = TileSmem<BIG_TS>;
+		const size_t smem = sizeof(TSm) * BIG_WARPS;
+		static bool configured = false;
+		if (!configured)
+		{
+			CU(cudaFuncSetAttribute(k_tile_round<BIG_TS, BIG_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+			configured = true;
+		}
+		const size_t nt = (size_t)ctx->tilesX * ctx->tilesY;
+		CU(ctx->sources.reserve((size_t)nsrc));
+		CU(cudaMemcpyAsync(ctx->sources.p, h_sources, (size_t)nsrc * 4, cudaMemcpyHostToDevice, ctx->stream));
+		CU(cudaMemsetAsync(ctx->stamp.p, 0, nt * 4, ctx->stream));
+		CU(cudaMemsetAsync(ctx->counters.p, 0, 8 * 4, ctx->stream));
+		uint8_t one = 1, zero = 0;
+		uint8_t prev_blocked = 0;
+		if (extra_blocked != MTD_M)
+		{
+			CU(cudaMemcpyAsync(&prev_blocked, ctx->blocked.p + extra_blocked, 1, cudaMemcpyDeviceToHost, ctx->stream));
+			CU(cudaStreamSynchronize(ctx->stream));
+			CU(cudaMemcpyAsync(ctx->blocked.p + extra_blocked, &one, 1, cudaMemcpyHostToDevice, ctx->stream));
+		}
+		(void)zero;
+		k_fill_u32<<<grid_blocks(ctx, ctx->T, 256), 256, 0, ctx->stream>>>(d_dist, ctx->T, MTD_INF);
+		LAUNCHED();
+
+		BigParams P;
+		memset(&P, 0, sizeof(P));
+		P.W = ctx->W;
+		P.H = ctx->H;
+		P.y0 = 0;
+		P.y1 = ctx->H;
+		P.tilesX = ctx->tilesX;
+		P.tilesY = ctx->tilesY;
+		P.dist = d_dist;
+		P.wpack = ctx->wpack.p;
+		P.blocked = ctx->blocked.p;
+		P.sources = ctx->sources.p;
+		P.nsrc = nsrc;
+		P.list[0] = ctx->list0.p;
+		P.list[1] = ctx->list1.p;
+		P.count = ctx->counters.p;
+		P.cursor = ctx->counters.p + 2;
+		P.total_active = ctx->counters.p + 3;
+		P.stamp = ctx->stamp.p;
+		P.status = ctx->d_status.p;
+
+		k_big_seed<BIG_TS><<<(nsrc + 127) / 128, 128, 0, ctx->stream>>>(P, extra_blocked);
+		LAUNCHED();
+
+		uint32_t *d_next = nullptr;
+		CU(cudaHostGetDevicePointer((void **)&d_next, &ctx->hflags->next_count, 0));
+		const int ctas_per_sm = (int)(MAX_SMEM / (smem + 1024));
+		const int blocks = ctx->sms * (ctas_per_sm > 0 ? ctas_per_sm : 1);
+		int round = 0;
+		int burst = 4;
+		for (;;)
+		{
+			for (int b = 0; b < burst; b++, round++)
+			{
+				k_tile_round<BIG_TS, BIG_WARPS><<<blocks, BIG_WARPS * 32, smem, ctx->stream>>>(P, round);
+				LAUNCHED();
+				k_round_advance<<<1, 1, 0, ctx->stream>>>(P, round, d_next);
+				LAUNCHED();
+			}
+			CU(cudaStreamSynchronize(ctx->stream));
+			if (ctx->hflags->next_count == 0)
+				break;
+			if (burst < 32)
+				burst *= 2;
+			if (round > 4 * (ctx->tilesX + ctx->tilesY) * 64 + 100000)
+				return fail(ctx, MTD_ERR_CUDA, "tile relaxation did not converge after %d rounds", round);
+		}
+		ctx->last_rounds = (uint32_t)round;
+		if (extra_blocked != MTD_M)
+			CU(cudaMemcpyAsync(ctx->blocked.p + extra_blocked, &prev_blocked, 1, cudaMemcpyHostToDevice, ctx->stream));
+		if (d_tiles)
+		{
+			k_directions<<<grid_blocks(ctx, ctx->T, 256), 256, 0, ctx->stream>>>(ctx->W, ctx->H, 0, ctx->H, d_dist, ctx->wpack.p, nullptr, nullptr, nullptr, d_tiles);
+			LAUNCHED();
+		}
+		if (extra_blocked != MTD_M)
+			CU(cudaStreamSynchronize(ctx->stream)); // prev_blocked lives on this stack frame
+		return MTD_OK;
+	}
+
+	int directions_dev(mtd_ctx *ctx, const uint32_t *sources, int nsrc, uint32_t extra_blocked, uint32_t *d_tiles, uint32_t *d_dist)
+	{
+		if (!ctx->have_grid)
+			return fail(ctx, MTD_ERR_STATE, "no grid uploaded");
+		if (!sources || nsrc < 1)
+			return fail(ctx, MTD_ERR_ARG, "sources must hold at least one tile");
+		for (int i = 0; i < nsrc; i++)
+			if (sources[i] >= ctx->T)
+				return fail(ctx, MTD_ERR_ARG, "source tile %u outside the grid", sources[i]);
+		if (extra_blocked != MTD_M && extra_blocked >= ctx->T)
+			return fail(ctx, MTD_ERR_ARG, "extra_blocked tile outside the grid");
+		if (!d_dist)
+		{
+			CU(ctx->trial_dist.reserve(ctx->T));
+			d_dist = ctx->trial_dist.p;
+		}
+		if (ctx->small && nsrc <= MTD_MAXSRC_SMALL)
+		{
+			CU(ctx->lwp.reserve(64));
+			CU(cudaMemcpyAsync(ctx->lwp.p + 32, sources, (size_t)nsrc * 4, cudaMemcpyHostToDevice, ctx->stream));
+			WaypointsSmallParams P;
+			memset(&P, 0, sizeof(P));
+			P.W = ctx->W;
+			P.H = ctx->H;
+			P.n = 1;
+			P.nmaps = 1;
+			P.nsrc = nsrc;
+			P.elev = ctx->elev.p;
+			P.flags = ctx->flags.p;
+			P.wp = ctx->lwp.p + 32;
+			P.extra_blocked = extra_blocked;
+			P.tiles = d_tiles;
+			P.dist = d_dist;
+			P.status = ctx->d_status.p;
+			return launch_waypoints_small(ctx, P);
+		}
+		return big_directions(ctx, sources, nsrc, extra_blocked, d_tiles, d_dist);
+	}
+
+	LayersView layers_view(mtd_ctx *ctx)
+	{
+		LayersView L;
+		L.W = ctx->W;
+		L.H = ctx->H;
+		L.ox = ctx->ox;
+		L.oy = ctx->oy;
+		L.n = ctx->nlayers;
+		L.elev = ctx->elev.p;
+		L.tiles = ctx->ltiles.p;
+		L.dist = ctx->ldist.p;
+		L.wp = ctx->lwp.p;
+		L.Dtab = ctx->dtab.p;
+		return L;
+	}
+
+	MonstersView monsters_view(mtd_ctx *ctx)
+	{
+		MonstersView M;
+		M.n = ctx->nmon;
+		M.tile = ctx->m_tile.p;
+		M.tileStart = ctx->m_tileStart.p;
+		M.tileEnd = ctx->m_tileEnd.p;
+		M.timeStart = ctx->m_timeStart.p;
+		M.timeEnd = ctx->m_timeEnd.p;
+		M.bits = ctx->m_bits.p;
+		M.timeToArrive = ctx->m_tta.p;
+		M.dotflags = ctx->m_has_dot ? ctx->m_dot.p : nullptr;
+		M.damage = ctx->m_has_damage ? ctx->m_damage.p : nullptr;
+		M.alive = ctx->m_alive.p;
+		return M;
+	}
+
+	int waypoints_dev(mtd_ctx *ctx, const uint32_t *wp_tiles, int n, uint32_t fullpath_cap)
+	{
+		if (!ctx->have_grid)
+			return fail(ctx, MTD_ERR_STATE, "no grid uploaded");
+		if (n < 0 || n > MTD_MAX_WAYPOINTS)
+			return fail(ctx, MTD_ERR_ARG, "waypoint count %d outside [0, %d]", n, MTD_MAX_WAYPOINTS);
+		ctx->nlayers = n;
+		if (n == 0)
+			return MTD_OK; // paths.cpp:113-114
+		for (int i = 0; i < n; i++)
+			if (wp_tiles[i] >= ctx->T)
+				return fail(ctx, MTD_ERR_ARG, "waypoint tile %u outside the grid", wp_tiles[i]);
+		CU(ctx->ltiles.reserve((size_t)n * ctx->T));
+		CU(ctx->ldist.reserve((size_t)n * ctx->T));
+		CU(ctx->lwp.reserve(64));
+		CU(ctx->dtab.reserve(FIND_MAXN * FIND_MAXN));
+		CU(ctx->fp_len.reserve(MTD_MAX_WAYPOINTS));
+		CU(ctx->fp_dist.reserve(MTD_MAX_WAYPOINTS));
+		CU(ctx->agg.reserve(4));
+		ctx->fp_cap = fullpath_cap;
+		if (fullpath_cap)
+			CU(ctx->fp_buf.reserve((size_t)n * fullpath_cap));
+		CU(cudaMemcpyAsync(ctx->lwp.p, wp_tiles, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+		CU(cudaMemsetAsync(ctx->fp_len.p, 0, MTD_MAX_WAYPOINTS * 4, ctx->stream));
+		CU(cudaMemsetAsync(ctx->fp_dist.p, 0, MTD_MAX_WAYPOINTS * 4, ctx->stream));
+		CU(cudaMemsetAsync(ctx->agg.p, 0, 16, ctx->stream));
+		const bool walks = n <= FIND_MAXN;
+		if (ctx->small && small_fits(ctx->W, ctx->H, n))
+		{
+			WaypointsSmallParams P;
+			memset(&P, 0, sizeof(P));
+			P.W = ctx->W;
+			P.H = ctx->H;
+			P.n = n;
+			P.nmaps = 1;
+			P.nsrc = 1;
+			P.elev = ctx->elev.p;
+			P.flags = ctx->flags.p;
+			P.wp = ctx->lwp.p;
+			P.extra_blocked = MTD_M;
+			P.tiles = ctx->ltiles.p;
+			P.dist = ctx->ldist.p;
+			P.fullpath = fullpath_cap ? ctx->fp_buf.p : nullptr;
+			P.cap = fullpath_cap;
+			P.fullpath_len = walks ? ctx->fp_len.p : nullptr;
+			P.full_distance = ctx->fp_dist.p;
+			P.agg = ctx->agg.p;
+			P.status = ctx->d_status.p;
+			int rc = launch_waypoints_small(ctx, P);
+			if (rc)
+				return rc;
+		}
+		else
+		{
+			// large grid: one tiled relaxation per layer (layers are independent; the multi-GPU host shards them).
+			// Full-path walks on large grids are out of scope for this round.
+			for (int l = 0; l < n; l++)
+			{
+				int rc = big_directions(ctx, wp_tiles + l, 1, MTD_M, ctx->ltiles.p + (size_t)l * ctx->T, ctx->ldist.p + (size_t)l * ctx->T);
+				if (rc)
+					return rc;
+			}
+		}
+		if (walks)
+		{
+			k_build_dtab<<<1, 64, 0, ctx->stream>>>(layers_view(ctx), ctx->dtab.p);
+			LAUNCHED();
+		}
+		return MTD_OK;
+	}
+}
+
+// =====================================================================================================
+// lifecycle
+// =====================================================================================================
+extern "C" int mtd_version(void)
+{
+	return 100;
+}
+
+extern "C" int mtd_create(mtd_ctx **out, int device, void *stream)
+{
+	if (!out)
+		return MTD_ERR_ARG;
+	*out = nullptr;
+	int ndev = 0;
+	if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0 || device < 0 || device >= ndev)
+		return MTD_ERR_CUDA; // no CPU fallback by design
+	mtd_ctx *ctx = new (std::nothrow) mtd_ctx();
+	if (!ctx)
+		return MTD_ERR_NOMEM;
+	ctx->device = device;
+	if (cudaSetDevice(device) != cudaSuccess)
+	{
+		delete ctx;
+		return MTD_ERR_CUDA;
+	}
+	cudaDeviceGetAttribute(&ctx->sms, cudaDevAttrMultiProcessorCount, device);
+	if (stream)
+		ctx->stream = (cudaStream_t)stream;
+	else
+	{
+		if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess)
+		{
+			delete ctx;
+			return MTD_ERR_CUDA;
+		}
+		ctx->own_stream = true;
+	}
+	if (cudaHostAlloc((void **)&ctx->hflags, sizeof(HostFlags), cudaHostAllocMapped) != cudaSuccess || ctx->d_status.reserve(1) != cudaSuccess || ctx->d_damage.reserve(1) != cudaSuccess || ctx->d_small.reserve(8) != cudaSuccess || ctx->d_trial.reserve(1) != cudaSuccess)
+	{
+		mtd_destroy(ctx);
+		return MTD_ERR_CUDA;
+	}
+	memset(ctx->hflags, 0, sizeof(HostFlags));
+	cudaMemsetAsync(ctx->d_status.p, 0, sizeof(int), ctx->stream);
+	*out = ctx;
+	return MTD_OK;
+}
+
+extern "C" void mtd_destroy(mtd_ctx *ctx)
+{
+	if (!ctx)
+		return;
+	DeviceGuard g(ctx->device);
+	cudaStreamSynchronize(ctx->stream);
+	ctx->elev.release();
+	ctx->flags.release();
+	ctx->wpack.release();
+	ctx->blocked.release();
+	ctx->list0.release();
+	ctx->list1.release();
+	ctx->stamp.release();
+	ctx->counters.release();
+	ctx->sources.release();
+	ctx->ltiles.release();
+	ctx->ldist.release();
+	ctx->lwp.release();
+	ctx->dtab.release();
+	ctx->fp_buf.release();
+	ctx->fp_len.release();
+	ctx->fp_dist.release();
+	ctx->agg.release();
+	ctx->trial_dist.release();
+	ctx->m_tile.release();
+	ctx->m_tileStart.release();
+	ctx->m_tileEnd.release();
+	ctx->m_timeStart.release();
+	ctx->m_timeEnd.release();
+	ctx->m_bits.release();
+	ctx->m_tta.release();
+	ctx->m_damage.release();
+	ctx->m_dot.release();
+	ctx->m_alive.release();
+	ctx->m_pos.release();
+	ctx->scratch_u32a.release();
+	ctx->scratch_u32b.release();
+	ctx->scratch_u32c.release();
+	ctx->scratch_u32d.release();
+	ctx->scratch_f.release();
+	ctx->d_status.release();
+	ctx->d_damage.release();
+	ctx->d_small.release();
+	ctx->d_trial.release();
+	if (ctx->hflags)
+		cudaFreeHost(ctx->hflags);
+	if (ctx->own_stream && ctx->stream)
+		cudaStreamDestroy(ctx->stream);
+	delete ctx;
+}
+
+extern "C" const char *mtd_last_error(const mtd_ctx *ctx)
+{
+	return ctx ? ctx->err : "null context";
+}
+
+extern "C" int mtd_synchronize(mtd_ctx *ctx)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	return sync_and_status(ctx);
+}
+
+extern "C" uint64_t mtd_launch_count(const mtd_ctx *ctx)
+{
+	return ctx ? ctx->launches : 0;
+}
+
+// =====================================================================================================
+// grid
+// =====================================================================================================
+static int grid_common(mtd_ctx *ctx, int32_t W, int32_t H, int32_t ox, int32_t oy, const int16_t *elev, const uint16_t *flags, cudaMemcpyKind kind)
+{
+	if (W < 1 || H < 1 || !elev || !flags)
+		return fail(ctx, MTD_ERR_ARG, "grid needs W, H >= 1 and non-null elev/flags");
+	if ((uint64_t)W * (uint64_t)H >= 0xFFFFFFFFull)
+		return fail(ctx, MTD_ERR_ARG, "grid too large for uint32 tile indices");
+	ctx->have_grid = false;
+	ctx->nlayers = 0;
+	ctx->W = W;
+	ctx->H = H;
+	ctx->ox = ox;
+	ctx->oy = oy;
+	ctx->T = (size_t)W * H;
+	CU(ctx->elev.reserve(ctx->T));
+	CU(ctx->flags.reserve(ctx->T));
+	CU(cudaMemcpyAsync(ctx->elev.p, elev, ctx->T * 2, kind, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->flags.p, flags, ctx->T * 2, kind, ctx->stream));
+	ctx->small = small_fits(W, H, 1);
+	if (!ctx->small)
+	{
+		int rc = big_prepare(ctx);
+		if (rc)
+			return rc;
+	}
+	if (kind == cudaMemcpyHostToDevice)
+		CU(cudaStreamSynchronize(ctx->stream)); // caller may reuse its host arrays (pageable memory is staged, but be explicit)
+	ctx->have_grid = true;
+	return MTD_OK;
+}
+
+extern "C" int mtd_grid_upload(mtd_ctx *ctx, int32_t W, int32_t H, int32_t ox, int32_t oy, const int16_t *elev, const uint16_t *flags)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	return grid_common(ctx, W, H, ox, oy, elev, flags, cudaMemcpyHostToDevice);
+}
+
+extern "C" int mtd_grid_upload_dev(mtd_ctx *ctx, int32_t W, int32_t H, int32_t ox, int32_t oy, const int16_t *d_elev, const uint16_t *d_flags)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	return grid_common(ctx, W, H, ox, oy, d_elev, d_flags, cudaMemcpyDeviceToDevice);
+}
+
+extern "C" int mtd_grid_set_flags(mtd_ctx *ctx, uint32_t tile, uint16_t flags)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (!ctx->have_grid)
+		return fail(ctx, MTD_ERR_STATE, "no grid uploaded");
+	if (tile >= ctx->T)
+		return fail(ctx, MTD_ERR_ARG, "tile outside the grid");
+	ctx->hflags->spawn[0] = flags; // staged in pinned memory so the async copy has a stable source
+	CU(cudaMemcpyAsync(ctx->flags.p + tile, &ctx->hflags->spawn[0], 2, cudaMemcpyHostToDevice, ctx->stream));
+	if (!ctx->small)
+	{
+		ctx->hflags->spawn[1] = (flags & F_BLOCKING) ? 1u : 0u;
+		CU(cudaMemcpyAsync(ctx->blocked.p + tile, &ctx->hflags->spawn[1], 1, cudaMemcpyHostToDevice, ctx->stream));
+	}
+	CU(cudaStreamSynchronize(ctx->stream));
+	return MTD_OK;
+}
+
+extern "C" int mtd_neighbor_distances(mtd_ctx *ctx, const uint32_t *a, const uint32_t *b, int32_t n, uint32_t *out)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (!ctx->have_grid)
+		return fail(ctx, MTD_ERR_STATE, "no grid uploaded");
+	if (n < 0 || (n && (!a || !b || !out)))
+		return fail(ctx, MTD_ERR_ARG, "bad arguments");
+	if (n == 0)
+		return MTD_OK;
+	for (int i = 0; i < n; i++)
+		if (a[i] >= ctx->T || b[i] >= ctx->T)
+			return fail(ctx, MTD_ERR_ARG, "tile outside the grid");
+	CU(ctx->scratch_u32a.reserve(n));
+	CU(ctx->scratch_u32b.reserve(n));
+	CU(ctx->scratch_u32c.reserve(n));
+	CU(cudaMemcpyAsync(ctx->scratch_u32a.p, a, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->scratch_u32b.p, b, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+	k_neighbor_distances<<<(n + 255) / 256, 256, 0, ctx->stream>>>(ctx->W, ctx->ox, ctx->oy, ctx->elev.p, ctx->scratch_u32a.p, ctx->scratch_u32b.p, n, ctx->scratch_u32c.p);
+	LAUNCHED();
+	CU(cudaMemcpyAsync(out, ctx->scratch_u32c.p, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	return MTD_OK;
+}
+
+extern "C" int mtd_edge_weights(mtd_ctx *ctx, uint32_t *right, uint32_t *down)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (!ctx->have_grid)
+		return fail(ctx, MTD_ERR_STATE, "no grid uploaded");
+	if (!right || !down)
+		return fail(ctx, MTD_ERR_ARG, "null output");
+	CU(ctx->scratch_u32a.reserve(ctx->T));
+	CU(ctx->scratch_u32b.reserve(ctx->T));
+	k_unpack_weights<<<grid_blocks(ctx, ctx->T, 256), 256, 0, ctx->stream>>>(ctx->W, ctx->H, ctx->elev.p, ctx->scratch_u32a.p, ctx->scratch_u32b.p);
+	LAUNCHED();
+	CU(cudaMemcpyAsync(right, ctx->scratch_u32a.p, ctx->T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaMemcpyAsync(down, ctx->scratch_u32b.p, ctx->T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	return MTD_OK;
+}
+
+// =====================================================================================================
+// Directions::update
+// =====================================================================================================
+extern "C" int mtd_directions_update_dev(mtd_ctx *ctx, const uint32_t *sources, int32_t nsrc, uint32_t extra_blocked, uint32_t *d_tiles, uint32_t *d_dist)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	return directions_dev(ctx, sources, nsrc, extra_blocked, d_tiles, d_dist);
+}
+
+extern "C" int mtd_directions_update(mtd_ctx *ctx, const uint32_t *sources, int32_t nsrc, uint32_t extra_blocked, uint32_t *tiles_out, uint32_t *dist_out)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (!ctx->have_grid)
+		return fail(ctx, MTD_ERR_STATE, "no grid uploaded");
+	CU(ctx->scratch_u32a.reserve(ctx->T));
+	CU(ctx->scratch_u32b.reserve(ctx->T));
+	int rc = directions_dev(ctx, sources, nsrc, extra_blocked, tiles_out ? ctx->scratch_u32a.p : nullptr, ctx->scratch_u32b.p);
+	if (rc)
+		return rc;
+	if (tiles_out)
+		CU(cudaMemcpyAsync(tiles_out, ctx->scratch_u32a.p, ctx->T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (dist_out)
+		CU(cudaMemcpyAsync(dist_out, ctx->scratch_u32b.p, ctx->T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	return sync_and_status(ctx);
+}
+
+// =====================================================================================================
+// Waypoints::update / find
+// =====================================================================================================
+extern "C" int mtd_waypoints_update_dev(mtd_ctx *ctx, const uint32_t *wp_tiles, int32_t n)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (n > 0 && !wp_tiles)
+		return fail(ctx, MTD_ERR_ARG, "null waypoint list");
+	return waypoints_dev(ctx, wp_tiles, n, ctx->fp_cap ? ctx->fp_cap : 4096u);
+}
+
+extern "C" int mtd_waypoints_update(mtd_ctx *ctx, const uint32_t *wp_tiles, int32_t n, uint32_t *tiles_out, uint32_t *dist_out, uint32_t *fullpath_buf, uint32_t fullpath_cap, uint32_t *fullpath_len, uint32_t *full_distance, uint32_t *agg3)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (n > 0 && !wp_tiles)
+		return fail(ctx, MTD_ERR_ARG, "null waypoint list");
+	int rc = waypoints_dev(ctx, wp_tiles, n, fullpath_buf ? fullpath_cap : 0u);
+	if (rc || n == 0)
+		return rc;
+	if (tiles_out)
+		CU(cudaMemcpyAsync(tiles_out, ctx->ltiles.p, (size_t)n * ctx->T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (dist_out)
+		CU(cudaMemcpyAsync(dist_out, ctx->ldist.p, (size_t)n * ctx->T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (fullpath_buf && fullpath_cap)
+		CU(cudaMemcpyAsync(fullpath_buf, ctx->fp_buf.p, (size_t)n * fullpath_cap * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (fullpath_len)
+		CU(cudaMemcpyAsync(fullpath_len, ctx->fp_len.p, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (full_distance)
+		CU(cudaMemcpyAsync(full_distance, ctx->fp_dist.p, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (agg3)
+		CU(cudaMemcpyAsync(agg3, ctx->agg.p, 12, cudaMemcpyDeviceToHost, ctx->stream));
+	return sync_and_status(ctx);
+}
+
+extern "C" int mtd_waypoints_layers_dev(mtd_ctx *ctx, uint32_t **d_tiles, uint32_t **d_dist)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	if (ctx->nlayers <= 0)
+		return fail(ctx, MTD_ERR_STATE, "no resident layers");
+	if (d_tiles)
+		*d_tiles = ctx->ltiles.p;
+	if (d_dist)
+		*d_dist = ctx->ldist.p;
+	return MTD_OK;
+}
+
+extern "C" int mtd_waypoints_find(mtd_ctx *ctx, const uint32_t *pos, const uint32_t *bits, int32_t nq, uint32_t *tile_out, uint32_t *dist_out)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (ctx->nlayers <= 0 || ctx->nlayers > FIND_MAXN)
+		return fail(ctx, MTD_ERR_STATE, "find needs 1..%d resident layers", FIND_MAXN);
+	if (nq < 0 || (nq && (!pos || !bits || !tile_out || !dist_out)))
+		return fail(ctx, MTD_ERR_ARG, "bad arguments");
+	if (nq == 0)
+		return MTD_OK;
+	for (int i = 0; i < nq; i++)
+		if (pos[i] >= ctx->T)
+			return fail(ctx, MTD_ERR_ARG, "position outside the grid");
+	CU(ctx->scratch_u32a.reserve(nq));
+	CU(ctx->scratch_u32b.reserve(nq));
+	CU(ctx->scratch_u32c.reserve(nq));
+	CU(ctx->scratch_u32d.reserve(nq));
+	CU(cudaMemcpyAsync(ctx->scratch_u32a.p, pos, (size_t)nq * 4, cudaMemcpyHostToDevice, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->scratch_u32b.p, bits, (size_t)nq * 4, cudaMemcpyHostToDevice, ctx->stream));
+	k_find_batch<<<(nq + 127) / 128, 128, 0, ctx->stream>>>(layers_view(ctx), ctx->scratch_u32a.p, ctx->scratch_u32b.p, nq, ctx->scratch_u32c.p, ctx->scratch_u32d.p);
+	LAUNCHED();
+	CU(cudaMemcpyAsync(tile_out, ctx->scratch_u32c.p, (size_t)nq * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaMemcpyAsync(dist_out, ctx->scratch_u32d.p, (size_t)nq * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	return MTD_OK;
+}
+
+extern "C" int mtd_placing_blocks(mtd_ctx *ctx, uint32_t candidate, int32_t *blocked_out)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (!blocked_out)
+		return fail(ctx, MTD_ERR_ARG, "null output");
+	if (ctx->nlayers <= 0)
+		return fail(ctx, MTD_ERR_STATE, "placing_blocks needs resident waypoints (call mtd_waypoints_update first)");
+	if (candidate >= ctx->T)
+		return fail(ctx, MTD_ERR_ARG, "candidate outside the grid");
+	// the trial source is waypoint 0 (buildingsPlacement.cpp:27); its tile is mirrored on the host in hflags->spawn[2]
+	uint32_t src;
+	CU(cudaMemcpyAsync(&ctx->hflags->spawn[2], ctx->lwp.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	src = ctx->hflags->spawn[2];
+	CU(ctx->trial_dist.reserve(ctx->T));
+	int rc = directions_dev(ctx, &src, 1, candidate, nullptr, ctx->trial_dist.p);
+	if (rc)
+		return rc;
+	CU(cudaMemsetAsync(ctx->d_trial.p, 0, sizeof(int), ctx->stream));
+	const int nthreads = ctx->nmon > ctx->nlayers ? ctx->nmon : ctx->nlayers;
+	k_trial_check<<<(nthreads + 255) / 256, 256, 0, ctx->stream>>>(ctx->trial_dist.p, ctx->lwp.p, ctx->nlayers, ctx->m_tile.p, ctx->m_alive.p, ctx->nmon, ctx->d_trial.p);
+	LAUNCHED();
+	CU(cudaMemcpyAsync(&ctx->hflags->trial_blocked, ctx->d_trial.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+	rc = sync_and_status(ctx);
+	*blocked_out = ctx->hflags->trial_blocked;
+	return rc;
+}
+
+// =====================================================================================================
+// procedural generator
+// =====================================================================================================
+static int mapgen_dev(mtd_ctx *ctx, const mtd_mapgen_params *p, uint64_t s1, uint64_t s2, int32_t first, int32_t nmaps, int16_t *d_elev, uint16_t *d_flags, uint32_t *d_wp, uint32_t *d_tiles, uint32_t *d_dist, uint32_t *d_fullpath, uint32_t *d_fplen, uint32_t *d_fdist, uint32_t *d_agg)
+{
+	if (!p || p->W < 1 || p->H < 1 || p->nwp < 0 || p->nwp > MTD_MAX_WAYPOINTS || nmaps < 0)
+		return fail(ctx, MTD_ERR_ARG, "bad mapgen parameters");
+	if (nmaps == 0)
+		return MTD_OK;
+	if (!d_elev || !d_flags || !d_wp)
+		return fail(ctx, MTD_ERR_ARG, "elev, flags and wp_tiles outputs are required");
+	const int T = p->W * p->H;
+	if (p->W > 256 || p->H > 256 || T >= 65536 || mapgen_grid_smem(T) > MAX_SMEM || !small_fits(p->W, p->H, p->nwp > 0 ? p->nwp : 1))
+		return fail(ctx, MTD_ERR_CAPACITY, "procedural maps must fit one CTA's shared memory (reference size is 101x101)");
+	static bool configured = false;
+	if (!configured)
+	{
+		CU(cudaFuncSetAttribute(k_mapgen_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MAX_SMEM));
+		configured = true;
+	}
+	MapgenGridParams G;
+	memset(&G, 0, sizeof(G));
+	G.W = p->W;
+	G.H = p->H;
+	G.ox = p->ox;
+	G.oy = p->oy;
+	G.radius = p->radius;
+	G.nwp = p->nwp;
+	G.s1 = s1;
+	G.s2 = s2;
+	G.first = first;
+	G.nmaps = nmaps;
+	G.elev = d_elev;
+	G.flags = d_flags;
+	G.wp_tiles = d_wp;
+	G.status = ctx->d_status.p;
+	const size_t gsm = mapgen_grid_smem(T);
+	const int per_sm = (int)(MAX_SMEM / (gsm + 1024)) > 0 ? (int)(MAX_SMEM / (gsm + 1024)) : 1;
+	const int gblocks = nmaps < ctx->sms * per_sm ? nmaps : ctx->sms * per_sm;
+	k_mapgen_grid<<<gblocks, 512, gsm, ctx->stream>>>(G);
+	LAUNCHED();
+	if (p->nwp == 0)
+		return MTD_OK;
+
+	WaypointsSmallParams P;
+	memset(&P, 0, sizeof(P));
+	P.W = p->W;
+	P.H = p->H;
+	P.n = p->nwp;
+	P.nmaps = nmaps;
+	P.nsrc = 1;
+	P.elev = d_elev;
+	P.flags = d_flags;
+	P.wp = d_wp;
+	P.extra_blocked = MTD_M;
+	P.tiles = d_tiles;
+	P.dist = d_dist;
+	P.fullpath = d_fullpath;
+	P.cap = d_fullpath ? p->fullpath_cap : 0u;
+	P.fullpath_len = p->nwp <= FIND_MAXN ? d_fplen : nullptr;
+	P.full_distance = d_fdist;
+	P.agg = d_agg;
+	P.status = ctx->d_status.p;
+	if (P.fullpath_len && (!d_fdist || !d_agg))
+		return fail(ctx, MTD_ERR_ARG, "fullpath_len, full_distance and agg outputs go together");
+	if (p->nwp > SMALL_MAX_RESIDENT && P.fullpath_len && !d_dist)
+		return fail(ctx, MTD_ERR_ARG, "more than %d waypoints need the dist output for the path walk", SMALL_MAX_RESIDENT);
+	return launch_waypoints_small(ctx, P);
+}
+
+extern "C" int mtd_mapgen_batch_dev(mtd_ctx *ctx, const mtd_mapgen_params *p, uint64_t s1, uint64_t s2, int32_t first, int32_t nmaps, int16_t *d_elev, uint16_t *d_flags, uint32_t *d_wp_tiles, uint32_t *d_tiles, uint32_t *d_dist, uint32_t *d_fullpath, uint32_t *d_fullpath_len, uint32_t *d_full_distance, uint32_t *d_agg)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	return mapgen_dev(ctx, p, s1, s2, first, nmaps, d_elev, d_flags, d_wp_tiles, d_tiles, d_dist, d_fullpath, d_fullpath_len, d_full_distance, d_agg);
+}
+
+extern "C" int mtd_mapgen_batch(mtd_ctx *ctx, const mtd_mapgen_params *p, uint64_t s1, uint64_t s2, int32_t first, int32_t nmaps, int16_t *elev, uint16_t *flags, uint32_t *wp_tiles, uint32_t *tiles, uint32_t *dist, uint32_t *fullpath, uint32_t *fullpath_len, uint32_t *full_distance, uint32_t *agg)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (!p || nmaps < 0)
+		return fail(ctx, MTD_ERR_ARG, "bad mapgen parameters");
+	const size_t T = (size_t)p->W * p->H;
+	const int n = p->nwp;
+	const size_t cap = fullpath ? p->fullpath_cap : 0;
+	// chunked so the device staging stays bounded (layers are 8 bytes per tile per waypoint)
+	const int chunk = 256;
+	DevBuf<int16_t> d_elev;
+	DevBuf<uint16_t> d_flags;
+	DevBuf<uint32_t> d_wp, d_tiles, d_dist, d_fp, d_fplen, d_fdist, d_agg;
+	int rc = MTD_OK;
+	auto cleanup = [&]()
+	{
+		d_elev.release();
+		d_flags.release();
+		d_wp.release();
+		d_tiles.release();
+		d_dist.release();
+		d_fp.release();
+		d_fplen.release();
+		d_fdist.release();
+		d_agg.release();
+	};
+#define CUX(call)                                                                                   \
+	do                                                                                              \
+	{                                                                                               \
+		cudaError_t e__ = (call);                                                                   \
+		if (e__ != cudaSuccess)                                                                     \
+		{                                                                                           \
+			cleanup();                                                                              \
+			return fail(ctx, MTD_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e__));        \
+		}                                                                                           \
+	} while (0)
+	CUX(d_elev.reserve(chunk * T));
+	CUX(d_flags.reserve(chunk * T));
+	CUX(d_wp.reserve((size_t)chunk * (n ? n : 1)));
+	if (n)
+	{
+		if (tiles)
+			CUX(d_tiles.reserve((size_t)chunk * n * T));
+		if (dist || n > SMALL_MAX_RESIDENT)
+			CUX(d_dist.reserve((size_t)chunk * n * T));
+		if (cap)
+			CUX(d_fp.reserve((size_t)chunk * n * cap));
+		CUX(d_fplen.reserve((size_t)chunk * n));
+		CUX(d_fdist.reserve((size_t)chunk * n));
+		CUX(d_agg.reserve((size_t)chunk * 3));
+	}
+	for (int done = 0; done < nmaps && rc == MTD_OK; done += chunk)
+	{
+		const int m = nmaps - done < chunk ? nmaps - done : chunk;
+		rc = mapgen_dev(ctx, p, s1, s2, first + done, m, d_elev.p, d_flags.p, d_wp.p, d_tiles.p, d_dist.p, d_fp.p, d_fplen.p, d_fdist.p, d_agg.p);
+		if (rc)
+			break;
+		if (elev)
+			CUX(cudaMemcpyAsync(elev + (size_t)done * T, d_elev.p, (size_t)m * T * 2, cudaMemcpyDeviceToHost, ctx->stream));
+		if (flags)
+			CUX(cudaMemcpyAsync(flags + (size_t)done * T, d_flags.p, (size_t)m * T * 2, cudaMemcpyDeviceToHost, ctx->stream));
+		if (wp_tiles && n)
+			CUX(cudaMemcpyAsync(wp_tiles + (size_t)done * n, d_wp.p, (size_t)m * n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		if (tiles && n)
+			CUX(cudaMemcpyAsync(tiles + (size_t)done * n * T, d_tiles.p, (size_t)m * n * T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		if (dist && n)
+			CUX(cudaMemcpyAsync(dist + (size_t)done * n * T, d_dist.p, (size_t)m * n * T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		if (fullpath && cap && n)
+			CUX(cudaMemcpyAsync(fullpath + (size_t)done * n * cap, d_fp.p, (size_t)m * n * cap * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		if (fullpath_len && n)
+			CUX(cudaMemcpyAsync(fullpath_len + (size_t)done * n, d_fplen.p, (size_t)m * n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		if (full_distance && n)
+			CUX(cudaMemcpyAsync(full_distance + (size_t)done * n, d_fdist.p, (size_t)m * n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		if (agg && n)
+			CUX(cudaMemcpyAsync(agg + (size_t)done * 3, d_agg.p, (size_t)m * 3 * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		rc = sync_and_status(ctx);
+	}
+#undef CUX
+	cleanup();
+	return rc;
+}
+
+__global__ void k_elevation_samples(uint64_t s1, uint64_t s2, const float *xy, int n, float *out)
+{
+	__shared__ float2 grad[128];
+	__shared__ noise::ElevationParams ep;
+	noise::fill_gradients(grad);
+	if (threadIdx.x == 0)
+	{
+		Rng g;
+		g.s0 = s1;
+		g.s1 = s2;
+		const float r1 = g.chance();
+		const float r2 = g.chance();
+		ep.off_x = __fmul_rn(r1, 1000.0f);
+		ep.off_y = __fmul_rn(r2, 1000.0f);
+		ep.seed = (int)(uint32_t)g.next();
+		ep.bounding = noise::fractal_bounding(4, 0.55f);
+	}
+	__syncthreads();
+	const noise::ElevationParams lp = ep;
+	for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+		out[i] = noise::elevation(grad, lp, xy[i * 2 + 0], xy[i * 2 + 1]);
+}
+
+extern "C" int mtd_elevation_samples(mtd_ctx *ctx, uint64_t s1, uint64_t s2, const float *xy, int32_t n, float *out)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (n < 0 || (n && (!xy || !out)))
+		return fail(ctx, MTD_ERR_ARG, "bad arguments");
+	if (n == 0)
+		return MTD_OK;
+	CU(ctx->scratch_f.reserve((size_t)n * 3));
+	CU(cudaMemcpyAsync(ctx->scratch_f.p, xy, (size_t)n * 8, cudaMemcpyHostToDevice, ctx->stream));
+	k_elevation_samples<<<grid_blocks(ctx, n, 256), 256, 0, ctx->stream>>>(s1, s2, ctx->scratch_f.p, n, ctx->scratch_f.p + (size_t)n * 2);
+	LAUNCHED();
+	CU(cudaMemcpyAsync(out, ctx->scratch_f.p + (size_t)n * 2, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	return MTD_OK;
+}
+
+// =====================================================================================================
+// monsters
+// =====================================================================================================
+extern "C" int mtd_monsters_upload(mtd_ctx *ctx, int32_t n, const uint32_t *tile, const uint32_t *tileStart, const uint32_t *tileEnd, const uint32_t *timeStart, const uint32_t *timeEnd, const uint32_t *bits, const uint32_t *timeToArrive, const uint8_t *dotflags, const uint32_t *damage, const uint8_t *alive)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (n < 0 || (n && (!tile || !tileStart || !tileEnd || !timeStart || !timeEnd || !bits || !timeToArrive)))
+		return fail(ctx, MTD_ERR_ARG, "bad monster arrays");
+	ctx->nmon = n;
+	if (n == 0)
+		return MTD_OK;
+	const size_t N = (size_t)n;
+	CU(ctx->m_tile.reserve(N));
+	CU(ctx->m_tileStart.reserve(N));
+	CU(ctx->m_tileEnd.reserve(N));
+	CU(ctx->m_timeStart.reserve(N));
+	CU(ctx->m_timeEnd.reserve(N));
+	CU(ctx->m_bits.reserve(N));
+	CU(ctx->m_tta.reserve(N));
+	CU(ctx->m_damage.reserve(N));
+	CU(ctx->m_dot.reserve(N));
+	CU(ctx->m_alive.reserve(N));
+	CU(cudaMemcpyAsync(ctx->m_tile.p, tile, N * 4, cudaMemcpyHostToDevice, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->m_tileStart.p, tileStart, N * 4, cudaMemcpyHostToDevice, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->m_tileEnd.p, tileEnd, N * 4, cudaMemcpyHostToDevice, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->m_timeStart.p, timeStart, N * 4, cudaMemcpyHostToDevice, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->m_timeEnd.p, timeEnd, N * 4, cudaMemcpyHostToDevice, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->m_bits.p, bits, N * 4, cudaMemcpyHostToDevice, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->m_tta.p, timeToArrive, N * 4, cudaMemcpyHostToDevice, ctx->stream));
+	ctx->m_has_dot = dotflags != nullptr;
+	ctx->m_has_damage = damage != nullptr;
+	if (dotflags)
+		CU(cudaMemcpyAsync(ctx->m_dot.p, dotflags, N, cudaMemcpyHostToDevice, ctx->stream));
+	if (damage)
+		CU(cudaMemcpyAsync(ctx->m_damage.p, damage, N * 4, cudaMemcpyHostToDevice, ctx->stream));
+	if (alive)
+		CU(cudaMemcpyAsync(ctx->m_alive.p, alive, N, cudaMemcpyHostToDevice, ctx->stream));
+	else
+		CU(cudaMemsetAsync(ctx->m_alive.p, 1, N, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	return MTD_OK;
+}
+
+extern "C" int mtd_monsters_download(mtd_ctx *ctx, uint32_t *tile, uint32_t *tileStart, uint32_t *tileEnd, uint32_t *timeStart, uint32_t *timeEnd, uint32_t *bits, uint8_t *alive)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	const size_t N = (size_t)ctx->nmon;
+	if (N == 0)
+		return MTD_OK;
+	if (tile)
+		CU(cudaMemcpyAsync(tile, ctx->m_tile.p, N * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (tileStart)
+		CU(cudaMemcpyAsync(tileStart, ctx->m_tileStart.p, N * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (tileEnd)
+		CU(cudaMemcpyAsync(tileEnd, ctx->m_tileEnd.p, N * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (timeStart)
+		CU(cudaMemcpyAsync(timeStart, ctx->m_timeStart.p, N * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (timeEnd)
+		CU(cudaMemcpyAsync(timeEnd, ctx->m_timeEnd.p, N * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (bits)
+		CU(cudaMemcpyAsync(bits, ctx->m_bits.p, N * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (alive)
+		CU(cudaMemcpyAsync(alive, ctx->m_alive.p, N, cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	return MTD_OK;
+}
+
+static int monsters_tick_dev(mtd_ctx *ctx, uint32_t gameTime)
+{
+	if (ctx->nlayers <= 0 || ctx->nlayers > FIND_MAXN)
+		return fail(ctx, MTD_ERR_STATE, "monster tick needs 1..%d resident waypoint layers", FIND_MAXN);
+	CU(cudaMemsetAsync(ctx->d_damage.p, 0, 8, ctx->stream));
+	CU(cudaMemsetAsync(ctx->d_small.p, 0, 4, ctx->stream));
+	if (ctx->nmon == 0)
+		return MTD_OK;
+	k_monsters_tick<<<(ctx->nmon + 255) / 256, 256, 0, ctx->stream>>>(layers_view(ctx), monsters_view(ctx), gameTime, ctx->d_damage.p, ctx->d_small.p);
+	LAUNCHED();
+	return MTD_OK;
+}
+
+extern "C" int mtd_monsters_tick_dev(mtd_ctx *ctx, uint32_t gameTime)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	return monsters_tick_dev(ctx, gameTime);
+}
+
+extern "C" int mtd_monsters_tick(mtd_ctx *ctx, uint32_t gameTime, int64_t *damage_out, uint32_t *alive_out)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	int rc = monsters_tick_dev(ctx, gameTime);
+	if (rc)
+		return rc;
+	CU(cudaMemcpyAsync(&ctx->hflags->damage, ctx->d_damage.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaMemcpyAsync(&ctx->hflags->alive, ctx->d_small.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	if (damage_out)
+		*damage_out = (int64_t)ctx->hflags->damage;
+	if (alive_out)
+		*alive_out = ctx->hflags->alive;
+	return MTD_OK;
+}
+
+extern "C" int mtd_monsters_positions_dev(mtd_ctx *ctx, uint32_t gameTime, float *d_out3n)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (!ctx->have_grid)
+		return fail(ctx, MTD_ERR_STATE, "no grid uploaded");
+	if (ctx->nmon == 0)
+		return MTD_OK;
+	if (!d_out3n)
+		return fail(ctx, MTD_ERR_ARG, "null output");
+	k_monsters_positions<<<(ctx->nmon + 255) / 256, 256, 0, ctx->stream>>>(layers_view(ctx), monsters_view(ctx), gameTime, d_out3n);
+	LAUNCHED();
+	return MTD_OK;
+}
+
+extern "C" int mtd_monsters_positions(mtd_ctx *ctx, uint32_t gameTime, float *out3n)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	{
+		std::lock_guard<std::mutex> lk(ctx->mu);
+		DeviceGuard g(ctx->device);
+		if (ctx->nmon == 0)
+			return MTD_OK;
+		if (!out3n)
+			return fail(ctx, MTD_ERR_ARG, "null output");
+		CU(ctx->m_pos.reserve((size_t)ctx->nmon * 3));
+	}
+	int rc = mtd_monsters_positions_dev(ctx, gameTime, ctx->m_pos.p);
+	if (rc)
+		return rc;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	CU(cudaMemcpyAsync(out3n, ctx->m_pos.p, (size_t)ctx->nmon * 12, cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	return MTD_OK;
+}
+
+extern "C" int mtd_monster_spawn(mtd_ctx *ctx, uint32_t gameTime, float speed, uint32_t *out3)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (ctx->nlayers <= 0 || ctx->nlayers > FIND_MAXN)
+		return fail(ctx, MTD_ERR_STATE, "spawn needs 1..%d resident waypoint layers", FIND_MAXN);
+	if (!out3)
+		return fail(ctx, MTD_ERR_ARG, "null output");
+	// minDistanceSpawner is agg[2] of the last update
+	CU(cudaMemcpyAsync(&ctx->hflags->spawn[0], ctx->agg.p + 2, 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	const uint32_t spawner = ctx->hflags->spawn[0];
+	k_monster_spawn<<<1, 1, 0, ctx->stream>>>(layers_view(ctx), spawner, gameTime, speed, ctx->d_small.p + 4);
+	LAUNCHED();
+	CU(cudaMemcpyAsync(ctx->hflags->spawn, ctx->d_small.p + 4, 12, cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	memcpy(out3, ctx->hflags->spawn, 12);
+	return MTD_OK;
+}

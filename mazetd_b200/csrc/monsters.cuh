@@ -1,0 +1,190 @@
+// monsters.cuh -- per-tick monster steering on SoA state (sources/game/monsters.cpp:55-99), the position lerp
+// (sources/game/game.cpp:15-21), spawn state (sources/game/monsterSpawning.cpp:205-216), batched Waypoints::find
+// (sources/map/paths.cpp:141-169) and the reachability scan of placingBuildingBlocksMonsters
+// (sources/player/buildingsPlacement.cpp:30-41). One thread per monster / query; all gathers go to the resident
+// distance layers in HBM/L2.
+#pragma once
+
+#include "common.cuh"
+#include "sssp_warp.cuh"
+
+namespace mtd
+{
+	struct LayersView
+	{
+		int W, H, ox, oy, n;
+		const int16_t *elev;
+		const uint32_t *tiles; // [n][T]
+		const uint32_t *dist;  // [n][T]
+		const uint32_t *wp;    // [n]
+		const uint32_t *Dtab;  // [8][8] inter-waypoint table D[a][b] = dist_b[wp_a]
+	};
+
+	struct MonstersView
+	{
+		int n;
+		uint32_t *tile, *tileStart, *tileEnd, *timeStart, *timeEnd, *bits;
+		const uint32_t *timeToArrive;
+		const uint8_t *dotflags;
+		const uint32_t *damage;
+		uint8_t *alive;
+	};
+
+	__global__ void k_build_dtab(LayersView L, uint32_t *Dtab)
+	{
+		const int i = threadIdx.x;
+		const size_t T = (size_t)L.W * L.H;
+		if (i < L.n * L.n)
+		{
+			const int a = i / L.n, b = i % L.n;
+			Dtab[a * FIND_MAXN + b] = L.dist[(size_t)b * T + L.wp[a]];
+		}
+	}
+
+	__device__ __forceinline__ void device_find(const LayersView &L, uint32_t pos, uint32_t bits, uint32_t &tile, uint32_t &distance)
+	{
+		const size_t T = (size_t)L.W * L.H;
+		const FindResult fr = find_best(L.n, bits, L.Dtab, [&](uint32_t i) { return L.dist[(size_t)i * T + pos]; });
+		distance = fr.distance;
+		tile = fr.layer == MTD_INF ? MTD_INF : L.tiles[(size_t)fr.layer * T + pos];
+	}
+
+	__global__ void k_find_batch(LayersView L, const uint32_t *pos, const uint32_t *bits, int nq, uint32_t *tile_out, uint32_t *dist_out)
+	{
+		const int i = blockIdx.x * blockDim.x + threadIdx.x;
+		if (i >= nq)
+			return;
+		uint32_t t, d;
+		device_find(L, pos[i], bits[i], t, d);
+		tile_out[i] = t;
+		dist_out[i] = d;
+	}
+
+	// monsters.cpp:60-98, statement by statement
+	__global__ void k_monsters_tick(LayersView L, MonstersView M, uint32_t gameTime, unsigned long long *damage_sum, uint32_t *alive_count)
+	{
+		const int i = blockIdx.x * blockDim.x + threadIdx.x;
+		bool alive = false;
+		if (i < M.n)
+		{
+			alive = M.alive[i] != 0;
+			uint32_t timeEnd = M.timeEnd[i];
+			if (alive && gameTime >= timeEnd) // :64
+			{
+				const uint32_t tile = M.tile[i];
+				uint32_t bits = M.bits[i];
+				for (int k = 0; k < L.n; k++) // :67-69
+					if (L.wp[k] == tile)
+						bits |= 1u << k;
+				M.bits[i] = bits;
+				if (__popc(bits) == L.n) // :70-77
+				{
+					if (M.damage)
+						atomicAdd(damage_sum, (unsigned long long)M.damage[i]);
+					M.alive[i] = 0;
+					alive = false;
+				}
+				else
+				{
+					uint32_t go_tile, go_dist;
+					device_find(L, tile, bits, go_tile, go_dist); // :79
+					M.tileStart[i] = tile;                          // :82-84
+					M.tileEnd[i] = go_tile;
+					M.tile[i] = go_tile;
+					M.timeStart[i] = gameTime;
+					const uint32_t tta = M.timeToArrive[i];
+					if (tta > gameTime) // :85-89 (uint64 arithmetic through distNext)
+					{
+						const unsigned long long distNext = go_tile < (uint32_t)(L.W * L.H) ? edge_weight(L.elev[tile], L.elev[go_tile]) : 0u; // m is asserted away in the reference (:80)
+						timeEnd = (uint32_t)((unsigned long long)gameTime + (unsigned long long)(tta - gameTime) * distNext / (unsigned long long)go_dist);
+					}
+					timeEnd = max(timeEnd, gameTime + 1u); // :90
+					const uint8_t df = M.dotflags ? M.dotflags[i] : (uint8_t)0;
+					const bool fire = df & 1, water = df & 2;
+					if (water && !fire) // :92-93
+						timeEnd = gameTime + (timeEnd - gameTime) * 2u;
+					if (fire && !water) // :94-95
+						timeEnd = gameTime + (timeEnd - gameTime) / 2u;
+					timeEnd = max(timeEnd, gameTime + 1u); // :96
+					M.timeEnd[i] = timeEnd;
+				}
+			}
+		}
+		const uint32_t bal = __ballot_sync(FULL_MASK, alive);
+		if (lane_id() == 0 && bal)
+			atomicAdd(alive_count, (uint32_t)__popc(bal));
+	}
+
+	// game.cpp:15-21: saturate(Real(gameTime - (sint64)timeStart) / Real(timeEnd - (sint64)timeStart)), interpolate
+	__global__ void k_monsters_positions(LayersView L, MonstersView M, uint32_t gameTime, float *out3n)
+	{
+		const int i = blockIdx.x * blockDim.x + threadIdx.x;
+		if (i >= M.n)
+			return;
+		const uint32_t ts = M.tileStart[i], te = M.tileEnd[i];
+		const float num = __ll2float_rn((long long)gameTime - (long long)M.timeStart[i]);
+		const float den = __ll2float_rn((long long)M.timeEnd[i] - (long long)M.timeStart[i]);
+		float fac = __fdiv_rn(num, den);
+		fac = fac > 0.0f ? fac : 0.0f; // max(v, 0) = v > 0 ? v : 0 ; NaN -> 0 (cage-core/math.h:1021-1032)
+		fac = fac < 1.0f ? fac : 1.0f;
+		const float ax = (float)((int)(ts % (uint32_t)L.W) - L.ox), az = (float)((int)(ts / (uint32_t)L.W) - L.oy);
+		const float bx = (float)((int)(te % (uint32_t)L.W) - L.ox), bz = (float)((int)(te / (uint32_t)L.W) - L.oy);
+		const float ay = stor(L.elev[ts]), by = stor(L.elev[te]);
+		out3n[(size_t)i * 3 + 0] = __fadd_rn(ax, __fmul_rn(__fsub_rn(bx, ax), fac));
+		out3n[(size_t)i * 3 + 1] = __fadd_rn(ay, __fmul_rn(__fsub_rn(by, ay), fac));
+		out3n[(size_t)i * 3 + 2] = __fadd_rn(az, __fmul_rn(__fsub_rn(bz, az), fac));
+	}
+
+	// monsterSpawning.cpp:205-216
+	__global__ void k_monster_spawn(LayersView L, uint32_t spawner, uint32_t gameTime, float speed, uint32_t *out3)
+	{
+		const uint32_t position = L.wp[spawner];
+		const uint32_t bits = 1u << spawner;
+		uint32_t t, d;
+		device_find(L, position, bits, t, d);
+		out3[0] = position;
+		out3[1] = bits;
+		out3[2] = gameTime + (uint32_t)__float2ll_rz(__fdiv_rn(__fmul_rn(30.0f, stor((int32_t)d)), speed));
+	}
+
+	// buildingsPlacement.cpp:30-41 on a trial distance layer
+	__global__ void k_trial_check(const uint32_t *trial_dist, const uint32_t *wp, int nwp, const uint32_t *monster_tile, const uint8_t *monster_alive, int nmonsters, int *blocked_out)
+	{
+		const int i = blockIdx.x * blockDim.x + threadIdx.x;
+		bool bad = false;
+		if (i < nwp)
+			bad = trial_dist[wp[i]] == MTD_INF;
+		if (i < nmonsters && (!monster_alive || monster_alive[i]))
+			bad |= trial_dist[monster_tile[i]] == MTD_INF;
+		if (__any_sync(FULL_MASK, bad) && lane_id() == 0)
+			*blocked_out = 1;
+	}
+
+	// Grid::neighborDistance for ANY pair of tiles (sources/map/grid.cpp:141-145): the general form with
+	// d = center(a) - center(b) and the dot-product sum order ((0 + d0*d0) + d1*d1) + d2*d2.
+	__global__ void k_neighbor_distances(int W, int ox, int oy, const int16_t *elev, const uint32_t *a, const uint32_t *b, int n, uint32_t *out)
+	{
+		const int i = blockIdx.x * blockDim.x + threadIdx.x;
+		if (i >= n)
+			return;
+		const uint32_t ta = a[i], tb = b[i];
+		const float d0 = __fsub_rn((float)((int)(ta % (uint32_t)W) - ox), (float)((int)(tb % (uint32_t)W) - ox));
+		const float d1 = __fsub_rn(stor(elev[ta]), stor(elev[tb]));
+		const float d2 = __fsub_rn((float)((int)(ta / (uint32_t)W) - oy), (float)((int)(tb / (uint32_t)W) - oy));
+		float sum = __fmul_rn(d0, d0);
+		sum = __fadd_rn(sum, __fmul_rn(d1, d1));
+		sum = __fadd_rn(sum, __fmul_rn(d2, d2));
+		out[i] = (uint32_t)rtos32(__fsqrt_rn(sum));
+	}
+
+	__global__ void k_unpack_weights(int W, int H, const int16_t *elev, uint32_t *right, uint32_t *down)
+	{
+		const size_t total = (size_t)W * H;
+		for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x)
+		{
+			const int x = (int)(i % (size_t)W), y = (int)(i / (size_t)W);
+			right[i] = x < W - 1 ? edge_weight(elev[i], elev[i + 1]) : 0u;
+			down[i] = y < H - 1 ? edge_weight(elev[i], elev[i + W]) : 0u;
+		}
+	}
+}

@@ -1,0 +1,431 @@
+"""GPU parity tests: every call goes through the C ABI (mazetd_b200.capi -> libmazetd_b200.so) and is compared
+bit for bit with the CPU oracle (oracle/libmazetd_oracle.so) and, where the prebuilt library travelled, with the
+reference's own compiled code (oracle/_ref/libmazetd_ref.so). Run with `-m gpu` on the B200 box."""
+import os
+
+import numpy as np
+import pytest
+
+from mazetd_b200 import synth
+from oracle_lib import KAT_SEED, M
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from mazetd_b200 import capi
+
+    c = capi.Context(0)
+    yield c
+    c.close()
+
+
+def diff_report(a, b, W):
+    bad = np.flatnonzero(a != b)
+    i = int(bad[0])
+    return f"{len(bad)} mismatches; first at tile {i} (x={i % W}, y={i // W}): got {a.reshape(-1)[i]} want {b.reshape(-1)[i]}"
+
+
+# ---------------------------------------------------------------------------------------------------
+# G4: edge weights
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("amp", [90, 512, 32768])
+def test_edge_weights_bit_exact(ctx, oracle, amp):
+    rng = np.random.default_rng(amp)
+    W, H = 257, 129
+    elev = rng.integers(-amp, amp, W * H).astype(np.int16)
+    flags = np.zeros(W * H, np.uint16)
+    ctx.grid_upload(W, H, elev, flags)
+    r, d = ctx.edge_weights()
+    ro, do = oracle.edge_weights(W, H, elev)
+    assert np.array_equal(r, ro), diff_report(r, ro, W)
+    assert np.array_equal(d, do), diff_report(d, do, W)
+
+
+def test_neighbor_distance_general_pairs(ctx, oracle):
+    """Grid::neighborDistance also for non-adjacent tiles (the reference API allows any pair)"""
+    import ctypes as C
+
+    rng = np.random.default_rng(3)
+    W, H = 101, 101
+    elev = rng.integers(-2200, 1200, W * H).astype(np.int16)
+    ctx.grid_upload(W, H, elev, np.zeros(W * H, np.uint16), 50, 50)
+    a = rng.integers(0, W * H, 4000).astype(np.uint32)
+    b = rng.integers(0, W * H, 4000).astype(np.uint32)
+    got = ctx.neighbor_distances(a, b)
+    g = oracle.grid(W, H, 50, 50, elev, None)
+    want = np.array([oracle.L.mo_neighbor_distance(C.byref(g), int(x), int(y)) for x, y in zip(a, b)], np.uint32)
+    assert np.array_equal(got, want)
+
+
+# ---------------------------------------------------------------------------------------------------
+# P1: Directions::update -- small (one CTA) path
+# ---------------------------------------------------------------------------------------------------
+SMALL_CASES = ["open", "walls30", "walls45", "maze", "tiny", "row", "col", "blocked_source", "flat", "default101"]
+
+
+def make_case(case):
+    if case == "tiny":
+        W, H = 1, 1
+    elif case == "row":
+        W, H = 37, 1
+    elif case == "col":
+        W, H = 1, 29
+    elif case == "default101":
+        W, H = 101, 101
+    else:
+        W, H = 67, 45
+    if case == "maze":
+        elev, flags = synth.maze_grid(W, H, 3)
+    elif case == "flat":
+        elev = np.zeros(W * H, np.int16)
+        flags = np.full(W * H, synth.FLAG_SUN, np.uint16)
+    else:
+        pct = {"open": 0, "walls30": 30, "walls45": 45, "default101": 35}.get(case, 20)
+        elev, flags = synth.random_grid(W, H, seed_k=11, wall_pct=pct, elev_mod=512)
+    if case == "blocked_source":
+        src = int(np.flatnonzero(flags & synth.FLAG_INVALID)[5])
+    else:
+        src = int(synth.pick_open_tiles(flags, 1, 2)[0]) if W * H > 1 else 0
+    return W, H, elev, flags, src
+
+
+@pytest.mark.parametrize("case", SMALL_CASES)
+def test_directions_small_bit_exact(ctx, oracle, case):
+    W, H, elev, flags, src = make_case(case)
+    ctx.grid_upload(W, H, elev, flags)
+    tiles, dist = ctx.directions_update(src)
+    to, do = oracle.directions_update(W, H, elev, flags, src)
+    assert np.array_equal(dist, do), diff_report(dist, do, W)
+    assert np.array_equal(tiles, to), diff_report(tiles, to, W)
+
+
+def test_directions_small_vs_reference_code(ctx, ref):
+    """same comparison against the reference's own compiled paths.cpp (oracle/_ref)"""
+    for case in ("walls30", "maze", "flat", "blocked_source"):
+        W, H, elev, flags, src = make_case(case)
+        ctx.grid_upload(W, H, elev, flags)
+        tiles, dist = ctx.directions_update(src)
+        tr, dr = ref.directions_update(W, H, elev, flags, src)
+        assert np.array_equal(dist, dr) and np.array_equal(tiles, tr), case
+
+
+def test_directions_extra_blocked_is_the_trial_grid(ctx, oracle):
+    """placingBuildingBlocksMonsters: a copy of the grid with Building on the cursor tile (buildingsPlacement.cpp:20-29)"""
+    W, H, elev, flags, src = make_case("walls30")
+    ctx.grid_upload(W, H, elev, flags)
+    open_tiles = np.flatnonzero((flags & (synth.FLAG_INVALID | synth.FLAG_BUILDING)) == 0)
+    for cand in open_tiles[:: max(1, len(open_tiles) // 12)]:
+        if cand == src:
+            continue
+        tiles, dist = ctx.directions_update(src, extra_blocked=int(cand))
+        f2 = flags.copy()
+        f2[cand] |= synth.FLAG_BUILDING
+        to, do = oracle.directions_update(W, H, elev, f2, src)
+        assert np.array_equal(dist, do) and np.array_equal(tiles, to)
+
+
+def test_directions_multi_source_extension(ctx, oracle):
+    W, H, elev, flags, _ = make_case("walls30")
+    ctx.grid_upload(W, H, elev, flags)
+    srcs = synth.pick_open_tiles(flags, 7, 4)
+    tiles, dist = ctx.directions_update(srcs)
+    to, do = oracle.directions_update(W, H, elev, flags, srcs)
+    assert np.array_equal(dist, do) and np.array_equal(tiles, to)
+
+
+def test_every_single_building_toggle_on_one_map(ctx, oracle):
+    """flip Building on every passable tile of one generated map, rebuild, compare"""
+    o = oracle.mapgen(KAT_SEED[0], KAT_SEED[1])
+    W = H = 101
+    flags = o["flags"].copy()
+    ctx.grid_upload(W, H, o["elev"], flags, 50, 50)
+    src = int(o["wp_tiles"][0])
+    passable = np.flatnonzero((flags & (synth.FLAG_INVALID | synth.FLAG_WAYPOINT)) == 0)
+    for t in passable[::37]:
+        f2 = flags.copy()
+        f2[t] |= synth.FLAG_BUILDING
+        ctx.grid_set_flags(int(t), int(f2[t]))
+        tiles, dist = ctx.directions_update(src)
+        to, do = oracle.directions_update(W, H, o["elev"], f2, src, 50, 50)
+        assert np.array_equal(dist, do) and np.array_equal(tiles, to), int(t)
+        ctx.grid_set_flags(int(t), int(flags[t]))
+
+
+# ---------------------------------------------------------------------------------------------------
+# P1: tiled path for large grids
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("shape,pct", [((300, 260), 30), ((513, 257), 0), ((640, 384), 40), ((1024, 1024), 30)])
+def test_directions_tiled_bit_exact(ctx, oracle, shape, pct):
+    W, H = shape
+    elev, flags = synth.random_grid(W, H, seed_k=21, wall_pct=pct, elev_mod=512)
+    src = int(synth.pick_open_tiles(flags, 1, 5)[0])
+    ctx.grid_upload(W, H, elev, flags)
+    tiles, dist = ctx.directions_update(src)
+    to, do = oracle.directions_update(W, H, elev, flags, src)
+    assert np.array_equal(dist, do), diff_report(dist, do, W)
+    assert np.array_equal(tiles, to), diff_report(tiles, to, W)
+
+
+def test_directions_tiled_maze_and_multisource(ctx, oracle):
+    W, H = 290, 270
+    elev, flags = synth.maze_grid(W, H, 7)
+    ctx.grid_upload(W, H, elev, flags)
+    tiles, dist = ctx.directions_update(0)
+    to, do = oracle.directions_update(W, H, elev, flags, 0)
+    assert np.array_equal(dist, do), diff_report(dist, do, W)
+    assert np.array_equal(tiles, to)
+    elev, flags = synth.random_grid(W, H, seed_k=2, wall_pct=30, elev_mod=512)
+    ctx.grid_upload(W, H, elev, flags)
+    srcs = synth.pick_open_tiles(flags, 16, 6)
+    tiles, dist = ctx.directions_update(srcs)
+    to, do = oracle.directions_update(W, H, elev, flags, srcs)
+    assert np.array_equal(dist, do), diff_report(dist, do, W)
+    assert np.array_equal(tiles, to)
+
+
+def test_directions_tiled_blocked_source_and_border_sources(ctx, oracle):
+    W, H = 300, 300
+    elev, flags = synth.random_grid(W, H, seed_k=9, wall_pct=25, elev_mod=300)
+    ctx.grid_upload(W, H, elev, flags)
+    blocked = np.flatnonzero(flags & synth.FLAG_INVALID)
+    # sources straddling tile borders (x or y = 63, 64, 127, 128 ...) and a blocked source
+    cands = [63 + 64 * W, 64 + 64 * W, 63 + 63 * W, 128 + 127 * W, int(blocked[100]), 0, W * H - 1, W - 1]
+    for s in cands:
+        tiles, dist = ctx.directions_update(s)
+        to, do = oracle.directions_update(W, H, elev, flags, s)
+        assert np.array_equal(dist, do), (s, diff_report(dist, do, W))
+        assert np.array_equal(tiles, to), s
+
+
+def test_tiled_properties_at_4096(ctx):
+    """full-size property checks where the oracle would take too long: the result is a fixpoint of relaxation
+    (every edge satisfied, every finite non-source distance attained by its next hop) and next hops are neighbours"""
+    W = H = 4096
+    elev, flags = synth.random_grid(W, H, seed_k=1, wall_pct=30, elev_mod=512)
+    srcs = synth.pick_open_tiles(flags, 8, 1)
+    ctx.grid_upload(W, H, elev, flags)
+    tiles, dist = ctx.directions_update(srcs)
+    r, d = ctx.edge_weights()
+    D = dist.reshape(H, W).astype(np.int64)
+    D[D == M] = 1 << 40
+    blocked = (flags.reshape(H, W) & synth.FLAG_INVALID) != 0
+    R = r.reshape(H, W).astype(np.int64)
+    Dn = d.reshape(H, W).astype(np.int64)
+    # no edge into an unblocked tile can improve it
+    assert np.all((D[:, :-1] + R[:, :-1] >= D[:, 1:]) | blocked[:, 1:])
+    assert np.all((D[:, 1:] + R[:, :-1] >= D[:, :-1]) | blocked[:, :-1])
+    assert np.all((D[:-1, :] + Dn[:-1, :] >= D[1:, :]) | blocked[1:, :])
+    assert np.all((D[1:, :] + Dn[:-1, :] >= D[:-1, :]) | blocked[:-1, :])
+    # every reached non-source tile has a next hop that is a neighbour and attains its distance exactly
+    t = tiles.astype(np.int64)
+    reached = (dist != M) & (dist != 0)
+    idx = np.flatnonzero(reached)
+    nh = t[idx]
+    assert np.all(nh != M)
+    dx = np.abs(nh % W - idx % W) + np.abs(nh // W - idx // W)
+    assert np.all(dx == 1)
+    lo = np.minimum(nh, idx)
+    w = np.where(np.abs(nh - idx) == 1, r[lo], d[lo]).astype(np.int64)
+    assert np.all(dist[nh].astype(np.int64) + w == dist[idx].astype(np.int64))
+    assert np.all(tiles[dist == M] == M) and np.all(tiles[srcs] == M) and np.all(dist[srcs] == 0)
+    assert reached.sum() > 0.5 * (~blocked).sum()
+
+
+# ---------------------------------------------------------------------------------------------------
+# P2-P4: Waypoints::update / find
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n", [1, 2, 3, 4])
+def test_waypoints_update_bit_exact(ctx, oracle, n):
+    W, H = 41, 37
+    elev, flags = synth.random_grid(W, H, seed_k=5, wall_pct=25, elev_mod=200)
+    wp = synth.pick_open_tiles(flags, n, 9)
+    ctx.grid_upload(W, H, elev, flags)
+    g = ctx.waypoints_update(wp)
+    o = oracle.waypoints_update(W, H, elev, flags, wp)
+    for k in ("dist", "tiles", "fullpath_len", "full_distance", "agg", "fullpath"):
+        assert np.array_equal(g[k], o[k]), k
+
+
+def test_waypoints_update_more_than_four_layers(ctx, oracle):
+    W, H = 41, 37
+    elev, flags = synth.random_grid(W, H, seed_k=5, wall_pct=20, elev_mod=200)
+    wp = synth.pick_open_tiles(flags, 6, 9)
+    ctx.grid_upload(W, H, elev, flags)
+    g = ctx.waypoints_update(wp)
+    o = oracle.waypoints_update(W, H, elev, flags, wp)
+    for k in ("dist", "tiles", "fullpath_len", "full_distance", "agg", "fullpath"):
+        assert np.array_equal(g[k], o[k]), k
+
+
+def test_waypoints_empty_is_a_noop(ctx):
+    W, H, elev, flags, _ = make_case("open")
+    ctx.grid_upload(W, H, elev, flags)
+    g = ctx.waypoints_update(np.zeros(0, np.uint32))  # paths.cpp:113-114
+    assert g["agg"].tolist() == [0, 0, 0]
+
+
+def test_waypoints_on_generated_maps_vs_reference_code(ctx, ref):
+    for k in (0, 3):
+        r = ref.mapgen(KAT_SEED[0] + k, KAT_SEED[1])
+        ctx.grid_upload(101, 101, r["elev"], r["flags"], 50, 50)
+        g = ctx.waypoints_update(r["wp_tiles"])
+        for key in ("dist", "tiles", "fullpath_len", "full_distance", "agg", "fullpath"):
+            assert np.array_equal(g[key], r[key]), (k, key)
+
+
+def test_find_batch_bit_exact_including_unreachable(ctx, oracle):
+    W, H = 29, 23
+    elev, flags = synth.random_grid(W, H, seed_k=8, wall_pct=38, elev_mod=300)
+    wp = synth.pick_open_tiles(flags, 4, 1)
+    ctx.grid_upload(W, H, elev, flags)
+    ctx.waypoints_update(wp)
+    o = oracle.waypoints_update(W, H, elev, flags, wp)
+    wv = oracle.waypoints_view(W, H, elev, flags, wp, o["tiles"], o["dist"])
+    rng = np.random.default_rng(3)
+    pos = rng.integers(0, W * H, 3000).astype(np.uint32)
+    bits = rng.integers(0, 16, 3000).astype(np.uint32)
+    t, d = ctx.waypoints_find(pos, bits)
+    want = np.array([oracle.find(wv, int(p), int(b)) for p, b in zip(pos, bits)], np.uint32)
+    assert np.array_equal(t, want[:, 0]) and np.array_equal(d, want[:, 1])
+
+
+def test_placing_blocks_matches_oracle(ctx, oracle):
+    o = oracle.mapgen(KAT_SEED[0] + 1, KAT_SEED[1])
+    W = H = 101
+    ctx.grid_upload(W, H, o["elev"], o["flags"], 50, 50)
+    ctx.waypoints_update(o["wp_tiles"])
+    passable = np.flatnonzero((o["flags"] & (synth.FLAG_INVALID | synth.FLAG_WAYPOINT)) == 0).astype(np.uint32)
+    rng = np.random.default_rng(2)
+    mt = rng.choice(passable, 500).astype(np.uint32)
+    alive = (rng.integers(0, 5, 500) > 0).astype(np.uint8)
+    z = np.zeros(500, np.uint32)
+    ctx.monsters_upload(dict(tile=mt, tileStart=mt, tileEnd=mt, timeStart=z, timeEnd=z, bits=z, timeToArrive=z, alive=alive))
+    got_any = set()
+    for cand in np.concatenate([o["fullpath"][0][: int(o["fullpath_len"][0])][1:60:3], rng.choice(passable, 25)]):
+        want = oracle.placing_blocks(W, H, o["elev"], o["flags"], o["wp_tiles"], int(cand), mt, alive, 50, 50)
+        got = ctx.placing_blocks(int(cand))
+        assert got == bool(want), int(cand)
+        got_any.add(got)
+    assert got_any  # ran
+
+
+# ---------------------------------------------------------------------------------------------------
+# M1-M7: procedural generator
+# ---------------------------------------------------------------------------------------------------
+def test_elevation_samples_bit_exact(ctx, oracle):
+    import ctypes as C
+
+    from oracle_lib import MoProcedural
+
+    rng = np.random.default_rng(4)
+    xy = np.concatenate([rng.uniform(-60, 60, (6000, 2)), np.array([[0, 0], [-50, -50], [50, 50], [30, 0], [0, -30.0001]])]).astype(np.float32)
+    for k in (0, 5):
+        got = ctx.elevation_samples(KAT_SEED[0] + k, KAT_SEED[1], xy)
+        g = oracle.rng(KAT_SEED[0] + k, KAT_SEED[1])
+        p = MoProcedural()
+        oracle.L.mo_procedural_init(C.byref(p), C.byref(g))
+        want = np.array([oracle.L.mo_elevation(C.byref(p), float(x), float(y)) for x, y in xy], np.float32)
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), f"{(got != want).sum()} of {len(xy)} samples differ"
+
+
+def test_mapgen_batch_bit_exact(ctx, oracle):
+    n = 24
+    g = ctx.mapgen_batch(KAT_SEED[0], KAT_SEED[1], 0, n, cap=2048)
+    for k in range(n):
+        o = oracle.mapgen(KAT_SEED[0] + k, KAT_SEED[1], cap=2048)
+        for key in ("elev", "flags", "wp_tiles", "dist", "tiles", "fullpath_len", "full_distance", "agg", "fullpath"):
+            assert np.array_equal(g[key][k], o[key]), (k, key)
+
+
+def test_mapgen_batch_vs_reference_code(ctx, ref):
+    g = ctx.mapgen_batch(KAT_SEED[0], KAT_SEED[1], 40, 3, cap=2048)
+    for j in range(3):
+        r = ref.mapgen(KAT_SEED[0] + 40 + j, KAT_SEED[1], cap=2048)
+        for key in ("elev", "flags", "wp_tiles", "dist", "tiles", "fullpath_len", "full_distance", "agg", "fullpath"):
+            assert np.array_equal(g[key][j], r[key]), (j, key)
+
+
+def test_mapgen_against_committed_golden(ctx):
+    """tests/golden/mapgen_k0_k7.npz was generated from the reference's compiled code (tests/golden/make_golden.py)"""
+    path = os.path.join(os.path.dirname(__file__), "golden", "mapgen_k0_k7.npz")
+    gold = np.load(path)
+    g = ctx.mapgen_batch(KAT_SEED[0], KAT_SEED[1], 0, 8, cap=1024)
+    assert np.array_equal(g["elev"], gold["elev"])
+    assert np.array_equal(g["flags"], gold["flags"])
+    assert np.array_equal(g["wp_tiles"], gold["wp_tiles"])
+    assert np.array_equal(g["agg"], gold["agg"])
+    assert np.array_equal(g["full_distance"], gold["full_distance"])
+    assert np.array_equal(g["fullpath_len"], gold["fullpath_len"])
+    for k in range(8):
+        for l in range(4):
+            assert int(np.bitwise_xor.reduce(g["dist"][k, l])) == int(gold["dist_xor"][k, l])
+            assert int(g["dist"][k, l].astype(np.uint64).sum() & 0xFFFFFFFF) == int(gold["dist_sum"][k, l])
+            assert int(g["tiles"][k, l].astype(np.uint64).sum() & 0xFFFFFFFF) == int(gold["tiles_sum"][k, l])
+
+
+# ---------------------------------------------------------------------------------------------------
+# S1-S3: steering
+# ---------------------------------------------------------------------------------------------------
+def test_steering_bit_exact_over_many_ticks(ctx, oracle):
+    o = oracle.mapgen(KAT_SEED[0] + 2, KAT_SEED[1])
+    W = H = 101
+    ctx.grid_upload(W, H, o["elev"], o["flags"], 50, 50)
+    g = ctx.waypoints_update(o["wp_tiles"])
+    assert np.array_equal(g["agg"], o["agg"])
+    wv = oracle.waypoints_view(W, H, o["elev"], o["flags"], o["wp_tiles"], o["tiles"], o["dist"], 50, 50)
+    spawner = int(o["agg"][2])
+    n = 2000
+    rng = np.random.default_rng(5)
+    speeds = rng.uniform(0.02, 0.6, n).astype(np.float32)
+    a = {k: np.zeros(n, np.uint32) for k in ("tile", "tileStart", "tileEnd", "timeStart", "timeEnd", "bits", "timeToArrive", "damage")}
+    a["dotflags"] = (np.arange(n) % 4).astype(np.uint8)
+    a["alive"] = np.ones(n, np.uint8)
+    a["damage"][:] = np.arange(n) % 7 + 1
+    for i in range(n):
+        so = oracle.monster_spawn(wv, spawner, i % 50, float(speeds[i]))
+        if i < 40:
+            assert np.array_equal(ctx.monster_spawn(i % 50, float(speeds[i])), so)
+        a["tile"][i] = a["tileStart"][i] = a["tileEnd"][i] = so[0]
+        a["bits"][i] = so[1]
+        a["timeToArrive"][i] = so[2]
+        a["timeStart"][i] = a["timeEnd"][i] = i % 50
+    ctx.monsters_upload(a)
+    dmg_g = dmg_o = 0
+    for t in range(0, 3000):
+        dg, alive_g = ctx.monsters_tick(t)
+        dmg_g += dg
+        dmg_o += oracle.monsters_tick(wv, t, a)
+        if t % 250 == 0 or t == 2999:
+            got = ctx.monsters_download()
+            for k in got:
+                assert np.array_equal(got[k], a[k]), (t, k)
+            assert alive_g == int(a["alive"].sum())
+            pg = ctx.monsters_positions(t)
+            po = oracle.monsters_position(W, H, 50, 50, o["elev"], t, a["tileStart"], a["tileEnd"], a["timeStart"], a["timeEnd"])
+            # north_star tolerance for float positions: abs 1e-4; the kernels are unfused so we hold them exact
+            assert np.array_equal(pg.view(np.uint32), po.view(np.uint32))
+    assert dmg_g == dmg_o and dmg_o > 0
+
+
+def test_directions_against_committed_golden(ctx):
+    """tests/golden/directions.npz: Directions::update of the reference's compiled paths.cpp (make_golden.py)"""
+    gold = np.load(os.path.join(os.path.dirname(__file__), "golden", "directions.npz"))
+    cases = {
+        "walls": (67, 45) + synth.random_grid(67, 45, seed_k=11, wall_pct=30, elev_mod=512),
+        "maze": (67, 45) + synth.maze_grid(67, 45, 3),
+    }
+    for name, (W, H, elev, flags) in cases.items():
+        ctx.grid_upload(W, H, elev, flags)
+        t, d = ctx.directions_update(int(gold[name + "_src"]))
+        assert np.array_equal(d, gold[name + "_dist"]) and np.array_equal(t, gold[name + "_tiles"]), name
+    W, H = 300, 260
+    elev, flags = synth.random_grid(W, H, seed_k=21, wall_pct=30, elev_mod=512)
+    ctx.grid_upload(W, H, elev, flags)
+    t, d = ctx.directions_update(int(gold["big_src"]))
+    assert int(np.bitwise_xor.reduce(d)) == int(gold["big_dist_xor"])
+    assert int(d.astype(np.uint64).sum() & 0xFFFFFFFF) == int(gold["big_dist_sum"])
+    assert int(t.astype(np.uint64).sum() & 0xFFFFFFFF) == int(gold["big_tiles_sum"])
+    assert np.array_equal(d[100 * W : 101 * W], gold["big_dist_row100"])
+    assert np.array_equal(t[100 * W : 101 * W], gold["big_tiles_row100"])
