@@ -25,7 +25,7 @@ using namespace mtd;
 
 namespace
 {
-	constexpr size_t MAX_SMEM = 227 * 1024;
+	constexpr size_t MAX_SMEM = 227 * 1024 - 1024; // dynamic budget: the opt-in limit is 227 KB per CTA including static __shared__
 	constexpr int BIG_TS = 64;
 	constexpr int BIG_WARPS = 2;
 
@@ -134,6 +134,8 @@ namespace
 	do                                                                                                    \
 	{                                                                                                     \
 		cudaError_t e__ = (call);                                                                         \
+		if (e__ != cudaSuccess)                                                                           \
+			(void)cudaGetLastError();                                                                     \
 		if (e__ != cudaSuccess)                                                                           \
 			return fail(ctx, e__ == cudaErrorMemoryAllocation ? MTD_ERR_NOMEM : MTD_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e__)); \
 	} while (0)
