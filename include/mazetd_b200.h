@@ -57,6 +57,22 @@ int mtd_synchronize(mtd_ctx *ctx);
 /* number of kernels this context has launched since creation (bench.py's gpu_launches) */
 uint64_t mtd_launch_count(const mtd_ctx *ctx);
 
+/* ---- kernel timing probe (bench.py's roofline: per-kernel device time measured live with CUDA events on the
+ *      context's stream; replaces the reference's ProfilingScope, externals/cage/sources/include/cage-core/profiling.h:37-51) */
+enum
+{
+	MTD_K_WAYPOINTS_SMALL = 0, /* fused Waypoints::update of shared-memory sized maps */
+	MTD_K_MAPGEN_GRID = 1,     /* newProcedural + newGrid + spawn picking */
+	MTD_K_BIG_RELAX = 2,       /* tiled relaxation of a large grid (all rounds of one Directions::update) */
+	MTD_K_BIG_DIRECTIONS = 3,  /* next-hop pass of a large grid */
+	MTD_K_MONSTERS_TICK = 4,
+	MTD_K_BIG_PREPARE = 5,     /* edge weights + blocking mask of a large grid */
+	MTD_K_COUNT = 6
+};
+int mtd_profile_enable(mtd_ctx *ctx, int on);
+/* synchronises the stream; returns the summed device time and number of bracketed regions of `kind` since the last read */
+int mtd_profile_read(mtd_ctx *ctx, int kind, double *total_ms, uint64_t *regions);
+
 /* ---- Grid (replaces the data side of struct Grid, sources/grid.h:38-53) ------------------------ */
 /* Upload a grid; builds the device-side derived data (packed edge weights = Grid::neighborDistance for the
  * right/down edge of every tile, sources/map/grid.cpp:141-145, and the Invalid|Building blocking mask). */

@@ -14,6 +14,7 @@ M = 0xFFFFFFFF
 
 EXPORTS = [
     "mtd_create", "mtd_destroy", "mtd_last_error", "mtd_version", "mtd_synchronize", "mtd_launch_count",
+    "mtd_profile_enable", "mtd_profile_read",
     "mtd_grid_upload", "mtd_grid_upload_dev", "mtd_grid_set_flags", "mtd_neighbor_distances", "mtd_edge_weights",
     "mtd_directions_update", "mtd_directions_update_dev",
     "mtd_waypoints_update", "mtd_waypoints_update_dev", "mtd_waypoints_find", "mtd_waypoints_layers_dev",
@@ -54,6 +55,8 @@ def load():
     L.mtd_synchronize.argtypes = [vp]
     L.mtd_launch_count.argtypes = [vp]
     L.mtd_launch_count.restype = u64
+    L.mtd_profile_enable.argtypes = [vp, C.c_int]
+    L.mtd_profile_read.argtypes = [vp, C.c_int, C.POINTER(C.c_double), C.POINTER(u64)]
     L.mtd_grid_upload.argtypes = [vp, i32, i32, i32, i32, vp, vp]
     L.mtd_grid_upload_dev.argtypes = [vp, i32, i32, i32, i32, vp, vp]
     L.mtd_grid_set_flags.argtypes = [vp, u32, C.c_uint16]
@@ -123,6 +126,18 @@ class Context:
     @property
     def launches(self):
         return int(self.L.mtd_launch_count(self.h))
+
+    # ---- kernel timing probe ----
+    K_WAYPOINTS_SMALL, K_MAPGEN_GRID, K_BIG_RELAX, K_BIG_DIRECTIONS, K_MONSTERS_TICK, K_BIG_PREPARE = range(6)
+
+    def profile_enable(self, on=True):
+        self._ck(self.L.mtd_profile_enable(self.h, int(bool(on))))
+
+    def profile_read(self, kind):
+        """(total device ms, bracketed regions) of `kind` since the last read; synchronises the stream"""
+        ms, n = C.c_double(0), C.c_uint64(0)
+        self._ck(self.L.mtd_profile_read(self.h, int(kind), C.byref(ms), C.byref(n)))
+        return ms.value, int(n.value)
 
     # ---- grid ----
     def grid_upload(self, W, H, elev, flags, ox=0, oy=0):

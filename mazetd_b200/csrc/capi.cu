@@ -114,6 +114,16 @@ struct mtd_ctx
 	DevBuf<uint32_t> d_small; // alive count, spawn out ...
 	DevBuf<int> d_trial;
 	HostFlags *hflags = nullptr; // pinned
+
+	// timing probe
+	bool profiling = false;
+	struct ProfRegion
+	{
+		int kind;
+		cudaEvent_t a, b;
+	};
+	std::vector<ProfRegion> prof_open;
+	std::vector<cudaEvent_t> prof_pool;
 };
 
 namespace
@@ -146,6 +156,39 @@ namespace
 		ctx->launches++;                                            \
 		CU(cudaGetLastError());                                     \
 	} while (0)
+
+	// RAII bracket of one kernel (or a loop of launches) with CUDA events when profiling is on
+	struct ProfScope
+	{
+		mtd_ctx *ctx;
+		cudaEvent_t b = nullptr;
+		ProfScope(mtd_ctx *c, int kind) : ctx(c)
+		{
+			if (!c->profiling)
+				return;
+			auto take = [&]() -> cudaEvent_t
+			{
+				cudaEvent_t e = nullptr;
+				if (!c->prof_pool.empty())
+				{
+					e = c->prof_pool.back();
+					c->prof_pool.pop_back();
+				}
+				else
+					cudaEventCreate(&e);
+				return e;
+			};
+			cudaEvent_t a = take();
+			b = take();
+			cudaEventRecord(a, c->stream);
+			c->prof_open.push_back({ kind, a, b });
+		}
+		~ProfScope()
+		{
+			if (b)
+				cudaEventRecord(b, ctx->stream);
+		}
+	};
 
 	struct DeviceGuard
 	{
@@ -223,6 +266,7 @@ namespace
 			configured = MAX_SMEM;
 		}
 		const int blocks = P.nmaps < ctx->sms * (smem * 2 <= MAX_SMEM ? 2 : 1) ? P.nmaps : ctx->sms * (smem * 2 <= MAX_SMEM ? 2 : 1);
+		ProfScope prof(ctx, MTD_K_WAYPOINTS_SMALL);
 		k_waypoints_small<<<blocks, SMALL_THREADS, smem, ctx->stream>>>(P);
 		LAUNCHED();
 		return MTD_OK;
@@ -241,6 +285,7 @@ namespace
 		CU(ctx->list1.reserve(nt));
 		CU(ctx->stamp.reserve(nt));
 		CU(ctx->counters.reserve(8));
+		ProfScope prof(ctx, MTD_K_BIG_PREPARE);
 		k_edge_weights<<<grid_blocks(ctx, ctx->T, 256), 256, 0, ctx->stream>>>(ctx->W, ctx->H, ctx->elev.p, nullptr, ctx->flags.p, ctx->wpack.p, ctx->blocked.p);
 		LAUNCHED();
 		return MTD_OK;
@@ -303,6 +348,12 @@ namespace
 		const int blocks = ctx->sms * (ctas_per_sm > 0 ? ctas_per_sm : 1);
 		int round = 0;
 		int burst = 4;
+		ProfScope *relax_prof = new ProfScope(ctx, MTD_K_BIG_RELAX);
+		struct ProfDone
+		{
+			ProfScope *&p;
+			~ProfDone() { delete p; p = nullptr; }
+		} relax_done{ relax_prof };
 		for (;;)
 		{
 			for (int b = 0; b < burst; b++, round++)
@@ -321,10 +372,13 @@ namespace
 				return fail(ctx, MTD_ERR_CUDA, "tile relaxation did not converge after %d rounds", round);
 		}
 		ctx->last_rounds = (uint32_t)round;
+		delete relax_prof;
+		relax_prof = nullptr;
 		if (extra_blocked != MTD_M)
 			CU(cudaMemcpyAsync(ctx->blocked.p + extra_blocked, &prev_blocked, 1, cudaMemcpyHostToDevice, ctx->stream));
 		if (d_tiles)
 		{
+			ProfScope prof(ctx, MTD_K_BIG_DIRECTIONS);
 			k_directions<<<grid_blocks(ctx, ctx->T, 256), 256, 0, ctx->stream>>>(ctx->W, ctx->H, 0, ctx->H, d_dist, ctx->wpack.p, nullptr, nullptr, nullptr, d_tiles);
 			LAUNCHED();
 		}
@@ -593,6 +647,51 @@ extern "C" int mtd_synchronize(mtd_ctx *ctx)
 extern "C" uint64_t mtd_launch_count(const mtd_ctx *ctx)
 {
 	return ctx ? ctx->launches : 0;
+}
+
+extern "C" int mtd_profile_enable(mtd_ctx *ctx, int on)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	ctx->profiling = on != 0;
+	return MTD_OK;
+}
+
+extern "C" int mtd_profile_read(mtd_ctx *ctx, int kind, double *total_ms, uint64_t *regions)
+{
+	if (!ctx || kind < 0 || kind >= MTD_K_COUNT)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	CU(cudaStreamSynchronize(ctx->stream));
+	double sum = 0;
+	uint64_t n = 0;
+	std::vector<mtd_ctx::ProfRegion> keep;
+	for (const auto &r : ctx->prof_open)
+	{
+		if (r.kind != kind)
+		{
+			keep.push_back(r);
+			continue;
+		}
+		float ms = 0;
+		if (cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess)
+		{
+			sum += ms;
+			n++;
+		}
+		else
+			(void)cudaGetLastError();
+		ctx->prof_pool.push_back(r.a);
+		ctx->prof_pool.push_back(r.b);
+	}
+	ctx->prof_open.swap(keep);
+	if (total_ms)
+		*total_ms = sum;
+	if (regions)
+		*regions = n;
+	return MTD_OK;
 }
 
 // =====================================================================================================
@@ -898,8 +997,11 @@ static int mapgen_dev(mtd_ctx *ctx, const mtd_mapgen_params *p, uint64_t s1, uin
 	const size_t gsm = mapgen_grid_smem(T);
 	const int per_sm = (int)(MAX_SMEM / (gsm + 1024)) > 0 ? (int)(MAX_SMEM / (gsm + 1024)) : 1;
 	const int gblocks = nmaps < ctx->sms * per_sm ? nmaps : ctx->sms * per_sm;
-	k_mapgen_grid<<<gblocks, 512, gsm, ctx->stream>>>(G);
-	LAUNCHED();
+	{
+		ProfScope prof(ctx, MTD_K_MAPGEN_GRID);
+		k_mapgen_grid<<<gblocks, 512, gsm, ctx->stream>>>(G);
+		LAUNCHED();
+	}
 	if (p->nwp == 0)
 		return MTD_OK;
 
@@ -1146,6 +1248,7 @@ static int monsters_tick_dev(mtd_ctx *ctx, uint32_t gameTime)
 	CU(cudaMemsetAsync(ctx->d_small.p, 0, 4, ctx->stream));
 	if (ctx->nmon == 0)
 		return MTD_OK;
+	ProfScope prof(ctx, MTD_K_MONSTERS_TICK);
 	k_monsters_tick<<<(ctx->nmon + 255) / 256, 256, 0, ctx->stream>>>(layers_view(ctx), monsters_view(ctx), gameTime, ctx->d_damage.p, ctx->d_small.p);
 	LAUNCHED();
 	return MTD_OK;

@@ -468,6 +468,39 @@ extern "C"
 		return mp;
 	}
 
+	// Batch of independent maps k = first .. first+nmaps-1 with seed (s1 + k, s2), `threads` host threads, one map
+	// per thread at a time (the reference generates one map per pool thread, sources/map/generate.cpp:193).
+	// Each map runs the reference's newProcedural -> newGrid -> newWaypoints (incl. Waypoints::update) and is
+	// destroyed again; returns a checksum of the aggregates so the work cannot be optimised away.
+	uint64_t ref_mapgen_batch(uint64_t s1, uint64_t s2, int first, int nmaps, int threads)
+	{
+		if (threads < 1)
+			threads = 1;
+		std::atomic<int> next{ 0 };
+		std::atomic<uint64_t> checksum{ 0 };
+		auto worker = [&]()
+		{
+			uint64_t cs = 0;
+			for (;;)
+			{
+				const int k = next.fetch_add(1);
+				if (k >= nmaps)
+					break;
+				RefMap *mp = (RefMap *)ref_mapgen(s1 + (uint64_t)(first + k), s2);
+				cs += (uint64_t)mp->wps->avgFullDistance + ((uint64_t)mp->wps->minFullDistance << 20) + ((uint64_t)mp->wps->minDistanceSpawner << 40);
+				delete mp;
+			}
+			checksum.fetch_add(cs);
+		};
+		std::vector<std::thread> thrs;
+		for (int t = 1; t < threads; t++)
+			thrs.emplace_back(worker);
+		worker();
+		for (auto &t : thrs)
+			t.join();
+		return checksum.load();
+	}
+
 	// newGrid only, on caller-provided RNG seed; no waypoints
 	void *ref_mapgen_grid_only(uint64_t s1, uint64_t s2)
 	{
