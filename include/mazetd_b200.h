@@ -73,6 +73,13 @@ int mtd_profile_enable(mtd_ctx *ctx, int on);
 /* synchronises the stream; returns the summed device time and number of bracketed regions of `kind` since the last read */
 int mtd_profile_read(mtd_ctx *ctx, int kind, double *total_ms, uint64_t *regions);
 
+/* ---- test hooks (no reference counterpart): force rarely taken kernel paths so the parity suite covers them ------ */
+enum
+{
+	MTD_DEBUG_QSEG_CAP = 1 /* > 0 caps the per-warp frontier queue segment of the one-CTA path: small values force the queue-less dense rounds */
+};
+int mtd_debug_set(mtd_ctx *ctx, int key, int64_t value);
+
 /* ---- Grid (replaces the data side of struct Grid, sources/grid.h:38-53) ------------------------ */
 /* Upload a grid; builds the device-side derived data (packed edge weights = Grid::neighborDistance for the
  * right/down edge of every tile, sources/map/grid.cpp:141-145, and the Invalid|Building blocking mask). */

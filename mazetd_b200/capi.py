@@ -14,7 +14,7 @@ M = 0xFFFFFFFF
 
 EXPORTS = [
     "mtd_create", "mtd_destroy", "mtd_last_error", "mtd_version", "mtd_synchronize", "mtd_launch_count",
-    "mtd_profile_enable", "mtd_profile_read",
+    "mtd_profile_enable", "mtd_profile_read", "mtd_debug_set",
     "mtd_grid_upload", "mtd_grid_upload_dev", "mtd_grid_set_flags", "mtd_neighbor_distances", "mtd_edge_weights",
     "mtd_directions_update", "mtd_directions_update_dev",
     "mtd_waypoints_update", "mtd_waypoints_update_dev", "mtd_waypoints_find", "mtd_waypoints_layers_dev",
@@ -57,6 +57,7 @@ def load():
     L.mtd_launch_count.restype = u64
     L.mtd_profile_enable.argtypes = [vp, C.c_int]
     L.mtd_profile_read.argtypes = [vp, C.c_int, C.POINTER(C.c_double), C.POINTER(u64)]
+    L.mtd_debug_set.argtypes = [vp, C.c_int, C.c_int64]
     L.mtd_grid_upload.argtypes = [vp, i32, i32, i32, i32, vp, vp]
     L.mtd_grid_upload_dev.argtypes = [vp, i32, i32, i32, i32, vp, vp]
     L.mtd_grid_set_flags.argtypes = [vp, u32, C.c_uint16]
@@ -115,6 +116,11 @@ class Context:
             self.close()
         except Exception:
             pass
+
+    DEBUG_QSEG_CAP = 1
+
+    def debug_set(self, key, value):
+        self._ck(self.L.mtd_debug_set(self.h, int(key), int(value)))
 
     def _ck(self, rc):
         if rc != 0:

@@ -98,6 +98,8 @@ struct mtd_ctx
 	DevBuf<uint32_t> fp_buf, fp_len, fp_dist, agg;
 	uint32_t fp_cap = 0;
 	DevBuf<uint32_t> trial_dist;
+	DevBuf<uint32_t> map_counter;
+	int debug_qseg_cap = 0;
 
 	// monsters
 	int nmon = 0;
@@ -232,16 +234,26 @@ namespace
 		return MTD_OK;
 	}
 
-	bool small_fits(int W, int H, int n)
+	// resident layers per pass that fit shared memory next to a usable queue (0 = the map does not fit the one-CTA path)
+	int small_resident(int W, int H, int n)
 	{
-		if (W > 256 || H > 256)
-			return false;
+		if (W > 256 || H > 256 || n < 1)
+			return 0;
 		const size_t T = (size_t)W * H;
 		if (T >= 65536)
-			return false;
-		const int R = n < SMALL_MAX_RESIDENT ? n : SMALL_MAX_RESIDENT;
-		// prefer full residency for n <= 4; fall back to fewer resident layers is not implemented -> big path
-		return waypoints_small_smem((int)T, R) <= MAX_SMEM;
+			return 0;
+		for (int R = n < SMALL_MAX_RESIDENT ? n : SMALL_MAX_RESIDENT; R >= 1; R--)
+		{
+			const SmallLayout L = small_layout((int)T, R, (uint32_t)MAX_SMEM, 0);
+			if (L.qseg >= 64 && L.total <= MAX_SMEM)
+				return R;
+		}
+		return 0;
+	}
+
+	bool small_fits(int W, int H, int n)
+	{
+		return small_resident(W, H, n) > 0;
 	}
 
 	int grid_blocks(mtd_ctx *ctx, size_t n, int threads, int per_sm = 8)
@@ -255,19 +267,25 @@ namespace
 	int launch_waypoints_small(mtd_ctx *ctx, WaypointsSmallParams P)
 	{
 		const int T = P.W * P.H;
-		const int R = P.n < SMALL_MAX_RESIDENT ? P.n : SMALL_MAX_RESIDENT;
-		const size_t smem = waypoints_small_smem(T, R);
-		if (smem > MAX_SMEM)
+		P.R = small_resident(P.W, P.H, P.n);
+		if (P.R < 1)
 			return fail(ctx, MTD_ERR_CAPACITY, "map of %d tiles with %d layers does not fit shared memory", T, P.n);
-		static size_t configured = 0;
-		if (smem > configured)
+		P.smem_budget = (uint32_t)MAX_SMEM;
+		P.qseg_cap = ctx->debug_qseg_cap;
+		const SmallLayout L = small_layout(T, P.R, P.smem_budget, P.qseg_cap);
+		static bool configured = false;
+		if (!configured)
 		{
 			CU(cudaFuncSetAttribute(k_waypoints_small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MAX_SMEM));
-			configured = MAX_SMEM;
+			configured = true;
 		}
-		const int blocks = P.nmaps < ctx->sms * (smem * 2 <= MAX_SMEM ? 2 : 1) ? P.nmaps : ctx->sms * (smem * 2 <= MAX_SMEM ? 2 : 1);
+		CU(ctx->map_counter.reserve(1));
+		CU(cudaMemsetAsync(ctx->map_counter.p, 0, 4, ctx->stream));
+		P.map_counter = ctx->map_counter.p;
+		const int per_sm = L.total * 2 + 2048 <= MAX_SMEM ? 2 : 1;
+		const int blocks = P.nmaps < ctx->sms * per_sm ? P.nmaps : ctx->sms * per_sm;
 		ProfScope prof(ctx, MTD_K_WAYPOINTS_SMALL);
-		k_waypoints_small<<<blocks, SMALL_THREADS, smem, ctx->stream>>>(P);
+		k_waypoints_small<<<blocks, SMALL_THREADS, L.total, ctx->stream>>>(P);
 		LAUNCHED();
 		return MTD_OK;
 	}
@@ -486,7 +504,8 @@ namespace
 		CU(cudaMemsetAsync(ctx->fp_dist.p, 0, MTD_MAX_WAYPOINTS * 4, ctx->stream));
 		CU(cudaMemsetAsync(ctx->agg.p, 0, 16, ctx->stream));
 		const bool walks = n <= FIND_MAXN;
-		if (ctx->small && small_fits(ctx->W, ctx->H, n))
+		const bool small_path = ctx->small && small_fits(ctx->W, ctx->H, n);
+		if (small_path)
 		{
 			WaypointsSmallParams P;
 			memset(&P, 0, sizeof(P));
@@ -514,7 +533,6 @@ namespace
 		else
 		{
 			// large grid: one tiled relaxation per layer (layers are independent; the multi-GPU host shards them).
-			// Full-path walks on large grids are out of scope for this round.
 			for (int l = 0; l < n; l++)
 			{
 				int rc = big_directions(ctx, wp_tiles + l, 1, MTD_M, ctx->ltiles.p + (size_t)l * ctx->T, ctx->ldist.p + (size_t)l * ctx->T);
@@ -526,6 +544,12 @@ namespace
 		{
 			k_build_dtab<<<1, 64, 0, ctx->stream>>>(layers_view(ctx), ctx->dtab.p);
 			LAUNCHED();
+			if (!small_path)
+			{
+				// large grid: the walks run on the layers in global memory
+				k_walk_global<<<1, 32 * n, 0, ctx->stream>>>(layers_view(ctx), fullpath_cap ? ctx->fp_buf.p : nullptr, fullpath_cap, ctx->fp_len.p, ctx->fp_dist.p, ctx->agg.p, ctx->d_status.p);
+				LAUNCHED();
+			}
 		}
 		return MTD_OK;
 	}
@@ -603,6 +627,7 @@ extern "C" void mtd_destroy(mtd_ctx *ctx)
 	ctx->fp_dist.release();
 	ctx->agg.release();
 	ctx->trial_dist.release();
+	ctx->map_counter.release();
 	ctx->m_tile.release();
 	ctx->m_tileStart.release();
 	ctx->m_tileEnd.release();
@@ -647,6 +672,21 @@ extern "C" int mtd_synchronize(mtd_ctx *ctx)
 extern "C" uint64_t mtd_launch_count(const mtd_ctx *ctx)
 {
 	return ctx ? ctx->launches : 0;
+}
+
+extern "C" int mtd_debug_set(mtd_ctx *ctx, int key, int64_t value)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	switch (key)
+	{
+	case MTD_DEBUG_QSEG_CAP:
+		ctx->debug_qseg_cap = (int)value;
+		return MTD_OK;
+	default:
+		return fail(ctx, MTD_ERR_ARG, "unknown debug key %d", key);
+	}
 }
 
 extern "C" int mtd_profile_enable(mtd_ctx *ctx, int on)

@@ -147,6 +147,61 @@ namespace mtd
 		out3[2] = gameTime + (uint32_t)__float2ll_rz(__fdiv_rn(__fmul_rn(30.0f, stor((int32_t)d)), speed));
 	}
 
+	// Full-path walks + aggregates of Waypoints::update (sources/map/paths.cpp:87-139) on layers resident in global
+	// memory (grids too large for the one-CTA kernel). One lane per spawner: a dependent chase through the next-hop
+	// layers, find() per hop exactly like the reference. Launch: 1 block of 32 * n threads.
+	__global__ void k_walk_global(LayersView L, uint32_t *fullpath, uint32_t cap, uint32_t *fullpath_len, uint32_t *full_distance, uint32_t *agg, int *status)
+	{
+		__shared__ uint32_t s_fd[FIND_MAXN];
+		const int s = threadIdx.x >> 5;
+		const size_t T = (size_t)L.W * L.H;
+		if (s < L.n && (threadIdx.x & 31) == 0)
+		{
+			uint32_t *path = fullpath ? fullpath + (size_t)s * cap : nullptr;
+			uint32_t bits = 0, prev = MTD_INF, distance = 0, len = 0;
+			uint32_t tile = L.wp[s];
+			while (tile != MTD_INF)
+			{
+				for (int k = 0; k < L.n; k++)
+					if (L.wp[k] == tile)
+						bits |= 1u << k;
+				if (path && len < cap)
+					path[len] = tile;
+				len++;
+				if (prev != MTD_INF)
+					distance += edge_weight(L.elev[prev], L.elev[tile]); // Grid::neighborDistance of adjacent tiles
+				prev = tile;
+				uint32_t d;
+				device_find(L, tile, bits, tile, d);
+				if ((size_t)len > T * (size_t)L.n + 8u)
+					break; // cannot happen on consistent layers
+			}
+			if (path)
+				for (uint32_t i = len; i < cap; i++)
+					path[i] = MTD_INF;
+			if (fullpath && len > cap)
+				atomicOr(status, 4); // ST_PATH_TRUNC
+			fullpath_len[s] = len;
+			full_distance[s] = distance;
+			s_fd[s] = distance;
+		}
+		__syncthreads();
+		if (threadIdx.x == 0)
+		{
+			uint32_t sum = 0;
+			for (int i = 0; i < L.n; i++)
+				sum += s_fd[i];
+			const float avg = __fdiv_rn(stor((int32_t)sum), (float)(unsigned long long)L.n);
+			uint32_t best = 0;
+			for (int i = 0; i < L.n; i++)
+				if (s_fd[i] < s_fd[best])
+					best = (uint32_t)i;
+			agg[0] = (uint32_t)__float2ll_rz(avg);
+			agg[1] = (uint32_t)__float2ll_rz(stor((int32_t)s_fd[best]));
+			agg[2] = best;
+		}
+	}
+
 	// buildingsPlacement.cpp:30-41 on a trial distance layer
 	__global__ void k_trial_check(const uint32_t *trial_dist, const uint32_t *wp, int nwp, const uint32_t *monster_tile, const uint8_t *monster_alive, int nmonsters, int *blocked_out)
 	{

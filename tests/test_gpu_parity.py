@@ -259,6 +259,52 @@ def test_waypoints_update_more_than_four_layers(ctx, oracle):
         assert np.array_equal(g[k], o[k]), k
 
 
+def test_dense_fallback_when_the_frontier_queue_overflows(ctx, oracle):
+    """a tiny queue segment forces the queue-less dense rounds of the one-CTA kernel; results must not change"""
+    W, H = 101, 101
+    elev, flags = synth.random_grid(W, H, seed_k=11, wall_pct=10, elev_mod=300)
+    wp = synth.pick_open_tiles(flags, 4, 2)
+    ctx.grid_upload(W, H, elev, flags, 50, 50)
+    o = oracle.waypoints_update(W, H, elev, flags, wp, 50, 50)
+    try:
+        for cap in (32, 40, 64):
+            ctx.debug_set(ctx.DEBUG_QSEG_CAP, cap)
+            g = ctx.waypoints_update(wp)
+            for k in ("dist", "tiles", "fullpath_len", "full_distance", "agg", "fullpath"):
+                assert np.array_equal(g[k], o[k]), (cap, k)
+            t, d = ctx.directions_update(wp[:1])
+            assert np.array_equal(d, o["dist"][0]) and np.array_equal(t, o["tiles"][0])
+    finally:
+        ctx.debug_set(ctx.DEBUG_QSEG_CAP, 0)
+
+
+@pytest.mark.parametrize("shape,n", [((150, 140), 4), ((170, 160), 3), ((200, 200), 3), ((255, 255), 2), ((33, 7), 6)])
+def test_waypoints_update_fewer_resident_layers_than_waypoints(ctx, oracle, shape, n):
+    """maps whose layers do not all fit shared memory at once go through several passes and walk on the L2 copies"""
+    W, H = shape
+    elev, flags = synth.random_grid(W, H, seed_k=21, wall_pct=22, elev_mod=400)
+    wp = synth.pick_open_tiles(flags, n, 5)
+    ctx.grid_upload(W, H, elev, flags)
+    g = ctx.waypoints_update(wp, cap=8192)
+    o = oracle.waypoints_update(W, H, elev, flags, wp, cap=8192)
+    for k in ("dist", "tiles", "fullpath_len", "full_distance", "agg", "fullpath"):
+        assert np.array_equal(g[k], o[k]), k
+
+
+def test_open_map_wide_frontier(ctx, oracle):
+    """no walls: the widest frontiers the 101x101 map can produce"""
+    W, H = 101, 101
+    rng = np.random.default_rng(5)
+    elev = rng.integers(-40, 40, W * H).astype(np.int16)
+    flags = np.zeros(W * H, np.uint16)
+    wp = np.array([0, W * H - 1, 50 * W + 50, 100], np.uint32)
+    ctx.grid_upload(W, H, elev, flags, 50, 50)
+    g = ctx.waypoints_update(wp)
+    o = oracle.waypoints_update(W, H, elev, flags, wp, 50, 50)
+    for k in ("dist", "tiles", "fullpath_len", "full_distance", "agg", "fullpath"):
+        assert np.array_equal(g[k], o[k]), k
+
+
 def test_waypoints_empty_is_a_noop(ctx):
     W, H, elev, flags, _ = make_case("open")
     ctx.grid_upload(W, H, elev, flags)
