@@ -233,6 +233,10 @@ def run_ours(args):
     torch.cuda.set_stream(stream)
     assert stream.cuda_stream != 0
     ctx = capi.Context(local, stream=stream.cuda_stream)
+    if args.gw:
+        ctx.debug_set(ctx.DEBUG_GROUP_WARPS, args.gw)  # tuning probe only; the default is the shipped configuration
+    if args.walker:
+        ctx.debug_set(ctx.DEBUG_WALKER, args.walker)
     maps = args.maps
     first = rank * maps
 
@@ -412,6 +416,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--gw", type=int, default=0, help="tuning probe: warps per layer in the one-CTA kernel (1, 2, 4)")
+    ap.add_argument("--walker", type=int, default=0, help="tuning probe: 1 = workers walk the paths, 2 = walker warp")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

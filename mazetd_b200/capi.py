@@ -118,6 +118,8 @@ class Context:
             pass
 
     DEBUG_QSEG_CAP = 1
+    DEBUG_GROUP_WARPS = 2
+    DEBUG_WALKER = 3
 
     def debug_set(self, key, value):
         self._ck(self.L.mtd_debug_set(self.h, int(key), int(value)))

@@ -100,6 +100,9 @@ struct mtd_ctx
 	DevBuf<uint32_t> trial_dist;
 	DevBuf<uint32_t> map_counter;
 	int debug_qseg_cap = 0;
+	int debug_gw = SMALL_GROUP_WARPS;
+	int debug_walker = 0; // 0 auto, 1 never, 2 always
+	DevBuf<uint32_t> scratch_tiles, scratch_dist;
 
 	// monsters
 	int nmon = 0;
@@ -264,7 +267,8 @@ namespace
 	}
 
 	// ---- small path launcher -------------------------------------------------------------------------
-	int launch_waypoints_small(mtd_ctx *ctx, WaypointsSmallParams P)
+	template<int GW>
+	int launch_waypoints_small_gw(mtd_ctx *ctx, WaypointsSmallParams P)
 	{
 		const int T = P.W * P.H;
 		P.R = small_resident(P.W, P.H, P.n);
@@ -272,11 +276,11 @@ namespace
 			return fail(ctx, MTD_ERR_CAPACITY, "map of %d tiles with %d layers does not fit shared memory", T, P.n);
 		P.smem_budget = (uint32_t)MAX_SMEM;
 		P.qseg_cap = ctx->debug_qseg_cap;
-		const SmallLayout L = small_layout(T, P.R, P.smem_budget, P.qseg_cap);
+		const SmallLayout L = small_layout(T, P.R, P.smem_budget, P.qseg_cap, GW);
 		static bool configured = false;
 		if (!configured)
 		{
-			CU(cudaFuncSetAttribute(k_waypoints_small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MAX_SMEM));
+			CU(cudaFuncSetAttribute(k_waypoints_small<GW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MAX_SMEM));
 			configured = true;
 		}
 		CU(ctx->map_counter.reserve(1));
@@ -284,10 +288,41 @@ namespace
 		P.map_counter = ctx->map_counter.p;
 		const int per_sm = L.total * 2 + 2048 <= MAX_SMEM ? 2 : 1;
 		const int blocks = P.nmaps < ctx->sms * per_sm ? P.nmaps : ctx->sms * per_sm;
+		// paths: a CTA that owns several maps hands the walks to its walker warp, which chases the layers in global memory
+		const bool want_walks = P.fullpath_len && P.nsrc <= 1;
+		P.walker = want_walks && ((P.nmaps > blocks && ctx->debug_walker != 1) || ctx->debug_walker == 2) ? 1 : 0;
+		if (want_walks && (P.walker || P.n > P.R) && (!P.tiles || !P.dist))
+		{
+			// the caller did not ask for the layers: keep them in library-owned scratch
+			const size_t need = (size_t)P.nmaps * P.n * T;
+			if (!P.tiles)
+			{
+				CU(ctx->scratch_tiles.reserve(need));
+				P.tiles = ctx->scratch_tiles.p;
+			}
+			if (!P.dist)
+			{
+				CU(ctx->scratch_dist.reserve(need));
+				P.dist = ctx->scratch_dist.p;
+			}
+		}
 		ProfScope prof(ctx, MTD_K_WAYPOINTS_SMALL);
-		k_waypoints_small<<<blocks, SMALL_THREADS, L.total, ctx->stream>>>(P);
+		k_waypoints_small<GW><<<blocks, SMALL_THREADS + 32, L.total, ctx->stream>>>(P);
 		LAUNCHED();
 		return MTD_OK;
+	}
+
+	int launch_waypoints_small(mtd_ctx *ctx, const WaypointsSmallParams &P)
+	{
+		switch (ctx->debug_gw)
+		{
+		case 1:
+			return launch_waypoints_small_gw<1>(ctx, P);
+		case 4:
+			return launch_waypoints_small_gw<4>(ctx, P);
+		default:
+			return launch_waypoints_small_gw<2>(ctx, P);
+		}
 	}
 
 	// ---- big path -----------------------------------------------------------------------------------
@@ -547,7 +582,7 @@ namespace
 			if (!small_path)
 			{
 				// large grid: the walks run on the layers in global memory
-				k_walk_global<<<1, 32 * n, 0, ctx->stream>>>(layers_view(ctx), fullpath_cap ? ctx->fp_buf.p : nullptr, fullpath_cap, ctx->fp_len.p, ctx->fp_dist.p, ctx->agg.p, ctx->d_status.p);
+				k_walk_global<<<1, 32, 0, ctx->stream>>>(layers_view(ctx), fullpath_cap ? ctx->fp_buf.p : nullptr, fullpath_cap, ctx->fp_len.p, ctx->fp_dist.p, ctx->agg.p, ctx->d_status.p);
 				LAUNCHED();
 			}
 		}
@@ -683,6 +718,14 @@ extern "C" int mtd_debug_set(mtd_ctx *ctx, int key, int64_t value)
 	{
 	case MTD_DEBUG_QSEG_CAP:
 		ctx->debug_qseg_cap = (int)value;
+		return MTD_OK;
+	case MTD_DEBUG_GROUP_WARPS:
+		if (value != 1 && value != 2 && value != 4)
+			return fail(ctx, MTD_ERR_ARG, "group warps must be 1, 2 or 4");
+		ctx->debug_gw = (int)value;
+		return MTD_OK;
+	case MTD_DEBUG_WALKER:
+		ctx->debug_walker = (int)value;
 		return MTD_OK;
 	default:
 		return fail(ctx, MTD_ERR_ARG, "unknown debug key %d", key);

@@ -7,6 +7,7 @@
 
 #include "common.cuh"
 #include "sssp_warp.cuh"
+#include "walk.cuh"
 
 namespace mtd
 {
@@ -148,58 +149,45 @@ namespace mtd
 	}
 
 	// Full-path walks + aggregates of Waypoints::update (sources/map/paths.cpp:87-139) on layers resident in global
-	// memory (grids too large for the one-CTA kernel). One lane per spawner: a dependent chase through the next-hop
-	// layers, find() per hop exactly like the reference. Launch: 1 block of 32 * n threads.
+	// memory (grids too large for the one-CTA kernel). One warp, lane s walks spawner s (walk.cuh). Launch: <<<1, 32>>>.
 	__global__ void k_walk_global(LayersView L, uint32_t *fullpath, uint32_t cap, uint32_t *fullpath_len, uint32_t *full_distance, uint32_t *agg, int *status)
 	{
-		__shared__ uint32_t s_fd[FIND_MAXN];
-		const int s = threadIdx.x >> 5;
+		__shared__ uint32_t s_fd[FIND_MAXN], s_wp[FIND_MAXN], s_D[FIND_MAXN * FIND_MAXN];
+		const uint32_t lane = lane_id();
+		const int n = L.n;
 		const size_t T = (size_t)L.W * L.H;
-		if (s < L.n && (threadIdx.x & 31) == 0)
+		GlobalLayersAcc acc;
+		acc.gdist = L.dist;
+		acc.gtiles = L.tiles;
+		acc.gelev = L.elev;
+		acc.T = T;
+		if ((int)lane < n)
+			s_wp[lane] = L.wp[lane];
+		for (int i = (int)lane; i < FIND_MAXN * FIND_MAXN; i += 32)
+			s_D[i] = L.Dtab[i];
+		__syncwarp();
+		const bool table_fast = walk_table_fast(n, s_D);
+		WalkResult r;
+		r.len = 0;
+		r.distance = 0;
+		if ((int)lane < n)
 		{
-			uint32_t *path = fullpath ? fullpath + (size_t)s * cap : nullptr;
-			uint32_t bits = 0, prev = MTD_INF, distance = 0, len = 0;
-			uint32_t tile = L.wp[s];
-			while (tile != MTD_INF)
-			{
-				for (int k = 0; k < L.n; k++)
-					if (L.wp[k] == tile)
-						bits |= 1u << k;
-				if (path && len < cap)
-					path[len] = tile;
-				len++;
-				if (prev != MTD_INF)
-					distance += edge_weight(L.elev[prev], L.elev[tile]); // Grid::neighborDistance of adjacent tiles
-				prev = tile;
-				uint32_t d;
-				device_find(L, tile, bits, tile, d);
-				if ((size_t)len > T * (size_t)L.n + 8u)
-					break; // cannot happen on consistent layers
-			}
-			if (path)
-				for (uint32_t i = len; i < cap; i++)
-					path[i] = MTD_INF;
-			if (fullpath && len > cap)
+			uint32_t *path = fullpath ? fullpath + (size_t)lane * cap : nullptr;
+			const size_t maxlen = T * (size_t)n + 8u;
+			r = walk_path(n, s_wp, s_D, table_fast, (int)lane, acc, path, cap, maxlen > 0xFFFFFFF0ull ? 0xFFFFFFF0u : (uint32_t)maxlen);
+			if (fullpath && r.len > cap)
 				atomicOr(status, 4); // ST_PATH_TRUNC
-			fullpath_len[s] = len;
-			full_distance[s] = distance;
-			s_fd[s] = distance;
+			fullpath_len[lane] = r.len;
+			full_distance[lane] = r.distance;
+			s_fd[lane] = r.distance;
 		}
-		__syncthreads();
-		if (threadIdx.x == 0)
-		{
-			uint32_t sum = 0;
-			for (int i = 0; i < L.n; i++)
-				sum += s_fd[i];
-			const float avg = __fdiv_rn(stor((int32_t)sum), (float)(unsigned long long)L.n);
-			uint32_t best = 0;
-			for (int i = 0; i < L.n; i++)
-				if (s_fd[i] < s_fd[best])
-					best = (uint32_t)i;
-			agg[0] = (uint32_t)__float2ll_rz(avg);
-			agg[1] = (uint32_t)__float2ll_rz(stor((int32_t)s_fd[best]));
-			agg[2] = best;
-		}
+		__syncwarp();
+		if (fullpath)
+			for (int s = 0; s < n; s++)
+				for (uint32_t i = __shfl_sync(FULL_MASK, r.len, s) + lane; i < cap; i += 32u)
+					fullpath[(size_t)s * cap + i] = MTD_INF;
+		if (lane == 0)
+			walk_aggregates(n, s_fd, agg);
 	}
 
 	// buildingsPlacement.cpp:30-41 on a trial distance layer

@@ -16,6 +16,7 @@
 
 #include "common.cuh"
 #include "sssp_warp.cuh"
+#include "walk.cuh"
 
 namespace mtd
 {
@@ -27,7 +28,8 @@ namespace mtd
 	};
 
 	constexpr int SMALL_THREADS = 512;
-	constexpr int SMALL_GROUP_WARPS = 4;   // warps cooperating on one layer
+	constexpr int SMALL_GROUP_WARPS = 2;   // default number of warps cooperating on one layer (template parameter GW: 1, 2 or 4)
+	constexpr int SMALL_WALKER_WARP = SMALL_THREADS / 32; // the extra warp that walks the previous map's paths
 	constexpr int SMALL_MAX_RESIDENT = 4;  // layers concurrently in shared memory
 	constexpr int MTD_MAXSRC_SMALL = 32;
 	constexpr int SMALL_OUT_CHUNK = 128;   // cells per write-out work item
@@ -54,6 +56,8 @@ namespace mtd
 		uint32_t *map_counter;   // zeroed before the launch
 		uint32_t smem_budget;    // dynamic shared memory of the launch
 		int qseg_cap;            // > 0 caps the queue segment size (tests force the dense fallback with it)
+		int walker;              // != 0: paths are walked by the walker warp on the layers in global memory (needs tiles + dist),
+		                         //       one map behind the workers; 0: the workers walk the resident layers themselves
 	};
 
 	// ---- shared memory layout (byte offsets), identical on host and device ---------------------------------
@@ -68,7 +72,7 @@ namespace mtd
 		return (v + 15u) & ~15u;
 	}
 
-	__host__ __device__ inline SmallLayout small_layout(int T, int R, uint32_t budget, int qseg_cap)
+	__host__ __device__ inline SmallLayout small_layout(int T, int R, uint32_t budget, int qseg_cap, int gw = SMALL_GROUP_WARPS)
 	{
 		SmallLayout L;
 		uint32_t o = 0;
@@ -89,7 +93,7 @@ namespace mtd
 		L.dtab = o;
 		o += FIND_MAXN * FIND_MAXN * 4u;
 		L.q = o;
-		const uint32_t per_entry = (uint32_t)R * 2u * SMALL_GROUP_WARPS * 2u; // layers x parities x segments x sizeof(u16)
+		const uint32_t per_entry = (uint32_t)R * 2u * (uint32_t)gw * 2u; // layers x parities x segments x sizeof(u16)
 		int qseg = budget > o ? (int)((budget - o) / per_entry) : 0;
 		qseg &= ~7;
 		if (qseg > 2048)
@@ -230,13 +234,13 @@ namespace mtd
 		return o;
 	}
 
-	// ---- one layer, SMALL_GROUP_WARPS warps -----------------------------------------------------------------------
+	// ---- one layer, GW warps ---------------------------------------------------------------------------------------
 	// ctl: [parity][0..3] = entries each warp appended for the round that reads `parity`, [parity][4..7] = min pending
 	// label each warp saw. q: [parity][warp][qseg] packed cells. Initial state (parity 0) is written by the caller.
 	// Returns true if a label hit the guard band.
+	template<int GW>
 	__device__ bool group_relax(uint32_t *dist, const uint16_t *wr, const uint16_t *wd, uint16_t *q, uint32_t *ctl, int W, int H, int T, int qseg, uint32_t magicW, int gw, uint32_t lane, int bar_id)
 	{
-		constexpr int GW = SMALL_GROUP_WARPS;
 		const uint32_t lt = lanemask_lt();
 		uint32_t parity = 0, thr_prev = 0;
 		bool guard = false, dense = false;
@@ -322,7 +326,10 @@ namespace mtd
 				ctl[(parity ^ 1u) * 8 + (uint32_t)gw] = outn;
 				ctl[(parity ^ 1u) * 8 + 4 + (uint32_t)gw] = newmin;
 			}
-			group_barrier(bar_id, GW * 32);
+			if (GW == 1)
+				__syncwarp();
+			else
+				group_barrier(bar_id, GW * 32);
 			thr_prev = thr;
 			parity ^= 1u;
 		}
@@ -363,74 +370,87 @@ namespace mtd
 		return best;
 	}
 
-	// Waypoints::find on registers: unvisited ids come from bit scans (no local array), k <= 3 is unrolled in
-	// lexicographic permutation order, larger k falls back to find_best's next_permutation loop.
-	template<class DistAtPos>
-	__device__ __forceinline__ FindResult find_small(int n, uint32_t bits, const uint32_t *D, DistAtPos A)
+	// layers held in shared memory: next-hop tiles are derived from the final distances on the fly
+	struct SmemLayersAcc
 	{
-		uint32_t m = ~bits & (n >= 32 ? 0xFFFFFFFFu : ((1u << n) - 1u));
-		const int k = __popc(m);
-		if (k > 3)
-			return find_best(n, bits, D, A);
-		FindResult r;
-		r.layer = MTD_INF;
-		r.distance = MTD_INF;
-		if (k == 0)
-			return r;
-		const uint32_t a = (uint32_t)__ffs((int)m) - 1u;
-		m &= m - 1u;
-		const uint32_t Aa = A(a);
-		if (k == 1)
+		const uint32_t *sdist; // [R][T]
+		const uint16_t *wr, *wd;
+		int W, H, T;
+		uint32_t magicW;
+		__device__ __forceinline__ uint32_t dist(uint32_t l, uint32_t t) const { return sdist[(size_t)l * T + t]; }
+		__device__ __forceinline__ uint32_t hop(uint32_t l, uint32_t t) const
 		{
-			if (Aa < r.distance)
-			{
-				r.distance = Aa;
-				r.layer = a;
-			}
-			return r;
+			const int y = (int)div_w(t, magicW), x = (int)t - y * W;
+			return next_hop(sdist + (size_t)l * T, wr, wd, W, H, x, y);
 		}
-		const uint32_t b = (uint32_t)__ffs((int)m) - 1u;
-		m &= m - 1u;
-		const uint32_t Ab = A(b);
-#define MTD_D(p, q) D[(p) * FIND_MAXN + (q)]
-		if (k == 2)
+		__device__ __forceinline__ uint32_t edge(uint32_t a, uint32_t b) const
 		{
-			const uint32_t c0 = Aa + MTD_D(a, b), c1 = Ab + MTD_D(b, a);
-			if (c0 < r.distance)
-			{
-				r.distance = c0;
-				r.layer = a;
-			}
-			if (c1 < r.distance)
-			{
-				r.distance = c1;
-				r.layer = b;
-			}
-			return r;
+			const uint32_t lo = a < b ? a : b, hi = a < b ? b : a;
+			return MIN_EDGE + (hi - lo == 1u ? wr[lo] : wd[lo]);
 		}
-		const uint32_t c = (uint32_t)__ffs((int)m) - 1u;
-		const uint32_t Ac = A(c);
-		const uint32_t dab = MTD_D(a, b), dac = MTD_D(a, c), dba = MTD_D(b, a), dbc = MTD_D(b, c), dca = MTD_D(c, a), dcb = MTD_D(c, b);
-#undef MTD_D
-		const uint32_t cost[6] = { Aa + dab + dbc, Aa + dac + dcb, Ab + dba + dac, Ab + dbc + dca, Ac + dca + dab, Ac + dcb + dba };
-		const uint32_t first[6] = { a, a, b, b, c, c };
-#pragma unroll
-		for (int p = 0; p < 6; p++)
-			if (cost[p] < r.distance)
+	};
+
+	// barrier of the 512 worker threads (the walker warp never takes part)
+	__device__ __forceinline__ void workers_sync()
+	{
+		group_barrier(1, SMALL_THREADS);
+	}
+
+	// Full-path walks + aggregates of one map on layers resident in global memory, by ONE warp: lane s walks spawner s
+	// (the dependent loads of the n chases overlap), then all lanes pad the path buffers. wp/D/fd: scratch in shared memory.
+	__device__ void walk_map_global(const WaypointsSmallParams &P, int mapi, uint32_t *wp, uint32_t *D, uint32_t *fd, uint32_t lane)
+	{
+		const int n = P.n;
+		const size_t T = (size_t)P.W * P.H;
+		GlobalLayersAcc acc;
+		acc.gdist = P.dist + (size_t)mapi * n * T;
+		acc.gtiles = P.tiles + (size_t)mapi * n * T;
+		acc.gelev = P.elev + (size_t)mapi * T;
+		acc.T = T;
+		if ((int)lane < n)
+			wp[lane] = P.wp[(size_t)mapi * n + lane];
+		__syncwarp();
+		for (int i = (int)lane; i < n * n; i += 32)
+		{
+			const int a = i / n, b = i % n;
+			D[a * FIND_MAXN + b] = acc.dist((uint32_t)b, wp[a]);
+		}
+		__syncwarp();
+		const bool table_fast = walk_table_fast(n, D);
+		WalkResult r;
+		r.len = 0;
+		r.distance = 0;
+		if ((int)lane < n)
+		{
+			uint32_t *path = P.fullpath ? P.fullpath + ((size_t)mapi * n + lane) * P.cap : nullptr;
+			r = walk_path(n, wp, D, table_fast, (int)lane, acc, path, P.cap, (uint32_t)T * (uint32_t)n + 8u);
+			if (P.fullpath && r.len > P.cap)
+				atomicOr(P.status, ST_PATH_TRUNC);
+			P.fullpath_len[(size_t)mapi * n + lane] = r.len;
+			P.full_distance[(size_t)mapi * n + lane] = r.distance;
+			fd[lane] = r.distance;
+		}
+		__syncwarp();
+		if (P.fullpath)
+			for (int s = 0; s < n; s++)
 			{
-				r.distance = cost[p];
-				r.layer = first[p];
+				uint32_t *path = P.fullpath + ((size_t)mapi * n + s) * P.cap;
+				for (uint32_t i = __shfl_sync(FULL_MASK, r.len, s) + lane; i < P.cap; i += 32u)
+					st_stream_u32(path + i, MTD_INF);
 			}
-		return r;
+		if (lane == 0)
+			walk_aggregates(n, fd, P.agg + (size_t)mapi * 3);
+		__syncwarp();
 	}
 
 	// =============================================================================================================
-	__global__ void __launch_bounds__(SMALL_THREADS, 1) k_waypoints_small(const WaypointsSmallParams P)
+	// 512 worker threads + 1 walker warp. GW = warps cooperating on one layer during the relaxation.
+	template<int GW>
+	__global__ void __launch_bounds__(SMALL_THREADS + 32, 1) k_waypoints_small(const WaypointsSmallParams P)
 	{
 		extern __shared__ __align__(16) unsigned char smem_raw[];
-		constexpr int GW = SMALL_GROUP_WARPS;
 		const int W = P.W, H = P.H, T = W * H, n = P.n, R = P.R;
-		const SmallLayout L = small_layout(T, R, P.smem_budget, P.qseg_cap);
+		const SmallLayout L = small_layout(T, R, P.smem_budget, P.qseg_cap, GW);
 		uint32_t *sdist = (uint32_t *)(smem_raw + L.dist);
 		uint16_t *wr = (uint16_t *)(smem_raw + L.wr);
 		uint16_t *wd = (uint16_t *)(smem_raw + L.wd);
@@ -444,6 +464,8 @@ namespace mtd
 		__shared__ uint32_t s_wp[MTD_MAXSRC_SMALL];
 		__shared__ int s_guard;
 		__shared__ uint32_t s_map, s_chunk;
+		// the walker warp's private copies (it works on the PREVIOUS map while the workers overwrite the above)
+		__shared__ uint32_t w_wp[FIND_MAXN], w_D[FIND_MAXN * FIND_MAXN], w_fd[FIND_MAXN];
 
 		const int tid = threadIdx.x;
 		const int warp = tid >> 5;
@@ -453,7 +475,9 @@ namespace mtd
 		const int nwp = P.nsrc > 1 ? P.nsrc : n;
 		const uint32_t magicW = W > 1 ? (uint32_t)((0x100000000ull + (uint32_t)W - 1u) / (uint32_t)W) : 0u; // y = umulhi(i, magicW) for i < 65536, W <= 256
 		const uint32_t stage_half = align16u((uint32_t)(T + 8) * 2u);
+		const bool want_walks = P.fullpath_len && P.nsrc <= 1;
 		uint32_t mbar_phase = 0;
+		int walker_prev = -1;
 
 		if (tid == 0)
 		{
@@ -463,11 +487,21 @@ namespace mtd
 
 		for (;;)
 		{
-			__syncthreads(); // the previous map is completely written out; shared memory is free
+			__syncthreads(); // all 544 threads: the previous map is completely written out and the walker finished the one before
 			if (tid == 0)
 				s_map = atomicAdd(P.map_counter, 1u);
 			__syncthreads();
 			const int mapi = (int)s_map;
+			if (warp == SMALL_WALKER_WARP)
+			{
+				// ---- walker warp: paths of the map the workers finished last, from its layers in global memory (still in L2) ----
+				if (P.walker && want_walks && walker_prev >= 0)
+					walk_map_global(P, walker_prev, w_wp, w_D, w_fd, lane);
+				if (mapi >= P.nmaps)
+					break;
+				walker_prev = mapi;
+				continue;
+			}
 			if (mapi >= P.nmaps)
 				break;
 			const int16_t *ge = P.elev + (size_t)mapi * T;
@@ -516,7 +550,7 @@ namespace mtd
 				}
 				mbar_wait(&s_mbar, mbar_phase);
 				mbar_phase ^= 1u;
-				__syncthreads();
+				workers_sync();
 			}
 
 			// ---- 2. edge weights (Grid::neighborDistance of the right and down edge, grid.cpp:141-145) + blocking bitmap ----
@@ -536,7 +570,7 @@ namespace mtd
 				if (lane == 0 && base + warp * 32 < T)
 					blk[(base >> 5) + warp] = bal;
 			}
-			__syncthreads(); // staging is dead from here on: the distance layers take its place
+			workers_sync(); // staging is dead from here on: the distance layers take its place
 
 			for (int l0 = 0; l0 < n; l0 += R)
 			{
@@ -548,7 +582,7 @@ namespace mtd
 					for (int r = 0; r < lb; r++)
 						sdist[(size_t)r * T + i] = v;
 				}
-				__syncthreads();
+				workers_sync();
 				// seeds: paths.cpp:48-49 (a blocked source still expands: the popped tile is never tested, paths.cpp:63-67)
 				if (warp < lb * GW && (warp % GW) == 0 && lane == 0)
 				{
@@ -575,17 +609,20 @@ namespace mtd
 					c[1] = c[2] = c[3] = 0u;
 					c[4] = 0u;
 					c[5] = c[6] = c[7] = MTD_INF;
+					// slots of warps that do not exist (GW < 4) stay empty in both parities
+					c[8] = c[9] = c[10] = c[11] = 0u;
+					c[12] = c[13] = c[14] = c[15] = MTD_INF;
 				}
-				__syncthreads();
+				workers_sync();
 
-				// ---- 3b. relaxation: four warps per layer, one named barrier per bucket ----
+				// ---- 3b. relaxation: GW warps per layer, one named barrier per bucket ----
 				if (warp < lb * GW)
 				{
 					const int g = warp / GW;
-					if (group_relax(sdist + (size_t)g * T, wr, wd, q + (size_t)g * 2 * GW * qseg, ctl + g * 16, W, H, T, qseg, magicW, warp % GW, lane, 1 + g) && lane == 0)
+					if (group_relax<GW>(sdist + (size_t)g * T, wr, wd, q + (size_t)g * 2 * GW * qseg, ctl + g * 16, W, H, T, qseg, magicW, warp % GW, lane, 2 + g) && lane == 0)
 						s_guard = 1;
 				}
-				__syncthreads();
+				workers_sync();
 
 				// ---- 3c. blocked, non-source tiles read "unreachable" (they were never relaxed: paths.cpp:65-67) ----
 				for (int i = tid; i < T; i += SMALL_THREADS)
@@ -604,7 +641,7 @@ namespace mtd
 							sdist[(size_t)r * T + i] = MTD_INF;
 					}
 				}
-				const bool walk_now = resident_all && P.fullpath_len && P.nsrc <= 1;
+				const bool walk_now = want_walks && !P.walker && resident_all; // single map: walk the resident layers while they are written out
 				if (walk_now && tid < n * n)
 				{
 					// inter-waypoint table D[a][b] = dist_b[wp_a]; a waypoint tile is either open or the source of its own layer,
@@ -617,44 +654,28 @@ namespace mtd
 						v = MTD_INF;
 					Dtab[a * FIND_MAXN + b] = v;
 				}
-				__syncthreads();
+				workers_sync();
 
 				// ---- 4. full-path walks (one lane per spawner) overlapped with next-hop tiles + write-out of this pass ----
 				uint32_t walk_len = 0;
 				if (walk_now && warp < n && lane == 0)
 				{
+					SmemLayersAcc acc;
+					acc.sdist = sdist;
+					acc.wr = wr;
+					acc.wd = wd;
+					acc.W = W;
+					acc.H = H;
+					acc.T = T;
+					acc.magicW = magicW;
 					uint32_t *path = P.fullpath ? P.fullpath + ((size_t)mapi * n + warp) * P.cap : nullptr;
-					uint32_t bits = 0, prev = MTD_INF, distance = 0, len = 0;
-					uint32_t tile = s_wp[warp];
-					while (tile != MTD_INF)
-					{
-						for (int k = 0; k < n; k++)
-							if (s_wp[k] == tile)
-								bits |= 1u << k;
-						if (path && len < P.cap)
-							path[len] = tile;
-						len++;
-						if (prev != MTD_INF)
-						{
-							// Grid::neighborDistance(prev, tile) for adjacent tiles = stored edge weight
-							const uint32_t lo = prev < tile ? prev : tile, hi = prev < tile ? tile : prev;
-							distance += MIN_EDGE + (hi - lo == 1u ? wr[lo] : wd[lo]);
-						}
-						prev = tile;
-						const FindResult fr = find_small(n, bits, Dtab, [&](uint32_t i) { return sdist[(size_t)i * T + tile]; });
-						if (fr.layer == MTD_INF)
-							break;
-						const int y = (int)div_w(tile, magicW), x = (int)tile - y * W;
-						tile = next_hop(sdist + (size_t)fr.layer * T, wr, wd, W, H, x, y);
-						if (len > (uint32_t)T * (uint32_t)n + 8u)
-							break; // cannot happen on consistent layers; guards against a hang on corrupted input
-					}
-					if (P.fullpath && len > P.cap)
+					const WalkResult r = walk_path(n, s_wp, Dtab, walk_table_fast(n, Dtab), warp, acc, path, P.cap, (uint32_t)T * (uint32_t)n + 8u);
+					if (P.fullpath && r.len > P.cap)
 						atomicOr(P.status, ST_PATH_TRUNC);
-					P.fullpath_len[(size_t)mapi * n + warp] = len;
-					P.full_distance[(size_t)mapi * n + warp] = distance;
-					s_fd[warp] = distance;
-					walk_len = len;
+					P.fullpath_len[(size_t)mapi * n + warp] = r.len;
+					P.full_distance[(size_t)mapi * n + warp] = r.distance;
+					s_fd[warp] = r.distance;
+					walk_len = r.len;
 				}
 				__syncwarp();
 				if (walk_now && warp < n && P.fullpath)
@@ -701,130 +722,28 @@ namespace mtd
 						}
 					}
 				}
-				__syncthreads();
+				workers_sync();
 				if (tid == 0)
 					s_chunk = 0;
 			}
 
 			if (s_guard && tid == 0)
 				atomicOr(P.status, ST_GUARD);
-			if (!P.fullpath_len || P.nsrc > 1)
+			if (!want_walks || P.walker)
 				continue;
 
 			if (!resident_all)
 			{
-				// more layers than fit: walk on the layers just written to global memory (L2)
-				__threadfence_block();
-				for (int i = tid; i < n * n; i += SMALL_THREADS)
-				{
-					const int a = i / n, b = i % n;
-					Dtab[a * FIND_MAXN + b] = __ldcg(gdist + (size_t)b * T + s_wp[a]);
-				}
-				__syncthreads();
-				uint32_t walk_len2 = 0;
-				if (warp < n && lane == 0)
-				{
-					uint32_t *path = P.fullpath ? P.fullpath + ((size_t)mapi * n + warp) * P.cap : nullptr;
-					uint32_t bits = 0, prev = MTD_INF, distance = 0, len = 0;
-					uint32_t tile = s_wp[warp];
-					while (tile != MTD_INF)
-					{
-						for (int k = 0; k < n; k++)
-							if (s_wp[k] == tile)
-								bits |= 1u << k;
-						if (path && len < P.cap)
-							path[len] = tile;
-						len++;
-						if (prev != MTD_INF)
-						{
-							const uint32_t lo = prev < tile ? prev : tile, hi = prev < tile ? tile : prev;
-							distance += MIN_EDGE + (hi - lo == 1u ? wr[lo] : wd[lo]);
-						}
-						prev = tile;
-						const FindResult fr = find_small(n, bits, Dtab, [&](uint32_t i) { return __ldcg(gdist + (size_t)i * T + tile); });
-						if (fr.layer == MTD_INF)
-							break;
-						const int y = (int)div_w(tile, magicW), x = (int)tile - y * W;
-						// same closed form as next_hop(), on L2-resident distances
-						const uint32_t *dl = gdist + (size_t)fr.layer * T;
-						const uint32_t dv = __ldcg(dl + tile);
-						uint32_t best = MTD_INF, bestd = MTD_INF;
-						if (dv != MTD_INF && dv != 0u)
-						{
-							if (y > 0)
-							{
-								const uint32_t du = __ldcg(dl + tile - W);
-								if (du != MTD_INF && du + MIN_EDGE + wd[tile - W] == dv && du < bestd)
-								{
-									bestd = du;
-									best = tile - (uint32_t)W;
-								}
-							}
-							if (x > 0)
-							{
-								const uint32_t du = __ldcg(dl + tile - 1);
-								if (du != MTD_INF && du + MIN_EDGE + wr[tile - 1] == dv && du < bestd)
-								{
-									bestd = du;
-									best = tile - 1u;
-								}
-							}
-							if (x < W - 1)
-							{
-								const uint32_t du = __ldcg(dl + tile + 1);
-								if (du != MTD_INF && du + MIN_EDGE + wr[tile] == dv && du < bestd)
-								{
-									bestd = du;
-									best = tile + 1u;
-								}
-							}
-							if (y < H - 1)
-							{
-								const uint32_t du = __ldcg(dl + tile + W);
-								if (du != MTD_INF && du + MIN_EDGE + wd[tile] == dv && du < bestd)
-								{
-									bestd = du;
-									best = tile + (uint32_t)W;
-								}
-							}
-						}
-						tile = best;
-						if (len > (uint32_t)T * (uint32_t)n + 8u)
-							break;
-					}
-					if (P.fullpath && len > P.cap)
-						atomicOr(P.status, ST_PATH_TRUNC);
-					P.fullpath_len[(size_t)mapi * n + warp] = len;
-					P.full_distance[(size_t)mapi * n + warp] = distance;
-					s_fd[warp] = distance;
-					walk_len2 = len;
-				}
-				__syncwarp();
-				if (warp < n && P.fullpath)
-				{
-					uint32_t *path = P.fullpath + ((size_t)mapi * n + warp) * P.cap;
-					for (uint32_t i = __shfl_sync(FULL_MASK, walk_len2, 0) + lane; i < P.cap; i += 32u)
-						st_stream_u32(path + i, MTD_INF);
-				}
-				__syncthreads();
+				// single map with more layers than fit: walk the layers just written to global memory (L2), warp 0
+				workers_sync(); // every warp's stores of the last pass are done
+				if (warp == 0)
+					walk_map_global(P, mapi, w_wp, w_D, w_fd, lane);
+				continue;
 			}
 
 			// ---- 5. aggregates: paths.cpp:122-138 ----
 			if (tid == 0)
-			{
-				uint32_t sum = 0;
-				for (int i = 0; i < n; i++)
-					sum += s_fd[i];
-				const float avg = __fdiv_rn(stor((int32_t)sum), (float)(unsigned long long)n);
-				uint32_t best = 0;
-				for (int i = 0; i < n; i++)
-					if (s_fd[i] < s_fd[best])
-						best = (uint32_t)i;
-				uint32_t *ag = P.agg + (size_t)mapi * 3;
-				ag[0] = (uint32_t)__float2ll_rz(avg);
-				ag[1] = (uint32_t)__float2ll_rz(stor((int32_t)s_fd[best]));
-				ag[2] = best;
-			}
+				walk_aggregates(n, s_fd, P.agg + (size_t)mapi * 3);
 		}
 	}
 }

@@ -385,6 +385,57 @@ def test_mapgen_batch_bit_exact(ctx, oracle):
             assert np.array_equal(g[key][k], o[key]), (k, key)
 
 
+@pytest.mark.parametrize("gw", [1, 2, 4])
+@pytest.mark.parametrize("walker", [1, 2])
+def test_mapgen_batch_walker_warp_and_group_widths(ctx, oracle, gw, walker):
+    """the batched kernel's variants -- 1/2/4 warps per layer, paths walked by the workers (1) or by the walker warp on the
+    previous map's layers in global memory (2) -- must all produce the reference's bits"""
+    n = 10
+    try:
+        ctx.debug_set(ctx.DEBUG_GROUP_WARPS, gw)
+        ctx.debug_set(ctx.DEBUG_WALKER, walker)
+        g = ctx.mapgen_batch(KAT_SEED[0], KAT_SEED[1], 100, n, cap=2048)
+    finally:
+        ctx.debug_set(ctx.DEBUG_GROUP_WARPS, 2)
+        ctx.debug_set(ctx.DEBUG_WALKER, 0)
+    for k in range(n):
+        o = oracle.mapgen(KAT_SEED[0] + 100 + k, KAT_SEED[1], cap=2048)
+        for key in ("elev", "flags", "wp_tiles", "dist", "tiles", "fullpath_len", "full_distance", "agg", "fullpath"):
+            assert np.array_equal(g[key][k], o[key]), (k, key)
+
+
+def test_mapgen_batch_many_maps_per_cta(ctx, oracle):
+    """more maps than CTAs: every CTA loops over several maps and its walker warp runs one map behind"""
+    n = 700
+    g = ctx.mapgen_batch(KAT_SEED[0], KAT_SEED[1], 1000, n, cap=1024)
+    for k in list(range(0, n, 37)) + [n - 1]:
+        o = oracle.mapgen(KAT_SEED[0] + 1000 + k, KAT_SEED[1], cap=1024)
+        for key in ("elev", "flags", "wp_tiles", "dist", "tiles", "fullpath_len", "full_distance", "agg", "fullpath"):
+            assert np.array_equal(g[key][k], o[key]), (k, key)
+
+
+@pytest.mark.parametrize("walker", [1, 2])
+def test_walks_with_unreachable_waypoints_take_the_per_hop_path(ctx, oracle, walker):
+    """a wall splits the map: some inter-waypoint distances are m, find()'s uint32 sums wrap, and the walk must follow the
+    reference's per-hop evaluation instead of the segment shortcut"""
+    W, H = 40, 30
+    rng = np.random.default_rng(3)
+    elev = rng.integers(-100, 100, W * H).astype(np.int16)
+    flags = np.zeros(W * H, np.uint16)
+    flags[np.arange(H) * W + 20] = synth.FLAG_BUILDING  # full-height wall at x = 20
+    for wp in ([5 * W + 3, 9 * W + 30, 20 * W + 10, 25 * W + 35], [5 * W + 3, 20 * W + 10, 9 * W + 30], [2 * W + 2, 3 * W + 20, 4 * W + 8]):
+        wp = np.array(wp, np.uint32)
+        ctx.grid_upload(W, H, elev, flags)
+        try:
+            ctx.debug_set(ctx.DEBUG_WALKER, walker)
+            g = ctx.waypoints_update(wp)
+        finally:
+            ctx.debug_set(ctx.DEBUG_WALKER, 0)
+        o = oracle.waypoints_update(W, H, elev, flags, wp)
+        for k in ("dist", "tiles", "fullpath_len", "full_distance", "agg", "fullpath"):
+            assert np.array_equal(g[k], o[k]), (list(wp), k)
+
+
 def test_mapgen_batch_vs_reference_code(ctx, ref):
     g = ctx.mapgen_batch(KAT_SEED[0], KAT_SEED[1], 40, 3, cap=2048)
     for j in range(3):
