@@ -318,10 +318,10 @@ namespace
 		{
 		case 1:
 			return launch_waypoints_small_gw<1>(ctx, P);
-		case 4:
-			return launch_waypoints_small_gw<4>(ctx, P);
-		default:
+		case 2:
 			return launch_waypoints_small_gw<2>(ctx, P);
+		default:
+			return launch_waypoints_small_gw<4>(ctx, P);
 		}
 	}
 

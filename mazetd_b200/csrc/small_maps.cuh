@@ -82,6 +82,8 @@ namespace mtd
 		__shared__ Rng rng;
 		__shared__ unsigned long long best_key;
 
+		const uint32_t magicW = W > 1 ? (uint32_t)((0x100000000ull + (uint32_t)W - 1u) / (uint32_t)W) : 0u; // y = umulhi(i, magicW) for i < 65536, W <= 256
+
 		noise::fill_gradients(grad);
 
 		for (int mapi = blockIdx.x; mapi < P.nmaps; mapi += gridDim.x)
@@ -112,7 +114,7 @@ namespace mtd
 			const noise::ElevationParams lp = ep;
 			for (int i = threadIdx.x; i < T; i += blockDim.x)
 			{
-				const int x = i % W, y = i / W;
+				const int y = (int)div_w((uint32_t)i, magicW), x = i - y * W;
 				float e = noise::elevation(grad, lp, (float)(x - P.ox), (float)(y - P.oy));
 				e = e > -100.0f ? e : -100.0f;
 				e = e < 100.0f ? e : 100.0f;
@@ -123,7 +125,7 @@ namespace mtd
 			// ---- biome flags, slope, radius: grid.cpp:160-183 (thresholds are rtos16(-7), (1), (6), (0.35)) ----
 			for (int i = threadIdx.x; i < T; i += blockDim.x)
 			{
-				const int x = i % W, y = i / W;
+				const int y = (int)div_w((uint32_t)i, magicW), x = i - y * W;
 				const int16_t me = elev[i];
 				uint16_t f = me < (int16_t)-1785 ? F_WATER : me < (int16_t)255 ? F_SUN : me < (int16_t)1530 ? F_WIND : F_SNOW;
 				int16_t r = 0; // maxSlope, grid.cpp:12-27 (int16 wrap semantics kept)
@@ -166,15 +168,37 @@ namespace mtd
 			__syncthreads();
 
 			// ---- fillUnreachable: grid.cpp:29-78 as union-find (root = lowest tile index = discovery order) ----
-			for (int i = threadIdx.x; i < T; i += blockDim.x)
+			// (1) horizontal runs by warp ballot: every valid tile points at the start of its run inside its 32-tile chunk
+			//     (or at the last tile of the previous chunk when the run continues there): chains are <= ceil(W/32)+1 deep
+			//     and no atomics are needed; (2) one union per pair of vertically overlapping runs, not per tile.
+			for (int base = 0; base < T; base += (int)blockDim.x)
 			{
-				if (flags[i] == F_INVALID)
+				const int i = base + (int)threadIdx.x;
+				bool valid = false, linked = false;
+				if (i < T)
+				{
+					valid = flags[i] != F_INVALID;
+					const int y = (int)div_w((uint32_t)i, magicW), x = i - y * W;
+					linked = valid && x > 0 && flags[i - 1] != F_INVALID;
+				}
+				const uint32_t lm = __ballot_sync(FULL_MASK, linked);
+				if (valid)
+				{
+					const uint32_t lane = lane_id();
+					const uint32_t stops = ~lm & (0xFFFFFFFFu >> (31u - lane)); // lanes <= mine that start a run
+					parent[i] = stops ? (uint32_t)(i - (int)lane + (31 - __clz((int)stops))) : (uint32_t)(i - (int)lane - 1);
+				}
+			}
+			__syncthreads();
+			for (int i = threadIdx.x; i < T - W; i += blockDim.x)
+			{
+				if (flags[i] == F_INVALID || flags[i + W] == F_INVALID)
 					continue;
-				const int x = i % W, y = i / W;
-				if (x < W - 1 && flags[i + 1] != F_INVALID)
-					uf_union(parent, (uint32_t)i, (uint32_t)i + 1);
-				if (y < H - 1 && flags[i + W] != F_INVALID)
-					uf_union(parent, (uint32_t)i, (uint32_t)(i + W));
+				const int y = (int)div_w((uint32_t)i, magicW), x = i - y * W;
+				// the pair to the left already joined the same two runs
+				if (x > 0 && flags[i - 1] != F_INVALID && flags[i + W - 1] != F_INVALID)
+					continue;
+				uf_union(parent, (uint32_t)i, (uint32_t)(i + W));
 			}
 			__syncthreads();
 			// flatten, then count members in the upper 16 bits of the root's word (T < 65536)
@@ -186,9 +210,16 @@ namespace mtd
 						parent[i] = r; // benign: only shortens chains, roots are untouched
 				}
 			__syncthreads();
-			for (int i = threadIdx.x; i < T; i += blockDim.x)
-				if (flags[i] != F_INVALID)
-					atomicAdd(&parent[parent[i] & 0xFFFFu], 1u << 16);
+			for (int base = 0; base < T; base += (int)blockDim.x)
+			{
+				const int i = base + (int)threadIdx.x;
+				const bool valid = i < T && flags[i] != F_INVALID;
+				const uint32_t r = valid ? (parent[i] & 0xFFFFu) : 0xFFFFFFFFu;
+				// one atomic per distinct root per warp
+				const uint32_t peers = __match_any_sync(FULL_MASK, r);
+				if (valid && (uint32_t)(__ffs((int)peers) - 1) == lane_id())
+					atomicAdd(&parent[r], (uint32_t)__popc(peers) << 16);
+			}
 			__syncthreads();
 			// largest count; ties -> first discovered = smallest root (grid.cpp:68-72 uses strict '>')
 			{
@@ -218,7 +249,7 @@ namespace mtd
 			// ---- findBorder + Mana: grid.cpp:80-97, 186-196 (border bits only land on invalid tiles, so in-place is safe) ----
 			for (int i = threadIdx.x; i < T; i += blockDim.x)
 			{
-				const int x = i % W, y = i / W;
+				const int y = (int)div_w((uint32_t)i, magicW), x = i - y * W;
 				uint16_t f = flags[i];
 				if (f & F_INVALID)
 				{

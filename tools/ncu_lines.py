@@ -49,6 +49,7 @@ def main():
     ap.add_argument("--lib", default="mazetd_b200/libmazetd_b200.so")
     ap.add_argument("--top", type=int, default=40)
     ap.add_argument("--launch", type=int, default=0, help="which matching launch in the report")
+    ap.add_argument("--fn", default=None, help="regex on the MANGLED function name when the kernel is a template with several instantiations (e.g. ILi2E)")
     a = ap.parse_args()
     raw = subprocess.run(["ncu", "-i", a.report, "--page", "source", "--csv", "--kernel-name", "regex:" + a.kernel], capture_output=True, text=True).stdout
     # the CSV holds one block per launch, each starting with a "Kernel Name" row
@@ -61,7 +62,8 @@ def main():
     col = {h: i for i, h in enumerate(hdr)}
     stall_cols = [h for h in hdr if h.startswith("stall_") and "Not Issued" not in h]
     lines = sass_lines(a.lib, a.kernel)
-    fn = max(lines, key=lambda k: len(lines[k]))
+    cands = [k for k in lines if a.fn is None or re.search(a.fn, k)]
+    fn = max(cands, key=lambda k: len(lines[k]))
     amap = lines[fn]
     base = None
     agg = collections.defaultdict(lambda: [0, 0, collections.Counter()])
