@@ -242,12 +242,12 @@ namespace
 	{
 		if (W > 256 || H > 256 || n < 1)
 			return 0;
-		const size_t T = (size_t)W * H;
-		if (T >= 65536)
+		if ((size_t)(W + 1) * (H + 2) >= 65536) // queue entries are 16-bit indices into the padded frame
 			return 0;
 		for (int R = n < SMALL_MAX_RESIDENT ? n : SMALL_MAX_RESIDENT; R >= 1; R--)
 		{
-			const SmallLayout L = small_layout((int)T, R, (uint32_t)MAX_SMEM, 0);
+			// sized for the widest group (most queue segments), so every GW instantiation fits
+			const SmallLayout L = small_layout(W, H, R, (uint32_t)MAX_SMEM, 0, 4);
 			if (L.qseg >= 64 && L.total <= MAX_SMEM)
 				return R;
 		}
@@ -276,7 +276,7 @@ namespace
 			return fail(ctx, MTD_ERR_CAPACITY, "map of %d tiles with %d layers does not fit shared memory", T, P.n);
 		P.smem_budget = (uint32_t)MAX_SMEM;
 		P.qseg_cap = ctx->debug_qseg_cap;
-		const SmallLayout L = small_layout(T, P.R, P.smem_budget, P.qseg_cap, GW);
+		const SmallLayout L = small_layout(P.W, P.H, P.R, P.smem_budget, P.qseg_cap, GW);
 		static bool configured = false;
 		if (!configured)
 		{

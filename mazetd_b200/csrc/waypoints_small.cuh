@@ -1,16 +1,19 @@
 // waypoints_small.cuh -- fused Waypoints::update (sources/map/paths.cpp:24-139) for maps that fit one CTA's
 // shared memory: the game's 101x101 map and batches of them.
 //
-// One persistent CTA (512 threads) per SM pulls maps from a global counter. Per map:
+// One persistent CTA (512 worker threads + 1 walker warp) per SM pulls maps from a global counter. Per map:
 //   1. TMA bulk copies (cp.async.bulk, mbarrier completion) stage the map's elevations and flags in shared memory
 //   2. edge weights = Grid::neighborDistance of every right/down edge (sources/map/grid.cpp:141-145), blocking bitmap
-//   3. up to SMALL_MAX_RESIDENT distance layers are relaxed concurrently, FOUR WARPS PER LAYER:
+//   3. up to SMALL_MAX_RESIDENT distance layers are relaxed concurrently, GW warps per layer:
 //        bucketed wavefront, bucket width 255 = lower bound of every edge weight, so a settled label is final
 //        (Dijkstra order without a heap); each warp appends the cells it reaches to its own queue segment with
-//        ballot compaction (no atomics on the queue), the group meets at one named barrier per bucket
-//   4. next-hop tiles (closed form of the heap's tie-break, see sssp_warp.cuh) + coalesced streaming write-out,
-//      overlapped with the full-path walks (paths.cpp:87-108) that one lane per spawner runs on the resident layers
-//   5. aggregates (paths.cpp:122-138)
+//        ballot compaction (no atomics on the queue), the group meets at one named barrier per bucket.
+//        The layers live in a PADDED frame (one parked column on the right, one parked row above and below): the four
+//        neighbours of a cell are p-1, p+1, p-Wp, p+Wp with no bounds test, and the queue holds linear indices.
+//   4. next-hop tiles (closed form of the heap's tie-break, see sssp_warp.cuh) + coalesced streaming write-out
+//   5. full paths + aggregates (paths.cpp:87-139): single map -> the workers walk the resident layers while they are
+//      written out; batches -> the walker warp chases the PREVIOUS map's layers in global memory (L2) while the
+//      workers relax the next map
 // Queue overflow (pathological frontiers) switches the layer to a queue-less dense sweep that needs no capacity.
 #pragma once
 
@@ -33,6 +36,8 @@ namespace mtd
 	constexpr int SMALL_MAX_RESIDENT = 4;  // layers concurrently in shared memory
 	constexpr int MTD_MAXSRC_SMALL = 32;
 	constexpr int SMALL_OUT_CHUNK = 128;   // cells per write-out work item
+	// a settled label this close to the guard band is reported instead of relaxed: labels + one edge (< 2^17) stay below MTD_GUARD
+	constexpr uint32_t SMALL_SETTLE_LIMIT = MTD_GUARD - (1u << 17);
 
 	struct WaypointsSmallParams
 	{
@@ -60,6 +65,29 @@ namespace mtd
 		                         //       one map behind the workers; 0: the workers walk the resident layers themselves
 	};
 
+	// ---- geometry of the padded frame -------------------------------------------------------------------------
+	// grid cell (x, y) lives at p = (y + 1) * Wp + x with Wp = W + 1; column W and rows 0 and H + 1 are parked at 0
+	struct SmallGeom
+	{
+		int W, H, T, Wp, Tp;
+		uint32_t magicW, magicWp; // ceil(2^32 / d): q = umulhi(i, magic) is exact for i < 65536, d <= 257
+		__host__ __device__ static uint32_t magic(uint32_t d) { return d > 1 ? (uint32_t)((0x100000000ull + d - 1u) / d) : 0u; }
+		__host__ __device__ SmallGeom(int w, int h) : W(w), H(h), T(w * h), Wp(w + 1), Tp((w + 1) * (h + 2)), magicW(magic((uint32_t)w)), magicWp(magic((uint32_t)w + 1u)) {}
+#ifdef __CUDACC__
+		__device__ __forceinline__ uint32_t row_of(uint32_t i) const { return magicW ? __umulhi(i, magicW) : i; }
+		__device__ __forceinline__ uint32_t g2p(uint32_t i) const
+		{
+			const uint32_t y = row_of(i);
+			return i + y + (uint32_t)Wp; // (y + 1) * Wp + (i - y * W)
+		}
+		__device__ __forceinline__ uint32_t p2g(uint32_t p) const
+		{
+			const uint32_t yp = __umulhi(p, magicWp); // Wp >= 2
+			return p - yp - (uint32_t)W;              // (yp - 1) * W + (p - yp * Wp)
+		}
+#endif
+	};
+
 	// ---- shared memory layout (byte offsets), identical on host and device ---------------------------------
 	struct SmallLayout
 	{
@@ -72,22 +100,23 @@ namespace mtd
 		return (v + 15u) & ~15u;
 	}
 
-	__host__ __device__ inline SmallLayout small_layout(int T, int R, uint32_t budget, int qseg_cap, int gw = SMALL_GROUP_WARPS)
+	__host__ __device__ inline SmallLayout small_layout(int W, int H, int R, uint32_t budget, int qseg_cap, int gw = SMALL_GROUP_WARPS)
 	{
 		SmallLayout L;
+		const uint32_t T = (uint32_t)(W * H), Tp = (uint32_t)((W + 1) * (H + 2));
 		uint32_t o = 0;
-		const uint32_t stage = 2u * align16u((uint32_t)(T + 8) * 2u); // elev + flags staging aliases the distance layers
-		uint32_t dist_bytes = (uint32_t)R * (uint32_t)T * 4u;
+		const uint32_t stage = 2u * align16u((T + 8u) * 2u); // elev + flags staging aliases the distance layers
+		uint32_t dist_bytes = (uint32_t)R * Tp * 4u;
 		if (dist_bytes < stage)
 			dist_bytes = stage;
 		L.dist = o;
 		o += align16u(dist_bytes);
 		L.wr = o;
-		o += align16u((uint32_t)T * 2u);
+		o += align16u(Tp * 2u);
 		L.wd = o;
-		o += align16u((uint32_t)T * 2u);
+		o += align16u(Tp * 2u);
 		L.blk = o;
-		o += align16u((uint32_t)((T + 31) >> 5) * 4u);
+		o += align16u(((T + 31u) >> 5) * 4u);
 		L.ctl = o;
 		o += (uint32_t)R * 64u; // [parity 2][counts 4 | mins 4] uint32
 		L.dtab = o;
@@ -104,7 +133,6 @@ namespace mtd
 		L.total = o + per_entry * (uint32_t)qseg;
 		return L;
 	}
-
 	// ---- small PTX helpers -----------------------------------------------------------------------------------
 	__device__ __forceinline__ uint32_t smem_u32(const void *p)
 	{
@@ -178,84 +206,54 @@ namespace mtd
 		return s;
 	}
 
-	// ---- per-cell relaxation shared by the queued and the dense round -----------------------------------------
-	// Settles cell c (distance d, final because d < dmin + 255) and relaxes its four neighbours with shared-memory
-	// atomicMin. fresh[k] != 0 iff neighbour k was reached for the first time (old label was "unreached"), which
-	// is the only way a cell enters the queue: labels of settled cells never improve again. Returns min of the
-	// improved labels (MTD_INF if none).
-	struct RelaxOut
-	{
-		uint32_t cell[4]; // packed y<<8|x of the neighbour
-		bool fresh[4];
-		uint32_t newmin;
-		bool guard;
-	};
-
-	__device__ __forceinline__ RelaxOut relax_cell(uint32_t *dist, const uint16_t *wr, const uint16_t *wd, int W, int H, bool settle, int x, int y, uint32_t c, uint32_t d)
-	{
-		RelaxOut o;
-		o.newmin = MTD_INF;
-		o.guard = false;
-		// 0: up, 1: left, 2: right, 3: down
-		const bool ok[4] = { settle && y > 0, settle && x > 0, settle && x < W - 1, settle && y < H - 1 };
-		const uint32_t nb[4] = { c - (uint32_t)W, c - 1u, c + 1u, c + (uint32_t)W };
-		uint32_t wv[4];
-		wv[0] = ok[0] ? wd[nb[0]] : 0u;
-		wv[1] = ok[1] ? wr[nb[1]] : 0u;
-		wv[2] = ok[2] ? wr[c] : 0u;
-		wv[3] = ok[3] ? wd[c] : 0u;
-		uint32_t old[4], nd[4];
-#pragma unroll
-		for (int k = 0; k < 4; k++)
-		{
-			nd[k] = d + MIN_EDGE + wv[k];
-			old[k] = 0u;
-			if (ok[k])
-			{
-				if (nd[k] >= MTD_GUARD)
-					o.guard = true;
-				else
-					old[k] = atomicMin(&dist[nb[k]], nd[k]);
-			}
-		}
-		const uint32_t e = ((uint32_t)y << 8) | (uint32_t)x;
-		o.cell[0] = e - 256u;
-		o.cell[1] = e - 1u;
-		o.cell[2] = e + 1u;
-		o.cell[3] = e + 256u;
-#pragma unroll
-		for (int k = 0; k < 4; k++)
-		{
-			const bool improved = ok[k] && nd[k] < old[k];
-			o.fresh[k] = improved && old[k] == MTD_INF;
-			if (improved)
-				o.newmin = min(o.newmin, nd[k]);
-		}
-		return o;
-	}
+#ifdef MTD_TIMING
+	// developer probe (never in the shipped build): cycle split of one warp's relaxation rounds, printed by CTA 0
+	__device__ unsigned long long g_timing[8];
+#define MTD_TICK(k)                                           \
+	do                                                        \
+	{                                                         \
+		const long long now__ = clock64();                    \
+		acc__[k] += (unsigned long long)(now__ - last__);     \
+		last__ = now__;                                       \
+	} while (0)
+#else
+#define MTD_TICK(k)
+#endif
 
 	// ---- one layer, GW warps ---------------------------------------------------------------------------------------
-	// ctl: [parity][0..3] = entries each warp appended for the round that reads `parity`, [parity][4..7] = min pending
-	// label each warp saw. q: [parity][warp][qseg] packed cells. Initial state (parity 0) is written by the caller.
-	// Returns true if a label hit the guard band.
+	// dist/wr/wd are in the padded frame: neighbours of p are p-1, p+1, p-Wp, p+Wp; parked cells (blocked, padding) hold 0
+	// and can never be lowered. ctl: [parity][0..3] = entries each warp appended for the round that reads `parity`,
+	// [parity][4..7] = min pending label each warp saw. q: [parity][warp][qseg] linear cell indices. Initial state
+	// (parity 0) is written by the caller. Returns true if a label hit the guard band.
 	template<int GW>
-	__device__ bool group_relax(uint32_t *dist, const uint16_t *wr, const uint16_t *wd, uint16_t *q, uint32_t *ctl, int W, int H, int T, int qseg, uint32_t magicW, int gw, uint32_t lane, int bar_id)
+	__device__ bool group_relax(uint32_t *dist, const uint16_t *wr, const uint16_t *wd, uint16_t *q, uint32_t *ctl, int Wp, int Tp, int qseg, int gw, uint32_t lane, int bar_id)
 	{
 		const uint32_t lt = lanemask_lt();
 		uint32_t parity = 0, thr_prev = 0;
 		bool guard = false, dense = false;
+#ifdef MTD_TIMING
+		const bool probe__ = blockIdx.x == 0 && bar_id == 2 && gw == 0 && lane == 0;
+		long long last__ = clock64();
+		unsigned long long acc__[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+#endif
 		for (;;)
 		{
+			MTD_TICK(4);
 			const uint4 cn = *reinterpret_cast<const uint4 *>(ctl + parity * 8);
 			const uint4 mn = *reinterpret_cast<const uint4 *>(ctl + parity * 8 + 4);
 			const uint32_t dmin = min(min(mn.x, mn.y), min(mn.z, mn.w));
 			if (dmin == MTD_INF)
 				break; // nothing pending
-			const uint32_t thr = dmin >= MTD_GUARD ? MTD_INF : dmin + MIN_EDGE;
+			const uint32_t thr = dmin + MIN_EDGE; // dmin < SMALL_SETTLE_LIMIT or every pending cell is reported below
 			const uint32_t cap = (uint32_t)qseg;
 			dense = dense || cn.x > cap || cn.y > cap || cn.z > cap || cn.w > cap; // an append was dropped: the queue is incomplete from now on
 			uint32_t newmin = MTD_INF, outn = 0;
 			uint16_t *wq = q + ((parity ^ 1u) * GW + (uint32_t)gw) * cap;
+			MTD_TICK(0);
+#ifdef MTD_TIMING
+			acc__[5] += 1;
+			acc__[6] += cn.x + cn.y + cn.z + cn.w;
+#endif
 			if (!dense)
 			{
 				const uint32_t p1 = cn.x, p2 = p1 + cn.y, p3 = p2 + cn.z, n = p3 + cn.w;
@@ -264,128 +262,195 @@ namespace mtd
 				{
 					const uint32_t idx = base + lane;
 					const bool active = idx < n;
-					const uint32_t seg = (idx >= p1) + (idx >= p2) + (idx >= p3);
-					const uint32_t off = idx - (seg == 0 ? 0u : seg == 1 ? p1 : seg == 2 ? p2 : p3);
-					const uint32_t e = active ? rq[seg * cap + off] : 0u;
-					const int y = (int)(e >> 8), x = (int)(e & 255u);
-					const uint32_t c = (uint32_t)(y * W + x);
+					uint32_t slot = idx;
+					if (GW > 1)
+					{
+						const uint32_t seg = (idx >= p1) + (GW > 2 ? (idx >= p2) + (idx >= p3) : 0u);
+						slot = seg * cap + idx - (seg == 0 ? 0u : seg == 1 ? p1 : seg == 2 ? p2 : p3);
+					}
+					const uint32_t c = active ? rq[slot] : 0u;
 					const uint32_t d = active ? dist[c] : MTD_INF;
-					const bool settle = active && d < thr;
-					const bool keep = active && !settle;
-					const RelaxOut r = relax_cell(dist, wr, wd, W, H, settle, x, y, c, d);
-					guard |= r.guard;
-					newmin = min(newmin, keep ? d : r.newmin);
+					bool settle = active && d < thr;
+					if (settle && d >= SMALL_SETTLE_LIMIT)
+					{
+						guard = true; // reference arithmetic is about to wrap: report, do not expand
+						settle = false;
+					}
+					const bool keep = active && d >= thr && d < SMALL_SETTLE_LIMIT;
+					uint32_t o0 = 0u, o1 = 0u, o2 = 0u, o3 = 0u, n0 = 0u, n1 = 0u, n2 = 0u, n3 = 0u;
+					if (settle)
+					{
+						// 0: up, 1: left, 2: right, 3: down -- weights are stored on the upper / left cell of an edge
+						const uint32_t base_nd = d + MIN_EDGE;
+						n0 = base_nd + wd[c - Wp];
+						n1 = base_nd + wr[c - 1];
+						n2 = base_nd + wr[c];
+						n3 = base_nd + wd[c];
+						o0 = atomicMin(&dist[c - Wp], n0);
+						o1 = atomicMin(&dist[c - 1], n1);
+						o2 = atomicMin(&dist[c + 1], n2);
+						o3 = atomicMin(&dist[c + Wp], n3);
+					}
+					// a cell enters the queue exactly once: when its label leaves "unreached" (labels of queued cells may
+					// still improve before they settle, settled labels are final)
+					const bool f0 = settle && o0 == MTD_INF, f1 = settle && o1 == MTD_INF, f2 = settle && o2 == MTD_INF, f3 = settle && o3 == MTD_INF;
+					uint32_t lm = keep ? d : MTD_INF;
+					lm = settle && n0 < o0 ? min(lm, n0) : lm;
+					lm = settle && n1 < o1 ? min(lm, n1) : lm;
+					lm = settle && n2 < o2 ? min(lm, n2) : lm;
+					lm = settle && n3 < o3 ? min(lm, n3) : lm;
+					newmin = min(newmin, lm);
 					// ---- append survivors and newly reached cells to this warp's segment (ballot compaction) ----
 					const uint32_t bk = __ballot_sync(FULL_MASK, keep);
-					const uint32_t b0 = __ballot_sync(FULL_MASK, r.fresh[0]);
-					const uint32_t b1 = __ballot_sync(FULL_MASK, r.fresh[1]);
-					const uint32_t b2 = __ballot_sync(FULL_MASK, r.fresh[2]);
-					const uint32_t b3 = __ballot_sync(FULL_MASK, r.fresh[3]);
-					uint32_t pos = outn;
-					if (keep && pos + __popc(bk & lt) < cap)
-						wq[pos + __popc(bk & lt)] = (uint16_t)e;
-					pos += __popc(bk);
-					if (r.fresh[0] && pos + __popc(b0 & lt) < cap)
-						wq[pos + __popc(b0 & lt)] = (uint16_t)r.cell[0];
-					pos += __popc(b0);
-					if (r.fresh[1] && pos + __popc(b1 & lt) < cap)
-						wq[pos + __popc(b1 & lt)] = (uint16_t)r.cell[1];
-					pos += __popc(b1);
-					if (r.fresh[2] && pos + __popc(b2 & lt) < cap)
-						wq[pos + __popc(b2 & lt)] = (uint16_t)r.cell[2];
-					pos += __popc(b2);
-					if (r.fresh[3] && pos + __popc(b3 & lt) < cap)
-						wq[pos + __popc(b3 & lt)] = (uint16_t)r.cell[3];
-					pos += __popc(b3);
-					outn = pos; // may exceed cap: that is the overflow signal read at the next round
+					const uint32_t b0 = __ballot_sync(FULL_MASK, f0);
+					const uint32_t b1 = __ballot_sync(FULL_MASK, f1);
+					const uint32_t b2 = __ballot_sync(FULL_MASK, f2);
+					const uint32_t b3 = __ballot_sync(FULL_MASK, f3);
+					uint32_t pos = outn + __popc(bk & lt);
+					if (keep && pos < cap)
+						wq[pos] = (uint16_t)c;
+					outn += __popc(bk);
+					pos = outn + __popc(b0 & lt);
+					if (f0 && pos < cap)
+						wq[pos] = (uint16_t)(c - Wp);
+					outn += __popc(b0);
+					pos = outn + __popc(b1 & lt);
+					if (f1 && pos < cap)
+						wq[pos] = (uint16_t)(c - 1u);
+					outn += __popc(b1);
+					pos = outn + __popc(b2 & lt);
+					if (f2 && pos < cap)
+						wq[pos] = (uint16_t)(c + 1u);
+					outn += __popc(b2);
+					pos = outn + __popc(b3 & lt);
+					if (f3 && pos < cap)
+						wq[pos] = (uint16_t)(c + Wp);
+					outn += __popc(b3); // may exceed cap: that is the overflow signal read at the next round
 				}
 			}
 			else
 			{
 				// dense round: every pending cell has thr_prev <= label < INF (settled ones are below thr_prev, parked
-				// blocked cells are 0), so the bucket is found by scanning the labels -- no queue, no capacity
+				// cells are 0), so the bucket is found by scanning the labels -- no queue, no capacity
 				outn = cap + 1u; // stay dense
-				for (int i = gw * 32 + (int)lane; i < T; i += GW * 32)
+				for (int c = gw * 32 + (int)lane; c < Tp; c += GW * 32)
 				{
-					const uint32_t d = dist[i];
-					const bool settle = d >= thr_prev && d < thr;
-					if (d >= thr && d != MTD_INF)
-						newmin = min(newmin, d);
-					if (__any_sync(__activemask(), settle))
+					const uint32_t d = dist[c];
+					bool settle = d >= thr_prev && d < thr;
+					if (settle && d >= SMALL_SETTLE_LIMIT)
 					{
-						const int y = (int)div_w((uint32_t)i, magicW), x = i - y * W;
-						const RelaxOut r = relax_cell(dist, wr, wd, W, H, settle, x, y, (uint32_t)i, d);
-						guard |= r.guard;
-						newmin = min(newmin, r.newmin);
+						guard = true;
+						settle = false;
+					}
+					if (d >= thr && d < SMALL_SETTLE_LIMIT)
+						newmin = min(newmin, d);
+					else if (d >= SMALL_SETTLE_LIMIT && d != MTD_INF)
+						guard = true;
+					if (settle)
+					{
+						// thr_prev > 0 in every dense round, so parked cells (and the padding they include) never settle:
+						// c - Wp ... c + Wp stay inside the frame
+						const uint32_t base_nd = d + MIN_EDGE;
+						const uint32_t n0 = base_nd + wd[c - Wp], n1 = base_nd + wr[c - 1], n2 = base_nd + wr[c], n3 = base_nd + wd[c];
+						if (n0 < atomicMin(&dist[c - Wp], n0))
+							newmin = min(newmin, n0);
+						if (n1 < atomicMin(&dist[c - 1], n1))
+							newmin = min(newmin, n1);
+						if (n2 < atomicMin(&dist[c + 1], n2))
+							newmin = min(newmin, n2);
+						if (n3 < atomicMin(&dist[c + Wp], n3))
+							newmin = min(newmin, n3);
 					}
 				}
 			}
+			MTD_TICK(1);
 			newmin = warp_min_u32(newmin);
 			if (lane == 0)
 			{
 				ctl[(parity ^ 1u) * 8 + (uint32_t)gw] = outn;
 				ctl[(parity ^ 1u) * 8 + 4 + (uint32_t)gw] = newmin;
 			}
+			MTD_TICK(2);
 			if (GW == 1)
 				__syncwarp();
 			else
 				group_barrier(bar_id, GW * 32);
+			MTD_TICK(3);
 			thr_prev = thr;
 			parity ^= 1u;
 		}
+#ifdef MTD_TIMING
+		if (probe__)
+			for (int k = 0; k < 8; k++)
+				g_timing[k] += acc__[k];
+#endif
 		return __any_sync(FULL_MASK, guard);
 	}
 
-	// next-hop with the four edge weights already loaded (wu = w(c-W,c), wl = w(c-1,c), wrr = w(c,c+1), wdn = w(c,c+W), all - 255)
-	__device__ __forceinline__ uint32_t next_hop_w(const uint32_t *dl, int W, int H, int x, int y, uint32_t c, uint32_t wu, uint32_t wl, uint32_t wrr, uint32_t wdn)
+	// tiles[v] from final labels in the padded frame (closed form of the heap's tie-break, sssp_warp.cuh): the neighbour u
+	// with d[u] + w(u, v) == d[v] minimising (d[u], u); neighbours in ascending tile index (up, left, right, down), replace
+	// only on a strictly smaller d[u]. dv = dl[p] must be a reached, non-source label (not 0, not INF). A parked neighbour
+	// holds 0 like a source does: is_src(u) tells them apart. Returns a padded index or MTD_INF.
+	template<class IsSrc>
+	__device__ __forceinline__ uint32_t next_hop_p(const uint32_t *dl, const uint16_t *wr, const uint16_t *wd, int Wp, uint32_t p, uint32_t dv, IsSrc is_src)
 	{
-		const uint32_t dv = dl[c];
-		if (dv == MTD_INF || dv == 0u)
-			return MTD_INF;
-		const uint32_t du0 = y > 0 ? dl[c - W] : MTD_INF;
-		const uint32_t du1 = x > 0 ? dl[c - 1] : MTD_INF;
-		const uint32_t du2 = x < W - 1 ? dl[c + 1] : MTD_INF;
-		const uint32_t du3 = y < H - 1 ? dl[c + W] : MTD_INF;
+		const uint32_t u0 = p - (uint32_t)Wp, u1 = p - 1u, u2 = p + 1u, u3 = p + (uint32_t)Wp;
+		const uint32_t d0 = dl[u0], d1 = dl[u1], d2 = dl[u2], d3 = dl[u3];
+		const uint32_t w0 = wd[u0], w1 = wr[u1], w2 = wr[p], w3 = wd[p];
 		uint32_t best = MTD_INF, bestd = MTD_INF;
-		if (du0 != MTD_INF && du0 + MIN_EDGE + wu == dv)
+		if (d0 != MTD_INF && d0 + MIN_EDGE + w0 == dv && (d0 != 0u || is_src(u0)))
 		{
-			bestd = du0;
-			best = c - (uint32_t)W;
+			bestd = d0;
+			best = u0;
 		}
-		if (du1 != MTD_INF && du1 + MIN_EDGE + wl == dv && du1 < bestd)
+		if (d1 != MTD_INF && d1 + MIN_EDGE + w1 == dv && d1 < bestd && (d1 != 0u || is_src(u1)))
 		{
-			bestd = du1;
-			best = c - 1u;
+			bestd = d1;
+			best = u1;
 		}
-		if (du2 != MTD_INF && du2 + MIN_EDGE + wrr == dv && du2 < bestd)
+		if (d2 != MTD_INF && d2 + MIN_EDGE + w2 == dv && d2 < bestd && (d2 != 0u || is_src(u2)))
 		{
-			bestd = du2;
-			best = c + 1u;
+			bestd = d2;
+			best = u2;
 		}
-		if (du3 != MTD_INF && du3 + MIN_EDGE + wdn == dv && du3 < bestd)
+		if (d3 != MTD_INF && d3 + MIN_EDGE + w3 == dv && d3 < bestd && (d3 != 0u || is_src(u3)))
 		{
-			bestd = du3;
-			best = c + (uint32_t)W;
+			bestd = d3;
+			best = u3;
 		}
 		return best;
 	}
 
-	// layers held in shared memory: next-hop tiles are derived from the final distances on the fly
+	// layers held in shared memory (padded frame, blocked tiles still parked at 0), single-source layers:
+	// srcp[l] = padded index of layer l's source
 	struct SmemLayersAcc
 	{
-		const uint32_t *sdist; // [R][T]
+		const uint32_t *sdist; // [R][Tp]
 		const uint16_t *wr, *wd;
-		int W, H, T;
-		uint32_t magicW;
-		__device__ __forceinline__ uint32_t dist(uint32_t l, uint32_t t) const { return sdist[(size_t)l * T + t]; }
+		const uint32_t *srcp;
+		SmallGeom G;
+		__device__ __forceinline__ SmemLayersAcc(const SmallGeom &g) : G(g) {}
+		__device__ __forceinline__ uint32_t dist(uint32_t l, uint32_t t) const
+		{
+			const uint32_t p = G.g2p(t);
+			const uint32_t v = sdist[(size_t)l * G.Tp + p];
+			return v == 0u && p != srcp[l] ? MTD_INF : v; // parked = blocked, never relaxed (paths.cpp:65-67)
+		}
 		__device__ __forceinline__ uint32_t hop(uint32_t l, uint32_t t) const
 		{
-			const int y = (int)div_w(t, magicW), x = (int)t - y * W;
-			return next_hop(sdist + (size_t)l * T, wr, wd, W, H, x, y);
+			const uint32_t p = G.g2p(t);
+			const uint32_t *dl = sdist + (size_t)l * G.Tp;
+			const uint32_t dv = dl[p];
+			if (dv == MTD_INF || dv == 0u)
+				return MTD_INF;
+			const uint32_t sp = srcp[l];
+			const uint32_t q = next_hop_p(dl, wr, wd, G.Wp, p, dv, [&](uint32_t u) { return u == sp; });
+			return q == MTD_INF ? MTD_INF : G.p2g(q);
 		}
 		__device__ __forceinline__ uint32_t edge(uint32_t a, uint32_t b) const
 		{
-			const uint32_t lo = a < b ? a : b, hi = a < b ? b : a;
+			const uint32_t pa = G.g2p(a), pb = G.g2p(b);
+			const uint32_t lo = pa < pb ? pa : pb, hi = pa < pb ? pb : pa;
 			return MIN_EDGE + (hi - lo == 1u ? wr[lo] : wd[lo]);
 		}
 	};
@@ -395,7 +460,6 @@ namespace mtd
 	{
 		group_barrier(1, SMALL_THREADS);
 	}
-
 	// Full-path walks + aggregates of one map on layers resident in global memory, by ONE warp: lane s walks spawner s
 	// (the dependent loads of the n chases overlap), then all lanes pad the path buffers. wp/D/fd: scratch in shared memory.
 	__device__ void walk_map_global(const WaypointsSmallParams &P, int mapi, uint32_t *wp, uint32_t *D, uint32_t *fd, uint32_t lane)
@@ -443,14 +507,16 @@ namespace mtd
 		__syncwarp();
 	}
 
+
 	// =============================================================================================================
 	// 512 worker threads + 1 walker warp. GW = warps cooperating on one layer during the relaxation.
 	template<int GW>
 	__global__ void __launch_bounds__(SMALL_THREADS + 32, 1) k_waypoints_small(const WaypointsSmallParams P)
 	{
 		extern __shared__ __align__(16) unsigned char smem_raw[];
-		const int W = P.W, H = P.H, T = W * H, n = P.n, R = P.R;
-		const SmallLayout L = small_layout(T, R, P.smem_budget, P.qseg_cap, GW);
+		const SmallGeom G(P.W, P.H);
+		const int W = G.W, H = G.H, T = G.T, Wp = G.Wp, Tp = G.Tp, n = P.n, R = P.R;
+		const SmallLayout L = small_layout(W, H, R, P.smem_budget, P.qseg_cap, GW);
 		uint32_t *sdist = (uint32_t *)(smem_raw + L.dist);
 		uint16_t *wr = (uint16_t *)(smem_raw + L.wr);
 		uint16_t *wd = (uint16_t *)(smem_raw + L.wd);
@@ -461,7 +527,7 @@ namespace mtd
 		const int qseg = L.qseg;
 		__shared__ __align__(8) uint64_t s_mbar;
 		__shared__ uint32_t s_fd[FIND_MAXN];
-		__shared__ uint32_t s_wp[MTD_MAXSRC_SMALL];
+		__shared__ uint32_t s_wp[MTD_MAXSRC_SMALL], s_srcp[MTD_MAXSRC_SMALL]; // waypoint / source tiles: grid index, padded index
 		__shared__ int s_guard;
 		__shared__ uint32_t s_map, s_chunk;
 		// the walker warp's private copies (it works on the PREVIOUS map while the workers overwrite the above)
@@ -473,7 +539,6 @@ namespace mtd
 		const bool resident_all = n <= R;
 		const int nsrc_layer = P.nsrc > 1 ? P.nsrc : 1;
 		const int nwp = P.nsrc > 1 ? P.nsrc : n;
-		const uint32_t magicW = W > 1 ? (uint32_t)((0x100000000ull + (uint32_t)W - 1u) / (uint32_t)W) : 0u; // y = umulhi(i, magicW) for i < 65536, W <= 256
 		const uint32_t stage_half = align16u((uint32_t)(T + 8) * 2u);
 		const bool want_walks = P.fullpath_len && P.nsrc <= 1;
 		uint32_t mbar_phase = 0;
@@ -541,11 +606,31 @@ namespace mtd
 				else if (warp == 2)
 				{
 					for (int i = (int)lane; i < nwp && i < MTD_MAXSRC_SMALL; i += 32)
-						s_wp[i] = gwp[i];
+					{
+						const uint32_t t = gwp[i];
+						s_wp[i] = t;
+						s_srcp[i] = G.g2p(t);
+					}
 					if (lane == 0)
 					{
 						s_guard = 0;
 						s_chunk = 0;
+					}
+				}
+				else if (warp == 3)
+				{
+					// weights of the padding (never matter: their far end is parked) are zeroed once per map for determinism
+					for (int k = (int)lane; k < Wp; k += 32)
+					{
+						wr[k] = 0;
+						wd[k] = 0;
+						wr[(H + 1) * Wp + k] = 0;
+						wd[(H + 1) * Wp + k] = 0;
+					}
+					for (int y = 1 + (int)lane; y <= H; y += 32)
+					{
+						wr[y * Wp + W] = 0;
+						wd[y * Wp + W] = 0;
 					}
 				}
 				mbar_wait(&s_mbar, mbar_phase);
@@ -560,10 +645,11 @@ namespace mtd
 				bool blocked = false;
 				if (i < T)
 				{
-					const int y = (int)div_w((uint32_t)i, magicW), x = i - y * W;
+					const int y = (int)G.row_of((uint32_t)i), x = i - y * W;
+					const int p = i + y + Wp;
 					const int16_t e = selev[i];
-					wr[i] = x < W - 1 ? (uint16_t)(edge_weight(e, selev[i + 1]) - MIN_EDGE) : (uint16_t)0;
-					wd[i] = y < H - 1 ? (uint16_t)(edge_weight(e, selev[i + W]) - MIN_EDGE) : (uint16_t)0;
+					wr[p] = x < W - 1 ? (uint16_t)(edge_weight(e, selev[i + 1]) - MIN_EDGE) : (uint16_t)0;
+					wd[p] = y < H - 1 ? (uint16_t)(edge_weight(e, selev[i + W]) - MIN_EDGE) : (uint16_t)0;
 					blocked = (sflags[i] & F_BLOCKING) != 0 || (uint32_t)i == P.extra_blocked;
 				}
 				const uint32_t bal = __ballot_sync(FULL_MASK, blocked);
@@ -575,34 +661,39 @@ namespace mtd
 			for (int l0 = 0; l0 < n; l0 += R)
 			{
 				const int lb = (n - l0) < R ? (n - l0) : R; // layers in this pass
-				// ---- 3a. init: paths.cpp:40-43; blocked tiles are parked at 0 during the run (never relaxed: >= 255 cannot lower 0) ----
-				for (int i = tid; i < T; i += SMALL_THREADS)
+				// ---- 3a. init: paths.cpp:40-43; blocked tiles and the padding are parked at 0 (never relaxed: >= 255 cannot lower 0) ----
+				for (int p = tid; p < Tp; p += SMALL_THREADS)
 				{
-					const uint32_t v = ((blk[i >> 5] >> (i & 31)) & 1u) ? 0u : MTD_INF;
+					const uint32_t yp = __umulhi((uint32_t)p, G.magicWp), x = (uint32_t)p - yp * (uint32_t)Wp;
+					uint32_t v = 0u;
+					if (yp >= 1u && yp <= (uint32_t)H && x < (uint32_t)W)
+					{
+						const uint32_t i = (uint32_t)p - yp - (uint32_t)W;
+						v = ((blk[i >> 5] >> (i & 31u)) & 1u) ? 0u : MTD_INF;
+					}
 					for (int r = 0; r < lb; r++)
-						sdist[(size_t)r * T + i] = v;
+						sdist[(size_t)r * Tp + p] = v;
 				}
 				workers_sync();
 				// seeds: paths.cpp:48-49 (a blocked source still expands: the popped tile is never tested, paths.cpp:63-67)
 				if (warp < lb * GW && (warp % GW) == 0 && lane == 0)
 				{
 					const int g = warp / GW;
-					uint32_t *dl = sdist + (size_t)g * T;
+					uint32_t *dl = sdist + (size_t)g * Tp;
 					uint32_t *c = ctl + g * 16;
 					uint16_t *q0 = q + (size_t)g * 2 * GW * qseg;
 					uint32_t nseed = 0;
 					for (int s = 0; s < nsrc_layer; s++)
 					{
-						const uint32_t src = P.nsrc > 1 ? s_wp[s] : s_wp[l0 + g];
+						const uint32_t sp = P.nsrc > 1 ? s_srcp[s] : s_srcp[l0 + g];
 						bool dup = false;
 						for (int s2 = 0; s2 < s; s2++)
-							dup |= P.nsrc > 1 && s_wp[s2] == src;
+							dup |= P.nsrc > 1 && s_srcp[s2] == sp;
 						if (dup)
 							continue;
-						dl[src] = 0u;
-						const uint32_t y = div_w(src, magicW);
+						dl[sp] = 0u;
 						if ((int)nseed < qseg)
-							q0[nseed] = (uint16_t)((y << 8) | (src - y * (uint32_t)W));
+							q0[nseed] = (uint16_t)sp;
 						nseed++;
 					}
 					c[0] = nseed;
@@ -619,55 +710,32 @@ namespace mtd
 				if (warp < lb * GW)
 				{
 					const int g = warp / GW;
-					if (group_relax<GW>(sdist + (size_t)g * T, wr, wd, q + (size_t)g * 2 * GW * qseg, ctl + g * 16, W, H, T, qseg, magicW, warp % GW, lane, 2 + g) && lane == 0)
+					if (group_relax<GW>(sdist + (size_t)g * Tp, wr, wd, q + (size_t)g * 2 * GW * qseg, ctl + g * 16, Wp, Tp, qseg, warp % GW, lane, 2 + g) && lane == 0)
 						s_guard = 1;
 				}
 				workers_sync();
 
-				// ---- 3c. blocked, non-source tiles read "unreachable" (they were never relaxed: paths.cpp:65-67) ----
-				for (int i = tid; i < T; i += SMALL_THREADS)
-				{
-					if (!((blk[i >> 5] >> (i & 31)) & 1u))
-						continue;
-					for (int r = 0; r < lb; r++)
-					{
-						bool is_src = false;
-						if (P.nsrc > 1)
-							for (int s = 0; s < nsrc_layer; s++)
-								is_src |= s_wp[s] == (uint32_t)i;
-						else
-							is_src = s_wp[l0 + r] == (uint32_t)i;
-						if (!is_src)
-							sdist[(size_t)r * T + i] = MTD_INF;
-					}
-				}
-				const bool walk_now = want_walks && !P.walker && resident_all; // single map: walk the resident layers while they are written out
-				if (walk_now && tid < n * n)
-				{
-					// inter-waypoint table D[a][b] = dist_b[wp_a]; a waypoint tile is either open or the source of its own layer,
-					// except blocked waypoints of OTHER layers, which the loop above may be rewriting concurrently: read the
-					// final value explicitly
-					const int a = tid / n, b = tid % n;
-					const uint32_t t = s_wp[a];
-					uint32_t v = sdist[(size_t)b * T + t];
-					if (((blk[t >> 5] >> (t & 31)) & 1u) && s_wp[b] != t)
-						v = MTD_INF;
-					Dtab[a * FIND_MAXN + b] = v;
-				}
-				workers_sync();
-
 				// ---- 4. full-path walks (one lane per spawner) overlapped with next-hop tiles + write-out of this pass ----
+				// Blocked tiles are still parked at 0 in the resident layers: every reader below maps "0 and not this layer's
+				// source" to m (they were never relaxed: paths.cpp:65-67).
+				const bool walk_now = want_walks && !P.walker && resident_all; // single map: walk the resident layers while they are written out
+				SmemLayersAcc acc(G);
+				acc.sdist = sdist;
+				acc.wr = wr;
+				acc.wd = wd;
+				acc.srcp = s_srcp;
+				if (walk_now)
+				{
+					if (tid < n * n)
+					{
+						const int a = tid / n, b = tid % n;
+						Dtab[a * FIND_MAXN + b] = acc.dist((uint32_t)b, s_wp[a]); // inter-waypoint table D[a][b] = dist_b[wp_a]
+					}
+					workers_sync();
+				}
 				uint32_t walk_len = 0;
 				if (walk_now && warp < n && lane == 0)
 				{
-					SmemLayersAcc acc;
-					acc.sdist = sdist;
-					acc.wr = wr;
-					acc.wd = wd;
-					acc.W = W;
-					acc.H = H;
-					acc.T = T;
-					acc.magicW = magicW;
 					uint32_t *path = P.fullpath ? P.fullpath + ((size_t)mapi * n + warp) * P.cap : nullptr;
 					const WalkResult r = walk_path(n, s_wp, Dtab, walk_table_fast(n, Dtab), warp, acc, path, P.cap, (uint32_t)T * (uint32_t)n + 8u);
 					if (P.fullpath && r.len > P.cap)
@@ -702,22 +770,59 @@ namespace mtd
 							const int i = (int)item * SMALL_OUT_CHUNK + k * 32 + (int)lane;
 							if (i >= T)
 								break;
-							const int y = (int)div_w((uint32_t)i, magicW), x = i - y * W;
-							uint32_t wu = 0, wl = 0, wrr = 0, wdn = 0;
-							if (gtiles)
+							const uint32_t bw = blk[i >> 5]; // warp-uniform: i - lane is a multiple of 32
+							if (bw == 0xFFFFFFFFu && P.nsrc <= 1)
 							{
-								wu = y > 0 ? wd[i - W] : 0u;
-								wl = x > 0 ? wr[i - 1] : 0u;
-								wrr = wr[i];
-								wdn = wd[i];
+								// 32 blocked tiles: m everywhere except a blocked tile that is the layer's own source
+								for (int r = 0; r < lb; r++)
+								{
+									const bool is_src = s_wp[l0 + r] == (uint32_t)i;
+									if (gdist)
+										st_stream_u32(gdist + (size_t)(l0 + r) * T + i, is_src ? 0u : MTD_INF);
+									if (gtiles)
+										st_stream_u32(gtiles + (size_t)(l0 + r) * T + i, MTD_INF);
+								}
+								continue;
 							}
+							const bool blocked = (bw >> (i & 31)) & 1u;
+							const uint32_t p = G.g2p((uint32_t)i);
 							for (int r = 0; r < lb; r++)
 							{
-								const uint32_t *dl = sdist + (size_t)r * T;
+								const uint32_t *dl = sdist + (size_t)r * Tp;
+								uint32_t dv = dl[p], hop = MTD_INF;
+								if (blocked)
+								{
+									// parked at 0: a blocked source keeps 0, every other blocked tile is unreachable
+									bool is_src = false;
+									if (P.nsrc > 1)
+										for (int s = 0; s < nsrc_layer; s++)
+											is_src |= s_srcp[s] == p;
+									else
+										is_src = s_srcp[l0 + r] == p;
+									dv = is_src ? 0u : MTD_INF;
+								}
+								else if (gtiles && dv != MTD_INF && dv != 0u)
+								{
+									uint32_t hp;
+									if (P.nsrc > 1)
+										hp = next_hop_p(dl, wr, wd, Wp, p, dv, [&](uint32_t u)
+											{
+												bool s_ = false;
+												for (int s = 0; s < nsrc_layer; s++)
+													s_ |= s_srcp[s] == u;
+												return s_;
+											});
+									else
+									{
+										const uint32_t sp = s_srcp[l0 + r];
+										hp = next_hop_p(dl, wr, wd, Wp, p, dv, [&](uint32_t u) { return u == sp; });
+									}
+									hop = hp == MTD_INF ? MTD_INF : G.p2g(hp);
+								}
 								if (gdist)
-									st_stream_u32(gdist + (size_t)(l0 + r) * T + i, dl[i]);
+									st_stream_u32(gdist + (size_t)(l0 + r) * T + i, dv);
 								if (gtiles)
-									st_stream_u32(gtiles + (size_t)(l0 + r) * T + i, next_hop_w(dl, W, H, x, y, (uint32_t)i, wu, wl, wrr, wdn));
+									st_stream_u32(gtiles + (size_t)(l0 + r) * T + i, hop);
 							}
 						}
 					}
@@ -735,7 +840,6 @@ namespace mtd
 			if (!resident_all)
 			{
 				// single map with more layers than fit: walk the layers just written to global memory (L2), warp 0
-				workers_sync(); // every warp's stores of the last pass are done
 				if (warp == 0)
 					walk_map_global(P, mapi, w_wp, w_D, w_fd, lane);
 				continue;
@@ -745,5 +849,13 @@ namespace mtd
 			if (tid == 0)
 				walk_aggregates(n, s_fd, P.agg + (size_t)mapi * 3);
 		}
+#ifdef MTD_TIMING
+		if (blockIdx.x == 0 && tid == 0)
+		{
+			printf("TIMING rounds=%llu items=%llu | ctl+thr=%llu body=%llu redux+sts=%llu barrier=%llu looptop=%llu (cycles, warp 0 of layer 0, CTA 0)\n", g_timing[5], g_timing[6], g_timing[0], g_timing[1], g_timing[2], g_timing[3], g_timing[4]);
+			for (int k = 0; k < 8; k++)
+				g_timing[k] = 0;
+		}
+#endif
 	}
 }

@@ -396,7 +396,7 @@ def test_mapgen_batch_walker_warp_and_group_widths(ctx, oracle, gw, walker):
         ctx.debug_set(ctx.DEBUG_WALKER, walker)
         g = ctx.mapgen_batch(KAT_SEED[0], KAT_SEED[1], 100, n, cap=2048)
     finally:
-        ctx.debug_set(ctx.DEBUG_GROUP_WARPS, 4)
+        ctx.debug_set(ctx.DEBUG_GROUP_WARPS, 2)
         ctx.debug_set(ctx.DEBUG_WALKER, 0)
     for k in range(n):
         o = oracle.mapgen(KAT_SEED[0] + 100 + k, KAT_SEED[1], cap=2048)
