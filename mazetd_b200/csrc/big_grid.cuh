@@ -1,18 +1,27 @@
 // big_grid.cuh -- distance / direction maps for grids that do not fit shared memory (4096^2 ... 16384^2).
 //
-// Directions::update (sources/map/paths.cpp:24-78) as tile-local wavefront relaxation:
+// Directions::update (sources/map/paths.cpp:24-78) as tile-local wavefront relaxation, all layers of one
+// Waypoints::update in flight together (a work item is one (layer, tile) pair):
 //   k_edge_weights   Grid::neighborDistance of every right/down edge, once per grid (sources/map/grid.cpp:141-145)
-//   k_big_init       distances := m, sources := 0 (paths.cpp:40-49), seed the tile work-list
-//   k_tile_round     one global round: every active TSxTS tile is loaded with a 1-cell apron into shared memory
-//                    by ONE WARP, relaxed to local convergence by the warp wavefront engine (sssp_warp.cuh),
-//                    written back, and the tiles across any improved edge are queued for the next round
+//   k_big_init       distances := m, blocked tiles PARKED at 0 (paths.cpp:40-43, 65-67), work-list cleared
+//   k_big_seed       sources := 0 (paths.cpp:48-49), their tiles queued for round 0
+//   k_tile_round     one global round: every active 64x64 tile is staged with a 1-cell apron in shared memory by ONE
+//                    WARP (16-byte cp.async.cg rows, L2-coherent), relaxed to local convergence by a bucketed
+//                    wavefront (bucket width 255 = lower bound of every edge weight), written back with 16-byte
+//                    stores, and the tiles across any improved border line are queued for the next round
 //   k_round_advance  flips the double-buffered work-list
-//   k_directions     tiles[v] from final distances (closed form of the heap order, see sssp_warp.cuh)
+//   k_big_finalize   tiles[v] from final distances (closed form of the heap order, see sssp_warp.cuh); parked blocked
+//                    tiles read m again
 // The fixpoint is unique, so the result is bit-identical to the reference whatever the schedule.
+//
+// Frame layout in shared memory: (TS + 2) rows of PITCH = TS + 8 words; grid column gx0 + rx sits at word rx + 3, so the
+// 64 interior words of a row start 16-byte aligned. The apron is read once (each finite apron label relaxes its one
+// interior neighbour) and then parked at 0 like blocked cells: the four neighbours of an interior cell are p-1, p+1,
+// p-PITCH, p+PITCH with no bounds or flag test, and nothing is ever relaxed outward.
 //
 // Row-striped multi-GPU: each rank runs the same kernels on rows [y0, y1) of the grid; the apron rows just
 // outside a stripe are read from the neighbour rank's distance array through a peer pointer (NVLink load) and
-// tiles of the neighbour stripe are activated by peer stores into its stamp/list -- see BigParams::peer_*.
+// improvements of a stripe's first / last row raise a flag the neighbour rank turns into tile activations.
 #pragma once
 
 #include "common.cuh"
@@ -20,27 +29,29 @@
 
 namespace mtd
 {
+	constexpr uint32_t BIG_SETTLE_LIMIT = MTD_GUARD - (1u << 17); // labels this close to the guard band are reported, not expanded
+
 	struct BigParams
 	{
 		int W, H;               // full grid
 		int y0, y1;             // rows owned by this rank (single GPU: 0, H)
 		int tilesX, tilesY;     // tiles of the owned stripe
-		uint32_t *dist;         // [H_local][W] rows y0..y1 (local row r = y - y0)
+		int nlayers, nsrc;      // independent layers relaxed together; sources per layer
+		uint32_t *dist;         // [nlayers][H_local][W] rows y0..y1 (local row r = y - y0)
+		size_t layer_stride;    // elements between layers of dist
 		const uint32_t *wpack;  // [H_local][W]  (wr - 255) | (wd - 255) << 16 ; wd of the last local row refers to row y1 (valid if y1 < H)
 		const uint8_t *blocked; // [H_local][W]
-		const uint32_t *sources; // device array of global tile indices
-		int nsrc;
-		uint32_t *list[2];      // tile work-lists
+		const uint32_t *sources; // device array [nlayers][nsrc] of global tile indices
+		uint32_t *list[2];      // work-lists of items = layer * ntiles + tile
 		uint32_t *count;        // [2]
 		uint32_t *cursor;       // [1]
-		uint32_t *stamp;        // [tiles] last round this tile was queued for
-		uint32_t *total_active; // [1] running sum of processed tiles (statistics)
+		uint32_t *stamp;        // [nlayers * ntiles] last round this item was queued for
+		uint32_t *total_active; // [1] running sum of processed items (statistics)
 		int *status;
-		// stripe neighbours (null on a single GPU or at the grid edge)
+		int aligned16;          // W % 4 == 0 and every base pointer 16-byte aligned: rows move as 16-byte vectors
+		// stripe neighbours (null on a single GPU or at the grid edge); nlayers == 1 when striped
 		const uint32_t *up_row;    // distance row y0-1 on the rank above (peer memory), [W]
 		const uint32_t *down_row;  // distance row y1 on the rank below, [W]
-		const uint8_t *up_blocked; // blocked row y0-1 / y1 (local copies made at upload)
-		const uint8_t *down_blocked;
 		const uint32_t *up_wpack;  // wpack row y0-1 (for wd of the edge (y0-1) -> y0), local copy
 		uint32_t *peer_flag_up;    // [tilesX] set to 1 when this rank improved its first row over that tile column
 		uint32_t *peer_flag_down;  // [tilesX] same for the last row
@@ -68,27 +79,34 @@ namespace mtd
 	}
 
 	// ---- init ----------------------------------------------------------------------------------------
-	__global__ void k_fill_u32(uint32_t *p, size_t n, uint32_t v)
+	// every layer: m everywhere, blocked tiles parked at 0 (never relaxed: >= 255 cannot lower 0)
+	__global__ void k_big_init(uint32_t *__restrict__ dist, size_t layer_stride, int nlayers, size_t n, const uint8_t *__restrict__ blocked)
 	{
 		for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-			p[i] = v;
+		{
+			const uint32_t v = blocked[i] ? 0u : MTD_INF;
+			for (int l = 0; l < nlayers; l++)
+				__stcg(dist + (size_t)l * layer_stride + i, v);
+		}
 	}
 
 	template<int TS>
-	__global__ void k_big_seed(const BigParams P, uint32_t extra_blocked_unused)
+	__global__ void k_big_seed(const BigParams P)
 	{
-		// one thread per source: distance 0 and queue its tile for round 0
+		// one thread per (layer, source): distance 0 and queue its tile for round 0
 		const int s = blockIdx.x * blockDim.x + threadIdx.x;
-		if (s >= P.nsrc)
+		if (s >= P.nlayers * P.nsrc)
 			return;
+		const int layer = s / P.nsrc;
 		const uint32_t src = P.sources[s];
 		const int x = (int)(src % (uint32_t)P.W), y = (int)(src / (uint32_t)P.W);
 		if (y < P.y0 || y >= P.y1)
 			return;
-		P.dist[(size_t)(y - P.y0) * P.W + x] = 0u;
-		const uint32_t tile = (uint32_t)(((y - P.y0) / TS) * P.tilesX + x / TS);
-		if (atomicMax(&P.stamp[tile], 1u) < 1u) // round r uses stamp r + 1
-			P.list[0][atomicAdd(&P.count[0], 1u)] = tile;
+		P.dist[(size_t)layer * P.layer_stride + (size_t)(y - P.y0) * P.W + x] = 0u;
+		const uint32_t ntiles = (uint32_t)(P.tilesX * P.tilesY);
+		const uint32_t item = (uint32_t)layer * ntiles + (uint32_t)(((y - P.y0) / TS) * P.tilesX + x / TS);
+		if (atomicMax(&P.stamp[item], 1u) < 1u) // round r uses stamp r + 1
+			P.list[0][atomicAdd(&P.count[0], 1u)] = item;
 	}
 
 	__global__ void k_round_advance(const BigParams P, int round, uint32_t *host_flag)
@@ -104,26 +122,34 @@ namespace mtd
 	template<int TS>
 	struct TileSmem
 	{
-		static constexpr int RW = TS + 2;
-		static constexpr int CELLS = RW * RW;
-		static constexpr int NW = (CELLS + 31) / 32;
-		static constexpr int QCAP = TS >= 64 ? 512 : 256;
-		uint32_t dist[CELLS];
-		uint16_t wr[CELLS];
-		uint16_t wd[CELLS];
-		uint32_t inq[NW];
-		uint16_t q[QCAP];
+		static constexpr int RW = TS + 2;      // frame rows / columns (interior + apron)
+		static constexpr int PITCH = TS + 8;   // words per frame row; column rx lives at word rx + 3
+		static constexpr int CELLS = RW * PITCH;
+		static constexpr int QCAP = 1024;
+		uint32_t d[CELLS];        // labels
+		uint32_t w[CELLS];        // packed edge weights of the same cells
 		uint32_t edge_old[4][TS]; // top, bottom, left, right interior lines as loaded
+		uint16_t q[2][QCAP];      // pending cells (frame word index), double buffered
 	};
 
-	__device__ __forceinline__ void activate_tile(const BigParams &P, int tx, int ty, int round)
+	__device__ __forceinline__ void cp_async_16(void *smem_dst, const void *gsrc)
+	{
+		asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+	}
+
+	__device__ __forceinline__ void cp_async_wait_all()
+	{
+		asm volatile("cp.async.wait_all;" ::: "memory");
+	}
+
+	__device__ __forceinline__ void activate_item(const BigParams &P, int layer, int tx, int ty, int round)
 	{
 		if (tx < 0 || tx >= P.tilesX || ty < 0 || ty >= P.tilesY)
 			return;
-		const uint32_t tile = (uint32_t)(ty * P.tilesX + tx);
+		const uint32_t item = (uint32_t)layer * (uint32_t)(P.tilesX * P.tilesY) + (uint32_t)(ty * P.tilesX + tx);
 		const uint32_t want = (uint32_t)round + 2u; // stamp for round + 1
-		if (atomicMax(&P.stamp[tile], want) < want)
-			P.list[(round + 1) & 1][atomicAdd(&P.count[(round + 1) & 1], 1u)] = tile;
+		if (atomicMax(&P.stamp[item], want) < want)
+			P.list[(round + 1) & 1][atomicAdd(&P.count[(round + 1) & 1], 1u)] = item;
 	}
 
 	template<int TS, int WARPS>
@@ -132,11 +158,12 @@ namespace mtd
 		extern __shared__ __align__(16) unsigned char smem_raw[];
 		using TSm = TileSmem<TS>;
 		TSm &S = ((TSm *)smem_raw)[threadIdx.x >> 5];
-		constexpr int RW = TSm::RW;
+		constexpr int RW = TSm::RW, PITCH = TSm::PITCH, QCAP = TSm::QCAP;
 		const uint32_t lane = lane_id();
 		const uint32_t lt = lanemask_lt();
 		const int W = P.W;
 		const int Hl = P.y1 - P.y0;
+		const uint32_t ntiles = (uint32_t)(P.tilesX * P.tilesY);
 		const uint32_t *list = P.list[round & 1];
 		const uint32_t count = P.count[round & 1];
 
@@ -148,162 +175,341 @@ namespace mtd
 			item = __shfl_sync(FULL_MASK, item, 0);
 			if (item >= count)
 				break;
-			const uint32_t tile = list[item];
+			const uint32_t it = list[item];
+			const int layer = (int)(it / ntiles);
+			const uint32_t tile = it - (uint32_t)layer * ntiles;
 			const int tx = (int)(tile % (uint32_t)P.tilesX), ty = (int)(tile / (uint32_t)P.tilesX);
-			const int gx0 = tx * TS - 1;          // global x of region column 0
-			const int ly0 = ty * TS - 1;          // local row of region row 0
+			const int gx0 = tx * TS - 1; // global x of frame column 0
+			const int ly0 = ty * TS - 1; // local row of frame row 0
+			uint32_t *ldist = P.dist + (size_t)layer * P.layer_stride;
+			const uint32_t *lsrc = P.sources + (size_t)layer * P.nsrc;
+			const bool full_w = P.aligned16 && gx0 + 1 + TS <= W; // the 64 interior columns are inside the grid and 16-byte aligned
 
-			// ---- load region (interior + apron) ----
+			// ---- stage the frame: labels + packed weights. Cells outside the grid are parked at 0. ----
 			for (int ry = 0; ry < RW; ry++)
 			{
 				const int ly = ly0 + ry; // local row; may be -1 or Hl (neighbour stripe or outside)
 				const uint32_t *drow = nullptr;
 				const uint32_t *wrow = nullptr;
-				const uint8_t *brow = nullptr;
 				if (ly >= 0 && ly < Hl)
 				{
-					drow = P.dist + (size_t)ly * W;
+					drow = ldist + (size_t)ly * W;
 					wrow = P.wpack + (size_t)ly * W;
-					brow = P.blocked + (size_t)ly * W;
 				}
 				else if (ly < 0 && P.up_row)
 				{
 					drow = P.up_row;
 					wrow = P.up_wpack;
-					brow = P.up_blocked;
 				}
 				else if (ly >= Hl && P.down_row)
+					drow = P.down_row; // weights of the row below are never needed (edges are stored on the upper / left cell)
+				uint32_t *sd = S.d + ry * PITCH + 3;
+				uint32_t *sw = S.w + ry * PITCH + 3;
+				if (drow && full_w)
 				{
-					drow = P.down_row;
-					wrow = nullptr; // weights of the row below are never needed (edges are stored on the upper/left cell)
-					brow = P.down_blocked;
-				}
-				for (int rx = (int)lane; rx < RW; rx += 32)
-				{
-					const int gx = gx0 + rx;
-					uint32_t v = 0u, wp = 0u; // outside the grid: parked at 0 like a blocked tile
-					if (drow && gx >= 0 && gx < W)
+					// 64 interior words = 16 x 16 bytes, L2-coherent (.cg); lanes 16..31 move the weights
+					const int k = (int)(lane & 15u) * 4;
+					if (lane < 16u)
+						cp_async_16(sd + 1 + k, drow + gx0 + 1 + k);
+					else if (wrow)
+						cp_async_16(sw + 1 + k, wrow + gx0 + 1 + k);
+					else
+						*reinterpret_cast<uint4 *>(sw + 1 + k) = make_uint4(0u, 0u, 0u, 0u);
+					// the two apron columns
+					if (lane < 2u)
 					{
-						v = __ldcg(drow + gx); // L2: other SMs (and peers) update these concurrently
-						if (brow[gx] && v != 0u)
-							v = 0u; // blocked, not a source
-						if (wrow)
-							wp = wrow[gx];
+						const int rx = lane == 0u ? 0 : RW - 1;
+						const int gx = gx0 + rx;
+						const bool in = gx >= 0 && gx < W;
+						sd[rx] = in ? __ldcg(drow + gx) : 0u;
+						sw[rx] = in && wrow ? wrow[gx] : 0u;
 					}
-					S.dist[ry * RW + rx] = v;
-					S.wr[ry * RW + rx] = (uint16_t)(wp & 0xFFFFu);
-					S.wd[ry * RW + rx] = (uint16_t)(wp >> 16);
+				}
+				else
+				{
+					for (int rx = (int)lane; rx < RW; rx += 32)
+					{
+						const int gx = gx0 + rx;
+						const bool in = drow && gx >= 0 && gx < W;
+						sd[rx] = in ? __ldcg(drow + gx) : 0u;
+						sw[rx] = in && wrow ? wrow[gx] : 0u;
+					}
 				}
 			}
-			for (int i = (int)lane; i < TSm::NW; i += 32)
-				S.inq[i] = 0u;
+			cp_async_wait_all();
 			__syncwarp();
 			// remember the interior border lines to detect changes
 			for (int i = (int)lane; i < TS; i += 32)
 			{
-				S.edge_old[0][i] = S.dist[1 * RW + 1 + i];
-				S.edge_old[1][i] = S.dist[TS * RW + 1 + i];
-				S.edge_old[2][i] = S.dist[(1 + i) * RW + 1];
-				S.edge_old[3][i] = S.dist[(1 + i) * RW + TS];
+				S.edge_old[0][i] = S.d[1 * PITCH + 4 + i];
+				S.edge_old[1][i] = S.d[TS * PITCH + 4 + i];
+				S.edge_old[2][i] = S.d[(1 + i) * PITCH + 4];
+				S.edge_old[3][i] = S.d[(1 + i) * PITCH + 3 + TS];
 			}
 
-			// ---- seeds: finite apron cells (improved neighbours) and every source inside the region.
-			//      A stored 0 is either a parked (blocked / outside) cell or a source; only the source list says which,
-			//      so sources are seeded explicitly -- also when they sit in the apron, because the first hop across a
-			//      tile border is only ever relaxed by the tile that owns the destination cell. ----
+			// ---- seeds ----
+			// Pending cells enter q[0] with ballot compaction. A label lowered here or later is appended every time it
+			// improves (duplicates are harmless: the second visit relaxes nothing).
 			uint32_t nq = 0, dmin = MTD_INF;
-			bool dropped0 = false;
-			auto seed = [&](bool want, int ry, int rx, bool is_source)
+			bool overflow = false, guard = false;
+			auto relax_into = [&](bool want, uint32_t v, uint32_t nd)
 			{
-				uint32_t v = MTD_INF;
-				const uint32_t c = (uint32_t)(ry * RW + rx);
-				const uint32_t bit = 1u << (c & 31u);
-				if (want)
-				{
-					v = S.dist[c];
-					want = is_source ? v == 0u : (v != MTD_INF && v != 0u);
-				}
-				if (want)
-					want = (atomicOr(&S.inq[c >> 5], bit) & bit) == 0; // dedup
-				const uint32_t bal = __ballot_sync(FULL_MASK, want);
-				if (want)
+				// want: this lane has a candidate label nd for interior cell v
+				bool improved = false;
+				if (want && nd >= BIG_SETTLE_LIMIT)
+					guard = true; // the reference's uint32 arithmetic is about to wrap: report, do not expand
+				else if (want)
+					improved = nd < atomicMin(&S.d[v], nd);
+				const uint32_t bal = __ballot_sync(FULL_MASK, improved);
+				if (improved)
 				{
 					const uint32_t slot = nq + __popc(bal & lt);
-					if (slot < (uint32_t)TSm::QCAP)
-						S.q[slot] = pack_yx(ry, rx);
-					dmin = min(dmin, v);
+					if (slot < (uint32_t)QCAP)
+						S.q[0][slot] = (uint16_t)v;
+					dmin = min(dmin, nd);
 				}
-				const uint32_t total = nq + (uint32_t)__popc(bal);
-				if (total > (uint32_t)TSm::QCAP)
-					dropped0 = true; // stays marked in inq; the engine re-collects it
-				nq = min(total, (uint32_t)TSm::QCAP);
+				nq += (uint32_t)__popc(bal);
 			};
-			for (int i0 = 0; i0 < RW; i0 += 32)
+			// (1) apron: every finite, non-parked apron label relaxes its single interior neighbour; a label of 0 is a
+			//     parked cell unless the source list says otherwise, so sources on the apron are handled from the list
+			for (int i0 = 0; i0 < TS; i0 += 32)
 			{
 				const int i = i0 + (int)lane;
-				const bool in = i >= 1 && i < RW - 1; // corners have no neighbour inside the tile
-				const int ii = in ? i : 1;
-				seed(in, 0, ii, false);
-				seed(in, RW - 1, ii, false);
-				seed(in, ii, 0, false);
-				seed(in, ii, RW - 1, false);
+				{
+					const uint32_t a = (uint32_t)(0 * PITCH + 4 + i), v = a + PITCH; // top
+					const uint32_t da = S.d[a];
+					relax_into(da != 0u && da != MTD_INF, v, da + MIN_EDGE + (S.w[a] >> 16));
+				}
+				{
+					const uint32_t a = (uint32_t)((TS + 1) * PITCH + 4 + i), v = a - PITCH; // bottom
+					const uint32_t da = S.d[a];
+					relax_into(da != 0u && da != MTD_INF, v, da + MIN_EDGE + (S.w[v] >> 16));
+				}
+				{
+					const uint32_t a = (uint32_t)((1 + i) * PITCH + 3), v = a + 1u; // left
+					const uint32_t da = S.d[a];
+					relax_into(da != 0u && da != MTD_INF, v, da + MIN_EDGE + (S.w[a] & 0xFFFFu));
+				}
+				{
+					const uint32_t a = (uint32_t)((1 + i) * PITCH + 4 + TS), v = a - 1u; // right
+					const uint32_t da = S.d[a];
+					relax_into(da != 0u && da != MTD_INF, v, da + MIN_EDGE + (S.w[v] & 0xFFFFu));
+				}
 			}
 			for (int s0 = 0; s0 < P.nsrc; s0 += 32)
 			{
 				const int s = s0 + (int)lane;
 				bool want = false;
-				int ry = 0, rx = 0;
+				uint32_t v = 0, nd = 0;
 				if (s < P.nsrc)
 				{
-					const uint32_t src = P.sources[s];
-					const int sx = (int)(src % (uint32_t)W), sy = (int)(src / (uint32_t)W) - P.y0;
-					rx = sx - gx0;
-					ry = sy - ly0;
-					want = rx >= 0 && rx < RW && ry >= 0 && ry < RW;
-					if (!want)
-						rx = ry = 0;
+					const uint32_t src = lsrc[s];
+					const int rx = (int)(src % (uint32_t)W) - gx0, ry = (int)(src / (uint32_t)W) - P.y0 - ly0;
+					const bool inx = rx >= 1 && rx <= TS, iny = ry >= 1 && ry <= TS;
+					const uint32_t a = (uint32_t)(ry * PITCH + rx + 3);
+					if (ry == 0 && inx)
+					{
+						want = true;
+						v = a + PITCH;
+						nd = MIN_EDGE + (S.w[a] >> 16);
+					}
+					else if (ry == TS + 1 && inx)
+					{
+						want = true;
+						v = a - PITCH;
+						nd = MIN_EDGE + (S.w[v] >> 16);
+					}
+					else if (rx == 0 && iny)
+					{
+						want = true;
+						v = a + 1u;
+						nd = MIN_EDGE + (S.w[a] & 0xFFFFu);
+					}
+					else if (rx == TS + 1 && iny)
+					{
+						want = true;
+						v = a - 1u;
+						nd = MIN_EDGE + (S.w[v] & 0xFFFFu);
+					}
 				}
-				seed(want, ry, rx, true);
+				relax_into(want, v, nd);
 			}
+			__syncwarp();
+			// (2) park the apron: nothing is relaxed outward, and interior cells need no bounds test
+			for (int i = (int)lane; i < TS; i += 32)
+			{
+				S.d[0 * PITCH + 4 + i] = 0u;
+				S.d[(TS + 1) * PITCH + 4 + i] = 0u;
+				S.d[(1 + i) * PITCH + 3] = 0u;
+				S.d[(1 + i) * PITCH + 4 + TS] = 0u;
+			}
+			__syncwarp();
+			// (3) sources inside the tile expand from label 0 (also when they are blocked: paths.cpp:63-67 test only the neighbour)
+			for (int s0 = 0; s0 < P.nsrc; s0 += 32)
+			{
+				const int s = s0 + (int)lane;
+				bool want = false;
+				uint32_t c = 0;
+				if (s < P.nsrc)
+				{
+					const uint32_t src = lsrc[s];
+					const int rx = (int)(src % (uint32_t)W) - gx0, ry = (int)(src / (uint32_t)W) - P.y0 - ly0;
+					want = rx >= 1 && rx <= TS && ry >= 1 && ry <= TS;
+					c = want ? (uint32_t)(ry * PITCH + rx + 3) : (uint32_t)(PITCH + 4);
+				}
+				relax_into(want, c - PITCH, MIN_EDGE + (S.w[c - PITCH] >> 16));
+				relax_into(want, c - 1u, MIN_EDGE + (S.w[c - 1u] & 0xFFFFu));
+				relax_into(want, c + 1u, MIN_EDGE + (S.w[c] & 0xFFFFu));
+				relax_into(want, c + PITCH, MIN_EDGE + (S.w[c] >> 16));
+			}
+			overflow = nq > (uint32_t)QCAP;
 			dmin = warp_min_u32(dmin);
 			__syncwarp();
 
-			WarpTile<uint16_t, TSm::QCAP> t;
-			t.dist = S.dist;
-			t.wr = S.wr;
-			t.wd = S.wd;
-			t.inq = S.inq;
-			t.q = S.q;
-			t.W = RW;
-			t.H = RW;
-			const bool guard = (nq || dropped0) ? warp_relax(t, nq, dmin, dropped0) : false;
-			if (guard && lane == 0)
+			// ---- bucketed wavefront on the frame (label-correcting across visits, Dijkstra order within one) ----
+			uint32_t par = 0;
+			while (dmin != MTD_INF && !overflow)
+			{
+				const uint32_t thr = dmin + MIN_EDGE;
+				const uint16_t *rq = S.q[par];
+				uint16_t *wq = S.q[par ^ 1u];
+				uint32_t outn = 0, newmin = MTD_INF;
+				for (uint32_t base = 0; base < nq; base += 32u)
+				{
+					const uint32_t idx = base + lane;
+					const bool active = idx < nq;
+					const uint32_t c = active ? rq[idx] : (uint32_t)(PITCH + 4);
+					const uint32_t d = active ? S.d[c] : MTD_INF;
+					const bool settle = d < thr;
+					const bool keep = active && !settle;
+					uint32_t n0 = 0, n1 = 0, n2 = 0, n3 = 0;
+					bool i0 = false, i1 = false, i2 = false, i3 = false;
+					if (settle)
+					{
+						// 0: up, 1: left, 2: right, 3: down -- weights are stored on the upper / left cell of an edge
+						const uint32_t wc = S.w[c], base_nd = d + MIN_EDGE;
+						n0 = base_nd + (S.w[c - PITCH] >> 16);
+						n1 = base_nd + (S.w[c - 1u] & 0xFFFFu);
+						n2 = base_nd + (wc & 0xFFFFu);
+						n3 = base_nd + (wc >> 16);
+						if (base_nd >= BIG_SETTLE_LIMIT)
+							guard = true;
+						else
+						{
+							i0 = n0 < atomicMin(&S.d[c - PITCH], n0);
+							i1 = n1 < atomicMin(&S.d[c - 1u], n1);
+							i2 = n2 < atomicMin(&S.d[c + 1u], n2);
+							i3 = n3 < atomicMin(&S.d[c + PITCH], n3);
+						}
+					}
+					uint32_t lm = keep ? d : MTD_INF;
+					lm = i0 ? min(lm, n0) : lm;
+					lm = i1 ? min(lm, n1) : lm;
+					lm = i2 ? min(lm, n2) : lm;
+					lm = i3 ? min(lm, n3) : lm;
+					newmin = min(newmin, lm);
+					const uint32_t bk = __ballot_sync(FULL_MASK, keep);
+					const uint32_t b0 = __ballot_sync(FULL_MASK, i0);
+					const uint32_t b1 = __ballot_sync(FULL_MASK, i1);
+					const uint32_t b2 = __ballot_sync(FULL_MASK, i2);
+					const uint32_t b3 = __ballot_sync(FULL_MASK, i3);
+					uint32_t pos = outn + __popc(bk & lt);
+					if (keep && pos < (uint32_t)QCAP)
+						wq[pos] = (uint16_t)c;
+					outn += __popc(bk);
+					pos = outn + __popc(b0 & lt);
+					if (i0 && pos < (uint32_t)QCAP)
+						wq[pos] = (uint16_t)(c - PITCH);
+					outn += __popc(b0);
+					pos = outn + __popc(b1 & lt);
+					if (i1 && pos < (uint32_t)QCAP)
+						wq[pos] = (uint16_t)(c - 1u);
+					outn += __popc(b1);
+					pos = outn + __popc(b2 & lt);
+					if (i2 && pos < (uint32_t)QCAP)
+						wq[pos] = (uint16_t)(c + 1u);
+					outn += __popc(b2);
+					pos = outn + __popc(b3 & lt);
+					if (i3 && pos < (uint32_t)QCAP)
+						wq[pos] = (uint16_t)(c + PITCH);
+					outn += __popc(b3);
+				}
+				overflow = outn > (uint32_t)QCAP;
+				nq = outn;
+				dmin = warp_min_u32(newmin);
+				par ^= 1u;
+				__syncwarp();
+			}
+			if (overflow)
+			{
+				// the pending set outgrew the queue (pathological frontiers): queue-less sweeps to the local fixpoint.
+				// Parked cells hold 0 and never expand; sources expanded in (3) before anything could overflow.
+				bool changed = true;
+				while (changed)
+				{
+					changed = false;
+					for (int i = (int)lane; i < TS * TS; i += 32)
+					{
+						const uint32_t c = (uint32_t)((1 + i / TS) * PITCH + 4 + i % TS);
+						const uint32_t d = S.d[c];
+						if (d == 0u || d == MTD_INF)
+							continue;
+						const uint32_t base_nd = d + MIN_EDGE;
+						if (base_nd >= BIG_SETTLE_LIMIT)
+						{
+							guard = true;
+							continue;
+						}
+						const uint32_t wc = S.w[c];
+						const uint32_t n0 = base_nd + (S.w[c - PITCH] >> 16), n1 = base_nd + (S.w[c - 1u] & 0xFFFFu), n2 = base_nd + (wc & 0xFFFFu), n3 = base_nd + (wc >> 16);
+						changed |= n0 < atomicMin(&S.d[c - PITCH], n0);
+						changed |= n1 < atomicMin(&S.d[c - 1u], n1);
+						changed |= n2 < atomicMin(&S.d[c + 1u], n2);
+						changed |= n3 < atomicMin(&S.d[c + PITCH], n3);
+					}
+					changed = __any_sync(FULL_MASK, changed);
+				}
+			}
+			if (__any_sync(FULL_MASK, guard) && lane == 0)
 				atomicOr(P.status, 1);
 			__syncwarp();
 
-			// ---- write back improved interior cells; 0 = parked/source: global already holds the right value ----
-			for (int ry = 1; ry <= TS; ry++)
+			// ---- write back the interior (labels only ever decrease; parked and unreached cells rewrite their own value) ----
+			if (full_w)
 			{
-				const int ly = ly0 + ry;
-				if (ly >= Hl)
-					break;
-				uint32_t *drow = P.dist + (size_t)ly * W;
-				for (int rx = 1 + (int)lane; rx <= TS; rx += 32)
+				// two rows per instruction, 16 bytes per lane
+				for (int r2 = 0; r2 < TS; r2 += 2)
 				{
-					const int gx = gx0 + rx;
-					const uint32_t v = S.dist[ry * RW + rx];
-					if (gx < W && v != 0u && v != MTD_INF)
-						__stcg(drow + gx, v);
+					const int iy = r2 + (int)(lane >> 4);
+					const int ly = ly0 + 1 + iy;
+					if (ly < Hl)
+					{
+						const int k = (int)(lane & 15u) * 4;
+						const uint4 v = *reinterpret_cast<const uint4 *>(S.d + (1 + iy) * PITCH + 4 + k);
+						__stcg(reinterpret_cast<uint4 *>(ldist + (size_t)ly * W + gx0 + 1 + k), v);
+					}
+				}
+			}
+			else
+			{
+				for (int iy = 0; iy < TS; iy++)
+				{
+					const int ly = ly0 + 1 + iy;
+					if (ly >= Hl)
+						break;
+					for (int ix = (int)lane; ix < TS; ix += 32)
+						if (gx0 + 1 + ix < W)
+							__stcg(ldist + (size_t)ly * W + gx0 + 1 + ix, S.d[(1 + iy) * PITCH + 4 + ix]);
 				}
 			}
 			// ---- activate neighbours across improved border lines ----
 			bool ch[4] = { false, false, false, false };
 			for (int i = (int)lane; i < TS; i += 32)
 			{
-				ch[0] |= S.dist[1 * RW + 1 + i] != S.edge_old[0][i];
-				ch[1] |= S.dist[TS * RW + 1 + i] != S.edge_old[1][i];
-				ch[2] |= S.dist[(1 + i) * RW + 1] != S.edge_old[2][i];
-				ch[3] |= S.dist[(1 + i) * RW + TS] != S.edge_old[3][i];
+				ch[0] |= S.d[1 * PITCH + 4 + i] != S.edge_old[0][i];
+				ch[1] |= S.d[TS * PITCH + 4 + i] != S.edge_old[1][i];
+				ch[2] |= S.d[(1 + i) * PITCH + 4] != S.edge_old[2][i];
+				ch[3] |= S.d[(1 + i) * PITCH + 3 + TS] != S.edge_old[3][i];
 			}
 			const bool c0 = __any_sync(FULL_MASK, ch[0]), c1 = __any_sync(FULL_MASK, ch[1]);
 			const bool c2 = __any_sync(FULL_MASK, ch[2]), c3 = __any_sync(FULL_MASK, ch[3]);
@@ -313,83 +519,103 @@ namespace mtd
 				if (c0)
 				{
 					if (ty > 0)
-						activate_tile(P, tx, ty - 1, round);
+						activate_item(P, layer, tx, ty - 1, round);
 					else if (P.peer_flag_up)
 						P.peer_flag_up[tx] = 1u;
 				}
 				if (c1)
 				{
 					if (ty < P.tilesY - 1)
-						activate_tile(P, tx, ty + 1, round);
+						activate_item(P, layer, tx, ty + 1, round);
 					else if (P.peer_flag_down)
 						P.peer_flag_down[tx] = 1u;
 				}
 				if (c2)
-					activate_tile(P, tx - 1, ty, round);
+					activate_item(P, layer, tx - 1, ty, round);
 				if (c3)
-					activate_tile(P, tx + 1, ty, round);
+					activate_item(P, layer, tx + 1, ty, round);
 				atomicAdd(P.total_active, 1u);
 			}
 			__syncwarp();
 		}
 	}
 
-	// ---- next-hop tiles from final distances -----------------------------------------------------------
-	// one thread per tile; neighbours come through L1/L2 (each distance is read by 5 threads of nearby warps)
-	__global__ void k_directions(int W, int Hl, int y0, int H, const uint32_t *__restrict__ dist, const uint32_t *__restrict__ wpack, const uint32_t *__restrict__ up_row, const uint32_t *__restrict__ up_wpack, const uint32_t *__restrict__ down_row, uint32_t *__restrict__ tiles)
+	// ---- next-hop tiles from final distances; parked blocked tiles read m again ---------------------------
+	// One thread per tile of one layer (blockIdx.y = layer); neighbours come through L1/L2. A label of 0 is a source or a
+	// parked blocked tile: the layer's source list tells them apart (a 2048-bit filter in shared memory answers almost
+	// every query without touching the list).
+	__global__ void k_big_finalize(int W, int Hl, int y0, int H, uint32_t *__restrict__ dist_base, size_t layer_stride, const uint32_t *__restrict__ wpack, const uint8_t *__restrict__ blocked, const uint32_t *__restrict__ sources_base, int nsrc, const uint32_t *__restrict__ up_row, const uint32_t *__restrict__ up_wpack, const uint32_t *__restrict__ down_row, uint32_t *__restrict__ tiles_base, size_t tiles_stride)
 	{
+		__shared__ uint32_t filter[64];
+		const int layer = blockIdx.y;
+		uint32_t *dist = dist_base + (size_t)layer * layer_stride;
+		uint32_t *tiles = tiles_base ? tiles_base + (size_t)layer * tiles_stride : nullptr;
+		const uint32_t *sources = sources_base + (size_t)layer * nsrc;
+		for (int i = threadIdx.x; i < 64; i += blockDim.x)
+			filter[i] = 0u;
+		__syncthreads();
+		for (int s = threadIdx.x; s < nsrc; s += blockDim.x)
+		{
+			const uint32_t h = (sources[s] * 2654435761u) >> 21;
+			atomicOr(&filter[h >> 5], 1u << (h & 31u));
+		}
+		__syncthreads();
+		auto is_source = [&](uint32_t g) -> bool
+		{
+			const uint32_t h = (g * 2654435761u) >> 21;
+			if (!((filter[h >> 5] >> (h & 31u)) & 1u))
+				return false;
+			for (int s = 0; s < nsrc; s++)
+				if (sources[s] == g)
+					return true;
+			return false;
+		};
 		const size_t total = (size_t)W * Hl;
 		for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x)
 		{
 			const int x = (int)(i % (size_t)W);
 			const int ly = (int)(i / (size_t)W);
 			const int gy = ly + y0;
+			const uint32_t g = (uint32_t)((size_t)gy * W + x);
 			const uint32_t dv = dist[i];
 			uint32_t best = MTD_INF, bestd = MTD_INF;
-			if (dv != MTD_INF && dv != 0u)
+			if (dv == 0u)
+			{
+				// source (keeps 0, no next hop: paths.cpp:49) or parked blocked tile (never relaxed: paths.cpp:65-67)
+				if (blocked[i] && !is_source(g))
+					dist[i] = MTD_INF;
+			}
+			else if (dv != MTD_INF && tiles)
 			{
 				const uint32_t wp = wpack[i];
+				auto cand = [&](uint32_t du, uint32_t w, uint32_t ug)
+				{
+					if (du != MTD_INF && du + MIN_EDGE + w == dv && du < bestd && (du != 0u || is_source(ug)))
+					{
+						bestd = du;
+						best = ug;
+					}
+				};
 				if (gy > 0)
 				{
 					const bool local = ly > 0;
 					const uint32_t du = local ? dist[i - W] : (up_row ? up_row[x] : MTD_INF);
 					const uint32_t wu = local ? wpack[i - W] : (up_wpack ? up_wpack[x] : 0u);
-					if (du != MTD_INF && du + MIN_EDGE + (wu >> 16) == dv && du < bestd)
-					{
-						bestd = du;
-						best = (uint32_t)((size_t)(gy - 1) * W + x);
-					}
+					cand(du, wu >> 16, g - (uint32_t)W);
 				}
 				if (x > 0)
-				{
-					const uint32_t du = dist[i - 1];
-					if (du != MTD_INF && du + MIN_EDGE + (wpack[i - 1] & 0xFFFFu) == dv && du < bestd)
-					{
-						bestd = du;
-						best = (uint32_t)((size_t)gy * W + x - 1);
-					}
-				}
+					cand(dist[i - 1], wpack[i - 1] & 0xFFFFu, g - 1u);
 				if (x < W - 1)
-				{
-					const uint32_t du = dist[i + 1];
-					if (du != MTD_INF && du + MIN_EDGE + (wp & 0xFFFFu) == dv && du < bestd)
-					{
-						bestd = du;
-						best = (uint32_t)((size_t)gy * W + x + 1);
-					}
-				}
+					cand(dist[i + 1], wp & 0xFFFFu, g + 1u);
 				if (gy < H - 1)
 				{
 					const bool local = ly < Hl - 1;
 					const uint32_t du = local ? dist[i + W] : (down_row ? down_row[x] : MTD_INF);
-					if (du != MTD_INF && du + MIN_EDGE + (wp >> 16) == dv && du < bestd)
-					{
-						bestd = du;
-						best = (uint32_t)((size_t)(gy + 1) * W + x);
-					}
+					cand(du, wp >> 16, g + (uint32_t)W);
 				}
 			}
-			__stcs(tiles + i, best);
+			if (tiles)
+				__stcs(tiles + i, best);
 		}
 	}
 }

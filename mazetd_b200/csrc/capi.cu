@@ -27,7 +27,7 @@ namespace
 {
 	constexpr size_t MAX_SMEM = 227 * 1024 - 1024; // dynamic budget: the opt-in limit is 227 KB per CTA including static __shared__
 	constexpr int BIG_TS = 64;
-	constexpr int BIG_WARPS = 2;
+	constexpr int BIG_WARPS = 1;
 
 	template<class T>
 	struct DevBuf
@@ -64,6 +64,7 @@ namespace
 		uint32_t alive;
 		unsigned long long damage;
 		uint32_t spawn[3];
+		uint32_t stage_blocked; // pinned staging word of the trial grid's extra blocked tile
 	};
 }
 
@@ -333,10 +334,6 @@ namespace
 		CU(ctx->blocked.reserve(ctx->T));
 		ctx->tilesX = (ctx->W + BIG_TS - 1) / BIG_TS;
 		ctx->tilesY = (ctx->H + BIG_TS - 1) / BIG_TS;
-		const size_t nt = (size_t)ctx->tilesX * ctx->tilesY;
-		CU(ctx->list0.reserve(nt));
-		CU(ctx->list1.reserve(nt));
-		CU(ctx->stamp.reserve(nt));
 		CU(ctx->counters.reserve(8));
 		ProfScope prof(ctx, MTD_K_BIG_PREPARE);
 		k_edge_weights<<<grid_blocks(ctx, ctx->T, 256), 256, 0, ctx->stream>>>(ctx->W, ctx->H, ctx->elev.p, nullptr, ctx->flags.p, ctx->wpack.p, ctx->blocked.p);
@@ -344,7 +341,9 @@ namespace
 		return MTD_OK;
 	}
 
-	int big_directions(mtd_ctx *ctx, const uint32_t *h_sources, int nsrc, uint32_t extra_blocked, uint32_t *d_tiles, uint32_t *d_dist)
+	// nlayers independent layers, nsrc sources each (h_sources = [nlayers][nsrc], host), relaxed together: a work item is
+	// one (layer, tile) pair. d_dist / d_tiles = [nlayers][T] (d_tiles may be null).
+	int big_layers(mtd_ctx *ctx, const uint32_t *h_sources, int nlayers, int nsrc, uint32_t extra_blocked, uint32_t *d_tiles, uint32_t *d_dist)
 	{
 		using TSm = TileSmem<BIG_TS>;
 		const size_t smem = sizeof(TSm) * BIG_WARPS;
@@ -355,21 +354,30 @@ namespace
 			configured = true;
 		}
 		const size_t nt = (size_t)ctx->tilesX * ctx->tilesY;
-		CU(ctx->sources.reserve((size_t)nsrc));
-		CU(cudaMemcpyAsync(ctx->sources.p, h_sources, (size_t)nsrc * 4, cudaMemcpyHostToDevice, ctx->stream));
-		CU(cudaMemsetAsync(ctx->stamp.p, 0, nt * 4, ctx->stream));
+		const size_t nitems = nt * (size_t)nlayers;
+		if (nitems >= 0xFFFFFFFFull)
+			return fail(ctx, MTD_ERR_CAPACITY, "too many (layer, tile) work items");
+		CU(ctx->list0.reserve(nitems));
+		CU(ctx->list1.reserve(nitems));
+		CU(ctx->stamp.reserve(nitems));
+		CU(ctx->sources.reserve((size_t)nlayers * nsrc));
+		CU(cudaMemcpyAsync(ctx->sources.p, h_sources, (size_t)nlayers * nsrc * 4, cudaMemcpyHostToDevice, ctx->stream));
+		CU(cudaMemsetAsync(ctx->stamp.p, 0, nitems * 4, ctx->stream));
 		CU(cudaMemsetAsync(ctx->counters.p, 0, 8 * 4, ctx->stream));
-		uint8_t one = 1, zero = 0;
 		uint8_t prev_blocked = 0;
 		if (extra_blocked != MTD_M)
 		{
+			// the trial grid of placingBuildingBlocksMonsters: one more blocked tile for the duration of this call
 			CU(cudaMemcpyAsync(&prev_blocked, ctx->blocked.p + extra_blocked, 1, cudaMemcpyDeviceToHost, ctx->stream));
 			CU(cudaStreamSynchronize(ctx->stream));
-			CU(cudaMemcpyAsync(ctx->blocked.p + extra_blocked, &one, 1, cudaMemcpyHostToDevice, ctx->stream));
+			ctx->hflags->stage_blocked = 1u;
+			CU(cudaMemcpyAsync(ctx->blocked.p + extra_blocked, &ctx->hflags->stage_blocked, 1, cudaMemcpyHostToDevice, ctx->stream));
 		}
-		(void)zero;
-		k_fill_u32<<<grid_blocks(ctx, ctx->T, 256), 256, 0, ctx->stream>>>(d_dist, ctx->T, MTD_INF);
-		LAUNCHED();
+		{
+			ProfScope prof(ctx, MTD_K_BIG_PREPARE);
+			k_big_init<<<grid_blocks(ctx, ctx->T, 256), 256, 0, ctx->stream>>>(d_dist, ctx->T, nlayers, ctx->T, ctx->blocked.p);
+			LAUNCHED();
+		}
 
 		BigParams P;
 		memset(&P, 0, sizeof(P));
@@ -379,11 +387,13 @@ namespace
 		P.y1 = ctx->H;
 		P.tilesX = ctx->tilesX;
 		P.tilesY = ctx->tilesY;
+		P.nlayers = nlayers;
+		P.nsrc = nsrc;
 		P.dist = d_dist;
+		P.layer_stride = ctx->T;
 		P.wpack = ctx->wpack.p;
 		P.blocked = ctx->blocked.p;
 		P.sources = ctx->sources.p;
-		P.nsrc = nsrc;
 		P.list[0] = ctx->list0.p;
 		P.list[1] = ctx->list1.p;
 		P.count = ctx->counters.p;
@@ -391,8 +401,9 @@ namespace
 		P.total_active = ctx->counters.p + 3;
 		P.stamp = ctx->stamp.p;
 		P.status = ctx->d_status.p;
+		P.aligned16 = (ctx->W % 4 == 0) && ((uintptr_t)d_dist % 16 == 0) && ((uintptr_t)ctx->wpack.p % 16 == 0) ? 1 : 0;
 
-		k_big_seed<BIG_TS><<<(nsrc + 127) / 128, 128, 0, ctx->stream>>>(P, extra_blocked);
+		k_big_seed<BIG_TS><<<(nlayers * nsrc + 127) / 128, 128, 0, ctx->stream>>>(P);
 		LAUNCHED();
 
 		uint32_t *d_next = nullptr;
@@ -401,42 +412,39 @@ namespace
 		const int blocks = ctx->sms * (ctas_per_sm > 0 ? ctas_per_sm : 1);
 		int round = 0;
 		int burst = 4;
-		ProfScope *relax_prof = new ProfScope(ctx, MTD_K_BIG_RELAX);
-		struct ProfDone
 		{
-			ProfScope *&p;
-			~ProfDone() { delete p; p = nullptr; }
-		} relax_done{ relax_prof };
-		for (;;)
-		{
-			for (int b = 0; b < burst; b++, round++)
+			ProfScope prof(ctx, MTD_K_BIG_RELAX);
+			for (;;)
 			{
-				k_tile_round<BIG_TS, BIG_WARPS><<<blocks, BIG_WARPS * 32, smem, ctx->stream>>>(P, round);
-				LAUNCHED();
-				k_round_advance<<<1, 1, 0, ctx->stream>>>(P, round, d_next);
-				LAUNCHED();
+				for (int b = 0; b < burst; b++, round++)
+				{
+					k_tile_round<BIG_TS, BIG_WARPS><<<blocks, BIG_WARPS * 32, smem, ctx->stream>>>(P, round);
+					LAUNCHED();
+					k_round_advance<<<1, 1, 0, ctx->stream>>>(P, round, d_next);
+					LAUNCHED();
+				}
+				CU(cudaStreamSynchronize(ctx->stream));
+				if (ctx->hflags->next_count == 0)
+					break;
+				if (burst < 32)
+					burst *= 2;
+				if (round > 4 * (ctx->tilesX + ctx->tilesY) * 64 + 100000)
+					return fail(ctx, MTD_ERR_CUDA, "tile relaxation did not converge after %d rounds", round);
 			}
-			CU(cudaStreamSynchronize(ctx->stream));
-			if (ctx->hflags->next_count == 0)
-				break;
-			if (burst < 32)
-				burst *= 2;
-			if (round > 4 * (ctx->tilesX + ctx->tilesY) * 64 + 100000)
-				return fail(ctx, MTD_ERR_CUDA, "tile relaxation did not converge after %d rounds", round);
 		}
 		ctx->last_rounds = (uint32_t)round;
-		delete relax_prof;
-		relax_prof = nullptr;
-		if (extra_blocked != MTD_M)
-			CU(cudaMemcpyAsync(ctx->blocked.p + extra_blocked, &prev_blocked, 1, cudaMemcpyHostToDevice, ctx->stream));
-		if (d_tiles)
 		{
 			ProfScope prof(ctx, MTD_K_BIG_DIRECTIONS);
-			k_directions<<<grid_blocks(ctx, ctx->T, 256), 256, 0, ctx->stream>>>(ctx->W, ctx->H, 0, ctx->H, d_dist, ctx->wpack.p, nullptr, nullptr, nullptr, d_tiles);
+			dim3 grid((unsigned)grid_blocks(ctx, ctx->T, 256, nlayers > 4 ? 2 : 8), (unsigned)nlayers);
+			k_big_finalize<<<grid, 256, 0, ctx->stream>>>(ctx->W, ctx->H, 0, ctx->H, d_dist, ctx->T, ctx->wpack.p, ctx->blocked.p, ctx->sources.p, nsrc, nullptr, nullptr, nullptr, d_tiles, ctx->T);
 			LAUNCHED();
 		}
 		if (extra_blocked != MTD_M)
-			CU(cudaStreamSynchronize(ctx->stream)); // prev_blocked lives on this stack frame
+		{
+			ctx->hflags->stage_blocked = prev_blocked;
+			CU(cudaMemcpyAsync(ctx->blocked.p + extra_blocked, &ctx->hflags->stage_blocked, 1, cudaMemcpyHostToDevice, ctx->stream));
+			CU(cudaStreamSynchronize(ctx->stream)); // the staging word is reused by the next call
+		}
 		return MTD_OK;
 	}
 
@@ -476,7 +484,7 @@ namespace
 			P.status = ctx->d_status.p;
 			return launch_waypoints_small(ctx, P);
 		}
-		return big_directions(ctx, sources, nsrc, extra_blocked, d_tiles, d_dist);
+		return big_layers(ctx, sources, 1, nsrc, extra_blocked, d_tiles, d_dist);
 	}
 
 	LayersView layers_view(mtd_ctx *ctx)
@@ -567,13 +575,10 @@ namespace
 		}
 		else
 		{
-			// large grid: one tiled relaxation per layer (layers are independent; the multi-GPU host shards them).
-			for (int l = 0; l < n; l++)
-			{
-				int rc = big_directions(ctx, wp_tiles + l, 1, MTD_M, ctx->ltiles.p + (size_t)l * ctx->T, ctx->ldist.p + (size_t)l * ctx->T);
-				if (rc)
-					return rc;
-			}
+			// large grid: all layers in one tiled relaxation (a work item is a (layer, tile) pair)
+			int rc = big_layers(ctx, wp_tiles, n, 1, MTD_M, ctx->ltiles.p, ctx->ldist.p);
+			if (rc)
+				return rc;
 		}
 		if (walks)
 		{
