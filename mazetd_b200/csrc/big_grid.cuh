@@ -30,6 +30,12 @@
 namespace mtd
 {
 	constexpr uint32_t BIG_SETTLE_LIMIT = MTD_GUARD - (1u << 17); // labels this close to the guard band are reported, not expanded
+#ifndef MTD_BIG_DELTA
+#define MTD_BIG_DELTA 255u
+#endif
+	// bucket width of the in-tile wavefront. 255 (= the minimum edge weight) settles only final labels; wider buckets take
+	// fewer rounds and re-relax a few labels (the engine re-queues every improvement, so any width is exact)
+	constexpr uint32_t BIG_DELTA = MTD_BIG_DELTA;
 
 	struct BigParams
 	{
@@ -137,6 +143,14 @@ namespace mtd
 		asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
 	}
 
+	// 4-byte variant (.ca is the only cache operator it has): used for the two apron columns. A line cached in L1 can
+	// be stale only against stores of the SAME round, and every such store re-activates this tile for the next round
+	// (a new kernel, L1 invalidated), so a stale read costs nothing but is never final.
+	__device__ __forceinline__ void cp_async_4(void *smem_dst, const void *gsrc)
+	{
+		asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+	}
+
 	__device__ __forceinline__ void cp_async_wait_all()
 	{
 		asm volatile("cp.async.wait_all;" ::: "memory");
@@ -215,14 +229,19 @@ namespace mtd
 						cp_async_16(sw + 1 + k, wrow + gx0 + 1 + k);
 					else
 						*reinterpret_cast<uint4 *>(sw + 1 + k) = make_uint4(0u, 0u, 0u, 0u);
-					// the two apron columns
-					if (lane < 2u)
+					// the two apron columns: lanes 0, 1 fetch the labels, lanes 2, 3 the weights (asynchronous as well: a
+					// synchronous load here would stall the warp once per frame row)
+					if (lane < 4u)
 					{
-						const int rx = lane == 0u ? 0 : RW - 1;
+						const int rx = (lane & 1u) ? RW - 1 : 0;
 						const int gx = gx0 + rx;
 						const bool in = gx >= 0 && gx < W;
-						sd[rx] = in ? __ldcg(drow + gx) : 0u;
-						sw[rx] = in && wrow ? wrow[gx] : 0u;
+						uint32_t *dst = lane < 2u ? sd + rx : sw + rx;
+						const uint32_t *src = lane < 2u ? drow : wrow;
+						if (in && src)
+							cp_async_4(dst, src + gx);
+						else
+							*dst = 0u;
 					}
 				}
 				else
@@ -370,7 +389,7 @@ namespace mtd
 			uint32_t par = 0;
 			while (dmin != MTD_INF && !overflow)
 			{
-				const uint32_t thr = dmin + MIN_EDGE;
+				const uint32_t thr = dmin + BIG_DELTA;
 				const uint16_t *rq = S.q[par];
 				uint16_t *wq = S.q[par ^ 1u];
 				uint32_t outn = 0, newmin = MTD_INF;
