@@ -5,10 +5,11 @@
 //   k_edge_weights   Grid::neighborDistance of every right/down edge, once per grid (sources/map/grid.cpp:141-145)
 //   k_big_init       distances := m, blocked tiles PARKED at 0 (paths.cpp:40-43, 65-67), work-list cleared
 //   k_big_seed       sources := 0 (paths.cpp:48-49), their tiles queued for round 0
-//   k_tile_round     one global round: every active 64x64 tile is staged with a 1-cell apron in shared memory by ONE
-//                    WARP (16-byte cp.async.cg rows, L2-coherent), relaxed to local convergence by a bucketed
-//                    wavefront (bucket width 255 = lower bound of every edge weight), written back with 16-byte
-//                    stores, and the tiles across any improved border line are queued for the next round
+//   k_tile_round     one global round: every active 64x64 tile is staged with a 1-cell apron in shared memory by one
+//                    4-warp CTA (16-byte cp.async.cg rows, L2-coherent), relaxed to local convergence by a bucketed
+//                    wavefront (measured: ~64 buckets per visit = the hop depth of a tile, whatever the bucket width),
+//                    written back with 16-byte stores, and the tiles across any improved border line are queued for
+//                    the next round
 //   k_round_advance  flips the double-buffered work-list
 //   k_big_finalize   tiles[v] from final distances (closed form of the heap order, see sssp_warp.cuh); parked blocked
 //                    tiles read m again
@@ -31,10 +32,11 @@ namespace mtd
 {
 	constexpr uint32_t BIG_SETTLE_LIMIT = MTD_GUARD - (1u << 17); // labels this close to the guard band are reported, not expanded
 #ifndef MTD_BIG_DELTA
-#define MTD_BIG_DELTA 255u
+#define MTD_BIG_DELTA 1024u
 #endif
 	// bucket width of the in-tile wavefront. 255 (= the minimum edge weight) settles only final labels; wider buckets take
-	// fewer rounds and re-relax a few labels (the engine re-queues every improvement, so any width is exact)
+	// fewer rounds and re-relax a few labels (the engine re-queues every improvement, so any width is exact).
+	// Measured on 4096^2 / 30 % walls / weights 255..570: 255 -> 72 buckets per visit, 1024 -> 64 (the hop depth).
 	constexpr uint32_t BIG_DELTA = MTD_BIG_DELTA;
 
 	struct BigParams
@@ -124,6 +126,21 @@ namespace mtd
 			*host_flag = P.count[(round + 1) & 1];
 	}
 
+#ifdef MTD_TIMING
+	// developer probe (never in the shipped build): cycles per phase of a tile visit, summed over all visits
+	__device__ unsigned long long g_big_timing[8];
+#define MTD_BTICK(k)                                                      \
+	do                                                                    \
+	{                                                                     \
+		const long long now__ = clock64();                                \
+		if (threadIdx.x == 0)                                             \
+			atomicAdd(&g_big_timing[k], (unsigned long long)(now__ - last__)); \
+		last__ = now__;                                                   \
+	} while (0)
+#else
+#define MTD_BTICK(k)
+#endif
+
 	// ---- one round ------------------------------------------------------------------------------------
 	template<int TS>
 	struct TileSmem
@@ -131,11 +148,14 @@ namespace mtd
 		static constexpr int RW = TS + 2;      // frame rows / columns (interior + apron)
 		static constexpr int PITCH = TS + 8;   // words per frame row; column rx lives at word rx + 3
 		static constexpr int CELLS = RW * PITCH;
-		static constexpr int QCAP = 1024;
+		static constexpr int QCAP = 2048;
 		uint32_t d[CELLS];        // labels
 		uint32_t w[CELLS];        // packed edge weights of the same cells
 		uint32_t edge_old[4][TS]; // top, bottom, left, right interior lines as loaded
 		uint16_t q[2][QCAP];      // pending cells (frame word index), double buffered
+		uint32_t tail[3], newmin[3]; // queue length / smallest pending label, rotating slots (see the engine)
+		uint32_t flags;           // bit 1: sweep changed something; bits 2..5: border line improved (top, bottom, left, right)
+		uint32_t item;
 	};
 
 	__device__ __forceinline__ void cp_async_16(void *smem_dst, const void *gsrc)
@@ -166,13 +186,16 @@ namespace mtd
 			P.list[(round + 1) & 1][atomicAdd(&P.count[(round + 1) & 1], 1u)] = item;
 	}
 
+	// One CTA of WARPS warps per (layer, tile) work item.
 	template<int TS, int WARPS>
 	__global__ void __launch_bounds__(WARPS * 32) k_tile_round(const BigParams P, int round)
 	{
 		extern __shared__ __align__(16) unsigned char smem_raw[];
 		using TSm = TileSmem<TS>;
-		TSm &S = ((TSm *)smem_raw)[threadIdx.x >> 5];
-		constexpr int RW = TSm::RW, PITCH = TSm::PITCH, QCAP = TSm::QCAP;
+		TSm &S = *(TSm *)smem_raw;
+		constexpr int RW = TSm::RW, PITCH = TSm::PITCH, QCAP = TSm::QCAP, NT = WARPS * 32;
+		const int tid = threadIdx.x;
+		const int warp = tid >> 5;
 		const uint32_t lane = lane_id();
 		const uint32_t lt = lanemask_lt();
 		const int W = P.W;
@@ -183,10 +206,11 @@ namespace mtd
 
 		for (;;)
 		{
-			uint32_t item = 0;
-			if (lane == 0)
-				item = atomicAdd(P.cursor, 1u);
-			item = __shfl_sync(FULL_MASK, item, 0);
+			__syncthreads(); // the previous item's shared memory is free
+			if (tid == 0)
+				S.item = atomicAdd(P.cursor, 1u);
+			__syncthreads();
+			const uint32_t item = S.item;
 			if (item >= count)
 				break;
 			const uint32_t it = list[item];
@@ -198,67 +222,95 @@ namespace mtd
 			uint32_t *ldist = P.dist + (size_t)layer * P.layer_stride;
 			const uint32_t *lsrc = P.sources + (size_t)layer * P.nsrc;
 			const bool full_w = P.aligned16 && gx0 + 1 + TS <= W; // the 64 interior columns are inside the grid and 16-byte aligned
+#ifdef MTD_TIMING
+			long long last__ = clock64();
+#endif
+			if (tid < 3)
+			{
+				S.tail[tid] = 0u;
+				S.newmin[tid] = MTD_INF;
+			}
+			if (tid == 0)
+				S.flags = 0u;
 
 			// ---- stage the frame: labels + packed weights. Cells outside the grid are parked at 0. ----
-			for (int ry = 0; ry < RW; ry++)
+			if (full_w && ly0 >= 0 && ly0 + RW <= Hl && gx0 >= 0 && gx0 + RW <= W)
 			{
-				const int ly = ly0 + ry; // local row; may be -1 or Hl (neighbour stripe or outside)
-				const uint32_t *drow = nullptr;
-				const uint32_t *wrow = nullptr;
-				if (ly >= 0 && ly < Hl)
+				// interior tile (the common case): no row or column tests. Per frame row 16 + 16 sixteen-byte copies
+				// (labels, weights) and 2 + 2 apron words; one warp instruction moves one row.
+				const int k = (int)(lane & 15u) * 4;
+				const uint32_t *src = (lane < 16u ? ldist : P.wpack) + (size_t)ly0 * W + gx0 + 1 + k;
+				uint32_t *dst = (lane < 16u ? S.d : S.w) + 4 + k;
+				const int rxa = (lane & 1u) ? RW - 1 : 0;
+				const uint32_t *asrc = ((lane & 2u) ? P.wpack : ldist) + (size_t)ly0 * W + gx0 + rxa;
+				uint32_t *adst = ((lane & 2u) ? S.w : S.d) + 3 + rxa;
+				for (int ry = warp; ry < RW; ry += WARPS)
 				{
-					drow = ldist + (size_t)ly * W;
-					wrow = P.wpack + (size_t)ly * W;
-				}
-				else if (ly < 0 && P.up_row)
-				{
-					drow = P.up_row;
-					wrow = P.up_wpack;
-				}
-				else if (ly >= Hl && P.down_row)
-					drow = P.down_row; // weights of the row below are never needed (edges are stored on the upper / left cell)
-				uint32_t *sd = S.d + ry * PITCH + 3;
-				uint32_t *sw = S.w + ry * PITCH + 3;
-				if (drow && full_w)
-				{
-					// 64 interior words = 16 x 16 bytes, L2-coherent (.cg); lanes 16..31 move the weights
-					const int k = (int)(lane & 15u) * 4;
-					if (lane < 16u)
-						cp_async_16(sd + 1 + k, drow + gx0 + 1 + k);
-					else if (wrow)
-						cp_async_16(sw + 1 + k, wrow + gx0 + 1 + k);
-					else
-						*reinterpret_cast<uint4 *>(sw + 1 + k) = make_uint4(0u, 0u, 0u, 0u);
-					// the two apron columns: lanes 0, 1 fetch the labels, lanes 2, 3 the weights (asynchronous as well: a
-					// synchronous load here would stall the warp once per frame row)
+					cp_async_16(dst + ry * PITCH, src + (size_t)ry * W);
 					if (lane < 4u)
-					{
-						const int rx = (lane & 1u) ? RW - 1 : 0;
-						const int gx = gx0 + rx;
-						const bool in = gx >= 0 && gx < W;
-						uint32_t *dst = lane < 2u ? sd + rx : sw + rx;
-						const uint32_t *src = lane < 2u ? drow : wrow;
-						if (in && src)
-							cp_async_4(dst, src + gx);
-						else
-							*dst = 0u;
-					}
+						cp_async_4(adst + ry * PITCH, asrc + (size_t)ry * W);
 				}
-				else
+			}
+			else
+			{
+				for (int ry = warp; ry < RW; ry += WARPS)
 				{
-					for (int rx = (int)lane; rx < RW; rx += 32)
+					const int ly = ly0 + ry; // local row; may be -1 or Hl (neighbour stripe or outside)
+					const uint32_t *drow = nullptr;
+					const uint32_t *wrow = nullptr;
+					if (ly >= 0 && ly < Hl)
 					{
-						const int gx = gx0 + rx;
-						const bool in = drow && gx >= 0 && gx < W;
-						sd[rx] = in ? __ldcg(drow + gx) : 0u;
-						sw[rx] = in && wrow ? wrow[gx] : 0u;
+						drow = ldist + (size_t)ly * W;
+						wrow = P.wpack + (size_t)ly * W;
+					}
+					else if (ly < 0 && P.up_row)
+					{
+						drow = P.up_row;
+						wrow = P.up_wpack;
+					}
+					else if (ly >= Hl && P.down_row)
+						drow = P.down_row; // weights of the row below are never needed (edges are stored on the upper / left cell)
+					uint32_t *sd = S.d + ry * PITCH + 3;
+					uint32_t *sw = S.w + ry * PITCH + 3;
+					if (drow && full_w)
+					{
+						const int k = (int)(lane & 15u) * 4;
+						if (lane < 16u)
+							cp_async_16(sd + 1 + k, drow + gx0 + 1 + k);
+						else if (wrow)
+							cp_async_16(sw + 1 + k, wrow + gx0 + 1 + k);
+						else
+							*reinterpret_cast<uint4 *>(sw + 1 + k) = make_uint4(0u, 0u, 0u, 0u);
+						if (lane < 4u)
+						{
+							const int rx = (lane & 1u) ? RW - 1 : 0;
+							const int gx = gx0 + rx;
+							const bool in = gx >= 0 && gx < W;
+							uint32_t *dst = lane < 2u ? sd + rx : sw + rx;
+							const uint32_t *src = lane < 2u ? drow : wrow;
+							if (in && src)
+								cp_async_4(dst, src + gx);
+							else
+								*dst = 0u;
+						}
+					}
+					else
+					{
+						for (int rx = (int)lane; rx < RW; rx += 32)
+						{
+							const int gx = gx0 + rx;
+							const bool in = drow && gx >= 0 && gx < W;
+							sd[rx] = in ? __ldcg(drow + gx) : 0u;
+							sw[rx] = in && wrow ? wrow[gx] : 0u;
+						}
 					}
 				}
 			}
 			cp_async_wait_all();
-			__syncwarp();
+			__syncthreads();
+			MTD_BTICK(0);
 			// remember the interior border lines to detect changes
-			for (int i = (int)lane; i < TS; i += 32)
+			for (int i = tid; i < TS; i += NT)
 			{
 				S.edge_old[0][i] = S.d[1 * PITCH + 4 + i];
 				S.edge_old[1][i] = S.d[TS * PITCH + 4 + i];
@@ -267,10 +319,11 @@ namespace mtd
 			}
 
 			// ---- seeds ----
-			// Pending cells enter q[0] with ballot compaction. A label lowered here or later is appended every time it
-			// improves (duplicates are harmless: the second visit relaxes nothing).
-			uint32_t nq = 0, dmin = MTD_INF;
-			bool overflow = false, guard = false;
+			// Pending cells enter q[0]. A label lowered here or later is appended every time it improves (duplicates are
+			// harmless: the second visit relaxes nothing). Appends: ballot compaction per warp, one shared-memory atomicAdd
+			// on the tail per warp instruction.
+			uint32_t my_min = MTD_INF;
+			bool guard = false;
 			auto relax_into = [&](bool want, uint32_t v, uint32_t nd)
 			{
 				// want: this lane has a candidate label nd for interior cell v
@@ -280,42 +333,57 @@ namespace mtd
 				else if (want)
 					improved = nd < atomicMin(&S.d[v], nd);
 				const uint32_t bal = __ballot_sync(FULL_MASK, improved);
-				if (improved)
+				if (bal)
 				{
-					const uint32_t slot = nq + __popc(bal & lt);
-					if (slot < (uint32_t)QCAP)
-						S.q[0][slot] = (uint16_t)v;
-					dmin = min(dmin, nd);
+					uint32_t base = 0;
+					if (lane == 0)
+						base = atomicAdd(&S.tail[0], (uint32_t)__popc(bal));
+					base = __shfl_sync(FULL_MASK, base, 0);
+					if (improved)
+					{
+						const uint32_t slot = base + __popc(bal & lt);
+						if (slot < (uint32_t)QCAP)
+							S.q[0][slot] = (uint16_t)v;
+						my_min = min(my_min, nd);
+					}
 				}
-				nq += (uint32_t)__popc(bal);
 			};
 			// (1) apron: every finite, non-parked apron label relaxes its single interior neighbour; a label of 0 is a
-			//     parked cell unless the source list says otherwise, so sources on the apron are handled from the list
-			for (int i0 = 0; i0 < TS; i0 += 32)
+			//     parked cell unless the source list says otherwise, so sources on the apron are handled from the list.
+			//     4 sides x TS cells, one candidate per thread and step.
+			for (int j0 = warp * 32; j0 < 4 * TS; j0 += NT)
 			{
-				const int i = i0 + (int)lane;
+				const int j = j0 + (int)lane;
+				const int side = j / TS, i = j - side * TS; // warp-uniform side (TS is a multiple of 32)
+				uint32_t a, v, wsel;
+				if (side == 0)
 				{
-					const uint32_t a = (uint32_t)(0 * PITCH + 4 + i), v = a + PITCH; // top
-					const uint32_t da = S.d[a];
-					relax_into(da != 0u && da != MTD_INF, v, da + MIN_EDGE + (S.w[a] >> 16));
+					a = (uint32_t)(0 * PITCH + 4 + i); // top
+					v = a + PITCH;
+					wsel = S.w[a] >> 16;
 				}
+				else if (side == 1)
 				{
-					const uint32_t a = (uint32_t)((TS + 1) * PITCH + 4 + i), v = a - PITCH; // bottom
-					const uint32_t da = S.d[a];
-					relax_into(da != 0u && da != MTD_INF, v, da + MIN_EDGE + (S.w[v] >> 16));
+					a = (uint32_t)((TS + 1) * PITCH + 4 + i); // bottom
+					v = a - PITCH;
+					wsel = S.w[v] >> 16;
 				}
+				else if (side == 2)
 				{
-					const uint32_t a = (uint32_t)((1 + i) * PITCH + 3), v = a + 1u; // left
-					const uint32_t da = S.d[a];
-					relax_into(da != 0u && da != MTD_INF, v, da + MIN_EDGE + (S.w[a] & 0xFFFFu));
+					a = (uint32_t)((1 + i) * PITCH + 3); // left
+					v = a + 1u;
+					wsel = S.w[a] & 0xFFFFu;
 				}
+				else
 				{
-					const uint32_t a = (uint32_t)((1 + i) * PITCH + 4 + TS), v = a - 1u; // right
-					const uint32_t da = S.d[a];
-					relax_into(da != 0u && da != MTD_INF, v, da + MIN_EDGE + (S.w[v] & 0xFFFFu));
+					a = (uint32_t)((1 + i) * PITCH + 4 + TS); // right
+					v = a - 1u;
+					wsel = S.w[v] & 0xFFFFu;
 				}
+				const uint32_t da = S.d[a];
+				relax_into(da != 0u && da != MTD_INF, v, da + MIN_EDGE + wsel);
 			}
-			for (int s0 = 0; s0 < P.nsrc; s0 += 32)
+			for (int s0 = warp * 32; s0 < P.nsrc; s0 += NT)
 			{
 				const int s = s0 + (int)lane;
 				bool want = false;
@@ -353,47 +421,73 @@ namespace mtd
 				}
 				relax_into(want, v, nd);
 			}
-			__syncwarp();
+			__syncthreads();
 			// (2) park the apron: nothing is relaxed outward, and interior cells need no bounds test
-			for (int i = (int)lane; i < TS; i += 32)
+			for (int i = tid; i < TS; i += NT)
 			{
 				S.d[0 * PITCH + 4 + i] = 0u;
 				S.d[(TS + 1) * PITCH + 4 + i] = 0u;
 				S.d[(1 + i) * PITCH + 3] = 0u;
 				S.d[(1 + i) * PITCH + 4 + TS] = 0u;
 			}
-			__syncwarp();
+			__syncthreads();
 			// (3) sources inside the tile expand from label 0 (also when they are blocked: paths.cpp:63-67 test only the neighbour)
-			for (int s0 = 0; s0 < P.nsrc; s0 += 32)
+			for (int s0 = warp * 32; s0 < P.nsrc; s0 += NT)
 			{
 				const int s = s0 + (int)lane;
 				bool want = false;
-				uint32_t c = 0;
+				uint32_t c = (uint32_t)(PITCH + 4);
 				if (s < P.nsrc)
 				{
 					const uint32_t src = lsrc[s];
 					const int rx = (int)(src % (uint32_t)W) - gx0, ry = (int)(src / (uint32_t)W) - P.y0 - ly0;
 					want = rx >= 1 && rx <= TS && ry >= 1 && ry <= TS;
-					c = want ? (uint32_t)(ry * PITCH + rx + 3) : (uint32_t)(PITCH + 4);
+					if (want)
+						c = (uint32_t)(ry * PITCH + rx + 3);
 				}
 				relax_into(want, c - PITCH, MIN_EDGE + (S.w[c - PITCH] >> 16));
 				relax_into(want, c - 1u, MIN_EDGE + (S.w[c - 1u] & 0xFFFFu));
 				relax_into(want, c + 1u, MIN_EDGE + (S.w[c] & 0xFFFFu));
 				relax_into(want, c + PITCH, MIN_EDGE + (S.w[c] >> 16));
 			}
-			overflow = nq > (uint32_t)QCAP;
-			dmin = warp_min_u32(dmin);
-			__syncwarp();
-
-			// ---- bucketed wavefront on the frame (label-correcting across visits, Dijkstra order within one) ----
-			uint32_t par = 0;
-			while (dmin != MTD_INF && !overflow)
+			my_min = warp_min_u32(my_min);
+			if (lane == 0 && my_min != MTD_INF)
+				atomicMin(&S.newmin[0], my_min);
+			__syncthreads();
+			MTD_BTICK(1);
+			// ---- bucketed wavefront on the frame (label-correcting across visits and inside wide buckets) ----
+			// Control words rotate through three slots: round r reads slot r % 3, appends to (r + 1) % 3 and clears
+			// (r + 2) % 3, so one barrier per round is enough.
+			uint32_t si = 0, par = 0;
+			bool overflow = false;
+			for (;;)
 			{
+				const uint32_t nq = S.tail[si], dmin = S.newmin[si];
+				if (nq > (uint32_t)QCAP)
+				{
+					overflow = true;
+					break;
+				}
+				if (nq == 0u || dmin == MTD_INF)
+					break;
+				const uint32_t so = si == 2u ? 0u : si + 1u, sr = so == 2u ? 0u : so + 1u;
+				if (tid == 0)
+				{
+					S.tail[sr] = 0u;
+					S.newmin[sr] = MTD_INF;
+				}
 				const uint32_t thr = dmin + BIG_DELTA;
 				const uint16_t *rq = S.q[par];
 				uint16_t *wq = S.q[par ^ 1u];
-				uint32_t outn = 0, newmin = MTD_INF;
-				for (uint32_t base = 0; base < nq; base += 32u)
+				uint32_t newmin = MTD_INF;
+#ifdef MTD_TIMING
+				if (tid == 0)
+				{
+					atomicAdd(&g_big_timing[5], 1ull);
+					atomicAdd(&g_big_timing[6], (unsigned long long)nq);
+				}
+#endif
+				for (uint32_t base = (uint32_t)warp * 32u; base < nq; base += (uint32_t)NT)
 				{
 					const uint32_t idx = base + lane;
 					const bool active = idx < nq;
@@ -432,42 +526,55 @@ namespace mtd
 					const uint32_t b1 = __ballot_sync(FULL_MASK, i1);
 					const uint32_t b2 = __ballot_sync(FULL_MASK, i2);
 					const uint32_t b3 = __ballot_sync(FULL_MASK, i3);
-					uint32_t pos = outn + __popc(bk & lt);
-					if (keep && pos < (uint32_t)QCAP)
-						wq[pos] = (uint16_t)c;
-					outn += __popc(bk);
-					pos = outn + __popc(b0 & lt);
-					if (i0 && pos < (uint32_t)QCAP)
-						wq[pos] = (uint16_t)(c - PITCH);
-					outn += __popc(b0);
-					pos = outn + __popc(b1 & lt);
-					if (i1 && pos < (uint32_t)QCAP)
-						wq[pos] = (uint16_t)(c - 1u);
-					outn += __popc(b1);
-					pos = outn + __popc(b2 & lt);
-					if (i2 && pos < (uint32_t)QCAP)
-						wq[pos] = (uint16_t)(c + 1u);
-					outn += __popc(b2);
-					pos = outn + __popc(b3 & lt);
-					if (i3 && pos < (uint32_t)QCAP)
-						wq[pos] = (uint16_t)(c + PITCH);
-					outn += __popc(b3);
+					const uint32_t ck = __popc(bk), c0n = __popc(b0), c1n = __popc(b1), c2n = __popc(b2), c3n = __popc(b3);
+					const uint32_t total = ck + c0n + c1n + c2n + c3n;
+					if (total)
+					{
+						uint32_t pos = 0;
+						if (lane == 0)
+							pos = atomicAdd(&S.tail[so], total);
+						pos = __shfl_sync(FULL_MASK, pos, 0);
+						uint32_t p = pos + __popc(bk & lt);
+						if (keep && p < (uint32_t)QCAP)
+							wq[p] = (uint16_t)c;
+						pos += ck;
+						p = pos + __popc(b0 & lt);
+						if (i0 && p < (uint32_t)QCAP)
+							wq[p] = (uint16_t)(c - PITCH);
+						pos += c0n;
+						p = pos + __popc(b1 & lt);
+						if (i1 && p < (uint32_t)QCAP)
+							wq[p] = (uint16_t)(c - 1u);
+						pos += c1n;
+						p = pos + __popc(b2 & lt);
+						if (i2 && p < (uint32_t)QCAP)
+							wq[p] = (uint16_t)(c + 1u);
+						pos += c2n;
+						p = pos + __popc(b3 & lt);
+						if (i3 && p < (uint32_t)QCAP)
+							wq[p] = (uint16_t)(c + PITCH);
+					}
 				}
-				overflow = outn > (uint32_t)QCAP;
-				nq = outn;
-				dmin = warp_min_u32(newmin);
+				newmin = warp_min_u32(newmin);
+				if (lane == 0 && newmin != MTD_INF)
+					atomicMin(&S.newmin[so], newmin);
+				__syncthreads();
+				si = so;
 				par ^= 1u;
-				__syncwarp();
 			}
+			MTD_BTICK(2);
 			if (overflow)
 			{
 				// the pending set outgrew the queue (pathological frontiers): queue-less sweeps to the local fixpoint.
 				// Parked cells hold 0 and never expand; sources expanded in (3) before anything could overflow.
-				bool changed = true;
-				while (changed)
+				for (;;)
 				{
-					changed = false;
-					for (int i = (int)lane; i < TS * TS; i += 32)
+					__syncthreads();
+					if (tid == 0)
+						S.flags &= ~2u;
+					__syncthreads();
+					bool changed = false;
+					for (int i = tid; i < TS * TS; i += NT)
 					{
 						const uint32_t c = (uint32_t)((1 + i / TS) * PITCH + 4 + i % TS);
 						const uint32_t d = S.d[c];
@@ -486,24 +593,28 @@ namespace mtd
 						changed |= n2 < atomicMin(&S.d[c + 1u], n2);
 						changed |= n3 < atomicMin(&S.d[c + PITCH], n3);
 					}
-					changed = __any_sync(FULL_MASK, changed);
+					if (changed)
+						atomicOr(&S.flags, 2u);
+					__syncthreads();
+					if (!(S.flags & 2u))
+						break;
 				}
 			}
-			if (__any_sync(FULL_MASK, guard) && lane == 0)
+			if (guard)
 				atomicOr(P.status, 1);
-			__syncwarp();
+			__syncthreads();
 
 			// ---- write back the interior (labels only ever decrease; parked and unreached cells rewrite their own value) ----
 			if (full_w)
 			{
-				// two rows per instruction, 16 bytes per lane
-				for (int r2 = 0; r2 < TS; r2 += 2)
+				// NT / 16 rows per instruction, 16 bytes per lane
+				for (int r0 = 0; r0 < TS; r0 += NT / 16)
 				{
-					const int iy = r2 + (int)(lane >> 4);
+					const int iy = r0 + (tid >> 4);
 					const int ly = ly0 + 1 + iy;
-					if (ly < Hl)
+					if (iy < TS && ly < Hl)
 					{
-						const int k = (int)(lane & 15u) * 4;
+						const int k = (tid & 15) * 4;
 						const uint4 v = *reinterpret_cast<const uint4 *>(S.d + (1 + iy) * PITCH + 4 + k);
 						__stcg(reinterpret_cast<uint4 *>(ldist + (size_t)ly * W + gx0 + 1 + k), v);
 					}
@@ -511,7 +622,7 @@ namespace mtd
 			}
 			else
 			{
-				for (int iy = 0; iy < TS; iy++)
+				for (int iy = warp; iy < TS; iy += WARPS)
 				{
 					const int ly = ly0 + 1 + iy;
 					if (ly >= Hl)
@@ -521,41 +632,46 @@ namespace mtd
 							__stcg(ldist + (size_t)ly * W + gx0 + 1 + ix, S.d[(1 + iy) * PITCH + 4 + ix]);
 				}
 			}
+			MTD_BTICK(3);
 			// ---- activate neighbours across improved border lines ----
-			bool ch[4] = { false, false, false, false };
-			for (int i = (int)lane; i < TS; i += 32)
 			{
-				ch[0] |= S.d[1 * PITCH + 4 + i] != S.edge_old[0][i];
-				ch[1] |= S.d[TS * PITCH + 4 + i] != S.edge_old[1][i];
-				ch[2] |= S.d[(1 + i) * PITCH + 4] != S.edge_old[2][i];
-				ch[3] |= S.d[(1 + i) * PITCH + 3 + TS] != S.edge_old[3][i];
+				uint32_t ch = 0;
+				for (int i = tid; i < TS; i += NT)
+				{
+					ch |= S.d[1 * PITCH + 4 + i] != S.edge_old[0][i] ? 4u : 0u;
+					ch |= S.d[TS * PITCH + 4 + i] != S.edge_old[1][i] ? 8u : 0u;
+					ch |= S.d[(1 + i) * PITCH + 4] != S.edge_old[2][i] ? 16u : 0u;
+					ch |= S.d[(1 + i) * PITCH + 3 + TS] != S.edge_old[3][i] ? 32u : 0u;
+				}
+				if (ch)
+					atomicOr(&S.flags, ch);
 			}
-			const bool c0 = __any_sync(FULL_MASK, ch[0]), c1 = __any_sync(FULL_MASK, ch[1]);
-			const bool c2 = __any_sync(FULL_MASK, ch[2]), c3 = __any_sync(FULL_MASK, ch[3]);
-			if (lane == 0)
+			__syncthreads();
+			if (tid == 0)
 			{
+				const uint32_t f = S.flags;
 				__threadfence(); // distances are visible before the neighbour can be scheduled
-				if (c0)
+				if (f & 4u)
 				{
 					if (ty > 0)
 						activate_item(P, layer, tx, ty - 1, round);
 					else if (P.peer_flag_up)
 						P.peer_flag_up[tx] = 1u;
 				}
-				if (c1)
+				if (f & 8u)
 				{
 					if (ty < P.tilesY - 1)
 						activate_item(P, layer, tx, ty + 1, round);
 					else if (P.peer_flag_down)
 						P.peer_flag_down[tx] = 1u;
 				}
-				if (c2)
+				if (f & 16u)
 					activate_item(P, layer, tx - 1, ty, round);
-				if (c3)
+				if (f & 32u)
 					activate_item(P, layer, tx + 1, ty, round);
 				atomicAdd(P.total_active, 1u);
 			}
-			__syncwarp();
+			MTD_BTICK(4);
 		}
 	}
 

@@ -27,7 +27,7 @@ namespace
 {
 	constexpr size_t MAX_SMEM = 227 * 1024 - 1024; // dynamic budget: the opt-in limit is 227 KB per CTA including static __shared__
 	constexpr int BIG_TS = 64;
-	constexpr int BIG_WARPS = 1;
+	constexpr int BIG_WARPS = 4; // warps of the CTA that owns one (layer, tile) work item
 
 	template<class T>
 	struct DevBuf
@@ -64,6 +64,7 @@ namespace
 		uint32_t alive;
 		unsigned long long damage;
 		uint32_t spawn[3];
+		uint32_t big_items;     // (layer, tile) visits of the last tiled relaxation (statistics)
 		uint32_t stage_blocked; // pinned staging word of the trial grid's extra blocked tile
 	};
 }
@@ -346,7 +347,7 @@ namespace
 	int big_layers(mtd_ctx *ctx, const uint32_t *h_sources, int nlayers, int nsrc, uint32_t extra_blocked, uint32_t *d_tiles, uint32_t *d_dist)
 	{
 		using TSm = TileSmem<BIG_TS>;
-		const size_t smem = sizeof(TSm) * BIG_WARPS;
+		const size_t smem = sizeof(TSm);
 		static bool configured = false;
 		if (!configured)
 		{
@@ -433,6 +434,17 @@ namespace
 			}
 		}
 		ctx->last_rounds = (uint32_t)round;
+		CU(cudaMemcpyAsync(&ctx->hflags->big_items, P.total_active, 4, cudaMemcpyDeviceToHost, ctx->stream));
+#ifdef MTD_TIMING
+		{
+			unsigned long long t[8], z[8] = { 0 };
+			cudaMemcpyFromSymbol(t, g_big_timing, sizeof(t));
+			cudaMemcpyToSymbol(g_big_timing, z, sizeof(z));
+			cudaStreamSynchronize(ctx->stream);
+			const double v = (double)ctx->hflags->big_items;
+			printf("BIGTIMING rounds=%d visits=%.0f | per visit cycles: stage=%.0f seed=%.0f engine=%.0f writeback=%.0f activate=%.0f | buckets/visit=%.1f cells/bucket=%.1f\n", round, v, t[0] / v, t[1] / v, t[2] / v, t[3] / v, t[4] / v, t[5] / v, t[5] ? (double)t[6] / t[5] : 0.0);
+		}
+#endif
 		{
 			ProfScope prof(ctx, MTD_K_BIG_DIRECTIONS);
 			dim3 grid((unsigned)grid_blocks(ctx, ctx->T, 256, nlayers > 4 ? 2 : 8), (unsigned)nlayers);
@@ -944,7 +956,16 @@ extern "C" int mtd_waypoints_update_dev(mtd_ctx *ctx, const uint32_t *wp_tiles, 
 	DeviceGuard g(ctx->device);
 	if (n > 0 && !wp_tiles)
 		return fail(ctx, MTD_ERR_ARG, "null waypoint list");
-	return waypoints_dev(ctx, wp_tiles, n, ctx->fp_cap ? ctx->fp_cap : 4096u);
+	// device-resident variant: the path buffers are library-owned; size them for long detours (8 x the half perimeter
+	// per visited waypoint), never below the 4096 entries the game-sized maps use
+	size_t cap = (size_t)8 * (size_t)(ctx->W + ctx->H) * (size_t)(n > 0 ? n : 1);
+	if (cap < 4096)
+		cap = 4096;
+	if (cap > ctx->T)
+		cap = ctx->T;
+	if (ctx->fp_cap > cap)
+		cap = ctx->fp_cap;
+	return waypoints_dev(ctx, wp_tiles, n, (uint32_t)cap);
 }
 
 extern "C" int mtd_waypoints_update(mtd_ctx *ctx, const uint32_t *wp_tiles, int32_t n, uint32_t *tiles_out, uint32_t *dist_out, uint32_t *fullpath_buf, uint32_t fullpath_cap, uint32_t *fullpath_len, uint32_t *full_distance, uint32_t *agg3)
