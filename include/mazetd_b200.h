@@ -102,6 +102,32 @@ int mtd_edge_weights(mtd_ctx *ctx, uint32_t *right, uint32_t *down);
 int mtd_directions_update(mtd_ctx *ctx, const uint32_t *sources, int32_t nsrc, uint32_t extra_blocked, uint32_t *tiles_out, uint32_t *dist_out);
 int mtd_directions_update_dev(mtd_ctx *ctx, const uint32_t *sources /* host */, int32_t nsrc, uint32_t extra_blocked, uint32_t *d_tiles, uint32_t *d_dist);
 
+/* n independent Directions (one target tile each) over the uploaded grid -- what Waypoints::update hands to
+ * tasksRunBlocking (sources/map/paths.cpp:82-85, 119) without the path walks. d_tiles (may be NULL) / d_dist = [n][W*H],
+ * device. On large grids all layers are relaxed together. This is the unit dealt to the GPUs when layers are sharded. */
+int mtd_directions_layers_dev(mtd_ctx *ctx, const uint32_t *targets /* host */, int32_t n, uint32_t *d_tiles, uint32_t *d_dist);
+
+/* ---- Directions::update of ONE large grid split into row stripes, one context (one GPU) per stripe --------
+ * (no reference counterpart beyond sources/map/paths.cpp:24-78 itself: the reference is single-threaded per layer;
+ * this is the partitioning of SURVEY.md 8e for the 16384^2 configuration.)
+ * A stripe owns rows [y0, y1) of a W x H grid. elev_rows / flags_rows hold rows [max(y0-1, 0), min(y1+1, H)), i.e. the
+ * owned rows plus one halo row on each inner side (needed for the edge weights across the cut).
+ * Protocol, identical on every rank (mazetd_b200/striped.py drives it over torch.distributed):
+ *   mtd_stripe_begin_dev(sources = ALL sources as global tile ids, d_dist = [y1-y0][W])   relax locally
+ *   repeat { send own first / last row of d_dist to the ranks above / below; receive theirs;
+ *            mtd_stripe_exchange_dev(row_above, row_below, &improved) }                  merge halos, relax again
+ *   until the sum of `improved` over all ranks is 0 (one all-reduce per sweep)
+ *   mtd_stripe_finalize_dev(d_tiles)                                                      next hops, GLOBAL tile ids
+ * While the protocol runs, blocked tiles of d_dist read 0 (parked); finalize rewrites them to MTD_M.
+ * The distance fixpoint is unique, so the result is bit-identical to one Directions::update over the whole grid. */
+int mtd_stripe_upload(mtd_ctx *ctx, int32_t W, int32_t H, int32_t y0, int32_t y1, const int16_t *elev_rows, const uint16_t *flags_rows);
+int mtd_stripe_upload_dev(mtd_ctx *ctx, int32_t W, int32_t H, int32_t y0, int32_t y1, const int16_t *d_elev_rows, const uint16_t *d_flags_rows);
+int mtd_stripe_begin_dev(mtd_ctx *ctx, const uint32_t *sources /* host */, int32_t nsrc, uint32_t *d_dist);
+/* d_row_above = current row y0-1 of the rank above (device, [W]) or NULL at the top; d_row_below likewise row y1.
+ * *improved_out = halo cells whose label dropped (0 on every rank = converged). Synchronous. */
+int mtd_stripe_exchange_dev(mtd_ctx *ctx, const uint32_t *d_row_above, const uint32_t *d_row_below, uint32_t *improved_out);
+int mtd_stripe_finalize_dev(mtd_ctx *ctx, uint32_t *d_tiles);
+
 /* ---- Waypoints::update (sources/map/paths.cpp:82-139) ------------------------------------------ */
 /* n Dijkstra layers + n full-path walks + aggregates, one call.
  *   tiles_out, dist_out : [n][W*H]            (may be NULL)

@@ -16,7 +16,8 @@ EXPORTS = [
     "mtd_create", "mtd_destroy", "mtd_last_error", "mtd_version", "mtd_synchronize", "mtd_launch_count",
     "mtd_profile_enable", "mtd_profile_read", "mtd_debug_set",
     "mtd_grid_upload", "mtd_grid_upload_dev", "mtd_grid_set_flags", "mtd_neighbor_distances", "mtd_edge_weights",
-    "mtd_directions_update", "mtd_directions_update_dev",
+    "mtd_directions_update", "mtd_directions_update_dev", "mtd_directions_layers_dev",
+    "mtd_stripe_upload", "mtd_stripe_upload_dev", "mtd_stripe_begin_dev", "mtd_stripe_exchange_dev", "mtd_stripe_finalize_dev",
     "mtd_waypoints_update", "mtd_waypoints_update_dev", "mtd_waypoints_find", "mtd_waypoints_layers_dev",
     "mtd_placing_blocks",
     "mtd_mapgen_batch", "mtd_mapgen_batch_dev", "mtd_elevation_samples",
@@ -65,6 +66,12 @@ def load():
     L.mtd_edge_weights.argtypes = [vp, vp, vp]
     L.mtd_directions_update.argtypes = [vp, vp, i32, u32, vp, vp]
     L.mtd_directions_update_dev.argtypes = [vp, vp, i32, u32, vp, vp]
+    L.mtd_directions_layers_dev.argtypes = [vp, vp, i32, vp, vp]
+    L.mtd_stripe_upload.argtypes = [vp, i32, i32, i32, i32, vp, vp]
+    L.mtd_stripe_upload_dev.argtypes = [vp, i32, i32, i32, i32, vp, vp]
+    L.mtd_stripe_begin_dev.argtypes = [vp, vp, i32, vp]
+    L.mtd_stripe_exchange_dev.argtypes = [vp, vp, vp, C.POINTER(u32)]
+    L.mtd_stripe_finalize_dev.argtypes = [vp, vp]
     L.mtd_waypoints_update.argtypes = [vp, vp, i32, vp, vp, vp, u32, vp, vp, vp]
     L.mtd_waypoints_update_dev.argtypes = [vp, vp, i32]
     L.mtd_waypoints_find.argtypes = [vp, vp, vp, i32, vp, vp]
@@ -186,6 +193,39 @@ class Context:
     def directions_update_dev(self, sources, d_tiles, d_dist, extra_blocked=M):
         src = np.ascontiguousarray(np.atleast_1d(sources), np.uint32)
         self._ck(self.L.mtd_directions_update_dev(self.h, _p(src), len(src), int(extra_blocked), _p(d_tiles), _p(d_dist)))
+
+    def layers_update_dev(self, targets, d_tiles, d_dist):
+        """n independent single-target Directions layers, device outputs [n][T]"""
+        t = np.ascontiguousarray(np.atleast_1d(targets), np.uint32)
+        self._ck(self.L.mtd_directions_layers_dev(self.h, _p(t), len(t), _p(d_tiles), _p(d_dist)))
+
+    # ---- row stripes of one large grid (one Context per stripe / GPU) ----
+    def stripe_upload(self, W, H, y0, y1, elev_rows, flags_rows):
+        """elev_rows / flags_rows: host arrays of rows [max(y0-1,0), min(y1+1,H)) of the full grid"""
+        elev_rows = np.ascontiguousarray(elev_rows, np.int16)
+        flags_rows = np.ascontiguousarray(flags_rows, np.uint16)
+        rows = (y1 - y0) + (1 if y0 > 0 else 0) + (1 if y1 < H else 0)
+        assert elev_rows.size == rows * W and flags_rows.size == rows * W
+        self._ck(self.L.mtd_stripe_upload(self.h, W, H, y0, y1, _p(elev_rows), _p(flags_rows)))
+        self.W, self.H, self.T = W, y1 - y0, W * (y1 - y0)
+
+    def stripe_upload_dev(self, W, H, y0, y1, d_elev_rows, d_flags_rows):
+        self._ck(self.L.mtd_stripe_upload_dev(self.h, W, H, y0, y1, _p(d_elev_rows), _p(d_flags_rows)))
+        self.W, self.H, self.T = W, y1 - y0, W * (y1 - y0)
+
+    def stripe_begin_dev(self, sources, d_dist):
+        src = np.ascontiguousarray(np.atleast_1d(sources), np.uint32)
+        self._ck(self.L.mtd_stripe_begin_dev(self.h, _p(src), len(src), _p(d_dist)))
+
+    def stripe_exchange_dev(self, d_row_above, d_row_below):
+        """merge the neighbours' boundary rows (device pointers or None) and relax again; returns the number of
+        halo cells whose label dropped"""
+        n = C.c_uint32(0)
+        self._ck(self.L.mtd_stripe_exchange_dev(self.h, _p(d_row_above), _p(d_row_below), C.byref(n)))
+        return int(n.value)
+
+    def stripe_finalize_dev(self, d_tiles):
+        self._ck(self.L.mtd_stripe_finalize_dev(self.h, _p(d_tiles)))
 
     # ---- Waypoints::update ----
     def waypoints_update(self, wp_tiles, cap=None, want_layers=True):

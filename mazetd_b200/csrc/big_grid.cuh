@@ -222,6 +222,7 @@ namespace mtd
 			uint32_t *ldist = P.dist + (size_t)layer * P.layer_stride;
 			const uint32_t *lsrc = P.sources + (size_t)layer * P.nsrc;
 			const bool full_w = P.aligned16 && gx0 + 1 + TS <= W; // the 64 interior columns are inside the grid and 16-byte aligned
+			const int brow = min(TS + 1, Hl - ly0); // frame row just below the tile's last row that exists in this stripe
 #ifdef MTD_TIMING
 			long long last__ = clock64();
 #endif
@@ -268,7 +269,7 @@ namespace mtd
 						drow = P.up_row;
 						wrow = P.up_wpack;
 					}
-					else if (ly >= Hl && P.down_row)
+					else if (ly == Hl && P.down_row)
 						drow = P.down_row; // weights of the row below are never needed (edges are stored on the upper / left cell)
 					uint32_t *sd = S.d + ry * PITCH + 3;
 					uint32_t *sw = S.w + ry * PITCH + 3;
@@ -364,7 +365,7 @@ namespace mtd
 				}
 				else if (side == 1)
 				{
-					a = (uint32_t)((TS + 1) * PITCH + 4 + i); // bottom
+					a = (uint32_t)(brow * PITCH + 4 + i); // bottom (the stripe's halo row when the tile is cut short)
 					v = a - PITCH;
 					wsel = S.w[v] >> 16;
 				}
@@ -426,7 +427,7 @@ namespace mtd
 			for (int i = tid; i < TS; i += NT)
 			{
 				S.d[0 * PITCH + 4 + i] = 0u;
-				S.d[(TS + 1) * PITCH + 4 + i] = 0u;
+				S.d[brow * PITCH + 4 + i] = 0u;
 				S.d[(1 + i) * PITCH + 3] = 0u;
 				S.d[(1 + i) * PITCH + 4 + TS] = 0u;
 			}
@@ -639,9 +640,12 @@ namespace mtd
 				for (int i = tid; i < TS; i += NT)
 				{
 					ch |= S.d[1 * PITCH + 4 + i] != S.edge_old[0][i] ? 4u : 0u;
-					ch |= S.d[TS * PITCH + 4 + i] != S.edge_old[1][i] ? 8u : 0u;
-					ch |= S.d[(1 + i) * PITCH + 4] != S.edge_old[2][i] ? 16u : 0u;
-					ch |= S.d[(1 + i) * PITCH + 3 + TS] != S.edge_old[3][i] ? 32u : 0u;
+					ch |= (TS < brow && S.d[TS * PITCH + 4 + i] != S.edge_old[1][i]) ? 8u : 0u;
+					if (1 + i < brow) // rows below a cut-short tile hold the parked halo / nothing
+					{
+						ch |= S.d[(1 + i) * PITCH + 4] != S.edge_old[2][i] ? 16u : 0u;
+						ch |= S.d[(1 + i) * PITCH + 3 + TS] != S.edge_old[3][i] ? 32u : 0u;
+					}
 				}
 				if (ch)
 					atomicOr(&S.flags, ch);
@@ -672,6 +676,44 @@ namespace mtd
 				atomicAdd(P.total_active, 1u);
 			}
 			MTD_BTICK(4);
+		}
+	}
+
+	// ---- row stripes (one rank per stripe) ------------------------------------------------------------------
+	// Sources on the halo rows (y0-1 and y1) belong to the neighbour stripes, but their first hop lands here: queue the
+	// border tile under / over them for round 0 (the visit finds them through the source list).
+	template<int TS>
+	__global__ void k_stripe_seed_halo(const BigParams P)
+	{
+		const int s = blockIdx.x * blockDim.x + threadIdx.x;
+		if (s >= P.nsrc)
+			return;
+		const uint32_t src = P.sources[s];
+		const int x = (int)(src % (uint32_t)P.W), y = (int)(src / (uint32_t)P.W);
+		if (y == P.y0 - 1)
+			activate_item(P, 0, x / TS, 0, -1);
+		else if (y == P.y1)
+			activate_item(P, 0, x / TS, P.tilesY - 1, -1);
+	}
+
+	// A boundary row arrived from the neighbour stripe: keep the smaller label per column in the local halo copy and queue
+	// the border tiles of the improved columns for round `round`. A label of 0 is a parked blocked tile or a source of the
+	// neighbour (sources are handled from the list), never an improvement.
+	template<int TS>
+	__global__ void k_stripe_merge(const BigParams P, uint32_t *__restrict__ halo, const uint32_t *__restrict__ incoming, int ty, int round, uint32_t *__restrict__ improved)
+	{
+		for (int x = blockIdx.x * blockDim.x + threadIdx.x; x < P.W; x += gridDim.x * blockDim.x)
+		{
+			const uint32_t n = incoming[x], o = halo[x];
+			if (n < o)
+			{
+				halo[x] = n;
+				if (n != 0u)
+				{
+					atomicAdd(improved, 1u);
+					activate_item(P, 0, x / TS, ty, round - 1);
+				}
+			}
 		}
 	}
 

@@ -66,6 +66,7 @@ namespace
 		uint32_t spawn[3];
 		uint32_t big_items;     // (layer, tile) visits of the last tiled relaxation (statistics)
 		uint32_t stage_blocked; // pinned staging word of the trial grid's extra blocked tile
+		uint32_t stripe_improved; // halo cells lowered by the last mtd_stripe_exchange_dev
 	};
 }
 
@@ -93,6 +94,12 @@ struct mtd_ctx
 	DevBuf<uint32_t> sources;
 	int tilesX = 0, tilesY = 0;
 	uint32_t last_rounds = 0;
+	// row stripe of a larger grid (multi-GPU, one rank per stripe): rows [sy0, sy1) of a W x sH grid are this context's grid
+	bool stripe = false;
+	int sy0 = 0, sy1 = 0, sH = 0, stripe_round = 0, stripe_nsrc = 0;
+	uint32_t *stripe_dist = nullptr;                 // caller-owned [sy1 - sy0][W]
+	DevBuf<uint32_t> halo_up, halo_down, up_wpack;   // local copies of the neighbour stripes' boundary rows; wpack of row sy0-1
+	DevBuf<uint8_t> up_blocked;
 
 	// resident layers
 	int nlayers = 0;
@@ -460,10 +467,76 @@ namespace
 		return MTD_OK;
 	}
 
+	// ---- row stripe of a larger grid (one rank per stripe) -------------------------------
+	BigParams stripe_params(mtd_ctx *ctx)
+	{
+		BigParams P;
+		memset(&P, 0, sizeof(P));
+		P.W = ctx->W;
+		P.H = ctx->sH;
+		P.y0 = ctx->sy0;
+		P.y1 = ctx->sy1;
+		P.tilesX = ctx->tilesX;
+		P.tilesY = ctx->tilesY;
+		P.nlayers = 1;
+		P.nsrc = ctx->stripe_nsrc;
+		P.dist = ctx->stripe_dist;
+		P.layer_stride = ctx->T;
+		P.wpack = ctx->wpack.p;
+		P.blocked = ctx->blocked.p;
+		P.sources = ctx->sources.p;
+		P.list[0] = ctx->list0.p;
+		P.list[1] = ctx->list1.p;
+		P.count = ctx->counters.p;
+		P.cursor = ctx->counters.p + 2;
+		P.total_active = ctx->counters.p + 3;
+		P.stamp = ctx->stamp.p;
+		P.status = ctx->d_status.p;
+		P.aligned16 = (ctx->W % 4 == 0) && ((uintptr_t)ctx->stripe_dist % 16 == 0) && ((uintptr_t)ctx->wpack.p % 16 == 0) && ((uintptr_t)ctx->halo_up.p % 16 == 0) && ((uintptr_t)ctx->halo_down.p % 16 == 0) && ((uintptr_t)ctx->up_wpack.p % 16 == 0) ? 1 : 0;
+		P.up_row = ctx->sy0 > 0 ? ctx->halo_up.p : nullptr;
+		P.up_wpack = ctx->sy0 > 0 ? ctx->up_wpack.p : nullptr;
+		P.down_row = ctx->sy1 < ctx->sH ? ctx->halo_down.p : nullptr;
+		return P;
+	}
+
+	// relax the stripe until its work-list is empty (the halo copies are constant meanwhile)
+	int stripe_run(mtd_ctx *ctx, const BigParams &P)
+	{
+		using TSm = TileSmem<BIG_TS>;
+		const size_t smem = sizeof(TSm);
+		CU(cudaFuncSetAttribute(k_tile_round<BIG_TS, BIG_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		uint32_t *d_next = nullptr;
+		CU(cudaHostGetDevicePointer((void **)&d_next, &ctx->hflags->next_count, 0));
+		const int ctas_per_sm = (int)(MAX_SMEM / (smem + 1024));
+		const int blocks = ctx->sms * (ctas_per_sm > 0 ? ctas_per_sm : 1);
+		const int limit = ctx->stripe_round + 4 * (ctx->tilesX + ctx->tilesY) * 64 + 100000;
+		int burst = 4;
+		ProfScope prof(ctx, MTD_K_BIG_RELAX);
+		for (;;)
+		{
+			for (int b = 0; b < burst; b++, ctx->stripe_round++)
+			{
+				k_tile_round<BIG_TS, BIG_WARPS><<<blocks, BIG_WARPS * 32, smem, ctx->stream>>>(P, ctx->stripe_round);
+				LAUNCHED();
+				k_round_advance<<<1, 1, 0, ctx->stream>>>(P, ctx->stripe_round, d_next);
+				LAUNCHED();
+			}
+			CU(cudaStreamSynchronize(ctx->stream));
+			if (ctx->hflags->next_count == 0)
+				break;
+			if (burst < 32)
+				burst *= 2;
+			if (ctx->stripe_round > limit)
+				return fail(ctx, MTD_ERR_CUDA, "stripe relaxation did not converge");
+		}
+		ctx->last_rounds = (uint32_t)ctx->stripe_round;
+		return MTD_OK;
+	}
+
 	int directions_dev(mtd_ctx *ctx, const uint32_t *sources, int nsrc, uint32_t extra_blocked, uint32_t *d_tiles, uint32_t *d_dist)
 	{
-		if (!ctx->have_grid)
-			return fail(ctx, MTD_ERR_STATE, "no grid uploaded");
+		if (!ctx->have_grid || ctx->stripe)
+			return fail(ctx, MTD_ERR_STATE, ctx->stripe ? "context holds a row stripe: use the mtd_stripe_* calls" : "no grid uploaded");
 		if (!sources || nsrc < 1)
 			return fail(ctx, MTD_ERR_ARG, "sources must hold at least one tile");
 		for (int i = 0; i < nsrc; i++)
@@ -534,8 +607,8 @@ namespace
 
 	int waypoints_dev(mtd_ctx *ctx, const uint32_t *wp_tiles, int n, uint32_t fullpath_cap)
 	{
-		if (!ctx->have_grid)
-			return fail(ctx, MTD_ERR_STATE, "no grid uploaded");
+		if (!ctx->have_grid || ctx->stripe)
+			return fail(ctx, MTD_ERR_STATE, "no grid uploaded (or the context holds a row stripe)");
 		if (n < 0 || n > MTD_MAX_WAYPOINTS)
 			return fail(ctx, MTD_ERR_ARG, "waypoint count %d outside [0, %d]", n, MTD_MAX_WAYPOINTS);
 		ctx->nlayers = n;
@@ -804,6 +877,7 @@ static int grid_common(mtd_ctx *ctx, int32_t W, int32_t H, int32_t ox, int32_t o
 	if ((uint64_t)W * (uint64_t)H >= 0xFFFFFFFFull)
 		return fail(ctx, MTD_ERR_ARG, "grid too large for uint32 tile indices");
 	ctx->have_grid = false;
+	ctx->stripe = false;
 	ctx->nlayers = 0;
 	ctx->W = W;
 	ctx->H = H;
@@ -845,14 +919,175 @@ extern "C" int mtd_grid_upload_dev(mtd_ctx *ctx, int32_t W, int32_t H, int32_t o
 	return grid_common(ctx, W, H, ox, oy, d_elev, d_flags, cudaMemcpyDeviceToDevice);
 }
 
+// ---- row stripes ---------------------------------------------------------------------------------------
+static int stripe_common(mtd_ctx *ctx, int32_t W, int32_t H, int32_t y0, int32_t y1, const int16_t *elev_rows, const uint16_t *flags_rows, cudaMemcpyKind kind)
+{
+	if (W < 1 || H < 1 || y0 < 0 || y1 > H || y0 >= y1 || !elev_rows || !flags_rows)
+		return fail(ctx, MTD_ERR_ARG, "stripe needs 0 <= y0 < y1 <= H and non-null rows");
+	if ((uint64_t)W * (uint64_t)H >= 0xFFFFFFFFull)
+		return fail(ctx, MTD_ERR_ARG, "grid too large for uint32 tile indices");
+	const int Hl = y1 - y0;
+	const int above = y0 > 0 ? 1 : 0, below = y1 < H ? 1 : 0;
+	ctx->have_grid = false;
+	ctx->nlayers = 0;
+	ctx->W = W;
+	ctx->H = Hl;
+	ctx->ox = ctx->oy = 0;
+	ctx->T = (size_t)W * Hl;
+	ctx->sy0 = y0;
+	ctx->sy1 = y1;
+	ctx->sH = H;
+	ctx->stripe = true;
+	ctx->small = false;
+	ctx->stripe_dist = nullptr;
+	// elev and flags keep the halo rows too: [above + Hl + below][W]
+	const size_t rows = (size_t)(above + Hl + below);
+	CU(ctx->elev.reserve(rows * W));
+	CU(ctx->flags.reserve(rows * W));
+	CU(cudaMemcpyAsync(ctx->elev.p, elev_rows, rows * W * 2, kind, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->flags.p, flags_rows, rows * W * 2, kind, ctx->stream));
+	CU(ctx->wpack.reserve(ctx->T));
+	CU(ctx->blocked.reserve(ctx->T));
+	CU(ctx->halo_up.reserve(W));
+	CU(ctx->halo_down.reserve(W));
+	CU(ctx->up_wpack.reserve(W));
+	CU(ctx->up_blocked.reserve(W));
+	CU(ctx->counters.reserve(8));
+	ctx->tilesX = (W + BIG_TS - 1) / BIG_TS;
+	ctx->tilesY = (Hl + BIG_TS - 1) / BIG_TS;
+	const int16_t *own_e = ctx->elev.p + (size_t)above * W;
+	const uint16_t *own_f = ctx->flags.p + (size_t)above * W;
+	{
+		ProfScope prof(ctx, MTD_K_BIG_PREPARE);
+		k_edge_weights<<<grid_blocks(ctx, ctx->T, 256), 256, 0, ctx->stream>>>(W, Hl, own_e, below ? own_e + (size_t)Hl * W : nullptr, own_f, ctx->wpack.p, ctx->blocked.p);
+		LAUNCHED();
+		if (above) // weights of the edges (y0-1) -> y0, stored on the upper cell like everywhere else
+		{
+			k_edge_weights<<<grid_blocks(ctx, W, 256), 256, 0, ctx->stream>>>(W, 1, ctx->elev.p, own_e, ctx->flags.p, ctx->up_wpack.p, ctx->up_blocked.p);
+			LAUNCHED();
+		}
+	}
+	if (kind == cudaMemcpyHostToDevice)
+		CU(cudaStreamSynchronize(ctx->stream));
+	ctx->have_grid = true;
+	return MTD_OK;
+}
+
+extern "C" int mtd_stripe_upload(mtd_ctx *ctx, int32_t W, int32_t H, int32_t y0, int32_t y1, const int16_t *elev_rows, const uint16_t *flags_rows)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	return stripe_common(ctx, W, H, y0, y1, elev_rows, flags_rows, cudaMemcpyHostToDevice);
+}
+
+extern "C" int mtd_stripe_upload_dev(mtd_ctx *ctx, int32_t W, int32_t H, int32_t y0, int32_t y1, const int16_t *d_elev_rows, const uint16_t *d_flags_rows)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	return stripe_common(ctx, W, H, y0, y1, d_elev_rows, d_flags_rows, cudaMemcpyDeviceToDevice);
+}
+
+extern "C" int mtd_stripe_begin_dev(mtd_ctx *ctx, const uint32_t *sources, int32_t nsrc, uint32_t *d_dist)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (!ctx->have_grid || !ctx->stripe)
+		return fail(ctx, MTD_ERR_STATE, "no stripe uploaded");
+	if (!sources || nsrc < 1 || !d_dist)
+		return fail(ctx, MTD_ERR_ARG, "stripe_begin needs sources and a distance buffer");
+	for (int i = 0; i < nsrc; i++)
+		if ((uint64_t)sources[i] >= (uint64_t)ctx->W * (uint64_t)ctx->sH)
+			return fail(ctx, MTD_ERR_ARG, "source tile %u outside the grid", sources[i]);
+	const size_t nt = (size_t)ctx->tilesX * ctx->tilesY;
+	CU(ctx->list0.reserve(nt));
+	CU(ctx->list1.reserve(nt));
+	CU(ctx->stamp.reserve(nt));
+	CU(ctx->sources.reserve(nsrc));
+	CU(cudaMemcpyAsync(ctx->sources.p, sources, (size_t)nsrc * 4, cudaMemcpyHostToDevice, ctx->stream));
+	CU(cudaMemsetAsync(ctx->stamp.p, 0, nt * 4, ctx->stream));
+	CU(cudaMemsetAsync(ctx->counters.p, 0, 8 * 4, ctx->stream));
+	CU(cudaMemsetAsync(ctx->halo_up.p, 0xFF, (size_t)ctx->W * 4, ctx->stream));
+	CU(cudaMemsetAsync(ctx->halo_down.p, 0xFF, (size_t)ctx->W * 4, ctx->stream));
+	ctx->stripe_dist = d_dist;
+	ctx->stripe_nsrc = nsrc;
+	ctx->stripe_round = 0;
+	{
+		ProfScope prof(ctx, MTD_K_BIG_PREPARE);
+		k_big_init<<<grid_blocks(ctx, ctx->T, 256), 256, 0, ctx->stream>>>(d_dist, ctx->T, 1, ctx->T, ctx->blocked.p);
+		LAUNCHED();
+	}
+	const BigParams P = stripe_params(ctx);
+	k_big_seed<BIG_TS><<<(nsrc + 127) / 128, 128, 0, ctx->stream>>>(P);
+	LAUNCHED();
+	k_stripe_seed_halo<BIG_TS><<<(nsrc + 127) / 128, 128, 0, ctx->stream>>>(P);
+	LAUNCHED();
+	return stripe_run(ctx, P);
+}
+
+extern "C" int mtd_stripe_exchange_dev(mtd_ctx *ctx, const uint32_t *d_row_above, const uint32_t *d_row_below, uint32_t *improved_out)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (!ctx->have_grid || !ctx->stripe || !ctx->stripe_dist)
+		return fail(ctx, MTD_ERR_STATE, "stripe_exchange before stripe_begin");
+	const BigParams P = stripe_params(ctx);
+	uint32_t *d_improved = ctx->counters.p + 4;
+	CU(cudaMemsetAsync(d_improved, 0, 4, ctx->stream));
+	const int blocks = (ctx->W + 255) / 256;
+	if (d_row_above && ctx->sy0 > 0)
+	{
+		k_stripe_merge<BIG_TS><<<blocks, 256, 0, ctx->stream>>>(P, ctx->halo_up.p, d_row_above, 0, ctx->stripe_round, d_improved);
+		LAUNCHED();
+	}
+	if (d_row_below && ctx->sy1 < ctx->sH)
+	{
+		k_stripe_merge<BIG_TS><<<blocks, 256, 0, ctx->stream>>>(P, ctx->halo_down.p, d_row_below, ctx->tilesY - 1, ctx->stripe_round, d_improved);
+		LAUNCHED();
+	}
+	CU(cudaMemcpyAsync(&ctx->hflags->stripe_improved, d_improved, 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	const uint32_t improved = ctx->hflags->stripe_improved;
+	if (improved_out)
+		*improved_out = improved;
+	if (improved == 0)
+		return MTD_OK;
+	return stripe_run(ctx, P);
+}
+
+extern "C" int mtd_stripe_finalize_dev(mtd_ctx *ctx, uint32_t *d_tiles)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (!ctx->have_grid || !ctx->stripe || !ctx->stripe_dist)
+		return fail(ctx, MTD_ERR_STATE, "stripe_finalize before stripe_begin");
+	const BigParams P = stripe_params(ctx);
+	{
+		ProfScope prof(ctx, MTD_K_BIG_DIRECTIONS);
+		k_big_finalize<<<dim3((unsigned)grid_blocks(ctx, ctx->T, 256, 8), 1u), 256, 0, ctx->stream>>>(ctx->W, ctx->H, ctx->sy0, ctx->sH, ctx->stripe_dist, ctx->T, ctx->wpack.p, ctx->blocked.p, ctx->sources.p, ctx->stripe_nsrc, P.up_row, P.up_wpack, P.down_row, d_tiles, ctx->T);
+		LAUNCHED();
+	}
+	ctx->stripe_dist = nullptr;
+	return MTD_OK;
+}
+
 extern "C" int mtd_grid_set_flags(mtd_ctx *ctx, uint32_t tile, uint16_t flags)
 {
 	if (!ctx)
 		return MTD_ERR_ARG;
 	std::lock_guard<std::mutex> lk(ctx->mu);
 	DeviceGuard g(ctx->device);
-	if (!ctx->have_grid)
-		return fail(ctx, MTD_ERR_STATE, "no grid uploaded");
+	if (!ctx->have_grid || ctx->stripe)
+		return fail(ctx, MTD_ERR_STATE, "no grid uploaded (or the context holds a row stripe)");
 	if (tile >= ctx->T)
 		return fail(ctx, MTD_ERR_ARG, "tile outside the grid");
 	ctx->hflags->spawn[0] = flags; // staged in pinned memory so the async copy has a stable source
@@ -872,8 +1107,8 @@ extern "C" int mtd_neighbor_distances(mtd_ctx *ctx, const uint32_t *a, const uin
 		return MTD_ERR_ARG;
 	std::lock_guard<std::mutex> lk(ctx->mu);
 	DeviceGuard g(ctx->device);
-	if (!ctx->have_grid)
-		return fail(ctx, MTD_ERR_STATE, "no grid uploaded");
+	if (!ctx->have_grid || ctx->stripe)
+		return fail(ctx, MTD_ERR_STATE, "no grid uploaded (or the context holds a row stripe)");
 	if (n < 0 || (n && (!a || !b || !out)))
 		return fail(ctx, MTD_ERR_ARG, "bad arguments");
 	if (n == 0)
@@ -899,8 +1134,8 @@ extern "C" int mtd_edge_weights(mtd_ctx *ctx, uint32_t *right, uint32_t *down)
 		return MTD_ERR_ARG;
 	std::lock_guard<std::mutex> lk(ctx->mu);
 	DeviceGuard g(ctx->device);
-	if (!ctx->have_grid)
-		return fail(ctx, MTD_ERR_STATE, "no grid uploaded");
+	if (!ctx->have_grid || ctx->stripe)
+		return fail(ctx, MTD_ERR_STATE, "no grid uploaded (or the context holds a row stripe)");
 	if (!right || !down)
 		return fail(ctx, MTD_ERR_ARG, "null output");
 	CU(ctx->scratch_u32a.reserve(ctx->T));
@@ -925,14 +1160,38 @@ extern "C" int mtd_directions_update_dev(mtd_ctx *ctx, const uint32_t *sources, 
 	return directions_dev(ctx, sources, nsrc, extra_blocked, d_tiles, d_dist);
 }
 
+extern "C" int mtd_directions_layers_dev(mtd_ctx *ctx, const uint32_t *targets, int32_t n, uint32_t *d_tiles, uint32_t *d_dist)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (!ctx->have_grid || ctx->stripe)
+		return fail(ctx, MTD_ERR_STATE, "no grid uploaded (or the context holds a row stripe)");
+	if (!targets || n < 1 || !d_dist)
+		return fail(ctx, MTD_ERR_ARG, "layers need targets and a distance buffer");
+	for (int i = 0; i < n; i++)
+		if (targets[i] >= ctx->T)
+			return fail(ctx, MTD_ERR_ARG, "target tile %u outside the grid", targets[i]);
+	if (!ctx->small)
+		return big_layers(ctx, targets, n, 1, MTD_M, d_tiles, d_dist); // all layers in flight together
+	for (int i = 0; i < n; i++)
+	{
+		int rc = directions_dev(ctx, targets + i, 1, MTD_M, d_tiles ? d_tiles + (size_t)i * ctx->T : nullptr, d_dist + (size_t)i * ctx->T);
+		if (rc)
+			return rc;
+	}
+	return MTD_OK;
+}
+
 extern "C" int mtd_directions_update(mtd_ctx *ctx, const uint32_t *sources, int32_t nsrc, uint32_t extra_blocked, uint32_t *tiles_out, uint32_t *dist_out)
 {
 	if (!ctx)
 		return MTD_ERR_ARG;
 	std::lock_guard<std::mutex> lk(ctx->mu);
 	DeviceGuard g(ctx->device);
-	if (!ctx->have_grid)
-		return fail(ctx, MTD_ERR_STATE, "no grid uploaded");
+	if (!ctx->have_grid || ctx->stripe)
+		return fail(ctx, MTD_ERR_STATE, "no grid uploaded (or the context holds a row stripe)");
 	CU(ctx->scratch_u32a.reserve(ctx->T));
 	CU(ctx->scratch_u32b.reserve(ctx->T));
 	int rc = directions_dev(ctx, sources, nsrc, extra_blocked, tiles_out ? ctx->scratch_u32a.p : nullptr, ctx->scratch_u32b.p);
@@ -1397,8 +1656,8 @@ extern "C" int mtd_monsters_positions_dev(mtd_ctx *ctx, uint32_t gameTime, float
 		return MTD_ERR_ARG;
 	std::lock_guard<std::mutex> lk(ctx->mu);
 	DeviceGuard g(ctx->device);
-	if (!ctx->have_grid)
-		return fail(ctx, MTD_ERR_STATE, "no grid uploaded");
+	if (!ctx->have_grid || ctx->stripe)
+		return fail(ctx, MTD_ERR_STATE, "no grid uploaded (or the context holds a row stripe)");
 	if (ctx->nmon == 0)
 		return MTD_OK;
 	if (!d_out3n)

@@ -526,3 +526,94 @@ def test_directions_against_committed_golden(ctx):
     assert int(t.astype(np.uint64).sum() & 0xFFFFFFFF) == int(gold["big_tiles_sum"])
     assert np.array_equal(d[100 * W : 101 * W], gold["big_dist_row100"])
     assert np.array_equal(t[100 * W : 101 * W], gold["big_tiles_row100"])
+
+
+# ---------------------------------------------------------------------------------------------------
+# row stripes of one large grid: several stripe contexts on one GPU run the multi-GPU protocol
+# ---------------------------------------------------------------------------------------------------
+def _striped_on_one_gpu(W, H, cuts, elev, flags, srcs):
+    from mazetd_b200 import shard, striped
+
+    stripes = []
+    for y0, y1 in zip(cuts[:-1], cuts[1:]):
+        ya, yb = shard.stripe_halo_rows(y0, y1, H)
+        stripes.append(striped.GpuStripe(0, W, H, y0, y1, elev.reshape(H, W)[ya:yb], flags.reshape(H, W)[ya:yb], srcs))
+    results, sweeps = striped.solve_local(stripes)
+    tiles = np.concatenate([t.cpu().numpy().view(np.uint32).reshape(-1) for t, _ in results])
+    d = np.concatenate([x.cpu().numpy().view(np.uint32).reshape(-1) for _, x in results])
+    launches = sum(s.ctx.launches for s in stripes)
+    for s in stripes:
+        s.close()
+    return tiles, d, sweeps, launches
+
+
+@pytest.mark.parametrize("W,H,cuts,nsrc,pct", [
+    (384, 320, [0, 128, 320], 1, 30),        # tile-aligned cut
+    (384, 320, [0, 64, 128, 192, 320], 4, 30),
+    (200, 301, [0, 97, 203, 301], 3, 35),    # ragged width, cuts inside tiles
+    (256, 256, [0, 1, 255, 256], 2, 20),     # one-row stripes at both ends
+    (1024, 1024, [0, 256, 512, 768, 1024], 16, 30),
+])
+def test_stripes_bit_exact_with_whole_grid(oracle, W, H, cuts, nsrc, pct):
+    elev, flags = synth.random_grid(W, H, seed_k=W + len(cuts), wall_pct=pct)
+    srcs = synth.pick_open_tiles(flags, nsrc, 2)
+    tiles, d, sweeps, launches = _striped_on_one_gpu(W, H, cuts, elev, flags, srcs)
+    to, do = oracle.directions_update(W, H, elev, flags, srcs)
+    assert np.array_equal(d, do), diff_report(d, do, W)
+    assert np.array_equal(tiles, to), diff_report(tiles, to, W)
+    assert sweeps >= 1 and launches > 0
+
+
+def test_stripes_maze_crosses_the_cut_many_times(oracle):
+    """a maze makes shortest paths wander across the cuts: many sweeps, same fixpoint"""
+    W, H = 320, 256
+    elev, flags = synth.maze_grid(W, H, seed_k=4)
+    srcs = synth.pick_open_tiles(flags, 1, 1)
+    tiles, d, sweeps, _ = _striped_on_one_gpu(W, H, [0, 64, 128, 192, 256], elev, flags, srcs)
+    to, do = oracle.directions_update(W, H, elev, flags, srcs)
+    assert np.array_equal(d, do), diff_report(d, do, W)
+    assert np.array_equal(tiles, to), diff_report(tiles, to, W)
+    assert sweeps > 2
+
+
+def test_stripes_sources_on_cut_rows_and_blocked_source(oracle):
+    W, H = 192, 192
+    elev, flags = synth.random_grid(W, H, seed_k=9, wall_pct=25)
+    flags = flags.copy()
+    srcs = np.array([63 * W + 10, 64 * W + 100, 127 * W + 191, 128 * W + 0], np.uint32)
+    flags[srcs] &= ~np.uint16(synth.FLAG_BUILDING | 1)
+    flags[srcs[1]] |= synth.FLAG_BUILDING  # a blocked source still expands (paths.cpp:63-67)
+    tiles, d, _, _ = _striped_on_one_gpu(W, H, [0, 64, 128, 192], elev, flags, srcs)
+    to, do = oracle.directions_update(W, H, elev, flags, srcs)
+    assert np.array_equal(d, do), diff_report(d, do, W)
+    assert np.array_equal(tiles, to), diff_report(tiles, to, W)
+
+
+def test_stripe_context_rejects_whole_grid_calls():
+    from mazetd_b200 import capi
+
+    c = capi.Context(0)
+    W, H = 128, 128
+    elev, flags = synth.random_grid(W, H, seed_k=1)
+    c.stripe_upload(W, H, 0, 64, elev.reshape(H, W)[0:65], flags.reshape(H, W)[0:65])
+    with pytest.raises(capi.MtdError):
+        c.directions_update(np.array([5], np.uint32))
+    c.close()
+
+
+def test_directions_layers_dev_matches_oracle_per_layer(ctx, oracle):
+    """mtd_directions_layers_dev: n independent single-target layers on a tiled grid (the unit sharded across GPUs in C5)"""
+    import torch
+
+    W, H = 320, 272
+    elev, flags = synth.random_grid(W, H, seed_k=6, wall_pct=30)
+    targets = synth.pick_open_tiles(flags, 5, 4)
+    ctx.grid_upload(W, H, elev, flags)
+    dt = torch.empty((5, W * H), dtype=torch.int32, device="cuda")
+    dd = torch.empty((5, W * H), dtype=torch.int32, device="cuda")
+    ctx.layers_update_dev(targets, dt.data_ptr(), dd.data_ptr())
+    ctx.synchronize()
+    for l in range(5):
+        to, do = oracle.directions_update(W, H, elev, flags, targets[l:l + 1])
+        assert np.array_equal(dd[l].cpu().numpy().view(np.uint32), do), f"layer {l}: " + diff_report(dd[l].cpu().numpy().view(np.uint32), do, W)
+        assert np.array_equal(dt[l].cpu().numpy().view(np.uint32), to)
