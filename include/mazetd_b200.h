@@ -168,6 +168,11 @@ typedef struct mtd_mapgen_params
 int mtd_mapgen_batch(mtd_ctx *ctx, const mtd_mapgen_params *p, uint64_t s1, uint64_t s2, int32_t first, int32_t nmaps, int16_t *elev, uint16_t *flags, uint32_t *wp_tiles, uint32_t *tiles, uint32_t *dist, uint32_t *fullpath, uint32_t *fullpath_len, uint32_t *full_distance, uint32_t *agg);
 /* same with DEVICE output pointers (all required except tiles/dist/fullpath, which may be NULL); asynchronous */
 int mtd_mapgen_batch_dev(mtd_ctx *ctx, const mtd_mapgen_params *p, uint64_t s1, uint64_t s2, int32_t first, int32_t nmaps, int16_t *d_elev, uint16_t *d_flags, uint32_t *d_wp_tiles, uint32_t *d_tiles, uint32_t *d_dist, uint32_t *d_fullpath, uint32_t *d_fullpath_len, uint32_t *d_full_distance, uint32_t *d_agg);
+/* newGrid after the elevation sampling (sources/map/grid.cpp:160-196): biome flags, maxSlope / radius invalidation,
+ * fillUnreachable (largest 4-connected component, first-discovered wins ties), findBorder, Mana -- on the CALLER's
+ * int16 elevations [nmaps][T] (host), flags out [nmaps][T] (host). Uses W, H, ox, oy, radius of *p. This is the part of
+ * the generator that the compiled reference pins independently of the noise library. */
+int mtd_grid_from_elevations(mtd_ctx *ctx, const mtd_mapgen_params *p, int32_t nmaps, const int16_t *elev, uint16_t *flags_out);
 /* raw float32 ProceduralImpl::elevation samples (procedural.cpp:65-70) for seed (s1, s2): parity probe */
 int mtd_elevation_samples(mtd_ctx *ctx, uint64_t s1, uint64_t s2, const float *xy, int32_t n, float *out);
 

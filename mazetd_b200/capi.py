@@ -20,7 +20,7 @@ EXPORTS = [
     "mtd_stripe_upload", "mtd_stripe_upload_dev", "mtd_stripe_begin_dev", "mtd_stripe_exchange_dev", "mtd_stripe_finalize_dev",
     "mtd_waypoints_update", "mtd_waypoints_update_dev", "mtd_waypoints_find", "mtd_waypoints_layers_dev",
     "mtd_placing_blocks",
-    "mtd_mapgen_batch", "mtd_mapgen_batch_dev", "mtd_elevation_samples",
+    "mtd_mapgen_batch", "mtd_mapgen_batch_dev", "mtd_grid_from_elevations", "mtd_elevation_samples",
     "mtd_monsters_upload", "mtd_monsters_download", "mtd_monsters_tick_dev", "mtd_monsters_tick",
     "mtd_monsters_positions_dev", "mtd_monsters_positions", "mtd_monster_spawn",
 ]
@@ -79,6 +79,7 @@ def load():
     L.mtd_placing_blocks.argtypes = [vp, u32, C.POINTER(i32)]
     L.mtd_mapgen_batch.argtypes = [vp, C.POINTER(MapgenParams), u64, u64, i32, i32] + [vp] * 9
     L.mtd_mapgen_batch_dev.argtypes = [vp, C.POINTER(MapgenParams), u64, u64, i32, i32] + [vp] * 9
+    L.mtd_grid_from_elevations.argtypes = [vp, C.POINTER(MapgenParams), i32, vp, vp]
     L.mtd_elevation_samples.argtypes = [vp, u64, u64, vp, i32, vp]
     L.mtd_monsters_upload.argtypes = [vp, i32] + [vp] * 10
     L.mtd_monsters_download.argtypes = [vp] + [vp] * 7
@@ -287,6 +288,14 @@ class Context:
         """ptrs: dict of raw device pointers (ints) for elev, flags, wp_tiles, tiles, dist, fullpath, fullpath_len, full_distance, agg"""
         p = MapgenParams(W, H, ox, oy, radius, nwp, cap)
         self._ck(self.L.mtd_mapgen_batch_dev(self.h, C.byref(p), s1, s2, first, nmaps, *[_p(ptrs.get(k)) for k in ("elev", "flags", "wp_tiles", "tiles", "dist", "fullpath", "fullpath_len", "full_distance", "agg")]))
+
+    def grid_from_elevations(self, elev, W=101, H=101, ox=50, oy=50, radius=45):
+        """newGrid after the elevation sampling on the caller's int16 elevations [nmaps][T] -> flags [nmaps][T]"""
+        elev = np.ascontiguousarray(elev, np.int16).reshape(-1, W * H)
+        flags = np.empty(elev.shape, np.uint16)
+        p = MapgenParams(W, H, ox, oy, radius, 0, 0)
+        self._ck(self.L.mtd_grid_from_elevations(self.h, C.byref(p), elev.shape[0], _p(elev), _p(flags)))
+        return flags
 
     def elevation_samples(self, s1, s2, xy):
         xy = np.ascontiguousarray(xy, np.float32)

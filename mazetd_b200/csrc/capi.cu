@@ -112,6 +112,8 @@ struct mtd_ctx
 	int debug_gw = SMALL_GROUP_WARPS;
 	int debug_walker = 0; // 0 auto, 1 never, 2 always
 	DevBuf<uint32_t> scratch_tiles, scratch_dist;
+	DevBuf<int16_t> scratch_elev_in, scratch_elev;
+	DevBuf<uint16_t> scratch_flags;
 
 	// monsters
 	int nmon = 0;
@@ -1329,7 +1331,7 @@ extern "C" int mtd_placing_blocks(mtd_ctx *ctx, uint32_t candidate, int32_t *blo
 // =====================================================================================================
 // procedural generator
 // =====================================================================================================
-static int mapgen_dev(mtd_ctx *ctx, const mtd_mapgen_params *p, uint64_t s1, uint64_t s2, int32_t first, int32_t nmaps, int16_t *d_elev, uint16_t *d_flags, uint32_t *d_wp, uint32_t *d_tiles, uint32_t *d_dist, uint32_t *d_fullpath, uint32_t *d_fplen, uint32_t *d_fdist, uint32_t *d_agg)
+static int mapgen_dev(mtd_ctx *ctx, const mtd_mapgen_params *p, uint64_t s1, uint64_t s2, int32_t first, int32_t nmaps, int16_t *d_elev, uint16_t *d_flags, uint32_t *d_wp, uint32_t *d_tiles, uint32_t *d_dist, uint32_t *d_fullpath, uint32_t *d_fplen, uint32_t *d_fdist, uint32_t *d_agg, const int16_t *d_elev_in = nullptr)
 {
 	if (!p || p->W < 1 || p->H < 1 || p->nwp < 0 || p->nwp > MTD_MAX_WAYPOINTS || nmaps < 0)
 		return fail(ctx, MTD_ERR_ARG, "bad mapgen parameters");
@@ -1362,6 +1364,7 @@ static int mapgen_dev(mtd_ctx *ctx, const mtd_mapgen_params *p, uint64_t s1, uin
 	G.flags = d_flags;
 	G.wp_tiles = d_wp;
 	G.status = ctx->d_status.p;
+	G.elev_in = d_elev_in;
 	const size_t gsm = mapgen_grid_smem(T);
 	const int per_sm = (int)(MAX_SMEM / (gsm + 1024)) > 0 ? (int)(MAX_SMEM / (gsm + 1024)) : 1;
 	const int gblocks = nmaps < ctx->sms * per_sm ? nmaps : ctx->sms * per_sm;
@@ -1514,6 +1517,39 @@ __global__ void k_elevation_samples(uint64_t s1, uint64_t s2, const float *xy, i
 	const noise::ElevationParams lp = ep;
 	for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
 		out[i] = noise::elevation(grad, lp, xy[i * 2 + 0], xy[i * 2 + 1]);
+}
+
+extern "C" int mtd_grid_from_elevations(mtd_ctx *ctx, const mtd_mapgen_params *p, int32_t nmaps, const int16_t *elev, uint16_t *flags_out)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (!p || nmaps < 0 || (nmaps && (!elev || !flags_out)))
+		return fail(ctx, MTD_ERR_ARG, "grid_from_elevations needs elevations in and flags out");
+	if (nmaps == 0)
+		return MTD_OK;
+	const size_t T = (size_t)p->W * p->H;
+	mtd_mapgen_params q = *p;
+	q.nwp = 0; // spawn picking belongs to newWaypoints (sources/map/paths.cpp:185-196), not newGrid
+	const int chunk = 1024;
+	CU(ctx->scratch_elev_in.reserve((size_t)chunk * T));
+	CU(ctx->scratch_elev.reserve((size_t)chunk * T));
+	CU(ctx->scratch_flags.reserve((size_t)chunk * T));
+	CU(ctx->scratch_u32a.reserve(64));
+	for (int first = 0; first < nmaps; first += chunk)
+	{
+		const int cnt = nmaps - first < chunk ? nmaps - first : chunk;
+		CU(cudaMemcpyAsync(ctx->scratch_elev_in.p, elev + (size_t)first * T, (size_t)cnt * T * 2, cudaMemcpyHostToDevice, ctx->stream));
+		int rc = mapgen_dev(ctx, &q, 0, 0, 0, cnt, ctx->scratch_elev.p, ctx->scratch_flags.p, ctx->scratch_u32a.p, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, ctx->scratch_elev_in.p);
+		if (rc)
+			return rc;
+		CU(cudaMemcpyAsync(flags_out + (size_t)first * T, ctx->scratch_flags.p, (size_t)cnt * T * 2, cudaMemcpyDeviceToHost, ctx->stream));
+		rc = sync_and_status(ctx);
+		if (rc)
+			return rc;
+	}
+	return MTD_OK;
 }
 
 extern "C" int mtd_elevation_samples(mtd_ctx *ctx, uint64_t s1, uint64_t s2, const float *xy, int32_t n, float *out)

@@ -27,6 +27,7 @@ namespace mtd
 		uint16_t *flags;    // [nmaps][T]
 		uint32_t *wp_tiles; // [nmaps][nwp]
 		int *status;
+		const int16_t *elev_in; // non-null: caller's elevations [nmaps][T] replace the noise (newGrid stages after grid.cpp:159)
 	};
 
 	// shared memory: parent u32[T] | elev i16[T] | flags u16[T] | grad float2[128]
@@ -112,14 +113,21 @@ namespace mtd
 
 			// ---- elevations: grid.cpp:153-159 ----
 			const noise::ElevationParams lp = ep;
-			for (int i = threadIdx.x; i < T; i += blockDim.x)
+			if (P.elev_in)
 			{
-				const int y = (int)div_w((uint32_t)i, magicW), x = i - y * W;
-				float e = noise::elevation(grad, lp, (float)(x - P.ox), (float)(y - P.oy));
-				e = e > -100.0f ? e : -100.0f;
-				e = e < 100.0f ? e : 100.0f;
-				elev[i] = rtos16(e);
+				const int16_t *src = P.elev_in + (size_t)mapi * T;
+				for (int i = threadIdx.x; i < T; i += blockDim.x)
+					elev[i] = src[i];
 			}
+			else
+				for (int i = threadIdx.x; i < T; i += blockDim.x)
+				{
+					const int y = (int)div_w((uint32_t)i, magicW), x = i - y * W;
+					float e = noise::elevation(grad, lp, (float)(x - P.ox), (float)(y - P.oy));
+					e = e > -100.0f ? e : -100.0f;
+					e = e < 100.0f ? e : 100.0f;
+					elev[i] = rtos16(e);
+				}
 			__syncthreads();
 
 			// ---- biome flags, slope, radius: grid.cpp:160-183 (thresholds are rtos16(-7), (1), (6), (0.35)) ----
@@ -286,7 +294,7 @@ namespace mtd
 					}
 					P.wp_tiles[(size_t)mapi * P.nwp + k] = t;
 				}
-				if (!any_valid)
+				if (!any_valid && P.nwp > 0) // without spawn picking an empty map is a legitimate newGrid result
 					atomicOr(P.status, ST_NO_VALID);
 			}
 			__syncthreads();

@@ -13,6 +13,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_SO = os.path.join(ROOT, "oracle", "libmazetd_oracle.so")
 REF_SO = os.path.join(ROOT, "oracle", "_ref", "libmazetd_ref.so")
+ADAPTER_SO = os.path.join(ROOT, "oracle", "_ref", "libmazetd_adapter.so")
 
 M = 0xFFFFFFFF
 KAT_SEED = (1346519564496, 42245614964156)  # externals/cage/sources/test-core/random.cpp:47
@@ -34,6 +35,10 @@ def ptr(a, t):
 
 def build_oracle():
     subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "oracle"])
+
+
+def build_adapter():
+    subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "adapter"])
 
 
 def build_ref():
@@ -243,8 +248,10 @@ class Ref:
     def available():
         return os.path.exists(REF_SO)
 
-    def __init__(self):
-        L = self.L = C.CDLL(REF_SO)
+    def __init__(self, path=None):
+        """path: another library exporting the same ref_* entry layer -- oracle/_ref/libmazetd_adapter.so is the product's
+        host adapter (mazetd_b200/host) linked under it instead of the reference's paths.cpp / grid.cpp"""
+        L = self.L = C.CDLL(path or REF_SO)
         L.ref_rng_next.restype = C.c_uint64
         L.ref_rng_chance.restype = C.c_float
         L.ref_rng_range_u32.restype = C.c_uint32

@@ -617,3 +617,42 @@ def test_directions_layers_dev_matches_oracle_per_layer(ctx, oracle):
         to, do = oracle.directions_update(W, H, elev, flags, targets[l:l + 1])
         assert np.array_equal(dd[l].cpu().numpy().view(np.uint32), do), f"layer {l}: " + diff_report(dd[l].cpu().numpy().view(np.uint32), do, W)
         assert np.array_equal(dt[l].cpu().numpy().view(np.uint32), to)
+
+
+# ---------------------------------------------------------------------------------------------------
+# M5-M7 without the noise: newGrid stages on caller-supplied elevations (pinned by the compiled reference's integer code)
+# ---------------------------------------------------------------------------------------------------
+def test_grid_from_elevations_synthetic_and_golden(ctx, oracle):
+    rng = np.random.default_rng(12)
+    W = H = 101
+    maps = []
+    # smooth random terrains (sum of a few sinusoids) so slopes straddle the 89 threshold and several components appear
+    yy, xx = np.mgrid[0:H, 0:W].astype(np.float64)
+    for k in range(6):
+        z = np.zeros((H, W))
+        for _ in range(5):
+            fx, fy, ph, amp = rng.uniform(0.02, 0.35), rng.uniform(0.02, 0.35), rng.uniform(0, 6.28), rng.uniform(100, 900)
+            z += amp * np.sin(fx * xx + fy * yy + ph)
+        maps.append(np.clip(z - 300 * k, -25500, 25500).astype(np.int16).reshape(-1))
+    maps.append(rng.integers(-3000, 3000, W * H).astype(np.int16))  # white noise: nearly everything Invalid
+    maps.append(np.zeros(W * H, np.int16))                          # flat: one disc-shaped component
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "mapgen_k0_k7.npz"))
+    if "elev" in g.files:
+        maps.extend(list(np.asarray(g["elev"]).reshape(-1, W * H)[:2]))
+    elev = np.stack(maps)
+    got = ctx.grid_from_elevations(elev)
+    for k in range(len(maps)):
+        want = oracle.grid_stages(W, H, 50, 50, 45, elev[k])
+        assert np.array_equal(got[k], want), f"map {k}: " + diff_report(got[k], want, W)
+
+
+def test_grid_from_elevations_ragged_size_and_ties(ctx, oracle):
+    """non-square grid, radius test disabled, two equal-sized components: the first discovered (lowest index) wins"""
+    W, H = 37, 23
+    elev = np.zeros(W * H, np.int16).reshape(H, W)
+    elev[:, 18] = 5000  # a wall of slope splits the grid into two 18-column halves (columns 17..19 become Invalid)
+    got = ctx.grid_from_elevations(elev.reshape(1, -1), W=W, H=H, ox=0, oy=0, radius=-1)[0]
+    want = oracle.grid_stages(W, H, 0, 0, -1, elev.reshape(-1))
+    assert np.array_equal(got, want), diff_report(got, want, W)
+    valid = (got & synth.FLAG_INVALID) == 0
+    assert valid.reshape(H, W)[:, :17].all() and not valid.reshape(H, W)[:, 19:].any()
