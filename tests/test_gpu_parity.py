@@ -656,3 +656,51 @@ def test_grid_from_elevations_ragged_size_and_ties(ctx, oracle):
     assert np.array_equal(got, want), diff_report(got, want, W)
     valid = (got & synth.FLAG_INVALID) == 0
     assert valid.reshape(H, W)[:, :17].all() and not valid.reshape(H, W)[:, 19:].any()
+
+
+# ---------------------------------------------------------------------------------------------------
+# C3 at reduced size: scripted tower place/remove events with monsters steering along the flow field, every piece of
+# state compared with the oracle after the script
+# ---------------------------------------------------------------------------------------------------
+class _OracleGame:
+    def __init__(self, oracle, W, H, elev, flags, wp, monsters):
+        self.o, self.W, self.H, self.elev, self.wp, self.a = oracle, W, H, elev, wp, monsters
+        self.flags = np.array(flags, np.uint16)
+        self.rebuild()
+
+    def trial_blocks(self, tile):
+        return bool(self.o.placing_blocks(self.W, self.H, self.elev, self.flags, self.wp, int(tile), self.a["tile"], self.a["alive"], 50, 50))
+
+    def set_flags(self, tile, value):
+        pass  # self.flags is the grid
+
+    def rebuild(self):
+        self.w = self.o.waypoints_update(self.W, self.H, self.elev, self.flags, self.wp, 50, 50)
+        self.view = self.o.waypoints_view(self.W, self.H, self.elev, self.flags, self.wp, self.w["tiles"], self.w["dist"], 50, 50)
+
+    def tick(self, t):
+        self.o.monsters_tick(self.view, t, self.a)
+
+
+def test_scripted_place_remove_events_with_monsters(ctx, oracle):
+    from mazetd_b200 import game_events
+
+    o = oracle.mapgen(KAT_SEED[0], KAT_SEED[1])
+    W = H = 101
+    ctx.grid_upload(W, H, o["elev"], o["flags"], 50, 50)
+    ctx.waypoints_update_dev(o["wp_tiles"])
+    sp = int(o["agg"][2])
+    mon = game_events.initial_monsters(3000, o["fullpath"][sp][: int(o["fullpath_len"][sp])], o["wp_tiles"], ctx.waypoints_find)
+    og = _OracleGame(oracle, W, H, o["elev"], o["flags"], o["wp_tiles"], {k: v.copy() for k, v in mon.items()})
+    gg = game_events.GpuGame(ctx, W, H, o["elev"], o["flags"], o["wp_tiles"])
+    ctx.monsters_upload(mon)
+    sg = game_events.run_events(gg, 400)
+    so = game_events.run_events(og, 400)
+    assert sg == so and sg["placed"] > 20 and sg["cleared"] >= 1, (sg, so)
+    assert np.array_equal(gg.flags, og.flags)
+    got = ctx.monsters_download()
+    for k in got:
+        assert np.array_equal(got[k], og.a[k]), k
+    w = ctx.waypoints_update(o["wp_tiles"], cap=2048)  # same grid state -> same layers as the oracle's last rebuild
+    for key in ("dist", "tiles", "full_distance", "agg"):
+        assert np.array_equal(w[key], og.w[key]), key
