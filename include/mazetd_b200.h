@@ -127,6 +127,12 @@ int mtd_stripe_begin_dev(mtd_ctx *ctx, const uint32_t *sources /* host */, int32
  * *improved_out = halo cells whose label dropped (0 on every rank = converged). Synchronous. */
 int mtd_stripe_exchange_dev(mtd_ctx *ctx, const uint32_t *d_row_above, const uint32_t *d_row_below, uint32_t *improved_out);
 int mtd_stripe_finalize_dev(mtd_ctx *ctx, uint32_t *d_tiles);
+/* rounds > 0: begin / exchange stop after that many relaxation rounds even if tiles are still queued (0 = run to local
+ * convergence). mtd_stripe_pending reports the queued (layer, tile) items; the protocol then ends when the sum of
+ * `improved` AND of `pending` over all ranks is 0. Swapping rows more often keeps a stripe from flooding itself with labels
+ * that the neighbour stripe is about to undercut. */
+int mtd_stripe_round_budget(mtd_ctx *ctx, int32_t rounds);
+int mtd_stripe_pending(mtd_ctx *ctx, uint32_t *items_out);
 
 /* ---- Waypoints::update (sources/map/paths.cpp:82-139) ------------------------------------------ */
 /* n Dijkstra layers + n full-path walks + aggregates, one call.

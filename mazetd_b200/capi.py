@@ -8,7 +8,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libmazetd_b200.so")
+LIB_PATH = os.environ.get("MTD_LIB") or os.path.join(HERE, "libmazetd_b200.so")  # MTD_LIB: developer probe builds only
 
 M = 0xFFFFFFFF
 
@@ -17,7 +17,7 @@ EXPORTS = [
     "mtd_profile_enable", "mtd_profile_read", "mtd_debug_set",
     "mtd_grid_upload", "mtd_grid_upload_dev", "mtd_grid_set_flags", "mtd_neighbor_distances", "mtd_edge_weights",
     "mtd_directions_update", "mtd_directions_update_dev", "mtd_directions_layers_dev",
-    "mtd_stripe_upload", "mtd_stripe_upload_dev", "mtd_stripe_begin_dev", "mtd_stripe_exchange_dev", "mtd_stripe_finalize_dev",
+    "mtd_stripe_upload", "mtd_stripe_upload_dev", "mtd_stripe_begin_dev", "mtd_stripe_exchange_dev", "mtd_stripe_finalize_dev", "mtd_stripe_round_budget", "mtd_stripe_pending",
     "mtd_waypoints_update", "mtd_waypoints_update_dev", "mtd_waypoints_find", "mtd_waypoints_layers_dev",
     "mtd_placing_blocks",
     "mtd_mapgen_batch", "mtd_mapgen_batch_dev", "mtd_grid_from_elevations", "mtd_elevation_samples",
@@ -72,6 +72,8 @@ def load():
     L.mtd_stripe_begin_dev.argtypes = [vp, vp, i32, vp]
     L.mtd_stripe_exchange_dev.argtypes = [vp, vp, vp, C.POINTER(u32)]
     L.mtd_stripe_finalize_dev.argtypes = [vp, vp]
+    L.mtd_stripe_round_budget.argtypes = [vp, i32]
+    L.mtd_stripe_pending.argtypes = [vp, C.POINTER(u32)]
     L.mtd_waypoints_update.argtypes = [vp, vp, i32, vp, vp, vp, u32, vp, vp, vp]
     L.mtd_waypoints_update_dev.argtypes = [vp, vp, i32]
     L.mtd_waypoints_find.argtypes = [vp, vp, vp, i32, vp, vp]
@@ -223,6 +225,14 @@ class Context:
         halo cells whose label dropped"""
         n = C.c_uint32(0)
         self._ck(self.L.mtd_stripe_exchange_dev(self.h, _p(d_row_above), _p(d_row_below), C.byref(n)))
+        return int(n.value)
+
+    def stripe_round_budget(self, rounds):
+        self._ck(self.L.mtd_stripe_round_budget(self.h, int(rounds)))
+
+    def stripe_pending(self):
+        n = C.c_uint32(0)
+        self._ck(self.L.mtd_stripe_pending(self.h, C.byref(n)))
         return int(n.value)
 
     def stripe_finalize_dev(self, d_tiles):

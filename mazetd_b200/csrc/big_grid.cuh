@@ -151,7 +151,7 @@ namespace mtd
 		static constexpr int QCAP = 2048;
 		uint32_t d[CELLS];        // labels
 		uint32_t w[CELLS];        // packed edge weights of the same cells
-		uint32_t edge_old[4][TS]; // top, bottom, left, right interior lines as loaded
+		uint32_t apron_old[4][TS]; // top, bottom, left, right apron labels as loaded (the neighbour tiles' border cells)
 		uint16_t q[2][QCAP];      // pending cells (frame word index), double buffered
 		uint32_t tail[3], newmin[3]; // queue length / smallest pending label, rotating slots (see the engine)
 		uint32_t flags;           // bit 1: sweep changed something; bits 2..5: border line improved (top, bottom, left, right)
@@ -310,14 +310,6 @@ namespace mtd
 			cp_async_wait_all();
 			__syncthreads();
 			MTD_BTICK(0);
-			// remember the interior border lines to detect changes
-			for (int i = tid; i < TS; i += NT)
-			{
-				S.edge_old[0][i] = S.d[1 * PITCH + 4 + i];
-				S.edge_old[1][i] = S.d[TS * PITCH + 4 + i];
-				S.edge_old[2][i] = S.d[(1 + i) * PITCH + 4];
-				S.edge_old[3][i] = S.d[(1 + i) * PITCH + 3 + TS];
-			}
 
 			// ---- seeds ----
 			// Pending cells enter q[0]. A label lowered here or later is appended every time it improves (duplicates are
@@ -382,6 +374,7 @@ namespace mtd
 					wsel = S.w[v] & 0xFFFFu;
 				}
 				const uint32_t da = S.d[a];
+				S.apron_old[side][i] = da; // what the neighbour tile holds there now: decides at the end whether it needs a visit
 				relax_into(da != 0u && da != MTD_INF, v, da + MIN_EDGE + wsel);
 			}
 			for (int s0 = warp * 32; s0 < P.nsrc; s0 += NT)
@@ -444,7 +437,13 @@ namespace mtd
 					const int rx = (int)(src % (uint32_t)W) - gx0, ry = (int)(src / (uint32_t)W) - P.y0 - ly0;
 					want = rx >= 1 && rx <= TS && ry >= 1 && ry <= TS;
 					if (want)
+					{
 						c = (uint32_t)(ry * PITCH + rx + 3);
+						// a source on a border line reaches into the neighbour tile: that tile finds it through the source list
+						const uint32_t sides = (ry == 1 ? 4u : 0u) | (ry == TS ? 8u : 0u) | (rx == 1 ? 16u : 0u) | (rx == TS ? 32u : 0u);
+						if (sides)
+							atomicOr(&S.flags, sides);
+					}
 				}
 				relax_into(want, c - PITCH, MIN_EDGE + (S.w[c - PITCH] >> 16));
 				relax_into(want, c - 1u, MIN_EDGE + (S.w[c - 1u] & 0xFFFFu));
@@ -636,15 +635,21 @@ namespace mtd
 			MTD_BTICK(3);
 			// ---- activate neighbours across improved border lines ----
 			{
+				// A neighbour tile needs a visit only if one of our border cells now offers its adjacent cell a smaller label
+				// than that cell held when we staged it (labels only decrease, so a stale apron only over-activates; a parked
+				// or source apron cell holds 0 and can never be improved). Our own parked cells (0) offer nothing.
 				uint32_t ch = 0;
+				auto offers = [&](uint32_t db, uint32_t w, uint32_t ap) -> bool { return db != 0u && db < BIG_SETTLE_LIMIT && db + MIN_EDGE + w < ap; };
 				for (int i = tid; i < TS; i += NT)
 				{
-					ch |= S.d[1 * PITCH + 4 + i] != S.edge_old[0][i] ? 4u : 0u;
-					ch |= (TS < brow && S.d[TS * PITCH + 4 + i] != S.edge_old[1][i]) ? 8u : 0u;
+					const uint32_t ct = (uint32_t)(1 * PITCH + 4 + i), cb = (uint32_t)(TS * PITCH + 4 + i);
+					ch |= offers(S.d[ct], S.w[ct - PITCH] >> 16, S.apron_old[0][i]) ? 4u : 0u;
+					ch |= (TS < brow && offers(S.d[cb], S.w[cb] >> 16, S.apron_old[1][i])) ? 8u : 0u;
 					if (1 + i < brow) // rows below a cut-short tile hold the parked halo / nothing
 					{
-						ch |= S.d[(1 + i) * PITCH + 4] != S.edge_old[2][i] ? 16u : 0u;
-						ch |= S.d[(1 + i) * PITCH + 3 + TS] != S.edge_old[3][i] ? 32u : 0u;
+						const uint32_t cl = (uint32_t)((1 + i) * PITCH + 4), cr = (uint32_t)((1 + i) * PITCH + 3 + TS);
+						ch |= offers(S.d[cl], S.w[cl - 1u] & 0xFFFFu, S.apron_old[2][i]) ? 16u : 0u;
+						ch |= offers(S.d[cr], S.w[cr] & 0xFFFFu, S.apron_old[3][i]) ? 32u : 0u;
 					}
 				}
 				if (ch)

@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <climits>
 #include <mutex>
 #include <new>
 #include <vector>
@@ -96,7 +97,8 @@ struct mtd_ctx
 	uint32_t last_rounds = 0;
 	// row stripe of a larger grid (multi-GPU, one rank per stripe): rows [sy0, sy1) of a W x sH grid are this context's grid
 	bool stripe = false;
-	int sy0 = 0, sy1 = 0, sH = 0, stripe_round = 0, stripe_nsrc = 0;
+	int sy0 = 0, sy1 = 0, sH = 0, stripe_round = 0, stripe_nsrc = 0, stripe_budget = 0;
+	uint32_t stripe_pending = 0;
 	uint32_t *stripe_dist = nullptr;                 // caller-owned [sy1 - sy0][W]
 	DevBuf<uint32_t> halo_up, halo_down, up_wpack;   // local copies of the neighbour stripes' boundary rows; wpack of row sy0-1
 	DevBuf<uint8_t> up_blocked;
@@ -512,19 +514,25 @@ namespace
 		const int ctas_per_sm = (int)(MAX_SMEM / (smem + 1024));
 		const int blocks = ctx->sms * (ctas_per_sm > 0 ? ctas_per_sm : 1);
 		const int limit = ctx->stripe_round + 4 * (ctx->tilesX + ctx->tilesY) * 64 + 100000;
+		// with a round budget the stripe stops early and reports what is still queued: the caller swaps halo rows more often,
+		// so labels that will be overwritten from the other side of the cut are not propagated all the way first
+		int left = ctx->stripe_budget > 0 ? ctx->stripe_budget : INT_MAX;
 		int burst = 4;
 		ProfScope prof(ctx, MTD_K_BIG_RELAX);
 		for (;;)
 		{
-			for (int b = 0; b < burst; b++, ctx->stripe_round++)
+			const int now = burst < left ? burst : left;
+			for (int b = 0; b < now; b++, ctx->stripe_round++)
 			{
 				k_tile_round<BIG_TS, BIG_WARPS><<<blocks, BIG_WARPS * 32, smem, ctx->stream>>>(P, ctx->stripe_round);
 				LAUNCHED();
 				k_round_advance<<<1, 1, 0, ctx->stream>>>(P, ctx->stripe_round, d_next);
 				LAUNCHED();
 			}
+			left -= now;
 			CU(cudaStreamSynchronize(ctx->stream));
-			if (ctx->hflags->next_count == 0)
+			ctx->stripe_pending = ctx->hflags->next_count;
+			if (ctx->stripe_pending == 0 || left == 0)
 				break;
 			if (burst < 32)
 				burst *= 2;
@@ -1019,6 +1027,7 @@ extern "C" int mtd_stripe_begin_dev(mtd_ctx *ctx, const uint32_t *sources, int32
 	ctx->stripe_dist = d_dist;
 	ctx->stripe_nsrc = nsrc;
 	ctx->stripe_round = 0;
+	ctx->stripe_pending = 0;
 	{
 		ProfScope prof(ctx, MTD_K_BIG_PREPARE);
 		k_big_init<<<grid_blocks(ctx, ctx->T, 256), 256, 0, ctx->stream>>>(d_dist, ctx->T, 1, ctx->T, ctx->blocked.p);
@@ -1059,9 +1068,27 @@ extern "C" int mtd_stripe_exchange_dev(mtd_ctx *ctx, const uint32_t *d_row_above
 	const uint32_t improved = ctx->hflags->stripe_improved;
 	if (improved_out)
 		*improved_out = improved;
-	if (improved == 0)
+	if (improved == 0 && ctx->stripe_pending == 0)
 		return MTD_OK;
 	return stripe_run(ctx, P);
+}
+
+extern "C" int mtd_stripe_round_budget(mtd_ctx *ctx, int32_t rounds)
+{
+	if (!ctx || rounds < 0)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	ctx->stripe_budget = rounds;
+	return MTD_OK;
+}
+
+extern "C" int mtd_stripe_pending(mtd_ctx *ctx, uint32_t *items_out)
+{
+	if (!ctx || !items_out)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	*items_out = ctx->stripe ? ctx->stripe_pending : 0u;
+	return MTD_OK;
 }
 
 extern "C" int mtd_stripe_finalize_dev(mtd_ctx *ctx, uint32_t *d_tiles)

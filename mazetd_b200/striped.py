@@ -15,7 +15,7 @@ from . import shard
 class GpuStripe:
     """rows [y0, y1) of a W x H grid on one CUDA device, through the C ABI. torch supplies the buffers and the stream."""
 
-    def __init__(self, device, W, H, y0, y1, elev_rows, flags_rows, sources, stream=None):
+    def __init__(self, device, W, H, y0, y1, elev_rows, flags_rows, sources, stream=None, round_budget=0):
         import torch
 
         from . import capi
@@ -31,6 +31,7 @@ class GpuStripe:
         else:
             self.ctx.stripe_upload(W, H, y0, y1, elev_rows, flags_rows)
         self.sources = sources
+        self.ctx.stripe_round_budget(round_budget)  # > 0: swap rows every that many relaxation rounds instead of at local convergence
         self.dist = torch.empty((y1 - y0, W), dtype=torch.int32, device=self.dev)  # uint32 bit patterns
         self.tiles = torch.empty((y1 - y0, W), dtype=torch.int32, device=self.dev)
 
@@ -45,8 +46,11 @@ class GpuStripe:
         return self.torch.empty(self.W, dtype=self.torch.int32, device=self.dev)
 
     def exchange(self, row_above, row_below):
+        """merge the neighbours' rows and relax again. Returns how much this call had to do: halo cells improved + tiles
+        that were still queued from the previous (budgeted) call; 0 on every rank = nothing moved anywhere = converged."""
         self.torch.cuda.current_stream(self.dev).synchronize()  # the received rows were written on torch's stream
-        return self.ctx.stripe_exchange_dev(row_above.data_ptr() if row_above is not None else None, row_below.data_ptr() if row_below is not None else None)
+        queued = self.ctx.stripe_pending()
+        return queued + self.ctx.stripe_exchange_dev(row_above.data_ptr() if row_above is not None else None, row_below.data_ptr() if row_below is not None else None)
 
     def finalize(self):
         self.ctx.stripe_finalize_dev(self.tiles.data_ptr())
@@ -103,10 +107,10 @@ def solve_local(solvers):
     return [s.finalize() for s in solvers], sweeps
 
 
-def make_gpu_stripe(device, rank, world, W, H, elev, flags, sources, stream=None):
+def make_gpu_stripe(device, rank, world, W, H, elev, flags, sources, stream=None, round_budget=0):
     """cut rank's stripe (with its halo rows) out of full host arrays elev / flags ([H][W]) and upload it"""
     y0, y1 = shard.stripe_rows(rank, world, H)
     ya, yb = shard.stripe_halo_rows(y0, y1, H)
     e = elev.reshape(H, W)[ya:yb]
     f = flags.reshape(H, W)[ya:yb]
-    return GpuStripe(device, W, H, y0, y1, e, f, sources, stream=stream)
+    return GpuStripe(device, W, H, y0, y1, e, f, sources, stream=stream, round_budget=round_budget)

@@ -531,13 +531,13 @@ def test_directions_against_committed_golden(ctx):
 # ---------------------------------------------------------------------------------------------------
 # row stripes of one large grid: several stripe contexts on one GPU run the multi-GPU protocol
 # ---------------------------------------------------------------------------------------------------
-def _striped_on_one_gpu(W, H, cuts, elev, flags, srcs):
+def _striped_on_one_gpu(W, H, cuts, elev, flags, srcs, round_budget=0):
     from mazetd_b200 import shard, striped
 
     stripes = []
     for y0, y1 in zip(cuts[:-1], cuts[1:]):
         ya, yb = shard.stripe_halo_rows(y0, y1, H)
-        stripes.append(striped.GpuStripe(0, W, H, y0, y1, elev.reshape(H, W)[ya:yb], flags.reshape(H, W)[ya:yb], srcs))
+        stripes.append(striped.GpuStripe(0, W, H, y0, y1, elev.reshape(H, W)[ya:yb], flags.reshape(H, W)[ya:yb], srcs, round_budget=round_budget))
     results, sweeps = striped.solve_local(stripes)
     tiles = np.concatenate([t.cpu().numpy().view(np.uint32).reshape(-1) for t, _ in results])
     d = np.concatenate([x.cpu().numpy().view(np.uint32).reshape(-1) for _, x in results])
@@ -562,6 +562,18 @@ def test_stripes_bit_exact_with_whole_grid(oracle, W, H, cuts, nsrc, pct):
     assert np.array_equal(d, do), diff_report(d, do, W)
     assert np.array_equal(tiles, to), diff_report(tiles, to, W)
     assert sweeps >= 1 and launches > 0
+
+
+@pytest.mark.parametrize("budget", [1, 3])
+def test_stripes_with_a_round_budget_swap_rows_before_local_convergence(oracle, budget):
+    W, H = 512, 512
+    elev, flags = synth.random_grid(W, H, seed_k=21, wall_pct=30)
+    srcs = synth.pick_open_tiles(flags, 3, 8)
+    tiles, d, sweeps, _ = _striped_on_one_gpu(W, H, [0, 128, 256, 512], elev, flags, srcs, round_budget=budget)
+    to, do = oracle.directions_update(W, H, elev, flags, srcs)
+    assert np.array_equal(d, do), diff_report(d, do, W)
+    assert np.array_equal(tiles, to), diff_report(tiles, to, W)
+    assert sweeps > 4
 
 
 def test_stripes_maze_crosses_the_cut_many_times(oracle):

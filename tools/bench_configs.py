@@ -33,6 +33,7 @@ def main():
     cfg = sys.argv[1] if len(sys.argv) > 1 else "C4"
     size = int(sys.argv[2]) if len(sys.argv) > 2 else (16384 if cfg == "C4" else 4096)
     reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
+    budget = int(sys.argv[4]) if len(sys.argv) > 4 else 8  # C4: relaxation rounds between halo swaps (0 = local convergence)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -62,12 +63,12 @@ def main():
         return float(t.item()), out
 
     if cfg == "C4":
-        st = striped.make_gpu_stripe(local, rank, world, W, H, elev, flags, srcs, stream=stream.cuda_stream)
+        st = striped.make_gpu_stripe(local, rank, world, W, H, elev, flags, srcs, stream=stream.cuda_stream, round_budget=budget if world > 1 else 0)
         del elev, flags
         for rep in range(reps):
             l0 = st.ctx.launches
             ms, (tiles, d, sweeps) = timed(lambda: striped.solve_distributed(st, rank, world))
-            line = dict(config="C4", grid=[W, H], sources=nsrc, n_gpus=world, rep=rep, ms=ms, sweeps=sweeps,
+            line = dict(config="C4", grid=[W, H], sources=nsrc, n_gpus=world, rep=rep, ms=ms, sweeps=sweeps, round_budget=budget,
                         tile_relaxations_per_s=W * H / (ms * 1e-3), algorithmic_GBps=W * H * 12 / (ms * 1e-3) / 1e9,
                         launches_rank0=st.ctx.launches - l0, dist_checksum=checksum(d, world), tiles_checksum=checksum(tiles, world))
             if rank == 0:
