@@ -78,7 +78,8 @@ enum
 {
 	MTD_DEBUG_QSEG_CAP = 1,    /* > 0 caps the per-warp frontier queue segment of the one-CTA path: small values force the queue-less dense rounds */
 	MTD_DEBUG_GROUP_WARPS = 2, /* warps cooperating on one distance layer in the one-CTA path: 1, 2 or 4 */
-	MTD_DEBUG_WALKER = 3       /* who walks the full paths in the one-CTA path: 0 auto (walker warp when a CTA owns several maps), 1 workers, 2 walker warp */
+	MTD_DEBUG_WALKER = 3,      /* who walks the full paths in the one-CTA path: 0 auto (walker warp when a CTA owns several maps), 1 workers, 2 walker warp */
+	MTD_DEBUG_TILE_DELTA = 4   /* large grids: width (label units) of the window of tile offers visited per round; 2^32-1 = visit everything (no priority). Performance only: any value gives the same result */
 };
 int mtd_debug_set(mtd_ctx *ctx, int key, int64_t value);
 

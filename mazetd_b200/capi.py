@@ -130,6 +130,7 @@ class Context:
     DEBUG_QSEG_CAP = 1
     DEBUG_GROUP_WARPS = 2
     DEBUG_WALKER = 3
+    DEBUG_TILE_DELTA = 4
 
     def debug_set(self, key, value):
         self._ck(self.L.mtd_debug_set(self.h, int(key), int(value)))

@@ -27,8 +27,8 @@ using namespace mtd;
 namespace
 {
 	constexpr size_t MAX_SMEM = 227 * 1024 - 1024; // dynamic budget: the opt-in limit is 227 KB per CTA including static __shared__
-	constexpr int BIG_TS = 64;
-	constexpr int BIG_WARPS = 4; // warps of the CTA that owns one (layer, tile) work item
+	constexpr int BIG_TS = 32;   // tile side of the large-grid path = warp width (tile_warp.cuh)
+	constexpr int BIG_WARPS = 4; // warps per CTA, each working on its own (layer, tile) item
 
 	template<class T>
 	struct DevBuf
@@ -60,7 +60,8 @@ namespace
 	struct HostFlags
 	{
 		int status;            // OR of ST_* bits written by kernels (copied back on demand)
-		uint32_t next_count;   // work-list size published by k_round_advance
+		uint32_t next_count;   // (unused)
+		uint32_t round_out[2]; // written by k_tile_rounds: items queued for the next round, index of the next round
 		int trial_blocked;
 		uint32_t alive;
 		unsigned long long damage;
@@ -91,10 +92,11 @@ struct mtd_ctx
 	// big path derived data
 	DevBuf<uint32_t> wpack;
 	DevBuf<uint8_t> blocked;
-	DevBuf<uint32_t> list0, list1, stamp, counters; // counters: count[2], cursor, total_active
+	DevBuf<uint32_t> list0, list1, list2, stamp, tilekey, counters; // counters: count[3], cursor[3], total_active, improved
 	DevBuf<uint32_t> sources;
 	int tilesX = 0, tilesY = 0;
 	uint32_t last_rounds = 0;
+	uint32_t tile_delta = 98304; // visit window of the tile-level priority (label units); swept 8k..inf on 4096^2 and 16384^2 (weights 255..570): flat optimum 64k..256k
 	// row stripe of a larger grid (multi-GPU, one rank per stripe): rows [sy0, sy1) of a W x sH grid are this context's grid
 	bool stripe = false;
 	int sy0 = 0, sy1 = 0, sH = 0, stripe_round = 0, stripe_nsrc = 0, stripe_budget = 0;
@@ -346,10 +348,44 @@ namespace
 		CU(ctx->blocked.reserve(ctx->T));
 		ctx->tilesX = (ctx->W + BIG_TS - 1) / BIG_TS;
 		ctx->tilesY = (ctx->H + BIG_TS - 1) / BIG_TS;
-		CU(ctx->counters.reserve(8));
+		CU(ctx->counters.reserve(16));
 		ProfScope prof(ctx, MTD_K_BIG_PREPARE);
 		k_edge_weights<<<grid_blocks(ctx, ctx->T, 256), 256, 0, ctx->stream>>>(ctx->W, ctx->H, ctx->elev.p, nullptr, ctx->flags.p, ctx->wpack.p, ctx->blocked.p);
 		LAUNCHED();
+		return MTD_OK;
+	}
+
+	// Runs relaxation rounds from `round` until the work-list is empty or `budget` rounds are done (budget <= 0: no limit).
+	// One cooperative launch of the persistent kernel; rounds are separated by grid-wide barriers inside it.
+	int run_rounds(mtd_ctx *ctx, const BigParams &P, int &round, int budget, uint32_t &pending)
+	{
+		using WF = WarpFrame<BIG_TS>;
+		const size_t smem = sizeof(WF) * BIG_WARPS;
+		static int ctas_per_sm = 0;
+		if (!ctas_per_sm)
+		{
+			CU(cudaFuncSetAttribute(k_tile_rounds<BIG_TS, BIG_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+			CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, k_tile_rounds<BIG_TS, BIG_WARPS>, BIG_WARPS * 32, smem));
+			if (ctas_per_sm < 1)
+				return fail(ctx, MTD_ERR_CUDA, "the tile relaxation kernel does not fit an SM");
+		}
+		const int limit = 4 * (ctx->tilesX + ctx->tilesY) * BIG_TS + 100000; // far above any wavefront depth: a safety net, not a tuning knob
+		int max_rounds = budget > 0 ? budget : limit;
+		uint32_t *d_out = nullptr;
+		CU(cudaHostGetDevicePointer((void **)&d_out, ctx->hflags->round_out, 0));
+		BigParams Pk = P;
+		int round0 = round;
+		void *args[] = { (void *)&Pk, (void *)&round0, (void *)&max_rounds, (void *)&d_out };
+		{
+			ProfScope prof(ctx, MTD_K_BIG_RELAX);
+			CU(cudaLaunchCooperativeKernel((const void *)k_tile_rounds<BIG_TS, BIG_WARPS>, dim3((unsigned)(ctx->sms * ctas_per_sm)), dim3(BIG_WARPS * 32), args, smem, ctx->stream));
+			LAUNCHED();
+		}
+		CU(cudaStreamSynchronize(ctx->stream));
+		pending = ctx->hflags->round_out[0];
+		round = (int)ctx->hflags->round_out[1];
+		if (budget <= 0 && pending != 0)
+			return fail(ctx, MTD_ERR_CUDA, "tile relaxation did not converge after %d rounds", round);
 		return MTD_OK;
 	}
 
@@ -357,25 +393,21 @@ namespace
 	// one (layer, tile) pair. d_dist / d_tiles = [nlayers][T] (d_tiles may be null).
 	int big_layers(mtd_ctx *ctx, const uint32_t *h_sources, int nlayers, int nsrc, uint32_t extra_blocked, uint32_t *d_tiles, uint32_t *d_dist)
 	{
-		using TSm = TileSmem<BIG_TS>;
-		const size_t smem = sizeof(TSm);
-		static bool configured = false;
-		if (!configured)
-		{
-			CU(cudaFuncSetAttribute(k_tile_round<BIG_TS, BIG_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-			configured = true;
-		}
 		const size_t nt = (size_t)ctx->tilesX * ctx->tilesY;
 		const size_t nitems = nt * (size_t)nlayers;
 		if (nitems >= 0xFFFFFFFFull)
 			return fail(ctx, MTD_ERR_CAPACITY, "too many (layer, tile) work items");
 		CU(ctx->list0.reserve(nitems));
 		CU(ctx->list1.reserve(nitems));
+		CU(ctx->list2.reserve(nitems));
 		CU(ctx->stamp.reserve(nitems));
+		CU(ctx->tilekey.reserve(nitems));
 		CU(ctx->sources.reserve((size_t)nlayers * nsrc));
 		CU(cudaMemcpyAsync(ctx->sources.p, h_sources, (size_t)nlayers * nsrc * 4, cudaMemcpyHostToDevice, ctx->stream));
 		CU(cudaMemsetAsync(ctx->stamp.p, 0, nitems * 4, ctx->stream));
-		CU(cudaMemsetAsync(ctx->counters.p, 0, 8 * 4, ctx->stream));
+		CU(cudaMemsetAsync(ctx->tilekey.p, 0xFF, nitems * 4, ctx->stream));
+		CU(cudaMemsetAsync(ctx->counters.p, 0, 16 * 4, ctx->stream));
+		CU(cudaMemsetAsync(ctx->counters.p + 8, 0xFF, 3 * 4, ctx->stream)); // minkey[3] = m
 		uint8_t prev_blocked = 0;
 		if (extra_blocked != MTD_M)
 		{
@@ -408,41 +440,26 @@ namespace
 		P.sources = ctx->sources.p;
 		P.list[0] = ctx->list0.p;
 		P.list[1] = ctx->list1.p;
+		P.list[2] = ctx->list2.p;
 		P.count = ctx->counters.p;
-		P.cursor = ctx->counters.p + 2;
-		P.total_active = ctx->counters.p + 3;
+		P.cursor = ctx->counters.p + 3;
+		P.total_active = ctx->counters.p + 6;
 		P.stamp = ctx->stamp.p;
+		P.key = ctx->tilekey.p;
+		P.minkey = ctx->counters.p + 8;
+		P.tile_delta = ctx->tile_delta;
 		P.status = ctx->d_status.p;
 		P.aligned16 = (ctx->W % 4 == 0) && ((uintptr_t)d_dist % 16 == 0) && ((uintptr_t)ctx->wpack.p % 16 == 0) ? 1 : 0;
 
 		k_big_seed<BIG_TS><<<(nlayers * nsrc + 127) / 128, 128, 0, ctx->stream>>>(P);
 		LAUNCHED();
 
-		uint32_t *d_next = nullptr;
-		CU(cudaHostGetDevicePointer((void **)&d_next, &ctx->hflags->next_count, 0));
-		const int ctas_per_sm = (int)(MAX_SMEM / (smem + 1024));
-		const int blocks = ctx->sms * (ctas_per_sm > 0 ? ctas_per_sm : 1);
 		int round = 0;
-		int burst = 4;
+		uint32_t pending = 0;
 		{
-			ProfScope prof(ctx, MTD_K_BIG_RELAX);
-			for (;;)
-			{
-				for (int b = 0; b < burst; b++, round++)
-				{
-					k_tile_round<BIG_TS, BIG_WARPS><<<blocks, BIG_WARPS * 32, smem, ctx->stream>>>(P, round);
-					LAUNCHED();
-					k_round_advance<<<1, 1, 0, ctx->stream>>>(P, round, d_next);
-					LAUNCHED();
-				}
-				CU(cudaStreamSynchronize(ctx->stream));
-				if (ctx->hflags->next_count == 0)
-					break;
-				if (burst < 32)
-					burst *= 2;
-				if (round > 4 * (ctx->tilesX + ctx->tilesY) * 64 + 100000)
-					return fail(ctx, MTD_ERR_CUDA, "tile relaxation did not converge after %d rounds", round);
-			}
+			const int rc = run_rounds(ctx, P, round, 0, pending);
+			if (rc)
+				return rc;
 		}
 		ctx->last_rounds = (uint32_t)round;
 		CU(cudaMemcpyAsync(&ctx->hflags->big_items, P.total_active, 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -491,10 +508,14 @@ namespace
 		P.sources = ctx->sources.p;
 		P.list[0] = ctx->list0.p;
 		P.list[1] = ctx->list1.p;
+		P.list[2] = ctx->list2.p;
 		P.count = ctx->counters.p;
-		P.cursor = ctx->counters.p + 2;
-		P.total_active = ctx->counters.p + 3;
+		P.cursor = ctx->counters.p + 3;
+		P.total_active = ctx->counters.p + 6;
 		P.stamp = ctx->stamp.p;
+		P.key = ctx->tilekey.p;
+		P.minkey = ctx->counters.p + 8;
+		P.tile_delta = ctx->tile_delta;
 		P.status = ctx->d_status.p;
 		P.aligned16 = (ctx->W % 4 == 0) && ((uintptr_t)ctx->stripe_dist % 16 == 0) && ((uintptr_t)ctx->wpack.p % 16 == 0) && ((uintptr_t)ctx->halo_up.p % 16 == 0) && ((uintptr_t)ctx->halo_down.p % 16 == 0) && ((uintptr_t)ctx->up_wpack.p % 16 == 0) ? 1 : 0;
 		P.up_row = ctx->sy0 > 0 ? ctx->halo_up.p : nullptr;
@@ -506,39 +527,11 @@ namespace
 	// relax the stripe until its work-list is empty (the halo copies are constant meanwhile)
 	int stripe_run(mtd_ctx *ctx, const BigParams &P)
 	{
-		using TSm = TileSmem<BIG_TS>;
-		const size_t smem = sizeof(TSm);
-		CU(cudaFuncSetAttribute(k_tile_round<BIG_TS, BIG_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-		uint32_t *d_next = nullptr;
-		CU(cudaHostGetDevicePointer((void **)&d_next, &ctx->hflags->next_count, 0));
-		const int ctas_per_sm = (int)(MAX_SMEM / (smem + 1024));
-		const int blocks = ctx->sms * (ctas_per_sm > 0 ? ctas_per_sm : 1);
-		const int limit = ctx->stripe_round + 4 * (ctx->tilesX + ctx->tilesY) * 64 + 100000;
 		// with a round budget the stripe stops early and reports what is still queued: the caller swaps halo rows more often,
 		// so labels that will be overwritten from the other side of the cut are not propagated all the way first
-		int left = ctx->stripe_budget > 0 ? ctx->stripe_budget : INT_MAX;
-		int burst = 4;
-		ProfScope prof(ctx, MTD_K_BIG_RELAX);
-		for (;;)
-		{
-			const int now = burst < left ? burst : left;
-			for (int b = 0; b < now; b++, ctx->stripe_round++)
-			{
-				k_tile_round<BIG_TS, BIG_WARPS><<<blocks, BIG_WARPS * 32, smem, ctx->stream>>>(P, ctx->stripe_round);
-				LAUNCHED();
-				k_round_advance<<<1, 1, 0, ctx->stream>>>(P, ctx->stripe_round, d_next);
-				LAUNCHED();
-			}
-			left -= now;
-			CU(cudaStreamSynchronize(ctx->stream));
-			ctx->stripe_pending = ctx->hflags->next_count;
-			if (ctx->stripe_pending == 0 || left == 0)
-				break;
-			if (burst < 32)
-				burst *= 2;
-			if (ctx->stripe_round > limit)
-				return fail(ctx, MTD_ERR_CUDA, "stripe relaxation did not converge");
-		}
+		const int rc = run_rounds(ctx, P, ctx->stripe_round, ctx->stripe_budget, ctx->stripe_pending);
+		if (rc)
+			return rc;
 		ctx->last_rounds = (uint32_t)ctx->stripe_round;
 		return MTD_OK;
 	}
@@ -827,6 +820,11 @@ extern "C" int mtd_debug_set(mtd_ctx *ctx, int key, int64_t value)
 	case MTD_DEBUG_WALKER:
 		ctx->debug_walker = (int)value;
 		return MTD_OK;
+	case MTD_DEBUG_TILE_DELTA:
+		if (value < 1 || value > 0xFFFFFFFFll)
+			return fail(ctx, MTD_ERR_ARG, "tile delta must be in 1 .. 2^32-1");
+		ctx->tile_delta = (uint32_t)value;
+		return MTD_OK;
 	default:
 		return fail(ctx, MTD_ERR_ARG, "unknown debug key %d", key);
 	}
@@ -962,7 +960,7 @@ static int stripe_common(mtd_ctx *ctx, int32_t W, int32_t H, int32_t y0, int32_t
 	CU(ctx->halo_down.reserve(W));
 	CU(ctx->up_wpack.reserve(W));
 	CU(ctx->up_blocked.reserve(W));
-	CU(ctx->counters.reserve(8));
+	CU(ctx->counters.reserve(16));
 	ctx->tilesX = (W + BIG_TS - 1) / BIG_TS;
 	ctx->tilesY = (Hl + BIG_TS - 1) / BIG_TS;
 	const int16_t *own_e = ctx->elev.p + (size_t)above * W;
@@ -1017,11 +1015,15 @@ extern "C" int mtd_stripe_begin_dev(mtd_ctx *ctx, const uint32_t *sources, int32
 	const size_t nt = (size_t)ctx->tilesX * ctx->tilesY;
 	CU(ctx->list0.reserve(nt));
 	CU(ctx->list1.reserve(nt));
+	CU(ctx->list2.reserve(nt));
 	CU(ctx->stamp.reserve(nt));
+	CU(ctx->tilekey.reserve(nt));
 	CU(ctx->sources.reserve(nsrc));
 	CU(cudaMemcpyAsync(ctx->sources.p, sources, (size_t)nsrc * 4, cudaMemcpyHostToDevice, ctx->stream));
 	CU(cudaMemsetAsync(ctx->stamp.p, 0, nt * 4, ctx->stream));
-	CU(cudaMemsetAsync(ctx->counters.p, 0, 8 * 4, ctx->stream));
+	CU(cudaMemsetAsync(ctx->tilekey.p, 0xFF, nt * 4, ctx->stream));
+	CU(cudaMemsetAsync(ctx->counters.p, 0, 16 * 4, ctx->stream));
+		CU(cudaMemsetAsync(ctx->counters.p + 8, 0xFF, 3 * 4, ctx->stream)); // minkey[3] = m
 	CU(cudaMemsetAsync(ctx->halo_up.p, 0xFF, (size_t)ctx->W * 4, ctx->stream));
 	CU(cudaMemsetAsync(ctx->halo_down.p, 0xFF, (size_t)ctx->W * 4, ctx->stream));
 	ctx->stripe_dist = d_dist;
@@ -1050,7 +1052,7 @@ extern "C" int mtd_stripe_exchange_dev(mtd_ctx *ctx, const uint32_t *d_row_above
 	if (!ctx->have_grid || !ctx->stripe || !ctx->stripe_dist)
 		return fail(ctx, MTD_ERR_STATE, "stripe_exchange before stripe_begin");
 	const BigParams P = stripe_params(ctx);
-	uint32_t *d_improved = ctx->counters.p + 4;
+	uint32_t *d_improved = ctx->counters.p + 7;
 	CU(cudaMemsetAsync(d_improved, 0, 4, ctx->stream));
 	const int blocks = (ctx->W + 255) / 256;
 	if (d_row_above && ctx->sy0 > 0)

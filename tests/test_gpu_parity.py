@@ -716,3 +716,24 @@ def test_scripted_place_remove_events_with_monsters(ctx, oracle):
     w = ctx.waypoints_update(o["wp_tiles"], cap=2048)  # same grid state -> same layers as the oracle's last rebuild
     for key in ("dist", "tiles", "full_distance", "agg"):
         assert np.array_equal(w[key], og.w[key]), key
+
+
+@pytest.mark.parametrize("delta", [1, 700, 20000, 0xFFFFFFFF])
+def test_tiled_priority_window_never_changes_the_result(oracle, delta):
+    """the tile-level priority (which queued tiles a round visits) is a schedule, not part of the answer"""
+    from mazetd_b200 import capi
+
+    c = capi.Context(0)
+    c.debug_set(c.DEBUG_TILE_DELTA, delta)
+    W, H = 448, 352
+    elev, flags = synth.random_grid(W, H, seed_k=31, wall_pct=33)
+    srcs = synth.pick_open_tiles(flags, 3, 6)
+    c.grid_upload(W, H, elev, flags)
+    t, d = c.directions_update(srcs)
+    to, do = oracle.directions_update(W, H, elev, flags, srcs)
+    assert np.array_equal(d, do), diff_report(d, do, W)
+    assert np.array_equal(t, to), diff_report(t, to, W)
+    w = c.waypoints_update(srcs, cap=64)
+    wo = oracle.waypoints_update(W, H, elev, flags, srcs, cap=64)
+    assert np.array_equal(w["dist"], wo["dist"]) and np.array_equal(w["tiles"], wo["tiles"])
+    c.close()

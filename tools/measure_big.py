@@ -15,6 +15,9 @@ srcs = synth.pick_open_tiles(flags, max(nsrc, layers), 1)
 print("gen", time.time() - t0, flush=True)
 ctx = capi.Context(0)
 ctx.profile_enable(True)
+import os
+if os.environ.get('MTD_TILE_DELTA'):
+    ctx.debug_set(ctx.DEBUG_TILE_DELTA, int(os.environ['MTD_TILE_DELTA']))
 ctx.grid_upload(W, H, elev, flags)
 if layers:
     for it in range(3):
