@@ -57,6 +57,25 @@ namespace
 		}
 	};
 
+	struct MapgenStage
+	{
+		DevBuf<int16_t> elev;
+		DevBuf<uint16_t> flags;
+		DevBuf<uint32_t> wp, tiles, dist, fp, fplen, fdist, agg;
+		void release()
+		{
+			elev.release();
+			flags.release();
+			wp.release();
+			tiles.release();
+			dist.release();
+			fp.release();
+			fplen.release();
+			fdist.release();
+			agg.release();
+		}
+	};
+
 	struct HostFlags
 	{
 		int status;            // OR of ST_* bits written by kernels (copied back on demand)
@@ -104,6 +123,11 @@ struct mtd_ctx
 	uint32_t *stripe_dist = nullptr;                 // caller-owned [sy1 - sy0][W]
 	DevBuf<uint32_t> halo_up, halo_down, up_wpack;   // local copies of the neighbour stripes' boundary rows; wpack of row sy0-1
 	DevBuf<uint8_t> up_blocked;
+
+	// staging of mtd_mapgen_batch (host outputs): two buffer sets, compute overlaps the drain of the previous chunk
+	MapgenStage mg[2];
+	cudaStream_t copy_stream = nullptr;
+	cudaEvent_t mg_done[2] = { nullptr, nullptr }, mg_copied[2] = { nullptr, nullptr };
 
 	// resident layers
 	int nlayers = 0;
@@ -743,6 +767,25 @@ extern "C" void mtd_destroy(mtd_ctx *ctx)
 	ctx->blocked.release();
 	ctx->list0.release();
 	ctx->list1.release();
+	ctx->list2.release();
+	ctx->tilekey.release();
+	ctx->halo_up.release();
+	ctx->halo_down.release();
+	ctx->up_wpack.release();
+	ctx->up_blocked.release();
+	ctx->scratch_elev_in.release();
+	ctx->scratch_elev.release();
+	ctx->scratch_flags.release();
+	for (int b = 0; b < 2; b++)
+	{
+		ctx->mg[b].release();
+		if (ctx->mg_done[b])
+			cudaEventDestroy(ctx->mg_done[b]);
+		if (ctx->mg_copied[b])
+			cudaEventDestroy(ctx->mg_copied[b]);
+	}
+	if (ctx->copy_stream)
+		cudaStreamDestroy(ctx->copy_stream);
 	ctx->stamp.release();
 	ctx->counters.release();
 	ctx->sources.release();
@@ -1451,78 +1494,78 @@ extern "C" int mtd_mapgen_batch(mtd_ctx *ctx, const mtd_mapgen_params *p, uint64
 	const size_t T = (size_t)p->W * p->H;
 	const int n = p->nwp;
 	const size_t cap = fullpath ? p->fullpath_cap : 0;
-	// chunked so the device staging stays bounded (layers are 8 bytes per tile per waypoint)
-	const int chunk = 256;
-	DevBuf<int16_t> d_elev;
-	DevBuf<uint16_t> d_flags;
-	DevBuf<uint32_t> d_wp, d_tiles, d_dist, d_fp, d_fplen, d_fdist, d_agg;
-	int rc = MTD_OK;
-	auto cleanup = [&]()
+	// Chunked so the device staging stays bounded (layers are 8 bytes per tile per waypoint), and double buffered: the
+	// kernels of chunk i + 1 run on the context's stream while chunk i drains to the host on a copy stream. The staging
+	// buffers live in the context (no cudaMalloc / cudaFree per call).
+	const int chunk = ctx->sms * 4;
+	if (!ctx->copy_stream)
 	{
-		d_elev.release();
-		d_flags.release();
-		d_wp.release();
-		d_tiles.release();
-		d_dist.release();
-		d_fp.release();
-		d_fplen.release();
-		d_fdist.release();
-		d_agg.release();
-	};
-#define CUX(call)                                                                                   \
-	do                                                                                              \
-	{                                                                                               \
-		cudaError_t e__ = (call);                                                                   \
-		if (e__ != cudaSuccess)                                                                     \
-		{                                                                                           \
-			cleanup();                                                                              \
-			return fail(ctx, MTD_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e__));        \
-		}                                                                                           \
-	} while (0)
-	CUX(d_elev.reserve(chunk * T));
-	CUX(d_flags.reserve(chunk * T));
-	CUX(d_wp.reserve((size_t)chunk * (n ? n : 1)));
-	if (n)
-	{
-		if (tiles)
-			CUX(d_tiles.reserve((size_t)chunk * n * T));
-		if (dist || n > SMALL_MAX_RESIDENT)
-			CUX(d_dist.reserve((size_t)chunk * n * T));
-		if (cap)
-			CUX(d_fp.reserve((size_t)chunk * n * cap));
-		CUX(d_fplen.reserve((size_t)chunk * n));
-		CUX(d_fdist.reserve((size_t)chunk * n));
-		CUX(d_agg.reserve((size_t)chunk * 3));
+		CU(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+		for (int b = 0; b < 2; b++)
+		{
+			CU(cudaEventCreateWithFlags(&ctx->mg_done[b], cudaEventDisableTiming));
+			CU(cudaEventCreateWithFlags(&ctx->mg_copied[b], cudaEventDisableTiming));
+		}
 	}
-	for (int done = 0; done < nmaps && rc == MTD_OK; done += chunk)
+	for (int b = 0; b < 2; b++)
+	{
+		MapgenStage &S = ctx->mg[b];
+		CU(S.elev.reserve(chunk * T));
+		CU(S.flags.reserve(chunk * T));
+		CU(S.wp.reserve((size_t)chunk * (n ? n : 1)));
+		if (n)
+		{
+			if (tiles)
+				CU(S.tiles.reserve((size_t)chunk * n * T));
+			if (dist || n > SMALL_MAX_RESIDENT)
+				CU(S.dist.reserve((size_t)chunk * n * T));
+			if (cap)
+				CU(S.fp.reserve((size_t)chunk * n * cap));
+			CU(S.fplen.reserve((size_t)chunk * n));
+			CU(S.fdist.reserve((size_t)chunk * n));
+			CU(S.agg.reserve((size_t)chunk * 3));
+		}
+	}
+	int rc = MTD_OK;
+	int i = 0;
+	cudaStream_t cs = ctx->copy_stream;
+	for (int done = 0; done < nmaps && rc == MTD_OK; done += chunk, i++)
 	{
 		const int m = nmaps - done < chunk ? nmaps - done : chunk;
-		rc = mapgen_dev(ctx, p, s1, s2, first + done, m, d_elev.p, d_flags.p, d_wp.p, d_tiles.p, d_dist.p, d_fp.p, d_fplen.p, d_fdist.p, d_agg.p);
+		const int b = i & 1;
+		MapgenStage &S = ctx->mg[b];
+		if (i >= 2)
+			CU(cudaStreamWaitEvent(ctx->stream, ctx->mg_copied[b], 0)); // the buffer has drained
+		rc = mapgen_dev(ctx, p, s1, s2, first + done, m, S.elev.p, S.flags.p, S.wp.p, tiles ? S.tiles.p : nullptr, (dist || n > SMALL_MAX_RESIDENT) ? S.dist.p : nullptr, cap ? S.fp.p : nullptr, S.fplen.p, S.fdist.p, S.agg.p);
 		if (rc)
 			break;
+		CU(cudaEventRecord(ctx->mg_done[b], ctx->stream));
+		CU(cudaStreamWaitEvent(cs, ctx->mg_done[b], 0));
 		if (elev)
-			CUX(cudaMemcpyAsync(elev + (size_t)done * T, d_elev.p, (size_t)m * T * 2, cudaMemcpyDeviceToHost, ctx->stream));
+			CU(cudaMemcpyAsync(elev + (size_t)done * T, S.elev.p, (size_t)m * T * 2, cudaMemcpyDeviceToHost, cs));
 		if (flags)
-			CUX(cudaMemcpyAsync(flags + (size_t)done * T, d_flags.p, (size_t)m * T * 2, cudaMemcpyDeviceToHost, ctx->stream));
+			CU(cudaMemcpyAsync(flags + (size_t)done * T, S.flags.p, (size_t)m * T * 2, cudaMemcpyDeviceToHost, cs));
 		if (wp_tiles && n)
-			CUX(cudaMemcpyAsync(wp_tiles + (size_t)done * n, d_wp.p, (size_t)m * n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+			CU(cudaMemcpyAsync(wp_tiles + (size_t)done * n, S.wp.p, (size_t)m * n * 4, cudaMemcpyDeviceToHost, cs));
 		if (tiles && n)
-			CUX(cudaMemcpyAsync(tiles + (size_t)done * n * T, d_tiles.p, (size_t)m * n * T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+			CU(cudaMemcpyAsync(tiles + (size_t)done * n * T, S.tiles.p, (size_t)m * n * T * 4, cudaMemcpyDeviceToHost, cs));
 		if (dist && n)
-			CUX(cudaMemcpyAsync(dist + (size_t)done * n * T, d_dist.p, (size_t)m * n * T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+			CU(cudaMemcpyAsync(dist + (size_t)done * n * T, S.dist.p, (size_t)m * n * T * 4, cudaMemcpyDeviceToHost, cs));
 		if (fullpath && cap && n)
-			CUX(cudaMemcpyAsync(fullpath + (size_t)done * n * cap, d_fp.p, (size_t)m * n * cap * 4, cudaMemcpyDeviceToHost, ctx->stream));
+			CU(cudaMemcpyAsync(fullpath + (size_t)done * n * cap, S.fp.p, (size_t)m * n * cap * 4, cudaMemcpyDeviceToHost, cs));
 		if (fullpath_len && n)
-			CUX(cudaMemcpyAsync(fullpath_len + (size_t)done * n, d_fplen.p, (size_t)m * n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+			CU(cudaMemcpyAsync(fullpath_len + (size_t)done * n, S.fplen.p, (size_t)m * n * 4, cudaMemcpyDeviceToHost, cs));
 		if (full_distance && n)
-			CUX(cudaMemcpyAsync(full_distance + (size_t)done * n, d_fdist.p, (size_t)m * n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+			CU(cudaMemcpyAsync(full_distance + (size_t)done * n, S.fdist.p, (size_t)m * n * 4, cudaMemcpyDeviceToHost, cs));
 		if (agg && n)
-			CUX(cudaMemcpyAsync(agg + (size_t)done * 3, d_agg.p, (size_t)m * 3 * 4, cudaMemcpyDeviceToHost, ctx->stream));
-		rc = sync_and_status(ctx);
+			CU(cudaMemcpyAsync(agg + (size_t)done * 3, S.agg.p, (size_t)m * 3 * 4, cudaMemcpyDeviceToHost, cs));
+		CU(cudaEventRecord(ctx->mg_copied[b], cs));
 	}
-#undef CUX
-	cleanup();
-	return rc;
+	const cudaError_t ce = cudaStreamSynchronize(cs);
+	const int rs = sync_and_status(ctx);
+	if (rc == MTD_OK && ce != cudaSuccess)
+		return fail(ctx, MTD_ERR_CUDA, "device to host copy failed: %s", cudaGetErrorString(ce));
+	return rc ? rc : rs;
 }
 
 __global__ void k_elevation_samples(uint64_t s1, uint64_t s2, const float *xy, int n, float *out)

@@ -33,7 +33,7 @@ def main():
     cfg = sys.argv[1] if len(sys.argv) > 1 else "C4"
     size = int(sys.argv[2]) if len(sys.argv) > 2 else (16384 if cfg == "C4" else 4096)
     reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
-    budget = int(sys.argv[4]) if len(sys.argv) > 4 else 8  # C4: relaxation rounds between halo swaps (0 = local convergence)
+    budget = int(sys.argv[4]) if len(sys.argv) > 4 else 16  # C4: relaxation rounds between halo swaps (0 = local convergence)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
