@@ -155,6 +155,67 @@ def time_cpu_sample(target_s=12.0):
 
 
 # --------------------------------------------------------------------------------------------------------
+def run_reference_other(args):
+    """CPU reference figures for the configurations that are not the bench headline: C1 = trial +
+    Waypoints::update on the default map after the scripted placement, C5 = 8 Directions::update on a 4096^2 grid.
+    The reference's own compiled code (oracle/_ref) when it travelled, else the oracle port."""
+    import numpy as np
+
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib
+    from mazetd_b200 import game_events, synth
+
+    cores = host_cores()
+    use_ref = oracle_lib.Ref.available()
+    if not use_ref:
+        oracle_lib.build_oracle()
+    eng = oracle_lib.Ref() if use_ref else oracle_lib.Oracle()
+    kind = "reference" if use_ref else "port"
+    if args.workload == "C1":
+        W = H = 101
+        g = eng.mapgen(KAT_SEED[0], KAT_SEED[1])
+        sp = int(g["agg"][2])
+        path = g["fullpath"][sp][: int(g["fullpath_len"][sp])]
+        on_path = np.zeros(W * H, bool)
+        on_path[path] = True
+        cand = int(np.flatnonzero(on_path & ((g["flags"] & game_events.UNBUILDABLE) == 0))[0])
+        f2 = g["flags"].copy()
+        f2[cand] |= synth.FLAG_BUILDING
+        if use_ref:
+            eng.L.ref_set_task_threads(min(4, cores))
+        lat = []
+        h = eng.map_create(W, H, g["elev"], f2, g["wp_tiles"], 50, 50) if use_ref else None
+        for _ in range(max(args.steps, 10) + 3):
+            t0 = time.perf_counter()
+            if use_ref:
+                eng.directions_update(W, H, g["elev"], f2, int(g["wp_tiles"][0]), 50, 50)  # the trial of placingBuildingBlocksMonsters (grid copy + one Dijkstra)
+                eng.L.ref_waypoints_update(h)  # Waypoints::update on the live objects, nothing copied out
+            else:
+                eng.directions_update(W, H, g["elev"], f2, g["wp_tiles"][:1], 50, 50)
+                eng.waypoints_update(W, H, g["elev"], f2, g["wp_tiles"], 50, 50)
+            lat.append(time.perf_counter() - t0)
+        if h:
+            eng.L.ref_map_destroy(h)
+        med = float(np.median(lat[3:]))
+        line = {"impl": "reference", "workload": "C1", "metric": "us per placement (trial Dijkstra + Waypoints::update, 101x101, 4 layers)", "value": med * 1e6, "unit": "us",
+                "higher_is_better": False, "tile_relaxations_per_s": W * H * NWP / med, "cpu_baseline": {"kind": kind, "cores": min(4, cores) if use_ref else 1, "cpu": cpu_model(), "sample": f"median of {len(lat) - 3} placements, candidate tile {cand}"}}
+    else:
+        from concurrent.futures import ThreadPoolExecutor
+
+        W = H = args.size
+        elev, flags = synth.random_grid(W, H, seed_k=1, wall_pct=30, elev_mod=512)
+        srcs = synth.pick_open_tiles(flags, 8, 1)
+        thr = min(8, cores)
+        one = (lambda s: eng.directions_update(W, H, elev, flags, int(s))) if use_ref else (lambda s: eng.directions_update(W, H, elev, flags, np.array([s], np.uint32)))
+        t0 = time.perf_counter()
+        with ThreadPoolExecutor(thr) as ex:
+            list(ex.map(one, srcs))
+        dt = time.perf_counter() - t0
+        line = {"impl": "reference", "workload": "C5", "metric": "tile relaxations/sec (8 Directions::update layers on one grid)", "value": W * H * 8 / dt, "unit": "tile relaxations/s",
+                "higher_is_better": True, "ms": dt * 1e3, "config": {"grid": [W, H], "layers": 8}, "cpu_baseline": {"kind": kind, "cores": thr, "cpu": cpu_model(), "sample": "one run of 8 concurrent heap Dijkstras"}}
+    print(json.dumps(line), flush=True)
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -416,10 +477,15 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--workload", default="C2", choices=["C2", "C1", "C5"], help="reference arm only: CPU figures for the non-headline configurations")
+    ap.add_argument("--size", type=int, default=4096, help="grid side of --workload C5")
     ap.add_argument("--gw", type=int, default=0, help="tuning probe: warps per layer in the one-CTA kernel (1, 2, 4)")
     ap.add_argument("--walker", type=int, default=0, help="tuning probe: 1 = workers walk the paths, 2 = walker warp")
     args = ap.parse_args()
-    if args.impl == "reference":
+    if args.impl == "reference" and args.workload != "C2":
+        if int(os.environ.get("RANK", "0")) == 0:
+            run_reference_other(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         world = int(os.environ.get("WORLD_SIZE", "1"))
