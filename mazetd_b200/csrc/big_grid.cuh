@@ -19,9 +19,9 @@
 // interior neighbour) and then parked at 0 like blocked cells: the four neighbours of an interior cell are p-1, p+1,
 // p-PITCH, p+PITCH with no bounds or flag test, and nothing is ever relaxed outward.
 //
-// Row-striped multi-GPU: each rank runs the same kernels on rows [y0, y1) of the grid; the apron rows just
-// outside a stripe are read from the neighbour rank's distance array through a peer pointer (NVLink load) and
-// improvements of a stripe's first / last row raise a flag the neighbour rank turns into tile activations.
+// Row-striped multi-GPU (one rank per stripe): each rank runs the same kernels on rows [y0, y1) of the grid; the apron rows
+// just outside a stripe are read from LOCAL copies of the neighbour stripes' boundary rows (up_row / down_row), which the
+// host protocol (mazetd_b200/striped.py) refreshes between relaxation sweeps and k_stripe_merge folds in.
 #pragma once
 
 #include "common.cuh"
@@ -60,11 +60,9 @@ namespace mtd
 		int *status;
 		int aligned16;          // W % 4 == 0 and every base pointer 16-byte aligned: rows move as 16-byte vectors
 		// stripe neighbours (null on a single GPU or at the grid edge); nlayers == 1 when striped
-		const uint32_t *up_row;    // distance row y0-1 on the rank above (peer memory), [W]
-		const uint32_t *down_row;  // distance row y1 on the rank below, [W]
+		const uint32_t *up_row;    // local copy of distance row y0-1 (owned by the rank above), [W]
+		const uint32_t *down_row;  // local copy of distance row y1 (owned by the rank below), [W]
 		const uint32_t *up_wpack;  // wpack row y0-1 (for wd of the edge (y0-1) -> y0), local copy
-		uint32_t *peer_flag_up;    // [tilesX] set to 1 when this rank improved its first row over that tile column
-		uint32_t *peer_flag_down;  // [tilesX] same for the last row
 	};
 
 	// ---- edge weights -------------------------------------------------------------------------------
