@@ -183,6 +183,14 @@ int mtd_grid_from_elevations(mtd_ctx *ctx, const mtd_mapgen_params *p, int32_t n
 /* raw float32 ProceduralImpl::elevation samples (procedural.cpp:65-70) for seed (s1, s2): parity probe */
 int mtd_elevation_samples(mtd_ctx *ctx, uint64_t s1, uint64_t s2, const float *xy, int32_t n, float *out);
 
+/* ---- terrain SDF for marching cubes (the mesh itself stays out of scope) -------------------- */
+/* Maker::sdf (sources/map/generate.cpp:85-96) = ProceduralImpl::sdf (sources/map/procedural.cpp:134) + the cliff term of
+ * invalid land tiles, sampled at every lattice position of MarchingCubes::updateByPosition
+ * (externals/cage/sources/libcore/mesh/marchingCubes.cpp:149-165, 247-257). The game uses box (-55,-15,-55)..(55,15,55) and
+ * resolution (220, 60, 220) (generate.cpp:107-117). flags = the generated grid's TileFlags (host, [W*H]); out = host
+ * [res[2]][res[1]][res[0]] float32 (x fastest). A headless buffer: what the reference hands to dualmc. */
+int mtd_sdf_lattice(mtd_ctx *ctx, uint64_t s1, uint64_t s2, int32_t W, int32_t H, int32_t ox, int32_t oy, const uint16_t *flags, const float *box_a, const float *box_b, const int32_t *res, float *out);
+
 /* ---- monster steering (sources/game/monsters.cpp:55-99, sources/game/game.cpp:15-21) ------------ */
 /* SoA mirror of PositionComponent / MovementComponent / MonsterComponent fields the tick touches
  * (sources/game.h:154-186). dotflags: bit0 = affected(Fire), bit1 = affected(Water); NULL = none.

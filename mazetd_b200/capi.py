@@ -20,7 +20,7 @@ EXPORTS = [
     "mtd_stripe_upload", "mtd_stripe_upload_dev", "mtd_stripe_begin_dev", "mtd_stripe_exchange_dev", "mtd_stripe_finalize_dev", "mtd_stripe_round_budget", "mtd_stripe_pending",
     "mtd_waypoints_update", "mtd_waypoints_update_dev", "mtd_waypoints_find", "mtd_waypoints_layers_dev",
     "mtd_placing_blocks",
-    "mtd_mapgen_batch", "mtd_mapgen_batch_dev", "mtd_grid_from_elevations", "mtd_elevation_samples",
+    "mtd_mapgen_batch", "mtd_mapgen_batch_dev", "mtd_grid_from_elevations", "mtd_elevation_samples", "mtd_sdf_lattice",
     "mtd_monsters_upload", "mtd_monsters_download", "mtd_monsters_tick_dev", "mtd_monsters_tick",
     "mtd_monsters_positions_dev", "mtd_monsters_positions", "mtd_monster_spawn",
 ]
@@ -82,6 +82,7 @@ def load():
     L.mtd_mapgen_batch.argtypes = [vp, C.POINTER(MapgenParams), u64, u64, i32, i32] + [vp] * 9
     L.mtd_mapgen_batch_dev.argtypes = [vp, C.POINTER(MapgenParams), u64, u64, i32, i32] + [vp] * 9
     L.mtd_grid_from_elevations.argtypes = [vp, C.POINTER(MapgenParams), i32, vp, vp]
+    L.mtd_sdf_lattice.argtypes = [vp, u64, u64, i32, i32, i32, i32, vp, vp, vp, vp, vp]
     L.mtd_elevation_samples.argtypes = [vp, u64, u64, vp, i32, vp]
     L.mtd_monsters_upload.argtypes = [vp, i32] + [vp] * 10
     L.mtd_monsters_download.argtypes = [vp] + [vp] * 7
@@ -307,6 +308,14 @@ class Context:
         p = MapgenParams(W, H, ox, oy, radius, 0, 0)
         self._ck(self.L.mtd_grid_from_elevations(self.h, C.byref(p), elev.shape[0], _p(elev), _p(flags)))
         return flags
+
+    def sdf_lattice(self, s1, s2, flags, W=101, H=101, ox=50, oy=50, box_a=(-55, -15, -55), box_b=(55, 15, 55), res=(220, 60, 220)):
+        """Maker::sdf on the marching-cubes lattice -> float32 [rz][ry][rx]"""
+        flags = np.ascontiguousarray(flags, np.uint16)
+        a, b, r = np.array(box_a, np.float32), np.array(box_b, np.float32), np.array(res, np.int32)
+        out = np.empty((int(r[2]), int(r[1]), int(r[0])), np.float32)
+        self._ck(self.L.mtd_sdf_lattice(self.h, s1, s2, W, H, ox, oy, _p(flags), _p(a), _p(b), _p(r), _p(out)))
+        return out
 
     def elevation_samples(self, s1, s2, xy):
         xy = np.ascontiguousarray(xy, np.float32)

@@ -1591,6 +1591,84 @@ __global__ void k_elevation_samples(uint64_t s1, uint64_t s2, const float *xy, i
 		out[i] = noise::elevation(grad, lp, xy[i * 2 + 0], xy[i * 2 + 1]);
 }
 
+// Terrain SDF over the marching-cubes lattice: Maker::sdf (sources/map/generate.cpp:85-96) at the lattice positions of
+// MarchingCubesCreateConfig::position (externals/cage/sources/libcore/mesh/marchingCubes.cpp:247-257), stored x fastest,
+// then y, then z (marchingCubes.cpp:149-165). elevation() depends on (x, z) only, so one thread owns a lattice column:
+// one noise evaluation serves the whole column (the reference evaluates the noise at every lattice point).
+__global__ void k_sdf_lattice(uint64_t s1, uint64_t s2, int W, int H, int ox, int oy, const uint16_t *__restrict__ flags, float ax, float ay, float az, float bx, float by, float bz, int rx, int ry, int rz, float *__restrict__ out)
+{
+	__shared__ float2 grad[128];
+	__shared__ noise::ElevationParams ep;
+	noise::fill_gradients(grad);
+	if (threadIdx.x == 0)
+	{
+		Rng g;
+		g.s0 = s1;
+		g.s1 = s2;
+		const float r1 = g.chance();
+		const float r2 = g.chance();
+		ep.off_x = __fmul_rn(r1, 1000.0f);
+		ep.off_y = __fmul_rn(r2, 1000.0f);
+		ep.seed = (int)(uint32_t)g.next();
+		ep.bounding = noise::fractal_bounding(4, 0.55f);
+	}
+	__syncthreads();
+	const noise::ElevationParams lp = ep;
+	const float dx = __fsub_rn((float)rx, 5.0f), dy = __fsub_rn((float)ry, 5.0f), dz = __fsub_rn((float)rz, 5.0f);
+	const float sx = __fsub_rn(bx, ax), sy = __fsub_rn(by, ay), sz = __fsub_rn(bz, az);
+	const int columns = rx * rz;
+	for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < columns; c += gridDim.x * blockDim.x)
+	{
+		const int z = c / rx, x = c - z * rx;
+		const float px = __fadd_rn(__fmul_rn(sx, __fdiv_rn(__fsub_rn((float)x, 2.0f), dx)), ax);
+		const float pz = __fadd_rn(__fmul_rn(sz, __fdiv_rn(__fsub_rn((float)z, 2.0f), dz)), az);
+		const float e = noise::elevation(grad, lp, px, pz);
+		// Grid::index(Vec3) -> index(Vec2(x, z)) -> Vec2i(pos + 200.5) - 200 (sources/map/grid.cpp:108-116)
+		const int tx = __float2int_rz(__fadd_rn(px, 200.5f)) - 200 + ox;
+		const int tz = __float2int_rz(__fadd_rn(pz, 200.5f)) - 200 + oy;
+		bool cliff = false; // invalid land tiles get a wall below the water line (generate.cpp:89-94)
+		if (tx >= 0 && tx < W && tz >= 0 && tz < H)
+		{
+			const uint16_t f = flags[tz * W + tx];
+			cliff = (f & F_INVALID) && !(f & F_WATER);
+		}
+		for (int y = 0; y < ry; y++)
+		{
+			const float py = __fadd_rn(__fmul_rn(sy, __fdiv_rn(__fsub_rn((float)y, 2.0f), dy)), ay);
+			float d = __fsub_rn(e, py);
+			if (cliff)
+			{
+				float t = __fdiv_rn(__fsub_rn(py, -7.5f), __fsub_rn(-6.5f, -7.5f)); // find(y, -7.5, -6.5), sources/map/generate.h:37-40
+				t = t > 0.0f ? t : 0.0f; // saturate = clamp(t, 0, 1) = min(max(t, 0), 1) with cage's a < b ? a : b selects
+				t = t < 1.0f ? t : 1.0f;
+				d = __fadd_rn(d, t);
+			}
+			__stcs(out + ((size_t)z * ry + y) * rx + x, d);
+		}
+	}
+}
+
+extern "C" int mtd_sdf_lattice(mtd_ctx *ctx, uint64_t s1, uint64_t s2, int32_t W, int32_t H, int32_t ox, int32_t oy, const uint16_t *flags, const float *box_a, const float *box_b, const int32_t *res, float *out)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (W < 1 || H < 1 || !flags || !box_a || !box_b || !res || !out)
+		return fail(ctx, MTD_ERR_ARG, "sdf_lattice needs flags, a box, a resolution and an output");
+	if (res[0] < 6 || res[1] < 6 || res[2] < 6) // marchingCubes.cpp:249-251
+		return fail(ctx, MTD_ERR_ARG, "lattice resolution must exceed 5 in every dimension");
+	const size_t T = (size_t)W * H, n = (size_t)res[0] * res[1] * res[2];
+	CU(ctx->scratch_flags.reserve(T));
+	CU(ctx->scratch_f.reserve(n));
+	CU(cudaMemcpyAsync(ctx->scratch_flags.p, flags, T * 2, cudaMemcpyHostToDevice, ctx->stream));
+	const int columns = res[0] * res[2];
+	k_sdf_lattice<<<(columns + 127) / 128, 128, 0, ctx->stream>>>(s1, s2, W, H, ox, oy, ctx->scratch_flags.p, box_a[0], box_a[1], box_a[2], box_b[0], box_b[1], box_b[2], res[0], res[1], res[2], ctx->scratch_f.p);
+	LAUNCHED();
+	CU(cudaMemcpyAsync(out, ctx->scratch_f.p, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	return sync_and_status(ctx);
+}
+
 extern "C" int mtd_grid_from_elevations(mtd_ctx *ctx, const mtd_mapgen_params *p, int32_t nmaps, const int16_t *elev, uint16_t *flags_out)
 {
 	if (!ctx)

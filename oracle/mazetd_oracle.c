@@ -819,3 +819,36 @@ int mo_placing_blocks(const mo_grid *g, const uint32_t *wp_tiles, int n, uint32_
 			return 1;
 	return 0;
 }
+
+/* Maker::sdf over the marching-cubes lattice: sources/map/generate.cpp:85-96 (sdf = procedural->sdf(pos) + cliff term of
+ * invalid land tiles), sources/map/procedural.cpp:134 (elevation(x, z) - y), lattice positions
+ * externals/cage/sources/libcore/mesh/marchingCubes.cpp:247-257 ((b - a) * ((xyz - 2) / (res - 5)) + a), storage order
+ * marchingCubes.cpp:149-165 (x fastest, then y, then z). Evaluated point by point like the reference. */
+void mo_sdf_lattice(const mo_procedural *p, const mo_grid *g, const float *a, const float *b, const int32_t *res, float *out)
+{
+	const float dx = (float)res[0] - 5.0f, dy = (float)res[1] - 5.0f, dz = (float)res[2] - 5.0f;
+	size_t o = 0;
+	for (int32_t z = 0; z < res[2]; z++)
+		for (int32_t y = 0; y < res[1]; y++)
+			for (int32_t x = 0; x < res[0]; x++)
+			{
+				const float fx = ((float)x - 2.0f) / dx, fy = ((float)y - 2.0f) / dy, fz = ((float)z - 2.0f) / dz;
+				const float px = (b[0] - a[0]) * fx + a[0];
+				const float py = (b[1] - a[1]) * fy + a[1];
+				const float pz = (b[2] - a[2]) * fz + a[2];
+				float d = mo_elevation(p, px, pz) - py;
+				const uint32_t i = mo_grid_index_f(g, px, pz); /* Grid::index(Vec3) = index(Vec2(x, z)), grid.cpp:113-116 */
+				if (i != MO_M)
+				{
+					const uint16_t f = g->flags[i];
+					if ((f & MO_FLAG_INVALID) && !(f & MO_FLAG_WATER))
+					{
+						float t = (py - -7.5f) / (-6.5f - -7.5f); /* find(value, lower, upper), generate.h:37-40 */
+						t = t > 0.0f ? t : 0.0f;                  /* saturate: min(max(t, 0), 1), math.h:1021-1032 */
+						t = t < 1.0f ? t : 1.0f;
+						d += t;
+					}
+				}
+				out[o++] = d;
+			}
+}

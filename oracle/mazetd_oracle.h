@@ -102,6 +102,8 @@ typedef struct mo_procedural
 } mo_procedural;
 void mo_procedural_init(mo_procedural *p, mo_rng *g);
 float mo_elevation(const mo_procedural *p, float x, float y);
+/* Maker::sdf at every marching-cubes lattice position (generate.cpp:85-96, marchingCubes.cpp:149-165, 247-257) */
+void mo_sdf_lattice(const mo_procedural *p, const mo_grid *g, const float *a, const float *b, const int32_t *res, float *out);
 /* newGrid for an arbitrary resolution/offset/radius (reference: 101, 50, 45) */
 void mo_new_grid(const mo_procedural *p, int32_t W, int32_t H, int32_t ox, int32_t oy, int32_t radius, int16_t *elev, uint16_t *flags, uint32_t *valid_tiles);
 /* the integer stages of newGrid on caller-provided elevations (flags thresholds + slope + radius) */

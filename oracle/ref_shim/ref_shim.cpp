@@ -520,6 +520,39 @@ extern "C"
 			out[i] = procedural->elevation(Vec2(xy[i * 2 + 0], xy[i * 2 + 1])).value;
 	}
 
+	// ---- terrain SDF over the marching-cubes lattice ----
+	// Maker::sdf (sources/map/generate.cpp:85-96) and MarchingCubesCreateConfig::position
+	// (externals/cage/sources/libcore/mesh/marchingCubes.cpp:247-257) cannot be linked (mesh library, dualmc); they are
+	// restated here with cage's own Vec3 arithmetic and call the COMPILED reference Procedural::sdf, newGrid and Grid::index.
+	// Storage order as MarchingCubes::updateByPosition (marchingCubes.cpp:149-165). flags_out: the grid's flags after newGrid.
+	void ref_sdf_lattice(uint64_t s1, uint64_t s2, const float *a, const float *b, const int32_t *res, float *out, uint16_t *flags_out)
+	{
+		detail::randomGenerator() = RandomGenerator(s1, s2);
+		Holder<Procedural> procedural = newProcedural();
+		Holder<Grid> grid = newGrid(procedural.share());
+		if (flags_out)
+			std::memcpy(flags_out, grid->flags.data(), grid->flags.size() * sizeof(uint16));
+		const Vec3 boxA(a[0], a[1], a[2]), boxB(b[0], b[1], b[2]);
+		const Vec3i resolution(res[0], res[1], res[2]);
+		size_t o = 0;
+		for (uint32 z = 0; z < (uint32)res[2]; z++)
+			for (uint32 y = 0; y < (uint32)res[1]; y++)
+				for (uint32 x = 0; x < (uint32)res[0]; x++)
+				{
+					const Vec3 f = (Vec3(x, y, z) - 2) / (Vec3(resolution) - 5);
+					const Vec3 pos = (boxB - boxA) * f + boxA;
+					Real d = procedural->sdf(pos);
+					const uint32 i = grid->index(pos);
+					if (i != m)
+					{
+						const TileFlags fl = grid->flags[i];
+						if (any(fl & TileFlags::Invalid) && none(fl & TileFlags::Water))
+							d += saturate(find(pos[1], -7.5, -6.5));
+					}
+					out[o++] = d.value;
+				}
+	}
+
 	// ---- monster steering: restatement over SoA calling the compiled reference map functions ----
 	// follows sources/game/monsters.cpp:60-98 statement by statement.
 	// alive[i]==0 entries are skipped; a monster that completes all waypoints gets alive=0 and its damage is

@@ -197,6 +197,17 @@ class Oracle:
         self.L.mo_add_mana(W, H, ptr(flags, u16p))
         return flags
 
+    def sdf_lattice(self, s1, s2, W, H, ox, oy, flags, box_a=(-55, -15, -55), box_b=(55, 15, 55), res=(220, 60, 220)):
+        """Maker::sdf on the marching-cubes lattice for the Procedural of seed (s1, s2) and the given grid flags"""
+        r = self.rng(s1, s2)
+        pr = MoProcedural()
+        self.L.mo_procedural_init(C.byref(pr), C.byref(r))
+        g = self.grid(W, H, ox, oy, None, np.ascontiguousarray(flags, np.uint16))
+        a, b, rs = np.array(box_a, np.float32), np.array(box_b, np.float32), np.array(res, np.int32)
+        out = np.empty((int(rs[2]), int(rs[1]), int(rs[0])), np.float32)
+        self.L.mo_sdf_lattice(C.byref(pr), C.byref(g), C.c_void_p(a.ctypes.data), C.c_void_p(b.ctypes.data), C.c_void_p(rs.ctypes.data), C.c_void_p(out.ctypes.data))
+        return out
+
     def monsters(self, arrs):
         ms = MoMonsters(
             len(arrs["tile"]),
@@ -343,6 +354,14 @@ class Ref:
         self.L.ref_map_get_grid(h, None, out["elev"].ctypes.data, out["flags"].ctypes.data)
         self.L.ref_map_destroy(h)
         return out
+
+    def sdf_lattice(self, s1, s2, box_a=(-55, -15, -55), box_b=(55, 15, 55), res=(220, 60, 220)):
+        """(sdf [rz][ry][rx], flags of the generated grid) from the compiled reference pieces"""
+        a, b, rs = np.array(box_a, np.float32), np.array(box_b, np.float32), np.array(res, np.int32)
+        out = np.empty((int(rs[2]), int(rs[1]), int(rs[0])), np.float32)
+        flags = np.zeros(101 * 101, np.uint16)
+        self.L.ref_sdf_lattice(C.c_uint64(s1), C.c_uint64(s2), C.c_void_p(a.ctypes.data), C.c_void_p(b.ctypes.data), C.c_void_p(rs.ctypes.data), C.c_void_p(out.ctypes.data), C.c_void_p(flags.ctypes.data))
+        return out, flags
 
     def find(self, h, pos, bits):
         out = np.zeros(2, np.uint32)

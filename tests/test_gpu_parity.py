@@ -737,3 +737,24 @@ def test_tiled_priority_window_never_changes_the_result(oracle, delta):
     wo = oracle.waypoints_update(W, H, elev, flags, srcs, cap=64)
     assert np.array_equal(w["dist"], wo["dist"]) and np.array_equal(w["tiles"], wo["tiles"])
     c.close()
+
+
+# ---------------------------------------------------------------------------------------------------
+# terrain SDF over the marching-cubes lattice (headless buffer; meshing stays out of scope)
+# ---------------------------------------------------------------------------------------------------
+def test_sdf_lattice_bit_exact(ctx, oracle):
+    o = oracle.mapgen(KAT_SEED[0] + 4, KAT_SEED[1])
+    for res in ((220, 60, 220), (33, 9, 47)):
+        got = ctx.sdf_lattice(KAT_SEED[0] + 4, KAT_SEED[1], o["flags"], res=res)
+        want = oracle.sdf_lattice(KAT_SEED[0] + 4, KAT_SEED[1], 101, 101, 50, 50, o["flags"], res=res)
+        bad = np.flatnonzero(got.view(np.uint32).reshape(-1) != want.view(np.uint32).reshape(-1))
+        assert bad.size == 0, f"{bad.size} of {got.size} lattice values differ; first at {int(bad[0])}: {got.reshape(-1)[bad[0]]} vs {want.reshape(-1)[bad[0]]}"
+    # the cliff term only shows on invalid land tiles below y = -6.5: it must be present somewhere
+    flat = ctx.sdf_lattice(KAT_SEED[0] + 4, KAT_SEED[1], np.zeros(101 * 101, np.uint16))
+    assert (got.shape == (47, 9, 33)) and not np.array_equal(flat, ctx.sdf_lattice(KAT_SEED[0] + 4, KAT_SEED[1], o["flags"]))
+
+
+def test_sdf_lattice_vs_reference_code(ctx, ref):
+    sr, flags = ref.sdf_lattice(KAT_SEED[0] + 9, KAT_SEED[1])
+    got = ctx.sdf_lattice(KAT_SEED[0] + 9, KAT_SEED[1], flags)
+    assert np.array_equal(got.view(np.uint32), sr.view(np.uint32))

@@ -270,3 +270,13 @@ def test_position_edge_cases_match_ref(oracle, ref):
         pr = ref.monsters_position(h, gt, ts, te, t0, t1)
         assert np.array_equal(po.view(np.uint32), pr.view(np.uint32))
     ref.L.ref_map_destroy(h)
+
+
+def test_sdf_lattice_matches_ref(oracle, ref):
+    """Maker::sdf on the marching-cubes lattice (SURVEY.md 8f rank 4): the oracle's restatement against the compiled
+    reference Procedural::sdf / newGrid / Grid::index, bit for bit, on a reduced lattice and on one slab of the game's own"""
+    for k, res in ((0, (40, 12, 36)), (3, (220, 7, 220))):
+        sr, flags = ref.sdf_lattice(KAT_SEED[0] + k, KAT_SEED[1], res=res)
+        so = oracle.sdf_lattice(KAT_SEED[0] + k, KAT_SEED[1], 101, 101, 50, 50, flags, res=res)
+        assert np.array_equal(so.view(np.uint32), sr.view(np.uint32))
+        assert np.isfinite(sr).all() and (sr > 0).any() and (sr < 0).any()
