@@ -207,6 +207,17 @@ int mtd_monsters_positions(mtd_ctx *ctx, uint32_t gameTime, float *out3n);
 /* SpawningGroup::spawnOne steering state (sources/game/monsterSpawning.cpp:205-216): out3 = tile, bits, timeToArrive */
 int mtd_monster_spawn(mtd_ctx *ctx, uint32_t gameTime, float speed, uint32_t *out3);
 
+/* ---- damage-over-time tick: "damage monsters", sources/game/monsters.cpp:101-183 ------------ */
+/* Integer state only (the RNG-driven visual effects of :140-149 and the ghost of :176 stay with the caller). The monsters
+ * are those of mtd_monsters_upload. duration / damage: [5][n] in DamageTypeEnum order Physical, Fire, Water, Poison, Magic
+ * (sources/game.h:18-27, 166-172); resist: [n] DamageTypeFlags bits 0..4 (may be NULL); life: [n] sint64; money: [n]
+ * (may be NULL). After this upload the steering tick reads affected(Fire) / affected(Water) from these dots. */
+int mtd_monsters_dots_upload(mtd_ctx *ctx, const uint32_t *duration, const uint32_t *damage, const uint8_t *resist, const int64_t *life, const uint32_t *money);
+/* one tick: dotsEliminateOposing x2, applyDot x5, life <= 0 -> dead (alive = 0), its money added to *money_out */
+int mtd_monsters_dots_tick_dev(mtd_ctx *ctx);
+int mtd_monsters_dots_tick(mtd_ctx *ctx, int64_t *money_out, uint32_t *killed_out);
+int mtd_monsters_dots_download(mtd_ctx *ctx, uint32_t *duration, uint32_t *damage, int64_t *life, uint8_t *alive);
+
 #ifdef __cplusplus
 }
 #endif

@@ -23,6 +23,7 @@ EXPORTS = [
     "mtd_mapgen_batch", "mtd_mapgen_batch_dev", "mtd_grid_from_elevations", "mtd_elevation_samples", "mtd_sdf_lattice",
     "mtd_monsters_upload", "mtd_monsters_download", "mtd_monsters_tick_dev", "mtd_monsters_tick",
     "mtd_monsters_positions_dev", "mtd_monsters_positions", "mtd_monster_spawn",
+    "mtd_monsters_dots_upload", "mtd_monsters_dots_tick_dev", "mtd_monsters_dots_tick", "mtd_monsters_dots_download",
 ]
 
 
@@ -91,6 +92,10 @@ def load():
     L.mtd_monsters_positions_dev.argtypes = [vp, u32, vp]
     L.mtd_monsters_positions.argtypes = [vp, u32, vp]
     L.mtd_monster_spawn.argtypes = [vp, u32, f32, vp]
+    L.mtd_monsters_dots_upload.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.mtd_monsters_dots_tick_dev.argtypes = [vp]
+    L.mtd_monsters_dots_tick.argtypes = [vp, C.POINTER(C.c_int64), C.POINTER(u32)]
+    L.mtd_monsters_dots_download.argtypes = [vp, vp, vp, vp, vp]
     _lib = L
     return L
 
@@ -352,6 +357,27 @@ class Context:
 
     def monsters_positions_dev(self, game_time, d_out):
         self._ck(self.L.mtd_monsters_positions_dev(self.h, int(game_time), _p(d_out)))
+
+    # ---- damage over time ----
+    def monsters_dots_upload(self, duration, damage, life, resist=None, money=None):
+        """duration / damage: uint32 [5][n] (Physical, Fire, Water, Poison, Magic); life int64 [n]; resist uint8 [n]; money uint32 [n]"""
+        self._ck(self.L.mtd_monsters_dots_upload(self.h, _p(np.ascontiguousarray(duration, np.uint32)), _p(np.ascontiguousarray(damage, np.uint32)),
+                                                 _p(None if resist is None else np.ascontiguousarray(resist, np.uint8)), _p(np.ascontiguousarray(life, np.int64)),
+                                                 _p(None if money is None else np.ascontiguousarray(money, np.uint32))))
+
+    def monsters_dots_tick(self):
+        money, killed = C.c_int64(0), C.c_uint32(0)
+        self._ck(self.L.mtd_monsters_dots_tick(self.h, C.byref(money), C.byref(killed)))
+        return money.value, killed.value
+
+    def monsters_dots_tick_dev(self):
+        self._ck(self.L.mtd_monsters_dots_tick_dev(self.h))
+
+    def monsters_dots_download(self):
+        n = self.nmon
+        out = dict(duration=np.empty((5, n), np.uint32), damage=np.empty((5, n), np.uint32), life=np.empty(n, np.int64), alive=np.empty(n, np.uint8))
+        self._ck(self.L.mtd_monsters_dots_download(self.h, _p(out["duration"]), _p(out["damage"]), _p(out["life"]), _p(out["alive"])))
+        return out
 
     def monster_spawn(self, game_time, speed):
         out = np.zeros(3, np.uint32)

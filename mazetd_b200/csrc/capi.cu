@@ -147,7 +147,10 @@ struct mtd_ctx
 	int nmon = 0;
 	DevBuf<uint32_t> m_tile, m_tileStart, m_tileEnd, m_timeStart, m_timeEnd, m_bits, m_tta, m_damage;
 	DevBuf<uint8_t> m_dot, m_alive;
-	bool m_has_dot = false, m_has_damage = false;
+	bool m_has_dot = false, m_has_damage = false, m_has_dots = false, m_has_resist = false, m_has_money = false;
+	DevBuf<uint32_t> m_dot_duration, m_dot_damage, m_money; // damage-over-time state: [5][n], [5][n], [n]
+	DevBuf<long long> m_life;
+	DevBuf<uint8_t> m_resist;
 	DevBuf<float> m_pos;
 
 	// scratch
@@ -817,6 +820,11 @@ extern "C" void mtd_destroy(mtd_ctx *ctx)
 	ctx->scratch_f.release();
 	ctx->d_status.release();
 	ctx->d_damage.release();
+	ctx->m_dot_duration.release();
+	ctx->m_dot_damage.release();
+	ctx->m_money.release();
+	ctx->m_life.release();
+	ctx->m_resist.release();
 	ctx->d_small.release();
 	ctx->d_trial.release();
 	if (ctx->hflags)
@@ -1754,6 +1762,7 @@ extern "C" int mtd_monsters_upload(mtd_ctx *ctx, int32_t n, const uint32_t *tile
 	CU(cudaMemcpyAsync(ctx->m_bits.p, bits, N * 4, cudaMemcpyHostToDevice, ctx->stream));
 	CU(cudaMemcpyAsync(ctx->m_tta.p, timeToArrive, N * 4, cudaMemcpyHostToDevice, ctx->stream));
 	ctx->m_has_dot = dotflags != nullptr;
+	ctx->m_has_dots = false; // a new population: its damage-over-time state has to be uploaded again
 	ctx->m_has_damage = damage != nullptr;
 	if (dotflags)
 		CU(cudaMemcpyAsync(ctx->m_dot.p, dotflags, N, cudaMemcpyHostToDevice, ctx->stream));
@@ -1834,6 +1843,114 @@ extern "C" int mtd_monsters_tick(mtd_ctx *ctx, uint32_t gameTime, int64_t *damag
 	if (alive_out)
 		*alive_out = ctx->hflags->alive;
 	return MTD_OK;
+}
+
+// ---- damage-over-time tick ----
+static DotsView dots_view(mtd_ctx *ctx)
+{
+	DotsView D;
+	D.n = ctx->nmon;
+	D.duration = ctx->m_dot_duration.p;
+	D.damage = ctx->m_dot_damage.p;
+	D.resist = ctx->m_has_resist ? ctx->m_resist.p : nullptr;
+	D.life = ctx->m_life.p;
+	D.money = ctx->m_has_money ? ctx->m_money.p : nullptr;
+	D.alive = ctx->m_alive.p;
+	D.dotflags = ctx->m_dot.p;
+	return D;
+}
+
+extern "C" int mtd_monsters_dots_upload(mtd_ctx *ctx, const uint32_t *duration, const uint32_t *damage, const uint8_t *resist, const int64_t *life, const uint32_t *money)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	const size_t n = (size_t)ctx->nmon;
+	if (n == 0)
+		return fail(ctx, MTD_ERR_STATE, "upload the monsters first (mtd_monsters_upload)");
+	if (!duration || !damage || !life)
+		return fail(ctx, MTD_ERR_ARG, "dots need duration, damage and life arrays");
+	CU(ctx->m_dot_duration.reserve(5 * n));
+	CU(ctx->m_dot_damage.reserve(5 * n));
+	CU(ctx->m_life.reserve(n));
+	CU(ctx->m_resist.reserve(n));
+	CU(ctx->m_money.reserve(n));
+	CU(ctx->m_dot.reserve(n));
+	CU(cudaMemcpyAsync(ctx->m_dot_duration.p, duration, 5 * n * 4, cudaMemcpyHostToDevice, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->m_dot_damage.p, damage, 5 * n * 4, cudaMemcpyHostToDevice, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->m_life.p, life, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+	ctx->m_has_resist = resist != nullptr;
+	ctx->m_has_money = money != nullptr;
+	if (resist)
+		CU(cudaMemcpyAsync(ctx->m_resist.p, resist, n, cudaMemcpyHostToDevice, ctx->stream));
+	if (money)
+		CU(cudaMemcpyAsync(ctx->m_money.p, money, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+	ctx->m_has_dots = true;
+	ctx->m_has_dot = true; // from now on the steering tick reads the fire / water bits derived from the dots
+	k_dots_flags<<<(ctx->nmon + 255) / 256, 256, 0, ctx->stream>>>(dots_view(ctx));
+	LAUNCHED();
+	CU(cudaStreamSynchronize(ctx->stream));
+	return MTD_OK;
+}
+
+static int dots_tick_dev(mtd_ctx *ctx)
+{
+	if (!ctx->m_has_dots || ctx->nmon == 0)
+		return fail(ctx, MTD_ERR_STATE, "no dots uploaded (mtd_monsters_dots_upload)");
+	CU(cudaMemsetAsync(ctx->d_damage.p, 0, 8, ctx->stream));
+	CU(cudaMemsetAsync(ctx->d_small.p + 4, 0, 4, ctx->stream));
+	k_monsters_dots<<<(ctx->nmon + 255) / 256, 256, 0, ctx->stream>>>(dots_view(ctx), ctx->d_damage.p, ctx->d_small.p + 4);
+	LAUNCHED();
+	return MTD_OK;
+}
+
+extern "C" int mtd_monsters_dots_tick_dev(mtd_ctx *ctx)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	return dots_tick_dev(ctx);
+}
+
+extern "C" int mtd_monsters_dots_tick(mtd_ctx *ctx, int64_t *money_out, uint32_t *killed_out)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	int rc = dots_tick_dev(ctx);
+	if (rc)
+		return rc;
+	CU(cudaMemcpyAsync(&ctx->hflags->damage, ctx->d_damage.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaMemcpyAsync(&ctx->hflags->alive, ctx->d_small.p + 4, 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	if (money_out)
+		*money_out = (int64_t)ctx->hflags->damage;
+	if (killed_out)
+		*killed_out = ctx->hflags->alive;
+	return MTD_OK;
+}
+
+extern "C" int mtd_monsters_dots_download(mtd_ctx *ctx, uint32_t *duration, uint32_t *damage, int64_t *life, uint8_t *alive)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (!ctx->m_has_dots)
+		return fail(ctx, MTD_ERR_STATE, "no dots uploaded (mtd_monsters_dots_upload)");
+	const size_t n = (size_t)ctx->nmon;
+	if (duration)
+		CU(cudaMemcpyAsync(duration, ctx->m_dot_duration.p, 5 * n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (damage)
+		CU(cudaMemcpyAsync(damage, ctx->m_dot_damage.p, 5 * n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (life)
+		CU(cudaMemcpyAsync(life, ctx->m_life.p, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+	if (alive)
+		CU(cudaMemcpyAsync(alive, ctx->m_alive.p, n, cudaMemcpyDeviceToHost, ctx->stream));
+	return sync_and_status(ctx);
 }
 
 extern "C" int mtd_monsters_positions_dev(mtd_ctx *ctx, uint32_t gameTime, float *d_out3n)

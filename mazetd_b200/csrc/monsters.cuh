@@ -116,6 +116,105 @@ namespace mtd
 			atomicAdd(alive_count, (uint32_t)__popc(bal));
 	}
 
+	// ---- "damage monsters" (sources/game/monsters.cpp:101-183), integer state only -------------------------------
+	// One thread per monster over SoA: dot arrays are [5][n] in DamageTypeEnum order (game.h:18-27). The RNG-driven visual
+	// effects (:140-149) and the ghost entity (:176) are not state and stay on the host. Also refreshes the fire / water bits
+	// the steering tick reads (MonsterComponent::affected, monsters.cpp:13-16, 92-95).
+	struct DotsView
+	{
+		int n;
+		uint32_t *duration, *damage; // [5][n]
+		const uint8_t *resist;       // [n] DamageTypeFlags bits 0..4, or null
+		long long *life;             // [n] sint64 (game.h:162)
+		const uint32_t *money;       // [n] or null
+		uint8_t *alive;              // [n]
+		uint8_t *dotflags;           // [n] bit0 = affected(Fire), bit1 = affected(Water)
+	};
+
+	__global__ void k_monsters_dots(DotsView D, unsigned long long *money_sum, uint32_t *killed)
+	{
+		const int i = blockIdx.x * blockDim.x + threadIdx.x;
+		const bool live = i < D.n && D.alive[i];
+		unsigned long long my_money = 0;
+		bool died = false;
+		if (live)
+		{
+			const size_t n = (size_t)D.n;
+			uint32_t du[5], da[5];
+#pragma unroll
+			for (int t = 0; t < 5; t++)
+			{
+				du[t] = D.duration[t * n + i];
+				da[t] = D.damage[t * n + i];
+			}
+			// dotsEliminateOposing<Fire, Water>, <Poison, Magic> (monsters.cpp:101-114)
+			if (du[1] > 0 && du[2] > 0)
+			{
+				da[1] = da[2] = 0;
+				du[1] = du[2] = 30;
+			}
+			if (du[3] > 0 && du[4] > 0)
+			{
+				da[3] = da[4] = 0;
+				du[3] = du[4] = 30;
+			}
+			const uint32_t resist = D.resist ? D.resist[i] : 0u;
+			long long life = D.life[i];
+#pragma unroll
+			for (int t = 0; t < 5; t++) // applyDot<Physical, Fire, Water, Poison, Magic> in this order (monsters.cpp:166-170)
+			{
+				const bool super = da[t == 0 ? 3 : 4] > 0; // read NOW: an earlier applyDot may have drained it
+				uint32_t d = da[t];
+				if (du[t] > 1)
+					d /= du[t];
+				if (du[t] > 0)
+					du[t]--;
+				if (d != 0)
+				{
+					da[t] -= d;
+					if (super)
+						d *= 2u;
+					if (resist & (1u << t))
+						d /= 4u;
+					life -= (long long)d;
+				}
+			}
+#pragma unroll
+			for (int t = 0; t < 5; t++)
+			{
+				D.duration[t * n + i] = du[t];
+				D.damage[t * n + i] = da[t];
+			}
+			D.life[i] = life;
+			D.dotflags[i] = (uint8_t)((da[1] > 0 ? 1u : 0u) | (da[2] > 0 ? 2u : 0u));
+			if (life <= 0) // monsters.cpp:172-178
+			{
+				died = true;
+				my_money = D.money ? D.money[i] : 0u;
+				D.alive[i] = 0;
+			}
+		}
+		// one atomic per warp
+		const uint32_t dead = __ballot_sync(FULL_MASK, died);
+		if (dead)
+		{
+			for (int o = 16; o > 0; o >>= 1)
+				my_money += __shfl_down_sync(FULL_MASK, my_money, o);
+			if ((threadIdx.x & 31) == 0)
+			{
+				atomicAdd(money_sum, my_money);
+				atomicAdd(killed, (uint32_t)__popc(dead));
+			}
+		}
+	}
+
+	__global__ void k_dots_flags(DotsView D)
+	{
+		const int i = blockIdx.x * blockDim.x + threadIdx.x;
+		if (i < D.n)
+			D.dotflags[i] = (uint8_t)((D.damage[(size_t)1 * D.n + i] > 0 ? 1u : 0u) | (D.damage[(size_t)2 * D.n + i] > 0 ? 2u : 0u));
+	}
+
 	// game.cpp:15-21: saturate(Real(gameTime - (sint64)timeStart) / Real(timeEnd - (sint64)timeStart)), interpolate
 	__global__ void k_monsters_positions(LayersView L, MonstersView M, uint32_t gameTime, float *out3n)
 	{

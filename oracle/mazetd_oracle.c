@@ -852,3 +852,58 @@ void mo_sdf_lattice(const mo_procedural *p, const mo_grid *g, const float *a, co
 				out[o++] = d;
 			}
 }
+
+/* =============================================================================================
+ * damage-over-time tick ("damage monsters") -- sources/game/monsters.cpp:101-183, integer part only
+ * (the RNG-driven visual effects of :140-149 and the ghost entity of :176 are not state).
+ * dot arrays are [5][n] in DamageTypeEnum order (game.h:18-27): Physical, Fire, Water, Poison, Magic.
+ * ============================================================================================= */
+static void mo_eliminate_opposing(uint32_t *dur, uint32_t *dmg, int n, int i, int a, int b) /* monsters.cpp:101-114 */
+{
+	if (dur[(size_t)a * n + i] > 0 && dur[(size_t)b * n + i] > 0)
+	{
+		dmg[(size_t)a * n + i] = 0;
+		dmg[(size_t)b * n + i] = 0;
+		dur[(size_t)a * n + i] = 30;
+		dur[(size_t)b * n + i] = 30;
+	}
+}
+
+static void mo_apply_dot(uint32_t *dur, uint32_t *dmg, int n, int i, int type, uint8_t resist, int64_t *life) /* monsters.cpp:116-150 */
+{
+	const int strengthen = type == 0 ? 3 : 4; /* Physical is strengthened by Poison, everything else by Magic */
+	const int super = dmg[(size_t)strengthen * n + i] > 0; /* affected(): dots[].damage > 0, monsters.cpp:13-16 */
+	uint32_t *du = &dur[(size_t)type * n + i], *da = &dmg[(size_t)type * n + i];
+	uint32_t d = *da;
+	if (*du > 1)
+		d /= *du;
+	if (*du > 0)
+		(*du)--;
+	if (d == 0)
+		return;
+	*da -= d;
+	if (super)
+		d *= 2; /* uint32, wraps like the reference */
+	if (resist & (1u << type))
+		d /= 4;
+	*life -= (int64_t)d;
+}
+
+void mo_monsters_dots_tick(int n, uint32_t *dot_duration, uint32_t *dot_damage, const uint8_t *resist, int64_t *life, const uint32_t *money, uint8_t *alive, int64_t *money_sum, uint32_t *killed)
+{
+	for (int i = 0; i < n; i++)
+	{
+		if (!alive[i])
+			continue;
+		mo_eliminate_opposing(dot_duration, dot_damage, n, i, 1, 2); /* Fire, Water */
+		mo_eliminate_opposing(dot_duration, dot_damage, n, i, 3, 4); /* Poison, Magic */
+		for (int t = 0; t < 5; t++)
+			mo_apply_dot(dot_duration, dot_damage, n, i, t, resist ? resist[i] : 0, &life[i]);
+		if (life[i] <= 0) /* monsters.cpp:172-178 */
+		{
+			*money_sum += money ? money[i] : 0;
+			alive[i] = 0;
+			(*killed)++;
+		}
+	}
+}

@@ -132,6 +132,8 @@ typedef struct mo_monsters
 	uint8_t *alive;
 } mo_monsters;
 void mo_monsters_tick(const mo_waypoints *w, uint32_t gameTime, mo_monsters *ms, int64_t *damage_sum);
+/* "damage monsters" (sources/game/monsters.cpp:101-183), integer state only; dot arrays [5][n], Physical..Magic */
+void mo_monsters_dots_tick(int n, uint32_t *dot_duration, uint32_t *dot_damage, const uint8_t *resist, int64_t *life, const uint32_t *money, uint8_t *alive, int64_t *money_sum, uint32_t *killed);
 void mo_monster_spawn(const mo_waypoints *w, uint32_t minDistanceSpawner, uint32_t gameTime, float speed, uint32_t *out3 /* tile, bits, timeToArrive */);
 void mo_monsters_position(const mo_grid *g, uint32_t gameTime, int n, const uint32_t *tileStart, const uint32_t *tileEnd, const uint32_t *timeStart, const uint32_t *timeEnd, float *out3n);
 /* trial of sources/player/buildingsPlacement.cpp:18-42: 1 if the candidate building would disconnect a waypoint or a monster */

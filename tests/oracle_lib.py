@@ -231,6 +231,14 @@ class Oracle:
         self.L.mo_monsters_tick(C.addressof(wview), game_time, C.addressof(ms), C.addressof(dmg))
         return dmg.value
 
+    def monsters_dots_tick(self, duration, damage, life, alive, resist=None, money=None):
+        """in place on uint32 [5][n] duration / damage, int64 life, uint8 alive; returns (money of the killed, killed)"""
+        n = len(life)
+        ms, kl = C.c_int64(0), C.c_uint32(0)
+        vp = lambda a: None if a is None else C.c_void_p(a.ctypes.data)
+        self.L.mo_monsters_dots_tick(n, vp(duration), vp(damage), vp(resist), vp(life), vp(money), vp(alive), C.byref(ms), C.byref(kl))
+        return ms.value, kl.value
+
     def monster_spawn(self, wview, spawner, game_time, speed):
         out = np.zeros(3, np.uint32)
         self.L.mo_monster_spawn(C.addressof(wview), spawner, game_time, speed, out.ctypes.data)

@@ -40,3 +40,34 @@ def test_oracle_directions_match_golden(oracle):
     assert int(t.astype(np.uint64).sum() & 0xFFFFFFFF) == int(gold["big_tiles_sum"])
     assert np.array_equal(d[100 * W : 101 * W], gold["big_dist_row100"])
     assert np.array_equal(t[100 * W : 101 * W], gold["big_tiles_row100"])
+
+
+def test_dots_tick_hand_checked_cases(oracle):
+    """"damage monsters" (sources/game/monsters.cpp:101-183), small cases worked out by hand from the source"""
+    n = 5
+    dur = np.zeros((5, n), np.uint32)
+    dmg = np.zeros((5, n), np.uint32)
+    life = np.full(n, 1000, np.int64)
+    alive = np.ones(n, np.uint8)
+    resist = np.zeros(n, np.uint8)
+    money = np.arange(1, n + 1, dtype=np.uint32) * 10
+    # 0: plain physical dot 100 over 4 ticks -> 25 now, 75 left, duration 3
+    dur[0, 0], dmg[0, 0] = 4, 100
+    # 1: fire + water both active -> both cancelled, durations forced to 30 then decremented to 29, no damage
+    dur[1, 1], dmg[1, 1], dur[2, 1], dmg[2, 1] = 5, 500, 2, 300
+    # 2: fire dot strengthened by magic (x2) and resisted (/4): 80/2 = 40 -> 80 -> 20; magic itself 10/1... duration 1 -> dmg 10, super by magic? magic strengthens itself: 10 x2 = 20
+    dur[1, 2], dmg[1, 2], dur[4, 2], dmg[4, 2] = 2, 80, 1, 10
+    resist[2] = 1 << 1
+    # 3: lethal: life 30, physical 64 with duration 0 (instant) -> dies, money 40
+    dmg[0, 3] = 64
+    life[3] = 30
+    # 4: dead already: untouched
+    alive[4] = 0
+    dmg[0, 4] = 999
+    ms, killed = oracle.monsters_dots_tick(dur, dmg, life, alive, resist, money)
+    assert (dur[0, 0], dmg[0, 0], life[0]) == (3, 75, 975)
+    assert (dur[1, 1], dmg[1, 1], dur[2, 1], dmg[2, 1], life[1]) == (29, 0, 29, 0, 1000)
+    # monster 2: fire first (magic still holds 10 > 0 -> super): 40 -> 80 -> /4 = 20; then magic: 10, super by itself (10 - 10 = 0 left, but `super` was read before the subtraction) -> 20
+    assert (dur[1, 2], dmg[1, 2], dur[4, 2], dmg[4, 2], life[2]) == (1, 40, 0, 0, 1000 - 20 - 20)
+    assert (life[3], alive[3]) == (30 - 64, 0) and (ms, killed) == (40, 1)
+    assert (dmg[0, 4], life[4], alive[4]) == (999, 1000, 0)

@@ -758,3 +758,49 @@ def test_sdf_lattice_vs_reference_code(ctx, ref):
     sr, flags = ref.sdf_lattice(KAT_SEED[0] + 9, KAT_SEED[1])
     got = ctx.sdf_lattice(KAT_SEED[0] + 9, KAT_SEED[1], flags)
     assert np.array_equal(got.view(np.uint32), sr.view(np.uint32))
+
+
+# ---------------------------------------------------------------------------------------------------
+# damage-over-time tick on the monster SoA
+# ---------------------------------------------------------------------------------------------------
+def test_dots_tick_bit_exact_and_feeds_the_steering_bits(ctx, oracle):
+    o = oracle.mapgen(KAT_SEED[0] + 2, KAT_SEED[1])
+    W = H = 101
+    ctx.grid_upload(W, H, o["elev"], o["flags"], 50, 50)
+    ctx.waypoints_update(o["wp_tiles"])
+    wv = oracle.waypoints_view(W, H, o["elev"], o["flags"], o["wp_tiles"], o["tiles"], o["dist"], 50, 50)
+    n = 4099
+    rng = np.random.default_rng(17)
+    sp = int(o["agg"][2])
+    path = o["fullpath"][sp][: int(o["fullpath_len"][sp])]
+    tile = rng.choice(path[:-5], n).astype(np.uint32)
+    a = dict(tile=tile.copy(), tileStart=tile.copy(), tileEnd=tile.copy(), timeStart=np.zeros(n, np.uint32), timeEnd=np.zeros(n, np.uint32),
+             bits=np.full(n, 1 << sp, np.uint32), timeToArrive=np.full(n, 5000, np.uint32), damage=np.ones(n, np.uint32), alive=(rng.integers(0, 20, n) > 0).astype(np.uint8))
+    dur = rng.integers(0, 40, (5, n)).astype(np.uint32) * (rng.integers(0, 3, (5, n)) > 0)
+    dmg = rng.integers(0, 3000, (5, n)).astype(np.uint32) * (rng.integers(0, 3, (5, n)) > 0)
+    dmg[0, :7] = 0xFFFFFFF0  # the x2 of a strengthened dot wraps in uint32, as in the reference
+    dmg[3, :7] = 5
+    life = rng.integers(1, 4000, n).astype(np.int64)
+    resist = rng.integers(0, 32, n).astype(np.uint8)
+    money = rng.integers(0, 100, n).astype(np.uint32)
+    ctx.monsters_upload(a)
+    ctx.monsters_dots_upload(dur, dmg, life, resist, money)
+    a["dotflags"] = np.zeros(n, np.uint8)
+    total_g = total_o = 0
+    for t in range(1, 120):
+        # the steering tick reads affected(Fire) / affected(Water): derive them from the oracle's dots like the device does
+        a["dotflags"][:] = (dmg[1] > 0).astype(np.uint8) | ((dmg[2] > 0).astype(np.uint8) << 1)
+        ctx.monsters_tick(t)
+        oracle.monsters_tick(wv, t, a)
+        mg, kg = ctx.monsters_dots_tick()
+        mo, ko = oracle.monsters_dots_tick(dur, dmg, life, a["alive"], resist, money)
+        assert (mg, kg) == (mo, ko), t
+        total_g += kg
+        if t % 17 == 0 or t == 119:
+            d = ctx.monsters_dots_download()
+            assert np.array_equal(d["duration"], dur) and np.array_equal(d["damage"], dmg), t
+            assert np.array_equal(d["life"], life) and np.array_equal(d["alive"], a["alive"]), t
+            got = ctx.monsters_download()
+            for k in got:
+                assert np.array_equal(got[k], a[k]), (t, k)
+    assert total_g > 100
