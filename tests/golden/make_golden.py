@@ -67,11 +67,41 @@ def directions_golden(ref):
     return out
 
 
+def sdf_golden(ref):
+    """Maker::sdf over a reduced marching-cubes lattice from the compiled reference pieces (ref_sdf_lattice)"""
+    res = (44, 10, 40)
+    sdf, flags = ref.sdf_lattice(KAT[0] + 6, KAT[1], res=res)
+    return dict(res=np.array(res, np.int32), seed_k=np.int32(6), sdf=sdf, flags=flags)
+
+
+def game_golden(ref, oracle):
+    """the scripted place/remove workload (mazetd_b200/game_events.py) at reduced size: map from the reference, event loop
+    over the oracle backend of tests/test_gpu_parity.py (which test_oracle_vs_ref.py pins to the reference): final state"""
+    from mazetd_b200 import game_events
+    from test_gpu_parity import _OracleGame
+
+    r = ref.mapgen(KAT[0], KAT[1])
+    sp = int(r["agg"][2])
+    wv = oracle.waypoints_view(101, 101, r["elev"], r["flags"], r["wp_tiles"], r["tiles"], r["dist"], 50, 50)
+    find = lambda pos, bits: tuple(np.array(x, np.uint32) for x in zip(*[oracle.find(wv, int(p), int(b)) for p, b in zip(pos, bits)]))
+    mon = game_events.initial_monsters(600, r["fullpath"][sp][: int(r["fullpath_len"][sp])], r["wp_tiles"], find)
+    og = _OracleGame(oracle, 101, 101, r["elev"], r["flags"], r["wp_tiles"], {k: v.copy() for k, v in mon.items()})
+    stats = game_events.run_events(og, 300)
+    out = {"mon0_" + k: v for k, v in mon.items()}
+    out.update({"mon_" + k: og.a[k] for k in ("tile", "tileStart", "tileEnd", "timeStart", "timeEnd", "bits", "alive")})
+    out.update(flags=og.flags, stats=np.array([stats[k] for k in ("placed", "cleared", "rejected_flags", "rejected_trial")], np.int32),
+               dist_sum=np.array([int(og.w["dist"][l].astype(np.uint64).sum() & 0xFFFFFFFF) for l in range(4)], np.uint32), agg=og.w["agg"], full_distance=og.w["full_distance"])
+    return out
+
+
 def main():
     oracle_lib.build_ref()
     ref = oracle_lib.Ref()
     np.savez_compressed(os.path.join(HERE, "mapgen_k0_k7.npz"), **mapgen_golden(ref))
     np.savez_compressed(os.path.join(HERE, "directions.npz"), **directions_golden(ref))
+    np.savez_compressed(os.path.join(HERE, "sdf_lattice.npz"), **sdf_golden(ref))
+    oracle_lib.build_oracle()
+    np.savez_compressed(os.path.join(HERE, "game_events.npz"), **game_golden(ref, oracle_lib.Oracle()))
     for f in sorted(os.listdir(HERE)):
         print(f, os.path.getsize(os.path.join(HERE, f)))
 

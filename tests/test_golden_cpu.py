@@ -71,3 +71,30 @@ def test_dots_tick_hand_checked_cases(oracle):
     assert (dur[1, 2], dmg[1, 2], dur[4, 2], dmg[4, 2], life[2]) == (1, 40, 0, 0, 1000 - 20 - 20)
     assert (life[3], alive[3]) == (30 - 64, 0) and (ms, killed) == (40, 1)
     assert (dmg[0, 4], life[4], alive[4]) == (999, 1000, 0)
+
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def test_oracle_reproduces_sdf_golden(oracle):
+    """tests/golden/sdf_lattice.npz was written by the compiled reference pieces (make_golden.py: ref_sdf_lattice)"""
+    g = np.load(os.path.join(GOLD, "sdf_lattice.npz"))
+    got = oracle.sdf_lattice(KAT_SEED[0] + int(g["seed_k"]), KAT_SEED[1], 101, 101, 50, 50, g["flags"], res=tuple(int(v) for v in g["res"]))
+    assert np.array_equal(got.view(np.uint32), g["sdf"].view(np.uint32))
+
+
+def test_oracle_reproduces_game_events_golden(oracle):
+    """the scripted place/remove workload at reduced size ends in the committed state (flags, monsters, layers)"""
+    from mazetd_b200 import game_events
+    from test_gpu_parity import _OracleGame
+
+    g = np.load(os.path.join(GOLD, "game_events.npz"))
+    o = oracle.mapgen(KAT_SEED[0], KAT_SEED[1])
+    mon = {k[5:]: g[k].copy() for k in g.files if k.startswith("mon0_")}
+    og = _OracleGame(oracle, 101, 101, o["elev"], o["flags"], o["wp_tiles"], mon)
+    stats = game_events.run_events(og, 300)
+    assert [stats[k] for k in ("placed", "cleared", "rejected_flags", "rejected_trial")] == list(g["stats"])
+    assert np.array_equal(og.flags, g["flags"])
+    for k in ("tile", "tileStart", "tileEnd", "timeStart", "timeEnd", "bits", "alive"):
+        assert np.array_equal(og.a[k], g["mon_" + k]), k
+    assert np.array_equal(og.w["agg"], g["agg"]) and np.array_equal(og.w["full_distance"], g["full_distance"])

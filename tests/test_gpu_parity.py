@@ -804,3 +804,28 @@ def test_dots_tick_bit_exact_and_feeds_the_steering_bits(ctx, oracle):
             for k in got:
                 assert np.array_equal(got[k], a[k]), (t, k)
     assert total_g > 100
+
+
+def test_sdf_and_game_events_against_committed_golden(ctx):
+    """no oracle in the loop: the device against fixtures written from the compiled reference (tests/golden/make_golden.py)"""
+    from mazetd_b200 import game_events
+
+    gold = os.path.join(os.path.dirname(__file__), "golden")
+    g = np.load(os.path.join(gold, "sdf_lattice.npz"))
+    got = ctx.sdf_lattice(KAT_SEED[0] + int(g["seed_k"]), KAT_SEED[1], g["flags"], res=tuple(int(v) for v in g["res"]))
+    assert np.array_equal(got.view(np.uint32), g["sdf"].view(np.uint32))
+
+    g = np.load(os.path.join(gold, "game_events.npz"))
+    m = ctx.mapgen_batch(KAT_SEED[0], KAT_SEED[1], 0, 1, cap=2048)
+    mon = {k[5:]: g[k].copy() for k in g.files if k.startswith("mon0_")}
+    game = game_events.GpuGame(ctx, 101, 101, m["elev"][0], m["flags"][0], m["wp_tiles"][0])
+    ctx.monsters_upload(mon)
+    stats = game_events.run_events(game, 300)
+    assert [stats[k] for k in ("placed", "cleared", "rejected_flags", "rejected_trial")] == list(g["stats"])
+    assert np.array_equal(game.flags, g["flags"])
+    got = ctx.monsters_download()
+    for k in got:
+        assert np.array_equal(got[k], g["mon_" + k]), k
+    w = ctx.waypoints_update(m["wp_tiles"][0], cap=4096)
+    assert np.array_equal(w["agg"], g["agg"]) and np.array_equal(w["full_distance"], g["full_distance"])
+    assert [int(w["dist"][l].astype(np.uint64).sum() & 0xFFFFFFFF) for l in range(4)] == list(g["dist_sum"])
