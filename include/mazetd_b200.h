@@ -135,6 +135,20 @@ int mtd_stripe_finalize_dev(mtd_ctx *ctx, uint32_t *d_tiles);
 int mtd_stripe_round_budget(mtd_ctx *ctx, int32_t rounds);
 int mtd_stripe_pending(mtd_ctx *ctx, uint32_t *items_out);
 
+/* Peer-coupled stripes: the same Directions::update (paths.cpp:24-78) with the ranks advancing round by round inside ONE
+ * kernel run per rank instead of through host-driven sweeps. A border tile stores its boundary row straight into the
+ * neighbour rank's halo copy over NVLink and posts the offered key there; rounds are separated by a barrier across the
+ * ranks (arrive counter in rank 0's block), all ranks follow the same wavefront position and stop in the same round.
+ *   export         creates this rank's peer block (after mtd_stripe_upload*) and returns its CUDA IPC handle (64 bytes)
+ *   connect        maps the blocks of rank-1, rank+1 and rank 0 from `handles` ([world][64], gathered by the caller)
+ *   launch_dev     queues initialisation, the relaxation kernel and the next-hop pass on the context's stream and returns;
+ *                  EVERY rank must call it (a missing rank makes the others give up after 4 s -> MTD_ERR_STATE at finish)
+ *   finish         waits for the stream, reports device status; *rounds_out = rounds the ranks ran */
+int mtd_stripe_peer_export(mtd_ctx *ctx, void *handle64);
+int mtd_stripe_peer_connect(mtd_ctx *ctx, int32_t rank, int32_t world, const void *handles);
+int mtd_stripe_peer_launch_dev(mtd_ctx *ctx, const uint32_t *sources /* host */, int32_t nsrc, uint32_t *d_dist, uint32_t *d_tiles);
+int mtd_stripe_peer_finish(mtd_ctx *ctx, uint32_t *rounds_out);
+
 /* ---- Waypoints::update (sources/map/paths.cpp:82-139) ------------------------------------------ */
 /* n Dijkstra layers + n full-path walks + aggregates, one call.
  *   tiles_out, dist_out : [n][W*H]            (may be NULL)

@@ -63,7 +63,28 @@ namespace mtd
 		const uint32_t *up_row;    // local copy of distance row y0-1 (owned by the rank above), [W]
 		const uint32_t *down_row;  // local copy of distance row y1 (owned by the rank below), [W]
 		const uint32_t *up_wpack;  // wpack row y0-1 (for wd of the edge (y0-1) -> y0), local copy
+		// peer-coupled stripes (ctl0 != null): the stripes of all ranks advance round by round inside ONE kernel run. A visit
+		// of a border tile stores its boundary row straight into the neighbour rank's halo copy (up_row / down_row above then
+		// point into this rank's peer block, written by the neighbours over NVLink) and posts the offered key in the
+		// neighbour's act array; rounds are separated by a barrier across the ranks (arrive counter on rank 0).
+		uint32_t *peer_up_halo;    // the rank above: its copy of my first row [W]           (null: no rank above)
+		uint32_t *peer_up_act;     // the rank above: keys offered to its last tile row [tilesX]
+		uint32_t *peer_down_halo;  // the rank below: its copy of my last row [W]
+		uint32_t *peer_down_act;   // the rank below: keys offered to its first tile row [tilesX]
+		uint32_t *act_up;          // mine: keys the rank above offered to my first tile row (MTD_INF: none)
+		uint32_t *act_down;        // mine: keys the rank below offered to my last tile row
+		uint32_t *ctl0;            // rank 0's control words (PEER_* below)
+		uint32_t *ctl;             // my control words (local scratch: PEER_GPENDING, PEER_EPOCH)
+		int world, rank;
 	};
+
+	// control words at the head of a peer block
+	constexpr int PEER_ARRIVE = 0;    // cumulative arrivals at the cross-rank barrier (rank 0's block only)
+	constexpr int PEER_PENDING = 4;   // [3] work items queued on all ranks for round r (slot r % 3)
+	constexpr int PEER_MINKEY = 8;    // [3] smallest key on all ranks' lists
+	constexpr int PEER_GPENDING = 12; // local: the value read from PEER_PENDING for the coming round
+	constexpr int PEER_EPOCH = 13;    // local: barriers this rank has passed since the block was created
+	constexpr int PEER_CTL_WORDS = 16;
 
 	// ---- edge weights -------------------------------------------------------------------------------
 	__global__ void k_edge_weights(int W, int Hl, const int16_t *__restrict__ elev, const int16_t *__restrict__ elev_below /* row after the stripe or null */, const uint16_t *__restrict__ flags, uint32_t *__restrict__ wpack, uint8_t *__restrict__ blocked)
@@ -95,6 +116,18 @@ namespace mtd
 			const uint32_t v = blocked[i] ? 0u : MTD_INF;
 			for (int l = 0; l < nlayers; l++)
 				__stcg(dist + (size_t)l * layer_stride + i, v);
+		}
+	}
+
+	// four tiles per thread (n % 4 == 0, 16-byte aligned bases)
+	__global__ void k_big_init4(uint32_t *__restrict__ dist, size_t layer_stride, int nlayers, size_t n4, const uint8_t *__restrict__ blocked)
+	{
+		for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < n4; q += (size_t)gridDim.x * blockDim.x)
+		{
+			const uchar4 b = reinterpret_cast<const uchar4 *>(blocked)[q];
+			const uint4 v = make_uint4(b.x ? 0u : MTD_INF, b.y ? 0u : MTD_INF, b.z ? 0u : MTD_INF, b.w ? 0u : MTD_INF);
+			for (int l = 0; l < nlayers; l++)
+				__stcg(reinterpret_cast<uint4 *>(dist + (size_t)l * layer_stride) + q, v);
 		}
 	}
 
@@ -282,6 +315,125 @@ namespace mtd
 			}
 			if (tiles)
 				__stcs(tiles + i, best);
+		}
+	}
+
+	// The same pass, four tiles of one row per thread (W % 4 == 0, 16-byte aligned bases): the own row, the rows above and
+	// below and the two weight rows move as 16-byte vectors, so the kernel issues a quarter of the load instructions and
+	// streams at HBM speed instead of queueing in the load/store unit.
+	__global__ void k_big_finalize4(int W, int Hl, int y0, int H, uint32_t *__restrict__ dist_base, size_t layer_stride, const uint32_t *__restrict__ wpack, const uint8_t *__restrict__ blocked, const uint32_t *__restrict__ sources_base, int nsrc, const uint32_t *__restrict__ up_row, const uint32_t *__restrict__ up_wpack, const uint32_t *__restrict__ down_row, uint32_t *__restrict__ tiles_base, size_t tiles_stride)
+	{
+		__shared__ uint32_t filter[64];
+		const int layer = blockIdx.y;
+		uint32_t *dist = dist_base + (size_t)layer * layer_stride;
+		uint32_t *tiles = tiles_base ? tiles_base + (size_t)layer * tiles_stride : nullptr;
+		const uint32_t *sources = sources_base + (size_t)layer * nsrc;
+		for (int i = threadIdx.x; i < 64; i += blockDim.x)
+			filter[i] = 0u;
+		__syncthreads();
+		for (int s = threadIdx.x; s < nsrc; s += blockDim.x)
+		{
+			const uint32_t h = (sources[s] * 2654435761u) >> 21;
+			atomicOr(&filter[h >> 5], 1u << (h & 31u));
+		}
+		__syncthreads();
+		auto is_source = [&](uint32_t g) -> bool
+		{
+			const uint32_t h = (g * 2654435761u) >> 21;
+			if (!((filter[h >> 5] >> (h & 31u)) & 1u))
+				return false;
+			for (int s = 0; s < nsrc; s++)
+				if (sources[s] == g)
+					return true;
+			return false;
+		};
+		const int QW = W >> 2;
+		const size_t total = (size_t)QW * Hl;
+		const uint4 inf4 = make_uint4(MTD_INF, MTD_INF, MTD_INF, MTD_INF);
+		const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
+		for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += (size_t)gridDim.x * blockDim.x)
+		{
+			const int x = (int)(q % (size_t)QW) << 2;
+			const int ly = (int)(q / (size_t)QW);
+			const int gy = ly + y0;
+			const size_t i = (size_t)ly * W + x;
+			const uint32_t g = (uint32_t)((size_t)gy * W + x);
+			const uint4 dq = *reinterpret_cast<const uint4 *>(dist + i);
+			uint32_t dv[4] = { dq.x, dq.y, dq.z, dq.w };
+			uint32_t best[4] = { MTD_INF, MTD_INF, MTD_INF, MTD_INF };
+			bool any_zero = false, any_live = false;
+#pragma unroll
+			for (int j = 0; j < 4; j++)
+			{
+				any_zero |= dv[j] == 0u;
+				any_live |= dv[j] != 0u && dv[j] != MTD_INF;
+			}
+			if (any_zero)
+			{
+				// source (keeps 0, no next hop: paths.cpp:49) or parked blocked tile (never relaxed: paths.cpp:65-67)
+				const uchar4 bq = *reinterpret_cast<const uchar4 *>(blocked + i);
+				const uint8_t b[4] = { bq.x, bq.y, bq.z, bq.w };
+#pragma unroll
+				for (int j = 0; j < 4; j++)
+					if (dv[j] == 0u && b[j] && !is_source(g + (uint32_t)j))
+						dist[i + j] = MTD_INF;
+			}
+			if (any_live && tiles)
+			{
+				uint4 du4 = inf4, dd4 = inf4, wu4 = zero4;
+				if (gy > 0)
+				{
+					if (ly > 0)
+					{
+						du4 = *reinterpret_cast<const uint4 *>(dist + i - W);
+						wu4 = *reinterpret_cast<const uint4 *>(wpack + i - W);
+					}
+					else if (up_row)
+					{
+						du4 = *reinterpret_cast<const uint4 *>(up_row + x);
+						if (up_wpack)
+							wu4 = *reinterpret_cast<const uint4 *>(up_wpack + x);
+					}
+				}
+				if (gy < H - 1)
+				{
+					if (ly < Hl - 1)
+						dd4 = *reinterpret_cast<const uint4 *>(dist + i + W);
+					else if (down_row)
+						dd4 = *reinterpret_cast<const uint4 *>(down_row + x);
+				}
+				const uint4 wq = *reinterpret_cast<const uint4 *>(wpack + i);
+				const uint32_t wp[4] = { wq.x, wq.y, wq.z, wq.w };
+				const uint32_t du[4] = { du4.x, du4.y, du4.z, du4.w };
+				const uint32_t dd[4] = { dd4.x, dd4.y, dd4.z, dd4.w };
+				const uint32_t wu[4] = { wu4.x, wu4.y, wu4.z, wu4.w };
+				const uint32_t dleft = x > 0 ? dist[i - 1] : MTD_INF;
+				const uint32_t wleft = x > 0 ? wpack[i - 1] & 0xFFFFu : 0u;
+				const uint32_t dright = x + 4 < W ? dist[i + 4] : MTD_INF;
+#pragma unroll
+				for (int j = 0; j < 4; j++)
+				{
+					const uint32_t v = dv[j];
+					if (v == 0u || v == MTD_INF)
+						continue;
+					uint32_t bestd = MTD_INF;
+					auto cand = [&](uint32_t dn, uint32_t w, uint32_t ug)
+					{
+						if (dn != MTD_INF && dn + MIN_EDGE + w == v && dn < bestd && (dn != 0u || is_source(ug)))
+						{
+							bestd = dn;
+							best[j] = ug;
+						}
+					};
+					// ascending tile index, so equal labels resolve to the smaller index: up, left, right, down
+					cand(du[j], wu[j] >> 16, g + (uint32_t)j - (uint32_t)W);
+					cand(j > 0 ? dv[j - 1] : dleft, j > 0 ? wp[j - 1] & 0xFFFFu : wleft, g + (uint32_t)j - 1u);
+					cand(j < 3 ? dv[j + 1] : dright, wp[j] & 0xFFFFu, g + (uint32_t)j + 1u);
+					cand(dd[j], wp[j] >> 16, g + (uint32_t)j + (uint32_t)W);
+				}
+			}
+			if (tiles)
+				__stcs(reinterpret_cast<uint4 *>(tiles + i), make_uint4(best[0], best[1], best[2], best[3]));
 		}
 	}
 }

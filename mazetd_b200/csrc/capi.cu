@@ -122,6 +122,12 @@ struct mtd_ctx
 	uint32_t stripe_pending = 0;
 	uint32_t *stripe_dist = nullptr;                 // caller-owned [sy1 - sy0][W]
 	DevBuf<uint32_t> halo_up, halo_down, up_wpack;   // local copies of the neighbour stripes' boundary rows; wpack of row sy0-1
+	// peer-coupled stripes: one block per rank that the neighbour ranks write into (layout: peer_layout())
+	DevBuf<uint32_t> peer_blk;
+	uint32_t *peer_above = nullptr, *peer_below = nullptr, *peer_root = nullptr; // the other ranks' blocks, mapped here
+	bool peer_ipc = false;      // mapped with cudaIpcOpenMemHandle (to be closed)
+	bool peer_linked = false, peer_on = false;
+	int peer_rank = 0, peer_world = 1;
 	DevBuf<uint8_t> up_blocked;
 
 	// staging of mtd_mapgen_batch (host outputs): two buffer sets, compute overlaps the drain of the previous chunk
@@ -263,6 +269,8 @@ namespace
 			return fail(ctx, MTD_ERR_STATE, "a generated map has no valid tile (the reference would never return from findSpawnPoint)");
 		if (st & ST_PATH_TRUNC)
 			return fail(ctx, MTD_ERR_CAPACITY, "a full path is longer than fullpath_cap (lengths are exact, tiles were truncated)");
+		if (st & ST_PEER_TIMEOUT)
+			return fail(ctx, MTD_ERR_STATE, "peer-coupled stripes: another rank did not reach a round barrier within 4 s (not launched, or its kernel is not resident)");
 		return MTD_OK;
 	}
 
@@ -306,6 +314,12 @@ namespace
 		size_t b = (n + threads - 1) / threads;
 		const size_t cap = (size_t)ctx->sms * per_sm;
 		return (int)(b < cap ? (b ? b : 1) : cap);
+	}
+
+	// k_big_finalize4 moves rows as 16-byte vectors: the width and every base it touches must allow that
+	bool finalize_vec_ok(mtd_ctx *ctx, const void *d_dist, const void *d_tiles)
+	{
+		return ctx->W % 4 == 0 && ctx->W >= 4 && (((uintptr_t)d_dist | (uintptr_t)d_tiles) & 15u) == 0;
 	}
 
 	// ---- small path launcher -------------------------------------------------------------------------
@@ -403,11 +417,14 @@ namespace
 		BigParams Pk = P;
 		int round0 = round;
 		void *args[] = { (void *)&Pk, (void *)&round0, (void *)&max_rounds, (void *)&d_out };
+		const int ctas = ctx->sms * ctas_per_sm;
 		{
 			ProfScope prof(ctx, MTD_K_BIG_RELAX);
-			CU(cudaLaunchCooperativeKernel((const void *)k_tile_rounds<BIG_TS, BIG_WARPS>, dim3((unsigned)(ctx->sms * ctas_per_sm)), dim3(BIG_WARPS * 32), args, smem, ctx->stream));
+			CU(cudaLaunchCooperativeKernel((const void *)k_tile_rounds<BIG_TS, BIG_WARPS>, dim3((unsigned)ctas), dim3(BIG_WARPS * 32), args, smem, ctx->stream));
 			LAUNCHED();
 		}
+		if (P.ctl0)
+			return MTD_OK; // peer-coupled: the ranks stop together inside the kernel; the caller waits in mtd_stripe_peer_finish
 		CU(cudaStreamSynchronize(ctx->stream));
 		pending = ctx->hflags->round_out[0];
 		round = (int)ctx->hflags->round_out[1];
@@ -446,7 +463,10 @@ namespace
 		}
 		{
 			ProfScope prof(ctx, MTD_K_BIG_PREPARE);
-			k_big_init<<<grid_blocks(ctx, ctx->T, 256), 256, 0, ctx->stream>>>(d_dist, ctx->T, nlayers, ctx->T, ctx->blocked.p);
+			if (finalize_vec_ok(ctx, d_dist, nullptr))
+				k_big_init4<<<grid_blocks(ctx, ctx->T / 4, 256), 256, 0, ctx->stream>>>(d_dist, ctx->T, nlayers, ctx->T / 4, ctx->blocked.p);
+			else
+				k_big_init<<<grid_blocks(ctx, ctx->T, 256), 256, 0, ctx->stream>>>(d_dist, ctx->T, nlayers, ctx->T, ctx->blocked.p);
 			LAUNCHED();
 		}
 
@@ -502,8 +522,16 @@ namespace
 #endif
 		{
 			ProfScope prof(ctx, MTD_K_BIG_DIRECTIONS);
-			dim3 grid((unsigned)grid_blocks(ctx, ctx->T, 256, nlayers > 4 ? 2 : 8), (unsigned)nlayers);
-			k_big_finalize<<<grid, 256, 0, ctx->stream>>>(ctx->W, ctx->H, 0, ctx->H, d_dist, ctx->T, ctx->wpack.p, ctx->blocked.p, ctx->sources.p, nsrc, nullptr, nullptr, nullptr, d_tiles, ctx->T);
+			if (finalize_vec_ok(ctx, d_dist, d_tiles))
+			{
+				dim3 grid((unsigned)grid_blocks(ctx, ctx->T / 4, 256, nlayers > 4 ? 2 : 8), (unsigned)nlayers);
+				k_big_finalize4<<<grid, 256, 0, ctx->stream>>>(ctx->W, ctx->H, 0, ctx->H, d_dist, ctx->T, ctx->wpack.p, ctx->blocked.p, ctx->sources.p, nsrc, nullptr, nullptr, nullptr, d_tiles, ctx->T);
+			}
+			else
+			{
+				dim3 grid((unsigned)grid_blocks(ctx, ctx->T, 256, nlayers > 4 ? 2 : 8), (unsigned)nlayers);
+				k_big_finalize<<<grid, 256, 0, ctx->stream>>>(ctx->W, ctx->H, 0, ctx->H, d_dist, ctx->T, ctx->wpack.p, ctx->blocked.p, ctx->sources.p, nsrc, nullptr, nullptr, nullptr, d_tiles, ctx->T);
+			}
 			LAUNCHED();
 		}
 		if (extra_blocked != MTD_M)
@@ -516,6 +544,23 @@ namespace
 	}
 
 	// ---- row stripe of a larger grid (one rank per stripe) -------------------------------
+	// words of a peer block: control, the two halo rows the neighbours write, the two key arrays they post offers in
+	struct PeerLayout
+	{
+		size_t halo_up, halo_down, act_up, act_down, words;
+	};
+	PeerLayout peer_layout(int W)
+	{
+		const size_t Wp = ((size_t)W + 3) & ~(size_t)3, Tp = (((size_t)W + BIG_TS - 1) / BIG_TS + 3) & ~(size_t)3;
+		PeerLayout L;
+		L.halo_up = PEER_CTL_WORDS;
+		L.halo_down = L.halo_up + Wp;
+		L.act_up = L.halo_down + Wp;
+		L.act_down = L.act_up + Tp;
+		L.words = L.act_down + Tp;
+		return L;
+	}
+
 	BigParams stripe_params(mtd_ctx *ctx)
 	{
 		BigParams P;
@@ -548,6 +593,24 @@ namespace
 		P.up_row = ctx->sy0 > 0 ? ctx->halo_up.p : nullptr;
 		P.up_wpack = ctx->sy0 > 0 ? ctx->up_wpack.p : nullptr;
 		P.down_row = ctx->sy1 < ctx->sH ? ctx->halo_down.p : nullptr;
+		if (ctx->peer_on)
+		{
+			const PeerLayout L = peer_layout(ctx->W);
+			uint32_t *mine = ctx->peer_blk.p;
+			P.up_row = ctx->sy0 > 0 ? mine + L.halo_up : nullptr;
+			P.down_row = ctx->sy1 < ctx->sH ? mine + L.halo_down : nullptr;
+			P.act_up = ctx->peer_above ? mine + L.act_up : nullptr;
+			P.act_down = ctx->peer_below ? mine + L.act_down : nullptr;
+			// my first row is the "down" halo of the rank above, my last row the "up" halo of the rank below
+			P.peer_up_halo = ctx->peer_above ? ctx->peer_above + L.halo_down : nullptr;
+			P.peer_up_act = ctx->peer_above ? ctx->peer_above + L.act_down : nullptr;
+			P.peer_down_halo = ctx->peer_below ? ctx->peer_below + L.halo_up : nullptr;
+			P.peer_down_act = ctx->peer_below ? ctx->peer_below + L.act_up : nullptr;
+			P.ctl0 = ctx->peer_root;
+			P.ctl = mine;
+			P.world = ctx->peer_world;
+			P.rank = ctx->peer_rank;
+		}
 		return P;
 	}
 
@@ -758,6 +821,11 @@ extern "C" int mtd_create(mtd_ctx **out, int device, void *stream)
 	return MTD_OK;
 }
 
+namespace
+{
+	void peer_unlink(mtd_ctx *ctx);
+}
+
 extern "C" void mtd_destroy(mtd_ctx *ctx)
 {
 	if (!ctx)
@@ -772,6 +840,8 @@ extern "C" void mtd_destroy(mtd_ctx *ctx)
 	ctx->list1.release();
 	ctx->list2.release();
 	ctx->tilekey.release();
+	peer_unlink(ctx);
+	ctx->peer_blk.release();
 	ctx->halo_up.release();
 	ctx->halo_down.release();
 	ctx->up_wpack.release();
@@ -1050,12 +1120,42 @@ extern "C" int mtd_stripe_upload_dev(mtd_ctx *ctx, int32_t W, int32_t H, int32_t
 	return stripe_common(ctx, W, H, y0, y1, d_elev_rows, d_flags_rows, cudaMemcpyDeviceToDevice);
 }
 
+namespace
+{
+	int stripe_prepare(mtd_ctx *ctx, const uint32_t *sources, int32_t nsrc, uint32_t *d_dist, bool peer);
+
+	// work-lists and per-tile words of a stripe (allocations may wait for the device: peer-coupled stripes make them when
+	// they connect, not between the launches of ranks that already wait for each other)
+	int stripe_reserve(mtd_ctx *ctx, int nsrc)
+	{
+		const size_t nt = (size_t)ctx->tilesX * ctx->tilesY;
+		CU(ctx->list0.reserve(nt));
+		CU(ctx->list1.reserve(nt));
+		CU(ctx->list2.reserve(nt));
+		CU(ctx->stamp.reserve(nt));
+		CU(ctx->tilekey.reserve(nt));
+		CU(ctx->sources.reserve(nsrc));
+		return MTD_OK;
+	}
+}
+
 extern "C" int mtd_stripe_begin_dev(mtd_ctx *ctx, const uint32_t *sources, int32_t nsrc, uint32_t *d_dist)
 {
 	if (!ctx)
 		return MTD_ERR_ARG;
 	std::lock_guard<std::mutex> lk(ctx->mu);
 	DeviceGuard g(ctx->device);
+	int rc = stripe_prepare(ctx, sources, nsrc, d_dist, false);
+	if (rc)
+		return rc;
+	return stripe_run(ctx, stripe_params(ctx));
+}
+
+namespace
+{
+// distances := m / parked, sources seeded, border tiles under halo sources queued; everything on the context's stream
+int stripe_prepare(mtd_ctx *ctx, const uint32_t *sources, int32_t nsrc, uint32_t *d_dist, bool peer)
+{
 	if (!ctx->have_grid || !ctx->stripe)
 		return fail(ctx, MTD_ERR_STATE, "no stripe uploaded");
 	if (!sources || nsrc < 1 || !d_dist)
@@ -1064,26 +1164,30 @@ extern "C" int mtd_stripe_begin_dev(mtd_ctx *ctx, const uint32_t *sources, int32
 		if ((uint64_t)sources[i] >= (uint64_t)ctx->W * (uint64_t)ctx->sH)
 			return fail(ctx, MTD_ERR_ARG, "source tile %u outside the grid", sources[i]);
 	const size_t nt = (size_t)ctx->tilesX * ctx->tilesY;
-	CU(ctx->list0.reserve(nt));
-	CU(ctx->list1.reserve(nt));
-	CU(ctx->list2.reserve(nt));
-	CU(ctx->stamp.reserve(nt));
-	CU(ctx->tilekey.reserve(nt));
-	CU(ctx->sources.reserve(nsrc));
+	int rc = stripe_reserve(ctx, nsrc);
+	if (rc)
+		return rc;
 	CU(cudaMemcpyAsync(ctx->sources.p, sources, (size_t)nsrc * 4, cudaMemcpyHostToDevice, ctx->stream));
 	CU(cudaMemsetAsync(ctx->stamp.p, 0, nt * 4, ctx->stream));
 	CU(cudaMemsetAsync(ctx->tilekey.p, 0xFF, nt * 4, ctx->stream));
 	CU(cudaMemsetAsync(ctx->counters.p, 0, 16 * 4, ctx->stream));
 		CU(cudaMemsetAsync(ctx->counters.p + 8, 0xFF, 3 * 4, ctx->stream)); // minkey[3] = m
-	CU(cudaMemsetAsync(ctx->halo_up.p, 0xFF, (size_t)ctx->W * 4, ctx->stream));
-	CU(cudaMemsetAsync(ctx->halo_down.p, 0xFF, (size_t)ctx->W * 4, ctx->stream));
+	if (!peer)
+	{
+		CU(cudaMemsetAsync(ctx->halo_up.p, 0xFF, (size_t)ctx->W * 4, ctx->stream));
+		CU(cudaMemsetAsync(ctx->halo_down.p, 0xFF, (size_t)ctx->W * 4, ctx->stream));
+	}
+	ctx->peer_on = peer; // peer-coupled: the halo rows live in the peer block and the neighbours fill them
 	ctx->stripe_dist = d_dist;
 	ctx->stripe_nsrc = nsrc;
 	ctx->stripe_round = 0;
 	ctx->stripe_pending = 0;
 	{
 		ProfScope prof(ctx, MTD_K_BIG_PREPARE);
-		k_big_init<<<grid_blocks(ctx, ctx->T, 256), 256, 0, ctx->stream>>>(d_dist, ctx->T, 1, ctx->T, ctx->blocked.p);
+		if (finalize_vec_ok(ctx, d_dist, nullptr))
+			k_big_init4<<<grid_blocks(ctx, ctx->T / 4, 256), 256, 0, ctx->stream>>>(d_dist, ctx->T, 1, ctx->T / 4, ctx->blocked.p);
+		else
+			k_big_init<<<grid_blocks(ctx, ctx->T, 256), 256, 0, ctx->stream>>>(d_dist, ctx->T, 1, ctx->T, ctx->blocked.p);
 		LAUNCHED();
 	}
 	const BigParams P = stripe_params(ctx);
@@ -1091,7 +1195,8 @@ extern "C" int mtd_stripe_begin_dev(mtd_ctx *ctx, const uint32_t *sources, int32
 	LAUNCHED();
 	k_stripe_seed_halo<BIG_TS><<<(nsrc + 127) / 128, 128, 0, ctx->stream>>>(P);
 	LAUNCHED();
-	return stripe_run(ctx, P);
+	return MTD_OK;
+}
 }
 
 extern "C" int mtd_stripe_exchange_dev(mtd_ctx *ctx, const uint32_t *d_row_above, const uint32_t *d_row_below, uint32_t *improved_out)
@@ -1155,11 +1260,159 @@ extern "C" int mtd_stripe_finalize_dev(mtd_ctx *ctx, uint32_t *d_tiles)
 	const BigParams P = stripe_params(ctx);
 	{
 		ProfScope prof(ctx, MTD_K_BIG_DIRECTIONS);
-		k_big_finalize<<<dim3((unsigned)grid_blocks(ctx, ctx->T, 256, 8), 1u), 256, 0, ctx->stream>>>(ctx->W, ctx->H, ctx->sy0, ctx->sH, ctx->stripe_dist, ctx->T, ctx->wpack.p, ctx->blocked.p, ctx->sources.p, ctx->stripe_nsrc, P.up_row, P.up_wpack, P.down_row, d_tiles, ctx->T);
+		if (finalize_vec_ok(ctx, ctx->stripe_dist, d_tiles))
+			k_big_finalize4<<<dim3((unsigned)grid_blocks(ctx, ctx->T / 4, 256, 8), 1u), 256, 0, ctx->stream>>>(ctx->W, ctx->H, ctx->sy0, ctx->sH, ctx->stripe_dist, ctx->T, ctx->wpack.p, ctx->blocked.p, ctx->sources.p, ctx->stripe_nsrc, P.up_row, P.up_wpack, P.down_row, d_tiles, ctx->T);
+		else
+			k_big_finalize<<<dim3((unsigned)grid_blocks(ctx, ctx->T, 256, 8), 1u), 256, 0, ctx->stream>>>(ctx->W, ctx->H, ctx->sy0, ctx->sH, ctx->stripe_dist, ctx->T, ctx->wpack.p, ctx->blocked.p, ctx->sources.p, ctx->stripe_nsrc, P.up_row, P.up_wpack, P.down_row, d_tiles, ctx->T);
 		LAUNCHED();
 	}
 	ctx->stripe_dist = nullptr;
 	return MTD_OK;
+}
+
+// ---- peer-coupled stripes -----------------------------------------------------------------------------
+namespace
+{
+	int peer_block_create(mtd_ctx *ctx)
+	{
+		if (!ctx->have_grid || !ctx->stripe)
+			return fail(ctx, MTD_ERR_STATE, "no stripe uploaded");
+		const PeerLayout L = peer_layout(ctx->W);
+		if (ctx->peer_blk.cap >= L.words)
+			return MTD_OK;
+		CU(ctx->peer_blk.reserve(L.words));
+		// halo rows and key arrays: m (nothing offered); control words: 0, smallest keys m
+		CU(cudaMemsetAsync(ctx->peer_blk.p, 0xFF, L.words * 4, ctx->stream));
+		CU(cudaMemsetAsync(ctx->peer_blk.p, 0, PEER_CTL_WORDS * 4, ctx->stream));
+		CU(cudaMemsetAsync(ctx->peer_blk.p + PEER_MINKEY, 0xFF, 3 * 4, ctx->stream));
+		CU(cudaStreamSynchronize(ctx->stream));
+		return MTD_OK;
+	}
+
+	void peer_unlink(mtd_ctx *ctx)
+	{
+		if (ctx->peer_ipc)
+		{
+			uint32_t *opened[3] = { ctx->peer_above, ctx->peer_below, ctx->peer_root };
+			for (int i = 0; i < 3; i++)
+			{
+				bool dup = opened[i] == nullptr || opened[i] == ctx->peer_blk.p;
+				for (int j = 0; j < i; j++)
+					dup |= opened[j] == opened[i];
+				if (!dup)
+					cudaIpcCloseMemHandle(opened[i]);
+			}
+		}
+		ctx->peer_above = ctx->peer_below = ctx->peer_root = nullptr;
+		ctx->peer_ipc = ctx->peer_linked = ctx->peer_on = false;
+	}
+}
+
+extern "C" int mtd_stripe_peer_export(mtd_ctx *ctx, void *handle64)
+{
+	if (!ctx || !handle64)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	static_assert(sizeof(cudaIpcMemHandle_t) == 64, "the ABI passes IPC handles as 64 opaque bytes");
+	int rc = peer_block_create(ctx);
+	if (rc)
+		return rc;
+	cudaIpcMemHandle_t h;
+	CU(cudaIpcGetMemHandle(&h, ctx->peer_blk.p));
+	memcpy(handle64, &h, 64);
+	return MTD_OK;
+}
+
+extern "C" int mtd_stripe_peer_connect(mtd_ctx *ctx, int32_t rank, int32_t world, const void *handles)
+{
+	if (!ctx || !handles || world < 1 || rank < 0 || rank >= world)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	int rc = peer_block_create(ctx);
+	if (rc)
+		return rc;
+	peer_unlink(ctx);
+	ctx->peer_ipc = true;
+	auto open = [&](int r, uint32_t *&out) -> int
+	{
+		if (r == rank)
+		{
+			out = ctx->peer_blk.p;
+			return MTD_OK;
+		}
+		cudaIpcMemHandle_t h;
+		memcpy(&h, (const uint8_t *)handles + (size_t)r * 64, 64);
+		void *p = nullptr;
+		CU(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+		out = (uint32_t *)p;
+		return MTD_OK;
+	};
+	if (rank > 0 && (rc = open(rank - 1, ctx->peer_above)))
+		return rc;
+	if (rank < world - 1 && (rc = open(rank + 1, ctx->peer_below)))
+		return rc;
+	if (rank == 1)
+		ctx->peer_root = ctx->peer_above; // a block can be mapped once per process
+	else if ((rc = open(0, ctx->peer_root)))
+		return rc;
+	if ((rc = stripe_reserve(ctx, 4096)))
+		return rc;
+	ctx->peer_rank = rank;
+	ctx->peer_world = world;
+	ctx->peer_linked = true;
+	return MTD_OK;
+}
+
+extern "C" int mtd_stripe_peer_launch_dev(mtd_ctx *ctx, const uint32_t *sources, int32_t nsrc, uint32_t *d_dist, uint32_t *d_tiles)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (!ctx->peer_linked)
+		return fail(ctx, MTD_ERR_STATE, "stripe_peer_launch before stripe_peer_connect");
+	int rc = stripe_prepare(ctx, sources, nsrc, d_dist, true);
+	if (rc)
+		return rc;
+	const BigParams P = stripe_params(ctx);
+	int round = 0;
+	uint32_t pending = 0;
+	rc = run_rounds(ctx, P, round, 0, pending); // returns once the kernel is queued: the ranks stop together on the device
+	if (rc)
+		return rc;
+	{
+		ProfScope prof(ctx, MTD_K_BIG_DIRECTIONS);
+		if (finalize_vec_ok(ctx, d_dist, d_tiles))
+			k_big_finalize4<<<dim3((unsigned)grid_blocks(ctx, ctx->T / 4, 256, 8), 1u), 256, 0, ctx->stream>>>(ctx->W, ctx->H, ctx->sy0, ctx->sH, d_dist, ctx->T, ctx->wpack.p, ctx->blocked.p, ctx->sources.p, nsrc, P.up_row, P.up_wpack, P.down_row, d_tiles, ctx->T);
+		else
+			k_big_finalize<<<dim3((unsigned)grid_blocks(ctx, ctx->T, 256, 8), 1u), 256, 0, ctx->stream>>>(ctx->W, ctx->H, ctx->sy0, ctx->sH, d_dist, ctx->T, ctx->wpack.p, ctx->blocked.p, ctx->sources.p, nsrc, P.up_row, P.up_wpack, P.down_row, d_tiles, ctx->T);
+		LAUNCHED();
+	}
+	ctx->stripe_dist = nullptr;
+	ctx->peer_on = false;
+	return MTD_OK;
+}
+
+extern "C" int mtd_stripe_peer_finish(mtd_ctx *ctx, uint32_t *rounds_out)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	const int rc = sync_and_status(ctx);
+	ctx->last_rounds = ctx->hflags->round_out[1];
+	if (rounds_out)
+		*rounds_out = ctx->last_rounds;
+	if (rc == MTD_ERR_STATE && ctx->peer_root && ctx->peer_blk.p)
+	{
+		uint32_t root[PEER_CTL_WORDS] = { 0 }, mine[PEER_CTL_WORDS] = { 0 };
+		cudaMemcpy(root, ctx->peer_root, sizeof(root), cudaMemcpyDeviceToHost);
+		cudaMemcpy(mine, ctx->peer_blk.p, sizeof(mine), cudaMemcpyDeviceToHost);
+		return fail(ctx, MTD_ERR_STATE, "peer-coupled stripes: another rank did not reach a round barrier within 4 s (not launched, or its kernel is not resident); rank %d of %d, barriers passed %u, arrivals counted %u, rounds %u", ctx->peer_rank, ctx->peer_world, mine[PEER_EPOCH], root[PEER_ARRIVE], ctx->last_rounds);
+	}
+	return rc;
 }
 
 extern "C" int mtd_grid_set_flags(mtd_ctx *ctx, uint32_t tile, uint16_t flags)

@@ -39,6 +39,41 @@ namespace mtd
 		return r;
 	}
 
+	// ---- peer-coupled stripes: a barrier across the ranks, on a cumulative arrive counter in rank 0's peer block ----
+	__device__ __forceinline__ uint32_t ld_sys(const uint32_t *p)
+	{
+		uint32_t v;
+		asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+		return v;
+	}
+
+	__device__ __forceinline__ unsigned long long global_timer_ns()
+	{
+		unsigned long long t;
+		asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+		return t;
+	}
+
+	// one thread per rank. false: the other ranks did not arrive within 4 s (a rank died or never launched)
+	__device__ inline bool peer_barrier(const BigParams &P, uint32_t &epoch, bool &dead)
+	{
+		if (dead)
+			return false; // one timeout is final: do not wait again
+		__threadfence_system();
+		atomicAdd_system(P.ctl0 + PEER_ARRIVE, 1u);
+		epoch++;
+		const uint32_t target = epoch * (uint32_t)P.world;
+		const unsigned long long t0 = global_timer_ns();
+		while ((int32_t)(ld_sys(P.ctl0 + PEER_ARRIVE) - target) < 0)
+			if (global_timer_ns() - t0 > 4000000000ull)
+			{
+				dead = true;
+				return false;
+			}
+		__threadfence_system();
+		return true;
+	}
+
 	// Runs rounds `round0`, `round0 + 1`, ... until the work-list is empty or `max_rounds` rounds are done. COOPERATIVE launch:
 	// every CTA is resident and the rounds are separated by grid.sync(). out[0] = items queued for the next round,
 	// out[1] = index of the next round.
@@ -63,6 +98,93 @@ namespace mtd
 #ifdef MTD_TIMING
 		unsigned long long tacc[8] = { 0, 0, 0, 0, 0, 0, 0, 0 }; // developer probe: cycles per phase, buckets, queue entries of this warp
 #endif
+
+		// Peer-coupled stripes: between two rounds every rank (1) waits until the boundary rows and keys of all ranks have
+		// landed, (2) queues the border tiles its neighbours offered a label to, (3) adds its queue length and smallest key
+		// to rank 0's totals, (4) waits again and reads the totals: all ranks see the same wavefront position and stop in
+		// the same round.
+		uint32_t epoch = 0;
+		bool peer_dead = false;
+		auto peer_round_sync = [&](int r_next, bool first)
+		{
+			__threadfence_system();
+			grid.sync();
+			if (blockIdx.x == 0)
+			{
+				const int slot = r_next % 3;
+				bool ok = true;
+				if (threadIdx.x == 0)
+				{
+					if (P.rank == 0)
+						for (int k = 0; k < 3; k++)
+							if (first || k == (r_next + 1) % 3) // last read two syncs ago: every rank has passed a barrier since
+							{
+								P.ctl0[PEER_PENDING + k] = 0u;
+								P.ctl0[PEER_MINKEY + k] = MTD_INF;
+							}
+					ok = peer_barrier(P, epoch, peer_dead);
+				}
+				__syncthreads();
+				for (int tx = (int)threadIdx.x; tx < P.tilesX; tx += (int)blockDim.x)
+				{
+					if (P.act_up)
+					{
+						const uint32_t k = atomicExch(P.act_up + tx, MTD_INF);
+						if (k != MTD_INF)
+							activate_item(P, 0, tx, 0, r_next - 1, k);
+					}
+					if (P.act_down)
+					{
+						const uint32_t k = atomicExch(P.act_down + tx, MTD_INF);
+						if (k != MTD_INF)
+							activate_item(P, 0, tx, P.tilesY - 1, r_next - 1, k);
+					}
+				}
+				__threadfence();
+				__syncthreads();
+				if (threadIdx.x == 0)
+				{
+					const uint32_t cnt = __ldcg(P.count + slot), mk = __ldcg(P.minkey + slot);
+					if (cnt)
+						atomicAdd_system(P.ctl0 + PEER_PENDING + slot, cnt);
+					if (mk != MTD_INF)
+						atomicMin_system(P.ctl0 + PEER_MINKEY + slot, mk);
+					ok = peer_barrier(P, epoch, peer_dead) && ok;
+					const uint32_t gp = ld_sys(P.ctl0 + PEER_PENDING + slot), gm = ld_sys(P.ctl0 + PEER_MINKEY + slot);
+					P.minkey[slot] = gm;
+					P.ctl[PEER_GPENDING] = ok ? gp : 0u;
+					P.ctl[PEER_EPOCH] = epoch;
+					if (!ok)
+						atomicOr(P.status, 8); // ST_PEER_TIMEOUT
+				}
+			}
+			__threadfence();
+			grid.sync();
+		};
+		if (P.ctl0)
+		{
+			epoch = P.ctl[PEER_EPOCH];
+			if (blockIdx.x == 0)
+			{
+				// every rank has entered this run (so nobody still reads the halo copies of the previous one): hand my
+				// boundary rows as initialised (m, parked blocked tiles and sources 0) to the neighbours
+				if (threadIdx.x == 0 && !peer_barrier(P, epoch, peer_dead))
+					atomicOr(P.status, 8);
+				__syncthreads();
+				for (int x = (int)threadIdx.x; x < W; x += (int)blockDim.x)
+				{
+					if (P.peer_up_halo)
+						P.peer_up_halo[x] = __ldcg(P.dist + x);
+					if (P.peer_down_halo)
+						P.peer_down_halo[x] = __ldcg(P.dist + (size_t)(Hl - 1) * W + x);
+				}
+				__threadfence_system();
+				__syncthreads();
+			}
+			peer_round_sync(round, true);
+			if (__ldcg(P.ctl + PEER_GPENDING) == 0u)
+				max_rounds = 0;
+		}
 
 		for (int done = 0; done < max_rounds; done++)
 		{
@@ -458,6 +580,19 @@ namespace mtd
 				}
 			}
 
+			if (P.ctl0)
+			{
+				// my boundary rows as they stand now, straight into the neighbour ranks' halo copies
+				const int gx = gx0 + 1 + (int)lane;
+				if (gx < W)
+				{
+					if (ty == 0 && P.peer_up_halo)
+						P.peer_up_halo[gx] = S.d[1 * PITCH + 4 + (int)lane];
+					if (ty == P.tilesY - 1 && P.peer_down_halo)
+						P.peer_down_halo[gx] = S.d[(brow - 1) * PITCH + 4 + (int)lane];
+				}
+			}
+
 			MTD_WTICK(3);
 			// ---- activate neighbours ----
 			// A neighbour tile needs a visit only if one of our border cells now offers its adjacent cell a smaller label than
@@ -466,12 +601,12 @@ namespace mtd
 			{
 				auto offers = [&](uint32_t db, uint32_t w, uint32_t ap) -> bool { return db != 0u && db < BIG_SETTLE_LIMIT && db + MIN_EDGE + w < ap; };
 				const int i = (int)lane;
-				const uint32_t ct = (uint32_t)(1 * PITCH + 4 + i), cb = (uint32_t)(TS * PITCH + 4 + i);
+				const uint32_t ct = (uint32_t)(1 * PITCH + 4 + i), cb = (uint32_t)((brow - 1) * PITCH + 4 + i); // first / last row of the tile that exists
 				const uint32_t cl = (uint32_t)((1 + i) * PITCH + 4), cr = (uint32_t)((1 + i) * PITCH + 3 + TS);
 				const bool row_exists = 1 + i < brow;
 				auto offer = [&](bool exists, uint32_t db, uint32_t w, uint32_t ap) -> uint32_t { return exists && offers(db, w, ap) ? db + MIN_EDGE + w : MTD_INF; };
 				uint32_t k_top = warp_redux_min(offer(true, S.d[ct], S.w[ct - PITCH] >> 16, ap_old[0]));
-				uint32_t k_bot = warp_redux_min(offer(TS < brow, S.d[cb], S.w[cb] >> 16, ap_old[1]));
+				uint32_t k_bot = warp_redux_min(offer(true, S.d[cb], S.w[cb] >> 16, ap_old[1])); // below a cut-short tile: the stripe's halo row or nothing (0)
 				uint32_t k_left = warp_redux_min(offer(row_exists, S.d[cl], S.w[cl - 1u] & 0xFFFFu, ap_old[2]));
 				uint32_t k_right = warp_redux_min(offer(row_exists, S.d[cr], S.w[cr] & 0xFFFFu, ap_old[3]));
 				const uint32_t f = __reduce_or_sync(FULL_MASK, src_sides); // sources on a border line: the neighbour finds them in the list
@@ -483,10 +618,20 @@ namespace mtd
 					k_left = 0u;
 				if (f & 32u)
 					k_right = 0u;
-				__threadfence(); // distances are visible before the neighbour can be scheduled
+				if (P.ctl0)
+					__threadfence_system(); // ... on the neighbour ranks too
+				else
+					__threadfence(); // distances are visible before the neighbour can be scheduled
 				__syncwarp();
 				if (lane == 0)
 				{
+					if (P.ctl0)
+					{
+						if (k_top != MTD_INF && ty == 0 && P.peer_up_act)
+							atomicMin_system(P.peer_up_act + tx, k_top);
+						if (k_bot != MTD_INF && ty == P.tilesY - 1 && P.peer_down_act)
+							atomicMin_system(P.peer_down_act + tx, k_bot);
+					}
 					if (k_top != MTD_INF && ty > 0)
 						activate_item(P, layer, tx, ty - 1, round, k_top);
 					if (k_bot != MTD_INF && ty < P.tilesY - 1)
@@ -501,6 +646,15 @@ namespace mtd
 			MTD_WTICK(4);
 		}
 		// ---- end of the round: everything appended to the next list is visible after the barrier ----
+		if (P.ctl0)
+		{
+			peer_round_sync(round + 1, false);
+			round++;
+			pending = __ldcg(P.ctl + PEER_GPENDING); // all ranks
+			if (pending == 0u)
+				break;
+			continue;
+		}
 		__threadfence();
 		grid.sync();
 		round++;

@@ -28,6 +28,7 @@ namespace mtd
 		ST_GUARD = 1,      // a distance reached the uint32 guard band
 		ST_NO_VALID = 2,   // generated map has no valid tile (reference would spin forever in findSpawnPoint)
 		ST_PATH_TRUNC = 4, // a full path exceeded fullpath_cap (length is still exact)
+		ST_PEER_TIMEOUT = 8, // peer-coupled stripes: the other ranks did not reach a round barrier
 	};
 
 	constexpr int SMALL_THREADS = 512;

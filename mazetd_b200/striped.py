@@ -57,6 +57,16 @@ class GpuStripe:
         self.ctx.synchronize()
         return self.tiles, self.dist
 
+    # ---- peer-coupled mode: one kernel run per rank, rows and keys go straight into the neighbours' memory ----
+    def peer_launch(self):
+        """queue the whole update (every rank must); returns at once"""
+        self.ctx.stripe_peer_launch_dev(self.sources, self.dist.data_ptr(), self.tiles.data_ptr())
+
+    def peer_finish(self):
+        """wait for this rank; returns (tiles, dist, rounds)"""
+        rounds = self.ctx.stripe_peer_finish()
+        return self.tiles, self.dist, rounds
+
     def close(self):
         self.ctx.close()
 
@@ -87,6 +97,24 @@ def solve_distributed(solver, rank, world, group=None):
             break
     tiles, d = solver.finalize()
     return tiles, d, sweeps
+
+
+def connect_peers(stripe, rank, world, group=None):
+    """once per stripe: every rank publishes the CUDA IPC handle of its peer block and maps its neighbours' and rank 0's"""
+    import torch.distributed as dist
+
+    mine = stripe.ctx.stripe_peer_export()
+    handles = [None] * world
+    dist.all_gather_object(handles, mine, group=group)
+    stripe.ctx.stripe_peer_connect(rank, world, handles)
+    dist.barrier(group=group)  # nobody launches before every block is mapped everywhere
+
+
+def solve_peer(stripe):
+    """Directions::update over all ranks in one kernel run per rank (connect_peers first). Returns (tiles, dist, rounds).
+    No host-side collective: the ranks meet at the round barriers on the device."""
+    stripe.peer_launch()
+    return stripe.peer_finish()
 
 
 def solve_local(solvers):

@@ -564,6 +564,24 @@ def test_stripes_bit_exact_with_whole_grid(oracle, W, H, cuts, nsrc, pct):
     assert sweeps >= 1 and launches > 0
 
 
+def test_peer_coupled_stripes_on_two_gpus(oracle):
+    """the stripes of two ranks run as ONE kernel each, write their boundary rows into each other's halo copies over
+    NVLink and meet at device-side round barriers (tests/peer_stripes_worker.py). Needs two GPUs and two processes:
+    concurrent kernels of one process on one GPU do not overlap reliably enough to wait for each other."""
+    import subprocess
+    import sys
+
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run by tools/gpu_multi.sh on a 2-GPU box)")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1", "--master-port", "29641",
+           os.path.join(root, "tests", "peer_stripes_worker.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=root)
+    assert r.returncode == 0 and "PEER-OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
 @pytest.mark.parametrize("budget", [1, 3])
 def test_stripes_with_a_round_budget_swap_rows_before_local_convergence(oracle, budget):
     W, H = 512, 512

@@ -28,7 +28,8 @@ if layers:
         wall = time.time() - t0
         relax, _ = ctx.profile_read(ctx.K_BIG_RELAX)
         dirs, _ = ctx.profile_read(ctx.K_BIG_DIRECTIONS)
-        print(json.dumps(dict(size=size, layers=layers, wall_ms=wall * 1e3, relax_ms=relax, dir_ms=dirs, launches=ctx.launches - l0, gbps_alg=W * H * (4 + 8 * layers) / (relax + dirs) / 1e6)), flush=True)
+        prep, _ = ctx.profile_read(ctx.K_BIG_PREPARE)
+        print(json.dumps(dict(size=size, layers=layers, wall_ms=wall * 1e3, relax_ms=relax, dir_ms=dirs, prep_ms=prep, launches=ctx.launches - l0, gbps_alg=W * H * (4 + 8 * layers) / (relax + dirs) / 1e6)), flush=True)
 else:
     dt = torch.empty(W * H, dtype=torch.int32, device='cuda')
     dd = torch.empty(W * H, dtype=torch.int32, device='cuda')
@@ -40,4 +41,5 @@ else:
         wall = time.time() - t0
         relax, _ = ctx.profile_read(ctx.K_BIG_RELAX)
         dirs, _ = ctx.profile_read(ctx.K_BIG_DIRECTIONS)
-        print(json.dumps(dict(size=size, nsrc=nsrc, wall_ms=wall * 1e3, relax_ms=relax, dir_ms=dirs, launches=ctx.launches - l0, gbps_alg=W * H * 12 / (relax + dirs) / 1e6)), flush=True)
+        prep, _ = ctx.profile_read(ctx.K_BIG_PREPARE)
+        print(json.dumps(dict(size=size, nsrc=nsrc, wall_ms=wall * 1e3, relax_ms=relax, dir_ms=dirs, prep_ms=prep, launches=ctx.launches - l0, gbps_alg=W * H * 12 / (relax + dirs) / 1e6)), flush=True)
