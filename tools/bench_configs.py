@@ -1,5 +1,6 @@
 """Timing of the two large-grid configurations of BASELINE.json next to bench.py's headline (C2):
     C4  one 16384^2 grid, 16 sources, one layer, row-striped over the ranks (halo rows swapped per sweep)
+    C4P the same with peer-coupled stripes: one kernel run per rank, rows and keys written into the neighbours' memory
     C5  one 4096^2 grid, 8 waypoint layers, layers dealt round-robin to the ranks (no collective)
 Run:  python tools/bench_configs.py C4 [size] [reps]                       (1 GPU)
       python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
@@ -31,7 +32,7 @@ def checksum(t, world):
 
 def main():
     cfg = sys.argv[1] if len(sys.argv) > 1 else "C4"
-    size = int(sys.argv[2]) if len(sys.argv) > 2 else (16384 if cfg == "C4" else 4096)
+    size = int(sys.argv[2]) if len(sys.argv) > 2 else (16384 if cfg in ("C4", "C4P") else 4096)
     reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
     budget = int(sys.argv[4]) if len(sys.argv) > 4 else 16  # C4: relaxation rounds between halo swaps (0 = local convergence)
     rank = int(os.environ.get("RANK", "0"))
@@ -45,7 +46,7 @@ def main():
     torch.cuda.set_stream(stream)
     W = H = size
     elev, flags = synth.random_grid(W, H, seed_k=1, wall_pct=30, elev_mod=512)
-    nsrc = 16 if cfg == "C4" else 8
+    nsrc = 16 if cfg in ("C4", "C4P") else 8
     srcs = synth.pick_open_tiles(flags, nsrc, 1)
 
     def timed(fn):
@@ -62,13 +63,18 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item()), out
 
-    if cfg == "C4":
-        st = striped.make_gpu_stripe(local, rank, world, W, H, elev, flags, srcs, stream=stream.cuda_stream, round_budget=budget if world > 1 else 0)
+    if cfg in ("C4", "C4P"):
+        peer = cfg == "C4P" and world > 1
+        st = striped.make_gpu_stripe(local, rank, world, W, H, elev, flags, srcs, stream=stream.cuda_stream, round_budget=budget if world > 1 and not peer else 0)
         del elev, flags
+        if os.environ.get("MTD_TILE_DELTA"):  # priority window of the tile scheduler (experiments)
+            st.ctx.debug_set(st.ctx.DEBUG_TILE_DELTA, int(os.environ["MTD_TILE_DELTA"]))
+        if peer:
+            striped.connect_peers(st, rank, world)
         for rep in range(reps):
             l0 = st.ctx.launches
-            ms, (tiles, d, sweeps) = timed(lambda: striped.solve_distributed(st, rank, world))
-            line = dict(config="C4", grid=[W, H], sources=nsrc, n_gpus=world, rep=rep, ms=ms, sweeps=sweeps, round_budget=budget,
+            ms, (tiles, d, sweeps) = timed((lambda: striped.solve_peer(st)) if peer else (lambda: striped.solve_distributed(st, rank, world)))
+            line = dict(config=cfg, grid=[W, H], sources=nsrc, n_gpus=world, rep=rep, ms=ms, sweeps=sweeps, round_budget=0 if peer else budget,
                         tile_relaxations_per_s=W * H / (ms * 1e-3), algorithmic_GBps=W * H * 12 / (ms * 1e-3) / 1e9,
                         launches_rank0=st.ctx.launches - l0, dist_checksum=checksum(d, world), tiles_checksum=checksum(tiles, world))
             if rank == 0:
