@@ -142,7 +142,8 @@ int mtd_stripe_pending(mtd_ctx *ctx, uint32_t *items_out);
  *   export         creates this rank's peer block (after mtd_stripe_upload*) and returns its CUDA IPC handle (64 bytes)
  *   connect        maps the blocks of rank-1, rank+1 and rank 0 from `handles` ([world][64], gathered by the caller)
  *   launch_dev     queues initialisation, the relaxation kernel and the next-hop pass on the context's stream and returns;
- *                  EVERY rank must call it (a missing rank makes the others give up after 4 s -> MTD_ERR_STATE at finish)
+ *                  EVERY rank must call it (the others wait 20 s for a rank to enter the run and 4 s at each round barrier,
+ *                  then give up -> MTD_ERR_STATE at finish; the barrier counters are then out of step: destroy the contexts)
  *   finish         waits for the stream, reports device status; *rounds_out = rounds the ranks ran */
 int mtd_stripe_peer_export(mtd_ctx *ctx, void *handle64);
 int mtd_stripe_peer_connect(mtd_ctx *ctx, int32_t rank, int32_t world, const void *handles);

@@ -270,7 +270,7 @@ namespace
 		if (st & ST_PATH_TRUNC)
 			return fail(ctx, MTD_ERR_CAPACITY, "a full path is longer than fullpath_cap (lengths are exact, tiles were truncated)");
 		if (st & ST_PEER_TIMEOUT)
-			return fail(ctx, MTD_ERR_STATE, "peer-coupled stripes: another rank did not reach a round barrier within 4 s (not launched, or its kernel is not resident)");
+			return fail(ctx, MTD_ERR_STATE, "peer-coupled stripes: another rank did not reach a barrier in time (20 s to enter the run, 4 s per round: not launched, or died)");
 		return MTD_OK;
 	}
 
@@ -1410,7 +1410,7 @@ extern "C" int mtd_stripe_peer_finish(mtd_ctx *ctx, uint32_t *rounds_out)
 		uint32_t root[PEER_CTL_WORDS] = { 0 }, mine[PEER_CTL_WORDS] = { 0 };
 		cudaMemcpy(root, ctx->peer_root, sizeof(root), cudaMemcpyDeviceToHost);
 		cudaMemcpy(mine, ctx->peer_blk.p, sizeof(mine), cudaMemcpyDeviceToHost);
-		return fail(ctx, MTD_ERR_STATE, "peer-coupled stripes: another rank did not reach a round barrier within 4 s (not launched, or its kernel is not resident); rank %d of %d, barriers passed %u, arrivals counted %u, rounds %u", ctx->peer_rank, ctx->peer_world, mine[PEER_EPOCH], root[PEER_ARRIVE], ctx->last_rounds);
+		return fail(ctx, MTD_ERR_STATE, "peer-coupled stripes: another rank did not reach a barrier in time (20 s to enter the run, 4 s per round: not launched, or died); rank %d of %d, barriers passed %u, arrivals counted %u, rounds %u", ctx->peer_rank, ctx->peer_world, mine[PEER_EPOCH], root[PEER_ARRIVE], ctx->last_rounds);
 	}
 	return rc;
 }

@@ -54,8 +54,8 @@ namespace mtd
 		return t;
 	}
 
-	// one thread per rank. false: the other ranks did not arrive within 4 s (a rank died or never launched)
-	__device__ inline bool peer_barrier(const BigParams &P, uint32_t &epoch, bool &dead)
+	// one thread per rank. false: the other ranks did not arrive within `limit_ns` (a rank died or never launched)
+	__device__ inline bool peer_barrier(const BigParams &P, uint32_t &epoch, bool &dead, unsigned long long limit_ns = 4000000000ull)
 	{
 		if (dead)
 			return false; // one timeout is final: do not wait again
@@ -65,7 +65,7 @@ namespace mtd
 		const uint32_t target = epoch * (uint32_t)P.world;
 		const unsigned long long t0 = global_timer_ns();
 		while ((int32_t)(ld_sys(P.ctl0 + PEER_ARRIVE) - target) < 0)
-			if (global_timer_ns() - t0 > 4000000000ull)
+			if (global_timer_ns() - t0 > limit_ns)
 			{
 				dead = true;
 				return false;
@@ -168,7 +168,7 @@ namespace mtd
 			{
 				// every rank has entered this run (so nobody still reads the halo copies of the previous one): hand my
 				// boundary rows as initialised (m, parked blocked tiles and sources 0) to the neighbours
-				if (threadIdx.x == 0 && !peer_barrier(P, epoch, peer_dead))
+				if (threadIdx.x == 0 && !peer_barrier(P, epoch, peer_dead, 20000000000ull)) // the ranks' hosts may reach the launch seconds apart
 					atomicOr(P.status, 8);
 				__syncthreads();
 				for (int x = (int)threadIdx.x; x < W; x += (int)blockDim.x)
