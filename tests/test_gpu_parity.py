@@ -564,6 +564,27 @@ def test_stripes_bit_exact_with_whole_grid(oracle, W, H, cuts, nsrc, pct):
     assert sweeps >= 1 and launches > 0
 
 
+def test_peer_coupled_protocol_with_a_single_rank(oracle):
+    """world size 1: no neighbour to write to, but the update still runs through the peer-coupled round protocol (barrier
+    epochs, totals in the rank's own block, termination on the global queue length), twice on the same peer block"""
+    from mazetd_b200 import striped
+
+    W, H = 320, 200
+    elev, flags = synth.random_grid(W, H, seed_k=12, wall_pct=30)
+    srcs = synth.pick_open_tiles(flags, 3, 5)
+    st = striped.GpuStripe(0, W, H, 0, H, elev, flags, srcs)
+    st.ctx.stripe_peer_connect(0, 1, [st.ctx.stripe_peer_export()])
+    to, do = oracle.directions_update(W, H, elev, flags, srcs)
+    for _ in range(2):
+        tiles, d, rounds = striped.solve_peer(st)
+        d = d.cpu().numpy().view(np.uint32).reshape(-1)
+        tiles = tiles.cpu().numpy().view(np.uint32).reshape(-1)
+        assert np.array_equal(d, do), diff_report(d, do, W)
+        assert np.array_equal(tiles, to), diff_report(tiles, to, W)
+        assert rounds >= 1
+    st.close()
+
+
 def test_peer_coupled_stripes_on_two_gpus(oracle):
     """the stripes of two ranks run as ONE kernel each, write their boundary rows into each other's halo copies over
     NVLink and meet at device-side round barriers (tests/peer_stripes_worker.py). Needs two GPUs and two processes:
