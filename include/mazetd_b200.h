@@ -147,6 +147,9 @@ int mtd_stripe_pending(mtd_ctx *ctx, uint32_t *items_out);
  *   finish         waits for the stream, reports device status; *rounds_out = rounds the ranks ran */
 int mtd_stripe_peer_export(mtd_ctx *ctx, void *handle64);
 int mtd_stripe_peer_connect(mtd_ctx *ctx, int32_t rank, int32_t world, const void *handles);
+/* the same for stripes that are contexts of THIS process on ONE device (tests: several stripes share a GPU); each kernel is
+ * limited to `ctas` CTAs so that all of them are resident together; export every context first */
+int mtd_stripe_peer_connect_local(mtd_ctx *ctx, int32_t rank, int32_t world, mtd_ctx *above, mtd_ctx *below, mtd_ctx *root, int32_t ctas);
 int mtd_stripe_peer_launch_dev(mtd_ctx *ctx, const uint32_t *sources /* host */, int32_t nsrc, uint32_t *d_dist, uint32_t *d_tiles);
 int mtd_stripe_peer_finish(mtd_ctx *ctx, uint32_t *rounds_out);
 

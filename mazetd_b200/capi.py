@@ -18,7 +18,7 @@ EXPORTS = [
     "mtd_grid_upload", "mtd_grid_upload_dev", "mtd_grid_set_flags", "mtd_neighbor_distances", "mtd_edge_weights",
     "mtd_directions_update", "mtd_directions_update_dev", "mtd_directions_layers_dev",
     "mtd_stripe_upload", "mtd_stripe_upload_dev", "mtd_stripe_begin_dev", "mtd_stripe_exchange_dev", "mtd_stripe_finalize_dev", "mtd_stripe_round_budget", "mtd_stripe_pending",
-    "mtd_stripe_peer_export", "mtd_stripe_peer_connect", "mtd_stripe_peer_launch_dev", "mtd_stripe_peer_finish",
+    "mtd_stripe_peer_export", "mtd_stripe_peer_connect", "mtd_stripe_peer_connect_local", "mtd_stripe_peer_launch_dev", "mtd_stripe_peer_finish",
     "mtd_waypoints_update", "mtd_waypoints_update_dev", "mtd_waypoints_find", "mtd_waypoints_layers_dev",
     "mtd_placing_blocks",
     "mtd_mapgen_batch", "mtd_mapgen_batch_dev", "mtd_grid_from_elevations", "mtd_elevation_samples", "mtd_sdf_lattice",
@@ -78,6 +78,7 @@ def load():
     L.mtd_stripe_pending.argtypes = [vp, C.POINTER(u32)]
     L.mtd_stripe_peer_export.argtypes = [vp, vp]
     L.mtd_stripe_peer_connect.argtypes = [vp, i32, i32, vp]
+    L.mtd_stripe_peer_connect_local.argtypes = [vp, i32, i32, vp, vp, vp, i32]
     L.mtd_stripe_peer_launch_dev.argtypes = [vp, vp, i32, vp, vp]
     L.mtd_stripe_peer_finish.argtypes = [vp, C.POINTER(u32)]
     L.mtd_waypoints_update.argtypes = [vp, vp, i32, vp, vp, vp, u32, vp, vp, vp]
@@ -259,6 +260,10 @@ class Context:
         buf = b"".join(handles)
         assert len(buf) == 64 * world
         self._ck(self.L.mtd_stripe_peer_connect(self.h, int(rank), int(world), buf))
+
+    def stripe_peer_connect_local(self, rank, world, above, below, root, ctas):
+        self._ck(self.L.mtd_stripe_peer_connect_local(self.h, int(rank), int(world), above.h if above is not None else None,
+                                                      below.h if below is not None else None, root.h, int(ctas)))
 
     def stripe_peer_launch_dev(self, sources, d_dist, d_tiles):
         src = np.ascontiguousarray(np.atleast_1d(sources), np.uint32)

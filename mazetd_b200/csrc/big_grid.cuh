@@ -76,6 +76,8 @@ namespace mtd
 		uint32_t *ctl0;            // rank 0's control words (PEER_* below)
 		uint32_t *ctl;             // my control words (local scratch: PEER_GPENDING, PEER_EPOCH)
 		int world, rank;
+		int soft_grid;             // the grid is smaller than the GPU and was launched plainly (several stripes share one GPU in
+		                           // tests): CTAs meet on a counter (count[11]) instead of grid.sync()
 	};
 
 	// control words at the head of a peer block

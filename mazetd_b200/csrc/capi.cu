@@ -127,7 +127,7 @@ struct mtd_ctx
 	uint32_t *peer_above = nullptr, *peer_below = nullptr, *peer_root = nullptr; // the other ranks' blocks, mapped here
 	bool peer_ipc = false;      // mapped with cudaIpcOpenMemHandle (to be closed)
 	bool peer_linked = false, peer_on = false;
-	int peer_rank = 0, peer_world = 1;
+	int peer_rank = 0, peer_world = 1, peer_ctas = 0;
 	DevBuf<uint8_t> up_blocked;
 
 	// staging of mtd_mapgen_batch (host outputs): two buffer sets, compute overlaps the drain of the previous chunk
@@ -417,10 +417,15 @@ namespace
 		BigParams Pk = P;
 		int round0 = round;
 		void *args[] = { (void *)&Pk, (void *)&round0, (void *)&max_rounds, (void *)&d_out };
-		const int ctas = ctx->sms * ctas_per_sm;
+		int ctas = ctx->sms * ctas_per_sm;
+		if (Pk.soft_grid)
+			ctas = ctx->peer_ctas < ctas ? ctx->peer_ctas : ctas;
 		{
 			ProfScope prof(ctx, MTD_K_BIG_RELAX);
-			CU(cudaLaunchCooperativeKernel((const void *)k_tile_rounds<BIG_TS, BIG_WARPS>, dim3((unsigned)ctas), dim3(BIG_WARPS * 32), args, smem, ctx->stream));
+			if (Pk.soft_grid) // several stripes share this GPU: plain launches of small grids that are resident together
+				k_tile_rounds<BIG_TS, BIG_WARPS><<<dim3((unsigned)ctas), dim3(BIG_WARPS * 32), smem, ctx->stream>>>(Pk, round0, max_rounds, d_out);
+			else
+				CU(cudaLaunchCooperativeKernel((const void *)k_tile_rounds<BIG_TS, BIG_WARPS>, dim3((unsigned)ctas), dim3(BIG_WARPS * 32), args, smem, ctx->stream));
 			LAUNCHED();
 		}
 		if (P.ctl0)
@@ -610,6 +615,7 @@ namespace
 			P.ctl = mine;
 			P.world = ctx->peer_world;
 			P.rank = ctx->peer_rank;
+			P.soft_grid = ctx->peer_ctas > 0 ? 1 : 0;
 		}
 		return P;
 	}
@@ -1361,6 +1367,33 @@ extern "C" int mtd_stripe_peer_connect(mtd_ctx *ctx, int32_t rank, int32_t world
 		return rc;
 	ctx->peer_rank = rank;
 	ctx->peer_world = world;
+	ctx->peer_ctas = 0;
+	ctx->peer_linked = true;
+	return MTD_OK;
+}
+
+extern "C" int mtd_stripe_peer_connect_local(mtd_ctx *ctx, int32_t rank, int32_t world, mtd_ctx *above, mtd_ctx *below, mtd_ctx *root, int32_t ctas)
+{
+	if (!ctx || !root || world < 1 || rank < 0 || rank >= world || (rank > 0 && !above) || (rank < world - 1 && !below) || ctas < 1)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	int rc = peer_block_create(ctx);
+	if (rc)
+		return rc;
+	peer_unlink(ctx);
+	mtd_ctx *others[3] = { rank > 0 ? above : nullptr, rank < world - 1 ? below : nullptr, root };
+	for (int i = 0; i < 3; i++)
+		if (others[i] && others[i] != ctx && (!others[i]->peer_blk.p || others[i]->device != ctx->device))
+			return fail(ctx, MTD_ERR_STATE, "a linked context has no peer block yet (call mtd_stripe_peer_export on every context first) or lives on another device");
+	ctx->peer_above = rank > 0 ? above->peer_blk.p : nullptr;
+	ctx->peer_below = rank < world - 1 ? below->peer_blk.p : nullptr;
+	ctx->peer_root = root->peer_blk.p;
+	if ((rc = stripe_reserve(ctx, 4096)))
+		return rc;
+	ctx->peer_rank = rank;
+	ctx->peer_world = world;
+	ctx->peer_ctas = ctas;
 	ctx->peer_linked = true;
 	return MTD_OK;
 }

@@ -103,12 +103,34 @@ namespace mtd
 		// landed, (2) queues the border tiles its neighbours offered a label to, (3) adds its queue length and smallest key
 		// to rank 0's totals, (4) waits again and reads the totals: all ranks see the same wavefront position and stop in
 		// the same round.
+		uint32_t grid_gen = 0;
+		auto peer_grid_sync = [&]()
+		{
+			if (!P.soft_grid)
+			{
+				grid.sync();
+				return;
+			}
+			__syncthreads();
+			if (threadIdx.x == 0)
+			{
+				uint32_t *bar = P.count + 11;
+				__threadfence();
+				grid_gen++;
+				atomicAdd(bar, 1u);
+				const uint32_t target = grid_gen * gridDim.x;
+				while ((int32_t)(*(volatile uint32_t *)bar - target) < 0)
+					;
+				__threadfence();
+			}
+			__syncthreads();
+		};
 		uint32_t epoch = 0;
 		bool peer_dead = false;
 		auto peer_round_sync = [&](int r_next, bool first)
 		{
 			__threadfence_system();
-			grid.sync();
+			peer_grid_sync();
 			if (blockIdx.x == 0)
 			{
 				const int slot = r_next % 3;
@@ -159,7 +181,7 @@ namespace mtd
 				}
 			}
 			__threadfence();
-			grid.sync();
+			peer_grid_sync();
 		};
 		if (P.ctl0)
 		{

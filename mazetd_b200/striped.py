@@ -117,6 +117,29 @@ def solve_peer(stripe):
     return stripe.peer_finish()
 
 
+def solve_peer_local(stripes, ctas=64):
+    """the peer-coupled protocol with every stripe a context of this process on ONE GPU (tests): each stripe's kernel is
+    limited to `ctas` CTAs so that all of them are resident together. Every kernel involved must have been launched once
+    before (CUDA loads kernels lazily, and a load while the first stripe's kernel waits holds the others back).
+    Returns ([(tiles, dist) per stripe], rounds)."""
+    n = len(stripes)
+    for s in stripes:
+        s.ctx.stripe_peer_export()
+    for i, s in enumerate(stripes):
+        s.ctx.stripe_peer_connect_local(i, n, stripes[i - 1].ctx if i > 0 else None, stripes[i + 1].ctx if i < n - 1 else None, stripes[0].ctx, ctas)
+    for s in stripes:
+        s.peer_launch()
+    out, err = [], None
+    for s in stripes:  # wait for every stripe even if one reports a barrier timeout
+        try:
+            out.append(s.peer_finish())
+        except Exception as e:  # noqa: BLE001
+            err = err or e
+    if err is not None:
+        raise err
+    return [(t, d) for t, d, _ in out], out[0][2]
+
+
 def solve_local(solvers):
     """The same protocol with every stripe in this process (stripes top to bottom; e.g. several contexts on one GPU).
     Returns ([(tiles, dist) per stripe], sweeps)."""

@@ -6,7 +6,7 @@ import os
 import numpy as np
 import pytest
 
-from mazetd_b200 import synth
+from mazetd_b200 import capi, synth
 from oracle_lib import KAT_SEED, M
 
 pytestmark = pytest.mark.gpu
@@ -564,6 +564,73 @@ def test_stripes_bit_exact_with_whole_grid(oracle, W, H, cuts, nsrc, pct):
     assert sweeps >= 1 and launches > 0
 
 
+def _peer_striped_on_one_gpu(W, H, cuts, elev, flags, srcs, repeat=1):
+    """stripes as contexts of this process whose kernels run side by side on the one GPU (64 CTAs each) and write into
+    each other's peer blocks. Skips if the box does not overlap them (the ranks then time out at the first barrier)."""
+    from mazetd_b200 import shard, striped
+
+    # CUDA loads kernels lazily, and a load while one stripe's kernel waits at a barrier holds the other stripes back:
+    # launch every kernel of the protocol once, alone
+    w0, h0 = 64, 64
+    e0, f0 = synth.random_grid(w0, h0, seed_k=1, wall_pct=10)
+    warm = striped.GpuStripe(0, w0, h0, 0, h0, e0, f0, synth.pick_open_tiles(f0, 1, 1))
+    striped.solve_peer_local([warm])
+    warm.close()
+    stripes = []
+    for y0, y1 in zip(cuts[:-1], cuts[1:]):
+        ya, yb = shard.stripe_halo_rows(y0, y1, H)
+        stripes.append(striped.GpuStripe(0, W, H, y0, y1, elev.reshape(H, W)[ya:yb], flags.reshape(H, W)[ya:yb], srcs))
+    try:
+        for _ in range(repeat):
+            results, rounds = striped.solve_peer_local(stripes, ctas=64)
+    except capi.MtdError as e:
+        if "did not reach a barrier" in str(e):
+            pytest.skip("the stripes' kernels did not run side by side on this GPU")
+        raise
+    tiles = np.concatenate([t.cpu().numpy().view(np.uint32).reshape(-1) for t, _ in results])
+    d = np.concatenate([x.cpu().numpy().view(np.uint32).reshape(-1) for _, x in results])
+    for s in stripes:
+        s.close()
+    return tiles, d, rounds
+
+
+@pytest.mark.parametrize("W,H,cuts,nsrc,pct", [
+    (384, 320, [0, 128, 320], 1, 30),
+    (384, 320, [0, 64, 128, 192, 320], 4, 30),
+    (200, 301, [0, 97, 203, 301], 3, 35),    # cuts inside tiles
+    (256, 256, [0, 1, 255, 256], 2, 20),     # one-row stripes at both ends
+    (1024, 1024, [0, 256, 512, 768, 1024], 16, 30),
+])
+def test_peer_coupled_stripes_side_by_side_on_one_gpu(oracle, W, H, cuts, nsrc, pct):
+    elev, flags = synth.random_grid(W, H, seed_k=W + len(cuts), wall_pct=pct)
+    srcs = synth.pick_open_tiles(flags, nsrc, 2)
+    tiles, d, rounds = _peer_striped_on_one_gpu(W, H, cuts, elev, flags, srcs, repeat=2)  # the second run reuses the peer blocks
+    to, do = oracle.directions_update(W, H, elev, flags, srcs)
+    assert np.array_equal(d, do), diff_report(d, do, W)
+    assert np.array_equal(tiles, to), diff_report(tiles, to, W)
+    assert rounds >= 1
+
+
+def test_peer_coupled_stripes_maze_and_sources_on_cut_rows(oracle):
+    W, H = 320, 256
+    elev, flags = synth.maze_grid(W, H, seed_k=4)
+    srcs = synth.pick_open_tiles(flags, 1, 1)
+    tiles, d, _ = _peer_striped_on_one_gpu(W, H, [0, 64, 128, 192, 256], elev, flags, srcs)
+    to, do = oracle.directions_update(W, H, elev, flags, srcs)
+    assert np.array_equal(d, do), diff_report(d, do, W)
+    assert np.array_equal(tiles, to), diff_report(tiles, to, W)
+    W, H = 192, 192
+    elev, flags = synth.random_grid(W, H, seed_k=9, wall_pct=25)
+    flags = flags.copy()
+    srcs = np.array([63 * W + 10, 64 * W + 100, 127 * W + 191, 128 * W + 0], np.uint32)
+    flags[srcs] &= ~np.uint16(synth.FLAG_BUILDING | 1)
+    flags[srcs[1]] |= synth.FLAG_BUILDING  # a blocked source still expands (paths.cpp:63-67)
+    tiles, d, _ = _peer_striped_on_one_gpu(W, H, [0, 64, 128, 192], elev, flags, srcs)
+    to, do = oracle.directions_update(W, H, elev, flags, srcs)
+    assert np.array_equal(d, do), diff_report(d, do, W)
+    assert np.array_equal(tiles, to), diff_report(tiles, to, W)
+
+
 def test_peer_coupled_protocol_with_a_single_rank(oracle):
     """world size 1: no neighbour to write to, but the update still runs through the peer-coupled round protocol (barrier
     epochs, totals in the rank's own block, termination on the global queue length), twice on the same peer block"""
@@ -587,15 +654,15 @@ def test_peer_coupled_protocol_with_a_single_rank(oracle):
 
 def test_peer_coupled_stripes_on_two_gpus(oracle):
     """the stripes of two ranks run as ONE kernel each, write their boundary rows into each other's halo copies over
-    NVLink and meet at device-side round barriers (tests/peer_stripes_worker.py). Needs two GPUs and two processes:
-    concurrent kernels of one process on one GPU do not overlap reliably enough to wait for each other."""
+    NVLink and meet at device-side round barriers (tests/peer_stripes_worker.py): the production set-up, one process
+    per GPU with the peer blocks mapped through CUDA IPC. The one-GPU tests above cover the same kernels in one process."""
     import subprocess
     import sys
 
     import torch
 
     if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs (run by tools/gpu_multi.sh on a 2-GPU box)")
+        pytest.skip("needs 2 GPUs: gpurun --gpus 2 -- python -m pytest tests -m gpu -k two_gpus")
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1", "--master-port", "29641",
            os.path.join(root, "tests", "peer_stripes_worker.py")]
