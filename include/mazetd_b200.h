@@ -137,10 +137,11 @@ int mtd_stripe_pending(mtd_ctx *ctx, uint32_t *items_out);
 
 /* Peer-coupled stripes: the same Directions::update (paths.cpp:24-78) with the ranks advancing round by round inside ONE
  * kernel run per rank instead of through host-driven sweeps. A border tile stores its boundary row straight into the
- * neighbour rank's halo copy over NVLink and posts the offered key there; rounds are separated by a barrier across the
- * ranks (arrive counter in rank 0's block), all ranks follow the same wavefront position and stop in the same round.
+ * neighbour rank's halo copy over NVLink and posts the offered key there; between rounds every rank stores a phase tag,
+ * its queue length and its smallest key into its slot of EVERY rank's block and waits on its own block for the others,
+ * so all ranks follow the same wavefront position and stop in the same round.
  *   export         creates this rank's peer block (after mtd_stripe_upload*) and returns its CUDA IPC handle (64 bytes)
- *   connect        maps the blocks of rank-1, rank+1 and rank 0 from `handles` ([world][64], gathered by the caller)
+ *   connect        maps the blocks of all other ranks from `handles` ([world][64], gathered by the caller; world <= 16)
  *   launch_dev     queues initialisation, the relaxation kernel and the next-hop pass on the context's stream and returns;
  *                  EVERY rank must call it (the others wait 20 s for a rank to enter the run and 4 s at each round barrier,
  *                  then give up -> MTD_ERR_STATE at finish; the barrier counters are then out of step: destroy the contexts)
@@ -149,7 +150,7 @@ int mtd_stripe_peer_export(mtd_ctx *ctx, void *handle64);
 int mtd_stripe_peer_connect(mtd_ctx *ctx, int32_t rank, int32_t world, const void *handles);
 /* the same for stripes that are contexts of THIS process on ONE device (tests: several stripes share a GPU); each kernel is
  * limited to `ctas` CTAs so that all of them are resident together; export every context first */
-int mtd_stripe_peer_connect_local(mtd_ctx *ctx, int32_t rank, int32_t world, mtd_ctx *above, mtd_ctx *below, mtd_ctx *root, int32_t ctas);
+int mtd_stripe_peer_connect_local(mtd_ctx *ctx, int32_t rank, int32_t world, mtd_ctx *const *all /* [world], all[rank] == ctx */, int32_t ctas);
 int mtd_stripe_peer_launch_dev(mtd_ctx *ctx, const uint32_t *sources /* host */, int32_t nsrc, uint32_t *d_dist, uint32_t *d_tiles);
 int mtd_stripe_peer_finish(mtd_ctx *ctx, uint32_t *rounds_out);
 

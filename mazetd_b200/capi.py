@@ -78,7 +78,7 @@ def load():
     L.mtd_stripe_pending.argtypes = [vp, C.POINTER(u32)]
     L.mtd_stripe_peer_export.argtypes = [vp, vp]
     L.mtd_stripe_peer_connect.argtypes = [vp, i32, i32, vp]
-    L.mtd_stripe_peer_connect_local.argtypes = [vp, i32, i32, vp, vp, vp, i32]
+    L.mtd_stripe_peer_connect_local.argtypes = [vp, i32, i32, C.POINTER(vp), i32]
     L.mtd_stripe_peer_launch_dev.argtypes = [vp, vp, i32, vp, vp]
     L.mtd_stripe_peer_finish.argtypes = [vp, C.POINTER(u32)]
     L.mtd_waypoints_update.argtypes = [vp, vp, i32, vp, vp, vp, u32, vp, vp, vp]
@@ -261,9 +261,10 @@ class Context:
         assert len(buf) == 64 * world
         self._ck(self.L.mtd_stripe_peer_connect(self.h, int(rank), int(world), buf))
 
-    def stripe_peer_connect_local(self, rank, world, above, below, root, ctas):
-        self._ck(self.L.mtd_stripe_peer_connect_local(self.h, int(rank), int(world), above.h if above is not None else None,
-                                                      below.h if below is not None else None, root.h, int(ctas)))
+    def stripe_peer_connect_local(self, rank, world, contexts, ctas):
+        """contexts: the Context of every rank (this process, this device), in rank order"""
+        arr = (C.c_void_p * world)(*[c.h.value for c in contexts])
+        self._ck(self.L.mtd_stripe_peer_connect_local(self.h, int(rank), int(world), arr, int(ctas)))
 
     def stripe_peer_launch_dev(self, sources, d_dist, d_tiles):
         src = np.ascontiguousarray(np.atleast_1d(sources), np.uint32)

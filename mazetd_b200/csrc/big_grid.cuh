@@ -66,27 +66,30 @@ namespace mtd
 		// peer-coupled stripes (ctl0 != null): the stripes of all ranks advance round by round inside ONE kernel run. A visit
 		// of a border tile stores its boundary row straight into the neighbour rank's halo copy (up_row / down_row above then
 		// point into this rank's peer block, written by the neighbours over NVLink) and posts the offered key in the
-		// neighbour's act array; rounds are separated by a barrier across the ranks (arrive counter on rank 0).
+		// neighbour's act array. Between rounds every rank stores a phase tag (then its queue length and smallest key) into
+		// ITS slot of EVERY rank's block and waits on its own block until all slots carry the tag: one NVLink store latency
+		// per phase, no remote polling, no remote atomics.
 		uint32_t *peer_up_halo;    // the rank above: its copy of my first row [W]           (null: no rank above)
 		uint32_t *peer_up_act;     // the rank above: keys offered to its last tile row [tilesX]
 		uint32_t *peer_down_halo;  // the rank below: its copy of my last row [W]
 		uint32_t *peer_down_act;   // the rank below: keys offered to its first tile row [tilesX]
 		uint32_t *act_up;          // mine: keys the rank above offered to my first tile row (MTD_INF: none)
 		uint32_t *act_down;        // mine: keys the rank below offered to my last tile row
-		uint32_t *ctl0;            // rank 0's control words (PEER_* below)
-		uint32_t *ctl;             // my control words (local scratch: PEER_GPENDING, PEER_EPOCH)
+		uint32_t *ctl0;            // non-null = peer-coupled mode (rank 0's block)
+		uint32_t *ctl;             // my block (PEER_* words below)
+		uint32_t *peers[16];       // every rank's block, mine included
 		int world, rank;
 		int soft_grid;             // the grid is smaller than the GPU and was launched plainly (several stripes share one GPU in
 		                           // tests): CTAs meet on a counter (count[11]) instead of grid.sync()
 	};
 
-	// control words at the head of a peer block
-	constexpr int PEER_ARRIVE = 0;    // cumulative arrivals at the cross-rank barrier (rank 0's block only)
-	constexpr int PEER_PENDING = 4;   // [3] work items queued on all ranks for round r (slot r % 3)
-	constexpr int PEER_MINKEY = 8;    // [3] smallest key on all ranks' lists
-	constexpr int PEER_GPENDING = 12; // local: the value read from PEER_PENDING for the coming round
-	constexpr int PEER_EPOCH = 13;    // local: barriers this rank has passed since the block was created
-	constexpr int PEER_CTL_WORDS = 16;
+	// words at the head of a peer block
+	constexpr int PEER_MAX_WORLD = 16;
+	constexpr int PEER_GPENDING = 12; // local: work items queued on all ranks for the coming round
+	constexpr int PEER_EPOCH = 13;    // local: phases this rank has been through since the block was created
+	constexpr int PEER_SLOT_A = 16;   // [16] phase tag of rank j ("everything I wrote into your block this round has landed")
+	constexpr int PEER_SLOT_B = 32;   // [16] x 64 bit: smallest key << 32 | queue length (24 bits) << 8 | phase tag (8 bits) of rank j
+	constexpr int PEER_CTL_WORDS = 64;
 
 	// ---- edge weights -------------------------------------------------------------------------------
 	__global__ void k_edge_weights(int W, int Hl, const int16_t *__restrict__ elev, const int16_t *__restrict__ elev_below /* row after the stripe or null */, const uint16_t *__restrict__ flags, uint32_t *__restrict__ wpack, uint8_t *__restrict__ blocked)

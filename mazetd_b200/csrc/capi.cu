@@ -124,7 +124,8 @@ struct mtd_ctx
 	DevBuf<uint32_t> halo_up, halo_down, up_wpack;   // local copies of the neighbour stripes' boundary rows; wpack of row sy0-1
 	// peer-coupled stripes: one block per rank that the neighbour ranks write into (layout: peer_layout())
 	DevBuf<uint32_t> peer_blk;
-	uint32_t *peer_above = nullptr, *peer_below = nullptr, *peer_root = nullptr; // the other ranks' blocks, mapped here
+	uint32_t *peers[PEER_MAX_WORLD] = { nullptr }; // every rank's block (mine included), mapped here
+	uint32_t *peer_above = nullptr, *peer_below = nullptr, *peer_root = nullptr; // = peers[rank - 1], peers[rank + 1], peers[0]
 	bool peer_ipc = false;      // mapped with cudaIpcOpenMemHandle (to be closed)
 	bool peer_linked = false, peer_on = false;
 	int peer_rank = 0, peer_world = 1, peer_ctas = 0;
@@ -613,6 +614,8 @@ namespace
 			P.peer_down_act = ctx->peer_below ? ctx->peer_below + L.act_up : nullptr;
 			P.ctl0 = ctx->peer_root;
 			P.ctl = mine;
+			for (int r = 0; r < PEER_MAX_WORLD; r++)
+				P.peers[r] = ctx->peers[r];
 			P.world = ctx->peer_world;
 			P.rank = ctx->peer_rank;
 			P.soft_grid = ctx->peer_ctas > 0 ? 1 : 0;
@@ -1290,27 +1293,35 @@ namespace
 		// halo rows and key arrays: m (nothing offered); control words: 0, smallest keys m
 		CU(cudaMemsetAsync(ctx->peer_blk.p, 0xFF, L.words * 4, ctx->stream));
 		CU(cudaMemsetAsync(ctx->peer_blk.p, 0, PEER_CTL_WORDS * 4, ctx->stream));
-		CU(cudaMemsetAsync(ctx->peer_blk.p + PEER_MINKEY, 0xFF, 3 * 4, ctx->stream));
 		CU(cudaStreamSynchronize(ctx->stream));
 		return MTD_OK;
 	}
 
 	void peer_unlink(mtd_ctx *ctx)
 	{
-		if (ctx->peer_ipc)
+		for (int r = 0; r < PEER_MAX_WORLD; r++)
 		{
-			uint32_t *opened[3] = { ctx->peer_above, ctx->peer_below, ctx->peer_root };
-			for (int i = 0; i < 3; i++)
-			{
-				bool dup = opened[i] == nullptr || opened[i] == ctx->peer_blk.p;
-				for (int j = 0; j < i; j++)
-					dup |= opened[j] == opened[i];
-				if (!dup)
-					cudaIpcCloseMemHandle(opened[i]);
-			}
+			if (ctx->peer_ipc && ctx->peers[r] && ctx->peers[r] != ctx->peer_blk.p)
+				cudaIpcCloseMemHandle(ctx->peers[r]);
+			ctx->peers[r] = nullptr;
 		}
 		ctx->peer_above = ctx->peer_below = ctx->peer_root = nullptr;
 		ctx->peer_ipc = ctx->peer_linked = ctx->peer_on = false;
+	}
+
+	int peer_linked_up(mtd_ctx *ctx, int rank, int world, int ctas)
+	{
+		ctx->peer_above = rank > 0 ? ctx->peers[rank - 1] : nullptr;
+		ctx->peer_below = rank < world - 1 ? ctx->peers[rank + 1] : nullptr;
+		ctx->peer_root = ctx->peers[0];
+		int rc = stripe_reserve(ctx, 4096);
+		if (rc)
+			return rc;
+		ctx->peer_rank = rank;
+		ctx->peer_world = world;
+		ctx->peer_ctas = ctas;
+		ctx->peer_linked = true;
+		return MTD_OK;
 	}
 }
 
@@ -1332,7 +1343,7 @@ extern "C" int mtd_stripe_peer_export(mtd_ctx *ctx, void *handle64)
 
 extern "C" int mtd_stripe_peer_connect(mtd_ctx *ctx, int32_t rank, int32_t world, const void *handles)
 {
-	if (!ctx || !handles || world < 1 || rank < 0 || rank >= world)
+	if (!ctx || !handles || world < 1 || world > PEER_MAX_WORLD || rank < 0 || rank >= world)
 		return MTD_ERR_ARG;
 	std::lock_guard<std::mutex> lk(ctx->mu);
 	DeviceGuard g(ctx->device);
@@ -1341,40 +1352,25 @@ extern "C" int mtd_stripe_peer_connect(mtd_ctx *ctx, int32_t rank, int32_t world
 		return rc;
 	peer_unlink(ctx);
 	ctx->peer_ipc = true;
-	auto open = [&](int r, uint32_t *&out) -> int
+	for (int r = 0; r < world; r++)
 	{
 		if (r == rank)
 		{
-			out = ctx->peer_blk.p;
-			return MTD_OK;
+			ctx->peers[r] = ctx->peer_blk.p;
+			continue;
 		}
 		cudaIpcMemHandle_t h;
 		memcpy(&h, (const uint8_t *)handles + (size_t)r * 64, 64);
 		void *p = nullptr;
 		CU(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
-		out = (uint32_t *)p;
-		return MTD_OK;
-	};
-	if (rank > 0 && (rc = open(rank - 1, ctx->peer_above)))
-		return rc;
-	if (rank < world - 1 && (rc = open(rank + 1, ctx->peer_below)))
-		return rc;
-	if (rank == 1)
-		ctx->peer_root = ctx->peer_above; // a block can be mapped once per process
-	else if ((rc = open(0, ctx->peer_root)))
-		return rc;
-	if ((rc = stripe_reserve(ctx, 4096)))
-		return rc;
-	ctx->peer_rank = rank;
-	ctx->peer_world = world;
-	ctx->peer_ctas = 0;
-	ctx->peer_linked = true;
-	return MTD_OK;
+		ctx->peers[r] = (uint32_t *)p;
+	}
+	return peer_linked_up(ctx, rank, world, 0);
 }
 
-extern "C" int mtd_stripe_peer_connect_local(mtd_ctx *ctx, int32_t rank, int32_t world, mtd_ctx *above, mtd_ctx *below, mtd_ctx *root, int32_t ctas)
+extern "C" int mtd_stripe_peer_connect_local(mtd_ctx *ctx, int32_t rank, int32_t world, mtd_ctx *const *all, int32_t ctas)
 {
-	if (!ctx || !root || world < 1 || rank < 0 || rank >= world || (rank > 0 && !above) || (rank < world - 1 && !below) || ctas < 1)
+	if (!ctx || !all || world < 1 || world > PEER_MAX_WORLD || rank < 0 || rank >= world || ctas < 1 || all[rank] != ctx)
 		return MTD_ERR_ARG;
 	std::lock_guard<std::mutex> lk(ctx->mu);
 	DeviceGuard g(ctx->device);
@@ -1382,20 +1378,13 @@ extern "C" int mtd_stripe_peer_connect_local(mtd_ctx *ctx, int32_t rank, int32_t
 	if (rc)
 		return rc;
 	peer_unlink(ctx);
-	mtd_ctx *others[3] = { rank > 0 ? above : nullptr, rank < world - 1 ? below : nullptr, root };
-	for (int i = 0; i < 3; i++)
-		if (others[i] && others[i] != ctx && (!others[i]->peer_blk.p || others[i]->device != ctx->device))
+	for (int r = 0; r < world; r++)
+	{
+		if (!all[r] || !all[r]->peer_blk.p || all[r]->device != ctx->device)
 			return fail(ctx, MTD_ERR_STATE, "a linked context has no peer block yet (call mtd_stripe_peer_export on every context first) or lives on another device");
-	ctx->peer_above = rank > 0 ? above->peer_blk.p : nullptr;
-	ctx->peer_below = rank < world - 1 ? below->peer_blk.p : nullptr;
-	ctx->peer_root = root->peer_blk.p;
-	if ((rc = stripe_reserve(ctx, 4096)))
-		return rc;
-	ctx->peer_rank = rank;
-	ctx->peer_world = world;
-	ctx->peer_ctas = ctas;
-	ctx->peer_linked = true;
-	return MTD_OK;
+		ctx->peers[r] = all[r]->peer_blk.p;
+	}
+	return peer_linked_up(ctx, rank, world, ctas);
 }
 
 extern "C" int mtd_stripe_peer_launch_dev(mtd_ctx *ctx, const uint32_t *sources, int32_t nsrc, uint32_t *d_dist, uint32_t *d_tiles)
@@ -1440,10 +1429,12 @@ extern "C" int mtd_stripe_peer_finish(mtd_ctx *ctx, uint32_t *rounds_out)
 		*rounds_out = ctx->last_rounds;
 	if (rc == MTD_ERR_STATE && ctx->peer_root && ctx->peer_blk.p)
 	{
-		uint32_t root[PEER_CTL_WORDS] = { 0 }, mine[PEER_CTL_WORDS] = { 0 };
-		cudaMemcpy(root, ctx->peer_root, sizeof(root), cudaMemcpyDeviceToHost);
+		uint32_t mine[PEER_CTL_WORDS] = { 0 };
 		cudaMemcpy(mine, ctx->peer_blk.p, sizeof(mine), cudaMemcpyDeviceToHost);
-		return fail(ctx, MTD_ERR_STATE, "peer-coupled stripes: another rank did not reach a barrier in time (20 s to enter the run, 4 s per round: not launched, or died); rank %d of %d, barriers passed %u, arrivals counted %u, rounds %u", ctx->peer_rank, ctx->peer_world, mine[PEER_EPOCH], root[PEER_ARRIVE], ctx->last_rounds);
+		uint32_t behind = 0;
+		for (int r = 0; r < ctx->peer_world; r++)
+			behind += (int32_t)(mine[PEER_SLOT_A + r] - mine[PEER_SLOT_A + ctx->peer_rank]) < 0 ? 1u : 0u;
+		return fail(ctx, MTD_ERR_STATE, "peer-coupled stripes: another rank did not reach a barrier in time (20 s to enter the run, 4 s per round: not launched, or died); rank %d of %d, phases passed %u, ranks behind %u, rounds %u", ctx->peer_rank, ctx->peer_world, mine[PEER_EPOCH], behind, ctx->last_rounds);
 	}
 	return rc;
 }

@@ -54,23 +54,70 @@ namespace mtd
 		return t;
 	}
 
-	// one thread per rank. false: the other ranks did not arrive within `limit_ns` (a rank died or never launched)
-	__device__ inline bool peer_barrier(const BigParams &P, uint32_t &epoch, bool &dead, unsigned long long limit_ns = 4000000000ull)
+	__device__ __forceinline__ void st_sys(uint32_t *p, uint32_t v)
+	{
+		asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+	}
+
+	__device__ __forceinline__ void st_sys64(unsigned long long *p, unsigned long long v)
+	{
+		asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+	}
+
+	__device__ __forceinline__ unsigned long long ld_sys64(const unsigned long long *p)
+	{
+		unsigned long long v;
+		asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+		return v;
+	}
+
+	// Phase A, one thread per rank: tell every rank that all I wrote into its block has landed, wait until every rank
+	// has told me. false: a rank did not get here within `limit_ns` (it died or never launched).
+	__device__ inline bool peer_arrive_wait(const BigParams &P, uint32_t &epoch, bool &dead, unsigned long long limit_ns = 4000000000ull)
 	{
 		if (dead)
 			return false; // one timeout is final: do not wait again
 		__threadfence_system();
-		atomicAdd_system(P.ctl0 + PEER_ARRIVE, 1u);
 		epoch++;
-		const uint32_t target = epoch * (uint32_t)P.world;
+		for (int j = 0; j < P.world; j++)
+			st_sys(P.peers[j] + PEER_SLOT_A + P.rank, epoch);
 		const unsigned long long t0 = global_timer_ns();
-		while ((int32_t)(ld_sys(P.ctl0 + PEER_ARRIVE) - target) < 0)
-			if (global_timer_ns() - t0 > limit_ns)
-			{
-				dead = true;
-				return false;
-			}
+		for (int j = 0; j < P.world; j++)
+			while ((int32_t)(ld_sys(P.ctl + PEER_SLOT_A + j) - epoch) < 0)
+				if (global_timer_ns() - t0 > limit_ns)
+				{
+					dead = true;
+					return false;
+				}
 		__threadfence_system();
+		return true;
+	}
+
+	// Phase B: every rank learns the total queue length and the smallest key of all ranks
+	__device__ inline bool peer_exchange(const BigParams &P, uint32_t &epoch, bool &dead, uint32_t count, uint32_t minkey, uint32_t &total, uint32_t &gmin)
+	{
+		total = 0u;
+		gmin = MTD_INF;
+		if (dead)
+			return false;
+		epoch++;
+		const unsigned long long tag = epoch & 0xFFull;
+		const unsigned long long v = ((unsigned long long)minkey << 32) | ((unsigned long long)(count < 0xFFFFFFu ? count : 0xFFFFFFu) << 8) | tag;
+		for (int j = 0; j < P.world; j++)
+			st_sys64(reinterpret_cast<unsigned long long *>(P.peers[j] + PEER_SLOT_B) + P.rank, v);
+		const unsigned long long t0 = global_timer_ns();
+		for (int j = 0; j < P.world; j++)
+		{
+			unsigned long long w;
+			while (((w = ld_sys64(reinterpret_cast<const unsigned long long *>(P.ctl + PEER_SLOT_B) + j)) & 0xFFull) != tag)
+				if (global_timer_ns() - t0 > 4000000000ull)
+				{
+					dead = true;
+					return false;
+				}
+			total += (uint32_t)((w >> 8) & 0xFFFFFFull);
+			gmin = min(gmin, (uint32_t)(w >> 32));
+		}
 		return true;
 	}
 
@@ -99,10 +146,10 @@ namespace mtd
 		unsigned long long tacc[8] = { 0, 0, 0, 0, 0, 0, 0, 0 }; // developer probe: cycles per phase, buckets, queue entries of this warp
 #endif
 
-		// Peer-coupled stripes: between two rounds every rank (1) waits until the boundary rows and keys of all ranks have
-		// landed, (2) queues the border tiles its neighbours offered a label to, (3) adds its queue length and smallest key
-		// to rank 0's totals, (4) waits again and reads the totals: all ranks see the same wavefront position and stop in
-		// the same round.
+		// Peer-coupled stripes: between two rounds every rank (1) tells all ranks that its boundary rows and keys have landed
+		// and waits for the same from all of them, (2) queues the border tiles its neighbours offered a label to, (3) stores
+		// its queue length and smallest key into every rank's block and reads everybody's: all ranks see the same wavefront
+		// position and stop in the same round.
 		uint32_t grid_gen = 0;
 		auto peer_grid_sync = [&]()
 		{
@@ -127,7 +174,7 @@ namespace mtd
 		};
 		uint32_t epoch = 0;
 		bool peer_dead = false;
-		auto peer_round_sync = [&](int r_next, bool first)
+		auto peer_round_sync = [&](int r_next)
 		{
 			__threadfence_system();
 			peer_grid_sync();
@@ -136,16 +183,7 @@ namespace mtd
 				const int slot = r_next % 3;
 				bool ok = true;
 				if (threadIdx.x == 0)
-				{
-					if (P.rank == 0)
-						for (int k = 0; k < 3; k++)
-							if (first || k == (r_next + 1) % 3) // last read two syncs ago: every rank has passed a barrier since
-							{
-								P.ctl0[PEER_PENDING + k] = 0u;
-								P.ctl0[PEER_MINKEY + k] = MTD_INF;
-							}
-					ok = peer_barrier(P, epoch, peer_dead);
-				}
+					ok = peer_arrive_wait(P, epoch, peer_dead);
 				__syncthreads();
 				for (int tx = (int)threadIdx.x; tx < P.tilesX; tx += (int)blockDim.x)
 				{
@@ -167,12 +205,8 @@ namespace mtd
 				if (threadIdx.x == 0)
 				{
 					const uint32_t cnt = __ldcg(P.count + slot), mk = __ldcg(P.minkey + slot);
-					if (cnt)
-						atomicAdd_system(P.ctl0 + PEER_PENDING + slot, cnt);
-					if (mk != MTD_INF)
-						atomicMin_system(P.ctl0 + PEER_MINKEY + slot, mk);
-					ok = peer_barrier(P, epoch, peer_dead) && ok;
-					const uint32_t gp = ld_sys(P.ctl0 + PEER_PENDING + slot), gm = ld_sys(P.ctl0 + PEER_MINKEY + slot);
+					uint32_t gp, gm;
+					ok = peer_exchange(P, epoch, peer_dead, cnt, mk, gp, gm) && ok;
 					P.minkey[slot] = gm;
 					P.ctl[PEER_GPENDING] = ok ? gp : 0u;
 					P.ctl[PEER_EPOCH] = epoch;
@@ -190,7 +224,7 @@ namespace mtd
 			{
 				// every rank has entered this run (so nobody still reads the halo copies of the previous one): hand my
 				// boundary rows as initialised (m, parked blocked tiles and sources 0) to the neighbours
-				if (threadIdx.x == 0 && !peer_barrier(P, epoch, peer_dead, 20000000000ull)) // the ranks' hosts may reach the launch seconds apart
+				if (threadIdx.x == 0 && !peer_arrive_wait(P, epoch, peer_dead, 20000000000ull)) // the ranks' hosts may reach the launch seconds apart
 					atomicOr(P.status, 8);
 				__syncthreads();
 				for (int x = (int)threadIdx.x; x < W; x += (int)blockDim.x)
@@ -203,7 +237,7 @@ namespace mtd
 				__threadfence_system();
 				__syncthreads();
 			}
-			peer_round_sync(round, true);
+			peer_round_sync(round);
 			if (__ldcg(P.ctl + PEER_GPENDING) == 0u)
 				max_rounds = 0;
 		}
@@ -670,7 +704,7 @@ namespace mtd
 		// ---- end of the round: everything appended to the next list is visible after the barrier ----
 		if (P.ctl0)
 		{
-			peer_round_sync(round + 1, false);
+			peer_round_sync(round + 1);
 			round++;
 			pending = __ldcg(P.ctl + PEER_GPENDING); // all ranks
 			if (pending == 0u)

@@ -126,7 +126,7 @@ def solve_peer_local(stripes, ctas=64):
     for s in stripes:
         s.ctx.stripe_peer_export()
     for i, s in enumerate(stripes):
-        s.ctx.stripe_peer_connect_local(i, n, stripes[i - 1].ctx if i > 0 else None, stripes[i + 1].ctx if i < n - 1 else None, stripes[0].ctx, ctas)
+        s.ctx.stripe_peer_connect_local(i, n, [t.ctx for t in stripes], ctas)
     for s in stripes:
         s.peer_launch()
     out, err = [], None
