@@ -224,7 +224,7 @@ namespace mtd
 			{
 				// every rank has entered this run (so nobody still reads the halo copies of the previous one): hand my
 				// boundary rows as initialised (m, parked blocked tiles and sources 0) to the neighbours
-				if (threadIdx.x == 0 && !peer_arrive_wait(P, epoch, peer_dead, 20000000000ull)) // the ranks' hosts may reach the launch seconds apart
+				if (threadIdx.x == 0 && !peer_arrive_wait(P, epoch, peer_dead, P.soft_grid ? 4000000000ull : 20000000000ull)) // the ranks' hosts may reach the launch seconds apart
 					atomicOr(P.status, 8);
 				__syncthreads();
 				for (int x = (int)threadIdx.x; x < W; x += (int)blockDim.x)
