@@ -143,7 +143,7 @@ namespace mtd
 		int round = round0;
 		uint32_t pending = 0;
 #ifdef MTD_TIMING
-		unsigned long long tacc[8] = { 0, 0, 0, 0, 0, 0, 0, 0 }; // developer probe: cycles per phase, buckets, queue entries of this warp
+		unsigned long long tacc[12] = { 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0 }; // developer probe: cycles per phase, buckets, queue entries, longest visit, visits over 60k / 100k cycles
 #endif
 
 		// Peer-coupled stripes: between two rounds every rank (1) tells all ranks that its boundary rows and keys have landed
@@ -301,6 +301,7 @@ namespace mtd
 			const bool interior = P.aligned16 && ly0 >= 0 && ly0 + RW <= Hl && gx0 >= 0 && gx0 + RW <= W;
 #ifdef MTD_TIMING
 			long long last__ = clock64();
+			const long long visit0__ = last__;
 #define MTD_WTICK(k)                          \
 	do                                        \
 	{                                         \
@@ -316,6 +317,20 @@ namespace mtd
 			if (interior)
 			{
 				// 34 rows x (8 + 8) sixteen-byte copies (labels, weights) + 34 x 2 x 2 apron words, spread over the lanes
+				// the two apron columns are 4-byte accesses a row apart: all of a lane's loads are issued before anything waits
+				// for one (L2 loads: the kernel lives across rounds, an L1 line would go stale), the row copies fly meanwhile
+				constexpr int APN = (RW * 4 + 31) / 32;
+				uint32_t apv[APN];
+#pragma unroll
+				for (int j = 0; j < APN; j++)
+				{
+					const int k = (int)lane + 32 * j;
+					const int ry = k >> 2, sel = k & 3; // sel bit0: right column, bit1: weights
+					const int rx = (sel & 1) ? RW - 1 : 0;
+					apv[j] = 0u;
+					if (k < RW * 4)
+						apv[j] = __ldcg(((sel & 2) ? P.wpack : ldist) + (size_t)(ly0 + ry) * W + gx0 + rx);
+				}
 				for (int k = (int)lane; k < RW * 16; k += 32)
 				{
 					const int ry = k >> 4, ch = k & 15;
@@ -323,12 +338,14 @@ namespace mtd
 					uint32_t *dst = (ch < 8 ? S.d : S.w) + ry * PITCH + 4 + (ch & 7) * 4;
 					cp_async_16(dst, src);
 				}
-				for (int k = (int)lane; k < RW * 4; k += 32)
+#pragma unroll
+				for (int j = 0; j < APN; j++)
 				{
-					const int ry = k >> 2, sel = k & 3; // sel bit0: right column, bit1: weights
+					const int k = (int)lane + 32 * j;
+					const int ry = k >> 2, sel = k & 3;
 					const int rx = (sel & 1) ? RW - 1 : 0;
-					const uint32_t *src = ((sel & 2) ? P.wpack : ldist) + (size_t)(ly0 + ry) * W + gx0 + rx;
-					(((sel & 2) ? S.w : S.d) + ry * PITCH + 3 + rx)[0] = __ldcg(src); // L2: the kernel lives across rounds, an L1 line would go stale
+					if (k < RW * 4)
+						(((sel & 2) ? S.w : S.d) + ry * PITCH + 3 + rx)[0] = apv[j];
 				}
 				cp_async_wait_all();
 			}
@@ -688,18 +705,27 @@ namespace mtd
 						if (k_bot != MTD_INF && ty == P.tilesY - 1 && P.peer_down_act)
 							atomicMin_system(P.peer_down_act + tx, k_bot);
 					}
-					if (k_top != MTD_INF && ty > 0)
-						activate_item(P, layer, tx, ty - 1, round, k_top);
-					if (k_bot != MTD_INF && ty < P.tilesY - 1)
-						activate_item(P, layer, tx, ty + 1, round, k_bot);
-					if (k_left != MTD_INF)
-						activate_item(P, layer, tx - 1, ty, round, k_left);
-					if (k_right != MTD_INF)
-						activate_item(P, layer, tx + 1, ty, round, k_right);
 					atomicAdd(P.total_active, 1u);
 				}
+				// one lane per neighbour: the four queue insertions (each a chain of dependent atomics) run side by side
+				if (lane == 0 && k_top != MTD_INF && ty > 0)
+					activate_item(P, layer, tx, ty - 1, round, k_top);
+				if (lane == 1 && k_bot != MTD_INF && ty < P.tilesY - 1)
+					activate_item(P, layer, tx, ty + 1, round, k_bot);
+				if (lane == 2 && k_left != MTD_INF)
+					activate_item(P, layer, tx - 1, ty, round, k_left);
+				if (lane == 3 && k_right != MTD_INF)
+					activate_item(P, layer, tx + 1, ty, round, k_right);
 			}
 			MTD_WTICK(4);
+#ifdef MTD_TIMING
+			{
+				const unsigned long long dv = (unsigned long long)(last__ - visit0__);
+				tacc[7] = dv > tacc[7] ? dv : tacc[7];
+				tacc[8] += dv > 60000ull ? 1ull : 0ull;
+				tacc[9] += dv > 100000ull ? 1ull : 0ull;
+			}
+#endif
 		}
 		// ---- end of the round: everything appended to the next list is visible after the barrier ----
 		if (P.ctl0)
@@ -722,9 +748,14 @@ namespace mtd
 			atomicOr(P.status, 1);
 #ifdef MTD_TIMING
 		if (lane == 0)
-			for (int k = 0; k < 8; k++)
+			for (int k = 0; k < 12; k++)
 				if (tacc[k])
-					atomicAdd(&g_big_timing[k], tacc[k]);
+				{
+					if (k == 7)
+						atomicMax(&g_big_timing[k], tacc[k]);
+					else
+						atomicAdd(&g_big_timing[k], tacc[k]);
+				}
 #endif
 		if (blockIdx.x == 0 && threadIdx.x == 0)
 		{
