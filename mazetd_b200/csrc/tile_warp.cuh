@@ -302,6 +302,7 @@ namespace mtd
 #ifdef MTD_TIMING
 			long long last__ = clock64();
 			const long long visit0__ = last__;
+			unsigned long long vsteps__ = 0, vstage__ = 0;
 #define MTD_WTICK(k)                          \
 	do                                        \
 	{                                         \
@@ -377,6 +378,9 @@ namespace mtd
 			}
 			__syncwarp();
 			MTD_WTICK(0);
+#ifdef MTD_TIMING
+			vstage__ = (unsigned long long)(last__ - visit0__);
+#endif
 
 			// ---- seeds: pending cells enter q[0]; every lowered label is appended (duplicates are harmless) ----
 			uint32_t tail = 0;            // entries in the queue being filled (warp-uniform)
@@ -530,6 +534,7 @@ namespace mtd
 #ifdef MTD_TIMING
 				tacc[5] += 1ull;
 				tacc[6] += nq;
+				vsteps__ += 1ull;
 #endif
 				uint32_t newmin = MTD_INF;
 				for (uint32_t base = 0; base < nq; base += 32u)
@@ -724,6 +729,11 @@ namespace mtd
 				tacc[7] = dv > tacc[7] ? dv : tacc[7];
 				tacc[8] += dv > 60000ull ? 1ull : 0ull;
 				tacc[9] += dv > 100000ull ? 1ull : 0ull;
+				if (dv > 60000ull)
+				{
+					tacc[10] += vsteps__; // what the long visits are made of
+					tacc[11] += vstage__;
+				}
 			}
 #endif
 		}
