@@ -159,7 +159,7 @@ namespace mtd
 
 #ifdef MTD_TIMING
 	// developer probe (never in the shipped build): cycles per phase of a tile visit, summed over all visits
-	__device__ unsigned long long g_big_timing[12];
+	__device__ unsigned long long g_big_timing[16];
 #define MTD_BTICK(k)                                                      \
 	do                                                                    \
 	{                                                                     \

@@ -518,12 +518,12 @@ namespace
 		CU(cudaMemcpyAsync(&ctx->hflags->big_items, P.total_active, 4, cudaMemcpyDeviceToHost, ctx->stream));
 #ifdef MTD_TIMING
 		{
-			unsigned long long t[12], z[12] = { 0 };
+			unsigned long long t[16], z[16] = { 0 };
 			cudaMemcpyFromSymbol(t, g_big_timing, sizeof(t));
 			cudaMemcpyToSymbol(g_big_timing, z, sizeof(z));
 			cudaStreamSynchronize(ctx->stream);
 			const double v = (double)ctx->hflags->big_items;
-			printf("BIGTIMING rounds=%d visits=%.0f | per visit cycles: stage=%.0f seed=%.0f engine=%.0f writeback=%.0f activate=%.0f | buckets/visit=%.1f cells/bucket=%.1f | longest visit=%llu cycles, visits over 60k cycles=%llu (steps per such visit %.1f, stage cycles %.0f), over 100k=%llu\n", round, v, t[0] / v, t[1] / v, t[2] / v, t[3] / v, t[4] / v, t[5] / v, t[5] ? (double)t[6] / t[5] : 0.0, t[7], t[8], t[8] ? (double)t[10] / t[8] : 0.0, t[8] ? (double)t[11] / t[8] : 0.0, t[9]);
+			printf("BIGTIMING rounds=%d visits=%.0f | per visit cycles: stage=%.0f seed=%.0f engine=%.0f writeback=%.0f activate=%.0f | buckets/visit=%.1f cells/bucket=%.1f | longest visit=%llu cycles, visits over 60k cycles=%llu (steps per such visit %.1f, stage cycles %.0f), over 100k=%llu | list entries dropped as stale=%llu, deferred by the priority window=%llu\n", round, v, t[0] / v, t[1] / v, t[2] / v, t[3] / v, t[4] / v, t[5] / v, t[5] ? (double)t[6] / t[5] : 0.0, t[7], t[8], t[8] ? (double)t[10] / t[8] : 0.0, t[8] ? (double)t[11] / t[8] : 0.0, t[9], t[12], t[13]);
 		}
 #endif
 		{

@@ -143,7 +143,7 @@ namespace mtd
 		int round = round0;
 		uint32_t pending = 0;
 #ifdef MTD_TIMING
-		unsigned long long tacc[12] = { 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0 }; // developer probe: cycles per phase, buckets, queue entries, longest visit, visits over 60k / 100k cycles
+		unsigned long long tacc[16] = { 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0 }; // developer probe: cycles per phase, buckets, queue entries, longest visit, visits over 60k / 100k cycles
 #endif
 
 		// Peer-coupled stripes: between two rounds every rank (1) tells all ranks that its boundary rows and keys have landed
@@ -290,6 +290,10 @@ namespace mtd
 					}
 				}
 				k = __shfl_sync(FULL_MASK, k, 0);
+#ifdef MTD_TIMING
+				tacc[12] += k == MTD_INF ? 1ull : 0ull;                 // stale entries dropped
+				tacc[13] += (k != MTD_INF && k >= kthr) ? 1ull : 0ull;  // entries deferred by the priority window
+#endif
 				if (k == MTD_INF || k >= kthr)
 					continue;
 			}
@@ -696,8 +700,8 @@ namespace mtd
 					k_left = 0u;
 				if (f & 32u)
 					k_right = 0u;
-				if (P.ctl0)
-					__threadfence_system(); // ... on the neighbour ranks too
+				if (P.ctl0 && (ty == 0 || ty == P.tilesY - 1))
+					__threadfence_system(); // a border tile of the stripe: ... on the neighbour rank too
 				else
 					__threadfence(); // distances are visible before the neighbour can be scheduled
 				__syncwarp();
@@ -758,7 +762,7 @@ namespace mtd
 			atomicOr(P.status, 1);
 #ifdef MTD_TIMING
 		if (lane == 0)
-			for (int k = 0; k < 12; k++)
+			for (int k = 0; k < 16; k++)
 				if (tacc[k])
 				{
 					if (k == 7)
