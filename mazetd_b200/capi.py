@@ -14,7 +14,7 @@ M = 0xFFFFFFFF
 
 EXPORTS = [
     "mtd_create", "mtd_destroy", "mtd_last_error", "mtd_version", "mtd_synchronize", "mtd_launch_count",
-    "mtd_profile_enable", "mtd_profile_read", "mtd_debug_set",
+    "mtd_profile_enable", "mtd_profile_read", "mtd_debug_set", "mtd_big_stats",
     "mtd_grid_upload", "mtd_grid_upload_dev", "mtd_grid_set_flags", "mtd_neighbor_distances", "mtd_edge_weights",
     "mtd_directions_update", "mtd_directions_update_dev", "mtd_directions_layers_dev",
     "mtd_stripe_upload", "mtd_stripe_upload_dev", "mtd_stripe_begin_dev", "mtd_stripe_exchange_dev", "mtd_stripe_finalize_dev", "mtd_stripe_round_budget", "mtd_stripe_pending",
@@ -61,6 +61,7 @@ def load():
     L.mtd_profile_enable.argtypes = [vp, C.c_int]
     L.mtd_profile_read.argtypes = [vp, C.c_int, C.POINTER(C.c_double), C.POINTER(u64)]
     L.mtd_debug_set.argtypes = [vp, C.c_int, C.c_int64]
+    L.mtd_big_stats.argtypes = [vp, C.c_void_p]
     L.mtd_grid_upload.argtypes = [vp, i32, i32, i32, i32, vp, vp]
     L.mtd_grid_upload_dev.argtypes = [vp, i32, i32, i32, i32, vp, vp]
     L.mtd_grid_set_flags.argtypes = [vp, u32, C.c_uint16]
@@ -143,6 +144,14 @@ class Context:
     DEBUG_GROUP_WARPS = 2
     DEBUG_WALKER = 3
     DEBUG_TILE_DELTA = 4
+    DEBUG_BIG_ASYNC = 5
+    DEBUG_ASYNC_DELTA = 6
+
+    def big_stats(self):
+        """rounds, tile visits, scheduler polls, dataflow flag of the last tiled update"""
+        out = (C.c_uint32 * 4)()
+        self._ck(self.L.mtd_big_stats(self.h, out))
+        return dict(rounds=int(out[0]), visits=int(out[1]), polls=int(out[2]), dataflow=bool(out[3]))
 
     def debug_set(self, key, value):
         self._ck(self.L.mtd_debug_set(self.h, int(key), int(value)))

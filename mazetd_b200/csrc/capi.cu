@@ -8,8 +8,10 @@
 #include <cstdlib>
 #include <cstring>
 #include <climits>
+#include <map>
 #include <mutex>
 #include <new>
+#include <utility>
 #include <vector>
 
 #include <cuda_runtime.h>
@@ -21,6 +23,7 @@
 #include "noise.cuh"
 #include "small_maps.cuh"
 #include "sssp_warp.cuh"
+#include "tile_async.cuh"
 
 using namespace mtd;
 
@@ -88,6 +91,7 @@ namespace
 		uint32_t big_items;     // (layer, tile) visits of the last tiled relaxation (statistics)
 		uint32_t stage_blocked; // pinned staging word of the trial grid's extra blocked tile
 		uint32_t stripe_improved; // halo cells lowered by the last mtd_stripe_exchange_dev
+		uint32_t async_ctl[4];    // ACTL_* words of the last k_tile_async run
 	};
 }
 
@@ -115,6 +119,11 @@ struct mtd_ctx
 	DevBuf<uint32_t> sources;
 	int tilesX = 0, tilesY = 0;
 	uint32_t last_rounds = 0;
+	DevBuf<uint32_t> a_inbox, a_tail, a_ctamin, a_ctl; // dataflow scheduler of k_tile_async: inbox rings, ring tails, per-CTA smallest keys, control words
+	bool big_async = true;         // large grids: k_tile_async (no global rounds); false = k_tile_rounds (A/B and multi-stripe contexts)
+	uint32_t async_delta = 32768;  // priority window of the dataflow scheduler (label units)
+	uint32_t last_visits = 0;
+	bool last_async = false;
 	uint32_t tile_delta = 98304; // visit window of the tile-level priority (label units); swept 8k..inf on 4096^2 and 16384^2 (weights 255..570): flat optimum 64k..256k
 	// row stripe of a larger grid (multi-GPU, one rank per stripe): rows [sy0, sy1) of a W x sH grid are this context's grid
 	bool stripe = false;
@@ -317,6 +326,35 @@ namespace
 		return (int)(b < cap ? (b ? b : 1) : cap);
 	}
 
+
+	// cudaFuncSetAttribute / occupancy are per DEVICE: one entry per (device, kernel), guarded by a process-wide mutex
+	// (contexts of several devices may live in one process and are locked independently)
+	std::mutex g_cfg_mu;
+	std::map<std::pair<int, const void *>, int> g_cfg;
+
+	// opts `func` in to `smem` bytes of dynamic shared memory on the context's device (once) and returns the resident
+	// CTAs per SM for `threads` threads, or -1 with the error recorded
+	int kernel_config(mtd_ctx *ctx, const void *func, int threads, size_t smem)
+	{
+		std::lock_guard<std::mutex> lk(g_cfg_mu);
+		const auto key = std::make_pair(ctx->device, func);
+		auto it = g_cfg.find(key);
+		if (it != g_cfg.end())
+			return it->second;
+		cudaError_t e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		int per_sm = 0;
+		if (e == cudaSuccess)
+			e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, func, threads, smem);
+		if (e != cudaSuccess)
+		{
+			(void)cudaGetLastError();
+			fail(ctx, MTD_ERR_CUDA, "kernel configuration failed: %s", cudaGetErrorString(e));
+			return -1;
+		}
+		g_cfg[key] = per_sm;
+		return per_sm;
+	}
+
 	// k_big_finalize4 moves rows as 16-byte vectors: the width and every base it touches must allow that
 	bool finalize_vec_ok(mtd_ctx *ctx, const void *d_dist, const void *d_tiles)
 	{
@@ -334,12 +372,8 @@ namespace
 		P.smem_budget = (uint32_t)MAX_SMEM;
 		P.qseg_cap = ctx->debug_qseg_cap;
 		const SmallLayout L = small_layout(P.W, P.H, P.R, P.smem_budget, P.qseg_cap, GW);
-		static bool configured = false;
-		if (!configured)
-		{
-			CU(cudaFuncSetAttribute(k_waypoints_small<GW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MAX_SMEM));
-			configured = true;
-		}
+		if (kernel_config(ctx, (const void *)k_waypoints_small<GW>, SMALL_THREADS + 32, MAX_SMEM) < 0)
+			return MTD_ERR_CUDA;
 		CU(ctx->map_counter.reserve(1));
 		CU(cudaMemsetAsync(ctx->map_counter.p, 0, 4, ctx->stream));
 		P.map_counter = ctx->map_counter.p;
@@ -403,14 +437,11 @@ namespace
 	{
 		using WF = WarpFrame<BIG_TS>;
 		const size_t smem = sizeof(WF) * BIG_WARPS;
-		static int ctas_per_sm = 0;
-		if (!ctas_per_sm)
-		{
-			CU(cudaFuncSetAttribute(k_tile_rounds<BIG_TS, BIG_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-			CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, k_tile_rounds<BIG_TS, BIG_WARPS>, BIG_WARPS * 32, smem));
-			if (ctas_per_sm < 1)
-				return fail(ctx, MTD_ERR_CUDA, "the tile relaxation kernel does not fit an SM");
-		}
+		const int ctas_per_sm = kernel_config(ctx, (const void *)k_tile_rounds<BIG_TS, BIG_WARPS>, BIG_WARPS * 32, smem);
+		if (ctas_per_sm < 0)
+			return MTD_ERR_CUDA;
+		if (ctas_per_sm < 1)
+			return fail(ctx, MTD_ERR_CUDA, "the tile relaxation kernel does not fit an SM");
 		const int limit = 4 * (ctx->tilesX + ctx->tilesY) * BIG_TS + 100000; // far above any wavefront depth: a safety net, not a tuning knob
 		int max_rounds = budget > 0 ? budget : limit;
 		uint32_t *d_out = nullptr;
@@ -436,6 +467,61 @@ namespace
 		round = (int)ctx->hflags->round_out[1];
 		if (budget <= 0 && pending != 0)
 			return fail(ctx, MTD_ERR_CUDA, "tile relaxation did not converge after %d rounds", round);
+		return MTD_OK;
+	}
+
+
+	// The dataflow form of run_rounds (tile_async.cuh): ONE launch, no global rounds. Returns MTD_ERR_CAPACITY (without a
+	// message) when a CTA would own more items than its scheduler holds: the caller then uses the round-based kernel.
+	bool async_fits(mtd_ctx *ctx, size_t nitems)
+	{
+		return (nitems + (size_t)ctx->sms - 1) / (size_t)ctx->sms + 64 <= (size_t)ASYNC_PCAP;
+	}
+
+	int run_async(mtd_ctx *ctx, BigParams P, size_t nitems)
+	{
+		const size_t smem = async_smem_bytes<BIG_TS>();
+		const int threads = (ASYNC_WORKERS + 1) * 32;
+		const int per_sm = kernel_config(ctx, (const void *)k_tile_async<BIG_TS>, threads, smem);
+		if (per_sm < 0)
+			return MTD_ERR_CUDA;
+		if (per_sm < 1)
+			return fail(ctx, MTD_ERR_CUDA, "the dataflow relaxation kernel does not fit an SM");
+		const int ctas = ctx->sms;
+		uint32_t cap = 64;
+		while ((size_t)cap < (nitems + ctas - 1) / ctas + 64)
+			cap <<= 1;
+		CU(ctx->a_inbox.reserve((size_t)ctas * cap));
+		CU(ctx->a_tail.reserve((size_t)ctas * 32));
+		CU(ctx->a_ctamin.reserve((size_t)ctas));
+		CU(ctx->a_ctl.reserve(ACTL_WORDS));
+		CU(cudaMemsetAsync(ctx->a_inbox.p, 0, (size_t)ctas * cap * 4, ctx->stream));
+		CU(cudaMemsetAsync(ctx->a_tail.p, 0, (size_t)ctas * 32 * 4, ctx->stream));
+		CU(cudaMemsetAsync(ctx->a_ctamin.p, 0xFF, (size_t)ctas * 4, ctx->stream));
+		CU(cudaMemsetAsync(ctx->a_ctl.p, 0, ACTL_WORDS * 4, ctx->stream));
+		AsyncParams A;
+		memset(&A, 0, sizeof(A));
+		A.inbox = ctx->a_inbox.p;
+		A.tail = ctx->a_tail.p;
+		A.ctamin = ctx->a_ctamin.p;
+		A.ctl = ctx->a_ctl.p;
+		A.cap_mask = cap - 1u;
+		A.ctas = ctas;
+		A.time_limit_ns = 20000000000ull; // an update that takes 20 s is reported, not waited for
+		P.tile_delta = ctx->async_delta;
+		k_async_seed<BIG_TS><<<(P.nlayers * P.nsrc + 127) / 128, 128, 0, ctx->stream>>>(P, A);
+		LAUNCHED();
+		void *args[] = { (void *)&P, (void *)&A };
+		{
+			ProfScope prof(ctx, MTD_K_BIG_RELAX);
+			CU(cudaLaunchCooperativeKernel((const void *)k_tile_async<BIG_TS>, dim3((unsigned)ctas), dim3((unsigned)threads), args, smem, ctx->stream));
+			LAUNCHED();
+		}
+		CU(cudaMemcpyAsync(ctx->hflags->async_ctl, ctx->a_ctl.p, 4 * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		CU(cudaStreamSynchronize(ctx->stream));
+		if (ctx->hflags->async_ctl[ACTL_ABORT] != 0 || ctx->hflags->async_ctl[ACTL_OUTSTANDING] != 0)
+			return fail(ctx, MTD_ERR_CUDA, "dataflow relaxation stopped with %u items outstanding (time limit)", ctx->hflags->async_ctl[ACTL_OUTSTANDING]);
+		ctx->last_visits = ctx->hflags->async_ctl[ACTL_VISITS];
 		return MTD_OK;
 	}
 
@@ -504,15 +590,23 @@ namespace
 		P.status = ctx->d_status.p;
 		P.aligned16 = (ctx->W % 4 == 0) && ((uintptr_t)d_dist % 16 == 0) && ((uintptr_t)ctx->wpack.p % 16 == 0) ? 1 : 0;
 
-		k_big_seed<BIG_TS><<<(nlayers * nsrc + 127) / 128, 128, 0, ctx->stream>>>(P);
-		LAUNCHED();
-
 		int round = 0;
 		uint32_t pending = 0;
+		if (ctx->big_async && async_fits(ctx, nitems))
 		{
+			const int rc = run_async(ctx, P, nitems);
+			if (rc)
+				return rc;
+			ctx->last_async = true;
+		}
+		else
+		{
+			k_big_seed<BIG_TS><<<(nlayers * nsrc + 127) / 128, 128, 0, ctx->stream>>>(P);
+			LAUNCHED();
 			const int rc = run_rounds(ctx, P, round, 0, pending);
 			if (rc)
 				return rc;
+			ctx->last_async = false;
 		}
 		ctx->last_rounds = (uint32_t)round;
 		CU(cudaMemcpyAsync(&ctx->hflags->big_items, P.total_active, 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -955,9 +1049,29 @@ extern "C" int mtd_debug_set(mtd_ctx *ctx, int key, int64_t value)
 			return fail(ctx, MTD_ERR_ARG, "tile delta must be in 1 .. 2^32-1");
 		ctx->tile_delta = (uint32_t)value;
 		return MTD_OK;
+	case MTD_DEBUG_BIG_ASYNC:
+		ctx->big_async = value != 0;
+		return MTD_OK;
+	case MTD_DEBUG_ASYNC_DELTA:
+		if (value < 1 || value > 0xFFFFFFFFll)
+			return fail(ctx, MTD_ERR_ARG, "async delta must be in 1 .. 2^32-1");
+		ctx->async_delta = (uint32_t)value;
+		return MTD_OK;
 	default:
 		return fail(ctx, MTD_ERR_ARG, "unknown debug key %d", key);
 	}
+}
+
+extern "C" int mtd_big_stats(mtd_ctx *ctx, uint32_t *out4)
+{
+	if (!ctx || !out4)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	out4[0] = ctx->last_rounds;
+	out4[1] = ctx->last_async ? ctx->last_visits : ctx->hflags->big_items;
+	out4[2] = ctx->last_async ? ctx->hflags->async_ctl[ACTL_IDLE_POLLS] : 0u;
+	out4[3] = ctx->last_async ? 1u : 0u;
+	return MTD_OK;
 }
 
 extern "C" int mtd_profile_enable(mtd_ctx *ctx, int on)
@@ -1699,12 +1813,8 @@ static int mapgen_dev(mtd_ctx *ctx, const mtd_mapgen_params *p, uint64_t s1, uin
 	const int T = p->W * p->H;
 	if (p->W > 256 || p->H > 256 || T >= 65536 || mapgen_grid_smem(T) > MAX_SMEM || !small_fits(p->W, p->H, p->nwp > 0 ? p->nwp : 1))
 		return fail(ctx, MTD_ERR_CAPACITY, "procedural maps must fit one CTA's shared memory (reference size is 101x101)");
-	static bool configured = false;
-	if (!configured)
-	{
-		CU(cudaFuncSetAttribute(k_mapgen_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MAX_SMEM));
-		configured = true;
-	}
+	if (kernel_config(ctx, (const void *)k_mapgen_grid, 512, MAX_SMEM) < 0)
+		return MTD_ERR_CUDA;
 	MapgenGridParams G;
 	memset(&G, 0, sizeof(G));
 	G.W = p->W;

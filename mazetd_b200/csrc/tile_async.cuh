@@ -1,0 +1,678 @@
+// tile_async.cuh -- the large-grid relaxation (Directions::update, sources/map/paths.cpp:51-77) WITHOUT global rounds.
+//
+// k_tile_rounds (tile_warp.cuh) stops every warp of the GPU at a grid-wide barrier ~290 times per update of a 16384^2 grid,
+// and a round lasts as long as its slowest warp: three quarters of a round were spent waiting (profiles/r01h_*). Here the
+// (layer, 32x32 tile) work items flow through the machine as a dataflow:
+//   * every item has ONE owner CTA (a fixed function of layer and tile position; tiles that are neighbours in the grid
+//     have different owners, so a wavefront -- a curve of tiles -- spreads over all SMs);
+//   * an offer to an item is `atomicMin(key[item], label)`; the offer that turns the key from "nothing pending" into a
+//     label also appends the item to the owner's inbox ring in global memory (so an item is on at most one list at a
+//     time and the ring, sized to the owner's items, cannot overflow);
+//   * each CTA = 16 worker warps + 1 scheduler warp. The scheduler drains the inbox into a pending list in shared memory,
+//     re-reads the pending keys (offers only ever lower them), publishes the CTA's smallest key, reads every CTA's
+//     smallest key (148 words) to get the global wavefront position, and hands the pending items with the smallest keys
+//     inside the priority window to idle workers through per-worker mailboxes in shared memory. Workers spin on shared
+//     memory only. A tile is never given to two workers at once (write-backs of one tile must not interleave);
+//   * termination: a global count of items that are pending or being visited; every increment (an offer that made an item
+//     pending) happens before the decrement of the visit that issued it, so the count reaches zero exactly once.
+// The labels converge to the unique fixpoint whatever the order of visits, so the result is bit-identical to the
+// round-based kernel and to the reference. The priority window (visit only items whose key is within `tile_delta` of the
+// smallest key anywhere) is what keeps warps from running ahead of the wavefront and multiplying revisits.
+#pragma once
+
+#include "common.cuh"
+#include "sssp_warp.cuh"
+// included after big_grid.cuh and tile_warp.cuh: BigParams, WarpFrame, cp_async_*, warp_redux_min, global_timer_ns
+
+namespace mtd
+{
+	constexpr int ASYNC_WORKERS = 16;     // worker warps per CTA (one CTA per SM)
+	constexpr int ASYNC_PCAP = 2048;      // pending items a scheduler can hold (>= items owned by a CTA, checked on the host)
+	constexpr int ASYNC_KX = 12;          // owner = (tx + KX * ty + KL * layer) mod CTAs: a 12 x 12 block of tiles has 144 different owners
+	constexpr int ASYNC_KL = 53;
+	constexpr uint32_t SLOT_IDLE = 0xFFFFFFFFu, SLOT_EXIT = 0xFFFFFFFEu;
+	// control words (AsyncCtl::ctl)
+	constexpr int ACTL_OUTSTANDING = 0; // items pending or in flight
+	constexpr int ACTL_ABORT = 1;       // a scheduler hit the time limit
+	constexpr int ACTL_VISITS = 2;      // statistics
+	constexpr int ACTL_IDLE_POLLS = 3;
+	constexpr int ACTL_WORDS = 32;
+
+	struct AsyncParams
+	{
+		uint32_t *inbox;     // [ctas][cap] item + 1, 0 = empty
+		uint32_t *tail;      // [ctas * 32] (one 128-byte line per CTA) entries ever appended to the CTA's inbox
+		uint32_t *ctamin;    // [ctas] smallest key among the CTA's pending and in-flight items (MTD_INF: none)
+		uint32_t *ctl;       // ACTL_* words
+		uint32_t cap_mask;   // cap - 1 (cap is a power of two >= items per owner)
+		int ctas;
+		unsigned long long time_limit_ns;
+	};
+
+	__device__ __forceinline__ int async_owner(const AsyncParams &A, int layer, int tx, int ty)
+	{
+		return (int)(((uint32_t)tx + (uint32_t)ASYNC_KX * (uint32_t)ty + (uint32_t)ASYNC_KL * (uint32_t)layer) % (uint32_t)A.ctas);
+	}
+
+	// offer label `key` to item (layer, tx, ty); the caller has made its labels visible (__threadfence) before
+	__device__ __forceinline__ void async_offer(const BigParams &P, const AsyncParams &A, int layer, int tx, int ty, uint32_t key)
+	{
+		if (tx < 0 || tx >= P.tilesX || ty < 0 || ty >= P.tilesY)
+			return;
+		const uint32_t item = (uint32_t)layer * (uint32_t)(P.tilesX * P.tilesY) + (uint32_t)(ty * P.tilesX + tx);
+		const uint32_t old = atomicMin(P.key + item, key);
+		if (old == MTD_INF)
+		{
+			atomicAdd(A.ctl + ACTL_OUTSTANDING, 1u);
+			const int o = async_owner(A, layer, tx, ty);
+			const uint32_t pos = atomicAdd(A.tail + o * 32, 1u);
+			__stcg(A.inbox + (size_t)o * (A.cap_mask + 1u) + (pos & A.cap_mask), item + 1u);
+			atomicMin(A.ctamin + o, key); // the owner's published wavefront position covers the offer before its scheduler has seen it
+		}
+	}
+
+	// sources := 0, their items pending (one thread per (layer, source)); ctl[OUTSTANDING] counts them
+	template<int TS>
+	__global__ void k_async_seed(const BigParams P, const AsyncParams A)
+	{
+		const int s = blockIdx.x * blockDim.x + threadIdx.x;
+		if (s >= P.nlayers * P.nsrc)
+			return;
+		const int layer = s / P.nsrc;
+		const uint32_t src = P.sources[s];
+		const int x = (int)(src % (uint32_t)P.W), y = (int)(src / (uint32_t)P.W);
+		if (y < P.y0 || y >= P.y1)
+			return;
+		P.dist[(size_t)layer * P.layer_stride + (size_t)(y - P.y0) * P.W + x] = 0u;
+		__threadfence();
+		async_offer(P, A, layer, x / TS, (y - P.y0) / TS, 0u);
+	}
+
+	// One visit of item (layer, tx, ty) by one warp: stage the 34 x 34 frame (labels + packed weights), seed from the apron
+	// and the sources, run the warp-synchronous bucketed wavefront to local convergence, write the interior back.
+	// Returns in k[4] (warp-uniform) the smallest label on offer to the tile above / below / left / right (MTD_INF: none).
+	// Same arithmetic as the visit inside k_tile_rounds; `guard` is raised when a label gets close to the uint32 wrap.
+	template<int TS>
+	__device__ __forceinline__ void warp_visit(const BigParams &P, WarpFrame<TS> &S, int layer, int tx, int ty, uint32_t lane, uint32_t lt, uint32_t (&k)[4], bool &guard)
+	{
+		using WT = WarpFrame<TS>;
+		constexpr int RW = WT::RW, PITCH = WT::PITCH, QCAP = WT::QCAP;
+		const int W = P.W;
+		const int Hl = P.y1 - P.y0;
+		const int gx0 = tx * TS - 1; // global x of frame column 0
+		const int ly0 = ty * TS - 1; // local row of frame row 0
+		uint32_t *ldist = P.dist + (size_t)layer * P.layer_stride;
+		const uint32_t *lsrc = P.sources + (size_t)layer * P.nsrc;
+		const int brow = min(TS + 1, Hl - ly0); // frame row just below the tile's last existing row
+		const bool interior = P.aligned16 && ly0 >= 0 && ly0 + RW <= Hl && gx0 >= 0 && gx0 + RW <= W;
+
+		// ---- stage ----
+		if (interior)
+		{
+			constexpr int APN = (RW * 4 + 31) / 32;
+			uint32_t apv[APN];
+#pragma unroll
+			for (int j = 0; j < APN; j++)
+			{
+				const int q = (int)lane + 32 * j;
+				const int ry = q >> 2, sel = q & 3; // sel bit0: right column, bit1: weights
+				const int rx = (sel & 1) ? RW - 1 : 0;
+				apv[j] = 0u;
+				if (q < RW * 4)
+					apv[j] = __ldcg(((sel & 2) ? P.wpack : ldist) + (size_t)(ly0 + ry) * W + gx0 + rx);
+			}
+			for (int q = (int)lane; q < RW * 16; q += 32)
+			{
+				const int ry = q >> 4, ch = q & 15;
+				const uint32_t *src = (ch < 8 ? ldist : P.wpack) + (size_t)(ly0 + ry) * W + gx0 + 1 + (ch & 7) * 4;
+				uint32_t *dst = (ch < 8 ? S.d : S.w) + ry * PITCH + 4 + (ch & 7) * 4;
+				cp_async_16(dst, src);
+			}
+#pragma unroll
+			for (int j = 0; j < APN; j++)
+			{
+				const int q = (int)lane + 32 * j;
+				const int ry = q >> 2, sel = q & 3;
+				const int rx = (sel & 1) ? RW - 1 : 0;
+				if (q < RW * 4)
+					(((sel & 2) ? S.w : S.d) + ry * PITCH + 3 + rx)[0] = apv[j];
+			}
+			cp_async_wait_all();
+		}
+		else
+		{
+			for (int q = (int)lane; q < RW * RW; q += 32)
+			{
+				const int ry = q / RW, rx = q - ry * RW;
+				const int ly = ly0 + ry, gx = gx0 + rx;
+				uint32_t dv = 0u, wv = 0u;
+				if (gx >= 0 && gx < W)
+				{
+					if (ly >= 0 && ly < Hl)
+					{
+						dv = __ldcg(ldist + (size_t)ly * W + gx);
+						wv = P.wpack[(size_t)ly * W + gx];
+					}
+					else if (ly == -1 && P.up_row)
+					{
+						dv = __ldcg(P.up_row + gx);
+						wv = P.up_wpack[gx];
+					}
+					else if (ly == Hl && P.down_row)
+						dv = __ldcg(P.down_row + gx);
+				}
+				S.d[ry * PITCH + 3 + rx] = dv;
+				S.w[ry * PITCH + 3 + rx] = wv;
+			}
+		}
+		__syncwarp();
+
+		// ---- seeds ----
+		uint32_t tail = 0;
+		uint32_t my_min = MTD_INF;
+		uint16_t *wq = S.q[0];
+		auto relax_into = [&](bool want, uint32_t v, uint32_t nd)
+		{
+			bool improved = false;
+			if (want && nd >= BIG_SETTLE_LIMIT)
+				guard = true;
+			else if (want)
+				improved = nd < atomicMin(&S.d[v], nd);
+			const uint32_t bal = __ballot_sync(0xFFFFFFFFu, improved);
+			if (improved)
+			{
+				const uint32_t slot = tail + __popc(bal & lt);
+				if (slot < (uint32_t)QCAP)
+					wq[slot] = (uint16_t)v;
+				my_min = min(my_min, nd);
+			}
+			tail += __popc(bal);
+		};
+		uint32_t ap_old[4];
+#pragma unroll
+		for (int side = 0; side < 4; side++)
+		{
+			const int i = (int)lane;
+			uint32_t a, v, wsel;
+			if (side == 0)
+			{
+				a = (uint32_t)(0 * PITCH + 4 + i);
+				v = a + PITCH;
+				wsel = S.w[a] >> 16;
+			}
+			else if (side == 1)
+			{
+				a = (uint32_t)(brow * PITCH + 4 + i);
+				v = a - PITCH;
+				wsel = S.w[v] >> 16;
+			}
+			else if (side == 2)
+			{
+				a = (uint32_t)((1 + i) * PITCH + 3);
+				v = a + 1u;
+				wsel = S.w[a] & 0xFFFFu;
+			}
+			else
+			{
+				a = (uint32_t)((1 + i) * PITCH + 4 + TS);
+				v = a - 1u;
+				wsel = S.w[v] & 0xFFFFu;
+			}
+			const uint32_t da = S.d[a];
+			ap_old[side] = da;
+			const bool row_exists = side < 2 || 1 + i < brow;
+			relax_into(row_exists && da != 0u && da != MTD_INF, v, da + MIN_EDGE + wsel);
+		}
+		uint32_t src_sides = 0;
+		for (int s0 = 0; s0 < P.nsrc; s0 += 32)
+		{
+			const int s = s0 + (int)lane;
+			bool want = false;
+			uint32_t v = 0, nd = 0;
+			if (s < P.nsrc)
+			{
+				const uint32_t src = lsrc[s];
+				const int rx = (int)(src % (uint32_t)W) - gx0, ry = (int)(src / (uint32_t)W) - P.y0 - ly0;
+				const bool inx = rx >= 1 && rx <= TS, iny = ry >= 1 && ry < brow;
+				const uint32_t a = (uint32_t)(ry * PITCH + rx + 3);
+				if (ry == 0 && inx)
+				{
+					want = true;
+					v = a + PITCH;
+					nd = MIN_EDGE + (S.w[a] >> 16);
+				}
+				else if (ry == brow && inx)
+				{
+					want = true;
+					v = a - PITCH;
+					nd = MIN_EDGE + (S.w[v] >> 16);
+				}
+				else if (rx == 0 && iny)
+				{
+					want = true;
+					v = a + 1u;
+					nd = MIN_EDGE + (S.w[a] & 0xFFFFu);
+				}
+				else if (rx == TS + 1 && iny)
+				{
+					want = true;
+					v = a - 1u;
+					nd = MIN_EDGE + (S.w[v] & 0xFFFFu);
+				}
+			}
+			relax_into(want, v, nd);
+		}
+		__syncwarp();
+		{
+			const int i = (int)lane;
+			S.d[0 * PITCH + 4 + i] = 0u;
+			S.d[brow * PITCH + 4 + i] = 0u;
+			S.d[(1 + i) * PITCH + 3] = 0u;
+			S.d[(1 + i) * PITCH + 4 + TS] = 0u;
+		}
+		__syncwarp();
+		for (int s0 = 0; s0 < P.nsrc; s0 += 32)
+		{
+			const int s = s0 + (int)lane;
+			bool want = false;
+			uint32_t c = (uint32_t)(PITCH + 4);
+			if (s < P.nsrc)
+			{
+				const uint32_t src = lsrc[s];
+				const int rx = (int)(src % (uint32_t)W) - gx0, ry = (int)(src / (uint32_t)W) - P.y0 - ly0;
+				want = rx >= 1 && rx <= TS && ry >= 1 && ry < brow;
+				if (want)
+				{
+					c = (uint32_t)(ry * PITCH + rx + 3);
+					src_sides |= (ry == 1 ? 4u : 0u) | (ry == TS ? 8u : 0u) | (rx == 1 ? 16u : 0u) | (rx == TS ? 32u : 0u);
+				}
+			}
+			relax_into(want, c - PITCH, MIN_EDGE + (S.w[c - PITCH] >> 16));
+			relax_into(want, c - 1u, MIN_EDGE + (S.w[c - 1u] & 0xFFFFu));
+			relax_into(want, c + 1u, MIN_EDGE + (S.w[c] & 0xFFFFu));
+			relax_into(want, c + PITCH, MIN_EDGE + (S.w[c] >> 16));
+		}
+		uint32_t dmin = warp_redux_min(my_min);
+		__syncwarp();
+
+		// ---- bucketed wavefront on the frame, warp-synchronous ----
+		uint32_t nq = tail, par = 0;
+		bool overflow = false;
+		while (nq != 0u && dmin != MTD_INF)
+		{
+			if (nq > (uint32_t)QCAP)
+			{
+				overflow = true;
+				break;
+			}
+			const uint32_t thr = dmin + BIG_DELTA;
+			const uint16_t *rq = S.q[par];
+			wq = S.q[par ^ 1u];
+			tail = 0;
+			uint32_t newmin = MTD_INF;
+			for (uint32_t base = 0; base < nq; base += 32u)
+			{
+				const uint32_t idx = base + lane;
+				const bool active = idx < nq;
+				const uint32_t c = active ? rq[idx] : (uint32_t)(PITCH + 4);
+				const uint32_t d = active ? S.d[c] : MTD_INF;
+				const bool settle = d < thr && d != 0u;
+				const bool keep = active && d >= thr;
+				uint32_t n0 = 0, n1 = 0, n2 = 0, n3 = 0;
+				bool i0 = false, i1 = false, i2 = false, i3 = false;
+				if (settle)
+				{
+					const uint32_t wc = S.w[c], base_nd = d + MIN_EDGE;
+					n0 = base_nd + (S.w[c - PITCH] >> 16);
+					n1 = base_nd + (S.w[c - 1u] & 0xFFFFu);
+					n2 = base_nd + (wc & 0xFFFFu);
+					n3 = base_nd + (wc >> 16);
+					if (base_nd >= BIG_SETTLE_LIMIT)
+						guard = true;
+					else
+					{
+						i0 = n0 < atomicMin(&S.d[c - PITCH], n0);
+						i1 = n1 < atomicMin(&S.d[c - 1u], n1);
+						i2 = n2 < atomicMin(&S.d[c + 1u], n2);
+						i3 = n3 < atomicMin(&S.d[c + PITCH], n3);
+					}
+				}
+				uint32_t lm = keep ? d : MTD_INF;
+				lm = i0 ? min(lm, n0) : lm;
+				lm = i1 ? min(lm, n1) : lm;
+				lm = i2 ? min(lm, n2) : lm;
+				lm = i3 ? min(lm, n3) : lm;
+				newmin = min(newmin, lm);
+				const uint32_t bk = __ballot_sync(0xFFFFFFFFu, keep);
+				const uint32_t b0 = __ballot_sync(0xFFFFFFFFu, i0);
+				const uint32_t b1 = __ballot_sync(0xFFFFFFFFu, i1);
+				const uint32_t b2 = __ballot_sync(0xFFFFFFFFu, i2);
+				const uint32_t b3 = __ballot_sync(0xFFFFFFFFu, i3);
+				uint32_t pos = tail;
+				uint32_t p = pos + __popc(bk & lt);
+				if (keep && p < (uint32_t)QCAP)
+					wq[p] = (uint16_t)c;
+				pos += __popc(bk);
+				p = pos + __popc(b0 & lt);
+				if (i0 && p < (uint32_t)QCAP)
+					wq[p] = (uint16_t)(c - PITCH);
+				pos += __popc(b0);
+				p = pos + __popc(b1 & lt);
+				if (i1 && p < (uint32_t)QCAP)
+					wq[p] = (uint16_t)(c - 1u);
+				pos += __popc(b1);
+				p = pos + __popc(b2 & lt);
+				if (i2 && p < (uint32_t)QCAP)
+					wq[p] = (uint16_t)(c + 1u);
+				pos += __popc(b2);
+				p = pos + __popc(b3 & lt);
+				if (i3 && p < (uint32_t)QCAP)
+					wq[p] = (uint16_t)(c + PITCH);
+				tail = pos + __popc(b3);
+			}
+			dmin = warp_redux_min(newmin);
+			nq = tail;
+			par ^= 1u;
+			__syncwarp();
+		}
+		if (overflow)
+		{
+			// the pending set outgrew the queue: queue-less sweeps to the local fixpoint (parked cells hold 0 and never expand)
+			for (;;)
+			{
+				bool changed = false;
+				for (int i = (int)lane; i < TS * TS; i += 32)
+				{
+					const uint32_t c = (uint32_t)((1 + i / TS) * PITCH + 4 + i % TS);
+					const uint32_t d = S.d[c];
+					if (d == 0u || d == MTD_INF)
+						continue;
+					const uint32_t base_nd = d + MIN_EDGE;
+					if (base_nd >= BIG_SETTLE_LIMIT)
+					{
+						guard = true;
+						continue;
+					}
+					const uint32_t wc = S.w[c];
+					const uint32_t n0 = base_nd + (S.w[c - PITCH] >> 16), n1 = base_nd + (S.w[c - 1u] & 0xFFFFu), n2 = base_nd + (wc & 0xFFFFu), n3 = base_nd + (wc >> 16);
+					changed |= n0 < atomicMin(&S.d[c - PITCH], n0);
+					changed |= n1 < atomicMin(&S.d[c - 1u], n1);
+					changed |= n2 < atomicMin(&S.d[c + 1u], n2);
+					changed |= n3 < atomicMin(&S.d[c + PITCH], n3);
+				}
+				__syncwarp();
+				if (!__any_sync(0xFFFFFFFFu, changed))
+					break;
+			}
+		}
+		__syncwarp();
+
+		// ---- write back the interior ----
+		if (interior)
+		{
+			for (int q = (int)lane; q < TS * 8; q += 32)
+			{
+				const int iy = q >> 3, ch = q & 7;
+				const uint4 v = *reinterpret_cast<const uint4 *>(S.d + (1 + iy) * PITCH + 4 + ch * 4);
+				__stcg(reinterpret_cast<uint4 *>(ldist + (size_t)(ly0 + 1 + iy) * W + gx0 + 1 + ch * 4), v);
+			}
+		}
+		else
+		{
+			for (int q = (int)lane; q < TS * TS; q += 32)
+			{
+				const int iy = q / TS, ix = q - iy * TS;
+				const int ly = ly0 + 1 + iy, gx = gx0 + 1 + ix;
+				if (ly < Hl && gx < W)
+					__stcg(ldist + (size_t)ly * W + gx, S.d[(1 + iy) * PITCH + 4 + ix]);
+			}
+		}
+
+		// ---- what do the border cells offer the neighbour tiles? ----
+		{
+			auto offer = [&](bool exists, uint32_t db, uint32_t w, uint32_t ap) -> uint32_t
+			{ return exists && db != 0u && db < BIG_SETTLE_LIMIT && db + MIN_EDGE + w < ap ? db + MIN_EDGE + w : MTD_INF; };
+			const int i = (int)lane;
+			const uint32_t ct = (uint32_t)(1 * PITCH + 4 + i), cb = (uint32_t)((brow - 1) * PITCH + 4 + i);
+			const uint32_t cl = (uint32_t)((1 + i) * PITCH + 4), cr = (uint32_t)((1 + i) * PITCH + 3 + TS);
+			const bool row_exists = 1 + i < brow;
+			k[0] = warp_redux_min(offer(true, S.d[ct], S.w[ct - PITCH] >> 16, ap_old[0]));
+			k[1] = warp_redux_min(offer(true, S.d[cb], S.w[cb] >> 16, ap_old[1]));
+			k[2] = warp_redux_min(offer(row_exists, S.d[cl], S.w[cl - 1u] & 0xFFFFu, ap_old[2]));
+			k[3] = warp_redux_min(offer(row_exists, S.d[cr], S.w[cr] & 0xFFFFu, ap_old[3]));
+			const uint32_t f = __reduce_or_sync(0xFFFFFFFFu, src_sides); // sources on a border line: the neighbour finds them in the list
+			if (f & 4u)
+				k[0] = 0u;
+			if (f & 8u)
+				k[1] = 0u;
+			if (f & 16u)
+				k[2] = 0u;
+			if (f & 32u)
+				k[3] = 0u;
+		}
+	}
+
+	struct AsyncSched
+	{
+		uint32_t pend_item[ASYNC_PCAP];
+		uint32_t pend_key[ASYNC_PCAP];
+		uint32_t slot[ASYNC_WORKERS];   // mailbox: SLOT_IDLE, SLOT_EXIT or the item to visit (written by the scheduler, reset by the worker)
+		uint32_t ifitem[ASYNC_WORKERS]; // what each worker was given last
+		uint32_t ifkey[ASYNC_WORKERS];  // the key it was given at
+	};
+
+	template<int TS>
+	constexpr size_t async_smem_bytes()
+	{
+		return sizeof(WarpFrame<TS>) * ASYNC_WORKERS + sizeof(AsyncSched);
+	}
+
+	// ONE launch per update; cooperative only so that all CTAs are resident together (there is no grid barrier inside).
+	template<int TS>
+	__global__ void __launch_bounds__((ASYNC_WORKERS + 1) * 32, 1) k_tile_async(const BigParams P, const AsyncParams A)
+	{
+		extern __shared__ __align__(16) unsigned char smem_raw[];
+		using WT = WarpFrame<TS>;
+		const int warp = threadIdx.x >> 5;
+		const uint32_t lane = lane_id();
+		const uint32_t lt = lanemask_lt();
+		AsyncSched &Q = *reinterpret_cast<AsyncSched *>(smem_raw + sizeof(WT) * ASYNC_WORKERS);
+		volatile uint32_t *slot = Q.slot;
+		const uint32_t ntiles = (uint32_t)(P.tilesX * P.tilesY);
+		if (threadIdx.x < ASYNC_WORKERS)
+		{
+			Q.slot[threadIdx.x] = SLOT_IDLE;
+			Q.ifitem[threadIdx.x] = MTD_INF;
+			Q.ifkey[threadIdx.x] = MTD_INF;
+		}
+		__syncthreads();
+
+		if (warp < ASYNC_WORKERS)
+		{
+			// ---------------- worker ----------------
+			WT &S = reinterpret_cast<WT *>(smem_raw)[warp];
+			bool guard = false;
+			uint32_t visits = 0;
+			for (;;)
+			{
+				uint32_t it = 0;
+				if (lane == 0)
+					while ((it = slot[warp]) == SLOT_IDLE)
+						__nanosleep(40);
+				it = __shfl_sync(0xFFFFFFFFu, it, 0);
+				if (it == SLOT_EXIT)
+					break;
+				const int layer = (int)(it / ntiles);
+				const uint32_t tile = it - (uint32_t)layer * ntiles;
+				const int tx = (int)(tile % (uint32_t)P.tilesX), ty = (int)(tile / (uint32_t)P.tilesX);
+				if (lane == 0)
+				{
+					atomicExch(P.key + it, MTD_INF); // consume the offers: whoever made one wrote its labels first
+					__threadfence();
+				}
+				__syncwarp();
+				uint32_t k[4];
+				warp_visit<TS>(P, S, layer, tx, ty, lane, lt, k, guard);
+				__threadfence(); // my labels are visible before a neighbour can be scheduled
+				__syncwarp();
+				if (lane == 0 && k[0] != MTD_INF)
+					async_offer(P, A, layer, tx, ty - 1, k[0]);
+				if (lane == 1 && k[1] != MTD_INF)
+					async_offer(P, A, layer, tx, ty + 1, k[1]);
+				if (lane == 2 && k[2] != MTD_INF)
+					async_offer(P, A, layer, tx - 1, ty, k[2]);
+				if (lane == 3 && k[3] != MTD_INF)
+					async_offer(P, A, layer, tx + 1, ty, k[3]);
+				__syncwarp();
+				visits++;
+				if (lane == 0)
+				{
+					__threadfence();
+					atomicSub(A.ctl + ACTL_OUTSTANDING, 1u); // after the increments of the offers above
+					slot[warp] = SLOT_IDLE;
+				}
+				__syncwarp();
+			}
+			if (lane == 0)
+			{
+				atomicAdd(A.ctl + ACTL_VISITS, visits);
+				atomicAdd(P.total_active, visits);
+				if (guard)
+					atomicOr(P.status, 1);
+			}
+			return;
+		}
+
+		// ---------------- scheduler warp ----------------
+		const int me = (int)blockIdx.x;
+		const uint32_t cap = A.cap_mask + 1u;
+		uint32_t *ring = A.inbox + (size_t)me * cap;
+		uint32_t head = 0, pn = 0, polls = 0;
+		const unsigned long long t0 = global_timer_ns();
+		bool stop = false;
+		while (!stop)
+		{
+			// everything the decision needs from global memory is requested up front: one L2 round trip per iteration
+			const uint32_t tail = __ldcg(A.tail + me * 32);
+			const uint32_t outstanding = __ldcg(A.ctl + ACTL_OUTSTANDING);
+			const uint32_t aborted = __ldcg(A.ctl + ACTL_ABORT);
+			uint32_t others = MTD_INF;
+			for (int c = (int)lane; c < A.ctas; c += 32)
+				if (c != me)
+					others = min(others, __ldcg(A.ctamin + c));
+			// drain the inbox: entries [head, tail) in order, up to the first one whose store has not landed yet
+			while (head != tail && pn < (uint32_t)ASYNC_PCAP)
+			{
+				const uint32_t n = min(min(tail - head, 32u), (uint32_t)ASYNC_PCAP - pn);
+				uint32_t v = 0;
+				if (lane < n)
+					v = __ldcg(ring + ((head + lane) & A.cap_mask));
+				const uint32_t missing = __ballot_sync(0xFFFFFFFFu, lane < n && v == 0u);
+				const uint32_t got = missing ? (uint32_t)(__ffs(missing) - 1) : n;
+				if (lane < got)
+				{
+					__stcg(ring + ((head + lane) & A.cap_mask), 0u);
+					Q.pend_item[pn + lane] = v - 1u;
+				}
+				head += got;
+				pn += got;
+				if (got < n)
+					break;
+			}
+			__syncwarp();
+			// pending keys as they stand now (offers only lower them)
+			uint32_t mymin = MTD_INF;
+			for (uint32_t i = lane; i < pn; i += 32)
+			{
+				const uint32_t kk = __ldcg(P.key + Q.pend_item[i]);
+				Q.pend_key[i] = kk;
+				mymin = min(mymin, kk);
+			}
+			// workers
+			uint32_t st = SLOT_EXIT;
+			if (lane < ASYNC_WORKERS)
+				st = slot[lane];
+			uint32_t idle = __ballot_sync(0xFFFFFFFFu, lane < ASYNC_WORKERS && st == SLOT_IDLE);
+			if (lane < ASYNC_WORKERS && st != SLOT_IDLE)
+				mymin = min(mymin, Q.ifkey[lane]);
+			const uint32_t cmin = warp_redux_min(mymin);
+			if (lane == 0)
+				__stcg(A.ctamin + me, cmin);
+			const uint32_t wm = min(cmin, warp_redux_min(others));
+			const uint32_t kthr = wm > MTD_INF - P.tile_delta ? MTD_INF : wm + P.tile_delta;
+			__syncwarp();
+			// hand the smallest eligible keys to idle workers
+			uint32_t skipped = 0; // pending entries found busy are hidden for this iteration by parking their cached key
+			while (idle != 0u && pn != 0u)
+			{
+				uint32_t bk = MTD_INF;
+				for (uint32_t i = lane; i < pn; i += 32)
+					bk = min(bk, Q.pend_key[i]);
+				const uint32_t kmin = warp_redux_min(bk);
+				if (kmin >= kthr) // also MTD_INF: nothing selectable
+					break;
+				uint32_t bi = MTD_INF;
+				for (uint32_t i = lane; i < pn; i += 32)
+					if (Q.pend_key[i] == kmin)
+						bi = min(bi, i);
+				bi = warp_redux_min(bi);
+				const uint32_t item = Q.pend_item[bi];
+				const bool busy = __any_sync(0xFFFFFFFFu, lane < ASYNC_WORKERS && !((idle >> lane) & 1u) && Q.ifitem[lane] == item);
+				__syncwarp();
+				if (busy)
+				{
+					// its tile is being visited right now: leave it pending, look at the next one
+					if (lane == 0)
+						Q.pend_key[bi] = MTD_INF;
+					skipped++;
+					__syncwarp();
+					continue;
+				}
+				const int w = __ffs(idle) - 1;
+				if (lane == 0)
+				{
+					Q.ifitem[w] = item;
+					Q.ifkey[w] = kmin;
+					Q.pend_item[bi] = Q.pend_item[pn - 1];
+					Q.pend_key[bi] = Q.pend_key[pn - 1];
+					__threadfence_block();
+					slot[w] = item;
+				}
+				pn--;
+				idle &= idle - 1u;
+				__syncwarp();
+			}
+			(void)skipped;
+			polls++;
+			if (aborted || outstanding == 0u)
+				stop = true;
+			else if (global_timer_ns() - t0 > A.time_limit_ns)
+			{
+				if (lane == 0)
+				{
+					atomicExch(A.ctl + ACTL_ABORT, 1u);
+					atomicOr(P.status, 16); // ST_ASYNC_TIMEOUT
+				}
+				stop = true;
+			}
+			else
+				__nanosleep(100);
+		}
+		// release the workers: a busy one finishes its visit first
+		for (;;)
+		{
+			uint32_t st = SLOT_EXIT;
+			if (lane < ASYNC_WORKERS)
+			{
+				st = slot[lane];
+				if (st == SLOT_IDLE)
+					slot[lane] = SLOT_EXIT;
+			}
+			if (!__any_sync(0xFFFFFFFFu, st != SLOT_EXIT && st != SLOT_IDLE))
+				break;
+			__nanosleep(200);
+		}
+		if (lane == 0)
+			atomicAdd(A.ctl + ACTL_IDLE_POLLS, polls);
+	}
+}

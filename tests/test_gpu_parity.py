@@ -21,6 +21,21 @@ def ctx():
     c.close()
 
 
+@pytest.fixture(params=["dataflow", "rounds"])
+def tctx(ctx, request):
+    """the tiled (large-grid) path under both schedulers: k_tile_async (default) and the round-based k_tile_rounds"""
+    ctx.debug_set(ctx.DEBUG_BIG_ASYNC, 1 if request.param == "dataflow" else 0)
+    yield ctx
+    ctx.debug_set(ctx.DEBUG_BIG_ASYNC, 1)
+
+
+GOLDEN_BIG = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "big_configs.npz")
+
+
+def _checks(a):
+    return int(np.bitwise_xor.reduce(a)), int(a.astype(np.uint64).sum() & np.uint64(0xFFFFFFFFFFFFFFFF))
+
+
 def diff_report(a, b, W):
     bad = np.flatnonzero(a != b)
     i = int(bad[0])
@@ -157,7 +172,8 @@ def test_every_single_building_toggle_on_one_map(ctx, oracle):
 # P1: tiled path for large grids
 # ---------------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("shape,pct", [((300, 260), 30), ((513, 257), 0), ((640, 384), 40), ((1024, 1024), 30)])
-def test_directions_tiled_bit_exact(ctx, oracle, shape, pct):
+def test_directions_tiled_bit_exact(tctx, oracle, shape, pct):
+    ctx = tctx
     W, H = shape
     elev, flags = synth.random_grid(W, H, seed_k=21, wall_pct=pct, elev_mod=512)
     src = int(synth.pick_open_tiles(flags, 1, 5)[0])
@@ -168,7 +184,8 @@ def test_directions_tiled_bit_exact(ctx, oracle, shape, pct):
     assert np.array_equal(tiles, to), diff_report(tiles, to, W)
 
 
-def test_directions_tiled_maze_and_multisource(ctx, oracle):
+def test_directions_tiled_maze_and_multisource(tctx, oracle):
+    ctx = tctx
     W, H = 290, 270
     elev, flags = synth.maze_grid(W, H, 7)
     ctx.grid_upload(W, H, elev, flags)
@@ -185,7 +202,8 @@ def test_directions_tiled_maze_and_multisource(ctx, oracle):
     assert np.array_equal(tiles, to)
 
 
-def test_directions_tiled_blocked_source_and_border_sources(ctx, oracle):
+def test_directions_tiled_blocked_source_and_border_sources(tctx, oracle):
+    ctx = tctx
     W, H = 300, 300
     elev, flags = synth.random_grid(W, H, seed_k=9, wall_pct=25, elev_mod=300)
     ctx.grid_upload(W, H, elev, flags)
@@ -197,6 +215,99 @@ def test_directions_tiled_blocked_source_and_border_sources(ctx, oracle):
         to, do = oracle.directions_update(W, H, elev, flags, s)
         assert np.array_equal(dist, do), (s, diff_report(dist, do, W))
         assert np.array_equal(tiles, to), s
+
+
+def test_dataflow_scheduler_really_runs_and_windows_agree(ctx, oracle):
+    """k_tile_async is the path taken by default (statistics say so), and its priority window changes nothing but time"""
+    W, H = 700, 520
+    elev, flags = synth.random_grid(W, H, seed_k=5, wall_pct=30, elev_mod=512)
+    srcs = synth.pick_open_tiles(flags, 3, 9)
+    to, do = oracle.directions_update(W, H, elev, flags, srcs)
+    ctx.grid_upload(W, H, elev, flags)
+    for delta in (1, 4096, 32768, 0xFFFFFFFF):
+        ctx.debug_set(ctx.DEBUG_ASYNC_DELTA, delta)
+        tiles, dist = ctx.directions_update(srcs)
+        st = ctx.big_stats()
+        assert st["dataflow"] and st["rounds"] == 0 and st["visits"] >= ((W + 31) // 32) * ((H + 31) // 32) // 2
+        assert np.array_equal(dist, do), (delta, diff_report(dist, do, W))
+        assert np.array_equal(tiles, to), delta
+    ctx.debug_set(ctx.DEBUG_ASYNC_DELTA, 32768)
+
+
+def test_c5_full_size_against_reference_golden_and_oracle(tctx, oracle):
+    """BASELINE config 5 at its own size (4096^2, 8 layers): every layer against the committed golden made from the
+    reference's compiled Directions::update (tests/golden/make_golden_big.py), and, array for array, against a CPU
+    Dijkstra run here (the compiled reference when it travelled, else the oracle restatement)"""
+    import oracle_lib
+    import torch
+
+    ctx = tctx
+    g = np.load(GOLDEN_BIG)
+    W = H = 4096
+    elev, flags = synth.random_grid(W, H, seed_k=1, wall_pct=30, elev_mod=512)
+    srcs = synth.pick_open_tiles(flags, 8, 1)
+    assert np.array_equal(srcs, g["C5_sources"])
+    ctx.grid_upload(W, H, elev, flags)
+    dt = torch.empty((8, W * H), dtype=torch.int32, device="cuda")
+    dd = torch.empty((8, W * H), dtype=torch.int32, device="cuda")
+    ctx.layers_update_dev(srcs, dt.data_ptr(), dd.data_ptr())
+    ctx.synchronize()
+    cpu = oracle_lib.Ref() if oracle_lib.Ref.available() else None
+    rows = [int(r) for r in g["C5_rows"]]
+    for l in range(8):
+        dist = dd[l].cpu().numpy().view(np.uint32)
+        tiles = dt[l].cpu().numpy().view(np.uint32)
+        assert _checks(dist) == (int(g["C5_dist_xor"][l]), int(g["C5_dist_sum"][l])), l
+        assert _checks(tiles) == (int(g["C5_tiles_xor"][l]), int(g["C5_tiles_sum"][l])), l
+        assert int((dist == M).sum()) == int(g["C5_unreachable"][l])
+        for j, r in enumerate(rows):
+            assert np.array_equal(dist[r * W:(r + 1) * W], g["C5_dist_rows"][l][j]) and np.array_equal(tiles[r * W:(r + 1) * W], g["C5_tiles_rows"][l][j])
+        if ctx.big_stats()["dataflow"] or l in (0, 6):  # all 8 layers array for array under the default scheduler
+            to, do = cpu.directions_update(W, H, elev, flags, int(srcs[l])) if cpu else oracle.directions_update(W, H, elev, flags, int(srcs[l]))
+            assert np.array_equal(dist, do), diff_report(dist, do, W)
+            assert np.array_equal(tiles, to), diff_report(tiles, to, W)
+
+
+def test_c4_full_size_against_reference_golden(ctx):
+    """BASELINE config 4 at its own size (16384^2, 16 sources, one layer) against the committed golden: distances = minimum
+    of 16 runs of the reference's compiled Directions::update, next hops = closed form of the heap order on them"""
+    import torch
+
+    g = np.load(GOLDEN_BIG)
+    if "C4_dist_sum" not in g:
+        pytest.skip("C4 golden not generated")
+    W = H = 16384
+    elev, flags = synth.random_grid(W, H, seed_k=1, wall_pct=30, elev_mod=512)
+    srcs = synth.pick_open_tiles(flags, 16, 1)
+    assert np.array_equal(srcs, g["C4_sources"])
+    ctx.grid_upload(W, H, elev, flags)
+    del elev, flags
+    dt = torch.empty(W * H, dtype=torch.int32, device="cuda")
+    dd = torch.empty(W * H, dtype=torch.int32, device="cuda")
+    ctx.directions_update_dev(srcs, dt.data_ptr(), dd.data_ptr())
+    ctx.synchronize()
+    assert ctx.big_stats()["dataflow"]
+    for name, t in (("dist", dd), ("tiles", dt)):
+        v = t.to(torch.int64) & 0xFFFFFFFF
+        s = 0
+        for part in torch.chunk(v, 16):  # 64-bit wrap-around sum without overflow surprises
+            s = (s + int(part.sum().item())) & 0xFFFFFFFFFFFFFFFF
+        x = t.view(-1)
+        xr = x[0:1].clone()
+        h = x
+        while h.numel() > 1:  # xor-reduce by halving
+            n = h.numel() // 2
+            rest = h[2 * n:]
+            h = torch.bitwise_xor(h[:n], h[n:2 * n])
+            if rest.numel():
+                h = torch.cat([h, rest])
+        del xr
+        assert (int(h.item()) & 0xFFFFFFFF) == int(g[f"C4_{name}_xor"]), name
+        assert s == int(g[f"C4_{name}_sum"]), name
+        for j, r in enumerate(int(r) for r in g["C4_rows"]):
+            assert np.array_equal(t[r * W:(r + 1) * W].cpu().numpy().view(np.uint32), g[f"C4_{name}_rows"][j]), (name, r)
+    assert int((dd == -1).sum().item()) == int(g["C4_unreachable"])
+    ctx.grid_upload(64, 64, np.zeros(4096, np.int16), np.zeros(4096, np.uint16))  # release the 2 GiB of derived data
 
 
 def test_tiled_properties_at_4096(ctx):
