@@ -260,6 +260,409 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+# --------------------------------------------------------------------------------------------------------
+# The other BASELINE.json configurations, measured in the same run and reported under "configs" (C2 stays `value`)
+# --------------------------------------------------------------------------------------------------------
+def hbm_peak():
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    if "hbm_gbs" in peaks:
+        return float(peaks["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+    return 6650.0, "fallback 6650 GB/s (of fallback)"
+
+
+def _golden_big():
+    import numpy as np
+
+    path = os.path.join(ROOT, "tests", "golden", "big_configs.npz")
+    return np.load(path) if os.path.exists(path) else None
+
+
+def _sum64(t):
+    """64-bit wrap-around sum of the uint32 bit patterns held by an int32 device tensor"""
+    import torch
+
+    s = 0
+    for part in torch.chunk(t.reshape(-1), 16):
+        s = (s + int((part.to(torch.int64) & 0xFFFFFFFF).sum().item())) & 0xFFFFFFFFFFFFFFFF
+    return s
+
+
+def _timed_reps(fn, reps, warm, stream, world, dev):
+    """device time per repetition (CUDA events on the launching stream, max over ranks)"""
+    import torch
+
+    def barrier():
+        if world > 1:
+            import torch.distributed as dist
+
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(warm):
+        fn()
+    ms = []
+    for _ in range(reps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        fn()
+        e1.record(stream)
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            import torch.distributed as dist
+
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms.append(float(t.item()))
+    return ms
+
+
+def _big_roofline(ctx, algo_bytes, update_ms, reps):
+    from mazetd_b200 import capi
+
+    peak, src = hbm_peak()
+    relax_ms, relax_n = ctx.profile_read(capi.Context.K_BIG_RELAX)
+    dir_ms, dir_n = ctx.profile_read(capi.Context.K_BIG_DIRECTIONS)
+    prep_ms, _ = ctx.profile_read(capi.Context.K_BIG_PREPARE)
+    st = ctx.big_stats()
+    achieved = algo_bytes / (update_ms * 1e-3) / 1e9
+    return {
+        "bound": "hbm", "kernel": "k_tile_async" if st["dataflow"] else "k_tile_rounds", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+        "traffic": None, "peak_source": src, "algorithmic_bytes_per_update": algo_bytes,
+        "note": "achieved = W*H*(4 + 8*layers) bytes of the WHOLE update / its device time (init + relaxation + next-hop pass), the conservative reading of SURVEY.md 8d",
+        "kernel_avg_ms": relax_ms / max(relax_n, 1), "kernel_share_of_update": (relax_ms / max(relax_n, 1)) / update_ms if update_ms > 0 else None,
+        "next_hop_pass_avg_ms": dir_ms / max(dir_n, 1), "init_avg_ms": prep_ms / max(reps, 1),
+        "tile_visits": st["visits"], "global_rounds": st["rounds"],
+    }
+
+
+def leg_c5(ctx, dev, stream, rank, world, args):
+    """C5: 8 Directions::update layers on one 4096^2 grid; layers dealt round-robin to the ranks, no collective"""
+    import numpy as np
+    import torch
+
+    from mazetd_b200 import shard, synth
+
+    Wb = Hb = 4096
+    L = 8
+    elev, flags = synth.random_grid_torch(Wb, Hb, seed_k=1, wall_pct=30, elev_mod=512, device=dev)
+    srcs = synth.pick_open_tiles_torch(flags, L, 1)
+    mine = shard.layer_assignment(rank, world, L)
+    ctx.grid_upload_dev(Wb, Hb, elev.data_ptr(), flags.data_ptr())
+    n = len(mine)
+    dt = torch.empty((max(n, 1), Wb * Hb), dtype=torch.int32, device=dev)
+    dd = torch.empty((max(n, 1), Wb * Hb), dtype=torch.int32, device=dev)
+
+    def run():
+        if n:
+            ctx.layers_update_dev(srcs[mine], dt.data_ptr(), dd.data_ptr())
+
+    ctx.profile_enable(True)
+    _timed_reps(run, 0, 2, stream, world, dev)
+    for k in (ctx.K_BIG_RELAX, ctx.K_BIG_DIRECTIONS, ctx.K_BIG_PREPARE):
+        ctx.profile_read(k)
+    reps = 5
+    ms = _timed_reps(run, reps, 0, stream, world, dev)
+    med = float(np.median(ms))
+    out = {
+        "workload": "C5: 8 waypoint layers (distance + direction) on one 4096x4096 grid, 30 % walls, weights 255..570", "grid": [Wb, Hb], "layers": L, "n_gpus": world,
+        "partition": "layers round-robin over the ranks, grid replicated, no collective" if world > 1 else "one GPU",
+        "ms": med, "ms_all": ms, "value": Wb * Hb * L / (med * 1e-3), "unit": "tile relaxations/s",
+        "roofline": _big_roofline(ctx, Wb * Hb * (4 * world + 8 * L), med, reps),
+    }
+    ctx.profile_enable(False)
+    g = _golden_big()
+    if g is not None and n:
+        ok = all(_sum64(dd[i]) == int(g["C5_dist_sum"][l]) and _sum64(dt[i]) == int(g["C5_tiles_sum"][l]) for i, l in enumerate(mine))
+        out["parity"] = "golden-ok" if ok else "GOLDEN-MISMATCH"
+    if rank == 0 and world == 1 and not args.no_e2e:
+        # e2e through the host ABI: grid H2D + 8 x mtd_directions_update with pinned host outputs
+        he = elev.cpu().numpy()
+        hf = flags.cpu().numpy().view(np.uint16)
+        ht = torch.empty((L, Wb * Hb), dtype=torch.int32, pin_memory=True)
+        hd = torch.empty((L, Wb * Hb), dtype=torch.int32, pin_memory=True)
+
+        def e2e():
+            ctx.grid_upload(Wb, Hb, he, hf)
+            for l in range(L):
+                ctx._ck(ctx.L.mtd_directions_update(ctx.h, C.c_void_p(srcs[l:l + 1].ctypes.data), 1, 0xFFFFFFFF, C.c_void_p(ht[l].data_ptr()), C.c_void_p(hd[l].data_ptr())))
+
+        e2e()
+        t0 = time.perf_counter()
+        e2e()
+        dt_s = time.perf_counter() - t0
+        out["e2e"] = {"value": Wb * Hb * L / dt_s, "unit": "tile relaxations/s", "ms": dt_s * 1e3, "h2d_bytes": int(he.nbytes + hf.nbytes), "d2h_bytes": int(ht.numel() * 4 * 2),
+                      "api": "mtd_grid_upload + 8 x mtd_directions_update (host buffers, pinned outputs)"}
+        if g is not None:
+            out["e2e"]["parity"] = "golden-ok" if all(_sum64(hd[l]) == int(g["C5_dist_sum"][l]) for l in range(L)) else "GOLDEN-MISMATCH"
+    if rank == 0 and world == 1 and not args.no_cpu:
+        out["cpu_baseline"] = cpu_c5(elev.cpu().numpy(), flags.cpu().numpy().view(np.uint16), srcs, Wb, Hb)
+    return out
+
+
+def cpu_c5(elev, flags, srcs, Wb, Hb):
+    from concurrent.futures import ThreadPoolExecutor
+
+    import numpy as np
+
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib
+
+    use_ref = oracle_lib.Ref.available()
+    if not use_ref:
+        oracle_lib.build_oracle()
+    eng = oracle_lib.Ref() if use_ref else oracle_lib.Oracle()
+    thr = min(len(srcs), host_cores())
+    one = (lambda s: eng.directions_update(Wb, Hb, elev, flags, int(s))) if use_ref else (lambda s: eng.directions_update(Wb, Hb, elev, flags, np.array([s], np.uint32)))
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(thr) as ex:
+        list(ex.map(one, srcs))
+    dt = time.perf_counter() - t0
+    return {"value": Wb * Hb * len(srcs) / dt, "unit": "tile relaxations/s", "ms": dt * 1e3, "cores": thr, "kind": "reference" if use_ref else "port", "cpu": cpu_model(),
+            "sample": f"the whole workload once: {len(srcs)} concurrent heap Dijkstras (Directions::update) on {thr} host threads"}
+
+
+def leg_c4(ctx, dev, stream, rank, world, args):
+    """C4: one 16384^2 grid, 16 sources, one layer. One GPU: the whole grid. N > 1: row stripes, peer-coupled."""
+    import numpy as np
+    import torch
+
+    from mazetd_b200 import shard, striped, synth
+
+    Wb = Hb = args.c4_size
+    nsrc = 16
+    elev, flags = synth.random_grid_torch(Wb, Hb, seed_k=1, wall_pct=30, elev_mod=512, device=dev)
+    srcs = synth.pick_open_tiles_torch(flags, nsrc, 1)
+    g = _golden_big() if Wb == 16384 else None
+    out = {"workload": f"C4: one {Wb}x{Hb} grid, 30 % walls, weights 255..570, 16 sources, one distance + direction layer", "grid": [Wb, Hb], "sources": nsrc, "n_gpus": world}
+    reps = 3
+    if world == 1:
+        ctx.grid_upload_dev(Wb, Hb, elev.data_ptr(), flags.data_ptr())
+        dt = torch.empty(Wb * Hb, dtype=torch.int32, device=dev)
+        dd = torch.empty(Wb * Hb, dtype=torch.int32, device=dev)
+        run = lambda: ctx.directions_update_dev(srcs, dt.data_ptr(), dd.data_ptr())  # noqa: E731
+        ctx.profile_enable(True)
+        _timed_reps(run, 0, 1, stream, world, dev)
+        for k in (ctx.K_BIG_RELAX, ctx.K_BIG_DIRECTIONS, ctx.K_BIG_PREPARE):
+            ctx.profile_read(k)
+        ms = _timed_reps(run, reps, 0, stream, world, dev)
+        med = float(np.median(ms))
+        out.update(partition="one GPU", ms=med, ms_all=ms, value=Wb * Hb / (med * 1e-3), unit="tile relaxations/s", roofline=_big_roofline(ctx, Wb * Hb * 12, med, reps))
+        ctx.profile_enable(False)
+        if g is not None:
+            out["parity"] = "golden-ok" if _sum64(dd) == int(g["C4_dist_sum"]) and _sum64(dt) == int(g["C4_tiles_sum"]) else "GOLDEN-MISMATCH"
+        if not args.no_e2e:
+            he = elev.cpu().numpy()
+            hf = flags.cpu().numpy().view(np.uint16)
+            ht = torch.empty(Wb * Hb, dtype=torch.int32, pin_memory=True)
+            hd = torch.empty(Wb * Hb, dtype=torch.int32, pin_memory=True)
+
+            def e2e():
+                ctx.grid_upload(Wb, Hb, he, hf)
+                ctx._ck(ctx.L.mtd_directions_update(ctx.h, C.c_void_p(srcs.ctypes.data), nsrc, 0xFFFFFFFF, C.c_void_p(ht.data_ptr()), C.c_void_p(hd.data_ptr())))
+
+            e2e()
+            t0 = time.perf_counter()
+            e2e()
+            dt_s = time.perf_counter() - t0
+            out["e2e"] = {"value": Wb * Hb / dt_s, "unit": "tile relaxations/s", "ms": dt_s * 1e3, "h2d_bytes": int(he.nbytes + hf.nbytes), "d2h_bytes": int(ht.numel() * 8),
+                          "api": "mtd_grid_upload + mtd_directions_update (host buffers, pinned outputs)"}
+            if g is not None:
+                out["e2e"]["parity"] = "golden-ok" if _sum64(hd) == int(g["C4_dist_sum"]) and _sum64(ht) == int(g["C4_tiles_sum"]) else "GOLDEN-MISMATCH"
+            del ht, hd
+        if not args.no_cpu:
+            out["cpu_baseline"] = cpu_c4_sample(elev, flags, Wb, Hb)
+        ctx.grid_upload(64, 64, np.zeros(4096, np.int16), np.zeros(4096, np.uint16))  # release the derived data of the big grid
+    else:
+        y0, y1 = shard.stripe_rows(rank, world, Hb)
+        ya, yb = shard.stripe_halo_rows(y0, y1, Hb)
+        e = elev.view(Hb, Wb)[ya:yb].contiguous()
+        f = flags.view(Hb, Wb)[ya:yb].contiguous()
+        del elev, flags
+        st = striped.GpuStripe(dev.index, Wb, Hb, y0, y1, e, f, srcs, stream=stream.cuda_stream)
+        striped.connect_peers(st, rank, world)
+        rounds = [0]
+
+        def run():
+            rounds[0] = striped.solve_peer(st)[2]
+
+        _timed_reps(run, 0, 1, stream, world, dev)
+        ms = _timed_reps(run, reps, 0, stream, world, dev)
+        med = float(np.median(ms))
+        peak, src = hbm_peak()
+        ach = Wb * Hb * 12 / (med * 1e-3) / 1e9
+        out.update(partition=f"{world} row stripes (cuts on 64-row tile boundaries), boundary rows and keys stored into the neighbour's memory by the relaxation kernel (CUDA IPC over NVLink)",
+                   ms=med, ms_all=ms, value=Wb * Hb / (med * 1e-3), unit="tile relaxations/s", global_rounds=int(rounds[0]),
+                   roofline={"bound": "hbm", "kernel": "k_tile_rounds (peer-coupled)", "achieved": ach, "peak": peak * world, "unit": "GB/s", "frac": ach / (peak * world), "traffic": None, "peak_source": src + f" x {world} GPUs"})
+        if g is not None:
+            import torch.distributed as dist
+
+            sums = torch.tensor([_sum64(st.dist) & 0x7FFFFFFFFFFFFFFF, _sum64(st.tiles) & 0x7FFFFFFFFFFFFFFF], dtype=torch.int64, device=dev)
+            parts = [torch.zeros_like(sums) for _ in range(world)]
+            dist.all_gather(parts, sums)
+            tot_d = sum(int(p[0].item()) for p in parts) & 0xFFFFFFFFFFFFFFFF
+            tot_t = sum(int(p[1].item()) for p in parts) & 0xFFFFFFFFFFFFFFFF
+            # per-rank sums were masked to 63 bits: compare modulo 2^63
+            ok = (tot_d & 0x7FFFFFFFFFFFFFFF) == (int(g["C4_dist_sum"]) & 0x7FFFFFFFFFFFFFFF) and (tot_t & 0x7FFFFFFFFFFFFFFF) == (int(g["C4_tiles_sum"]) & 0x7FFFFFFFFFFFFFFF)
+            out["parity"] = "golden-ok" if ok else "GOLDEN-MISMATCH"
+            out["peer_parity"] = "PEER-OK" if ok else "PEER-MISMATCH"
+        st.close()
+    return out
+
+
+def cpu_c4_sample(elev_t, flags_t, Wb, Hb):
+    """bounded CPU sample of C4: the top-left 4096 x 4096 block of the same grid (1/16 of the tiles) with one source,
+    i.e. C4's source density, one heap Dijkstra on one host thread (a Directions::update is single-threaded)"""
+    import numpy as np
+
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib
+    from mazetd_b200 import synth
+
+    S = min(4096, Wb)
+    e = elev_t.view(Hb, Wb)[:S, :S].contiguous().cpu().numpy().reshape(-1)
+    f = flags_t.view(Hb, Wb)[:S, :S].contiguous().cpu().numpy().view(np.uint16).reshape(-1)
+    src = int(synth.pick_open_tiles(f, 1, 1)[0])
+    use_ref = oracle_lib.Ref.available()
+    if not use_ref:
+        oracle_lib.build_oracle()
+    eng = oracle_lib.Ref() if use_ref else oracle_lib.Oracle()
+    t0 = time.perf_counter()
+    if use_ref:
+        eng.directions_update(S, S, e, f, src)
+    else:
+        eng.directions_update(S, S, e, f, np.array([src], np.uint32))
+    dt = time.perf_counter() - t0
+    return {"value": S * S / dt, "unit": "tile relaxations/s", "ms_sample": dt * 1e3, "ms_extrapolated_full_grid": dt * 1e3 * (Wb * Hb) / (S * S), "cores": 1, "kind": "reference" if use_ref else "port", "cpu": cpu_model(),
+            "sample": f"top-left {S}x{S} block of the grid (1/{(Wb * Hb) // (S * S)} of the tiles), one source, one Directions::update on one host thread"}
+
+
+def leg_c1_c3(ctx, args, cpu):
+    """C1: the default generated map, trial + flag delta + full rebuild after the scripted placement, through the host ABI.
+    C3: 10 000 place/remove events on it with 1 000 000 monsters ticking between events (bounded CPU sample beside it)."""
+    import numpy as np
+
+    from mazetd_b200 import game_events, synth
+
+    out = {}
+    s1, s2 = KAT_SEED
+    g = ctx.mapgen_batch(s1, s2, 0, 1, cap=4096)
+    elev, flags, wp = g["elev"][0], g["flags"][0], g["wp_tiles"][0]
+    sp = int(g["agg"][0][2])
+    path = g["fullpath"][0][sp][: int(g["fullpath_len"][0][sp])]
+    ctx.grid_upload(W, H, elev, flags, 50, 50)
+    ctx.waypoints_update_dev(wp)
+    on_path = np.zeros(T, bool)
+    on_path[path] = True
+    cand = int(np.flatnonzero(on_path & ((flags & game_events.UNBUILDABLE) == 0))[0])
+    lat = []
+    for _ in range(120):
+        t0 = time.perf_counter()
+        ctx.placing_blocks(cand)                                  # P5: the trial Dijkstra
+        ctx.grid_set_flags(cand, int(flags[cand]) | synth.FLAG_BUILDING)  # P6: flag delta
+        ctx.waypoints_update(wp, cap=4096)                        # P2: 4 layers + walks + aggregates, everything copied to the host
+        lat.append(time.perf_counter() - t0)
+        ctx.grid_set_flags(cand, int(flags[cand]))
+    med = float(np.median(lat[20:]))
+    res = []
+    for _ in range(120):
+        t0 = time.perf_counter()
+        ctx.waypoints_update_dev(wp)
+        ctx.synchronize()
+        res.append(time.perf_counter() - t0)
+    out["C1"] = {"workload": "C1: default generated map (seed k=0), scripted tower placement: trial + flag delta + Waypoints::update, 101x101, 4 layers", "metric": "us per placement", "value": med * 1e6, "unit": "us",
+                 "higher_is_better": False, "tile_relaxations_per_s": T * NWP / med, "e2e": {"value": med * 1e6, "unit": "us", "d2h_bytes": T * NWP * 8 + 4 * 4096 * NWP, "api": "mtd_placing_blocks + mtd_grid_set_flags + mtd_waypoints_update (host outputs), wall clock"},
+                 "resident_us": float(np.median(res[20:])) * 1e6, "candidate_tile": cand, "roofline": None, "roofline_note": "latency-bound by design (10 201 tiles in one SM's shared memory): reported as latency, SURVEY.md 8d"}
+    if cpu:
+        out["C1"]["cpu_baseline"] = cpu_c1(elev, flags, wp, cand)
+
+    nevents, nmon = args.c3_events, args.c3_monsters
+    ctx.grid_upload(W, H, elev, flags, 50, 50)
+    ctx.waypoints_update_dev(wp)
+    mon = game_events.initial_monsters(nmon, path, wp, ctx.waypoints_find, speed_range=(0.03, 0.06))
+    game = game_events.GpuGame(ctx, W, H, elev, flags, wp)
+    ctx.monsters_upload(mon)
+    l0 = ctx.launches
+    ctx.synchronize()
+    t0 = time.perf_counter()
+    stats = game_events.run_events(game, nevents)
+    _, alive = ctx.monsters_tick(nevents + 1)
+    wall = time.perf_counter() - t0
+    peak, src = hbm_peak()
+    ach = 28.0 * nmon * nevents / wall / 1e9
+    out["C3"] = {"workload": f"C3: {nevents} random tower place/remove events on the default map, {nmon} monsters steering along the flow field, one tick per event", "metric": "monster ticks/s", "value": nmon * nevents / wall, "unit": "monster ticks/s",
+                 "events_per_s": nevents / wall, "wall_s": wall, "rebuilds": stats["placed"] + stats["cleared"], "trials": stats["placed"] + stats["rejected_trial"], "stats": stats, "alive": int(alive), "gpu_launches": ctx.launches - l0,
+                 "roofline": {"bound": "hbm", "kernel": "k_monsters_tick", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": src,
+                              "note": "28 B per monster per tick (SURVEY.md 8d) over the WALL time of the whole script incl. rebuilds and trials (host-driven event loop)"},
+                 "e2e": {"value": nmon * nevents / wall, "unit": "monster ticks/s", "note": "the script itself is the host-facing path: every event is a synchronous C-ABI call sequence"}}
+    if cpu:
+        out["C3"]["cpu_baseline"] = cpu_c3(elev, flags, wp, path)
+    return out
+
+
+def cpu_c1(elev, flags, wp, cand):
+    import numpy as np
+
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib
+    from mazetd_b200 import synth
+
+    use_ref = oracle_lib.Ref.available()
+    if not use_ref:
+        oracle_lib.build_oracle()
+    eng = oracle_lib.Ref() if use_ref else oracle_lib.Oracle()
+    cores = host_cores()
+    f2 = flags.copy()
+    f2[cand] |= synth.FLAG_BUILDING
+    if use_ref:
+        eng.L.ref_set_task_threads(min(4, cores))
+    h = eng.map_create(W, H, elev, f2, wp, 50, 50) if use_ref else None
+    lat = []
+    for _ in range(60):
+        t0 = time.perf_counter()
+        if use_ref:
+            eng.directions_update(W, H, elev, f2, int(wp[0]), 50, 50)
+            eng.L.ref_waypoints_update(h)
+        else:
+            eng.directions_update(W, H, elev, f2, wp[:1], 50, 50)
+            eng.waypoints_update(W, H, elev, f2, wp, 50, 50)
+        lat.append(time.perf_counter() - t0)
+    if h:
+        eng.L.ref_map_destroy(h)
+    med = float(np.median(lat[5:]))
+    return {"value": med * 1e6, "unit": "us", "cores": min(4, cores) if use_ref else 1, "kind": "reference" if use_ref else "port", "cpu": cpu_model(), "sample": "median of 55 placements (trial Dijkstra + Waypoints::update on the live objects)"}
+
+
+def cpu_c3(elev, flags, wp, path, nevents=300, nmon=100000):
+    """bounded sample: the same script, fewer events and monsters, single host thread (the reference's ECS visitor and its
+    placement code run on the control thread)"""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib
+    from mazetd_b200 import game_events
+
+    oracle_lib.build_oracle()
+    orc = oracle_lib.Oracle()
+    w = orc.waypoints_update(W, H, elev, flags, wp, 50, 50)
+    view = orc.waypoints_view(W, H, elev, flags, wp, w["tiles"], w["dist"], 50, 50)
+    import numpy as np
+
+    find = lambda pos, bits: tuple(np.array(x, np.uint32) for x in zip(*[orc.find(view, int(p), int(b)) for p, b in zip(pos, bits)]))  # noqa: E731
+    mon = game_events.initial_monsters(2000, path, wp, find, speed_range=(0.03, 0.06))
+    reps = nmon // 2000
+    mon = {k: np.tile(v, reps) for k, v in mon.items()}
+    og = oracle_lib.OracleGame(orc, W, H, elev, flags, wp, mon)
+    t0 = time.perf_counter()
+    stats = game_events.run_events(og, nevents)
+    dt = time.perf_counter() - t0
+    n = len(mon["tile"])
+    return {"value": n * nevents / dt, "unit": "monster ticks/s", "events_per_s": nevents / dt, "cores": 1, "kind": "port", "cpu": cpu_model(),
+            "sample": f"{nevents} events x {n} monsters ({dt:.1f} s): oracle restatement of monsters.cpp:55-99 + Waypoints::update / trial per event, one thread; rebuilds {stats['placed'] + stats['cleared']}"}
+
+
 def workload_config(args, maps):
     return {
         "workload": f"C2: batch of {maps} procedurally generated {W}x{H} maps per GPU (seeds (s1+k, s2), k = rank*{maps}..), map gen + {NWP} distance/direction layers + full paths + aggregates",
@@ -440,6 +843,23 @@ def run_ours(args):
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = time_cpu_sample()
 
+    # ---- the other BASELINE.json configurations, same run (C2 above stays the headline `value`) ----
+    del d
+    torch.cuda.empty_cache()
+    configs = {}
+    if not args.no_configs:
+        for name, fn in (("C5", lambda: leg_c5(ctx, dev, stream, rank, world, args)), ("C4", lambda: leg_c4(ctx, dev, stream, rank, world, args))):
+            try:
+                configs[name] = fn()
+            except Exception as e:  # noqa: BLE001  (a failing leg must not take the headline line with it)
+                configs[name] = {"error": f"{type(e).__name__}: {e}"[:400]}
+            torch.cuda.empty_cache()
+        if world == 1:
+            try:
+                configs.update(leg_c1_c3(ctx, args, cpu=not args.no_cpu))
+            except Exception as e:  # noqa: BLE001
+                configs["C1_C3"] = {"error": f"{type(e).__name__}: {e}"[:400]}
+
     if rank == 0:
         line = {
             "metric": "tile relaxations/sec (map gen + Waypoints::update on batched 101x101 maps)",
@@ -461,6 +881,7 @@ def run_ours(args):
             "clocks": clocks,
             "e2e": e2e,
             "gpu_launches": launches,
+            "configs": configs,
         }
         print(json.dumps(line), flush=True)
     ctx.close()
@@ -478,6 +899,10 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the C1/C3/C4/C5 legs (C2 headline only)")
+    ap.add_argument("--c4-size", type=int, default=16384)
+    ap.add_argument("--c3-events", type=int, default=10000)
+    ap.add_argument("--c3-monsters", type=int, default=1000000)
     ap.add_argument("--workload", default="C2", choices=["C2", "C1", "C5"], help="reference arm only: CPU figures for the non-headline configurations")
     ap.add_argument("--size", type=int, default=4096, help="grid side of --workload C5")
     ap.add_argument("--gw", type=int, default=0, help="tuning probe: warps per layer in the one-CTA kernel (1, 2, 4)")

@@ -393,3 +393,24 @@ class Ref:
         out = np.zeros((n, 3), np.float32)
         self.L.ref_monsters_position(h, game_time, n, tileStart.ctypes.data, tileEnd.ctypes.data, timeStart.ctypes.data, timeEnd.ctypes.data, out.ctypes.data)
         return out
+
+
+class OracleGame:
+    """the four map operations of mazetd_b200.game_events over the CPU oracle (scripted place/remove workload, C3)"""
+    def __init__(self, oracle, W, H, elev, flags, wp, monsters):
+        self.o, self.W, self.H, self.elev, self.wp, self.a = oracle, W, H, elev, wp, monsters
+        self.flags = np.array(flags, np.uint16)
+        self.rebuild()
+
+    def trial_blocks(self, tile):
+        return bool(self.o.placing_blocks(self.W, self.H, self.elev, self.flags, self.wp, int(tile), self.a["tile"], self.a["alive"], 50, 50))
+
+    def set_flags(self, tile, value):
+        pass  # self.flags is the grid
+
+    def rebuild(self):
+        self.w = self.o.waypoints_update(self.W, self.H, self.elev, self.flags, self.wp, 50, 50)
+        self.view = self.o.waypoints_view(self.W, self.H, self.elev, self.flags, self.wp, self.w["tiles"], self.w["dist"], 50, 50)
+
+    def tick(self, t):
+        self.o.monsters_tick(self.view, t, self.a)

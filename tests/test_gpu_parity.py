@@ -897,24 +897,7 @@ def test_grid_from_elevations_ragged_size_and_ties(ctx, oracle):
 # C3 at reduced size: scripted tower place/remove events with monsters steering along the flow field, every piece of
 # state compared with the oracle after the script
 # ---------------------------------------------------------------------------------------------------
-class _OracleGame:
-    def __init__(self, oracle, W, H, elev, flags, wp, monsters):
-        self.o, self.W, self.H, self.elev, self.wp, self.a = oracle, W, H, elev, wp, monsters
-        self.flags = np.array(flags, np.uint16)
-        self.rebuild()
-
-    def trial_blocks(self, tile):
-        return bool(self.o.placing_blocks(self.W, self.H, self.elev, self.flags, self.wp, int(tile), self.a["tile"], self.a["alive"], 50, 50))
-
-    def set_flags(self, tile, value):
-        pass  # self.flags is the grid
-
-    def rebuild(self):
-        self.w = self.o.waypoints_update(self.W, self.H, self.elev, self.flags, self.wp, 50, 50)
-        self.view = self.o.waypoints_view(self.W, self.H, self.elev, self.flags, self.wp, self.w["tiles"], self.w["dist"], 50, 50)
-
-    def tick(self, t):
-        self.o.monsters_tick(self.view, t, self.a)
+from oracle_lib import OracleGame as _OracleGame  # noqa: E402  (tests/golden/make_golden.py imports it from here)
 
 
 def test_scripted_place_remove_events_with_monsters(ctx, oracle):
