@@ -80,12 +80,13 @@ enum
 	MTD_DEBUG_GROUP_WARPS = 2, /* warps cooperating on one distance layer in the one-CTA path: 1, 2 or 4 */
 	MTD_DEBUG_WALKER = 3,      /* who walks the full paths in the one-CTA path: 0 auto (walker warp when a CTA owns several maps), 1 workers, 2 walker warp */
 	MTD_DEBUG_BIG_ASYNC = 5,   /* large grids: 1 (default) = dataflow scheduler without global rounds (k_tile_async), 0 = round-based kernel (k_tile_rounds). Same result */
+	MTD_DEBUG_BIG_TMA = 7,     /* dataflow scheduler: 1 (default) = tile frames staged by 2-D bulk tensor copies (TMA), 0 = cp.async rows. Same result */
 	MTD_DEBUG_ASYNC_DELTA = 6, /* priority window (label units) of the dataflow scheduler. Performance only */
 	MTD_DEBUG_TILE_DELTA = 4   /* large grids: width (label units) of the window of tile offers visited per round; 2^32-1 = visit everything (no priority). Performance only: any value gives the same result */
 };
 int mtd_debug_set(mtd_ctx *ctx, int key, int64_t value);
 /* Statistics of the last large-grid (tiled) update: out4 = { global rounds (0 with the dataflow scheduler), tile visits,
- * scheduler polls, 1 if the dataflow scheduler ran }. Diagnostics for bench.py; no reference counterpart. */
+ * scheduler polls, bit 0: the dataflow scheduler ran, bit 1: frames were staged by TMA }. Diagnostics for bench.py; no reference counterpart. */
 int mtd_big_stats(mtd_ctx *ctx, uint32_t *out4);
 
 /* ---- Grid (replaces the data side of struct Grid, sources/grid.h:38-53) ------------------------ */

@@ -36,7 +36,8 @@ def build(force=False, verbose=False):
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     extra = os.environ.get("MTD_NVCC_EXTRA", "").split()  # developer probes only (e.g. -DMTD_TIMING)
-    cmd = [nvcc] + NVCC_FLAGS + extra + ["-o", LIB, os.path.join(CSRC, "capi.cu")]
+    tmp = LIB + ".tmp"  # the library appears atomically: a snapshot taken for the GPU box meanwhile ships the old or the new one
+    cmd = [nvcc] + NVCC_FLAGS + extra + ["-o", tmp, os.path.join(CSRC, "capi.cu")]
     r = subprocess.run(cmd, capture_output=True, text=True)
     log = os.path.join(HERE, "build.log")
     with open(log, "w") as f:
@@ -44,6 +45,7 @@ def build(force=False, verbose=False):
     if r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)
         raise RuntimeError("nvcc failed building libmazetd_b200.so")
+    os.replace(tmp, LIB)
     if verbose:
         print(r.stdout + r.stderr)
     return LIB

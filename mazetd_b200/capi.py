@@ -146,12 +146,13 @@ class Context:
     DEBUG_TILE_DELTA = 4
     DEBUG_BIG_ASYNC = 5
     DEBUG_ASYNC_DELTA = 6
+    DEBUG_BIG_TMA = 7
 
     def big_stats(self):
         """rounds, tile visits, scheduler polls, dataflow flag of the last tiled update"""
         out = (C.c_uint32 * 4)()
         self._ck(self.L.mtd_big_stats(self.h, out))
-        return dict(rounds=int(out[0]), visits=int(out[1]), polls=int(out[2]), dataflow=bool(out[3]))
+        return dict(rounds=int(out[0]), visits=int(out[1]), polls=int(out[2]), dataflow=bool(out[3] & 1), tma=bool(out[3] & 2))
 
     def debug_set(self, key, value):
         self._ck(self.L.mtd_debug_set(self.h, int(key), int(value)))

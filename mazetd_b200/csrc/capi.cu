@@ -123,7 +123,8 @@ struct mtd_ctx
 	bool big_async = true;         // large grids: k_tile_async (no global rounds); false = k_tile_rounds (A/B and multi-stripe contexts)
 	uint32_t async_delta = 32768;  // priority window of the dataflow scheduler (label units)
 	uint32_t last_visits = 0;
-	bool last_async = false;
+	bool last_async = false, last_tma = false;
+	bool big_tma = true;           // dataflow scheduler: stage frames with bulk tensor copies (TMA) when the width allows it
 	uint32_t tile_delta = 98304; // visit window of the tile-level priority (label units); swept 8k..inf on 4096^2 and 16384^2 (weights 255..570): flat optimum 64k..256k
 	// row stripe of a larger grid (multi-GPU, one rank per stripe): rows [sy0, sy1) of a W x sH grid are this context's grid
 	bool stripe = false;
@@ -281,6 +282,10 @@ namespace
 			return fail(ctx, MTD_ERR_CAPACITY, "a full path is longer than fullpath_cap (lengths are exact, tiles were truncated)");
 		if (st & ST_PEER_TIMEOUT)
 			return fail(ctx, MTD_ERR_STATE, "peer-coupled stripes: another rank did not reach a barrier in time (20 s to enter the run, 4 s per round: not launched, or died)");
+		if (st & ST_ASYNC_TIMEOUT)
+			return fail(ctx, MTD_ERR_CUDA, "the dataflow relaxation hit its time limit");
+		if (st & ST_MONSTER_STUCK)
+			return fail(ctx, MTD_ERR_STATE, "a monster stands on a tile outside the grid or cannot reach its next waypoint (the reference asserts on this, sources/game/monsters.cpp:80): its state was left untouched");
 		return MTD_OK;
 	}
 
@@ -478,6 +483,40 @@ namespace
 		return (nitems + (size_t)ctx->sms - 1) / (size_t)ctx->sms + 64 <= (size_t)ASYNC_PCAP;
 	}
 
+	// cuTensorMapEncodeTiled through the runtime's driver entry point lookup (no link-time dependency on libcuda)
+	typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+									  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+	EncodeTiledFn encode_tiled_fn()
+	{
+		static EncodeTiledFn fn = nullptr;
+		static std::once_flag once;
+		std::call_once(once, []()
+					   {
+						   void *p = nullptr;
+						   cudaDriverEntryPointQueryResult q;
+						   if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+							   fn = (EncodeTiledFn)p;
+						   else
+							   (void)cudaGetLastError();
+					   });
+		return fn;
+	}
+
+	// a tensor of uint32 [nz][ny][nx] (row pitch nx, plane pitch `plane` elements) read in boxes of 40 x 34 x 1 words
+	bool frame_tensor_map(CUtensorMap *tm, const void *base, int nx, int ny, int nz, size_t plane)
+	{
+		EncodeTiledFn enc = encode_tiled_fn();
+		if (!enc || nx % 4 != 0 || ((uintptr_t)base & 15u) != 0 || (plane % 4) != 0)
+			return false;
+		const cuuint64_t gdim[3] = { (cuuint64_t)nx, (cuuint64_t)ny, (cuuint64_t)nz };
+		const cuuint64_t gstride[2] = { (cuuint64_t)nx * 4u, (cuuint64_t)plane * 4u };
+		const cuuint32_t box[3] = { (cuuint32_t)(BIG_TS + 8), (cuuint32_t)(BIG_TS + 2), 1u };
+		const cuuint32_t estr[3] = { 1u, 1u, 1u };
+		const int rank = nz > 0 ? 3 : 2;
+		return enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, (cuuint32_t)rank, const_cast<void *>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+				   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+	}
+
 	int run_async(mtd_ctx *ctx, BigParams P, size_t nitems)
 	{
 		const size_t smem = async_smem_bytes<BIG_TS>();
@@ -509,9 +548,15 @@ namespace
 		A.ctas = ctas;
 		A.time_limit_ns = 20000000000ull; // an update that takes 20 s is reported, not waited for
 		P.tile_delta = ctx->async_delta;
+		// frames staged by TMA: one tensor map over the labels of all layers, one over the packed weights
+		alignas(64) CUtensorMap tm_dist, tm_w;
+		memset(&tm_dist, 0, sizeof(tm_dist));
+		memset(&tm_w, 0, sizeof(tm_w));
+		A.use_tma = ctx->big_tma && P.aligned16 && frame_tensor_map(&tm_dist, P.dist, P.W, P.y1 - P.y0, P.nlayers, P.layer_stride) && frame_tensor_map(&tm_w, P.wpack, P.W, P.y1 - P.y0, 0, 0) ? 1 : 0;
+		ctx->last_tma = A.use_tma != 0;
 		k_async_seed<BIG_TS><<<(P.nlayers * P.nsrc + 127) / 128, 128, 0, ctx->stream>>>(P, A);
 		LAUNCHED();
-		void *args[] = { (void *)&P, (void *)&A };
+		void *args[] = { (void *)&P, (void *)&A, (void *)&tm_dist, (void *)&tm_w };
 		{
 			ProfScope prof(ctx, MTD_K_BIG_RELAX);
 			CU(cudaLaunchCooperativeKernel((const void *)k_tile_async<BIG_TS>, dim3((unsigned)ctas), dim3((unsigned)threads), args, smem, ctx->stream));
@@ -545,13 +590,31 @@ namespace
 		CU(cudaMemsetAsync(ctx->counters.p, 0, 16 * 4, ctx->stream));
 		CU(cudaMemsetAsync(ctx->counters.p + 8, 0xFF, 3 * 4, ctx->stream)); // minkey[3] = m
 		uint8_t prev_blocked = 0;
+		// the trial grid of placingBuildingBlocksMonsters: one more blocked tile for the duration of this call, taken back on
+		// EVERY way out (an error must not leave the trial building in the mask)
+		struct RestoreBlocked
+		{
+			mtd_ctx *ctx;
+			uint32_t tile;
+			uint8_t prev;
+			bool armed;
+			~RestoreBlocked()
+			{
+				if (!armed)
+					return;
+				ctx->hflags->stage_blocked = prev;
+				cudaMemcpyAsync(ctx->blocked.p + tile, &ctx->hflags->stage_blocked, 1, cudaMemcpyHostToDevice, ctx->stream);
+				cudaStreamSynchronize(ctx->stream); // the staging word is reused by the next call
+			}
+		} restore{ ctx, extra_blocked, 0, false };
 		if (extra_blocked != MTD_M)
 		{
-			// the trial grid of placingBuildingBlocksMonsters: one more blocked tile for the duration of this call
 			CU(cudaMemcpyAsync(&prev_blocked, ctx->blocked.p + extra_blocked, 1, cudaMemcpyDeviceToHost, ctx->stream));
 			CU(cudaStreamSynchronize(ctx->stream));
 			ctx->hflags->stage_blocked = 1u;
 			CU(cudaMemcpyAsync(ctx->blocked.p + extra_blocked, &ctx->hflags->stage_blocked, 1, cudaMemcpyHostToDevice, ctx->stream));
+			restore.prev = prev_blocked;
+			restore.armed = true;
 		}
 		{
 			ProfScope prof(ctx, MTD_K_BIG_PREPARE);
@@ -634,13 +697,7 @@ namespace
 			}
 			LAUNCHED();
 		}
-		if (extra_blocked != MTD_M)
-		{
-			ctx->hflags->stage_blocked = prev_blocked;
-			CU(cudaMemcpyAsync(ctx->blocked.p + extra_blocked, &ctx->hflags->stage_blocked, 1, cudaMemcpyHostToDevice, ctx->stream));
-			CU(cudaStreamSynchronize(ctx->stream)); // the staging word is reused by the next call
-		}
-		return MTD_OK;
+		return MTD_OK; // `restore` takes the trial building out of the mask
 	}
 
 	// ---- row stripe of a larger grid (one rank per stripe) -------------------------------
@@ -798,6 +855,7 @@ namespace
 		M.dotflags = ctx->m_has_dot ? ctx->m_dot.p : nullptr;
 		M.damage = ctx->m_has_damage ? ctx->m_damage.p : nullptr;
 		M.alive = ctx->m_alive.p;
+		M.status = ctx->d_status.p;
 		return M;
 	}
 
@@ -807,12 +865,12 @@ namespace
 			return fail(ctx, MTD_ERR_STATE, "no grid uploaded (or the context holds a row stripe)");
 		if (n < 0 || n > MTD_MAX_WAYPOINTS)
 			return fail(ctx, MTD_ERR_ARG, "waypoint count %d outside [0, %d]", n, MTD_MAX_WAYPOINTS);
-		ctx->nlayers = n;
-		if (n == 0)
-			return MTD_OK; // paths.cpp:113-114
 		for (int i = 0; i < n; i++)
 			if (wp_tiles[i] >= ctx->T)
-				return fail(ctx, MTD_ERR_ARG, "waypoint tile %u outside the grid", wp_tiles[i]);
+				return fail(ctx, MTD_ERR_ARG, "waypoint tile %u outside the grid", wp_tiles[i]); // a rejected call leaves the resident layers as they were
+		ctx->nlayers = 0; // from here on the resident layers are being rewritten: they count again once the launches went through
+		if (n == 0)
+			return MTD_OK; // paths.cpp:113-114
 		CU(ctx->ltiles.reserve((size_t)n * ctx->T));
 		CU(ctx->ldist.reserve((size_t)n * ctx->T));
 		CU(ctx->lwp.reserve(64));
@@ -861,6 +919,7 @@ namespace
 			if (rc)
 				return rc;
 		}
+		ctx->nlayers = n;
 		if (walks)
 		{
 			k_build_dtab<<<1, 64, 0, ctx->stream>>>(layers_view(ctx), ctx->dtab.p);
@@ -1052,6 +1111,9 @@ extern "C" int mtd_debug_set(mtd_ctx *ctx, int key, int64_t value)
 	case MTD_DEBUG_BIG_ASYNC:
 		ctx->big_async = value != 0;
 		return MTD_OK;
+	case MTD_DEBUG_BIG_TMA:
+		ctx->big_tma = value != 0;
+		return MTD_OK;
 	case MTD_DEBUG_ASYNC_DELTA:
 		if (value < 1 || value > 0xFFFFFFFFll)
 			return fail(ctx, MTD_ERR_ARG, "async delta must be in 1 .. 2^32-1");
@@ -1070,7 +1132,7 @@ extern "C" int mtd_big_stats(mtd_ctx *ctx, uint32_t *out4)
 	out4[0] = ctx->last_rounds;
 	out4[1] = ctx->last_async ? ctx->last_visits : ctx->hflags->big_items;
 	out4[2] = ctx->last_async ? ctx->hflags->async_ctl[ACTL_IDLE_POLLS] : 0u;
-	out4[3] = ctx->last_async ? 1u : 0u;
+	out4[3] = ctx->last_async ? (ctx->last_tma ? 3u : 1u) : 0u;
 	return MTD_OK;
 }
 
@@ -2224,12 +2286,12 @@ extern "C" int mtd_monsters_tick(mtd_ctx *ctx, uint32_t gameTime, int64_t *damag
 		return rc;
 	CU(cudaMemcpyAsync(&ctx->hflags->damage, ctx->d_damage.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
 	CU(cudaMemcpyAsync(&ctx->hflags->alive, ctx->d_small.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
-	CU(cudaStreamSynchronize(ctx->stream));
+	rc = sync_and_status(ctx); // ST_MONSTER_STUCK and friends
 	if (damage_out)
 		*damage_out = (int64_t)ctx->hflags->damage;
 	if (alive_out)
 		*alive_out = ctx->hflags->alive;
-	return MTD_OK;
+	return rc;
 }
 
 // ---- damage-over-time tick ----

@@ -29,6 +29,7 @@ namespace mtd
 		const uint8_t *dotflags;
 		const uint32_t *damage;
 		uint8_t *alive;
+		int *status; // ST_MONSTER_STUCK is raised here
 	};
 
 	__global__ void k_build_dtab(LayersView L, uint32_t *Dtab)
@@ -74,6 +75,12 @@ namespace mtd
 			{
 				const uint32_t tile = M.tile[i];
 				uint32_t bits = M.bits[i];
+				if (tile >= (uint32_t)(L.W * L.H))
+				{
+					// not a tile of this grid (the reference would read out of bounds): leave the monster alone and report
+					atomicOr(M.status, 32); // ST_MONSTER_STUCK
+					goto count;
+				}
 				for (int k = 0; k < L.n; k++) // :67-69
 					if (L.wp[k] == tile)
 						bits |= 1u << k;
@@ -89,6 +96,13 @@ namespace mtd
 				{
 					uint32_t go_tile, go_dist;
 					device_find(L, tile, bits, go_tile, go_dist); // :79
+					if (go_tile >= (uint32_t)(L.W * L.H) || go_dist == 0u)
+					{
+						// CAGE_ASSERT(go.tile != m) / a division by zero in the reference (:80, :88): reachable through the
+						// ABI (arbitrary uploaded tiles, a tile blocked by mtd_grid_set_flags): state untouched, reported
+						atomicOr(M.status, 32); // ST_MONSTER_STUCK
+						goto count;
+					}
 					M.tileStart[i] = tile;                          // :82-84
 					M.tileEnd[i] = go_tile;
 					M.tile[i] = go_tile;
@@ -96,7 +110,7 @@ namespace mtd
 					const uint32_t tta = M.timeToArrive[i];
 					if (tta > gameTime) // :85-89 (uint64 arithmetic through distNext)
 					{
-						const unsigned long long distNext = go_tile < (uint32_t)(L.W * L.H) ? edge_weight(L.elev[tile], L.elev[go_tile]) : 0u; // m is asserted away in the reference (:80)
+						const unsigned long long distNext = edge_weight(L.elev[tile], L.elev[go_tile]);
 						timeEnd = (uint32_t)((unsigned long long)gameTime + (unsigned long long)(tta - gameTime) * distNext / (unsigned long long)go_dist);
 					}
 					timeEnd = max(timeEnd, gameTime + 1u); // :90
@@ -111,6 +125,7 @@ namespace mtd
 				}
 			}
 		}
+	count:
 		const uint32_t bal = __ballot_sync(FULL_MASK, alive);
 		if (lane_id() == 0 && bal)
 			atomicAdd(alive_count, (uint32_t)__popc(bal));

@@ -20,6 +20,8 @@
 // smallest key anywhere) is what keeps warps from running ahead of the wavefront and multiplying revisits.
 #pragma once
 
+#include <cuda.h> // CUtensorMap (the driver entry point that encodes it is looked up at run time, nothing links libcuda)
+
 #include "common.cuh"
 #include "sssp_warp.cuh"
 // included after big_grid.cuh and tile_warp.cuh: BigParams, WarpFrame, cp_async_*, warp_redux_min, global_timer_ns
@@ -38,6 +40,41 @@ namespace mtd
 	constexpr int ACTL_IDLE_POLLS = 3;
 	constexpr int ACTL_WORDS = 32;
 
+	// A worker's frame: the WarpFrame layout (34 rows of 40 words, grid column gx0 + rx at word rx + 3) with both arrays on
+	// 128-byte boundaries, so that ONE 2-D TMA box of 40 x 34 words per array (origin tile_x0 - 4, tile_y0 - 1) lands exactly
+	// on it; cells outside the grid are zero-filled by the TMA unit, which is the "parked" label the engine expects.
+	template<int TS>
+	struct alignas(128) AsyncFrame
+	{
+		static constexpr int RW = TS + 2;
+		static constexpr int PITCH = TS + 8;
+		static constexpr int CELLS = RW * PITCH;
+		static constexpr int QCAP = 512;
+		uint32_t d[CELLS];
+		uint64_t bar; // mbarrier the two bulk tensor loads of a visit complete on
+		alignas(128) uint32_t w[CELLS];
+		uint16_t q[2][QCAP];
+	};
+
+	// generic-proxy accesses (the atomics on the tile keys, stores of other SMs made visible by them, the previous visit's use
+	// of the frame) are ordered before the bulk tensor copies that follow (async proxy), in global and in shared memory
+	__device__ __forceinline__ void fence_proxy_async_all()
+	{
+		asm volatile("fence.proxy.async;" ::: "memory");
+	}
+
+	__device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *tm, int x, int y, int z, uint64_t *bar)
+	{
+		asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(smem_u32(dst)), "l"(tm), "r"(x), "r"(y), "r"(z), "r"(smem_u32(bar))
+					 : "memory");
+	}
+
+	__device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *tm, int x, int y, uint64_t *bar)
+	{
+		asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(smem_u32(dst)), "l"(tm), "r"(x), "r"(y), "r"(smem_u32(bar))
+					 : "memory");
+	}
+
 	struct AsyncParams
 	{
 		uint32_t *inbox;     // [ctas][cap] item + 1, 0 = empty
@@ -46,6 +83,7 @@ namespace mtd
 		uint32_t *ctl;       // ACTL_* words
 		uint32_t cap_mask;   // cap - 1 (cap is a power of two >= items per owner)
 		int ctas;
+		int use_tma;         // frames are staged by two bulk tensor copies (needs W % 4 == 0); else by cp.async rows / scalar loads
 		unsigned long long time_limit_ns;
 	};
 
@@ -92,10 +130,9 @@ namespace mtd
 	// and the sources, run the warp-synchronous bucketed wavefront to local convergence, write the interior back.
 	// Returns in k[4] (warp-uniform) the smallest label on offer to the tile above / below / left / right (MTD_INF: none).
 	// Same arithmetic as the visit inside k_tile_rounds; `guard` is raised when a label gets close to the uint32 wrap.
-	template<int TS>
-	__device__ __forceinline__ void warp_visit(const BigParams &P, WarpFrame<TS> &S, int layer, int tx, int ty, uint32_t lane, uint32_t lt, uint32_t (&k)[4], bool &guard)
+	template<int TS, class WT>
+	__device__ __forceinline__ void warp_visit(const BigParams &P, WT &S, int layer, int tx, int ty, uint32_t lane, uint32_t lt, uint32_t (&k)[4], bool &guard, const CUtensorMap *tm_dist, const CUtensorMap *tm_w, uint32_t &tma_phase)
 	{
-		using WT = WarpFrame<TS>;
 		constexpr int RW = WT::RW, PITCH = WT::PITCH, QCAP = WT::QCAP;
 		const int W = P.W;
 		const int Hl = P.y1 - P.y0;
@@ -104,10 +141,28 @@ namespace mtd
 		uint32_t *ldist = P.dist + (size_t)layer * P.layer_stride;
 		const uint32_t *lsrc = P.sources + (size_t)layer * P.nsrc;
 		const int brow = min(TS + 1, Hl - ly0); // frame row just below the tile's last existing row
+		const bool use_tma = tm_dist != nullptr;
+		// the whole frame lies inside the grid and rows move as 16-byte vectors (staging without TMA); the write-back needs
+		// only the tile itself inside
 		const bool interior = P.aligned16 && ly0 >= 0 && ly0 + RW <= Hl && gx0 >= 0 && gx0 + RW <= W;
+		const bool interior_wb = P.aligned16 && ly0 + 1 + TS <= Hl && gx0 + 1 + TS <= W;
 
 		// ---- stage ----
-		if (interior)
+		if (use_tma)
+		{
+			// two boxes of 40 x 34 words (labels of this layer, packed weights), origin (tile_x0 - 4, tile_y0 - 1); what lies
+			// outside the grid arrives as 0 = parked
+			if (lane == 0)
+			{
+				fence_proxy_async_all();
+				mbar_expect_tx(&S.bar, 2u * (uint32_t)(RW * PITCH * 4));
+				tma_load_3d(S.d, tm_dist, tx * TS - 4, ly0, layer, &S.bar);
+				tma_load_2d(S.w, tm_w, tx * TS - 4, ly0, &S.bar);
+			}
+			mbar_wait(&S.bar, tma_phase);
+			tma_phase ^= 1u;
+		}
+		else if (interior)
 		{
 			constexpr int APN = (RW * 4 + 31) / 32;
 			uint32_t apv[APN];
@@ -408,7 +463,7 @@ namespace mtd
 		__syncwarp();
 
 		// ---- write back the interior ----
-		if (interior)
+		if (interior_wb)
 		{
 			for (int q = (int)lane; q < TS * 8; q += 32)
 			{
@@ -464,15 +519,15 @@ namespace mtd
 	template<int TS>
 	constexpr size_t async_smem_bytes()
 	{
-		return sizeof(WarpFrame<TS>) * ASYNC_WORKERS + sizeof(AsyncSched);
+		return sizeof(AsyncFrame<TS>) * ASYNC_WORKERS + sizeof(AsyncSched);
 	}
 
 	// ONE launch per update; cooperative only so that all CTAs are resident together (there is no grid barrier inside).
 	template<int TS>
-	__global__ void __launch_bounds__((ASYNC_WORKERS + 1) * 32, 1) k_tile_async(const BigParams P, const AsyncParams A)
+	__global__ void __launch_bounds__((ASYNC_WORKERS + 1) * 32, 1) k_tile_async(const BigParams P, const AsyncParams A, const __grid_constant__ CUtensorMap tm_dist, const __grid_constant__ CUtensorMap tm_w)
 	{
-		extern __shared__ __align__(16) unsigned char smem_raw[];
-		using WT = WarpFrame<TS>;
+		extern __shared__ __align__(128) unsigned char smem_raw[];
+		using WT = AsyncFrame<TS>;
 		const int warp = threadIdx.x >> 5;
 		const uint32_t lane = lane_id();
 		const uint32_t lt = lanemask_lt();
@@ -492,7 +547,13 @@ namespace mtd
 			// ---------------- worker ----------------
 			WT &S = reinterpret_cast<WT *>(smem_raw)[warp];
 			bool guard = false;
-			uint32_t visits = 0;
+			uint32_t visits = 0, tma_phase = 0;
+			if (lane == 0)
+			{
+				mbar_init(&S.bar, 1u);
+				asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+			}
+			__syncwarp();
 			for (;;)
 			{
 				uint32_t it = 0;
@@ -512,7 +573,7 @@ namespace mtd
 				}
 				__syncwarp();
 				uint32_t k[4];
-				warp_visit<TS>(P, S, layer, tx, ty, lane, lt, k, guard);
+				warp_visit<TS>(P, S, layer, tx, ty, lane, lt, k, guard, A.use_tma ? &tm_dist : nullptr, A.use_tma ? &tm_w : nullptr, tma_phase);
 				__threadfence(); // my labels are visible before a neighbour can be scheduled
 				__syncwarp();
 				if (lane == 0 && k[0] != MTD_INF)

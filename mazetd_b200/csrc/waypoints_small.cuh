@@ -29,6 +29,8 @@ namespace mtd
 		ST_NO_VALID = 2,   // generated map has no valid tile (reference would spin forever in findSpawnPoint)
 		ST_PATH_TRUNC = 4, // a full path exceeded fullpath_cap (length is still exact)
 		ST_PEER_TIMEOUT = 8, // peer-coupled stripes: the other ranks did not reach a round barrier
+		ST_ASYNC_TIMEOUT = 16, // the dataflow relaxation hit its time limit
+		ST_MONSTER_STUCK = 32, // a monster stands on a tile outside the grid or cannot reach its next waypoint: its state was left untouched
 	};
 
 	constexpr int SMALL_THREADS = 512;

@@ -15,18 +15,20 @@ for (W, H, nsrc, wall) in [(96, 70, 1, 30), (300, 260, 3, 30), (700, 500, 5, 30)
     srcs = synth.pick_open_tiles(flags, nsrc, 2)
     to, do = orc.directions_update(W, H, elev, flags, srcs)
     ctx.grid_upload(W, H, elev, flags)
-    for mode in (1, 0):
-        ctx.debug_set(ctx.DEBUG_BIG_ASYNC, mode)
+    for mode in (3, 1, 0):
+        ctx.debug_set(ctx.DEBUG_BIG_ASYNC, 1 if mode else 0)
+        ctx.debug_set(ctx.DEBUG_BIG_TMA, 1 if mode == 3 else 0)
         t, d = ctx.directions_update(srcs)
         st = ctx.big_stats()
         e = np.array_equal(d, do) and np.array_equal(t, to)
         ok &= e
-        print(W, H, nsrc, "async" if mode else "rounds", "OK" if e else "MISMATCH %d" % int((d != do).sum()), st, flush=True)
+        print(W, H, nsrc, {3: "async+tma", 1: "async", 0: "rounds"}[mode], "OK" if e else "MISMATCH %d" % int((d != do).sum()), st, flush=True)
 elev, flags = synth.maze_grid(200, 160, 3)
 srcs = synth.pick_open_tiles(flags, 1, 2)
 to, do = orc.directions_update(200, 160, elev, flags, srcs)
 ctx.grid_upload(200, 160, elev, flags)
 ctx.debug_set(ctx.DEBUG_BIG_ASYNC, 1)
+ctx.debug_set(ctx.DEBUG_BIG_TMA, 1)
 t, d = ctx.directions_update(srcs)
 print("maze", "OK" if np.array_equal(d, do) and np.array_equal(t, to) else "MISMATCH", ctx.big_stats(), flush=True)
 print("PARITY", "GREEN" if ok else "RED", flush=True)
@@ -42,7 +44,8 @@ def timing(size, nsrc, layers, modes):
     dd = torch.empty((n, W * H), dtype=torch.int32, device='cuda')
     ref = None
     for (mode, delta) in modes:
-        ctx.debug_set(ctx.DEBUG_BIG_ASYNC, mode)
+        ctx.debug_set(ctx.DEBUG_BIG_ASYNC, 1 if mode else 0)
+        ctx.debug_set(ctx.DEBUG_BIG_TMA, 1 if mode == 3 else 0)
         if mode:
             ctx.debug_set(ctx.DEBUG_ASYNC_DELTA, delta)
         else:
@@ -59,9 +62,9 @@ def timing(size, nsrc, layers, modes):
         cs = int((dd.to(torch.int64) & 0xFFFFFFFF).sum().item()), int((dt.to(torch.int64) & 0xFFFFFFFF).sum().item())
         if ref is None:
             ref = cs
-        print(json.dumps(dict(size=size, nsrc=nsrc, layers=layers, mode="async" if mode else "rounds", delta=delta, relax_ms=round(relax, 3), dir_ms=round(dirs, 3), prep_ms=round(prep, 3), same=cs == ref, **ctx.big_stats())), flush=True)
+        print(json.dumps(dict(size=size, nsrc=nsrc, layers=layers, mode={3: "async+tma", 1: "async", 0: "rounds"}[mode], delta=delta, relax_ms=round(relax, 3), dir_ms=round(dirs, 3), prep_ms=round(prep, 3), same=cs == ref, **ctx.big_stats())), flush=True)
 
 quick = len(sys.argv) > 1 and sys.argv[1] == "quick"
-timing(4096, 1, 8, [(0, 98304), (1, 32768), (1, 16384), (1, 65536), (1, 8192)])
+timing(4096, 1, 8, [(0, 98304), (1, 32768), (3, 32768), (3, 16384), (3, 65536), (3, 8192)])
 if not quick:
-    timing(16384, 16, 0, [(0, 98304), (1, 32768), (1, 16384), (1, 65536), (1, 131072)])
+    timing(16384, 16, 0, [(0, 98304), (1, 32768), (3, 32768), (3, 16384), (3, 65536), (3, 131072)])
