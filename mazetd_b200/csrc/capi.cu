@@ -567,6 +567,20 @@ namespace
 		if (ctx->hflags->async_ctl[ACTL_ABORT] != 0 || ctx->hflags->async_ctl[ACTL_OUTSTANDING] != 0)
 			return fail(ctx, MTD_ERR_CUDA, "dataflow relaxation stopped with %u items outstanding (time limit)", ctx->hflags->async_ctl[ACTL_OUTSTANDING]);
 		ctx->last_visits = ctx->hflags->async_ctl[ACTL_VISITS];
+#ifdef MTD_TIMING
+		{
+			unsigned long long t[16], z[16] = { 0 };
+			cudaMemcpyFromSymbol(t, g_async_timing, sizeof(t));
+			cudaMemcpyToSymbol(g_async_timing, z, sizeof(z));
+			const double v = (double)ctx->last_visits;
+			double tot = 0;
+			for (int q = 0; q < 7; q++)
+				tot += (double)t[q];
+			printf("ASYNCTIMING visits=%.0f | worker cycles per visit: wait=%.0f consume=%.0f stage=%.0f seed=%.0f engine=%.0f writeback=%.0f offers+finish=%.0f | idle share %.2f | steps/visit=%.1f cells/step=%.1f cycles/step=%.0f\n", v, t[0] / v, t[1] / v, t[2] / v,
+				   t[3] / v, t[4] / v, t[5] / v, t[6] / v, tot > 0 ? t[0] / tot : 0.0, t[7] / v, t[7] ? (double)t[8] / t[7] : 0.0, t[7] ? (double)t[4] / t[7] : 0.0);
+			fflush(stdout);
+		}
+#endif
 		return MTD_OK;
 	}
 

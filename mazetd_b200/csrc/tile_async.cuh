@@ -75,6 +75,36 @@ namespace mtd
 					 : "memory");
 	}
 
+#ifdef MTD_TIMING
+	// developer probe (never in the shipped build): cycles per phase summed over all workers
+	// 0 wait for work, 1 consume key, 2 stage, 3 seed, 4 engine, 5 write back + offers computed, 6 offers sent + finish, 7 engine steps, 8 cells popped
+	__device__ unsigned long long g_async_timing[16];
+#define MTD_ATICK(k)                                     \
+	do                                                   \
+	{                                                    \
+		const long long now__ = clock64();               \
+		tacc[k] += (unsigned long long)(now__ - last__); \
+		last__ = now__;                                  \
+	} while (0)
+#define MTD_ATIMING_ARGS , unsigned long long *tacc, long long &last__
+#define MTD_ATIMING_PASS , tacc, last__
+#else
+#define MTD_ATICK(k)
+#define MTD_ATIMING_ARGS
+#define MTD_ATIMING_PASS
+#endif
+
+	// hint: bring the frame of the item this worker visits next into L2 while it is busy with the current one
+	__device__ __forceinline__ void tma_prefetch_3d(const CUtensorMap *tm, int x, int y, int z)
+	{
+		asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];" ::"l"(tm), "r"(x), "r"(y), "r"(z) : "memory");
+	}
+
+	__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap *tm, int x, int y)
+	{
+		asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(tm), "r"(x), "r"(y) : "memory");
+	}
+
 	struct AsyncParams
 	{
 		uint32_t *inbox;     // [ctas][cap] item + 1, 0 = empty
@@ -92,21 +122,20 @@ namespace mtd
 		return (int)(((uint32_t)tx + (uint32_t)ASYNC_KX * (uint32_t)ty + (uint32_t)ASYNC_KL * (uint32_t)layer) % (uint32_t)A.ctas);
 	}
 
-	// offer label `key` to item (layer, tx, ty); the caller has made its labels visible (__threadfence) before
-	__device__ __forceinline__ void async_offer(const BigParams &P, const AsyncParams &A, int layer, int tx, int ty, uint32_t key)
+	// Offer label `key` to item (layer, tx, ty); the caller has made its labels visible (__threadfence) before AND has
+	// already counted the item in ctl[OUTSTANDING] (the count must never be behind). Returns true if the offer made the
+	// item pending (it is now on its owner's inbox), false if it already was (the caller takes its count back).
+	__device__ __forceinline__ bool async_offer(const BigParams &P, const AsyncParams &A, int layer, int tx, int ty, uint32_t key)
 	{
-		if (tx < 0 || tx >= P.tilesX || ty < 0 || ty >= P.tilesY)
-			return;
 		const uint32_t item = (uint32_t)layer * (uint32_t)(P.tilesX * P.tilesY) + (uint32_t)(ty * P.tilesX + tx);
 		const uint32_t old = atomicMin(P.key + item, key);
-		if (old == MTD_INF)
-		{
-			atomicAdd(A.ctl + ACTL_OUTSTANDING, 1u);
-			const int o = async_owner(A, layer, tx, ty);
-			const uint32_t pos = atomicAdd(A.tail + o * 32, 1u);
-			__stcg(A.inbox + (size_t)o * (A.cap_mask + 1u) + (pos & A.cap_mask), item + 1u);
-			atomicMin(A.ctamin + o, key); // the owner's published wavefront position covers the offer before its scheduler has seen it
-		}
+		if (old != MTD_INF)
+			return false;
+		const int o = async_owner(A, layer, tx, ty);
+		const uint32_t pos = atomicAdd(A.tail + o * 32, 1u);
+		__stcg(A.inbox + (size_t)o * (A.cap_mask + 1u) + (pos & A.cap_mask), item + 1u);
+		atomicMin(A.ctamin + o, key); // the owner's published wavefront position covers the offer before its scheduler has seen it
+		return true;
 	}
 
 	// sources := 0, their items pending (one thread per (layer, source)); ctl[OUTSTANDING] counts them
@@ -122,8 +151,10 @@ namespace mtd
 		if (y < P.y0 || y >= P.y1)
 			return;
 		P.dist[(size_t)layer * P.layer_stride + (size_t)(y - P.y0) * P.W + x] = 0u;
+		atomicAdd(A.ctl + ACTL_OUTSTANDING, 1u);
 		__threadfence();
-		async_offer(P, A, layer, x / TS, (y - P.y0) / TS, 0u);
+		if (!async_offer(P, A, layer, x / TS, (y - P.y0) / TS, 0u))
+			atomicSub(A.ctl + ACTL_OUTSTANDING, 1u); // several sources in one tile: one item
 	}
 
 	// One visit of item (layer, tx, ty) by one warp: stage the 34 x 34 frame (labels + packed weights), seed from the apron
@@ -131,7 +162,7 @@ namespace mtd
 	// Returns in k[4] (warp-uniform) the smallest label on offer to the tile above / below / left / right (MTD_INF: none).
 	// Same arithmetic as the visit inside k_tile_rounds; `guard` is raised when a label gets close to the uint32 wrap.
 	template<int TS, class WT>
-	__device__ __forceinline__ void warp_visit(const BigParams &P, WT &S, int layer, int tx, int ty, uint32_t lane, uint32_t lt, uint32_t (&k)[4], bool &guard, const CUtensorMap *tm_dist, const CUtensorMap *tm_w, uint32_t &tma_phase)
+	__device__ __forceinline__ void warp_visit(const BigParams &P, WT &S, int layer, int tx, int ty, uint32_t lane, uint32_t lt, uint32_t (&k)[4], bool &guard, const CUtensorMap *tm_dist, const CUtensorMap *tm_w, uint32_t &tma_phase, uint32_t next_item MTD_ATIMING_ARGS)
 	{
 		constexpr int RW = WT::RW, PITCH = WT::PITCH, QCAP = WT::QCAP;
 		const int W = P.W;
@@ -158,6 +189,16 @@ namespace mtd
 				mbar_expect_tx(&S.bar, 2u * (uint32_t)(RW * PITCH * 4));
 				tma_load_3d(S.d, tm_dist, tx * TS - 4, ly0, layer, &S.bar);
 				tma_load_2d(S.w, tm_w, tx * TS - 4, ly0, &S.bar);
+				if (next_item < SLOT_EXIT)
+				{
+					// the item waiting in my second mailbox: its frames are on their way to L2 while this one is relaxed
+					const uint32_t nt = (uint32_t)(P.tilesX * P.tilesY);
+					const int nl = (int)(next_item / nt);
+					const uint32_t ntile = next_item - (uint32_t)nl * nt;
+					const int nx = (int)(ntile % (uint32_t)P.tilesX) * TS - 4, ny = (int)(ntile / (uint32_t)P.tilesX) * TS - 1;
+					tma_prefetch_3d(tm_dist, nx, ny, nl);
+					tma_prefetch_2d(tm_w, nx, ny);
+				}
 			}
 			mbar_wait(&S.bar, tma_phase);
 			tma_phase ^= 1u;
@@ -222,6 +263,7 @@ namespace mtd
 		}
 		__syncwarp();
 
+		MTD_ATICK(2);
 		// ---- seeds ----
 		uint32_t tail = 0;
 		uint32_t my_min = MTD_INF;
@@ -350,6 +392,7 @@ namespace mtd
 		uint32_t dmin = warp_redux_min(my_min);
 		__syncwarp();
 
+		MTD_ATICK(3);
 		// ---- bucketed wavefront on the frame, warp-synchronous ----
 		uint32_t nq = tail, par = 0;
 		bool overflow = false;
@@ -364,6 +407,10 @@ namespace mtd
 			const uint16_t *rq = S.q[par];
 			wq = S.q[par ^ 1u];
 			tail = 0;
+#ifdef MTD_TIMING
+			tacc[7] += 1ull;
+			tacc[8] += nq;
+#endif
 			uint32_t newmin = MTD_INF;
 			for (uint32_t base = 0; base < nq; base += 32u)
 			{
@@ -462,6 +509,7 @@ namespace mtd
 		}
 		__syncwarp();
 
+		MTD_ATICK(4);
 		// ---- write back the interior ----
 		if (interior_wb)
 		{
@@ -507,13 +555,15 @@ namespace mtd
 		}
 	}
 
+	constexpr int ASYNC_SLOTS = 2 * ASYNC_WORKERS; // every worker has a mailbox of two: the item it visits and the one it visits next
+
 	struct AsyncSched
 	{
 		uint32_t pend_item[ASYNC_PCAP];
 		uint32_t pend_key[ASYNC_PCAP];
-		uint32_t slot[ASYNC_WORKERS];   // mailbox: SLOT_IDLE, SLOT_EXIT or the item to visit (written by the scheduler, reset by the worker)
-		uint32_t ifitem[ASYNC_WORKERS]; // what each worker was given last
-		uint32_t ifkey[ASYNC_WORKERS];  // the key it was given at
+		uint32_t slot[ASYNC_SLOTS];  // mailbox [worker][2]: SLOT_IDLE, SLOT_EXIT or the item to visit (written by the scheduler, reset by the worker)
+		uint32_t ifkey[ASYNC_SLOTS]; // the key each handed-out item was given at
+		uint32_t asg_slot[ASYNC_SLOTS], asg_item[ASYNC_SLOTS]; // hand-outs of the current scheduler iteration
 	};
 
 	template<int TS>
@@ -526,18 +576,17 @@ namespace mtd
 	template<int TS>
 	__global__ void __launch_bounds__((ASYNC_WORKERS + 1) * 32, 1) k_tile_async(const BigParams P, const AsyncParams A, const __grid_constant__ CUtensorMap tm_dist, const __grid_constant__ CUtensorMap tm_w)
 	{
-		extern __shared__ __align__(128) unsigned char smem_raw[];
+		extern __shared__ __align__(128) unsigned char smem_async[];
 		using WT = AsyncFrame<TS>;
 		const int warp = threadIdx.x >> 5;
 		const uint32_t lane = lane_id();
 		const uint32_t lt = lanemask_lt();
-		AsyncSched &Q = *reinterpret_cast<AsyncSched *>(smem_raw + sizeof(WT) * ASYNC_WORKERS);
+		AsyncSched &Q = *reinterpret_cast<AsyncSched *>(smem_async + sizeof(WT) * ASYNC_WORKERS);
 		volatile uint32_t *slot = Q.slot;
 		const uint32_t ntiles = (uint32_t)(P.tilesX * P.tilesY);
-		if (threadIdx.x < ASYNC_WORKERS)
+		if (threadIdx.x < ASYNC_SLOTS)
 		{
 			Q.slot[threadIdx.x] = SLOT_IDLE;
-			Q.ifitem[threadIdx.x] = MTD_INF;
 			Q.ifkey[threadIdx.x] = MTD_INF;
 		}
 		__syncthreads();
@@ -545,9 +594,13 @@ namespace mtd
 		if (warp < ASYNC_WORKERS)
 		{
 			// ---------------- worker ----------------
-			WT &S = reinterpret_cast<WT *>(smem_raw)[warp];
+			WT &S = reinterpret_cast<WT *>(smem_async)[warp];
 			bool guard = false;
-			uint32_t visits = 0, tma_phase = 0;
+			uint32_t visits = 0, tma_phase = 0, take = 0;
+#ifdef MTD_TIMING
+			unsigned long long tacc[16] = { 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0 };
+			long long last__ = clock64();
+#endif
 			if (lane == 0)
 			{
 				mbar_init(&S.bar, 1u);
@@ -556,44 +609,55 @@ namespace mtd
 			__syncwarp();
 			for (;;)
 			{
+				const int mine = warp * 2 + (int)take;
 				uint32_t it = 0;
 				if (lane == 0)
-					while ((it = slot[warp]) == SLOT_IDLE)
-						__nanosleep(40);
+				{
+					while ((it = slot[mine]) == SLOT_IDLE)
+						__nanosleep(20);
+					__threadfence(); // acquire: the scheduler consumed the item's key (and fenced) before it wrote the mailbox
+				}
 				it = __shfl_sync(0xFFFFFFFFu, it, 0);
 				if (it == SLOT_EXIT)
 					break;
+				MTD_ATICK(0);
 				const int layer = (int)(it / ntiles);
 				const uint32_t tile = it - (uint32_t)layer * ntiles;
 				const int tx = (int)(tile % (uint32_t)P.tilesX), ty = (int)(tile / (uint32_t)P.tilesX);
-				if (lane == 0)
-				{
-					atomicExch(P.key + it, MTD_INF); // consume the offers: whoever made one wrote its labels first
-					__threadfence();
-				}
-				__syncwarp();
+				MTD_ATICK(1);
 				uint32_t k[4];
-				warp_visit<TS>(P, S, layer, tx, ty, lane, lt, k, guard, A.use_tma ? &tm_dist : nullptr, A.use_tma ? &tm_w : nullptr, tma_phase);
-				__threadfence(); // my labels are visible before a neighbour can be scheduled
+				warp_visit<TS>(P, S, layer, tx, ty, lane, lt, k, guard, A.use_tma ? &tm_dist : nullptr, A.use_tma ? &tm_w : nullptr, tma_phase, slot[mine ^ 1] MTD_ATIMING_PASS);
+				// offers to the four neighbours. The items they may create are counted BEFORE the offers are made (the
+				// count of pending + in-flight items is never behind, so it cannot read zero early); mine is given up with them.
+				const uint32_t kk = lane == 0 ? k[0] : lane == 1 ? k[1] : lane == 2 ? k[2] : k[3];
+				const bool have = lane < 4u && kk != MTD_INF && (lane == 0 ? ty > 0 : lane == 1 ? ty < P.tilesY - 1 : lane == 2 ? tx > 0 : tx < P.tilesX - 1);
+				const uint32_t noff = (uint32_t)__popc(__ballot_sync(0xFFFFFFFFu, have));
+				if (lane == 0 && noff != 1u)
+					atomicAdd(A.ctl + ACTL_OUTSTANDING, noff - 1u); // noff == 0: this visit's own count goes
+				__threadfence(); // my labels (and the count) are visible before a neighbour can be scheduled
 				__syncwarp();
-				if (lane == 0 && k[0] != MTD_INF)
-					async_offer(P, A, layer, tx, ty - 1, k[0]);
-				if (lane == 1 && k[1] != MTD_INF)
-					async_offer(P, A, layer, tx, ty + 1, k[1]);
-				if (lane == 2 && k[2] != MTD_INF)
-					async_offer(P, A, layer, tx - 1, ty, k[2]);
-				if (lane == 3 && k[3] != MTD_INF)
-					async_offer(P, A, layer, tx + 1, ty, k[3]);
-				__syncwarp();
+				MTD_ATICK(5);
+				bool made = false;
+				if (have)
+					made = async_offer(P, A, layer, lane == 2 ? tx - 1 : lane == 3 ? tx + 1 : tx, lane == 0 ? ty - 1 : lane == 1 ? ty + 1 : ty, kk);
+				const uint32_t stale = (uint32_t)__popc(__ballot_sync(0xFFFFFFFFu, have && !made));
 				visits++;
 				if (lane == 0)
 				{
-					__threadfence();
-					atomicSub(A.ctl + ACTL_OUTSTANDING, 1u); // after the increments of the offers above
-					slot[warp] = SLOT_IDLE;
+					if (stale)
+						atomicSub(A.ctl + ACTL_OUTSTANDING, stale); // those items were pending already
+					slot[mine] = SLOT_IDLE;
 				}
+				take ^= 1u;
 				__syncwarp();
+				MTD_ATICK(6);
 			}
+#ifdef MTD_TIMING
+			if (lane == 0)
+				for (int q = 0; q < 16; q++)
+					if (tacc[q])
+						atomicAdd(&g_async_timing[q], tacc[q]);
+#endif
 			if (lane == 0)
 			{
 				atomicAdd(A.ctl + ACTL_VISITS, visits);
@@ -609,6 +673,7 @@ namespace mtd
 		const uint32_t cap = A.cap_mask + 1u;
 		uint32_t *ring = A.inbox + (size_t)me * cap;
 		uint32_t head = 0, pn = 0, polls = 0;
+		uint32_t fill = 0; // lane w < WORKERS: which of worker w's two mailboxes is filled next (the worker empties them in the same order)
 		const unsigned long long t0 = global_timer_ns();
 		bool stop = false;
 		while (!stop)
@@ -649,22 +714,26 @@ namespace mtd
 				Q.pend_key[i] = kk;
 				mymin = min(mymin, kk);
 			}
-			// workers
-			uint32_t st = SLOT_EXIT;
-			if (lane < ASYNC_WORKERS)
-				st = slot[lane];
-			uint32_t idle = __ballot_sync(0xFFFFFFFFu, lane < ASYNC_WORKERS && st == SLOT_IDLE);
-			if (lane < ASYNC_WORKERS && st != SLOT_IDLE)
+			// mailboxes: lane l looks at slot l (worker l / 2)
+			uint32_t cur = slot[lane];
+			if (cur < SLOT_EXIT)
 				mymin = min(mymin, Q.ifkey[lane]);
+			const uint32_t busy_slots = __ballot_sync(0xFFFFFFFFu, cur < SLOT_EXIT);
 			const uint32_t cmin = warp_redux_min(mymin);
 			if (lane == 0)
 				__stcg(A.ctamin + me, cmin);
 			const uint32_t wm = min(cmin, warp_redux_min(others));
 			const uint32_t kthr = wm > MTD_INF - P.tile_delta ? MTD_INF : wm + P.tile_delta;
+			// workers that can take an item: first the ones with nothing to do, then the ones that have no NEXT item yet
+			uint32_t idle_w = 0, half_w = 0;
+			{
+				const uint32_t b0 = (busy_slots >> (2u * (lane & 15u))) & 3u;
+				idle_w = __ballot_sync(0xFFFFFFFFu, lane < ASYNC_WORKERS && b0 == 0u);
+				half_w = __ballot_sync(0xFFFFFFFFu, lane < ASYNC_WORKERS && (b0 == 1u || b0 == 2u));
+			}
 			__syncwarp();
-			// hand the smallest eligible keys to idle workers
-			uint32_t skipped = 0; // pending entries found busy are hidden for this iteration by parking their cached key
-			while (idle != 0u && pn != 0u)
+			uint32_t nasg = 0;
+			while ((idle_w | half_w) != 0u && pn != 0u)
 			{
 				uint32_t bk = MTD_INF;
 				for (uint32_t i = lane; i < pn; i += 32)
@@ -678,32 +747,48 @@ namespace mtd
 						bi = min(bi, i);
 				bi = warp_redux_min(bi);
 				const uint32_t item = Q.pend_item[bi];
-				const bool busy = __any_sync(0xFFFFFFFFu, lane < ASYNC_WORKERS && !((idle >> lane) & 1u) && Q.ifitem[lane] == item);
-				__syncwarp();
-				if (busy)
+				if (__any_sync(0xFFFFFFFFu, cur == item))
 				{
-					// its tile is being visited right now: leave it pending, look at the next one
+					// its tile is being visited (or waits in a mailbox): it stays pending; hidden for this iteration
 					if (lane == 0)
 						Q.pend_key[bi] = MTD_INF;
-					skipped++;
 					__syncwarp();
 					continue;
 				}
-				const int w = __ffs(idle) - 1;
+				const int w = idle_w ? __ffs(idle_w) - 1 : __ffs(half_w) - 1;
+				const uint32_t f = __shfl_sync(0xFFFFFFFFu, fill, w);
+				const uint32_t sl = (uint32_t)w * 2u + f;
+				if (lane == (uint32_t)w)
+					fill ^= 1u;
+				if (lane == sl)
+					cur = item;
 				if (lane == 0)
 				{
-					Q.ifitem[w] = item;
-					Q.ifkey[w] = kmin;
+					Q.ifkey[sl] = kmin;
+					Q.asg_slot[nasg] = sl;
+					Q.asg_item[nasg] = item;
 					Q.pend_item[bi] = Q.pend_item[pn - 1];
 					Q.pend_key[bi] = Q.pend_key[pn - 1];
-					__threadfence_block();
-					slot[w] = item;
 				}
+				nasg++;
 				pn--;
-				idle &= idle - 1u;
+				if (idle_w)
+					idle_w &= idle_w - 1u;
+				else
+					half_w &= half_w - 1u;
 				__syncwarp();
 			}
-			(void)skipped;
+			if (nasg)
+			{
+				// consume the offers of everything handed out (whoever made one wrote its labels first), THEN ring the mailboxes
+				if (lane < nasg)
+					atomicExch(P.key + Q.asg_item[lane], MTD_INF);
+				__threadfence();
+				__syncwarp();
+				if (lane < nasg)
+					slot[Q.asg_slot[lane]] = Q.asg_item[lane];
+				__syncwarp();
+			}
 			polls++;
 			if (aborted || outstanding == 0u)
 				stop = true;
@@ -716,20 +801,19 @@ namespace mtd
 				}
 				stop = true;
 			}
-			else
+			else if (nasg == 0)
 				__nanosleep(100);
 		}
-		// release the workers: a busy one finishes its visit first
+		// release the workers: a busy one finishes what is in its mailboxes first
 		for (;;)
 		{
-			uint32_t st = SLOT_EXIT;
-			if (lane < ASYNC_WORKERS)
+			uint32_t st = slot[lane];
+			if (st == SLOT_IDLE)
 			{
-				st = slot[lane];
-				if (st == SLOT_IDLE)
-					slot[lane] = SLOT_EXIT;
+				slot[lane] = SLOT_EXIT;
+				st = SLOT_EXIT;
 			}
-			if (!__any_sync(0xFFFFFFFFu, st != SLOT_EXIT && st != SLOT_IDLE))
+			if (!__any_sync(0xFFFFFFFFu, st != SLOT_EXIT))
 				break;
 			__nanosleep(200);
 		}

@@ -907,3 +907,129 @@ void mo_monsters_dots_tick(int n, uint32_t *dot_duration, uint32_t *dot_damage, 
 		}
 	}
 }
+
+/* ---- "attacks": sources/game/attacks.cpp:132-160 per tower, queries by brute force (see mazetd_oracle.h) ---- */
+static float mo_flat_dist2(const float *a, const float *b)
+{
+	/* distanceSquared(a * Vec3(1, 0, 1), b * Vec3(1, 0, 1)): dot sums ((0 + dx*dx) + 0*0) + dz*dz (cage-core/math.h:919-938) */
+	const float d0 = a[0] - b[0], d2 = a[2] - b[2];
+	float sum = 0;
+	sum += d0 * d0;
+	sum += 0.0f;
+	sum += d2 * d2;
+	return sum;
+}
+
+void mo_towers_attack(const mo_grid *g, uint32_t gameTime, mo_towers *tw, int nm, const uint32_t *tileStart, const uint32_t *tileEnd, const uint32_t *timeStart, const uint32_t *timeEnd, const uint8_t *alive,
+					  const uint8_t *monsterClass, const uint32_t *timeToArrive, const int64_t *life, uint32_t *dot_duration, uint32_t *dot_damage)
+{
+	float *pos = (float *)malloc((size_t)(nm > 0 ? nm : 1) * 3 * sizeof(float));
+	mo_monsters_position(g, gameTime, nm, tileStart, tileEnd, timeStart, timeEnd, pos); /* spatial.cpp:30 and attacks.cpp:80: mv.position() */
+	for (int t = 0; t < tw->n; t++)
+	{
+		tw->target_out[t] = -1;
+		tw->hits_out[t] = 0;
+		if (tw->firingDelay[t] > 0) /* :136-140 */
+		{
+			tw->firingDelay[t]--;
+			continue;
+		}
+		/* applyMods, :40-71 */
+		uint32_t damage = tw->damage[t], overTime = tw->overTime[t], firingPeriod = tw->firingPeriod[t], manaCost = tw->manaCost[t];
+		float firingRange = tw->firingRange[t], splashRadius = tw->splashRadius[t];
+		const int element = tw->element[t];
+		if (element != 0)
+		{
+			overTime = (uint32_t)(sqrtf((float)damage) * 20.0f);
+			damage *= 3u;
+		}
+		switch (tw->bonus[t])
+		{
+		case 1: damage *= 2u; manaCost *= 2u; break;
+		case 2: firingPeriod /= 2u; break;
+		case 3: firingRange += 4.0f; break;
+		case 4: splashRadius += 2.0f; manaCost *= 3u; break;
+		case 5: overTime /= 5u; break;
+		case 6: manaCost /= 3u; break;
+		default: break;
+		}
+		float mp[3];
+		mo_grid_center(g, tw->tile[t], mp);
+		/* findMonstersForTower + pickTargetMonster: first strictly smallest value in ascending monster index */
+		int best = -1, count = 0;
+		float bv = 0;
+		const int targeting = tw->targeting[t];
+		const uint64_t rw = tw->random_words ? tw->random_words[t] : 0;
+		for (int i = 0; i < nm; i++)
+		{
+			if (!alive[i] || (monsterClass && (monsterClass[i] & tw->invalidClasses[t])))
+				continue;
+			if (!(sqrtf(mo_flat_dist2(&pos[i * 3], mp)) <= firingRange))
+				continue;
+			count++;
+			float v;
+			switch (targeting)
+			{
+			case 1: v = (float)timeToArrive[i]; break;            /* Front */
+			case 2: v = (float)(-(int32_t)timeToArrive[i]); break; /* Back: -numeric_cast<sint32>(timeToArrive) */
+			case 3: v = mo_flat_dist2(&pos[i * 3], mp); break;     /* Closest */
+			case 4: v = -mo_flat_dist2(&pos[i * 3], mp); break;    /* Farthest */
+			case 5: v = (float)(-life[i]); break;                  /* Strongest */
+			case 6: v = (float)life[i]; break;                     /* Weakest */
+			default: v = 0; break;                                 /* Random: resolved below */
+			}
+			if (best < 0 || (targeting != 0 && v < bv))
+			{
+				best = i;
+				bv = v;
+			}
+		}
+		if (count == 0)
+			continue; /* :152-153 */
+		if (manaCost > 0) /* consumeMana, :95-105 */
+		{
+			if (tw->mana[t] < manaCost)
+				continue;
+			tw->mana[t] -= manaCost;
+		}
+		if (targeting == 0)
+		{
+			uint64_t want = rw % (uint64_t)count, seen = 0;
+			for (int i = 0; i < nm; i++)
+			{
+				if (!alive[i] || (monsterClass && (monsterClass[i] & tw->invalidClasses[t])))
+					continue;
+				if (!(sqrtf(mo_flat_dist2(&pos[i * 3], mp)) <= firingRange))
+					continue;
+				if (seen++ == want)
+				{
+					best = i;
+					break;
+				}
+			}
+		}
+		tw->target_out[t] = best;
+		/* damageMonsters on the target, or on the splash set around it (:157-159, :120-130) */
+		if (splashRadius > 0)
+		{
+			for (int i = 0; i < nm; i++)
+			{
+				if (!alive[i] || (monsterClass && (monsterClass[i] & tw->invalidClasses[t])))
+					continue;
+				if (!(sqrtf(mo_flat_dist2(&pos[i * 3], &pos[best * 3])) <= splashRadius))
+					continue;
+				dot_damage[(size_t)element * nm + i] += damage;
+				dot_duration[(size_t)element * nm + i] += overTime;
+				tw->hits_out[t]++;
+			}
+		}
+		else
+		{
+			dot_damage[(size_t)element * nm + best] += damage;
+			dot_duration[(size_t)element * nm + best] += overTime;
+			tw->hits_out[t] = 1;
+		}
+		tw->firingDelay[t] += firingPeriod; /* :161 */
+	}
+	free(pos);
+}

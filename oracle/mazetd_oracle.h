@@ -139,6 +139,28 @@ void mo_monsters_position(const mo_grid *g, uint32_t gameTime, int n, const uint
 /* trial of sources/player/buildingsPlacement.cpp:18-42: 1 if the candidate building would disconnect a waypoint or a monster */
 int mo_placing_blocks(const mo_grid *g, const uint32_t *wp_tiles, int n, uint32_t candidate, const uint32_t *monster_tiles, const uint8_t *monster_alive, int nmonsters, uint32_t *scratch_tiles, uint32_t *scratch_dist);
 
+/* "attacks" (sources/game/attacks.cpp:132-160) with the monster queries of sources/game/spatial.cpp:24-34 done by brute
+ * force: the SET a sphere query returns is what is restated (externals/cage/sources/libcore/geometry/geometry.cpp:82-86,
+ * 471-474: sqrt(dx*dx + dz*dz) <= radius on the y-flattened positions); the ORDER cage's BVH enumerates it in is not
+ * observable, so ties of a picker's value go to the LOWEST monster index here. TargetingEnum::Random (attacks.cpp:216-228)
+ * depends on that order and on the global RNG: picks candidate number `random_words[tower] % count` in index order (unpinned).
+ * Arrays: towers SoA (DamageComponent / AttackComponent / PositionComponent / ManaStorageComponent fields, sources/game.h:206-245),
+ * monsters SoA; dot arrays [5][nm]. target_out: picked monster per tower or -1; hits_out: monsters that received the dot. */
+typedef struct
+{
+	int n;
+	const uint32_t *tile;
+	const uint32_t *damage, *overTime, *firingPeriod, *manaCost;
+	const float *firingRange, *splashRadius;
+	const uint8_t *invalidClasses, *element, *bonus, *targeting;
+	uint32_t *firingDelay, *mana;
+	const uint64_t *random_words; /* may be NULL (0) */
+	int32_t *target_out;
+	uint32_t *hits_out;
+} mo_towers;
+void mo_towers_attack(const mo_grid *g, uint32_t gameTime, mo_towers *tw, int nm, const uint32_t *tileStart, const uint32_t *tileEnd, const uint32_t *timeStart, const uint32_t *timeEnd, const uint8_t *alive,
+					  const uint8_t *monsterClass, const uint32_t *timeToArrive, const int64_t *life, uint32_t *dot_duration, uint32_t *dot_damage);
+
 #ifdef __cplusplus
 }
 #endif
