@@ -80,6 +80,8 @@ enum
 	MTD_DEBUG_GROUP_WARPS = 2, /* warps cooperating on one distance layer in the one-CTA path: 1, 2 or 4 */
 	MTD_DEBUG_WALKER = 3,      /* who walks the full paths in the one-CTA path: 0 auto (walker warp when a CTA owns several maps), 1 workers, 2 walker warp */
 	MTD_DEBUG_BIG_ASYNC = 5,   /* large grids: 1 (default) = dataflow scheduler without global rounds (k_tile_async), 0 = round-based kernel (k_tile_rounds). Same result */
+	MTD_DEBUG_ASYNC_NB_RULE = 8, /* dataflow scheduler: value >= 0: a tile does not start while a neighbour tile is in flight or waits with a key smaller by more than `value`; < 0: off. Performance only */
+	MTD_DEBUG_ASYNC_DEPTH = 9, /* dataflow scheduler: mailboxes per worker (1, or 2 = the next item is handed out and prefetched early). Performance only */
 	MTD_DEBUG_BIG_TMA = 7,     /* dataflow scheduler: 1 (default) = tile frames staged by 2-D bulk tensor copies (TMA), 0 = cp.async rows. Same result */
 	MTD_DEBUG_ASYNC_DELTA = 6, /* priority window (label units) of the dataflow scheduler. Performance only */
 	MTD_DEBUG_TILE_DELTA = 4   /* large grids: width (label units) of the window of tile offers visited per round; 2^32-1 = visit everything (no priority). Performance only: any value gives the same result */
@@ -242,6 +244,27 @@ int mtd_monsters_dots_upload(mtd_ctx *ctx, const uint32_t *duration, const uint3
 int mtd_monsters_dots_tick_dev(mtd_ctx *ctx);
 int mtd_monsters_dots_tick(mtd_ctx *ctx, int64_t *money_out, uint32_t *killed_out);
 int mtd_monsters_dots_download(mtd_ctx *ctx, uint32_t *duration, uint32_t *damage, int64_t *life, uint8_t *alive);
+
+/* ---- Towers: monster spatial index + attack pass ------------------------------
+ * Replaces, per game tick, the "spatial rebuild" listener (sources/game/spatial.cpp:24-34: cage's BVH over
+ * MovementComponent::position() of every monster) and the "attacks" listener (sources/game/attacks.cpp:132-160) on the
+ * resident monster SoA. The BVH becomes a uniform grid (one bin per map tile, counting sort); every tower is served by one
+ * warp: firing delay, applyMods (:40-71), sphere query + class filter (:73-92), mana (:95-105), target picker (:171-216),
+ * splash query (:94-98), damage-over-time added to the hit monsters (:120-130).
+ * Parity: the SET a query returns and the picker's VALUE order are the reference's; the order in which cage's BVH
+ * enumerates a set is not observable, so ties of a value go to the lowest monster index. TargetingEnum::Random depends
+ * on that order and on the global RNG stream: it picks candidate number random_words[tower] % count in index order
+ * (documented as unpinned). Rendering effects (:107-117) stay on the host.
+ * Tower arrays: PositionComponent::tile, DamageComponent {damage, overTime, firingPeriod, firingRange, splashRadius,
+ * manaCost, invalidClasses}, AttackComponent {element 0..4, bonus 0..6, targeting 0..6, firingDelay},
+ * ManaStorageComponent::mana (sources/game.h:206-245). Needs mtd_monsters_upload + mtd_monsters_dots_upload before. */
+int mtd_monsters_class_upload(mtd_ctx *ctx, const uint8_t *monsterClass /* MonsterClassFlags per monster, NULL = none */);
+int mtd_towers_upload(mtd_ctx *ctx, int32_t n, const uint32_t *tile, const uint32_t *damage, const uint32_t *overTime, const uint32_t *firingPeriod, const float *firingRange, const float *splashRadius,
+					  const uint32_t *manaCost, const uint8_t *invalidClasses, const uint8_t *element, const uint8_t *bonus, const uint8_t *targeting, const uint32_t *firingDelay, const uint32_t *mana);
+/* one tick at gameTime: index rebuild + every tower; random_words: host array [n] for Random targeting or NULL. Asynchronous. */
+int mtd_towers_attack_dev(mtd_ctx *ctx, uint32_t gameTime, const uint64_t *random_words);
+/* tower state after the last tick (any pointer may be NULL): firingDelay, mana, picked monster (-1: did not fire), monsters hit. Synchronises. */
+int mtd_towers_download(mtd_ctx *ctx, uint32_t *firingDelay, uint32_t *mana, int32_t *target, uint32_t *hits);
 
 #ifdef __cplusplus
 }

@@ -25,6 +25,7 @@ EXPORTS = [
     "mtd_monsters_upload", "mtd_monsters_download", "mtd_monsters_tick_dev", "mtd_monsters_tick",
     "mtd_monsters_positions_dev", "mtd_monsters_positions", "mtd_monster_spawn",
     "mtd_monsters_dots_upload", "mtd_monsters_dots_tick_dev", "mtd_monsters_dots_tick", "mtd_monsters_dots_download",
+    "mtd_monsters_class_upload", "mtd_towers_upload", "mtd_towers_attack_dev", "mtd_towers_download",
 ]
 
 
@@ -103,6 +104,10 @@ def load():
     L.mtd_monsters_dots_tick_dev.argtypes = [vp]
     L.mtd_monsters_dots_tick.argtypes = [vp, C.POINTER(C.c_int64), C.POINTER(u32)]
     L.mtd_monsters_dots_download.argtypes = [vp, vp, vp, vp, vp]
+    L.mtd_monsters_class_upload.argtypes = [vp, vp]
+    L.mtd_towers_upload.argtypes = [vp, i32] + [vp] * 13
+    L.mtd_towers_attack_dev.argtypes = [vp, u32, vp]
+    L.mtd_towers_download.argtypes = [vp, vp, vp, vp, vp]
     _lib = L
     return L
 
@@ -147,6 +152,8 @@ class Context:
     DEBUG_BIG_ASYNC = 5
     DEBUG_ASYNC_DELTA = 6
     DEBUG_BIG_TMA = 7
+    DEBUG_ASYNC_NB_RULE = 8
+    DEBUG_ASYNC_DEPTH = 9
 
     def big_stats(self):
         """rounds, tile visits, scheduler polls, dataflow flag of the last tiled update"""
@@ -420,6 +427,31 @@ class Context:
         n = self.nmon
         out = dict(duration=np.empty((5, n), np.uint32), damage=np.empty((5, n), np.uint32), life=np.empty(n, np.int64), alive=np.empty(n, np.uint8))
         self._ck(self.L.mtd_monsters_dots_download(self.h, _p(out["duration"]), _p(out["damage"]), _p(out["life"]), _p(out["alive"])))
+        return out
+
+    # ---- towers: spatial index + attack pass ----
+    TOWER_U32 = ("tile", "damage", "overTime", "firingPeriod")
+    TOWER_FIELDS = ("tile", "damage", "overTime", "firingPeriod", "firingRange", "splashRadius", "manaCost", "invalidClasses", "element", "bonus", "targeting", "firingDelay", "mana")
+
+    def monsters_class_upload(self, monster_class):
+        self._ck(self.L.mtd_monsters_class_upload(self.h, _p(None if monster_class is None else np.ascontiguousarray(monster_class, np.uint8))))
+
+    def towers_upload(self, tw):
+        """tw: dict of arrays named like the reference's components (TOWER_FIELDS)"""
+        dt = dict(firingRange=np.float32, splashRadius=np.float32, invalidClasses=np.uint8, element=np.uint8, bonus=np.uint8, targeting=np.uint8)
+        arrs = [np.ascontiguousarray(tw[k], dt.get(k, np.uint32)) for k in self.TOWER_FIELDS]
+        self.ntowers = len(arrs[0])
+        self._ck(self.L.mtd_towers_upload(self.h, self.ntowers, *[_p(a) for a in arrs]))
+
+    def towers_attack_dev(self, game_time, random_words=None):
+        rw = None if random_words is None else np.ascontiguousarray(random_words, np.uint64)
+        self._ck(self.L.mtd_towers_attack_dev(self.h, int(game_time), _p(rw)))
+        self._rw_keep = rw  # the copy is asynchronous
+
+    def towers_download(self):
+        n = self.ntowers
+        out = dict(firingDelay=np.empty(n, np.uint32), mana=np.empty(n, np.uint32), target=np.empty(n, np.int32), hits=np.empty(n, np.uint32))
+        self._ck(self.L.mtd_towers_download(self.h, _p(out["firingDelay"]), _p(out["mana"]), _p(out["target"]), _p(out["hits"])))
         return out
 
     def monster_spawn(self, game_time, speed):

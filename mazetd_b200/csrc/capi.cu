@@ -24,6 +24,7 @@
 #include "small_maps.cuh"
 #include "sssp_warp.cuh"
 #include "tile_async.cuh"
+#include "towers.cuh"
 
 using namespace mtd;
 
@@ -119,9 +120,12 @@ struct mtd_ctx
 	DevBuf<uint32_t> sources;
 	int tilesX = 0, tilesY = 0;
 	uint32_t last_rounds = 0;
-	DevBuf<uint32_t> a_inbox, a_tail, a_ctamin, a_ctl; // dataflow scheduler of k_tile_async: inbox rings, ring tails, per-CTA smallest keys, control words
+	DevBuf<unsigned long long> a_inbox;
+	DevBuf<uint32_t> a_tail, a_ctamin, a_ctl, a_fly;
+	int async_nb_rule = 0, async_depth = 2; // measured (profiles/r02g_*): the neighbour rule halves the visits but not the time; two mailboxes: 14.5 -> 13.0 ms on C4
+	uint32_t async_nb_margin = 0; // dataflow scheduler of k_tile_async: inbox rings, ring tails, per-CTA smallest keys, control words
 	bool big_async = true;         // large grids: k_tile_async (no global rounds); false = k_tile_rounds (A/B and multi-stripe contexts)
-	uint32_t async_delta = 32768;  // priority window of the dataflow scheduler (label units)
+	uint32_t async_delta = 65536;  // priority window of the dataflow scheduler (label units); swept 8k..256k on C4 / C5 (profiles/r02c_*, r02g_*)
 	uint32_t last_visits = 0;
 	bool last_async = false, last_tma = false;
 	bool big_tma = true;           // dataflow scheduler: stage frames with bulk tensor copies (TMA) when the width allows it
@@ -169,6 +173,17 @@ struct mtd_ctx
 	DevBuf<long long> m_life;
 	DevBuf<uint8_t> m_resist;
 	DevBuf<float> m_pos;
+	DevBuf<uint8_t> m_class;
+	bool m_has_class = false;
+	// towers (attack pass) and the uniform-grid monster index they query
+	int ntowers = 0;
+	DevBuf<uint32_t> t_tile, t_damage, t_overTime, t_period, t_manaCost, t_delay, t_mana, t_hits;
+	DevBuf<float> t_range, t_splash;
+	DevBuf<uint8_t> t_invalid, t_element, t_bonus, t_targeting;
+	DevBuf<unsigned long long> t_random;
+	DevBuf<int> t_target;
+	DevBuf<uint32_t> sp_count, sp_start, sp_binof, sp_rank, sp_sorted;
+	DevBuf<float2> sp_xz;
 
 	// scratch
 	DevBuf<uint32_t> scratch_u32a, scratch_u32b, scratch_u32c, scratch_u32d;
@@ -534,7 +549,9 @@ namespace
 		CU(ctx->a_tail.reserve((size_t)ctas * 32));
 		CU(ctx->a_ctamin.reserve((size_t)ctas));
 		CU(ctx->a_ctl.reserve(ACTL_WORDS));
-		CU(cudaMemsetAsync(ctx->a_inbox.p, 0, (size_t)ctas * cap * 4, ctx->stream));
+		CU(ctx->a_fly.reserve(nitems));
+		CU(cudaMemsetAsync(ctx->a_fly.p, 0xFF, nitems * 4, ctx->stream));
+		CU(cudaMemsetAsync(ctx->a_inbox.p, 0, (size_t)ctas * cap * 8, ctx->stream));
 		CU(cudaMemsetAsync(ctx->a_tail.p, 0, (size_t)ctas * 32 * 4, ctx->stream));
 		CU(cudaMemsetAsync(ctx->a_ctamin.p, 0xFF, (size_t)ctas * 4, ctx->stream));
 		CU(cudaMemsetAsync(ctx->a_ctl.p, 0, ACTL_WORDS * 4, ctx->stream));
@@ -546,6 +563,10 @@ namespace
 		A.ctl = ctx->a_ctl.p;
 		A.cap_mask = cap - 1u;
 		A.ctas = ctas;
+		A.fly = ctx->a_fly.p;
+		A.nb_rule = ctx->async_nb_rule;
+		A.nb_margin = ctx->async_nb_margin;
+		A.depth = ctx->async_depth;
 		A.time_limit_ns = 20000000000ull; // an update that takes 20 s is reported, not waited for
 		P.tile_delta = ctx->async_delta;
 		// frames staged by TMA: one tensor map over the labels of all layers, one over the packed weights
@@ -578,6 +599,13 @@ namespace
 				tot += (double)t[q];
 			printf("ASYNCTIMING visits=%.0f | worker cycles per visit: wait=%.0f consume=%.0f stage=%.0f seed=%.0f engine=%.0f writeback=%.0f offers+finish=%.0f | idle share %.2f | steps/visit=%.1f cells/step=%.1f cycles/step=%.0f\n", v, t[0] / v, t[1] / v, t[2] / v,
 				   t[3] / v, t[4] / v, t[5] / v, t[6] / v, tot > 0 ? t[0] / tot : 0.0, t[7] / v, t[7] ? (double)t[8] / t[7] : 0.0, t[7] ? (double)t[4] / t[7] : 0.0);
+			unsigned long long x[4], zx[4] = { 0 };
+			cudaMemcpyFromSymbol(x, g_async_sched_extra, sizeof(x));
+			cudaMemcpyToSymbol(g_async_sched_extra, zx, sizeof(zx));
+			printf("ASYNCSCHED2 per iteration: handed out %.2f | pending left: runnable but no free mailbox here %.2f, tile in flight %.2f, beyond the window %.2f\n", t[9] ? (double)x[1] / t[9] : 0.0, t[9] ? (double)t[14] / t[9] : 0.0,
+				   t[9] ? (double)x[0] / t[9] : 0.0, t[9] ? (double)t[15] / t[9] : 0.0);
+			printf("ASYNCSCHED iterations=%llu (%.2f us each at %d schedulers over the kernel) | per iteration: idle workers seen %.2f, left idle %.2f (held back by the window %.2f), pending entries %.1f\n", t[9], 0.0, ctas, t[9] ? (double)t[10] / t[9] : 0.0,
+				   t[9] ? (double)t[11] / t[9] : 0.0, t[9] ? (double)t[12] / t[9] : 0.0, t[9] ? (double)t[13] / t[9] : 0.0);
 			fflush(stdout);
 		}
 #endif
@@ -1124,6 +1152,13 @@ extern "C" int mtd_debug_set(mtd_ctx *ctx, int key, int64_t value)
 		return MTD_OK;
 	case MTD_DEBUG_BIG_ASYNC:
 		ctx->big_async = value != 0;
+		return MTD_OK;
+	case MTD_DEBUG_ASYNC_NB_RULE:
+		ctx->async_nb_rule = value >= 0 ? 1 : 0; // value = margin (label units); negative = rule off
+		ctx->async_nb_margin = value >= 0 ? (uint32_t)value : 0u;
+		return MTD_OK;
+	case MTD_DEBUG_ASYNC_DEPTH:
+		ctx->async_depth = value >= 2 ? 2 : 1;
 		return MTD_OK;
 	case MTD_DEBUG_BIG_TMA:
 		ctx->big_tma = value != 0;
@@ -2476,4 +2511,181 @@ extern "C" int mtd_monster_spawn(mtd_ctx *ctx, uint32_t gameTime, float speed, u
 	CU(cudaStreamSynchronize(ctx->stream));
 	memcpy(out3, ctx->hflags->spawn, 12);
 	return MTD_OK;
+}
+
+// =====================================================================================================
+// towers: monster spatial index + attack pass (sources/game/spatial.cpp:24-34, sources/game/attacks.cpp:132-160)
+// =====================================================================================================
+extern "C" int mtd_monsters_class_upload(mtd_ctx *ctx, const uint8_t *monsterClass)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (ctx->nmon <= 0)
+		return fail(ctx, MTD_ERR_STATE, "upload the monsters first (mtd_monsters_upload)");
+	ctx->m_has_class = monsterClass != nullptr;
+	if (monsterClass)
+	{
+		CU(ctx->m_class.reserve((size_t)ctx->nmon));
+		CU(cudaMemcpyAsync(ctx->m_class.p, monsterClass, (size_t)ctx->nmon, cudaMemcpyHostToDevice, ctx->stream));
+		CU(cudaStreamSynchronize(ctx->stream));
+	}
+	return MTD_OK;
+}
+
+extern "C" int mtd_towers_upload(mtd_ctx *ctx, int32_t n, const uint32_t *tile, const uint32_t *damage, const uint32_t *overTime, const uint32_t *firingPeriod, const float *firingRange, const float *splashRadius,
+								 const uint32_t *manaCost, const uint8_t *invalidClasses, const uint8_t *element, const uint8_t *bonus, const uint8_t *targeting, const uint32_t *firingDelay, const uint32_t *mana)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (n < 0 || (n && (!tile || !damage || !overTime || !firingPeriod || !firingRange || !splashRadius || !manaCost || !invalidClasses || !element || !bonus || !targeting || !firingDelay || !mana)))
+		return fail(ctx, MTD_ERR_ARG, "bad tower arrays");
+	if (!ctx->have_grid || ctx->stripe)
+		return fail(ctx, MTD_ERR_STATE, "no grid uploaded (or the context holds a row stripe)");
+	for (int i = 0; i < n; i++)
+		if (tile[i] >= ctx->T || element[i] >= 5 || bonus[i] > 6 || targeting[i] > 6)
+			return fail(ctx, MTD_ERR_ARG, "tower %d: tile outside the grid or element / bonus / targeting out of range", i);
+	ctx->ntowers = n;
+	if (n == 0)
+		return MTD_OK;
+	const size_t N = (size_t)n;
+	CU(ctx->t_tile.reserve(N));
+	CU(ctx->t_damage.reserve(N));
+	CU(ctx->t_overTime.reserve(N));
+	CU(ctx->t_period.reserve(N));
+	CU(ctx->t_manaCost.reserve(N));
+	CU(ctx->t_delay.reserve(N));
+	CU(ctx->t_mana.reserve(N));
+	CU(ctx->t_hits.reserve(N));
+	CU(ctx->t_range.reserve(N));
+	CU(ctx->t_splash.reserve(N));
+	CU(ctx->t_invalid.reserve(N));
+	CU(ctx->t_element.reserve(N));
+	CU(ctx->t_bonus.reserve(N));
+	CU(ctx->t_targeting.reserve(N));
+	CU(ctx->t_random.reserve(N));
+	CU(ctx->t_target.reserve(N));
+	const cudaMemcpyKind k = cudaMemcpyHostToDevice;
+	CU(cudaMemcpyAsync(ctx->t_tile.p, tile, N * 4, k, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->t_damage.p, damage, N * 4, k, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->t_overTime.p, overTime, N * 4, k, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->t_period.p, firingPeriod, N * 4, k, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->t_manaCost.p, manaCost, N * 4, k, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->t_delay.p, firingDelay, N * 4, k, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->t_mana.p, mana, N * 4, k, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->t_range.p, firingRange, N * 4, k, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->t_splash.p, splashRadius, N * 4, k, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->t_invalid.p, invalidClasses, N, k, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->t_element.p, element, N, k, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->t_bonus.p, bonus, N, k, ctx->stream));
+	CU(cudaMemcpyAsync(ctx->t_targeting.p, targeting, N, k, ctx->stream));
+	CU(cudaMemsetAsync(ctx->t_target.p, 0xFF, N * 4, ctx->stream));
+	CU(cudaMemsetAsync(ctx->t_hits.p, 0, N * 4, ctx->stream));
+	CU(cudaStreamSynchronize(ctx->stream));
+	return MTD_OK;
+}
+
+static int towers_attack_dev(mtd_ctx *ctx, uint32_t gameTime, const uint64_t *random_words)
+{
+	if (!ctx->have_grid || ctx->stripe)
+		return fail(ctx, MTD_ERR_STATE, "no grid uploaded (or the context holds a row stripe)");
+	if (ctx->nmon <= 0 || !ctx->m_has_dots)
+		return fail(ctx, MTD_ERR_STATE, "the attack pass needs the monsters and their damage-over-time state (mtd_monsters_upload, mtd_monsters_dots_upload)");
+	if (ctx->ntowers == 0)
+		return MTD_OK;
+	const size_t N = (size_t)ctx->nmon, B = ctx->T + 1;
+	CU(ctx->m_pos.reserve(N * 3));
+	CU(ctx->sp_count.reserve(B));
+	CU(ctx->sp_start.reserve(B));
+	CU(ctx->sp_binof.reserve(N));
+	CU(ctx->sp_rank.reserve(N));
+	CU(ctx->sp_sorted.reserve(N));
+	CU(ctx->sp_xz.reserve(N));
+	CU(cudaMemsetAsync(ctx->sp_count.p, 0, B * 4, ctx->stream));
+	if (random_words)
+	{
+		CU(cudaMemcpyAsync(ctx->t_random.p, random_words, (size_t)ctx->ntowers * 8, cudaMemcpyHostToDevice, ctx->stream));
+	}
+	SpatialView S;
+	S.W = ctx->W;
+	S.H = ctx->H;
+	S.ox = ctx->ox;
+	S.oy = ctx->oy;
+	S.n = ctx->nmon;
+	S.pos = ctx->m_pos.p;
+	S.bin_count = ctx->sp_count.p;
+	S.bin_start = ctx->sp_start.p;
+	S.bin_of = ctx->sp_binof.p;
+	S.rank = ctx->sp_rank.p;
+	S.sorted_idx = ctx->sp_sorted.p;
+	S.sorted_xz = ctx->sp_xz.p;
+	TowersView Tw;
+	Tw.n = ctx->ntowers;
+	Tw.tile = ctx->t_tile.p;
+	Tw.damage = ctx->t_damage.p;
+	Tw.overTime = ctx->t_overTime.p;
+	Tw.firingPeriod = ctx->t_period.p;
+	Tw.manaCost = ctx->t_manaCost.p;
+	Tw.firingRange = ctx->t_range.p;
+	Tw.splashRadius = ctx->t_splash.p;
+	Tw.invalidClasses = ctx->t_invalid.p;
+	Tw.element = ctx->t_element.p;
+	Tw.bonus = ctx->t_bonus.p;
+	Tw.targeting = ctx->t_targeting.p;
+	Tw.firingDelay = ctx->t_delay.p;
+	Tw.mana = ctx->t_mana.p;
+	Tw.random_words = random_words ? ctx->t_random.p : nullptr;
+	Tw.target = ctx->t_target.p;
+	Tw.hits = ctx->t_hits.p;
+	TargetStats G;
+	G.monsterClass = ctx->m_has_class ? ctx->m_class.p : nullptr;
+	G.timeToArrive = ctx->m_tta.p;
+	G.life = ctx->m_life.p;
+	G.dot_duration = ctx->m_dot_duration.p;
+	G.dot_damage = ctx->m_dot_damage.p;
+	const int mb = (ctx->nmon + 255) / 256;
+	k_spatial_bin<<<mb, 256, 0, ctx->stream>>>(layers_view(ctx), monsters_view(ctx), S, gameTime);
+	LAUNCHED();
+	k_spatial_scan<<<1, 1024, 0, ctx->stream>>>(S);
+	LAUNCHED();
+	k_spatial_scatter<<<mb, 256, 0, ctx->stream>>>(S);
+	LAUNCHED();
+	k_towers_attack<<<(ctx->ntowers + 3) / 4, 128, 0, ctx->stream>>>(Tw, S, G, ctx->W, ctx->ox, ctx->oy);
+	LAUNCHED();
+	// MonsterComponent::affected(Fire / Water) is read live by the next steering tick (monsters.cpp:13-16, 92-95)
+	k_dots_flags<<<mb, 256, 0, ctx->stream>>>(dots_view(ctx));
+	LAUNCHED();
+	return MTD_OK;
+}
+
+extern "C" int mtd_towers_attack_dev(mtd_ctx *ctx, uint32_t gameTime, const uint64_t *random_words)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	return towers_attack_dev(ctx, gameTime, random_words);
+}
+
+extern "C" int mtd_towers_download(mtd_ctx *ctx, uint32_t *firingDelay, uint32_t *mana, int32_t *target, uint32_t *hits)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	const size_t N = (size_t)ctx->ntowers;
+	if (N == 0)
+		return MTD_OK;
+	if (firingDelay)
+		CU(cudaMemcpyAsync(firingDelay, ctx->t_delay.p, N * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (mana)
+		CU(cudaMemcpyAsync(mana, ctx->t_mana.p, N * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (target)
+		CU(cudaMemcpyAsync(target, ctx->t_target.p, N * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (hits)
+		CU(cudaMemcpyAsync(hits, ctx->t_hits.p, N * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	return sync_and_status(ctx);
 }

@@ -63,6 +63,13 @@ namespace mtd
 		asm volatile("fence.proxy.async;" ::: "memory");
 	}
 
+	// release / acquire at GPU scope for the message passing between workers, schedulers and offers (__threadfence() is a
+	// sequentially consistent fence plus an L1 invalidation: neither is needed, every shared word is read at L2)
+	__device__ __forceinline__ void fence_gpu()
+	{
+		asm volatile("fence.acq_rel.gpu;" ::: "memory");
+	}
+
 	__device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *tm, int x, int y, int z, uint64_t *bar)
 	{
 		asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(smem_u32(dst)), "l"(tm), "r"(x), "r"(y), "r"(z), "r"(smem_u32(bar))
@@ -79,6 +86,7 @@ namespace mtd
 	// developer probe (never in the shipped build): cycles per phase summed over all workers
 	// 0 wait for work, 1 consume key, 2 stage, 3 seed, 4 engine, 5 write back + offers computed, 6 offers sent + finish, 7 engine steps, 8 cells popped
 	__device__ unsigned long long g_async_timing[16];
+	__device__ unsigned long long g_async_sched_extra[4];
 #define MTD_ATICK(k)                                     \
 	do                                                   \
 	{                                                    \
@@ -107,13 +115,17 @@ namespace mtd
 
 	struct AsyncParams
 	{
-		uint32_t *inbox;     // [ctas][cap] item + 1, 0 = empty
+		unsigned long long *inbox; // [ctas][cap] key << 32 | (item + 1), 0 = empty
 		uint32_t *tail;      // [ctas * 32] (one 128-byte line per CTA) entries ever appended to the CTA's inbox
 		uint32_t *ctamin;    // [ctas] smallest key among the CTA's pending and in-flight items (MTD_INF: none)
 		uint32_t *ctl;       // ACTL_* words
 		uint32_t cap_mask;   // cap - 1 (cap is a power of two >= items per owner)
 		int ctas;
 		int use_tma;         // frames are staged by two bulk tensor copies (needs W % 4 == 0); else by cp.async rows / scalar loads
+		uint32_t *fly;       // [items] key an item is being visited at (MTD_INF: not in flight); read by the neighbours' schedulers
+		int nb_rule;         // 1: an item does not start while a neighbour tile is in flight or pending with a smaller key
+		uint32_t nb_margin;  // ... smaller by more than this
+		int depth;           // mailboxes per worker in use: 1 or 2
 		unsigned long long time_limit_ns;
 	};
 
@@ -133,7 +145,7 @@ namespace mtd
 			return false;
 		const int o = async_owner(A, layer, tx, ty);
 		const uint32_t pos = atomicAdd(A.tail + o * 32, 1u);
-		__stcg(A.inbox + (size_t)o * (A.cap_mask + 1u) + (pos & A.cap_mask), item + 1u);
+		__stcg(A.inbox + (size_t)o * (A.cap_mask + 1u) + (pos & A.cap_mask), ((unsigned long long)key << 32) | (unsigned long long)(item + 1u));
 		atomicMin(A.ctamin + o, key); // the owner's published wavefront position covers the offer before its scheduler has seen it
 		return true;
 	}
@@ -614,8 +626,8 @@ namespace mtd
 				if (lane == 0)
 				{
 					while ((it = slot[mine]) == SLOT_IDLE)
-						__nanosleep(20);
-					__threadfence(); // acquire: the scheduler consumed the item's key (and fenced) before it wrote the mailbox
+						__nanosleep(100);
+					fence_gpu(); // acquire: the scheduler consumed the item's key (and fenced) before it wrote the mailbox
 				}
 				it = __shfl_sync(0xFFFFFFFFu, it, 0);
 				if (it == SLOT_EXIT)
@@ -634,7 +646,7 @@ namespace mtd
 				const uint32_t noff = (uint32_t)__popc(__ballot_sync(0xFFFFFFFFu, have));
 				if (lane == 0 && noff != 1u)
 					atomicAdd(A.ctl + ACTL_OUTSTANDING, noff - 1u); // noff == 0: this visit's own count goes
-				__threadfence(); // my labels (and the count) are visible before a neighbour can be scheduled
+				fence_gpu(); // my labels (and the count) are visible before a neighbour can be scheduled
 				__syncwarp();
 				MTD_ATICK(5);
 				bool made = false;
@@ -646,6 +658,7 @@ namespace mtd
 				{
 					if (stale)
 						atomicSub(A.ctl + ACTL_OUTSTANDING, stale); // those items were pending already
+					__stcg(A.fly + it, MTD_INF);
 					slot[mine] = SLOT_IDLE;
 				}
 				take ^= 1u;
@@ -671,49 +684,81 @@ namespace mtd
 		// ---------------- scheduler warp ----------------
 		const int me = (int)blockIdx.x;
 		const uint32_t cap = A.cap_mask + 1u;
-		uint32_t *ring = A.inbox + (size_t)me * cap;
+		unsigned long long *ring = A.inbox + (size_t)me * cap;
 		uint32_t head = 0, pn = 0, polls = 0;
 		uint32_t fill = 0; // lane w < WORKERS: which of worker w's two mailboxes is filled next (the worker empties them in the same order)
 		const unsigned long long t0 = global_timer_ns();
 		bool stop = false;
 		while (!stop)
 		{
-			// everything the decision needs from global memory is requested up front: one L2 round trip per iteration
-			const uint32_t tail = __ldcg(A.tail + me * 32);
+			// everything the decision needs from global memory is requested at once: ONE L2 round trip per iteration
+			//   * the next 32 inbox entries past `head` (an entry is 0 until its store has landed: no tail needed),
+			//   * the keys of the pending entries (offers only ever lower them),
+			//   * every CTA's smallest key, the count of items alive, the abort flag
+			const unsigned long long e = __ldcg(ring + ((head + lane) & A.cap_mask));
 			const uint32_t outstanding = __ldcg(A.ctl + ACTL_OUTSTANDING);
 			const uint32_t aborted = __ldcg(A.ctl + ACTL_ABORT);
 			uint32_t others = MTD_INF;
 			for (int c = (int)lane; c < A.ctas; c += 32)
 				if (c != me)
 					others = min(others, __ldcg(A.ctamin + c));
-			// drain the inbox: entries [head, tail) in order, up to the first one whose store has not landed yet
-			while (head != tail && pn < (uint32_t)ASYNC_PCAP)
-			{
-				const uint32_t n = min(min(tail - head, 32u), (uint32_t)ASYNC_PCAP - pn);
-				uint32_t v = 0;
-				if (lane < n)
-					v = __ldcg(ring + ((head + lane) & A.cap_mask));
-				const uint32_t missing = __ballot_sync(0xFFFFFFFFu, lane < n && v == 0u);
-				const uint32_t got = missing ? (uint32_t)(__ffs(missing) - 1) : n;
-				if (lane < got)
-				{
-					__stcg(ring + ((head + lane) & A.cap_mask), 0u);
-					Q.pend_item[pn + lane] = v - 1u;
-				}
-				head += got;
-				pn += got;
-				if (got < n)
-					break;
-			}
-			__syncwarp();
-			// pending keys as they stand now (offers only lower them)
 			uint32_t mymin = MTD_INF;
 			for (uint32_t i = lane; i < pn; i += 32)
 			{
-				const uint32_t kk = __ldcg(P.key + Q.pend_item[i]);
-				Q.pend_key[i] = kk;
+				const uint32_t item = Q.pend_item[i];
+				uint32_t kk = __ldcg(P.key + item);
 				mymin = min(mymin, kk);
+				if (A.nb_rule)
+				{
+					// Tile-level Dijkstra order, locally: a visit that starts while a neighbour tile is still being relaxed, or
+					// waits with a smaller key, is repeated when that neighbour's offer arrives (tools/sim: 4.0 -> 2.7 visits
+					// per tile). Such an entry stays pending and is looked at again next iteration.
+					const uint32_t layer0 = (item / ntiles) * ntiles, tile = item - layer0;
+					const int tx = (int)(tile % (uint32_t)P.tilesX), ty = (int)(tile / (uint32_t)P.tilesX);
+					uint32_t nk = MTD_INF, nf = MTD_INF;
+					if (ty > 0)
+					{
+						nk = min(nk, __ldcg(P.key + item - P.tilesX));
+						nf = min(nf, __ldcg(A.fly + item - P.tilesX));
+					}
+					if (ty < P.tilesY - 1)
+					{
+						nk = min(nk, __ldcg(P.key + item + P.tilesX));
+						nf = min(nf, __ldcg(A.fly + item + P.tilesX));
+					}
+					if (tx > 0)
+					{
+						nk = min(nk, __ldcg(P.key + item - 1));
+						nf = min(nf, __ldcg(A.fly + item - 1));
+					}
+					if (tx < P.tilesX - 1)
+					{
+						nk = min(nk, __ldcg(P.key + item + 1));
+						nf = min(nf, __ldcg(A.fly + item + 1));
+					}
+					if (nf != MTD_INF || (nk != MTD_INF && nk + A.nb_margin < kk))
+						kk = MTD_INF; // hidden for this iteration (its real key is in mymin)
+				}
+				Q.pend_key[i] = kk;
 			}
+			// drain: entries in order up to the first empty one; each comes with the key it was offered at
+			{
+				const uint32_t room = (uint32_t)ASYNC_PCAP - pn;
+				const uint32_t missing = __ballot_sync(0xFFFFFFFFu, e == 0ull);
+				uint32_t got = missing ? (uint32_t)(__ffs(missing) - 1) : 32u;
+				got = min(got, room);
+				if (lane < got)
+				{
+					__stcg(ring + ((head + lane) & A.cap_mask), 0ull);
+					const uint32_t kk = (uint32_t)(e >> 32);
+					Q.pend_item[pn + lane] = (uint32_t)(e & 0xFFFFFFFFull) - 1u;
+					Q.pend_key[pn + lane] = A.nb_rule ? MTD_INF : kk; // with the neighbour rule: judged next iteration, with its neighbours' state
+					mymin = min(mymin, kk);
+				}
+				head += got;
+				pn += got;
+			}
+			__syncwarp();
 			// mailboxes: lane l looks at slot l (worker l / 2)
 			uint32_t cur = slot[lane];
 			if (cur < SLOT_EXIT)
@@ -729,10 +774,14 @@ namespace mtd
 			{
 				const uint32_t b0 = (busy_slots >> (2u * (lane & 15u))) & 3u;
 				idle_w = __ballot_sync(0xFFFFFFFFu, lane < ASYNC_WORKERS && b0 == 0u);
-				half_w = __ballot_sync(0xFFFFFFFFu, lane < ASYNC_WORKERS && (b0 == 1u || b0 == 2u));
+				half_w = __ballot_sync(0xFFFFFFFFu, lane < ASYNC_WORKERS && (b0 == 1u || b0 == 2u) && A.depth > 1);
 			}
 			__syncwarp();
 			uint32_t nasg = 0;
+#ifdef MTD_TIMING
+			const uint32_t idle_before__ = (uint32_t)__popc(idle_w);
+			uint32_t blocked__ = 0;
+#endif
 			while ((idle_w | half_w) != 0u && pn != 0u)
 			{
 				uint32_t bk = MTD_INF;
@@ -740,7 +789,12 @@ namespace mtd
 					bk = min(bk, Q.pend_key[i]);
 				const uint32_t kmin = warp_redux_min(bk);
 				if (kmin >= kthr) // also MTD_INF: nothing selectable
+				{
+#ifdef MTD_TIMING
+					blocked__ = kmin != MTD_INF ? 1u : 0u;
+#endif
 					break;
+				}
 				uint32_t bi = MTD_INF;
 				for (uint32_t i = lane; i < pn; i += 32)
 					if (Q.pend_key[i] == kmin)
@@ -782,14 +836,51 @@ namespace mtd
 			{
 				// consume the offers of everything handed out (whoever made one wrote its labels first), THEN ring the mailboxes
 				if (lane < nasg)
+				{
+					__stcg(A.fly + Q.asg_item[lane], Q.ifkey[Q.asg_slot[lane]]);
 					atomicExch(P.key + Q.asg_item[lane], MTD_INF);
-				__threadfence();
+				}
+				fence_gpu();
 				__syncwarp();
 				if (lane < nasg)
 					slot[Q.asg_slot[lane]] = Q.asg_item[lane];
 				__syncwarp();
 			}
 			polls++;
+#ifdef MTD_TIMING
+			{
+				// pending entries that could run right now (inside the window, tile not in flight) but found no free mailbox here
+				uint32_t sur = 0, hid = 0, far = 0;
+				for (uint32_t i = lane; i < pn; i += 32)
+				{
+					const uint32_t kk = Q.pend_key[i];
+					sur += kk < kthr ? 1u : 0u;
+					hid += kk == MTD_INF ? 1u : 0u;
+					far += (kk != MTD_INF && kk >= kthr) ? 1u : 0u;
+				}
+				sur = __reduce_add_sync(0xFFFFFFFFu, sur);
+				hid = __reduce_add_sync(0xFFFFFFFFu, hid);
+				far = __reduce_add_sync(0xFFFFFFFFu, far);
+				if (lane == 0)
+				{
+					atomicAdd(&g_async_timing[14], (unsigned long long)sur);
+					atomicAdd(&g_async_timing[15], (unsigned long long)far);
+					atomicAdd(&g_async_timing[8 + 0], 0ull);
+					atomicAdd(&g_async_sched_extra[0], (unsigned long long)hid);
+					atomicAdd(&g_async_sched_extra[1], (unsigned long long)nasg);
+				}
+			}
+			if (lane == 0)
+			{
+				// 9 iterations, 10 idle workers seen, 11 idle workers left without an item, 12 ... because the window held the rest back, 13 pending entries seen
+				const uint32_t idle_after__ = (uint32_t)__popc(idle_w);
+				atomicAdd(&g_async_timing[9], 1ull);
+				atomicAdd(&g_async_timing[10], (unsigned long long)idle_before__);
+				atomicAdd(&g_async_timing[11], (unsigned long long)idle_after__);
+				atomicAdd(&g_async_timing[12], (unsigned long long)(blocked__ ? idle_after__ : 0u));
+				atomicAdd(&g_async_timing[13], (unsigned long long)(pn + nasg));
+			}
+#endif
 			if (aborted || outstanding == 0u)
 				stop = true;
 			else if (global_timer_ns() - t0 > A.time_limit_ns)

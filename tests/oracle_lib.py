@@ -62,6 +62,11 @@ class MoProcedural(C.Structure):
     _fields_ = [("off_x", C.c_float), ("off_y", C.c_float), ("seeds", C.c_uint32 * 5), ("fractal_bounding", C.c_float)]
 
 
+class MoTowers(C.Structure):
+    _fields_ = [("n", C.c_int)] + [(k, C.c_void_p) for k in ("tile", "damage", "overTime", "firingPeriod", "manaCost", "firingRange", "splashRadius", "invalidClasses", "element", "bonus", "targeting",
+                                                              "firingDelay", "mana", "random_words", "target_out", "hits_out")]
+
+
 class MoMonsters(C.Structure):
     _fields_ = [
         ("n", C.c_int),
@@ -238,6 +243,31 @@ class Oracle:
         vp = lambda a: None if a is None else C.c_void_p(a.ctypes.data)
         self.L.mo_monsters_dots_tick(n, vp(duration), vp(damage), vp(resist), vp(life), vp(money), vp(alive), C.byref(ms), C.byref(kl))
         return ms.value, kl.value
+
+    TOWER_DTYPES = dict(firingRange=np.float32, splashRadius=np.float32, invalidClasses=np.uint8, element=np.uint8, bonus=np.uint8, targeting=np.uint8)
+
+    def towers_attack(self, W, H, ox, oy, elev, game_time, tw, mon, monster_class, life, dot_duration, dot_damage, random_words=None):
+        """one "attacks" tick (sources/game/attacks.cpp:132-160). tw: dict of tower arrays (firingDelay and mana are updated in
+        place), mon: monster SoA dict, dots uint32 [5][n] updated in place. Returns (target per tower, hits per tower)."""
+        g = self.grid(W, H, ox, oy, elev, None)
+        n = len(tw["tile"])
+        for k in tw:
+            want = self.TOWER_DTYPES.get(k, np.uint32)
+            assert tw[k].dtype == want and tw[k].flags["C_CONTIGUOUS"], k
+        target = np.full(n, -1, np.int32)
+        hits = np.zeros(n, np.uint32)
+        rw = None if random_words is None else np.ascontiguousarray(random_words, np.uint64)
+        t = MoTowers()
+        t.n = n
+        for k in ("tile", "damage", "overTime", "firingPeriod", "manaCost", "firingRange", "splashRadius", "invalidClasses", "element", "bonus", "targeting", "firingDelay", "mana"):
+            setattr(t, k, tw[k].ctypes.data)
+        t.random_words = None if rw is None else rw.ctypes.data
+        t.target_out = target.ctypes.data
+        t.hits_out = hits.ctypes.data
+        vp = lambda a: None if a is None else C.c_void_p(a.ctypes.data)
+        self.L.mo_towers_attack(C.byref(g), C.c_uint32(game_time), C.byref(t), len(mon["tileStart"]), vp(mon["tileStart"]), vp(mon["tileEnd"]), vp(mon["timeStart"]), vp(mon["timeEnd"]), vp(mon["alive"]),
+                                vp(monster_class), vp(mon["timeToArrive"]), vp(life), vp(dot_duration), vp(dot_damage))
+        return target, hits
 
     def monster_spawn(self, wview, spawner, game_time, speed):
         out = np.zeros(3, np.uint32)

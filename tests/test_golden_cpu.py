@@ -98,3 +98,59 @@ def test_oracle_reproduces_game_events_golden(oracle):
     for k in ("tile", "tileStart", "tileEnd", "timeStart", "timeEnd", "bits", "alive"):
         assert np.array_equal(og.a[k], g["mon_" + k]), k
     assert np.array_equal(og.w["agg"], g["agg"]) and np.array_equal(og.w["full_distance"], g["full_distance"])
+
+
+def _towers(rows):
+    """rows: list of dicts with the reference's component fields; defaults are DamageComponent / AttackComponent's (game.h:226-245)"""
+    base = dict(tile=0, damage=0, overTime=0, firingPeriod=30, firingRange=5.0, splashRadius=0.0, manaCost=12, invalidClasses=0, element=0, bonus=0, targeting=0, firingDelay=0, mana=0)
+    dt = dict(firingRange=np.float32, splashRadius=np.float32, invalidClasses=np.uint8, element=np.uint8, bonus=np.uint8, targeting=np.uint8)
+    return {k: np.array([dict(base, **r)[k] for r in rows], dt.get(k, np.uint32)) for k in base}
+
+
+def test_towers_attack_hand_checked_cases(oracle):
+    """"attacks" (sources/game/attacks.cpp:132-216) on an 11 x 11 flat grid (offset 5: tile (x, y) sits at world (x-5, y-5)),
+    five standing monsters, ten towers at the origin; every expectation below is worked out by hand from the source"""
+    W = H = 11
+    T = lambda x, z: (z + 5) * W + (x + 5)  # noqa: E731
+    elev = np.zeros(W * H, np.int16)
+    mt = np.array([T(2, 0), T(0, 1), T(1, 1), T(2, 1), T(-1, 0)], np.uint32)
+    n = len(mt)
+    mon = dict(tileStart=mt.copy(), tileEnd=mt.copy(), timeStart=np.zeros(n, np.uint32), timeEnd=np.zeros(n, np.uint32), alive=np.ones(n, np.uint8),
+               timeToArrive=np.array([100, 90, 90, 10, 5], np.uint32))
+    life = np.array([50, 70, 70, 5, 1], np.int64)
+    cls = np.array([0, 0, 0, 0, 1], np.uint8)  # monster 4 is a flier
+    o = T(0, 0)
+    tw = _towers([
+        dict(tile=o, firingRange=2, targeting=1, invalidClasses=1, damage=7, manaCost=0),                      # A Front, no fliers: tta tie 90 -> lowest index 1
+        dict(tile=o, firingRange=2, targeting=3, damage=1, manaCost=0),                                        # B Closest: d2 = 1 for monsters 1 and 4 -> 1
+        dict(tile=o, firingRange=2, targeting=5, element=1, damage=16, splashRadius=1, manaCost=0),            # C Strongest (life 70 tie -> 1), fire, splash 1 hits 1 and 2
+        dict(tile=o, firingRange=2, firingDelay=3),                                                            # D waits
+        dict(tile=o, firingRange=2, targeting=1, manaCost=12, mana=5),                                         # E no mana
+        dict(tile=o, firingRange=2, targeting=6, bonus=1, damage=4, manaCost=12, mana=30),                     # F Weakest -> 4, damage x2, mana cost x2
+        dict(tile=o, firingRange=2, targeting=2, damage=1, manaCost=0),                                        # G Back: largest tta -> 0
+        dict(tile=T(-5, -5), firingRange=0.5, targeting=1, damage=1, manaCost=0),                              # H nobody in range
+        dict(tile=o, firingRange=2, targeting=4, bonus=3, damage=1, manaCost=0),                               # I range 2 + 4: Farthest -> 3 (d2 = 5)
+        dict(tile=o, firingRange=2, targeting=1, bonus=2, damage=1, manaCost=0, firingPeriod=31),              # J Front, fliers allowed -> 4; firing rate: period 31 / 2 = 15
+    ])
+    dur = np.zeros((5, n), np.uint32)
+    dmg = np.zeros((5, n), np.uint32)
+    target, hits = oracle.towers_attack(W, H, 5, 5, elev, 0, tw, mon, cls, life, dur, dmg)
+    assert target.tolist() == [1, 1, 1, -1, -1, 4, 0, -1, 3, 4]
+    assert hits.tolist() == [1, 1, 2, 0, 0, 1, 1, 0, 1, 1]
+    assert tw["firingDelay"].tolist() == [30, 30, 30, 2, 0, 30, 30, 0, 30, 15]
+    assert tw["mana"].tolist() == [0, 0, 0, 0, 5, 6, 0, 0, 0, 0]
+    want = np.zeros((5, n), np.uint32)
+    want[0, 1] = 7 + 1      # A, B
+    want[0, 4] = 8 + 1      # F, J (Front with fliers allowed: tta 5)
+    want[0, 0] = 1          # G
+    want[0, 3] = 1          # I
+    want[1, 1] = want[1, 2] = 48  # C: fire, damage x3
+    assert np.array_equal(dmg, want)
+    wd = np.zeros((5, n), np.uint32)
+    wd[1, 1] = wd[1, 2] = 80  # sqrt(16) * 20
+    assert np.array_equal(dur, wd)
+    # dead monsters are not in the index; Random takes candidate number word % count in index order
+    mon["alive"][1] = 0
+    tw2 = _towers([dict(tile=o, firingRange=2, targeting=0, damage=1, manaCost=0), dict(tile=o, firingRange=2, targeting=3, damage=1, manaCost=0)])
+    target, hits = oracle.towers_attack(W, H, 5, 5, elev, 0, tw2, mon, cls, life, dur, dmg, random_words=np.array([5, 0], np.uint64))
+    assert target.tolist() == [4, 4]  # candidates 0, 2, 4: 5 % 3 = 2 -> monster 4; closest now monster 4 (d2 = 1)

@@ -231,7 +231,7 @@ def test_dataflow_scheduler_really_runs_and_windows_agree(ctx, oracle):
         assert st["dataflow"] and st["rounds"] == 0 and st["visits"] >= ((W + 31) // 32) * ((H + 31) // 32) // 2
         assert np.array_equal(dist, do), (delta, diff_report(dist, do, W))
         assert np.array_equal(tiles, to), delta
-    ctx.debug_set(ctx.DEBUG_ASYNC_DELTA, 32768)
+    ctx.debug_set(ctx.DEBUG_ASYNC_DELTA, 65536)
 
 
 def test_c5_full_size_against_reference_golden_and_oracle(tctx, oracle):
@@ -1035,3 +1035,77 @@ def test_sdf_and_game_events_against_committed_golden(ctx):
     w = ctx.waypoints_update(m["wp_tiles"][0], cap=4096)
     assert np.array_equal(w["agg"], g["agg"]) and np.array_equal(w["full_distance"], g["full_distance"])
     assert [int(w["dist"][l].astype(np.uint64).sum() & 0xFFFFFFFF) for l in range(4)] == list(g["dist_sum"])
+
+
+# ---------------------------------------------------------------------------------------------------
+# monster spatial index + tower attack pass
+# ---------------------------------------------------------------------------------------------------
+def _random_towers(rng, n, flags, W):
+    open_tiles = np.flatnonzero((flags & synth.FLAG_INVALID) == 0)
+    tw = dict(
+        tile=rng.choice(open_tiles, n).astype(np.uint32),
+        damage=rng.integers(1, 400, n).astype(np.uint32),
+        overTime=np.zeros(n, np.uint32),
+        firingPeriod=rng.integers(1, 40, n).astype(np.uint32),
+        firingRange=rng.choice(np.array([0.5, 1.0, 2.0, 3.5, 5.0, 9.0], np.float32), n),
+        splashRadius=rng.choice(np.array([0.0, 0.0, 1.0, 2.5], np.float32), n),
+        manaCost=rng.choice(np.array([0, 5, 12, 40], np.uint32), n),
+        invalidClasses=rng.choice(np.array([0, 0, 1, 2, 3], np.uint8), n),
+        element=rng.integers(0, 5, n).astype(np.uint8),
+        bonus=rng.integers(0, 7, n).astype(np.uint8),
+        targeting=rng.integers(0, 7, n).astype(np.uint8),
+        firingDelay=rng.integers(0, 4, n).astype(np.uint32),
+        mana=rng.integers(0, 400, n).astype(np.uint32),
+    )
+    tw["overTime"][tw["element"] == 0] = rng.integers(0, 30, int((tw["element"] == 0).sum())).astype(np.uint32)
+    return tw
+
+
+@pytest.mark.parametrize("nmon,ntow", [(3000, 257), (60000, 1000)])
+def test_towers_attack_pass_matches_oracle(ctx, oracle, nmon, ntow):
+    """spatial rebuild + attacks (sources/game/spatial.cpp:24-34, attacks.cpp:132-160) on moving monsters, interleaved with
+    steering ticks: picked targets, hit counts, tower delays / mana and the monsters' damage-over-time state, bit for bit"""
+    from mazetd_b200 import game_events
+
+    o = oracle.mapgen(KAT_SEED[0] + 3, KAT_SEED[1])
+    W = H = 101
+    ctx.grid_upload(W, H, o["elev"], o["flags"], 50, 50)
+    ctx.waypoints_update(o["wp_tiles"])
+    wv = oracle.waypoints_view(W, H, o["elev"], o["flags"], o["wp_tiles"], o["tiles"], o["dist"], 50, 50)
+    sp = int(o["agg"][2])
+    path = o["fullpath"][sp][: int(o["fullpath_len"][sp])]
+    rng = np.random.default_rng(nmon)
+    a = game_events.initial_monsters(nmon, path, o["wp_tiles"], ctx.waypoints_find, speed_range=(0.05, 0.2))
+    a["alive"] = (rng.integers(0, 25, nmon) > 0).astype(np.uint8)
+    # distinct picker values wherever the reference's own order would decide (ties go to the lowest index on both sides anyway)
+    life = rng.integers(1, 1 << 40, nmon).astype(np.int64)
+    cls = rng.choice(np.array([0, 0, 0, 1, 2], np.uint8), nmon)
+    dur = np.zeros((5, nmon), np.uint32)
+    dmg = np.zeros((5, nmon), np.uint32)
+    tw = _random_towers(rng, ntow, o["flags"], W)
+    ctx.monsters_upload(a)
+    ctx.monsters_dots_upload(dur, dmg, life)
+    ctx.monsters_class_upload(cls)
+    ctx.towers_upload(tw)
+    a["dotflags"] = np.zeros(nmon, np.uint8)
+    fired = 0
+    for t in range(1, 13):
+        ctx.monsters_tick(t)
+        oracle.monsters_tick(wv, t, a)
+        words = rng.integers(0, 1 << 62, ntow).astype(np.uint64)
+        ctx.towers_attack_dev(t, words)
+        target, hits = oracle.towers_attack(W, H, 50, 50, o["elev"], t, tw, a, cls, life, dur, dmg, random_words=words)
+        got = ctx.towers_download()
+        assert np.array_equal(got["target"], target), (t, np.flatnonzero(got["target"] != target)[:5], tw["targeting"][np.flatnonzero(got["target"] != target)[:5]])
+        assert np.array_equal(got["hits"], hits), t
+        assert np.array_equal(got["firingDelay"], tw["firingDelay"]) and np.array_equal(got["mana"], tw["mana"]), t
+        fired += int((target >= 0).sum())
+        d = ctx.monsters_dots_download()
+        assert np.array_equal(d["damage"], dmg) and np.array_equal(d["duration"], dur), t
+        a["dotflags"][:] = (dmg[1] > 0).astype(np.uint8) | ((dmg[2] > 0).astype(np.uint8) << 1)
+        if t % 4 == 0:
+            # the damage pass of the same tick, then steering reads the refreshed fire / water bits
+            ctx.monsters_dots_tick()
+            oracle.monsters_dots_tick(dur, dmg, life, a["alive"])
+    assert fired > ntow // 4  # towers really fired
+    assert (hits > 1).any()  # and splashes hit several monsters

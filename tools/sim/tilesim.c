@@ -203,10 +203,106 @@ static int tor_engine(uint32_t G[RW][RW], int *conv)
 }
 int tor_order[4] = { 0, 1, 2, 3 };
 
+// ---- column-owner engine: lane c owns column c of the tile; per step every lane pops ONE pending cell of its column,
+// relaxes up / down itself and hands the left / right candidates to the neighbour lanes (no atomics, no shared queue).
+// variant 0: lowest pending row; 1: elevator (continue in the current direction); 2: pending cell with the smallest label;
+// 3: as 2 but only cells below (warp-min pending label + delta) are popped
+static uint64_t col_steps[8], col_pops[8];
+static void col_engine(uint32_t Fin[RW][RW], int variant, uint32_t delta)
+{
+	static uint32_t G[RW][RW];
+	uint32_t pend[TS + 2];
+	int dir[TS + 2], last[TS + 2];
+	memcpy(G, Fin, sizeof(G));
+	memset(pend, 0, sizeof(pend));
+	for (int c = 0; c < TS + 2; c++) { dir[c] = 1; last[c] = 0; }
+	// seeds as in wavefront_steps
+	for (int i = 1; i <= TS; i++)
+	{
+		if (!FB[1][i] && G[0][i] < INF && G[0][i] + FD[0][i] < G[1][i]) { G[1][i] = G[0][i] + FD[0][i]; pend[i] |= 1u << 0; }
+		if (!FB[TS][i] && G[RW - 1][i] < INF && G[RW - 1][i] + FD[TS][i] < G[TS][i]) { G[TS][i] = G[RW - 1][i] + FD[TS][i]; pend[i] |= 1u << (TS - 1); }
+		if (!FB[i][1] && G[i][0] < INF && G[i][0] + FR[i][0] < G[i][1]) { G[i][1] = G[i][0] + FR[i][0]; pend[1] |= 1u << (i - 1); }
+		if (!FB[i][TS] && G[i][RW - 1] < INF && G[i][RW - 1] + FR[i][TS] < G[i][TS]) { G[i][TS] = G[i][RW - 1] + FR[i][TS]; pend[TS] |= 1u << (i - 1); }
+	}
+	for (int y = 1; y <= TS; y++) for (int x = 1; x <= TS; x++) if (!FB[y][x] && G[y][x] < INF)
+	{
+		int imp = 0;
+		if (y > 1 && !FB[y - 1][x] && G[y][x] + FD[y - 1][x] < G[y - 1][x]) imp = 1;
+		if (y < TS && !FB[y + 1][x] && G[y][x] + FD[y][x] < G[y + 1][x]) imp = 1;
+		if (x > 1 && !FB[y][x - 1] && G[y][x] + FR[y][x - 1] < G[y][x - 1]) imp = 1;
+		if (x < TS && !FB[y][x + 1] && G[y][x] + FR[y][x] < G[y][x + 1]) imp = 1;
+		if (imp) pend[x] |= 1u << (y - 1);
+	}
+	for (;;)
+	{
+		int any = 0;
+		for (int c = 1; c <= TS; c++) any |= pend[c] != 0;
+		if (!any) break;
+		col_steps[variant]++;
+		uint32_t thr = 0xFFFFFFFFu;
+		if (variant == 3)
+		{
+			uint32_t m = INF;
+			for (int c = 1; c <= TS; c++) for (int r = 0; r < TS; r++) if ((pend[c] >> r) & 1u) if (G[r + 1][c] < m) m = G[r + 1][c];
+			thr = m + delta;
+		}
+		int pr[TS + 2]; uint32_t pd[TS + 2];
+		for (int c = 1; c <= TS; c++)
+		{
+			pr[c] = -1;
+			if (!pend[c]) continue;
+			int r = -1;
+			if (variant == 0) r = __builtin_ctz(pend[c]);
+			else if (variant == 1 || variant >= 4)
+			{
+				// next pending row at or beyond `last` in direction dir, else turn round
+				for (int pass = 0; pass < 2 && r < 0; pass++)
+				{
+					if (dir[c] > 0) { uint32_t m = pend[c] & ~((last[c] >= 32 ? 0xFFFFFFFFu : (1u << last[c])) - 1u); if (last[c] < 32 && m) r = __builtin_ctz(m); else dir[c] = -1; }
+					else { uint32_t m = pend[c] & ((last[c] >= 31 ? 0xFFFFFFFFu : ((2u << last[c]) - 1u))); if (m) r = 31 - __builtin_clz(m); else dir[c] = 1; }
+				}
+				if (r < 0) r = __builtin_ctz(pend[c]);
+			}
+			else
+			{
+				uint32_t best = 0xFFFFFFFFu;
+				for (int q = 0; q < TS; q++) if ((pend[c] >> q) & 1u) if (G[q + 1][c] < best) { best = G[q + 1][c]; r = q; }
+				if (variant == 3 && best >= thr) r = -1;
+			}
+			if (r < 0) continue;
+			pr[c] = r; pd[c] = G[r + 1][c];
+			if (variant < 4) { last[c] = r; pend[c] &= ~(1u << r); col_pops[variant]++; }
+		}
+		if (variant >= 4)
+		{
+			uint32_t m = 0xFFFFFFFFu;
+			for (int c = 1; c <= TS; c++) if (pr[c] >= 0 && pd[c] < m) m = pd[c];
+			for (int c = 1; c <= TS; c++)
+			{
+				if (pr[c] < 0) continue;
+				if (pd[c] - m >= delta) { pr[c] = -1; /* candidate stays pending; look at another one next step */ last[c] = (last[c] + dir[c]) & 31; continue; }
+				last[c] = pr[c]; pend[c] &= ~(1u << pr[c]); col_pops[variant]++;
+			}
+		}
+		// relax: vertical by the owner, lateral handed to the neighbours (applied after all lanes popped: same step)
+		for (int c = 1; c <= TS; c++)
+		{
+			if (pr[c] < 0) continue;
+			int y = pr[c] + 1; uint32_t v = pd[c];
+			if (y > 1 && !FB[y - 1][c] && v + FD[y - 1][c] < G[y - 1][c]) { G[y - 1][c] = v + FD[y - 1][c]; pend[c] |= 1u << (y - 2); }
+			if (y < TS && !FB[y + 1][c] && v + FD[y][c] < G[y + 1][c]) { G[y + 1][c] = v + FD[y][c]; pend[c] |= 1u << y; }
+			if (c > 1 && !FB[y][c - 1] && v + FR[y][c - 1] < G[y][c - 1]) { G[y][c - 1] = v + FR[y][c - 1]; pend[c - 1] |= 1u << (y - 1); }
+			if (c < TS && !FB[y][c + 1] && v + FR[y][c] < G[y][c + 1]) { G[y][c + 1] = v + FR[y][c]; pend[c + 1] |= 1u << (y - 1); }
+		}
+	}
+	for (int y = 1; y <= TS; y++) for (int x = 1; x <= TS; x++) if (!FB[y][x] && G[y][x] != FCHK[y][x]) { printf("column engine mismatch v%d\n", variant); exit(1); }
+}
+
 static uint32_t *key; // per tile offered key
 static int first_quadrant_hint = -1;
 
 // visits tile (tx,ty); returns offers to 4 neighbours in off[4] (INF = none): up, down, left, right
+static uint32_t RES[TS][TS]; static int defer_wb = 0; static int last_steps = 0;
 static void visit(int tx, int ty, uint32_t off[4], int engine_stats)
 {
 	int gx0 = tx * TS - 1, gy0 = ty * TS - 1;
@@ -241,6 +337,9 @@ static void visit(int tx, int ty, uint32_t off[4], int engine_stats)
 		tot_passes += np; tot_conv += conv; hist_passes[np < 127 ? np : 127]++;
 		for (int y = 1; y <= TS; y++) for (int x = 1; x <= TS; x++) G3[0][0] = 0;
 		memcpy(FCHK, G3, sizeof(G3));
+		static uint32_t G4[RW][RW];
+		for (int v = 0; v < 4; v++) { memcpy(G4, F, sizeof(F)); col_engine(G4, v, 1024); }
+		memcpy(G4, F, sizeof(F)); col_engine(G4, 4, 1024); memcpy(G4, F, sizeof(F)); col_engine(G4, 5, 2048); memcpy(G4, F, sizeof(F)); col_engine(G4, 6, 4096); memcpy(G4, F, sizeof(F)); col_engine(G4, 7, 8192);
 	}
 	// sweep engine (this one produces the result)
 	int nosw = 0, ns = 0, q = 0, nch = 0;
@@ -251,8 +350,9 @@ static void visit(int tx, int ty, uint32_t off[4], int engine_stats)
 	}
 	tot_sweeps += ns; tot_changed_sweeps += nch; hist_sweeps[ns < 63 ? ns : 63]++;
 	if (engine_stats) for (int y = 1; y <= TS; y++) for (int x = 1; x <= TS; x++) if (!FB[y][x] && F[y][x] != FCHK[y][x]) { printf("toroidal engine mismatch\n"); exit(1); }
+	if (defer_wb) { uint64_t pp = 0; static uint32_t G5[RW][RW]; memcpy(G5, F, sizeof(F)); (void)pp; for (int y = 1; y <= TS; y++) for (int x = 1; x <= TS; x++) RES[y - 1][x - 1] = F[y][x]; last_steps = ns; }
 	// write back
-	for (int y = 1; y <= TS; y++) for (int x = 1; x <= TS; x++)
+	if (!defer_wb) for (int y = 1; y <= TS; y++) for (int x = 1; x <= TS; x++)
 	{
 		int gx = gx0 + x, gy = gy0 + y;
 		if (gx >= W || gy >= H) continue;
@@ -338,6 +438,77 @@ int main(int argc, char **argv)
 			}
 		}
 	}
+
+	else if (mode == 2)
+	{
+		// event-driven: P workers, a visit stages at its start and writes back / offers at its end (duration in ticks grows
+		// with the work it did); policy bit 0: window; bit 1: a tile does not start while a neighbour tile is in flight or
+		// pending with a smaller key (margin)
+		int P = argc > 8 ? atoi(argv[8]) : 37;
+		int policy = argc > 9 ? atoi(argv[9]) : 1;
+		uint32_t margin = argc > 10 ? (uint32_t)atoi(argv[10]) : 0;
+		typedef struct { int tile, end; uint32_t key; uint32_t off[4]; uint32_t res[TS][TS]; } Job;
+		Job *jobs = calloc(P, sizeof(Job));
+		for (int w = 0; w < P; w++) jobs[w].tile = -1;
+		uint8_t *busy = calloc(NT, 1);
+		int now = 0; uint64_t busy_ticks = 0; int inflight = 0;
+		defer_wb = 1;
+		for (;;)
+		{
+			// finish
+			for (int w = 0; w < P; w++) if (jobs[w].tile >= 0 && jobs[w].end <= now)
+			{
+				int t = jobs[w].tile, tx = t % TX, ty = t / TX;
+				for (int y = 0; y < TS; y++) for (int x = 0; x < TS; x++)
+				{
+					int gx = tx * TS + x, gy = ty * TS + y; if (gx >= W || gy >= H) continue;
+					size_t i = (size_t)gy * W + gx; if (!blocked[i] && jobs[w].res[y][x] < d[i]) d[i] = jobs[w].res[y][x];
+				}
+				uint32_t *off = jobs[w].off;
+				if (off[0] < INF && ty > 0 && off[0] < key[t - TX]) key[t - TX] = off[0];
+				if (off[1] < INF && ty + 1 < TY && off[1] < key[t + TX]) key[t + TX] = off[1];
+				if (off[2] < INF && tx > 0 && off[2] < key[t - 1]) key[t - 1] = off[2];
+				if (off[3] < INF && tx + 1 < TX && off[3] < key[t + 1]) key[t + 1] = off[3];
+				busy[t] = 0; jobs[w].tile = -1; inflight--;
+			}
+			// watermark
+			uint32_t wm = INF; int npend = 0;
+			for (int t = 0; t < NT; t++) if (key[t] < INF) { npend++; if (key[t] < wm) wm = key[t]; }
+			for (int w = 0; w < P; w++) if (jobs[w].tile >= 0 && jobs[w].key < wm) wm = jobs[w].key;
+			if (npend == 0 && inflight == 0) break;
+			// assign
+			for (int w = 0; w < P; w++) if (jobs[w].tile < 0)
+			{
+				uint32_t bk = INF; int bt = -1;
+				for (int t = 0; t < NT; t++)
+				{
+					if (key[t] >= INF || busy[t] || key[t] >= bk) continue;
+					if ((policy & 1) && key[t] - wm >= window) continue;
+					if (policy & 2)
+					{
+						int tx = t % TX, ty = t / TX, ok = 1;
+						int nb[4] = { ty > 0 ? t - TX : -1, ty + 1 < TY ? t + TX : -1, tx > 0 ? t - 1 : -1, tx + 1 < TX ? t + 1 : -1 };
+						for (int q = 0; q < 4 && ok; q++) if (nb[q] >= 0)
+						{
+							if (busy[nb[q]]) ok = 0;
+							else if (key[nb[q]] < INF && key[nb[q]] + margin < key[t]) ok = 0;
+						}
+						if (!ok) continue;
+					}
+					bk = key[t]; bt = t;
+				}
+				if (bt < 0) break;
+				jobs[w].tile = bt; jobs[w].key = key[bt]; key[bt] = INF; busy[bt] = 1; inflight++;
+				visit(bt % TX, bt / TX, jobs[w].off, 0);
+				memcpy(jobs[w].res, RES, sizeof(RES));
+				jobs[w].end = now + 6 + last_steps; // ticks: fixed part + engine
+				rounds++;
+			}
+			busy_ticks += inflight;
+			now++;
+		}
+		printf("async P=%d policy=%d margin=%u: makespan %d ticks, avg busy workers %.1f\n", P, policy, margin, now, (double)busy_ticks / (now ? now : 1));
+	}
 	else
 	{
 		for (;;)
@@ -359,6 +530,7 @@ int main(int argc, char **argv)
 	printf("sweep engine: %.2f sweeps/visit (%.2f changing); wavefront d1024: %.1f steps/visit, %.0f pops/visit; d255: %.1f steps/visit\n", (double)tot_sweeps / tot_visits, (double)tot_changed_sweeps / tot_visits, (double)tot_steps1024 / tot_visits, (double)tot_cells_popped / tot_visits, (double)tot_steps255 / tot_visits);
 	printf("toroidal engine: %.2f passes/visit, %.2f layout conversions/visit\n passes hist:", (double)tot_passes / tot_visits, (double)tot_conv / tot_visits);
 	for (int i = 0; i < 128; i++) if (hist_passes[i]) printf(" %d:%llu", i, (unsigned long long)hist_passes[i]); printf("\n");
+	for (int v = 0; v < 8; v++) printf("column engine v%d: %.1f steps/visit, %.0f pops/visit\n", v, (double)col_steps[v] / tot_visits, (double)col_pops[v] / tot_visits);
 	printf("sweeps hist:"); for (int i = 0; i < 64; i++) if (hist_sweeps[i]) printf(" %d:%llu", i, (unsigned long long)hist_sweeps[i]); printf("\n");
 	return 0;
 }
