@@ -604,6 +604,49 @@ def leg_c1_c3(ctx, args, cpu):
     return out
 
 
+def leg_c3_sharded(ctx, dev, rank, world, args):
+    """C3 at N > 1: every rank holds a replica of the 101x101 map and 1/N of the monsters; per trial one
+    all-reduce of the verdict, per accepted event one broadcast of the 326 KB of layers from rank 0"""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from mazetd_b200 import game_events, sharded_game
+
+    s1, s2 = KAT_SEED
+    g = ctx.mapgen_batch(s1, s2, 0, 1, cap=4096)
+    elev, flags, wp = g["elev"][0], g["flags"][0], g["wp_tiles"][0]
+    sp = int(g["agg"][0][2])
+    path = g["fullpath"][0][sp][: int(g["fullpath_len"][0][sp])]
+    ctx.grid_upload(W, H, elev, flags, 50, 50)
+    ctx.waypoints_update_dev(wp)
+    nevents, nmon = min(args.c3_events, 2000), args.c3_monsters
+    mon = game_events.initial_monsters(nmon, path, wp, ctx.waypoints_find, speed_range=(0.03, 0.06))
+    mine = sharded_game.shard_monsters(mon, rank, world)
+    out = {}
+    for mode in ("broadcast", "replicate"):
+        local = sharded_game.GpuShardBackend(ctx, W, H, elev, flags, wp, dev)
+        ctx.monsters_upload(mine)
+        game = sharded_game.ShardedGame(local, rank, world, mode=mode, device=dev)
+        dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        stats = game_events.run_events(game, nevents)
+        _, alive = ctx.monsters_tick(nevents + 1)
+        tot = torch.tensor([int(alive)], dtype=torch.int64, device=dev)
+        dist.all_reduce(tot)
+        wall = time.perf_counter() - t0
+        t = torch.tensor([wall], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        wall = float(t.item())
+        out[mode] = {"wall_s": wall, "value": nmon * nevents / wall, "unit": "monster ticks/s", "events_per_s": nevents / wall, "collectives_per_rank": game.collectives, "alive_total": int(tot.item()),
+                     "stats": stats}
+    return {"workload": f"C3 sharded: {nevents} place/remove events on the default map (replica per GPU), {nmon} monsters split by index over {world} GPUs", "n_gpus": world,
+            "partition": "monsters by index; trial verdict all-reduce(MAX) per trial; layers broadcast from rank 0 per accepted event (mode broadcast) or rebuilt on every rank (mode replicate)",
+            "value": out["broadcast"]["value"], "unit": "monster ticks/s", "modes": out,
+            "note": "latency-bound on the per-event rebuild and trial (one SM each); sharding the monsters shortens only the tick"}
+
+
 def cpu_c1(elev, flags, wp, cand):
     import numpy as np
 
@@ -759,6 +802,33 @@ def run_ours(args):
     relax_per_step = maps * T * NWP * world
     value = relax_per_step / (ms_step * 1e-3)
 
+    # ---- the same batch in STRONG form: 4096 maps in total, a contiguous block of map indices per rank (BASELINE.json
+    #      configs[1]: "sharded per GPU at 2/4/8"); the weak form above keeps 4096 maps on every GPU ----
+    strong = None
+    if world > 1:
+        from mazetd_b200 import shard
+
+        s_first, s_last = shard.map_range(rank, world, maps)
+        s_n = s_last - s_first
+
+        def step_strong():
+            ctx.mapgen_batch_dev(KAT_SEED[0], KAT_SEED[1], s_first, s_n, ptrs, W, H, 50, 50, 45, NWP, FULLPATH_CAP)
+
+        for _ in range(3):
+            step_strong()
+        barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record(stream)
+        for _ in range(args.steps):
+            step_strong()
+        f1.record(stream)
+        barrier()
+        ts = torch.tensor([f0.elapsed_time(f1)], dtype=torch.float64, device=dev)
+        dist.all_reduce(ts, op=dist.ReduceOp.MAX)
+        ms_strong = float(ts.item()) / args.steps
+        strong = {"scaling": "strong", "maps_total": maps, "maps_per_gpu": s_n, "ms_per_step": ms_strong, "value": maps * T * NWP / (ms_strong * 1e-3), "unit": "tile relaxations/s",
+                  "map_rebuilds_per_s": maps / (ms_strong * 1e-3)}
+
     # ---- roofline of the dominant kernel (k_waypoints_small): algorithmic bytes per DESIGN.md ----
     peaks = {}
     try:
@@ -847,6 +917,25 @@ def run_ours(args):
     del d
     torch.cuda.empty_cache()
     configs = {}
+    line_so_far = {}
+
+    def bail_out():
+        # a leg that hangs (a rank died inside a collective) must not take the headline measurement with it
+        if rank == 0 and line_so_far:
+            line_so_far["configs"] = dict(configs, error="the remaining legs were cut off after the time limit")
+            print(json.dumps(line_so_far), flush=True)
+        os._exit(0 if line_so_far or rank != 0 else 1)
+
+    watchdog = threading.Timer(args.legs_timeout, bail_out)
+    watchdog.daemon = True
+    if rank == 0:
+        line_so_far.update({
+            "metric": "tile relaxations/sec (map gen + Waypoints::update on batched 101x101 maps)", "value": value, "unit": "tile relaxations/s",
+            "map_rebuilds_per_s": maps * world / (ms_step * 1e-3), "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic", "config": workload_config(args, maps),
+            "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "strong": strong,
+        })
+    watchdog.start()
     if not args.no_configs:
         for name, fn in (("C5", lambda: leg_c5(ctx, dev, stream, rank, world, args)), ("C4", lambda: leg_c4(ctx, dev, stream, rank, world, args))):
             try:
@@ -859,7 +948,13 @@ def run_ours(args):
                 configs.update(leg_c1_c3(ctx, args, cpu=not args.no_cpu))
             except Exception as e:  # noqa: BLE001
                 configs["C1_C3"] = {"error": f"{type(e).__name__}: {e}"[:400]}
+        else:
+            try:
+                configs["C3"] = leg_c3_sharded(ctx, dev, rank, world, args)
+            except Exception as e:  # noqa: BLE001
+                configs["C3"] = {"error": f"{type(e).__name__}: {e}"[:400]}
 
+    watchdog.cancel()
     if rank == 0:
         line = {
             "metric": "tile relaxations/sec (map gen + Waypoints::update on batched 101x101 maps)",
@@ -881,6 +976,7 @@ def run_ours(args):
             "clocks": clocks,
             "e2e": e2e,
             "gpu_launches": launches,
+            "strong": strong,
             "configs": configs,
         }
         print(json.dumps(line), flush=True)
@@ -900,6 +996,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-configs", action="store_true", help="skip the C1/C3/C4/C5 legs (C2 headline only)")
+    ap.add_argument("--legs-timeout", type=float, default=900.0, help="seconds the C1/C3/C4/C5 legs may take before the line is printed without them")
     ap.add_argument("--c4-size", type=int, default=16384)
     ap.add_argument("--c3-events", type=int, default=10000)
     ap.add_argument("--c3-monsters", type=int, default=1000000)

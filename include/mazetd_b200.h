@@ -266,6 +266,11 @@ int mtd_towers_attack_dev(mtd_ctx *ctx, uint32_t gameTime, const uint64_t *rando
 /* tower state after the last tick (any pointer may be NULL): firingDelay, mana, picked monster (-1: did not fire), monsters hit. Synchronises. */
 int mtd_towers_download(mtd_ctx *ctx, uint32_t *firingDelay, uint32_t *mana, int32_t *target, uint32_t *hits);
 
+/* ---- C3 over several GPUs (monsters sharded by index, the 326 KB of layers broadcast per accepted event) ----
+ * After another rank's layers were copied INTO this context's resident layer buffers (the device pointers of
+ * mtd_waypoints_layers_dev, e.g. by ncclBroadcast), rebuild what Waypoints::find reads beside them (the inter-waypoint table). */
+int mtd_waypoints_layers_refresh(mtd_ctx *ctx);
+
 #ifdef __cplusplus
 }
 #endif

@@ -25,7 +25,7 @@ EXPORTS = [
     "mtd_monsters_upload", "mtd_monsters_download", "mtd_monsters_tick_dev", "mtd_monsters_tick",
     "mtd_monsters_positions_dev", "mtd_monsters_positions", "mtd_monster_spawn",
     "mtd_monsters_dots_upload", "mtd_monsters_dots_tick_dev", "mtd_monsters_dots_tick", "mtd_monsters_dots_download",
-    "mtd_monsters_class_upload", "mtd_towers_upload", "mtd_towers_attack_dev", "mtd_towers_download",
+    "mtd_monsters_class_upload", "mtd_towers_upload", "mtd_towers_attack_dev", "mtd_towers_download", "mtd_waypoints_layers_refresh",
 ]
 
 
@@ -108,6 +108,7 @@ def load():
     L.mtd_towers_upload.argtypes = [vp, i32] + [vp] * 13
     L.mtd_towers_attack_dev.argtypes = [vp, u32, vp]
     L.mtd_towers_download.argtypes = [vp, vp, vp, vp, vp]
+    L.mtd_waypoints_layers_refresh.argtypes = [vp]
     _lib = L
     return L
 
@@ -327,6 +328,9 @@ class Context:
         a, b = C.c_void_p(), C.c_void_p()
         self._ck(self.L.mtd_waypoints_layers_dev(self.h, C.byref(a), C.byref(b)))
         return a.value, b.value
+
+    def layers_refresh(self):
+        self._ck(self.L.mtd_waypoints_layers_refresh(self.h))
 
     def placing_blocks(self, candidate):
         out = C.c_int32(0)

@@ -2689,3 +2689,22 @@ extern "C" int mtd_towers_download(mtd_ctx *ctx, uint32_t *firingDelay, uint32_t
 		CU(cudaMemcpyAsync(hits, ctx->t_hits.p, N * 4, cudaMemcpyDeviceToHost, ctx->stream));
 	return sync_and_status(ctx);
 }
+
+// =====================================================================================================
+// C3 across GPUs: the layers of one rank are broadcast INTO the resident layer buffers of the others
+// =====================================================================================================
+extern "C" int mtd_waypoints_layers_refresh(mtd_ctx *ctx)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (ctx->nlayers <= 0)
+		return fail(ctx, MTD_ERR_STATE, "no resident waypoint layers (mtd_waypoints_update_dev once, to size them)");
+	if (ctx->nlayers <= FIND_MAXN)
+	{
+		k_build_dtab<<<1, 64, 0, ctx->stream>>>(layers_view(ctx), ctx->dtab.p);
+		LAUNCHED();
+	}
+	return MTD_OK;
+}

@@ -406,16 +406,23 @@ namespace mtd
 
 		MTD_ATICK(3);
 		// ---- bucketed wavefront on the frame, warp-synchronous ----
+		// A step settles the queued cells whose label is below `thr` and relaxes their four neighbours; improved cells and
+		// cells still above the threshold go to the other queue. The body is branch-free (the ncu capture of the first
+		// version, profiles/r02f_*, showed 2.1 cycles of branch-resolving stall per issued instruction): lanes with nothing
+		// to settle run the same code with candidates of MTD_INF, positions come from three bit-plane ballots of the
+		// per-lane output count instead of five ballots, and the threshold advances by one bucket per step (jumping ahead
+		// only when a step settled nothing) instead of tracking the exact minimum.
+		const uint32_t spare = (lane + 1u) * (uint32_t)PITCH + ((lane >> 2) % 6u < 3u ? (lane >> 2) % 6u : 34u + (lane >> 2) % 6u); // words 0..2 / 37..39 of frame row lane + 1
 		uint32_t nq = tail, par = 0;
 		bool overflow = false;
-		while (nq != 0u && dmin != MTD_INF)
+		uint32_t thr = dmin == MTD_INF ? MTD_INF : dmin + BIG_DELTA;
+		while (nq != 0u)
 		{
 			if (nq > (uint32_t)QCAP)
 			{
 				overflow = true;
 				break;
 			}
-			const uint32_t thr = dmin + BIG_DELTA;
 			const uint16_t *rq = S.q[par];
 			wq = S.q[par ^ 1u];
 			tail = 0;
@@ -423,68 +430,66 @@ namespace mtd
 			tacc[7] += 1ull;
 			tacc[8] += nq;
 #endif
-			uint32_t newmin = MTD_INF;
+			uint32_t kept_min = MTD_INF;
+			bool settled_any = false;
 			for (uint32_t base = 0; base < nq; base += 32u)
 			{
 				const uint32_t idx = base + lane;
 				const bool active = idx < nq;
-				const uint32_t c = active ? rq[idx] : (uint32_t)(PITCH + 4);
-				const uint32_t d = active ? S.d[c] : MTD_INF;
-				const bool settle = d < thr && d != 0u;
+				const uint32_t c = rq[active ? idx : 0u];
+				const uint32_t d = S.d[c];
+				const bool settle = active && d < thr && d != 0u;
 				const bool keep = active && d >= thr;
-				uint32_t n0 = 0, n1 = 0, n2 = 0, n3 = 0;
-				bool i0 = false, i1 = false, i2 = false, i3 = false;
-				if (settle)
-				{
-					const uint32_t wc = S.w[c], base_nd = d + MIN_EDGE;
-					n0 = base_nd + (S.w[c - PITCH] >> 16);
-					n1 = base_nd + (S.w[c - 1u] & 0xFFFFu);
-					n2 = base_nd + (wc & 0xFFFFu);
-					n3 = base_nd + (wc >> 16);
-					if (base_nd >= BIG_SETTLE_LIMIT)
-						guard = true;
-					else
-					{
-						i0 = n0 < atomicMin(&S.d[c - PITCH], n0);
-						i1 = n1 < atomicMin(&S.d[c - 1u], n1);
-						i2 = n2 < atomicMin(&S.d[c + 1u], n2);
-						i3 = n3 < atomicMin(&S.d[c + PITCH], n3);
-					}
-				}
-				uint32_t lm = keep ? d : MTD_INF;
-				lm = i0 ? min(lm, n0) : lm;
-				lm = i1 ? min(lm, n1) : lm;
-				lm = i2 ? min(lm, n2) : lm;
-				lm = i3 ? min(lm, n3) : lm;
-				newmin = min(newmin, lm);
-				const uint32_t bk = __ballot_sync(0xFFFFFFFFu, keep);
-				const uint32_t b0 = __ballot_sync(0xFFFFFFFFu, i0);
-				const uint32_t b1 = __ballot_sync(0xFFFFFFFFu, i1);
-				const uint32_t b2 = __ballot_sync(0xFFFFFFFFu, i2);
-				const uint32_t b3 = __ballot_sync(0xFFFFFFFFu, i3);
-				uint32_t pos = tail;
-				uint32_t p = pos + __popc(bk & lt);
+				const uint32_t wc = S.w[c], wu = S.w[c - PITCH] >> 16, wl = S.w[c - 1u] & 0xFFFFu;
+				const uint32_t base_nd = d + MIN_EDGE;
+				const bool ok = settle && base_nd < BIG_SETTLE_LIMIT;
+				guard |= settle && !ok;
+				settled_any |= settle;
+				const uint32_t n0 = base_nd + wu, n1 = base_nd + wl, n2 = base_nd + (wc & 0xFFFFu), n3 = base_nd + (wc >> 16);
+				// Four UNCONDITIONAL shared-memory atomics: a lane with nothing to settle aims them at its own spare word of the
+				// frame (the three words left and right of the apron in every row are never read) with MTD_INF, which changes
+				// nothing. `if (ok) atomicMin(...)` -- also as predicated inline PTX -- compiles to a divergent branch per
+				// atomic, and branch resolving was the largest single stall reason in profiles/r02f_*.
+				const uint32_t sel = ok ? 0xFFFFFFFFu : 0u;
+				const uint32_t a0 = ((c - PITCH) & sel) | (spare & ~sel), a1 = ((c - 1u) & sel) | (spare & ~sel), a2 = ((c + 1u) & sel) | (spare & ~sel), a3 = ((c + PITCH) & sel) | (spare & ~sel);
+#ifdef MTD_LOOK_BEFORE
+				const uint32_t c0 = S.d[c - PITCH], c1 = S.d[c - 1u], c2 = S.d[c + 1u], c3 = S.d[c + PITCH];
+				const uint32_t o0 = atomicMin(&S.d[n0 < c0 ? a0 : spare], ok && n0 < c0 ? n0 : MTD_INF), o1 = atomicMin(&S.d[n1 < c1 ? a1 : spare], ok && n1 < c1 ? n1 : MTD_INF);
+				const uint32_t o2 = atomicMin(&S.d[n2 < c2 ? a2 : spare], ok && n2 < c2 ? n2 : MTD_INF), o3 = atomicMin(&S.d[n3 < c3 ? a3 : spare], ok && n3 < c3 ? n3 : MTD_INF);
+#else
+				const uint32_t o0 = atomicMin(&S.d[a0], n0 | ~sel), o1 = atomicMin(&S.d[a1], n1 | ~sel);
+				const uint32_t o2 = atomicMin(&S.d[a2], n2 | ~sel), o3 = atomicMin(&S.d[a3], n3 | ~sel);
+#endif
+				const bool i0 = ok && n0 < o0, i1 = ok && n1 < o1, i2 = ok && n2 < o2, i3 = ok && n3 < o3;
+				kept_min = min(kept_min, keep ? d : MTD_INF);
+				// every lane has up to five entries for the other queue; exclusive prefix of the counts from three ballots
+				const uint32_t cnt = (keep ? 1u : 0u) + (i0 ? 1u : 0u) + (i1 ? 1u : 0u) + (i2 ? 1u : 0u) + (i3 ? 1u : 0u);
+				const uint32_t p0 = __ballot_sync(0xFFFFFFFFu, cnt & 1u), p1 = __ballot_sync(0xFFFFFFFFu, cnt & 2u), p2 = __ballot_sync(0xFFFFFFFFu, cnt & 4u);
+				uint32_t p = tail + (uint32_t)__popc(p0 & lt) + 2u * (uint32_t)__popc(p1 & lt) + 4u * (uint32_t)__popc(p2 & lt);
+				tail += (uint32_t)__popc(p0) + 2u * (uint32_t)__popc(p1) + 4u * (uint32_t)__popc(p2);
 				if (keep && p < (uint32_t)QCAP)
 					wq[p] = (uint16_t)c;
-				pos += __popc(bk);
-				p = pos + __popc(b0 & lt);
+				p += keep ? 1u : 0u;
 				if (i0 && p < (uint32_t)QCAP)
 					wq[p] = (uint16_t)(c - PITCH);
-				pos += __popc(b0);
-				p = pos + __popc(b1 & lt);
+				p += i0 ? 1u : 0u;
 				if (i1 && p < (uint32_t)QCAP)
 					wq[p] = (uint16_t)(c - 1u);
-				pos += __popc(b1);
-				p = pos + __popc(b2 & lt);
+				p += i1 ? 1u : 0u;
 				if (i2 && p < (uint32_t)QCAP)
 					wq[p] = (uint16_t)(c + 1u);
-				pos += __popc(b2);
-				p = pos + __popc(b3 & lt);
+				p += i2 ? 1u : 0u;
 				if (i3 && p < (uint32_t)QCAP)
 					wq[p] = (uint16_t)(c + PITCH);
-				tail = pos + __popc(b3);
 			}
-			dmin = warp_redux_min(newmin);
+			if (__any_sync(0xFFFFFFFFu, settled_any))
+				thr = thr > MTD_INF - BIG_DELTA ? MTD_INF : thr + BIG_DELTA;
+			else
+			{
+				// nothing was below the threshold: jump to the bucket of the smallest pending label
+				const uint32_t km = warp_redux_min(kept_min);
+				thr = km > MTD_INF - BIG_DELTA ? MTD_INF : km + BIG_DELTA;
+			}
 			nq = tail;
 			par ^= 1u;
 			__syncwarp();

@@ -4,12 +4,15 @@
 //       tiny per-call geometry used all over the game: they stay on the host and read the host arrays.
 //       The float32 operation order of center() and neighborDistance() is kept, because distances are compared bit for bit.
 //   newGrid(Holder<Procedural>)                                 reference sources/map/grid.cpp:147-198
-//       elevation sampling goes through the caller's Procedural object (it is an opaque virtual interface,
-//       sources/map/generate.h:25-31); everything after it -- biome flags, slope / radius invalidation, largest connected
-//       component, border, mana (grid.cpp:160-196) -- runs on the GPU: mtd_grid_from_elevations.
-//       Batched generation from seeds (noise included) is mtd_mapgen_batch; the game never needs more than one map.
+//       ONE device call when the Procedural came from the replacement newProcedural() (procedural_b200.cpp): it carries the
+//       generator state its constructor started from, the device repeats the seven draws and samples the elevations
+//       itself (mtd_mapgen_batch with no waypoints: noise -> int16, biome flags, slope / radius invalidation, largest
+//       connected component, border, mana; grid.cpp:153-196). A foreign Procedural is an opaque virtual interface
+//       (sources/map/generate.h:25-31): its elevations are sampled through it on the CPU and only the stages after
+//       them run on the GPU (mtd_grid_from_elevations).
 #include "map/generate.h"
 #include "mtd_host.h"
+#include "procedural_b200.h"
 
 #include <cage-core/pointerRangeHolder.h>
 
@@ -81,19 +84,26 @@ namespace mazetd
 		PointerRangeHolder<const sint16> heights;
 		heights.resize(total);
 		sint16 *h = const_cast<sint16 *>(heights.data());
-		for (uint32 i = 0; i < total; i++)
-		{
-			const Real e = procedural->elevation(Vec2(grid->position(i)));
-			h[i] = rtos16(clamp(e, -100, 100));
-		}
-
 		PointerRangeHolder<TileFlags> flags;
 		flags.resize(total);
+		mtd_mapgen_params params = {};
+		params.W = params.H = MapSize;
+		params.ox = params.oy = MapOrigin;
+		params.radius = MapRadius;
+		params.nwp = 0; // newWaypoints() draws the spawn tiles afterwards, from the caller's generator
+		if (const b200::SeededProcedural *seeded = dynamic_cast<const b200::SeededProcedural *>(+procedural))
 		{
-			mtd_mapgen_params params = {};
-			params.W = params.H = MapSize;
-			params.ox = params.oy = MapOrigin;
-			params.radius = MapRadius;
+			b200::Device &dev = b200::device();
+			std::lock_guard<std::mutex> lock(dev.mutex);
+			b200::check(dev, mtd_mapgen_batch(dev.ctx, &params, seeded->s1, seeded->s2, 0, 1, h, (uint16_t *)flags.data(), nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr));
+		}
+		else
+		{
+			for (uint32 i = 0; i < total; i++)
+			{
+				const Real e = procedural->elevation(Vec2(grid->position(i)));
+				h[i] = rtos16(clamp(e, -100, 100));
+			}
 			b200::Device &dev = b200::device();
 			std::lock_guard<std::mutex> lock(dev.mutex);
 			b200::check(dev, mtd_grid_from_elevations(dev.ctx, &params, 1, h, (uint16_t *)flags.data()));

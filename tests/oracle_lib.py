@@ -444,3 +444,13 @@ class OracleGame:
 
     def tick(self, t):
         self.o.monsters_tick(self.view, t, self.a)
+
+    # the two layer hooks of mazetd_b200.sharded_game (C3 over several ranks)
+    def export_layers(self):
+        import torch
+
+        return torch.from_numpy(self.w["tiles"].view(np.int32).reshape(-1)), torch.from_numpy(self.w["dist"].view(np.int32).reshape(-1))
+
+    def import_layers(self, tiles, d):
+        # the broadcast wrote into self.w's arrays (the tensors alias them); the view holds pointers to the same arrays
+        self.view = self.o.waypoints_view(self.W, self.H, self.elev, self.flags, self.wp, self.w["tiles"], self.w["dist"], 50, 50)

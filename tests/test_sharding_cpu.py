@@ -141,3 +141,68 @@ def test_stripe_protocol_and_map_ranges_over_gloo(oracle, world):
     assert ok, "striped distances / next hops differ from the whole-grid oracle"
     assert ok_maps
     assert sweeps >= 1
+
+
+# ---- C3 over several ranks: monsters sharded by index, layers broadcast per accepted event ----
+def _c3_inputs(orc, nmon):
+    import oracle_lib
+    from mazetd_b200 import game_events
+
+    o = orc.mapgen(oracle_lib.KAT_SEED[0], oracle_lib.KAT_SEED[1])
+    sp = int(o["agg"][2])
+    view = orc.waypoints_view(101, 101, o["elev"], o["flags"], o["wp_tiles"], o["tiles"], o["dist"], 50, 50)
+    find = lambda pos, bits: tuple(np.array(x, np.uint32) for x in zip(*[orc.find(view, int(p), int(b)) for p, b in zip(pos, bits)]))  # noqa: E731
+    mon = game_events.initial_monsters(nmon, o["fullpath"][sp][: int(o["fullpath_len"][sp])], o["wp_tiles"], find)
+    return o, mon
+
+
+def _c3_worker(rank, world, port, mode, nmon, nevents, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import oracle_lib
+        from mazetd_b200 import game_events, sharded_game
+
+        orc = oracle_lib.Oracle()
+        o, mon = _c3_inputs(orc, nmon)
+        mine = sharded_game.shard_monsters(mon, rank, world)
+        local = oracle_lib.OracleGame(orc, 101, 101, o["elev"], o["flags"], o["wp_tiles"], mine)
+        game = sharded_game.ShardedGame(local, rank, world, mode=mode)
+        stats = game_events.run_events(game, nevents)
+        parts = [None] * world
+        dist.gather_object((rank, {k: v for k, v in mine.items()}, stats, local.flags.copy(), game.collectives), parts if rank == 0 else None, dst=0)
+        if rank == 0:
+            parts.sort(key=lambda p: p[0])
+            merged = {k: np.concatenate([p[1][k] for p in parts]) for k in mine}
+            out.put((merged, [p[2] for p in parts], [p[3] for p in parts], parts[0][4]))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("mode", ["broadcast", "replicate"])
+def test_c3_monsters_sharded_over_gloo_match_one_process(oracle, mode):
+    """two ranks, each ticking half of the monsters; trial verdicts OR-ed, layers broadcast from rank 0 (or rebuilt on
+    every rank): the union of the shards equals one process running all monsters, event for event"""
+    import oracle_lib
+    from mazetd_b200 import game_events
+
+    nmon, nevents, world = 1201, 70, 2
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_c3_worker, args=(r, world, port, mode, nmon, nevents, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    merged, stats, flags, collectives = out.get(timeout=240)
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    o, mon = _c3_inputs(oracle, nmon)
+    one = oracle_lib.OracleGame(oracle, 101, 101, o["elev"], o["flags"], o["wp_tiles"], mon)
+    want = game_events.run_events(one, nevents)
+    assert all(s == want for s in stats), (stats, want)
+    assert want["placed"] > 3
+    assert all(np.array_equal(f, one.flags) for f in flags)
+    for k in ("tile", "tileStart", "tileEnd", "timeStart", "timeEnd", "bits", "alive"):
+        assert np.array_equal(merged[k], one.a[k]), k
+    assert collectives > 0
