@@ -449,17 +449,12 @@ namespace mtd
 				// Four UNCONDITIONAL shared-memory atomics: a lane with nothing to settle aims them at its own spare word of the
 				// frame (the three words left and right of the apron in every row are never read) with MTD_INF, which changes
 				// nothing. `if (ok) atomicMin(...)` -- also as predicated inline PTX -- compiles to a divergent branch per
-				// atomic, and branch resolving was the largest single stall reason in profiles/r02f_*.
+				// atomic, and branch resolving was the largest single stall reason in profiles/r02f_*. (Reading the four labels
+				// first and skipping atomics that cannot improve was measured again in r02i: 812 -> 998 cycles per step.)
 				const uint32_t sel = ok ? 0xFFFFFFFFu : 0u;
 				const uint32_t a0 = ((c - PITCH) & sel) | (spare & ~sel), a1 = ((c - 1u) & sel) | (spare & ~sel), a2 = ((c + 1u) & sel) | (spare & ~sel), a3 = ((c + PITCH) & sel) | (spare & ~sel);
-#ifdef MTD_LOOK_BEFORE
-				const uint32_t c0 = S.d[c - PITCH], c1 = S.d[c - 1u], c2 = S.d[c + 1u], c3 = S.d[c + PITCH];
-				const uint32_t o0 = atomicMin(&S.d[n0 < c0 ? a0 : spare], ok && n0 < c0 ? n0 : MTD_INF), o1 = atomicMin(&S.d[n1 < c1 ? a1 : spare], ok && n1 < c1 ? n1 : MTD_INF);
-				const uint32_t o2 = atomicMin(&S.d[n2 < c2 ? a2 : spare], ok && n2 < c2 ? n2 : MTD_INF), o3 = atomicMin(&S.d[n3 < c3 ? a3 : spare], ok && n3 < c3 ? n3 : MTD_INF);
-#else
 				const uint32_t o0 = atomicMin(&S.d[a0], n0 | ~sel), o1 = atomicMin(&S.d[a1], n1 | ~sel);
 				const uint32_t o2 = atomicMin(&S.d[a2], n2 | ~sel), o3 = atomicMin(&S.d[a3], n3 | ~sel);
-#endif
 				const bool i0 = ok && n0 < o0, i1 = ok && n1 < o1, i2 = ok && n2 < o2, i3 = ok && n3 < o3;
 				kept_min = min(kept_min, keep ? d : MTD_INF);
 				// every lane has up to five entries for the other queue; exclusive prefix of the counts from three ballots
