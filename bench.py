@@ -566,17 +566,30 @@ def leg_c1_c3(ctx, args, cpu):
         ctx.grid_set_flags(cand, int(flags[cand]) | synth.FLAG_BUILDING)  # P6: flag delta
         ctx.waypoints_update(wp, cap=4096)                        # P2: 4 layers + walks + aggregates, everything copied to the host
         lat.append(time.perf_counter() - t0)
-        ctx.grid_set_flags(cand, int(flags[cand]))
+        ctx.grid_set_flags(cand, int(flags[cand]))  # untimed: the tower is sold again and the layers follow (clearStructure path)
+        ctx.waypoints_update_dev(wp)
     med = float(np.median(lat[20:]))
     res = []
-    for _ in range(120):
+    for rep in range(120):
+        ctx.grid_set_flags(cand, (int(flags[cand]) | synth.FLAG_BUILDING) if rep % 2 == 0 else int(flags[cand]))  # place / sell alternately
         t0 = time.perf_counter()
         ctx.waypoints_update_dev(wp)
         ctx.synchronize()
         res.append(time.perf_counter() - t0)
+    inc = ctx.big_stats()
+    ctx.debug_set(ctx.DEBUG_INCREMENTAL, 0)
+    full = []
+    for rep in range(60):
+        ctx.grid_set_flags(cand, (int(flags[cand]) | synth.FLAG_BUILDING) if rep % 2 == 0 else int(flags[cand]))
+        t0 = time.perf_counter()
+        ctx.waypoints_update_dev(wp)
+        ctx.synchronize()
+        full.append(time.perf_counter() - t0)
+    ctx.debug_set(ctx.DEBUG_INCREMENTAL, 1)
     out["C1"] = {"workload": "C1: default generated map (seed k=0), scripted tower placement: trial + flag delta + Waypoints::update, 101x101, 4 layers", "metric": "us per placement", "value": med * 1e6, "unit": "us",
                  "higher_is_better": False, "tile_relaxations_per_s": T * NWP / med, "e2e": {"value": med * 1e6, "unit": "us", "d2h_bytes": T * NWP * 8 + 4 * 4096 * NWP, "api": "mtd_placing_blocks + mtd_grid_set_flags + mtd_waypoints_update (host outputs), wall clock"},
-                 "resident_us": float(np.median(res[20:])) * 1e6, "candidate_tile": cand, "roofline": None, "roofline_note": "latency-bound by design (10 201 tiles in one SM's shared memory): reported as latency, SURVEY.md 8d"}
+                 "resident_us": float(np.median(res[20:])) * 1e6, "resident_from_scratch_us": float(np.median(full[10:])) * 1e6, "incremental_updates": inc["rounds"], "incremental_trials": inc["visits"],
+                 "candidate_tile": cand, "roofline": None, "roofline_note": "latency-bound by design (10 201 tiles in one SM's shared memory): reported as latency, SURVEY.md 8d"}
     if cpu:
         out["C1"]["cpu_baseline"] = cpu_c1(elev, flags, wp, cand)
 

@@ -82,13 +82,15 @@ enum
 	MTD_DEBUG_BIG_ASYNC = 5,   /* large grids: 1 (default) = dataflow scheduler without global rounds (k_tile_async), 0 = round-based kernel (k_tile_rounds). Same result */
 	MTD_DEBUG_ASYNC_NB_RULE = 8, /* dataflow scheduler: value >= 0: a tile does not start while a neighbour tile is in flight or waits with a key smaller by more than `value`; < 0: off. Performance only */
 	MTD_DEBUG_ASYNC_DEPTH = 9, /* dataflow scheduler: mailboxes per worker (1, or 2 = the next item is handed out and prefetched early). Performance only */
+	MTD_DEBUG_INCREMENTAL = 10, /* one-CTA path: 1 (default) = after ONE blocking flip the resident layers are repaired (subtree cut out and re-relaxed / improvement propagated) and the trial reuses layer 0; 0 = always from scratch. Same result */
 	MTD_DEBUG_BIG_TMA = 7,     /* dataflow scheduler: 1 (default) = tile frames staged by 2-D bulk tensor copies (TMA), 0 = cp.async rows. Same result */
 	MTD_DEBUG_ASYNC_DELTA = 6, /* priority window (label units) of the dataflow scheduler. Performance only */
 	MTD_DEBUG_TILE_DELTA = 4   /* large grids: width (label units) of the window of tile offers visited per round; 2^32-1 = visit everything (no priority). Performance only: any value gives the same result */
 };
 int mtd_debug_set(mtd_ctx *ctx, int key, int64_t value);
 /* Statistics of the last large-grid (tiled) update: out4 = { global rounds (0 with the dataflow scheduler), tile visits,
- * scheduler polls, bit 0: the dataflow scheduler ran, bit 1: frames were staged by TMA }. Diagnostics for bench.py; no reference counterpart. */
+ * scheduler polls, bit 0: the dataflow scheduler ran, bit 1: frames were staged by TMA }. While the context holds a grid of the
+ * one-CTA path: { incremental updates, incremental trials since mtd_create, 0, 0 }. Diagnostics for bench.py; no reference counterpart. */
 int mtd_big_stats(mtd_ctx *ctx, uint32_t *out4);
 
 /* ---- Grid (replaces the data side of struct Grid, sources/grid.h:38-53) ------------------------ */

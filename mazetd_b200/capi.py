@@ -153,6 +153,7 @@ class Context:
     DEBUG_BIG_ASYNC = 5
     DEBUG_ASYNC_DELTA = 6
     DEBUG_BIG_TMA = 7
+    DEBUG_INCREMENTAL = 10
     DEBUG_ASYNC_NB_RULE = 8
     DEBUG_ASYNC_DEPTH = 9
 

@@ -127,6 +127,14 @@ struct mtd_ctx
 	bool big_async = true;         // large grids: k_tile_async (no global rounds); false = k_tile_rounds (A/B and multi-stripe contexts)
 	uint32_t async_delta = 65536;  // priority window of the dataflow scheduler (label units); swept 8k..256k on C4 / C5 (profiles/r02c_*, r02g_*)
 	uint32_t last_visits = 0;
+	// incremental re-pathing of the one-CTA path: the resident layers are valid for the grid as it was before `inc_dirty` blocking
+	// flips (inc_dirty == 1: the tile is inc_tile); h_blocking mirrors the blocking bits of a grid uploaded from the host
+	bool inc_enabled = true, inc_layers_ok = false;
+	int inc_dirty = 0, inc_n = 0;
+	uint32_t inc_tile = MTD_M, inc_wp[MTD_MAX_WAYPOINTS] = { 0 };
+	std::vector<uint8_t> h_blocking;
+	std::vector<int16_t> h_elev; // host mirror of the elevations of a small grid uploaded from the host: a re-upload of the same grid is a flag delta
+	uint64_t inc_updates = 0, inc_trials = 0;
 	bool last_async = false, last_tma = false;
 	bool big_tma = true;           // dataflow scheduler: stage frames with bulk tensor copies (TMA) when the width allows it
 	uint32_t tile_delta = 98304; // visit window of the tile-level priority (label units); swept 8k..inf on 4096^2 and 16384^2 (weights 255..570): flat optimum 64k..256k
@@ -862,6 +870,16 @@ namespace
 			P.tiles = d_tiles;
 			P.dist = d_dist;
 			P.status = ctx->d_status.p;
+			P.inc_tile = MTD_M;
+			// the trial of placingBuildingBlocksMonsters from waypoint 0: layer 0 of the resident layers, with the candidate
+			// blocked, is a repair of that layer (buildingsPlacement.cpp:18-42 runs a fresh Dijkstra for it)
+			if (ctx->inc_enabled && ctx->inc_layers_ok && ctx->inc_dirty == 0 && nsrc == 1 && extra_blocked != MTD_M && ctx->inc_n >= 1 && sources[0] == ctx->inc_wp[0] && !ctx->h_blocking.empty() &&
+				!ctx->h_blocking[extra_blocked] && d_dist != ctx->ldist.p)
+			{
+				P.prev_dist = ctx->ldist.p;
+				P.inc_tile = extra_blocked;
+				ctx->inc_trials++;
+			}
 			return launch_waypoints_small(ctx, P);
 		}
 		return big_layers(ctx, sources, 1, nsrc, extra_blocked, d_tiles, d_dist);
@@ -950,9 +968,28 @@ namespace
 			P.full_distance = ctx->fp_dist.p;
 			P.agg = ctx->agg.p;
 			P.status = ctx->d_status.p;
+			// one blocking flip since the layers were computed for these waypoints: repair them instead of starting over
+			// (same outputs: distances are the unique fixpoint, next hops / walks / aggregates are recomputed from them)
+			bool same_wp = ctx->inc_layers_ok && ctx->inc_n == n && n <= small_resident(ctx->W, ctx->H, n);
+			for (int i = 0; same_wp && i < n; i++)
+				same_wp = ctx->inc_wp[i] == wp_tiles[i];
+			if (ctx->inc_enabled && same_wp && ctx->inc_dirty == 1 && !ctx->h_blocking.empty())
+			{
+				P.prev_dist = ctx->ldist.p;
+				P.inc_tile = ctx->inc_tile;
+				ctx->inc_updates++;
+			}
+			else
+				P.inc_tile = MTD_M;
+			ctx->inc_layers_ok = false;
 			int rc = launch_waypoints_small(ctx, P);
 			if (rc)
 				return rc;
+			ctx->inc_layers_ok = !ctx->h_blocking.empty();
+			ctx->inc_dirty = 0;
+			ctx->inc_n = n;
+			for (int i = 0; i < n; i++)
+				ctx->inc_wp[i] = wp_tiles[i];
 		}
 		else
 		{
@@ -1160,6 +1197,9 @@ extern "C" int mtd_debug_set(mtd_ctx *ctx, int key, int64_t value)
 	case MTD_DEBUG_ASYNC_DEPTH:
 		ctx->async_depth = value >= 2 ? 2 : 1;
 		return MTD_OK;
+	case MTD_DEBUG_INCREMENTAL:
+		ctx->inc_enabled = value != 0;
+		return MTD_OK;
 	case MTD_DEBUG_BIG_TMA:
 		ctx->big_tma = value != 0;
 		return MTD_OK;
@@ -1182,6 +1222,12 @@ extern "C" int mtd_big_stats(mtd_ctx *ctx, uint32_t *out4)
 	out4[1] = ctx->last_async ? ctx->last_visits : ctx->hflags->big_items;
 	out4[2] = ctx->last_async ? ctx->hflags->async_ctl[ACTL_IDLE_POLLS] : 0u;
 	out4[3] = ctx->last_async ? (ctx->last_tma ? 3u : 1u) : 0u;
+	if (ctx->small)
+	{
+		// one-CTA path: how many updates / trials were incremental repairs since the context was created
+		out4[0] = (uint32_t)ctx->inc_updates;
+		out4[1] = (uint32_t)ctx->inc_trials;
+	}
 	return MTD_OK;
 }
 
@@ -1239,6 +1285,27 @@ static int grid_common(mtd_ctx *ctx, int32_t W, int32_t H, int32_t ox, int32_t o
 		return fail(ctx, MTD_ERR_ARG, "grid needs W, H >= 1 and non-null elev/flags");
 	if ((uint64_t)W * (uint64_t)H >= 0xFFFFFFFFull)
 		return fail(ctx, MTD_ERR_ARG, "grid too large for uint32 tile indices");
+	// The reference mutates Grid::flags in place and calls update() (buildingsPlacement.cpp:128-129), so the drop-in
+	// adapter re-uploads the whole grid before every update. When it is the grid this context already holds (same shape,
+	// same elevations) only the flags travel, the resident layers stay, and the blocking bits that flipped are counted:
+	// exactly one flip lets the next update repair the layers instead of recomputing them.
+	if (kind == cudaMemcpyHostToDevice && ctx->have_grid && !ctx->stripe && ctx->small && W == ctx->W && H == ctx->H && ox == ctx->ox && oy == ctx->oy && ctx->h_elev.size() == (size_t)W * H &&
+		ctx->h_blocking.size() == ctx->h_elev.size() && memcmp(ctx->h_elev.data(), elev, ctx->h_elev.size() * 2) == 0)
+	{
+		for (size_t i = 0; i < ctx->T; i++)
+		{
+			const uint8_t nb = (flags[i] & F_BLOCKING) ? 1 : 0;
+			if (nb != ctx->h_blocking[i])
+			{
+				ctx->h_blocking[i] = nb;
+				ctx->inc_dirty++;
+				ctx->inc_tile = (uint32_t)i;
+			}
+		}
+		CU(cudaMemcpyAsync(ctx->flags.p, flags, ctx->T * 2, kind, ctx->stream));
+		CU(cudaStreamSynchronize(ctx->stream));
+		return MTD_OK;
+	}
 	ctx->have_grid = false;
 	ctx->stripe = false;
 	ctx->nlayers = 0;
@@ -1260,6 +1327,17 @@ static int grid_common(mtd_ctx *ctx, int32_t W, int32_t H, int32_t ox, int32_t o
 	}
 	if (kind == cudaMemcpyHostToDevice)
 		CU(cudaStreamSynchronize(ctx->stream)); // caller may reuse its host arrays (pageable memory is staged, but be explicit)
+	ctx->inc_layers_ok = false;
+	ctx->inc_dirty = 0;
+	ctx->h_blocking.clear();
+	ctx->h_elev.clear();
+	if (kind == cudaMemcpyHostToDevice && ctx->small)
+	{
+		ctx->h_blocking.resize(ctx->T);
+		for (size_t i = 0; i < ctx->T; i++)
+			ctx->h_blocking[i] = (flags[i] & F_BLOCKING) ? 1 : 0;
+		ctx->h_elev.assign(elev, elev + ctx->T);
+	}
 	ctx->have_grid = true;
 	return MTD_OK;
 }
@@ -1674,6 +1752,18 @@ extern "C" int mtd_grid_set_flags(mtd_ctx *ctx, uint32_t tile, uint16_t flags)
 		return fail(ctx, MTD_ERR_STATE, "no grid uploaded (or the context holds a row stripe)");
 	if (tile >= ctx->T)
 		return fail(ctx, MTD_ERR_ARG, "tile outside the grid");
+	if (!ctx->h_blocking.empty())
+	{
+		const uint8_t nb = (flags & F_BLOCKING) ? 1 : 0;
+		if (nb != ctx->h_blocking[tile])
+		{
+			ctx->h_blocking[tile] = nb;
+			ctx->inc_dirty++;
+			ctx->inc_tile = tile;
+		}
+	}
+	else
+		ctx->inc_layers_ok = false; // no host mirror of the blocking bits: the next update is a full one
 	ctx->hflags->spawn[0] = flags; // staged in pinned memory so the async copy has a stable source
 	CU(cudaMemcpyAsync(ctx->flags.p + tile, &ctx->hflags->spawn[0], 2, cudaMemcpyHostToDevice, ctx->stream));
 	if (!ctx->small)
@@ -1893,9 +1983,14 @@ extern "C" int mtd_placing_blocks(mtd_ctx *ctx, uint32_t candidate, int32_t *blo
 		return fail(ctx, MTD_ERR_ARG, "candidate outside the grid");
 	// the trial source is waypoint 0 (buildingsPlacement.cpp:27); its tile is mirrored on the host in hflags->spawn[2]
 	uint32_t src;
-	CU(cudaMemcpyAsync(&ctx->hflags->spawn[2], ctx->lwp.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
-	CU(cudaStreamSynchronize(ctx->stream));
-	src = ctx->hflags->spawn[2];
+	if (ctx->inc_layers_ok && ctx->inc_n >= 1)
+		src = ctx->inc_wp[0]; // host mirror of the resident waypoints
+	else
+	{
+		CU(cudaMemcpyAsync(&ctx->hflags->spawn[2], ctx->lwp.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+		CU(cudaStreamSynchronize(ctx->stream));
+		src = ctx->hflags->spawn[2];
+	}
 	CU(ctx->trial_dist.reserve(ctx->T));
 	int rc = directions_dev(ctx, &src, 1, candidate, nullptr, ctx->trial_dist.p);
 	if (rc)
@@ -2706,5 +2801,8 @@ extern "C" int mtd_waypoints_layers_refresh(mtd_ctx *ctx)
 		k_build_dtab<<<1, 64, 0, ctx->stream>>>(layers_view(ctx), ctx->dtab.p);
 		LAUNCHED();
 	}
+	// the imported layers belong to the grid as it is now
+	ctx->inc_dirty = 0;
+	ctx->inc_layers_ok = ctx->inc_n == ctx->nlayers && !ctx->h_blocking.empty();
 	return MTD_OK;
 }

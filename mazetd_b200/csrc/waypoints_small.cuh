@@ -66,6 +66,10 @@ namespace mtd
 		int qseg_cap;            // > 0 caps the queue segment size (tests force the dense fallback with it)
 		int walker;              // != 0: paths are walked by the walker warp on the layers in global memory (needs tiles + dist),
 		                         //       one map behind the workers; 0: the workers walk the resident layers themselves
+		// incremental re-pathing: the layers of the previous update are still valid except for ONE tile
+		// whose blocking state flipped since (sources/player/buildingsPlacement.cpp:120-130, 143-164, trial :18-42)
+		const uint32_t *prev_dist; // [n][T] distances before the flip (may alias `dist`), or null
+		uint32_t inc_tile;         // the flipped tile, MTD_M = none (full update). Needs nmaps == 1, n <= R, nsrc == 1
 	};
 
 	// ---- geometry of the padded frame -------------------------------------------------------------------------
@@ -390,6 +394,238 @@ namespace mtd
 		return __any_sync(FULL_MASK, guard);
 	}
 
+	// ---- incremental re-pathing on one layer in the padded frame (one warp) -------------------------------------------
+	// Labels of cells that belong to the subtree under repair carry INC_MARK; inc_lab() strips it. All finite labels are
+	// below INC_MARK in this mode (checked when the previous layers are loaded).
+	constexpr uint32_t INC_MARK = 0x80000000u;
+
+	__device__ __forceinline__ uint32_t inc_lab(uint32_t v)
+	{
+		return v == MTD_INF ? MTD_INF : (v & ~INC_MARK);
+	}
+
+	// is u the next hop of v (label dv)? Closed form of the heap order as in next_hop_p, on labels that may be marked.
+	__device__ __forceinline__ bool inc_is_child(const uint32_t *dl, const uint16_t *wr, const uint16_t *wd, int Wp, uint32_t v, uint32_t dv, uint32_t u, uint32_t srcp)
+	{
+		const uint32_t u0 = v - (uint32_t)Wp, u1 = v - 1u, u2 = v + 1u, u3 = v + (uint32_t)Wp;
+		const uint32_t d0 = inc_lab(dl[u0]), d1 = inc_lab(dl[u1]), d2 = inc_lab(dl[u2]), d3 = inc_lab(dl[u3]);
+		const uint32_t w0 = wd[u0], w1 = wr[u1], w2 = wr[v], w3 = wd[v];
+		uint32_t best = MTD_INF, bestd = MTD_INF;
+		if (d0 != MTD_INF && d0 + MIN_EDGE + w0 == dv && (d0 != 0u || u0 == srcp))
+		{
+			bestd = d0;
+			best = u0;
+		}
+		if (d1 != MTD_INF && d1 + MIN_EDGE + w1 == dv && d1 < bestd && (d1 != 0u || u1 == srcp))
+		{
+			bestd = d1;
+			best = u1;
+		}
+		if (d2 != MTD_INF && d2 + MIN_EDGE + w2 == dv && d2 < bestd && (d2 != 0u || u2 == srcp))
+		{
+			bestd = d2;
+			best = u2;
+		}
+		if (d3 != MTD_INF && d3 + MIN_EDGE + w3 == dv && d3 < bestd && (d3 != 0u || u3 == srcp))
+		{
+			bestd = d3;
+			best = u3;
+		}
+		return best == u;
+	}
+
+	// smallest label the unmarked neighbours offer cell v (MTD_INF: none). A parked neighbour holds 0 like the source does.
+	__device__ __forceinline__ uint32_t inc_offer(const uint32_t *dl, const uint16_t *wr, const uint16_t *wd, int Wp, uint32_t v, uint32_t srcp)
+	{
+		const uint32_t u[4] = { v - (uint32_t)Wp, v - 1u, v + 1u, v + (uint32_t)Wp };
+		const uint32_t w[4] = { wd[u[0]], wr[u[1]], wr[v], wd[v] };
+		uint32_t best = MTD_INF;
+#pragma unroll
+		for (int k = 0; k < 4; k++)
+		{
+			const uint32_t d = dl[u[k]];
+			if (d == MTD_INF || (d & INC_MARK) || (d == 0u && u[k] != srcp))
+				continue;
+			best = min(best, d + MIN_EDGE + w[k]);
+		}
+		return best;
+	}
+
+	// Repairs layer `dl` after tile bp flipped. now_blocked: the subtree of bp in the next-hop tree (every tile whose path ran
+	// through bp) is cut out and its rim seeds the bucket queue that group_relax then settles; labels elsewhere cannot
+	// change. !now_blocked: bp gets its label from its neighbours and the improvement is propagated (label-correcting, one
+	// warp) -- labels only drop, and only behind bp. Returns false when the repair does not fit (lists full, labels too large,
+	// bp is the source): the caller then recomputes the layer from scratch. list: cap entries of scratch (the layer's queue).
+	__device__ bool inc_repair(uint32_t *dl, const uint16_t *wr, const uint16_t *wd, int Wp, uint32_t bp, uint32_t srcp, bool now_blocked, uint32_t d_b_old, uint16_t *list, uint32_t cap, uint32_t qseg, uint32_t *c, uint32_t lane)
+	{
+		const uint32_t lt = lanemask_lt();
+		uint32_t nseed = 0, seedmin = MTD_INF;
+		bool ok = true;
+		if (bp == srcp)
+			return false;
+		if (now_blocked)
+		{
+			if (d_b_old != MTD_INF)
+			{
+				// ---- subtree of bp, breadth first; list[0 .. n) collects it ----
+				if (lane == 0)
+				{
+					dl[bp] = d_b_old | INC_MARK; // parked by the caller; its old label is what its children were computed from
+					list[0] = (uint16_t)bp;
+				}
+				__syncwarp();
+				uint32_t f0 = 0, n = 1;
+				while (f0 < n && ok)
+				{
+					const uint32_t f1 = n;
+					for (uint32_t base = f0; base < f1; base += 32u)
+					{
+						const uint32_t idx = base + lane;
+						const bool act = idx < f1;
+						const uint32_t u = act ? list[idx] : bp;
+#pragma unroll
+						for (int k = 0; k < 4; k++)
+						{
+							const uint32_t v = k == 0 ? u - (uint32_t)Wp : k == 1 ? u - 1u : k == 2 ? u + 1u : u + (uint32_t)Wp;
+							const uint32_t dv = dl[v];
+							const bool child = act && dv != 0u && dv != MTD_INF && !(dv & INC_MARK) && inc_is_child(dl, wr, wd, Wp, v, dv, u, srcp);
+							const uint32_t bal = __ballot_sync(FULL_MASK, child);
+							if (child)
+							{
+								const uint32_t pos = n + __popc(bal & lt);
+								if (pos < cap)
+									list[pos] = (uint16_t)v;
+								dl[v] = dv | INC_MARK; // a tile has one next hop: nobody else marks v
+							}
+							n += __popc(bal);
+							__syncwarp();
+						}
+					}
+					if (n > cap)
+						ok = false;
+					f0 = f1;
+				}
+				if (!ok)
+					return false;
+				// ---- rim: what the untouched neighbours offer each cut-out tile (marks stay on while everybody reads) ----
+				for (uint32_t base = 1; base < n; base += 32u)
+				{
+					const uint32_t idx = base + lane;
+					if (idx < n)
+					{
+						const uint32_t v = list[idx];
+						const uint32_t nl = inc_offer(dl, wr, wd, Wp, v, srcp);
+						if (nl != MTD_INF && nl >= SMALL_SETTLE_LIMIT)
+							ok = false;
+						dl[v] = nl == MTD_INF ? MTD_INF : (nl | INC_MARK);
+					}
+				}
+				__syncwarp();
+				if (!__all_sync(FULL_MASK, ok))
+					return false;
+				// ---- marks off; tiles with a label are the seeds (compacted in place: seeds never outrun the reads) ----
+				for (uint32_t base = 1; base < n; base += 32u)
+				{
+					const uint32_t idx = base + lane;
+					uint32_t v = 0, val = MTD_INF;
+					if (idx < n)
+					{
+						v = list[idx];
+						val = inc_lab(dl[v]);
+						dl[v] = val;
+					}
+					const bool seed = val != MTD_INF;
+					const uint32_t bal = __ballot_sync(FULL_MASK, seed);
+					__syncwarp();
+					if (seed)
+					{
+						const uint32_t pos = nseed + __popc(bal & lt);
+						if (pos < qseg)
+							list[pos] = (uint16_t)v;
+						seedmin = min(seedmin, val);
+					}
+					nseed += __popc(bal);
+					__syncwarp();
+				}
+				if (lane == 0)
+					dl[bp] = 0u; // parked again
+				if (nseed > qseg)
+					return false;
+				seedmin = warp_min_u32(seedmin);
+			}
+		}
+		else
+		{
+			// bp was blocked (label m in the previous layers), now it is a tile like any other
+			if (d_b_old != MTD_INF)
+				return false; // it already had a label: not the single flip this mode is for
+			const uint32_t nl = inc_offer(dl, wr, wd, Wp, bp, srcp);
+			if (nl != MTD_INF)
+			{
+				if (nl >= SMALL_SETTLE_LIMIT)
+					return false;
+				if (lane == 0)
+				{
+					dl[bp] = nl;
+					list[0] = (uint16_t)bp;
+				}
+				__syncwarp();
+				// label-correcting propagation, two lists in the halves of the scratch
+				const uint32_t half = cap / 2u;
+				uint32_t cur = 0, ncur = 1;
+				while (ncur != 0u)
+				{
+					const uint16_t *rq = list + cur * half;
+					uint16_t *wq = list + (cur ^ 1u) * half;
+					uint32_t nn = 0;
+					for (uint32_t base = 0; base < ncur; base += 32u)
+					{
+						const uint32_t idx = base + lane;
+						const bool act = idx < ncur;
+						const uint32_t cc = act ? rq[idx] : bp;
+						const uint32_t d = dl[cc];
+						const uint32_t base_nd = d + MIN_EDGE;
+						if (act && base_nd >= SMALL_SETTLE_LIMIT)
+							ok = false;
+#pragma unroll
+						for (int k = 0; k < 4; k++)
+						{
+							const uint32_t v = k == 0 ? cc - (uint32_t)Wp : k == 1 ? cc - 1u : k == 2 ? cc + 1u : cc + (uint32_t)Wp;
+							const uint32_t w = k == 0 ? wd[v] : k == 1 ? wr[v] : k == 2 ? wr[cc] : wd[cc];
+							const uint32_t nd = base_nd + w;
+							bool imp = false;
+							if (act && ok)
+								imp = nd < atomicMin(&dl[v], nd); // parked cells hold 0: never improved
+							const uint32_t bal = __ballot_sync(FULL_MASK, imp);
+							if (imp)
+							{
+								const uint32_t pos = nn + __popc(bal & lt);
+								if (pos < half)
+									wq[pos] = (uint16_t)v;
+							}
+							nn += __popc(bal);
+						}
+					}
+					__syncwarp();
+					if (nn > half || !__all_sync(FULL_MASK, ok))
+						return false;
+					ncur = nn;
+					cur ^= 1u;
+				}
+			}
+		}
+		if (lane == 0)
+		{
+			c[0] = nseed;
+			c[1] = c[2] = c[3] = 0u;
+			c[4] = seedmin;
+			c[5] = c[6] = c[7] = MTD_INF;
+			c[8] = c[9] = c[10] = c[11] = 0u;
+			c[12] = c[13] = c[14] = c[15] = MTD_INF;
+		}
+		return true;
+	}
+
 	// tiles[v] from final labels in the padded frame (closed form of the heap's tie-break, sssp_warp.cuh): the neighbour u
 	// with d[u] + w(u, v) == d[v] minimising (d[u], u); neighbours in ascending tile index (up, left, right, down), replace
 	// only on a strictly smaller d[u]. dv = dl[p] must be a reached, non-source label (not 0, not INF). A parked neighbour
@@ -531,7 +767,7 @@ namespace mtd
 		__shared__ __align__(8) uint64_t s_mbar;
 		__shared__ uint32_t s_fd[FIND_MAXN];
 		__shared__ uint32_t s_wp[MTD_MAXSRC_SMALL], s_srcp[MTD_MAXSRC_SMALL]; // waypoint / source tiles: grid index, padded index
-		__shared__ int s_guard;
+		__shared__ int s_guard, s_inc_fail;
 		__shared__ uint32_t s_map, s_chunk;
 		// the walker warp's private copies (it works on the PREVIOUS map while the workers overwrite the above)
 		__shared__ uint32_t w_wp[FIND_MAXN], w_D[FIND_MAXN * FIND_MAXN], w_fd[FIND_MAXN];
@@ -664,51 +900,95 @@ namespace mtd
 			for (int l0 = 0; l0 < n; l0 += R)
 			{
 				const int lb = (n - l0) < R ? (n - l0) : R; // layers in this pass
-				// ---- 3a. init: paths.cpp:40-43; blocked tiles and the padding are parked at 0 (never relaxed: >= 255 cannot lower 0) ----
-				for (int p = tid; p < Tp; p += SMALL_THREADS)
+				// ---- 3a'. incremental: the previous layers are the starting point, one warp per layer repairs what the flipped
+				//      tile changed (inc_repair); anything it cannot handle falls back to the full update below ----
+				bool inc = P.inc_tile != MTD_M && P.prev_dist && resident_all && P.nsrc <= 1;
+				if (inc)
 				{
-					const uint32_t yp = __umulhi((uint32_t)p, G.magicWp), x = (uint32_t)p - yp * (uint32_t)Wp;
-					uint32_t v = 0u;
-					if (yp >= 1u && yp <= (uint32_t)H && x < (uint32_t)W)
+					if (tid == 0)
+						s_inc_fail = 0;
+					workers_sync();
+					bool big = false;
+					for (int p = tid; p < Tp; p += SMALL_THREADS)
 					{
-						const uint32_t i = (uint32_t)p - yp - (uint32_t)W;
-						v = ((blk[i >> 5] >> (i & 31u)) & 1u) ? 0u : MTD_INF;
+						const uint32_t yp = __umulhi((uint32_t)p, G.magicWp), x = (uint32_t)p - yp * (uint32_t)Wp;
+						const bool cell = yp >= 1u && yp <= (uint32_t)H && x < (uint32_t)W;
+						const uint32_t i = cell ? (uint32_t)p - yp - (uint32_t)W : 0u;
+						const bool blocked = cell && ((blk[i >> 5] >> (i & 31u)) & 1u);
+						for (int r = 0; r < lb; r++)
+						{
+							uint32_t v = 0u;
+							if (cell && !blocked)
+							{
+								v = __ldcg(P.prev_dist + (size_t)(l0 + r) * T + i);
+								big |= v != MTD_INF && v >= INC_MARK - (1u << 17);
+							}
+							sdist[(size_t)r * Tp + p] = v;
+						}
 					}
-					for (int r = 0; r < lb; r++)
-						sdist[(size_t)r * Tp + p] = v;
+					if (big)
+						s_inc_fail = 1;
+					workers_sync();
+					if (warp < lb * GW && (warp % GW) == 0 && !s_inc_fail)
+					{
+						const int g = warp / GW;
+						const uint32_t b = P.inc_tile;
+						const bool now_blocked = (blk[b >> 5] >> (b & 31u)) & 1u;
+						const uint32_t d_b_old = __ldcg(P.prev_dist + (size_t)(l0 + g) * T + b);
+						if (!inc_repair(sdist + (size_t)g * Tp, wr, wd, Wp, G.g2p(b), s_srcp[l0 + g], now_blocked, d_b_old, q + (size_t)g * 2 * GW * qseg, (uint32_t)(2 * GW * qseg), (uint32_t)qseg, ctl + g * 16, lane) && lane == 0)
+							s_inc_fail = 1;
+					}
+					workers_sync();
+					inc = !s_inc_fail;
 				}
-				workers_sync();
-				// seeds: paths.cpp:48-49 (a blocked source still expands: the popped tile is never tested, paths.cpp:63-67)
-				if (warp < lb * GW && (warp % GW) == 0 && lane == 0)
+				if (!inc)
 				{
-					const int g = warp / GW;
-					uint32_t *dl = sdist + (size_t)g * Tp;
-					uint32_t *c = ctl + g * 16;
-					uint16_t *q0 = q + (size_t)g * 2 * GW * qseg;
-					uint32_t nseed = 0;
-					for (int s = 0; s < nsrc_layer; s++)
+					// ---- 3a. init: paths.cpp:40-43; blocked tiles and the padding are parked at 0 (never relaxed: >= 255 cannot lower 0) ----
+					for (int p = tid; p < Tp; p += SMALL_THREADS)
 					{
-						const uint32_t sp = P.nsrc > 1 ? s_srcp[s] : s_srcp[l0 + g];
-						bool dup = false;
-						for (int s2 = 0; s2 < s; s2++)
-							dup |= P.nsrc > 1 && s_srcp[s2] == sp;
-						if (dup)
-							continue;
-						dl[sp] = 0u;
-						if ((int)nseed < qseg)
-							q0[nseed] = (uint16_t)sp;
-						nseed++;
+						const uint32_t yp = __umulhi((uint32_t)p, G.magicWp), x = (uint32_t)p - yp * (uint32_t)Wp;
+						uint32_t v = 0u;
+						if (yp >= 1u && yp <= (uint32_t)H && x < (uint32_t)W)
+						{
+							const uint32_t i = (uint32_t)p - yp - (uint32_t)W;
+							v = ((blk[i >> 5] >> (i & 31u)) & 1u) ? 0u : MTD_INF;
+						}
+						for (int r = 0; r < lb; r++)
+							sdist[(size_t)r * Tp + p] = v;
 					}
-					c[0] = nseed;
-					c[1] = c[2] = c[3] = 0u;
-					c[4] = 0u;
-					c[5] = c[6] = c[7] = MTD_INF;
-					// slots of warps that do not exist (GW < 4) stay empty in both parities
-					c[8] = c[9] = c[10] = c[11] = 0u;
-					c[12] = c[13] = c[14] = c[15] = MTD_INF;
-				}
-				workers_sync();
+					workers_sync();
+					// seeds: paths.cpp:48-49 (a blocked source still expands: the popped tile is never tested, paths.cpp:63-67)
+					if (warp < lb * GW && (warp % GW) == 0 && lane == 0)
+					{
+						const int g = warp / GW;
+						uint32_t *dl = sdist + (size_t)g * Tp;
+						uint32_t *c = ctl + g * 16;
+						uint16_t *q0 = q + (size_t)g * 2 * GW * qseg;
+						uint32_t nseed = 0;
+						for (int s = 0; s < nsrc_layer; s++)
+						{
+							const uint32_t sp = P.nsrc > 1 ? s_srcp[s] : s_srcp[l0 + g];
+							bool dup = false;
+							for (int s2 = 0; s2 < s; s2++)
+								dup |= P.nsrc > 1 && s_srcp[s2] == sp;
+							if (dup)
+								continue;
+							dl[sp] = 0u;
+							if ((int)nseed < qseg)
+								q0[nseed] = (uint16_t)sp;
+							nseed++;
+						}
+						c[0] = nseed;
+						c[1] = c[2] = c[3] = 0u;
+						c[4] = 0u;
+						c[5] = c[6] = c[7] = MTD_INF;
+						// slots of warps that do not exist (GW < 4) stay empty in both parities
+						c[8] = c[9] = c[10] = c[11] = 0u;
+						c[12] = c[13] = c[14] = c[15] = MTD_INF;
+					}
+					workers_sync();
 
+				}
 				// ---- 3b. relaxation: GW warps per layer, one named barrier per bucket ----
 				if (warp < lb * GW)
 				{

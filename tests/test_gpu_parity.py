@@ -1109,3 +1109,84 @@ def test_towers_attack_pass_matches_oracle(ctx, oracle, nmon, ntow):
             oracle.monsters_dots_tick(dur, dmg, life, a["alive"])
     assert fired > ntow // 4  # towers really fired
     assert (hits > 1).any()  # and splashes hit several monsters
+
+
+# ---------------------------------------------------------------------------------------------------
+# incremental re-pathing (one blocking flip -> the resident layers are repaired)
+# ---------------------------------------------------------------------------------------------------
+def test_incremental_repathing_matches_full_updates(ctx, oracle):
+    """random single place / remove flips on a generated map, each followed by Waypoints::update through the repair path
+    (the statistics prove it was taken) and compared with the oracle's from-scratch result: all layers, next hops, paths,
+    aggregates; plus the trial of placingBuildingBlocksMonsters, which reuses layer 0 (buildingsPlacement.cpp:18-42)"""
+    from mazetd_b200 import game_events
+
+    o = oracle.mapgen(KAT_SEED[0] + 5, KAT_SEED[1], cap=2048)
+    W = H = 101
+    flags = o["flags"].copy()
+    wp = o["wp_tiles"]
+    ctx.debug_set(ctx.DEBUG_INCREMENTAL, 1)
+    ctx.grid_upload(W, H, o["elev"], flags, 50, 50)
+    ctx.waypoints_update(wp, cap=2048)
+    rng = np.random.default_rng(11)
+    sp = int(o["agg"][2])
+    path = o["fullpath"][sp][: int(o["fullpath_len"][sp])]
+    mon = game_events.initial_monsters(500, path, wp, ctx.waypoints_find)
+    ctx.monsters_upload(mon)
+    passable = np.flatnonzero((flags & (synth.FLAG_INVALID | synth.FLAG_WAYPOINT)) == 0)
+    on_path = [int(t) for t in path[3:-3:7] if (flags[t] & synth.FLAG_WAYPOINT) == 0]
+    cands = on_path[:12] + [int(t) for t in rng.choice(passable, 40)]
+    base = ctx.big_stats()
+    placed = []
+    checked_trials = 0
+    for step, t in enumerate(cands):
+        if flags[t] & synth.FLAG_BUILDING:
+            continue
+        # trial on the current grid (layers are up to date: the repair path of layer 0)
+        got = ctx.placing_blocks(t)
+        want = oracle.placing_blocks(W, H, o["elev"], flags, wp, t, mon["tile"], mon["alive"], 50, 50)
+        assert bool(got) == bool(want), (step, t)
+        checked_trials += 1
+        if want:
+            continue
+        flags[t] |= synth.FLAG_BUILDING
+        ctx.grid_set_flags(t, int(flags[t]))
+        placed.append(t)
+        w = ctx.waypoints_update(wp, cap=2048)
+        wo = oracle.waypoints_update(W, H, o["elev"], flags, wp, 50, 50, cap=2048)
+        for key in ("dist", "tiles", "fullpath_len", "full_distance", "agg", "fullpath"):
+            assert np.array_equal(w[key], wo[key]), (step, t, key)
+        if step % 3 == 2 and placed:
+            # sell an earlier tower again: labels only drop, behind the freed tile
+            r = placed.pop(int(rng.integers(0, len(placed))))
+            flags[r] &= ~np.uint16(synth.FLAG_BUILDING)
+            ctx.grid_set_flags(r, int(flags[r]))
+            w = ctx.waypoints_update(wp, cap=2048)
+            wo = oracle.waypoints_update(W, H, o["elev"], flags, wp, 50, 50, cap=2048)
+            for key in ("dist", "tiles", "fullpath_len", "full_distance", "agg", "fullpath"):
+                assert np.array_equal(w[key], wo[key]), (step, "sell", r, key)
+    st = ctx.big_stats()
+    assert st["rounds"] - base["rounds"] >= 20, st  # incremental updates taken
+    assert st["visits"] - base["visits"] >= 10, st  # incremental trials taken
+    assert checked_trials >= 30
+    # the drop-in adapter's pattern: the whole grid is uploaded again with one flag changed -> still a repair
+    t = int(passable[len(passable) // 2])
+    if not (flags[t] & synth.FLAG_BUILDING):
+        flags[t] |= synth.FLAG_BUILDING
+        ctx.grid_upload(W, H, o["elev"], flags, 50, 50)
+        before = ctx.big_stats()["rounds"]
+        w = ctx.waypoints_update(wp, cap=2048)
+        assert ctx.big_stats()["rounds"] == before + 1
+        wo = oracle.waypoints_update(W, H, o["elev"], flags, wp, 50, 50, cap=2048)
+        for key in ("dist", "tiles", "fullpath_len", "full_distance", "agg", "fullpath"):
+            assert np.array_equal(w[key], wo[key]), ("re-upload", key)
+    # two flips between updates: from scratch, same answer
+    a, b = int(passable[7]), int(passable[len(passable) - 9])
+    for t in (a, b):
+        flags[t] ^= np.uint16(synth.FLAG_BUILDING)
+        ctx.grid_set_flags(t, int(flags[t]))
+    before = ctx.big_stats()["rounds"]
+    w = ctx.waypoints_update(wp, cap=2048)
+    assert ctx.big_stats()["rounds"] == before
+    wo = oracle.waypoints_update(W, H, o["elev"], flags, wp, 50, 50, cap=2048)
+    for key in ("dist", "tiles", "agg"):
+        assert np.array_equal(w[key], wo[key]), ("two flips", key)
