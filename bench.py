@@ -568,6 +568,7 @@ def leg_c1_c3(ctx, args, cpu):
         lat.append(time.perf_counter() - t0)
         ctx.grid_set_flags(cand, int(flags[cand]))  # untimed: the tower is sold again and the layers follow (clearStructure path)
         ctx.waypoints_update_dev(wp)
+        ctx.synchronize()
     med = float(np.median(lat[20:]))
     res = []
     for rep in range(120):

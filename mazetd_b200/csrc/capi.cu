@@ -1591,7 +1591,17 @@ namespace
 			return fail(ctx, MTD_ERR_STATE, "no stripe uploaded");
 		const PeerLayout L = peer_layout(ctx->W);
 		if (ctx->peer_blk.cap >= L.words)
+		{
+			// (Re-)connecting: the barrier words restart from zero and the halo / key arrays from "nothing offered", so a rank
+			// that timed out in an earlier run cannot leave the ranks at different epochs (every rank resets its OWN block here;
+			// the caller's host barrier after the connect makes sure nobody launches before all blocks are reset)
+			CU(cudaMemsetAsync(ctx->peer_blk.p, 0xFF, L.words * 4, ctx->stream));
+			CU(cudaMemsetAsync(ctx->peer_blk.p, 0, PEER_CTL_WORDS * 4, ctx->stream));
+			CU(cudaStreamSynchronize(ctx->stream));
 			return MTD_OK;
+		}
+		if (ctx->peer_linked)
+			return fail(ctx, MTD_ERR_STATE, "the stripe grew while its peer block is mapped by other ranks: destroy the contexts and connect again");
 		CU(ctx->peer_blk.reserve(L.words));
 		// halo rows and key arrays: m (nothing offered); control words: 0, smallest keys m
 		CU(cudaMemsetAsync(ctx->peer_blk.p, 0xFF, L.words * 4, ctx->stream));

@@ -398,6 +398,7 @@ namespace mtd
 	// Labels of cells that belong to the subtree under repair carry INC_MARK; inc_lab() strips it. All finite labels are
 	// below INC_MARK in this mode (checked when the previous layers are loaded).
 	constexpr uint32_t INC_MARK = 0x80000000u;
+	constexpr uint32_t INC_MAX_LEVELS = 20;
 
 	__device__ __forceinline__ uint32_t inc_lab(uint32_t v)
 	{
@@ -474,9 +475,13 @@ namespace mtd
 					list[0] = (uint16_t)bp;
 				}
 				__syncwarp();
-				uint32_t f0 = 0, n = 1;
+				uint32_t f0 = 0, n = 1, levels = 0;
 				while (f0 < n && ok)
 				{
+					// a level costs ~1 us of dependent shared-memory accesses on one warp, a bucket of the full update ~0.6 us
+					// for the whole layer: a subtree deeper than this is cheaper to recompute (r02m: the first path tile)
+					if (++levels > INC_MAX_LEVELS)
+						return false;
 					const uint32_t f1 = n;
 					for (uint32_t base = f0; base < f1; base += 32u)
 					{
