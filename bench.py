@@ -816,33 +816,6 @@ def run_ours(args):
     relax_per_step = maps * T * NWP * world
     value = relax_per_step / (ms_step * 1e-3)
 
-    # ---- the same batch in STRONG form: 4096 maps in total, a contiguous block of map indices per rank (BASELINE.json
-    #      configs[1]: "sharded per GPU at 2/4/8"); the weak form above keeps 4096 maps on every GPU ----
-    strong = None
-    if world > 1:
-        from mazetd_b200 import shard
-
-        s_first, s_last = shard.map_range(rank, world, maps)
-        s_n = s_last - s_first
-
-        def step_strong():
-            ctx.mapgen_batch_dev(KAT_SEED[0], KAT_SEED[1], s_first, s_n, ptrs, W, H, 50, 50, 45, NWP, FULLPATH_CAP)
-
-        for _ in range(3):
-            step_strong()
-        barrier()
-        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        f0.record(stream)
-        for _ in range(args.steps):
-            step_strong()
-        f1.record(stream)
-        barrier()
-        ts = torch.tensor([f0.elapsed_time(f1)], dtype=torch.float64, device=dev)
-        dist.all_reduce(ts, op=dist.ReduceOp.MAX)
-        ms_strong = float(ts.item()) / args.steps
-        strong = {"scaling": "strong", "maps_total": maps, "maps_per_gpu": s_n, "ms_per_step": ms_strong, "value": maps * T * NWP / (ms_strong * 1e-3), "unit": "tile relaxations/s",
-                  "map_rebuilds_per_s": maps / (ms_strong * 1e-3)}
-
     # ---- roofline of the dominant kernel (k_waypoints_small): algorithmic bytes per DESIGN.md ----
     peaks = {}
     try:
@@ -922,6 +895,33 @@ def run_ours(args):
             "d2h_bytes_per_step": d2h,
             "api": "mtd_mapgen_batch (include/mazetd_b200.h), pinned host outputs, synchronous",
         }
+
+    # ---- the same batch in STRONG form: 4096 maps in total, a contiguous block of map indices per rank (BASELINE.json
+    #      configs[1]: "sharded per GPU at 2/4/8"); the weak form above keeps 4096 maps on every GPU ----
+    strong = None
+    if world > 1:
+        from mazetd_b200 import shard
+
+        s_first, s_last = shard.map_range(rank, world, maps)
+        s_n = s_last - s_first
+
+        def step_strong():
+            ctx.mapgen_batch_dev(KAT_SEED[0], KAT_SEED[1], s_first, s_n, ptrs, W, H, 50, 50, 45, NWP, FULLPATH_CAP)
+
+        for _ in range(3):
+            step_strong()
+        barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record(stream)
+        for _ in range(args.steps):
+            step_strong()
+        f1.record(stream)
+        barrier()
+        ts = torch.tensor([f0.elapsed_time(f1)], dtype=torch.float64, device=dev)
+        dist.all_reduce(ts, op=dist.ReduceOp.MAX)
+        ms_strong = float(ts.item()) / args.steps
+        strong = {"scaling": "strong", "maps_total": maps, "maps_per_gpu": s_n, "ms_per_step": ms_strong, "value": maps * T * NWP / (ms_strong * 1e-3), "unit": "tile relaxations/s",
+                  "map_rebuilds_per_s": maps / (ms_strong * 1e-3)}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:

@@ -70,6 +70,7 @@ namespace mtd
 		// whose blocking state flipped since (sources/player/buildingsPlacement.cpp:120-130, 143-164, trial :18-42)
 		const uint32_t *prev_dist; // [n][T] distances before the flip (may alias `dist`), or null
 		uint32_t inc_tile;         // the flipped tile, MTD_M = none (full update). Needs nmaps == 1, n <= R, nsrc == 1
+		uint32_t delta;            // bucket width of the relaxation (0 = MIN_EDGE: label-setting)
 	};
 
 	// ---- geometry of the padded frame -------------------------------------------------------------------------
@@ -233,8 +234,13 @@ namespace mtd
 	// [parity][4..7] = min pending label each warp saw. q: [parity][warp][qseg] linear cell indices. Initial state
 	// (parity 0) is written by the caller. Returns true if a label hit the guard band.
 	template<int GW>
-	__device__ bool group_relax(uint32_t *dist, const uint16_t *wr, const uint16_t *wd, uint16_t *q, uint32_t *ctl, int Wp, int Tp, int qseg, int gw, uint32_t lane, int bar_id)
+	__device__ bool group_relax(uint32_t *dist, const uint16_t *wr, const uint16_t *wd, uint16_t *q, uint32_t *ctl, int Wp, int Tp, int qseg, int gw, uint32_t lane, int bar_id, uint32_t delta = MIN_EDGE)
 	{
+		// delta = MIN_EDGE (255, the smallest edge weight): every label below the threshold is final (label-setting, a cell is
+		// queued once). A wider bucket takes fewer of the barrier-separated steps that bound this kernel; a cell settled with a
+		// label that a later relaxation of the same bucket lowers is queued again (label-correcting inside the bucket: any width
+		// reaches the same fixpoint).
+		const bool wide = delta > MIN_EDGE;
 		const uint32_t lt = lanemask_lt();
 		uint32_t parity = 0, thr_prev = 0;
 		bool guard = false, dense = false;
@@ -251,7 +257,7 @@ namespace mtd
 			const uint32_t dmin = min(min(mn.x, mn.y), min(mn.z, mn.w));
 			if (dmin == MTD_INF)
 				break; // nothing pending
-			const uint32_t thr = dmin + MIN_EDGE; // dmin < SMALL_SETTLE_LIMIT or every pending cell is reported below
+			const uint32_t thr = dmin + delta; // dmin < SMALL_SETTLE_LIMIT or every pending cell is reported below
 			const uint32_t cap = (uint32_t)qseg;
 			dense = dense || cn.x > cap || cn.y > cap || cn.z > cap || cn.w > cap; // an append was dropped: the queue is incomplete from now on
 			uint32_t newmin = MTD_INF, outn = 0;
@@ -300,7 +306,9 @@ namespace mtd
 					}
 					// a cell enters the queue exactly once: when its label leaves "unreached" (labels of queued cells may
 					// still improve before they settle, settled labels are final)
-					const bool f0 = settle && o0 == MTD_INF, f1 = settle && o1 == MTD_INF, f2 = settle && o2 == MTD_INF, f3 = settle && o3 == MTD_INF;
+					// (wide buckets: also when a label already below the threshold -- settled in this bucket -- drops again)
+					const bool f0 = settle && (o0 == MTD_INF || (wide && n0 < o0 && o0 < thr)), f1 = settle && (o1 == MTD_INF || (wide && n1 < o1 && o1 < thr));
+					const bool f2 = settle && (o2 == MTD_INF || (wide && n2 < o2 && o2 < thr)), f3 = settle && (o3 == MTD_INF || (wide && n3 < o3 && o3 < thr));
 					uint32_t lm = keep ? d : MTD_INF;
 					lm = settle && n0 < o0 ? min(lm, n0) : lm;
 					lm = settle && n1 < o1 ? min(lm, n1) : lm;
@@ -343,13 +351,15 @@ namespace mtd
 				for (int c = gw * 32 + (int)lane; c < Tp; c += GW * 32)
 				{
 					const uint32_t d = dist[c];
-					bool settle = d >= thr_prev && d < thr;
+					// wide buckets: a label below thr_prev may have dropped again, so a dense round relaxes every reached cell
+					// and the rounds go on until nothing improves (Bellman-Ford; only after a queue overflow)
+					bool settle = wide ? (d != 0u && d != MTD_INF) : (d >= thr_prev && d < thr);
 					if (settle && d >= SMALL_SETTLE_LIMIT)
 					{
 						guard = true;
 						settle = false;
 					}
-					if (d >= thr && d < SMALL_SETTLE_LIMIT)
+					if (!wide && d >= thr && d < SMALL_SETTLE_LIMIT)
 						newmin = min(newmin, d);
 					else if (d >= SMALL_SETTLE_LIMIT && d != MTD_INF)
 						guard = true;
@@ -998,7 +1008,7 @@ namespace mtd
 				if (warp < lb * GW)
 				{
 					const int g = warp / GW;
-					if (group_relax<GW>(sdist + (size_t)g * Tp, wr, wd, q + (size_t)g * 2 * GW * qseg, ctl + g * 16, Wp, Tp, qseg, warp % GW, lane, 2 + g) && lane == 0)
+					if (group_relax<GW>(sdist + (size_t)g * Tp, wr, wd, q + (size_t)g * 2 * GW * qseg, ctl + g * 16, Wp, Tp, qseg, warp % GW, lane, 2 + g, P.delta ? P.delta : MIN_EDGE) && lane == 0)
 						s_guard = 1;
 				}
 				workers_sync();
