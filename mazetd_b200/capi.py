@@ -133,8 +133,6 @@ class Context:
         if rc != 0:
             raise MtdError(rc, "mtd_create failed (no CUDA device? the library has no CPU fallback)")
         self.h = h
-        if os.environ.get("MTD_SMALL_DELTA"):  # developer probe: bucket width of the one-CTA relaxation
-            self.L.mtd_debug_set(self.h, 11, int(os.environ["MTD_SMALL_DELTA"]))
         self.W = self.H = self.T = 0
 
     def close(self):
@@ -156,7 +154,6 @@ class Context:
     DEBUG_ASYNC_DELTA = 6
     DEBUG_BIG_TMA = 7
     DEBUG_INCREMENTAL = 10
-    DEBUG_SMALL_DELTA = 11
     DEBUG_ASYNC_NB_RULE = 8
     DEBUG_ASYNC_DEPTH = 9
 

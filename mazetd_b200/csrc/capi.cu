@@ -167,7 +167,6 @@ struct mtd_ctx
 	DevBuf<uint32_t> map_counter;
 	int debug_qseg_cap = 0;
 	int debug_gw = SMALL_GROUP_WARPS;
-	uint32_t small_delta = 0; // bucket width of the one-CTA relaxation (0 = 255, label-setting)
 	int debug_walker = 0; // 0 auto, 1 never, 2 always
 	DevBuf<uint32_t> scratch_tiles, scratch_dist;
 	DevBuf<int16_t> scratch_elev_in, scratch_elev;
@@ -400,7 +399,6 @@ namespace
 			return fail(ctx, MTD_ERR_CAPACITY, "map of %d tiles with %d layers does not fit shared memory", T, P.n);
 		P.smem_budget = (uint32_t)MAX_SMEM;
 		P.qseg_cap = ctx->debug_qseg_cap;
-		P.delta = ctx->small_delta;
 		const SmallLayout L = small_layout(P.W, P.H, P.R, P.smem_budget, P.qseg_cap, GW);
 		if (kernel_config(ctx, (const void *)k_waypoints_small<GW>, SMALL_THREADS + 32, MAX_SMEM) < 0)
 			return MTD_ERR_CUDA;
@@ -1198,11 +1196,6 @@ extern "C" int mtd_debug_set(mtd_ctx *ctx, int key, int64_t value)
 		return MTD_OK;
 	case MTD_DEBUG_ASYNC_DEPTH:
 		ctx->async_depth = value >= 2 ? 2 : 1;
-		return MTD_OK;
-	case MTD_DEBUG_SMALL_DELTA:
-		if (value < 0 || value > 0xFFFFFF)
-			return fail(ctx, MTD_ERR_ARG, "bucket width must be in 0 .. 2^24");
-		ctx->small_delta = value < 255 ? 0u : (uint32_t)value;
 		return MTD_OK;
 	case MTD_DEBUG_INCREMENTAL:
 		ctx->inc_enabled = value != 0;

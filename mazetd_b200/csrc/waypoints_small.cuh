@@ -70,7 +70,6 @@ namespace mtd
 		// whose blocking state flipped since (sources/player/buildingsPlacement.cpp:120-130, 143-164, trial :18-42)
 		const uint32_t *prev_dist; // [n][T] distances before the flip (may alias `dist`), or null
 		uint32_t inc_tile;         // the flipped tile, MTD_M = none (full update). Needs nmaps == 1, n <= R, nsrc == 1
-		uint32_t delta;            // bucket width of the relaxation (0 = MIN_EDGE: label-setting)
 	};
 
 	// ---- geometry of the padded frame -------------------------------------------------------------------------
@@ -224,8 +223,20 @@ namespace mtd
 		acc__[k] += (unsigned long long)(now__ - last__);     \
 		last__ = now__;                                       \
 	} while (0)
+	__device__ unsigned long long g_phase[8];
+#define MTD_PHASE(k)                                                   \
+	do                                                                 \
+	{                                                                  \
+		if (blockIdx.x == 0 && threadIdx.x == 0)                       \
+		{                                                              \
+			const long long now__ = clock64();                         \
+			g_phase[k] += (unsigned long long)(now__ - phase_last__);  \
+			phase_last__ = now__;                                      \
+		}                                                              \
+	} while (0)
 #else
 #define MTD_TICK(k)
+#define MTD_PHASE(k)
 #endif
 
 	// ---- one layer, GW warps ---------------------------------------------------------------------------------------
@@ -234,13 +245,8 @@ namespace mtd
 	// [parity][4..7] = min pending label each warp saw. q: [parity][warp][qseg] linear cell indices. Initial state
 	// (parity 0) is written by the caller. Returns true if a label hit the guard band.
 	template<int GW>
-	__device__ bool group_relax(uint32_t *dist, const uint16_t *wr, const uint16_t *wd, uint16_t *q, uint32_t *ctl, int Wp, int Tp, int qseg, int gw, uint32_t lane, int bar_id, uint32_t delta = MIN_EDGE)
+	__device__ bool group_relax(uint32_t *dist, const uint16_t *wr, const uint16_t *wd, uint16_t *q, uint32_t *ctl, int Wp, int Tp, int qseg, int gw, uint32_t lane, int bar_id)
 	{
-		// delta = MIN_EDGE (255, the smallest edge weight): every label below the threshold is final (label-setting, a cell is
-		// queued once). A wider bucket takes fewer of the barrier-separated steps that bound this kernel; a cell settled with a
-		// label that a later relaxation of the same bucket lowers is queued again (label-correcting inside the bucket: any width
-		// reaches the same fixpoint).
-		const bool wide = delta > MIN_EDGE;
 		const uint32_t lt = lanemask_lt();
 		uint32_t parity = 0, thr_prev = 0;
 		bool guard = false, dense = false;
@@ -257,7 +263,7 @@ namespace mtd
 			const uint32_t dmin = min(min(mn.x, mn.y), min(mn.z, mn.w));
 			if (dmin == MTD_INF)
 				break; // nothing pending
-			const uint32_t thr = dmin + delta; // dmin < SMALL_SETTLE_LIMIT or every pending cell is reported below
+			const uint32_t thr = dmin + MIN_EDGE; // dmin < SMALL_SETTLE_LIMIT or every pending cell is reported below
 			const uint32_t cap = (uint32_t)qseg;
 			dense = dense || cn.x > cap || cn.y > cap || cn.z > cap || cn.w > cap; // an append was dropped: the queue is incomplete from now on
 			uint32_t newmin = MTD_INF, outn = 0;
@@ -306,9 +312,7 @@ namespace mtd
 					}
 					// a cell enters the queue exactly once: when its label leaves "unreached" (labels of queued cells may
 					// still improve before they settle, settled labels are final)
-					// (wide buckets: also when a label already below the threshold -- settled in this bucket -- drops again)
-					const bool f0 = settle && (o0 == MTD_INF || (wide && n0 < o0 && o0 < thr)), f1 = settle && (o1 == MTD_INF || (wide && n1 < o1 && o1 < thr));
-					const bool f2 = settle && (o2 == MTD_INF || (wide && n2 < o2 && o2 < thr)), f3 = settle && (o3 == MTD_INF || (wide && n3 < o3 && o3 < thr));
+					const bool f0 = settle && o0 == MTD_INF, f1 = settle && o1 == MTD_INF, f2 = settle && o2 == MTD_INF, f3 = settle && o3 == MTD_INF;
 					uint32_t lm = keep ? d : MTD_INF;
 					lm = settle && n0 < o0 ? min(lm, n0) : lm;
 					lm = settle && n1 < o1 ? min(lm, n1) : lm;
@@ -351,15 +355,13 @@ namespace mtd
 				for (int c = gw * 32 + (int)lane; c < Tp; c += GW * 32)
 				{
 					const uint32_t d = dist[c];
-					// wide buckets: a label below thr_prev may have dropped again, so a dense round relaxes every reached cell
-					// and the rounds go on until nothing improves (Bellman-Ford; only after a queue overflow)
-					bool settle = wide ? (d != 0u && d != MTD_INF) : (d >= thr_prev && d < thr);
+					bool settle = d >= thr_prev && d < thr;
 					if (settle && d >= SMALL_SETTLE_LIMIT)
 					{
 						guard = true;
 						settle = false;
 					}
-					if (!wide && d >= thr && d < SMALL_SETTLE_LIMIT)
+					if (d >= thr && d < SMALL_SETTLE_LIMIT)
 						newmin = min(newmin, d);
 					else if (d >= SMALL_SETTLE_LIMIT && d != MTD_INF)
 						guard = true;
@@ -804,6 +806,9 @@ namespace mtd
 			asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 		}
 
+#ifdef MTD_TIMING
+		long long phase_last__ = clock64();
+#endif
 		for (;;)
 		{
 			__syncthreads(); // all 544 threads: the previous map is completely written out and the walker finished the one before
@@ -811,6 +816,7 @@ namespace mtd
 				s_map = atomicAdd(P.map_counter, 1u);
 			__syncthreads();
 			const int mapi = (int)s_map;
+			MTD_PHASE(0); // waiting for the walker / claiming a map
 			if (warp == SMALL_WALKER_WARP)
 			{
 				// ---- walker warp: paths of the map the workers finished last, from its layers in global memory (still in L2) ----
@@ -891,6 +897,7 @@ namespace mtd
 				mbar_phase ^= 1u;
 				workers_sync();
 			}
+			MTD_PHASE(1); // staging
 
 			// ---- 2. edge weights (Grid::neighborDistance of the right and down edge, grid.cpp:141-145) + blocking bitmap ----
 			for (int base = 0; base < T; base += SMALL_THREADS)
@@ -911,6 +918,7 @@ namespace mtd
 					blk[(base >> 5) + warp] = bal;
 			}
 			workers_sync(); // staging is dead from here on: the distance layers take its place
+			MTD_PHASE(2); // weights
 
 			for (int l0 = 0; l0 < n; l0 += R)
 			{
@@ -1004,14 +1012,16 @@ namespace mtd
 					workers_sync();
 
 				}
+				MTD_PHASE(3); // init + seeds (or incremental repair)
 				// ---- 3b. relaxation: GW warps per layer, one named barrier per bucket ----
 				if (warp < lb * GW)
 				{
 					const int g = warp / GW;
-					if (group_relax<GW>(sdist + (size_t)g * Tp, wr, wd, q + (size_t)g * 2 * GW * qseg, ctl + g * 16, Wp, Tp, qseg, warp % GW, lane, 2 + g, P.delta ? P.delta : MIN_EDGE) && lane == 0)
+					if (group_relax<GW>(sdist + (size_t)g * Tp, wr, wd, q + (size_t)g * 2 * GW * qseg, ctl + g * 16, Wp, Tp, qseg, warp % GW, lane, 2 + g) && lane == 0)
 						s_guard = 1;
 				}
 				workers_sync();
+				MTD_PHASE(4); // relaxation (slowest layer)
 
 				// ---- 4. full-path walks (one lane per spawner) overlapped with next-hop tiles + write-out of this pass ----
 				// Blocked tiles are still parked at 0 in the resident layers: every reader below maps "0 and not this layer's
@@ -1126,6 +1136,7 @@ namespace mtd
 					}
 				}
 				workers_sync();
+				MTD_PHASE(5); // next hops + write-out
 				if (tid == 0)
 					s_chunk = 0;
 			}
@@ -1151,8 +1162,9 @@ namespace mtd
 		if (blockIdx.x == 0 && tid == 0)
 		{
 			printf("TIMING rounds=%llu items=%llu | ctl+thr=%llu body=%llu redux+sts=%llu barrier=%llu looptop=%llu (cycles, warp 0 of layer 0, CTA 0)\n", g_timing[5], g_timing[6], g_timing[0], g_timing[1], g_timing[2], g_timing[3], g_timing[4]);
+			printf("PHASES wait=%llu stage=%llu weights=%llu init=%llu relax=%llu writeout=%llu (cycles, CTA 0)\n", g_phase[0], g_phase[1], g_phase[2], g_phase[3], g_phase[4], g_phase[5]);
 			for (int k = 0; k < 8; k++)
-				g_timing[k] = 0;
+				g_timing[k] = g_phase[k] = 0;
 		}
 #endif
 	}

@@ -1214,3 +1214,31 @@ def test_incremental_repathing_matches_full_updates(ctx, oracle):
     wo = oracle.waypoints_update(W, H, o["elev"], flags, wp, 50, 50, cap=2048)
     for key in ("dist", "tiles", "agg"):
         assert np.array_equal(w[key], wo[key]), ("two flips", key)
+
+
+def test_scripted_events_at_a_larger_size(ctx, oracle):
+    """the C3 script two orders of magnitude above the golden fixture's size: 1 500 events x 200 000 monsters (3e8 monster
+    ticks, several hundred rebuilds and trials through the incremental path), every integer of the final state against the
+    oracle; the bench runs 10 000 x 1 000 000 of the same script"""
+    from mazetd_b200 import game_events
+    from oracle_lib import OracleGame
+
+    o = oracle.mapgen(KAT_SEED[0], KAT_SEED[1])
+    W = H = 101
+    ctx.grid_upload(W, H, o["elev"], o["flags"], 50, 50)
+    ctx.waypoints_update_dev(o["wp_tiles"])
+    sp = int(o["agg"][2])
+    mon = game_events.initial_monsters(200000, o["fullpath"][sp][: int(o["fullpath_len"][sp])], o["wp_tiles"], ctx.waypoints_find, speed_range=(0.03, 0.3))
+    og = OracleGame(oracle, W, H, o["elev"], o["flags"], o["wp_tiles"], {k: v.copy() for k, v in mon.items()})
+    gg = game_events.GpuGame(ctx, W, H, o["elev"], o["flags"], o["wp_tiles"])
+    ctx.monsters_upload(mon)
+    sg = game_events.run_events(gg, 1500)
+    so = game_events.run_events(og, 1500)
+    assert sg == so and sg["placed"] > 100 and sg["cleared"] >= 5, (sg, so)
+    assert np.array_equal(gg.flags, og.flags)
+    got = ctx.monsters_download()
+    for k in got:
+        assert np.array_equal(got[k], og.a[k]), k
+    w = ctx.waypoints_update(o["wp_tiles"], cap=2048)
+    for key in ("dist", "tiles", "full_distance", "agg"):
+        assert np.array_equal(w[key], og.w[key]), key
