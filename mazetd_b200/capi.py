@@ -133,6 +133,11 @@ class Context:
         if rc != 0:
             raise MtdError(rc, "mtd_create failed (no CUDA device? the library has no CPU fallback)")
         self.h = h
+        # developer probe: MTD_DEBUG="key=value,key=value" applies mtd_debug_set to every new context (performance knobs only)
+        for kv in filter(None, os.environ.get("MTD_DEBUG", "").split(",")):
+            k, v = kv.split("=")
+            if self.L.mtd_debug_set(self.h, int(k), int(v)) != 0:
+                raise MtdError(-1, "MTD_DEBUG: key %s rejected" % k)
         self.W = self.H = self.T = 0
 
     def close(self):

@@ -86,6 +86,12 @@ namespace mtd
 		const uint32_t magicW = W > 1 ? (uint32_t)((0x100000000ull + (uint32_t)W - 1u) / (uint32_t)W) : 0u; // y = umulhi(i, magicW) for i < 65536, W <= 256
 
 		noise::fill_gradients(grad);
+#ifdef MTD_TIMING
+		long long phase_last__ = clock64();
+#define MTD_GPHASE(k) do { if (blockIdx.x == 0 && threadIdx.x == 0) { const long long now__ = clock64(); g_phase[8 + k] += (unsigned long long)(now__ - phase_last__); phase_last__ = now__; } } while (0)
+#else
+#define MTD_GPHASE(k)
+#endif
 
 		for (int mapi = blockIdx.x; mapi < P.nmaps; mapi += gridDim.x)
 		{
@@ -110,6 +116,7 @@ namespace mtd
 				best_key = 0ull;
 			}
 			__syncthreads();
+			MTD_GPHASE(0); // rng
 
 			// ---- elevations: grid.cpp:153-159 ----
 			const noise::ElevationParams lp = ep;
@@ -129,6 +136,7 @@ namespace mtd
 					elev[i] = rtos16(e);
 				}
 			__syncthreads();
+			MTD_GPHASE(1); // noise
 
 			// ---- biome flags, slope, radius: grid.cpp:160-183 (thresholds are rtos16(-7), (1), (6), (0.35)) ----
 			for (int i = threadIdx.x; i < T; i += blockDim.x)
@@ -174,6 +182,7 @@ namespace mtd
 				parent[i] = (uint32_t)i;
 			}
 			__syncthreads();
+			MTD_GPHASE(2); // flags
 
 			// ---- fillUnreachable: grid.cpp:29-78 as union-find (root = lowest tile index = discovery order) ----
 			// (1) horizontal runs by warp ballot: every valid tile points at the start of its run inside its 32-tile chunk
@@ -253,6 +262,7 @@ namespace mtd
 				if (flags[i] == F_INVALID || !any_valid || (parent[i] & 0xFFFFu) != best_root)
 					flags[i] = F_INVALID;
 			__syncthreads();
+			MTD_GPHASE(3); // components
 
 			// ---- findBorder + Mana: grid.cpp:80-97, 186-196 (border bits only land on invalid tiles, so in-place is safe) ----
 			for (int i = threadIdx.x; i < T; i += blockDim.x)
@@ -274,6 +284,7 @@ namespace mtd
 				flags[i] = f;
 			}
 			__syncthreads();
+			MTD_GPHASE(4); // border
 
 			// ---- newWaypoints spawn picking: paths.cpp:173-183, 190-196 (inherently sequential in the RNG stream) ----
 			if (threadIdx.x == 0)
@@ -298,6 +309,7 @@ namespace mtd
 					atomicOr(P.status, ST_NO_VALID);
 			}
 			__syncthreads();
+			MTD_GPHASE(5); // spawn picking
 
 			// ---- write out (coalesced 4-byte words; T even-padded arrays are 4-byte aligned per map only if T is even,
 			//      so use 2-byte stores: 40 KB per map, negligible next to the layers) ----
@@ -308,6 +320,15 @@ namespace mtd
 				ge[i] = elev[i];
 				gf[i] = flags[i];
 			}
+			MTD_GPHASE(6); // write-out
 		}
+#ifdef MTD_TIMING
+		if (blockIdx.x == 0 && threadIdx.x == 0)
+		{
+			printf("MAPGEN rng=%llu noise=%llu flags=%llu components=%llu border=%llu spawn=%llu writeout=%llu (cycles, CTA 0)\n", g_phase[8], g_phase[9], g_phase[10], g_phase[11], g_phase[12], g_phase[13], g_phase[14]);
+			for (int k = 8; k < 16; k++)
+				g_phase[k] = 0;
+		}
+#endif
 	}
 }

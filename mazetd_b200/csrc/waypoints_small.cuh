@@ -223,7 +223,7 @@ namespace mtd
 		acc__[k] += (unsigned long long)(now__ - last__);     \
 		last__ = now__;                                       \
 	} while (0)
-	__device__ unsigned long long g_phase[8];
+	__device__ unsigned long long g_phase[16];
 #define MTD_PHASE(k)                                                   \
 	do                                                                 \
 	{                                                                  \
