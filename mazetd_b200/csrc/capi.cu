@@ -400,7 +400,7 @@ namespace
 		P.smem_budget = (uint32_t)MAX_SMEM;
 		P.qseg_cap = ctx->debug_qseg_cap;
 		const SmallLayout L = small_layout(P.W, P.H, P.R, P.smem_budget, P.qseg_cap, GW);
-		if (kernel_config(ctx, (const void *)k_waypoints_small<GW>, SMALL_THREADS + 32, MAX_SMEM) < 0)
+		if (kernel_config(ctx, (const void *)k_waypoints_small<GW>, SMALL_BLOCK, MAX_SMEM) < 0)
 			return MTD_ERR_CUDA;
 		CU(ctx->map_counter.reserve(1));
 		CU(cudaMemsetAsync(ctx->map_counter.p, 0, 4, ctx->stream));
@@ -426,7 +426,7 @@ namespace
 			}
 		}
 		ProfScope prof(ctx, MTD_K_WAYPOINTS_SMALL);
-		k_waypoints_small<GW><<<blocks, SMALL_THREADS + 32, L.total, ctx->stream>>>(P);
+		k_waypoints_small<GW><<<blocks, SMALL_BLOCK, L.total, ctx->stream>>>(P);
 		LAUNCHED();
 		return MTD_OK;
 	}

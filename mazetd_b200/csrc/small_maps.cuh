@@ -207,6 +207,7 @@ namespace mtd
 				}
 			}
 			__syncthreads();
+			MTD_GPHASE(3); // runs
 			for (int i = threadIdx.x; i < T - W; i += blockDim.x)
 			{
 				if (flags[i] == F_INVALID || flags[i + W] == F_INVALID)
@@ -218,6 +219,7 @@ namespace mtd
 				uf_union(parent, (uint32_t)i, (uint32_t)(i + W));
 			}
 			__syncthreads();
+			MTD_GPHASE(4); // unions
 			// flatten, then count members in the upper 16 bits of the root's word (T < 65536)
 			for (int i = threadIdx.x; i < T; i += blockDim.x)
 				if (flags[i] != F_INVALID)
@@ -227,6 +229,7 @@ namespace mtd
 						parent[i] = r; // benign: only shortens chains, roots are untouched
 				}
 			__syncthreads();
+			MTD_GPHASE(5); // flatten
 			for (int base = 0; base < T; base += (int)blockDim.x)
 			{
 				const int i = base + (int)threadIdx.x;
@@ -238,6 +241,7 @@ namespace mtd
 					atomicAdd(&parent[r], (uint32_t)__popc(peers) << 16);
 			}
 			__syncthreads();
+			MTD_GPHASE(6); // count
 			// largest count; ties -> first discovered = smallest root (grid.cpp:68-72 uses strict '>')
 			{
 				unsigned long long key = 0ull;
@@ -256,13 +260,14 @@ namespace mtd
 					atomicMax(&best_key, key);
 			}
 			__syncthreads();
+			MTD_GPHASE(7); // best
 			const bool any_valid = best_key != 0ull;
 			const uint32_t best_root = 0xFFFFFFFFu - (uint32_t)(best_key & 0xFFFFFFFFull);
 			for (int i = threadIdx.x; i < T; i += blockDim.x)
 				if (flags[i] == F_INVALID || !any_valid || (parent[i] & 0xFFFFu) != best_root)
 					flags[i] = F_INVALID;
 			__syncthreads();
-			MTD_GPHASE(3); // components
+			MTD_GPHASE(8); // apply
 
 			// ---- findBorder + Mana: grid.cpp:80-97, 186-196 (border bits only land on invalid tiles, so in-place is safe) ----
 			for (int i = threadIdx.x; i < T; i += blockDim.x)
@@ -284,7 +289,7 @@ namespace mtd
 				flags[i] = f;
 			}
 			__syncthreads();
-			MTD_GPHASE(4); // border
+			MTD_GPHASE(9); // border
 
 			// ---- newWaypoints spawn picking: paths.cpp:173-183, 190-196 (inherently sequential in the RNG stream) ----
 			if (threadIdx.x == 0)
@@ -309,7 +314,7 @@ namespace mtd
 					atomicOr(P.status, ST_NO_VALID);
 			}
 			__syncthreads();
-			MTD_GPHASE(5); // spawn picking
+			MTD_GPHASE(10); // spawn picking
 
 			// ---- write out (coalesced 4-byte words; T even-padded arrays are 4-byte aligned per map only if T is even,
 			//      so use 2-byte stores: 40 KB per map, negligible next to the layers) ----
@@ -320,13 +325,13 @@ namespace mtd
 				ge[i] = elev[i];
 				gf[i] = flags[i];
 			}
-			MTD_GPHASE(6); // write-out
+			MTD_GPHASE(11); // write-out
 		}
 #ifdef MTD_TIMING
 		if (blockIdx.x == 0 && threadIdx.x == 0)
 		{
-			printf("MAPGEN rng=%llu noise=%llu flags=%llu components=%llu border=%llu spawn=%llu writeout=%llu (cycles, CTA 0)\n", g_phase[8], g_phase[9], g_phase[10], g_phase[11], g_phase[12], g_phase[13], g_phase[14]);
-			for (int k = 8; k < 16; k++)
+			printf("MAPGEN rng=%llu noise=%llu flags=%llu runs=%llu unions=%llu flatten=%llu count=%llu best=%llu apply=%llu border=%llu spawn=%llu writeout=%llu (cycles, CTA 0)\n", g_phase[8], g_phase[9], g_phase[10], g_phase[11], g_phase[12], g_phase[13], g_phase[14], g_phase[15], g_phase[16], g_phase[17], g_phase[18], g_phase[19]);
+			for (int k = 8; k < 24; k++)
 				g_phase[k] = 0;
 		}
 #endif

@@ -35,7 +35,10 @@ namespace mtd
 
 	constexpr int SMALL_THREADS = 512;
 	constexpr int SMALL_GROUP_WARPS = 2;   // default number of warps cooperating on one layer (template parameter GW: 1, 2 or 4)
-	constexpr int SMALL_WALKER_WARP = SMALL_THREADS / 32; // the extra warp that walks the previous map's paths
+	constexpr int SMALL_WALKER_WARP = SMALL_THREADS / 32; // first of the extra warps that walk the finished maps' paths
+	constexpr int SMALL_WALKERS = 2;                      // walker warps (finished maps alternate between them)
+	constexpr int SMALL_BLOCK = SMALL_THREADS + SMALL_WALKERS * 32;
+	constexpr uint32_t SMALL_RING = 8;                    // finished maps the workers may be ahead of the walkers
 	constexpr int SMALL_MAX_RESIDENT = 4;  // layers concurrently in shared memory
 	constexpr int MTD_MAXSRC_SMALL = 32;
 	constexpr int SMALL_OUT_CHUNK = 128;   // cells per write-out work item
@@ -223,7 +226,7 @@ namespace mtd
 		acc__[k] += (unsigned long long)(now__ - last__);     \
 		last__ = now__;                                       \
 	} while (0)
-	__device__ unsigned long long g_phase[16];
+	__device__ unsigned long long g_phase[24];
 #define MTD_PHASE(k)                                                   \
 	do                                                                 \
 	{                                                                  \
@@ -711,7 +714,15 @@ namespace mtd
 		}
 	};
 
-	// barrier of the 512 worker threads (the walker warp never takes part)
+	__device__ __forceinline__ uint32_t ld_volatile_shared(const uint32_t *p)
+	{
+		return *(const volatile uint32_t *)p;
+	}
+	__device__ __forceinline__ void st_volatile_shared(uint32_t *p, uint32_t v)
+	{
+		*(volatile uint32_t *)p = v;
+	}
+	// barrier of the 512 worker threads (the walker warps never take part)
 	__device__ __forceinline__ void workers_sync()
 	{
 		group_barrier(1, SMALL_THREADS);
@@ -765,9 +776,11 @@ namespace mtd
 
 
 	// =============================================================================================================
-	// 512 worker threads + 1 walker warp. GW = warps cooperating on one layer during the relaxation.
+	// 512 worker threads + SMALL_WALKERS walker warps. GW = warps cooperating on one layer during the relaxation.
+	// The walkers are decoupled from the workers: a finished map (layers written to global memory) is published in a small
+	// ring in shared memory, entry k is walked by walker k % SMALL_WALKERS while the workers go on with the next maps.
 	template<int GW>
-	__global__ void __launch_bounds__(SMALL_THREADS + 32, 1) k_waypoints_small(const WaypointsSmallParams P)
+	__global__ void __launch_bounds__(SMALL_BLOCK, 1) k_waypoints_small(const WaypointsSmallParams P)
 	{
 		extern __shared__ __align__(16) unsigned char smem_raw[];
 		const SmallGeom G(P.W, P.H);
@@ -786,8 +799,11 @@ namespace mtd
 		__shared__ uint32_t s_wp[MTD_MAXSRC_SMALL], s_srcp[MTD_MAXSRC_SMALL]; // waypoint / source tiles: grid index, padded index
 		__shared__ int s_guard, s_inc_fail;
 		__shared__ uint32_t s_map, s_chunk;
-		// the walker warp's private copies (it works on the PREVIOUS map while the workers overwrite the above)
-		__shared__ uint32_t w_wp[FIND_MAXN], w_D[FIND_MAXN * FIND_MAXN], w_fd[FIND_MAXN];
+		// the walker warps' private copies (they work on EARLIER maps while the workers overwrite the above)
+		__shared__ uint32_t w_wp[SMALL_WALKERS][FIND_MAXN], w_D[SMALL_WALKERS][FIND_MAXN * FIND_MAXN], w_fd[SMALL_WALKERS][FIND_MAXN];
+		__shared__ uint32_t s_ring[SMALL_RING];      // finished maps, entry k in slot k % SMALL_RING
+		__shared__ uint32_t s_head, s_stop;          // entries published so far / the workers are done
+		__shared__ uint32_t s_walked[SMALL_WALKERS]; // entries each walker completed
 
 		const int tid = threadIdx.x;
 		const int warp = tid >> 5;
@@ -798,12 +814,42 @@ namespace mtd
 		const uint32_t stage_half = align16u((uint32_t)(T + 8) * 2u);
 		const bool want_walks = P.fullpath_len && P.nsrc <= 1;
 		uint32_t mbar_phase = 0;
-		int walker_prev = -1;
+		uint32_t published = 0; // thread 0: entries in the ring so far
 
 		if (tid == 0)
 		{
 			mbar_init(&s_mbar, 1);
 			asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+			s_head = 0;
+			s_stop = 0;
+			for (int w = 0; w < SMALL_WALKERS; w++)
+				s_walked[w] = 0;
+		}
+		__syncthreads();
+
+		if (warp >= SMALL_WALKER_WARP)
+		{
+			// ---- walker warps: paths of finished maps, from their layers in global memory (still in L2) ----
+			const int w = warp - SMALL_WALKER_WARP;
+			for (uint32_t k = (uint32_t)w;; k += SMALL_WALKERS)
+			{
+				uint32_t head;
+				for (;;)
+				{
+					const uint32_t stop = ld_volatile_shared(&s_stop);
+					head = ld_volatile_shared(&s_head); // read after the stop flag: a set flag means the last entry is visible
+					if (head > k || stop)
+						break;
+					__nanosleep(200);
+				}
+				if (head <= k)
+					break;
+				__threadfence(); // acquire: the workers' stores of this map's layers
+				walk_map_global(P, (int)ld_volatile_shared(&s_ring[k % SMALL_RING]), w_wp[w], w_D[w], w_fd[w], lane);
+				if (lane == 0)
+					st_volatile_shared(&s_walked[w], k / SMALL_WALKERS + 1u);
+			}
+			return;
 		}
 
 #ifdef MTD_TIMING
@@ -811,22 +857,12 @@ namespace mtd
 #endif
 		for (;;)
 		{
-			__syncthreads(); // all 544 threads: the previous map is completely written out and the walker finished the one before
+			workers_sync(); // the previous map is completely written out
 			if (tid == 0)
 				s_map = atomicAdd(P.map_counter, 1u);
-			__syncthreads();
+			workers_sync();
 			const int mapi = (int)s_map;
-			MTD_PHASE(0); // waiting for the walker / claiming a map
-			if (warp == SMALL_WALKER_WARP)
-			{
-				// ---- walker warp: paths of the map the workers finished last, from its layers in global memory (still in L2) ----
-				if (P.walker && want_walks && walker_prev >= 0)
-					walk_map_global(P, walker_prev, w_wp, w_D, w_fd, lane);
-				if (mapi >= P.nmaps)
-					break;
-				walker_prev = mapi;
-				continue;
-			}
+			MTD_PHASE(0); // claiming a map
 			if (mapi >= P.nmaps)
 				break;
 			const int16_t *ge = P.elev + (size_t)mapi * T;
@@ -1094,6 +1130,62 @@ namespace mtd
 							}
 							const bool blocked = (bw >> (i & 31)) & 1u;
 							const uint32_t p = G.g2p((uint32_t)i);
+							if (lb == 4 && P.nsrc <= 1 && gdist && gtiles)
+							{
+								// the usual case, four single-source layers: the tile's four edge weights are loaded once and the 20
+								// label loads of the four layers are independent of each other (the per-layer loop below serialises them)
+								uint32_t dv[4], hop[4];
+								const uint32_t u0 = p - (uint32_t)Wp, u1 = p - 1u, u2 = p + 1u, u3 = p + (uint32_t)Wp;
+								const uint32_t w0 = MIN_EDGE + wd[u0], w1 = MIN_EDGE + wr[u1], w2 = MIN_EDGE + wr[p], w3 = MIN_EDGE + wd[p];
+								uint32_t c[4], d0[4], d1[4], d2[4], d3[4];
+#pragma unroll
+								for (int r = 0; r < 4; r++)
+								{
+									const uint32_t *dl = sdist + (size_t)r * Tp;
+									c[r] = dl[p];
+									d0[r] = dl[u0];
+									d1[r] = dl[u1];
+									d2[r] = dl[u2];
+									d3[r] = dl[u3];
+								}
+#pragma unroll
+								for (int r = 0; r < 4; r++)
+								{
+									const uint32_t sp = s_srcp[l0 + r];
+									uint32_t best = MTD_INF, bestd = MTD_INF;
+									// same order and strict '<' as next_hop_p: up, left, right, down
+									if (d0[r] != MTD_INF && d0[r] + w0 == c[r] && (d0[r] != 0u || u0 == sp))
+									{
+										bestd = d0[r];
+										best = u0;
+									}
+									if (d1[r] != MTD_INF && d1[r] + w1 == c[r] && d1[r] < bestd && (d1[r] != 0u || u1 == sp))
+									{
+										bestd = d1[r];
+										best = u1;
+									}
+									if (d2[r] != MTD_INF && d2[r] + w2 == c[r] && d2[r] < bestd && (d2[r] != 0u || u2 == sp))
+									{
+										bestd = d2[r];
+										best = u2;
+									}
+									if (d3[r] != MTD_INF && d3[r] + w3 == c[r] && d3[r] < bestd && (d3[r] != 0u || u3 == sp))
+									{
+										bestd = d3[r];
+										best = u3;
+									}
+									const bool reach = !blocked && c[r] != MTD_INF && c[r] != 0u;
+									hop[r] = reach && best != MTD_INF ? G.p2g(best) : MTD_INF;
+									dv[r] = blocked ? (sp == p ? 0u : MTD_INF) : c[r];
+								}
+#pragma unroll
+								for (int r = 0; r < 4; r++)
+								{
+									st_stream_u32(gdist + (size_t)(l0 + r) * T + i, dv[r]);
+									st_stream_u32(gtiles + (size_t)(l0 + r) * T + i, hop[r]);
+								}
+								continue;
+							}
 							for (int r = 0; r < lb; r++)
 							{
 								const uint32_t *dl = sdist + (size_t)r * Tp;
@@ -1143,20 +1235,44 @@ namespace mtd
 
 			if (s_guard && tid == 0)
 				atomicOr(P.status, ST_GUARD);
-			if (!want_walks || P.walker)
+			if (want_walks && P.walker)
+			{
+				// hand the map to a walker. The last workers_sync() ordered every worker's stores before this thread; the fence
+				// makes them visible to the walker that reads the new head
+				if (tid == 0)
+				{
+					if (published >= SMALL_RING)
+					{
+						const uint32_t old = published - SMALL_RING; // its slot is reused: wait until that entry has been walked
+						while (ld_volatile_shared(&s_walked[old % SMALL_WALKERS]) <= old / SMALL_WALKERS)
+							__nanosleep(200);
+					}
+					st_volatile_shared(&s_ring[published % SMALL_RING], (uint32_t)mapi);
+					published++;
+					__threadfence();
+					st_volatile_shared(&s_head, published);
+				}
+				continue;
+			}
+			if (!want_walks)
 				continue;
 
 			if (!resident_all)
 			{
 				// single map with more layers than fit: walk the layers just written to global memory (L2), warp 0
 				if (warp == 0)
-					walk_map_global(P, mapi, w_wp, w_D, w_fd, lane);
+					walk_map_global(P, mapi, w_wp[0], w_D[0], w_fd[0], lane);
 				continue;
 			}
 
 			// ---- 5. aggregates: paths.cpp:122-138 ----
 			if (tid == 0)
 				walk_aggregates(n, s_fd, P.agg + (size_t)mapi * 3);
+		}
+		if (tid == 0)
+		{
+			__threadfence();
+			st_volatile_shared(&s_stop, 1u); // after the last head update: the walkers drain the ring and leave
 		}
 #ifdef MTD_TIMING
 		if (blockIdx.x == 0 && tid == 0)
