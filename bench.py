@@ -745,9 +745,13 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device; libmazetd_b200 has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = None
     if world > 1:
         import torch.distributed as dist
+        from mazetd_b200 import numa as numa_mod
 
+        # before any pinned allocation: this rank's host buffers go to the NUMA node its GPU hangs off
+        numa = numa_mod.bind_to_gpu_node(local)
         dist.init_process_group("nccl", device_id=dev)
     # a real (non-default) stream: the library treats a NULL handle as "create your own", and torch's events must
     # be recorded on the stream the kernels are launched on
@@ -824,12 +828,12 @@ def run_ours(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (of fallback)"
-    bytes_per_map = T * (4 + 8 * NWP)  # read elev+flags once, write dist+tiles per layer
+    bytes_per_map = T * (4 + 8 * NWP)  # elev+flags once (read, or written when the generator is fused in), dist+tiles written per layer
     wp_avg_ms = wp_ms / max(wp_n, 1)
     achieved = maps * bytes_per_map / (wp_avg_ms * 1e-3) / 1e9 if wp_avg_ms > 0 else 0.0
     roofline = {
         "bound": "hbm",
-        "kernel": "k_waypoints_small",
+        "kernel": "k_waypoints_small" + (" (generator fused in)" if mg_n == 0 else ""),
         "achieved": achieved,
         "peak": peak,
         "unit": "GB/s",
@@ -840,7 +844,7 @@ def run_ours(args):
         "avg_launch_ms": wp_avg_ms,
         "launches_timed": wp_n,
         "share_of_step": wp_ms / (ms_total if ms_total > 0 else 1.0),
-        "other_kernels": {"k_mapgen_grid_avg_ms": mg_ms / max(mg_n, 1)},
+        "other_kernels": {"k_mapgen_grid_avg_ms": mg_ms / mg_n} if mg_n else {},
     }
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(traffic_file):
@@ -894,6 +898,7 @@ def run_ours(args):
             "h2d_bytes_per_step": 64,  # seeds + mtd_mapgen_params; the generator has no bulk input
             "d2h_bytes_per_step": d2h,
             "api": "mtd_mapgen_batch (include/mazetd_b200.h), pinned host outputs, synchronous",
+            "host_numa": numa,  # N > 1: rank 0's process was bound to its GPU's NUMA node before the pinned buffers were allocated
         }
 
     # ---- the same batch in STRONG form: 4096 maps in total, a contiguous block of map indices per rank (BASELINE.json

@@ -159,6 +159,8 @@ class Context:
     DEBUG_ASYNC_DELTA = 6
     DEBUG_BIG_TMA = 7
     DEBUG_INCREMENTAL = 10
+    DEBUG_FUSED_MAPGEN = 11
+    DEBUG_GEN_WARPS = 12
     DEBUG_ASYNC_NB_RULE = 8
     DEBUG_ASYNC_DEPTH = 9
 

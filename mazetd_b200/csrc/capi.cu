@@ -30,7 +30,7 @@ using namespace mtd;
 
 namespace
 {
-	constexpr size_t MAX_SMEM = 227 * 1024 - 1024; // dynamic budget: the opt-in limit is 227 KB per CTA including static __shared__
+	constexpr size_t MAX_SMEM = 227 * 1024 - 2560; // dynamic budget: the opt-in limit is 227 KB per CTA including static __shared__ (k_waypoints_small: 2.2 KB)
 	constexpr int BIG_TS = 32;   // tile side of the large-grid path = warp width (tile_warp.cuh)
 	constexpr int BIG_WARPS = 4; // warps per CTA, each working on its own (layer, tile) item
 
@@ -167,6 +167,8 @@ struct mtd_ctx
 	DevBuf<uint32_t> map_counter;
 	int debug_qseg_cap = 0;
 	int debug_gw = SMALL_GROUP_WARPS;
+	bool fused_mapgen = false; // mtd_mapgen_batch with waypoints: generator inside k_waypoints_small (measured slower, r02s / r02t)
+	int gen_warps = 8;        // ... warps that compute the next map's elevations during the relaxation
 	int debug_walker = 0; // 0 auto, 1 never, 2 always
 	DevBuf<uint32_t> scratch_tiles, scratch_dist;
 	DevBuf<int16_t> scratch_elev_in, scratch_elev;
@@ -1200,6 +1202,12 @@ extern "C" int mtd_debug_set(mtd_ctx *ctx, int key, int64_t value)
 	case MTD_DEBUG_INCREMENTAL:
 		ctx->inc_enabled = value != 0;
 		return MTD_OK;
+	case MTD_DEBUG_FUSED_MAPGEN:
+		ctx->fused_mapgen = value != 0;
+		return MTD_OK;
+	case MTD_DEBUG_GEN_WARPS:
+		ctx->gen_warps = value < 0 ? 0 : value > 16 ? 16 : (int)value;
+		return MTD_OK;
 	case MTD_DEBUG_BIG_TMA:
 		ctx->big_tma = value != 0;
 		return MTD_OK;
@@ -2048,10 +2056,15 @@ static int mapgen_dev(mtd_ctx *ctx, const mtd_mapgen_params *p, uint64_t s1, uin
 	G.wp_tiles = d_wp;
 	G.status = ctx->d_status.p;
 	G.elev_in = d_elev_in;
-	const size_t gsm = mapgen_grid_smem(T);
-	const int per_sm = (int)(MAX_SMEM / (gsm + 1024)) > 0 ? (int)(MAX_SMEM / (gsm + 1024)) : 1;
-	const int gblocks = nmaps < ctx->sms * per_sm ? nmaps : ctx->sms * per_sm;
+	// maps WITH waypoints: the generator runs inside k_waypoints_small (the next map's elevations are computed by the warps
+	// that have no layer to relax); maps only, the caller's elevations, or shapes the fused mode cannot hold: k_mapgen_grid
+	const int Rres = p->nwp > 0 ? small_resident(p->W, p->H, p->nwp) : 0;
+	const bool fused = ctx->fused_mapgen && p->nwp > 0 && !d_elev_in && p->nwp <= Rres && small_gen_fits(p->W, p->H, Rres);
+	if (!fused)
 	{
+		const size_t gsm = mapgen_grid_smem(T);
+		const int per_sm = (int)(MAX_SMEM / (gsm + 1024)) > 0 ? (int)(MAX_SMEM / (gsm + 1024)) : 1;
+		const int gblocks = nmaps < ctx->sms * per_sm ? nmaps : ctx->sms * per_sm;
 		ProfScope prof(ctx, MTD_K_MAPGEN_GRID);
 		k_mapgen_grid<<<gblocks, 512, gsm, ctx->stream>>>(G);
 		LAUNCHED();
@@ -2078,6 +2091,17 @@ static int mapgen_dev(mtd_ctx *ctx, const mtd_mapgen_params *p, uint64_t s1, uin
 	P.full_distance = d_fdist;
 	P.agg = d_agg;
 	P.status = ctx->d_status.p;
+	if (fused)
+	{
+		P.gen = 1;
+		P.gen_warps = ctx->gen_warps;
+		P.gen_ox = p->ox;
+		P.gen_oy = p->oy;
+		P.gen_radius = p->radius;
+		P.gen_first = first;
+		P.gen_s1 = s1;
+		P.gen_s2 = s2;
+	}
 	if (P.fullpath_len && (!d_fdist || !d_agg))
 		return fail(ctx, MTD_ERR_ARG, "fullpath_len, full_distance and agg outputs go together");
 	if (p->nwp > SMALL_MAX_RESIDENT && P.fullpath_len && !d_dist)

@@ -18,6 +18,7 @@
 #pragma once
 
 #include "common.cuh"
+#include "mapgen_steps.cuh"
 #include "sssp_warp.cuh"
 #include "walk.cuh"
 
@@ -73,6 +74,12 @@ namespace mtd
 		// whose blocking state flipped since (sources/player/buildingsPlacement.cpp:120-130, 143-164, trial :18-42)
 		const uint32_t *prev_dist; // [n][T] distances before the flip (may alias `dist`), or null
 		uint32_t inc_tile;         // the flipped tile, MTD_M = none (full update). Needs nmaps == 1, n <= R, nsrc == 1
+		// fused generator (newProcedural + newGrid + spawn picking, mapgen_steps.cuh): the kernel WRITES elev / flags / wp of
+		// every map before it relaxes it. Needs nsrc == 1, n <= R, small_gen_fits()
+		int gen;
+		int gen_warps; // warps (of those without a layer) that compute the next map's elevations during the relaxation
+		int gen_ox, gen_oy, gen_radius, gen_first;
+		uint64_t gen_s1, gen_s2;
 	};
 
 	// ---- geometry of the padded frame -------------------------------------------------------------------------
@@ -143,6 +150,17 @@ namespace mtd
 		L.total = o + per_entry * (uint32_t)qseg;
 		return L;
 	}
+	// fused generator: elevations, flags and the union-find parents of one map live in the distance layers' memory
+	// before the layers are initialised
+	__host__ __device__ inline uint32_t small_gen_parent_offset(int W, int H)
+	{
+		return 2u * align16u(((uint32_t)(W * H) + 8u) * 2u) + 32u;
+	}
+	__host__ __device__ inline bool small_gen_fits(int W, int H, int R)
+	{
+		return small_gen_parent_offset(W, H) + (uint32_t)(W * H) * 4u <= (uint32_t)R * (uint32_t)((W + 1) * (H + 2)) * 4u;
+	}
+
 	// ---- small PTX helpers -----------------------------------------------------------------------------------
 	__device__ __forceinline__ uint32_t smem_u32(const void *p)
 	{
@@ -188,12 +206,6 @@ namespace mtd
 	__device__ __forceinline__ void group_barrier(int id, int threads)
 	{
 		asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
-	}
-
-	// i / W for i < 65536, W <= 256 with magicW = ceil(2^32 / W); W == 1 has no 32-bit magic and passes 0
-	__device__ __forceinline__ uint32_t div_w(uint32_t i, uint32_t magicW)
-	{
-		return magicW ? __umulhi(i, magicW) : i;
 	}
 
 	// stage T int16/uint16 elements of `src` (2-byte aligned) at `dst_base + (src & 15)` so that the 16-byte aligned
@@ -290,37 +302,38 @@ namespace mtd
 						const uint32_t seg = (idx >= p1) + (GW > 2 ? (idx >= p2) + (idx >= p3) : 0u);
 						slot = seg * cap + idx - (seg == 0 ? 0u : seg == 1 ? p1 : seg == 2 ? p2 : p3);
 					}
-					const uint32_t c = active ? rq[slot] : 0u;
-					const uint32_t d = active ? dist[c] : MTD_INF;
-					bool settle = active && d < thr;
+					// idle lanes read an in-frame cell too (loads without a branch); the label and the four edge weights are
+					// independent loads
+					const uint32_t c = active ? rq[slot] : (uint32_t)Wp + 1u;
+					const uint32_t dc = dist[c];
+					// 0: up, 1: left, 2: right, 3: down -- weights are stored on the upper / left cell of an edge
+					const uint32_t w0 = wd[c - Wp], w1 = wr[c - 1], w2 = wr[c], w3 = wd[c];
+					const uint32_t d = active ? dc : MTD_INF;
+					bool settle = d < thr;
 					if (settle && d >= SMALL_SETTLE_LIMIT)
 					{
 						guard = true; // reference arithmetic is about to wrap: report, do not expand
 						settle = false;
 					}
 					const bool keep = active && d >= thr && d < SMALL_SETTLE_LIMIT;
-					uint32_t o0 = 0u, o1 = 0u, o2 = 0u, o3 = 0u, n0 = 0u, n1 = 0u, n2 = 0u, n3 = 0u;
-					if (settle)
-					{
-						// 0: up, 1: left, 2: right, 3: down -- weights are stored on the upper / left cell of an edge
-						const uint32_t base_nd = d + MIN_EDGE;
-						n0 = base_nd + wd[c - Wp];
-						n1 = base_nd + wr[c - 1];
-						n2 = base_nd + wr[c];
-						n3 = base_nd + wd[c];
-						o0 = atomicMin(&dist[c - Wp], n0);
-						o1 = atomicMin(&dist[c - 1], n1);
-						o2 = atomicMin(&dist[c + 1], n2);
-						o3 = atomicMin(&dist[c + Wp], n3);
-					}
+					// no branch around the atomics: a lane with nothing to settle offers MTD_INF (which lowers nothing) to a parked
+					// cell of the top padding row, one per lane so that the idle lanes do not serialise on one word
+					const uint32_t base_nd = d + MIN_EDGE;
+					const uint32_t n0 = settle ? base_nd + w0 : MTD_INF, n1 = settle ? base_nd + w1 : MTD_INF;
+					const uint32_t n2 = settle ? base_nd + w2 : MTD_INF, n3 = settle ? base_nd + w3 : MTD_INF;
+					const uint32_t spare = lane < (uint32_t)Wp ? lane : 0u;
+					const uint32_t o0 = atomicMin(&dist[settle ? c - Wp : spare], n0);
+					const uint32_t o1 = atomicMin(&dist[settle ? c - 1u : spare], n1);
+					const uint32_t o2 = atomicMin(&dist[settle ? c + 1u : spare], n2);
+					const uint32_t o3 = atomicMin(&dist[settle ? c + Wp : spare], n3);
 					// a cell enters the queue exactly once: when its label leaves "unreached" (labels of queued cells may
 					// still improve before they settle, settled labels are final)
 					const bool f0 = settle && o0 == MTD_INF, f1 = settle && o1 == MTD_INF, f2 = settle && o2 == MTD_INF, f3 = settle && o3 == MTD_INF;
 					uint32_t lm = keep ? d : MTD_INF;
-					lm = settle && n0 < o0 ? min(lm, n0) : lm;
-					lm = settle && n1 < o1 ? min(lm, n1) : lm;
-					lm = settle && n2 < o2 ? min(lm, n2) : lm;
-					lm = settle && n3 < o3 ? min(lm, n3) : lm;
+					lm = n0 < o0 ? min(lm, n0) : lm; // never true for an idle lane: it offered MTD_INF
+					lm = n1 < o1 ? min(lm, n1) : lm;
+					lm = n2 < o2 ? min(lm, n2) : lm;
+					lm = n3 < o3 ? min(lm, n3) : lm;
 					newmin = min(newmin, lm);
 					// ---- append survivors and newly reached cells to this warp's segment (ballot compaction) ----
 					const uint32_t bk = __ballot_sync(FULL_MASK, keep);
@@ -804,6 +817,12 @@ namespace mtd
 		__shared__ uint32_t s_ring[SMALL_RING];      // finished maps, entry k in slot k % SMALL_RING
 		__shared__ uint32_t s_head, s_stop;          // entries published so far / the workers are done
 		__shared__ uint32_t s_walked[SMALL_WALKERS]; // entries each walker completed
+		// fused generator
+		__shared__ float2 s_grad[128];
+		__shared__ noise::ElevationParams s_ep; // of the map whose elevations are computed next
+		__shared__ Rng s_rng;                   // the current map's stream after the generator's draws
+		__shared__ unsigned long long s_best_key;
+		__shared__ uint32_t s_next;
 
 		const int tid = threadIdx.x;
 		const int warp = tid >> 5;
@@ -852,19 +871,79 @@ namespace mtd
 			return;
 		}
 
+		// ---- fused generator: the first map's elevations are computed by all workers, every later map's by the warps that
+		//      have no layer to relax while the map before it is relaxed ----
+		const bool gen = P.gen != 0;
+		MapgenShape S;
+		S.W = W;
+		S.H = H;
+		S.ox = P.gen_ox;
+		S.oy = P.gen_oy;
+		S.radius = P.gen_radius;
+		S.magicW = G.magicW;
+		int16_t *const gen_elev = const_cast<int16_t *>(P.elev);
+		uint16_t *const gen_flags = const_cast<uint16_t *>(P.flags);
+		uint32_t *const gen_wp = const_cast<uint32_t *>(P.wp);
+		int gen_cur = 0;
+		const int gen_warps = min(max(P.gen_warps, 0), SMALL_THREADS / 32 - min(n, R) * GW); // warps that compute elevations during the relaxation
+		if (gen)
+		{
+			for (int i = tid; i < 128; i += SMALL_THREADS)
+				s_grad[i] = noise::gradient(i);
+			if (tid == 0)
+			{
+				const uint32_t m = atomicAdd(P.map_counter, 1u);
+				s_next = m;
+				if (m < (uint32_t)P.nmaps)
+				{
+					Rng g;
+					noise::ElevationParams e;
+					mapgen_draws(P.gen_s1, P.gen_s2, P.gen_first + (int)m, e, g);
+					s_ep = e;
+				}
+			}
+			workers_sync();
+			gen_cur = (int)s_next;
+			if (gen_cur < P.nmaps)
+			{
+				const noise::ElevationParams lp = s_ep;
+				mapgen_elevations(s_grad, lp, S, gen_elev + (size_t)gen_cur * T, tid, SMALL_THREADS);
+			}
+		}
+
 #ifdef MTD_TIMING
 		long long phase_last__ = clock64();
 #endif
 		for (;;)
 		{
-			workers_sync(); // the previous map is completely written out
+			workers_sync(); // the previous map is completely written out (and this map's elevations, when they are generated here)
 			if (tid == 0)
-				s_map = atomicAdd(P.map_counter, 1u);
+			{
+				if (!gen)
+					s_map = atomicAdd(P.map_counter, 1u);
+				else if (gen_cur < P.nmaps)
+				{
+					// claim the map after this one now: its elevations are computed while this one is relaxed
+					Rng g;
+					noise::ElevationParams e;
+					mapgen_draws(P.gen_s1, P.gen_s2, P.gen_first + gen_cur, e, g);
+					s_rng = g;
+					const uint32_t m = atomicAdd(P.map_counter, 1u);
+					s_next = m;
+					if (m < (uint32_t)P.nmaps)
+					{
+						mapgen_draws(P.gen_s1, P.gen_s2, P.gen_first + (int)m, e, g);
+						s_ep = e;
+					}
+				}
+			}
 			workers_sync();
-			const int mapi = (int)s_map;
+			const int mapi = gen ? gen_cur : (int)s_map;
 			MTD_PHASE(0); // claiming a map
 			if (mapi >= P.nmaps)
 				break;
+			const int gen_next = gen ? (int)s_next : P.nmaps;
+			gen_cur = gen_next;
 			const int16_t *ge = P.elev + (size_t)mapi * T;
 			const uint16_t *gf = P.flags + (size_t)mapi * T;
 			const uint32_t *gwp = P.wp + (size_t)mapi * nwp;
@@ -876,6 +955,65 @@ namespace mtd
 			unsigned char *st_f = smem_raw + L.dist + stage_half + ((uintptr_t)gf & 15u);
 			const int16_t *selev = (const int16_t *)st_e;
 			const uint16_t *sflags = (const uint16_t *)st_f;
+			if (gen)
+			{
+				// ---- 1g. the rest of the generator, in the memory the distance layers take afterwards ----
+				int16_t *se = (int16_t *)st_e;
+				uint16_t *sf = (uint16_t *)st_f;
+				uint32_t *parent = (uint32_t *)(smem_raw + L.dist + small_gen_parent_offset(W, H));
+				for (int i0 = tid; i0 < T; i0 += 4 * SMALL_THREADS)
+				{
+					// written by this CTA one map ago; four independent loads in flight per thread
+					int16_t v[4];
+#pragma unroll
+					for (int k = 0; k < 4; k++)
+						v[k] = i0 + k * SMALL_THREADS < T ? __ldcg(ge + i0 + k * SMALL_THREADS) : (int16_t)0;
+#pragma unroll
+					for (int k = 0; k < 4; k++)
+						if (i0 + k * SMALL_THREADS < T)
+							se[i0 + k * SMALL_THREADS] = v[k];
+				}
+				if (warp == 2 && lane == 0)
+				{
+					s_guard = 0;
+					s_chunk = 0;
+				}
+				else if (warp == 3)
+				{
+					for (int k = (int)lane; k < Wp; k += 32)
+					{
+						wr[k] = 0;
+						wd[k] = 0;
+						wr[(H + 1) * Wp + k] = 0;
+						wd[(H + 1) * Wp + k] = 0;
+					}
+					for (int y = 1 + (int)lane; y <= H; y += 32)
+					{
+						wr[y * Wp + W] = 0;
+						wd[y * Wp + W] = 0;
+					}
+				}
+				workers_sync();
+				MTD_PHASE(6); // generator: elevations back from L2
+				const bool any_valid = mapgen_flags(S, se, sf, parent, &s_best_key, tid, SMALL_THREADS, [] { workers_sync(); });
+				MTD_PHASE(7); // generator: flags, components, border
+				if (tid == 0)
+				{
+					mapgen_pick_spawns(s_rng, T, sf, nwp, any_valid, s_wp, P.status);
+					for (int k = 0; k < nwp; k++)
+					{
+						const uint32_t t = s_wp[k];
+						gen_wp[(size_t)mapi * nwp + k] = t;
+						s_srcp[k] = G.g2p(t < (uint32_t)T ? t : 0u); // a map without valid tiles is reported (ST_NO_VALID), not relaxed into
+					}
+				}
+				workers_sync();
+				MTD_PHASE(8); // generator: spawn picking
+				uint16_t *gfo = gen_flags + (size_t)mapi * T;
+				for (int i = tid; i < T; i += SMALL_THREADS)
+					gfo[i] = sf[i];
+			}
+			else
 			{
 				const StagePlan pe = stage_plan(ge, (uint32_t)T * 2u), pf = stage_plan(gf, (uint32_t)T * 2u);
 				if (tid == 0)
@@ -905,7 +1043,7 @@ namespace mtd
 					{
 						const uint32_t t = gwp[i];
 						s_wp[i] = t;
-						s_srcp[i] = G.g2p(t);
+						s_srcp[i] = G.g2p(t < (uint32_t)T ? t : 0u); // the host validates waypoints; MTD_INF comes from a generated map without valid tiles (reported)
 					}
 					if (lane == 0)
 					{
@@ -1056,7 +1194,21 @@ namespace mtd
 					if (group_relax<GW>(sdist + (size_t)g * Tp, wr, wd, q + (size_t)g * 2 * GW * qseg, ctl + g * 16, Wp, Tp, qseg, warp % GW, lane, 2 + g) && lane == 0)
 						s_guard = 1;
 				}
+				else if (gen_next < P.nmaps && warp < lb * GW + gen_warps)
+				{
+					// fused generator: warps without a layer compute the next map's elevations (pure arithmetic, no shared
+					// memory beyond the gradient table) into its slot of the output, where step 1g picks them up. Not all of
+					// them: the relaxation is a chain of dependent instructions and every ready warp next to it delays its issue
+					const noise::ElevationParams lp = s_ep;
+					mapgen_elevations(s_grad, lp, S, gen_elev + (size_t)gen_next * T, tid - lb * GW * 32, gen_warps * 32);
+				}
 				workers_sync();
+				if (gen_next < P.nmaps && gen_warps == 0)
+				{
+					// every warp had a layer: the elevations are computed by all of them now
+					const noise::ElevationParams lp = s_ep;
+					mapgen_elevations(s_grad, lp, S, gen_elev + (size_t)gen_next * T, tid, SMALL_THREADS);
+				}
 				MTD_PHASE(4); // relaxation (slowest layer)
 
 				// ---- 4. full-path walks (one lane per spawner) overlapped with next-hop tiles + write-out of this pass ----
@@ -1278,9 +1430,10 @@ namespace mtd
 		if (blockIdx.x == 0 && tid == 0)
 		{
 			printf("TIMING rounds=%llu items=%llu | ctl+thr=%llu body=%llu redux+sts=%llu barrier=%llu looptop=%llu (cycles, warp 0 of layer 0, CTA 0)\n", g_timing[5], g_timing[6], g_timing[0], g_timing[1], g_timing[2], g_timing[3], g_timing[4]);
-			printf("PHASES wait=%llu stage=%llu weights=%llu init=%llu relax=%llu writeout=%llu (cycles, CTA 0)\n", g_phase[0], g_phase[1], g_phase[2], g_phase[3], g_phase[4], g_phase[5]);
+			printf("PHASES wait=%llu stage=%llu weights=%llu init=%llu relax=%llu writeout=%llu | generator: load=%llu flags=%llu spawns=%llu (cycles, CTA 0)\n", g_phase[0], g_phase[1], g_phase[2], g_phase[3], g_phase[4], g_phase[5], g_phase[6], g_phase[7], g_phase[8]);
 			for (int k = 0; k < 8; k++)
 				g_timing[k] = g_phase[k] = 0;
+			g_phase[8] = 0;
 		}
 #endif
 	}

@@ -29,6 +29,15 @@ def tctx(ctx, request):
     ctx.debug_set(ctx.DEBUG_BIG_ASYNC, 1)
 
 
+@pytest.fixture(params=["fused", "two_kernels"])
+def gctx(ctx, request):
+    """mtd_mapgen_batch with waypoints under both forms: generator fused into k_waypoints_small (default: the next map's
+    elevations are computed by the warps without a layer while the current map is relaxed) and k_mapgen_grid first"""
+    ctx.debug_set(ctx.DEBUG_FUSED_MAPGEN, 1 if request.param == "fused" else 0)
+    yield ctx
+    ctx.debug_set(ctx.DEBUG_FUSED_MAPGEN, 1)
+
+
 GOLDEN_BIG = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "big_configs.npz")
 
 
@@ -487,7 +496,8 @@ def test_elevation_samples_bit_exact(ctx, oracle):
         assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), f"{(got != want).sum()} of {len(xy)} samples differ"
 
 
-def test_mapgen_batch_bit_exact(ctx, oracle):
+def test_mapgen_batch_bit_exact(gctx, oracle):
+    ctx = gctx
     n = 24
     g = ctx.mapgen_batch(KAT_SEED[0], KAT_SEED[1], 0, n, cap=2048)
     for k in range(n):
@@ -498,9 +508,10 @@ def test_mapgen_batch_bit_exact(ctx, oracle):
 
 @pytest.mark.parametrize("gw", [1, 2, 4])
 @pytest.mark.parametrize("walker", [1, 2])
-def test_mapgen_batch_walker_warp_and_group_widths(ctx, oracle, gw, walker):
-    """the batched kernel's variants -- 1/2/4 warps per layer, paths walked by the workers (1) or by the walker warp on the
-    previous map's layers in global memory (2) -- must all produce the reference's bits"""
+def test_mapgen_batch_walker_warp_and_group_widths(gctx, oracle, gw, walker):
+    """the batched kernel's variants -- 1/2/4 warps per layer, paths walked by the workers (1) or by the walker warps on
+    finished maps' layers in global memory (2), generator fused or not -- must all produce the reference's bits"""
+    ctx = gctx
     n = 10
     try:
         ctx.debug_set(ctx.DEBUG_GROUP_WARPS, gw)
@@ -515,8 +526,9 @@ def test_mapgen_batch_walker_warp_and_group_widths(ctx, oracle, gw, walker):
             assert np.array_equal(g[key][k], o[key]), (k, key)
 
 
-def test_mapgen_batch_many_maps_per_cta(ctx, oracle):
-    """more maps than CTAs: every CTA loops over several maps and its walker warp runs one map behind"""
+def test_mapgen_batch_many_maps_per_cta(gctx, oracle):
+    """more maps than CTAs: every CTA loops over several maps and its walker warps run behind the workers"""
+    ctx = gctx
     n = 700
     g = ctx.mapgen_batch(KAT_SEED[0], KAT_SEED[1], 1000, n, cap=1024)
     for k in list(range(0, n, 37)) + [n - 1]:
@@ -547,7 +559,8 @@ def test_walks_with_unreachable_waypoints_take_the_per_hop_path(ctx, oracle, wal
             assert np.array_equal(g[k], o[k]), (list(wp), k)
 
 
-def test_mapgen_batch_vs_reference_code(ctx, ref):
+def test_mapgen_batch_vs_reference_code(gctx, ref):
+    ctx = gctx
     g = ctx.mapgen_batch(KAT_SEED[0], KAT_SEED[1], 40, 3, cap=2048)
     for j in range(3):
         r = ref.mapgen(KAT_SEED[0] + 40 + j, KAT_SEED[1], cap=2048)

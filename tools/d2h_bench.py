@@ -13,6 +13,12 @@ world = int(os.environ.get("WORLD_SIZE", "1"))
 local = int(os.environ.get("LOCAL_RANK", "0"))
 torch.cuda.set_device(local)
 dev = torch.device("cuda", local)
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from mazetd_b200 import numa
+
+numa_info = numa.bind_to_gpu_node(local) if world > 1 else None  # MTD_NO_NUMA_BIND=1 leaves the affinity alone
 if world > 1:
     dist.init_process_group("nccl", device_id=dev)
 n = 1536 * 1024 * 1024
@@ -38,6 +44,6 @@ else:
     parts = [t]
 if rank == 0:
     per = [float(p.item()) for p in parts]
-    print(json.dumps({"n_gpus": world, "bytes_per_rank": n, "d2h_GBps_per_rank": [round(x, 1) for x in per], "d2h_GBps_total": round(sum(per), 1), "host_cpus": len(os.sched_getaffinity(0))}), flush=True)
+    print(json.dumps({"n_gpus": world, "bytes_per_rank": n, "d2h_GBps_per_rank": [round(x, 1) for x in per], "d2h_GBps_total": round(sum(per), 1), "host_cpus": len(os.sched_getaffinity(0)), "numa_rank0": numa_info}), flush=True)
 if world > 1:
     dist.destroy_process_group()
