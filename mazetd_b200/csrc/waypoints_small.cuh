@@ -914,13 +914,16 @@ namespace mtd
 #ifdef MTD_TIMING
 		long long phase_last__ = clock64();
 #endif
+		uint32_t claim = 0; // thread 0: the next map of this CTA
+		if (tid == 0 && !gen)
+			claim = atomicAdd(P.map_counter, 1u);
 		for (;;)
 		{
 			workers_sync(); // the previous map is completely written out (and this map's elevations, when they are generated here)
 			if (tid == 0)
 			{
 				if (!gen)
-					s_map = atomicAdd(P.map_counter, 1u);
+					s_map = claim; // issued during the previous map's write-out: the L2 round trip is off the critical path
 				else if (gen_cur < P.nmaps)
 				{
 					// claim the map after this one now: its elevations are computed while this one is relaxed
@@ -1210,6 +1213,8 @@ namespace mtd
 					mapgen_elevations(s_grad, lp, S, gen_elev + (size_t)gen_next * T, tid, SMALL_THREADS);
 				}
 				MTD_PHASE(4); // relaxation (slowest layer)
+				if (tid == 0 && !gen && l0 + R >= n)
+					claim = atomicAdd(P.map_counter, 1u); // consumed at the top of the loop
 
 				// ---- 4. full-path walks (one lane per spawner) overlapped with next-hop tiles + write-out of this pass ----
 				// Blocked tiles are still parked at 0 in the resident layers: every reader below maps "0 and not this layer's
