@@ -96,6 +96,14 @@ namespace
 	};
 }
 
+// one flag word (and its blocking byte on the tiled path) set from kernel arguments: mtd_grid_set_flags
+__global__ void k_poke_flags(uint16_t *flag, uint16_t value, uint8_t *blocked, uint8_t b)
+{
+	*flag = value;
+	if (blocked)
+		*blocked = b;
+}
+
 struct mtd_ctx
 {
 	int device = 0;
@@ -122,6 +130,7 @@ struct mtd_ctx
 	uint32_t last_rounds = 0;
 	DevBuf<unsigned long long> a_inbox;
 	DevBuf<uint32_t> a_tail, a_ctamin, a_ctl, a_fly;
+	int async_workers = ASYNC_WORKERS; // worker warps per SM in use
 	int async_nb_rule = 0, async_depth = 2; // measured (profiles/r02g_*): the neighbour rule halves the visits but not the time; two mailboxes: 14.5 -> 13.0 ms on C4
 	uint32_t async_nb_margin = 0; // dataflow scheduler of k_tile_async: inbox rings, ring tails, per-CTA smallest keys, control words
 	bool big_async = true;         // large grids: k_tile_async (no global rounds); false = k_tile_rounds (A/B and multi-stripe contexts)
@@ -203,6 +212,8 @@ struct mtd_ctx
 	DevBuf<uint32_t> d_small; // alive count, spawn out ...
 	DevBuf<int> d_trial;
 	HostFlags *hflags = nullptr; // pinned
+	unsigned char *pin_stage = nullptr; // pinned staging for small device->host results that go to pageable memory
+	size_t pin_stage_bytes = 0;
 
 	// timing probe
 	bool profiling = false;
@@ -324,6 +335,75 @@ namespace
 			CU(cudaMemsetAsync(ctx->d_status.p, 0, sizeof(int), ctx->stream));
 			return status_to_error(ctx, st);
 		}
+		return MTD_OK;
+	}
+
+	// Results of one call going to the caller's host memory. A copy from the device into PAGEABLE memory is staged by the
+	// driver copy by copy and blocks the calling thread each time (six of them cost more than the kernel on the game-sized
+	// map); small result sets therefore travel into one pinned arena with asynchronous copies, one synchronisation, and are
+	// moved to the caller's buffers by memcpy. Page-locked destinations and large results are copied straight.
+	struct D2HItem
+	{
+		void *dst;
+		const void *src;
+		size_t bytes;
+	};
+
+	int d2h_results(mtd_ctx *ctx, const D2HItem *items, int n)
+	{
+		size_t total = 0, biggest = 0;
+		int ib = -1;
+		for (int i = 0; i < n; i++)
+			if (items[i].dst && items[i].bytes)
+			{
+				total += (items[i].bytes + 15) & ~(size_t)15;
+				if (items[i].bytes > biggest)
+				{
+					biggest = items[i].bytes;
+					ib = i;
+				}
+			}
+		bool stage = ib >= 0 && total <= ((size_t)4 << 20);
+		if (stage)
+		{
+			cudaPointerAttributes at;
+			if (cudaPointerGetAttributes(&at, items[ib].dst) == cudaSuccess)
+				stage = at.type == cudaMemoryTypeUnregistered;
+			else
+				cudaGetLastError();
+		}
+		if (stage && ctx->pin_stage_bytes < total)
+		{
+			if (ctx->pin_stage)
+				cudaFreeHost(ctx->pin_stage);
+			ctx->pin_stage = nullptr;
+			ctx->pin_stage_bytes = 0;
+			const size_t want = total < ((size_t)1 << 20) ? ((size_t)1 << 20) : ((size_t)4 << 20);
+			if (cudaHostAlloc((void **)&ctx->pin_stage, want, cudaHostAllocDefault) == cudaSuccess)
+				ctx->pin_stage_bytes = want;
+			else
+			{
+				cudaGetLastError();
+				stage = false;
+			}
+		}
+		size_t off = 0;
+		for (int i = 0; i < n; i++)
+			if (items[i].dst && items[i].bytes)
+			{
+				CU(cudaMemcpyAsync(stage ? (void *)(ctx->pin_stage + off) : items[i].dst, items[i].src, items[i].bytes, cudaMemcpyDeviceToHost, ctx->stream));
+				off += (items[i].bytes + 15) & ~(size_t)15;
+			}
+		const int rc = sync_and_status(ctx);
+		if (rc || !stage)
+			return rc;
+		off = 0;
+		for (int i = 0; i < n; i++)
+			if (items[i].dst && items[i].bytes)
+			{
+				memcpy(items[i].dst, ctx->pin_stage + off, items[i].bytes);
+				off += (items[i].bytes + 15) & ~(size_t)15;
+			}
 		return MTD_OK;
 	}
 
@@ -577,6 +657,7 @@ namespace
 		A.nb_rule = ctx->async_nb_rule;
 		A.nb_margin = ctx->async_nb_margin;
 		A.depth = ctx->async_depth;
+		A.workers = ctx->async_workers;
 		A.time_limit_ns = 20000000000ull; // an update that takes 20 s is reported, not waited for
 		P.tile_delta = ctx->async_delta;
 		// frames staged by TMA: one tensor map over the labels of all layers, one over the packed weights
@@ -1142,6 +1223,8 @@ extern "C" void mtd_destroy(mtd_ctx *ctx)
 	ctx->d_trial.release();
 	if (ctx->hflags)
 		cudaFreeHost(ctx->hflags);
+	if (ctx->pin_stage)
+		cudaFreeHost(ctx->pin_stage);
 	if (ctx->own_stream && ctx->stream)
 		cudaStreamDestroy(ctx->stream);
 	delete ctx;
@@ -1195,6 +1278,9 @@ extern "C" int mtd_debug_set(mtd_ctx *ctx, int key, int64_t value)
 	case MTD_DEBUG_ASYNC_NB_RULE:
 		ctx->async_nb_rule = value >= 0 ? 1 : 0; // value = margin (label units); negative = rule off
 		ctx->async_nb_margin = value >= 0 ? (uint32_t)value : 0u;
+		return MTD_OK;
+	case MTD_DEBUG_ASYNC_WORKERS:
+		ctx->async_workers = value < 1 ? 1 : value > ASYNC_WORKERS ? ASYNC_WORKERS : (int)value;
 		return MTD_OK;
 	case MTD_DEBUG_ASYNC_DEPTH:
 		ctx->async_depth = value >= 2 ? 2 : 1;
@@ -1782,14 +1868,10 @@ extern "C" int mtd_grid_set_flags(mtd_ctx *ctx, uint32_t tile, uint16_t flags)
 	}
 	else
 		ctx->inc_layers_ok = false; // no host mirror of the blocking bits: the next update is a full one
-	ctx->hflags->spawn[0] = flags; // staged in pinned memory so the async copy has a stable source
-	CU(cudaMemcpyAsync(ctx->flags.p + tile, &ctx->hflags->spawn[0], 2, cudaMemcpyHostToDevice, ctx->stream));
-	if (!ctx->small)
-	{
-		ctx->hflags->spawn[1] = (flags & F_BLOCKING) ? 1u : 0u;
-		CU(cudaMemcpyAsync(ctx->blocked.p + tile, &ctx->hflags->spawn[1], 1, cudaMemcpyHostToDevice, ctx->stream));
-	}
-	CU(cudaStreamSynchronize(ctx->stream));
+	// the value travels as a kernel argument: no staging memory whose reuse would need a synchronisation, so a scripted
+	// game (flag flip, rebuild, tick, ...) stays asynchronous up to the call that returns something
+	k_poke_flags<<<1, 1, 0, ctx->stream>>>(ctx->flags.p + tile, flags, ctx->small ? nullptr : ctx->blocked.p + tile, (uint8_t)((flags & F_BLOCKING) ? 1 : 0));
+	LAUNCHED();
 	return MTD_OK;
 }
 
@@ -1889,11 +1971,8 @@ extern "C" int mtd_directions_update(mtd_ctx *ctx, const uint32_t *sources, int3
 	int rc = directions_dev(ctx, sources, nsrc, extra_blocked, tiles_out ? ctx->scratch_u32a.p : nullptr, ctx->scratch_u32b.p);
 	if (rc)
 		return rc;
-	if (tiles_out)
-		CU(cudaMemcpyAsync(tiles_out, ctx->scratch_u32a.p, ctx->T * 4, cudaMemcpyDeviceToHost, ctx->stream));
-	if (dist_out)
-		CU(cudaMemcpyAsync(dist_out, ctx->scratch_u32b.p, ctx->T * 4, cudaMemcpyDeviceToHost, ctx->stream));
-	return sync_and_status(ctx);
+	const D2HItem out[2] = { { tiles_out, ctx->scratch_u32a.p, (size_t)ctx->T * 4 }, { dist_out, ctx->scratch_u32b.p, (size_t)ctx->T * 4 } };
+	return d2h_results(ctx, out, 2);
 }
 
 // =====================================================================================================
@@ -1930,19 +2009,15 @@ extern "C" int mtd_waypoints_update(mtd_ctx *ctx, const uint32_t *wp_tiles, int3
 	int rc = waypoints_dev(ctx, wp_tiles, n, fullpath_buf ? fullpath_cap : 0u);
 	if (rc || n == 0)
 		return rc;
-	if (tiles_out)
-		CU(cudaMemcpyAsync(tiles_out, ctx->ltiles.p, (size_t)n * ctx->T * 4, cudaMemcpyDeviceToHost, ctx->stream));
-	if (dist_out)
-		CU(cudaMemcpyAsync(dist_out, ctx->ldist.p, (size_t)n * ctx->T * 4, cudaMemcpyDeviceToHost, ctx->stream));
-	if (fullpath_buf && fullpath_cap)
-		CU(cudaMemcpyAsync(fullpath_buf, ctx->fp_buf.p, (size_t)n * fullpath_cap * 4, cudaMemcpyDeviceToHost, ctx->stream));
-	if (fullpath_len)
-		CU(cudaMemcpyAsync(fullpath_len, ctx->fp_len.p, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
-	if (full_distance)
-		CU(cudaMemcpyAsync(full_distance, ctx->fp_dist.p, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
-	if (agg3)
-		CU(cudaMemcpyAsync(agg3, ctx->agg.p, 12, cudaMemcpyDeviceToHost, ctx->stream));
-	return sync_and_status(ctx);
+	const D2HItem out[6] = {
+		{ tiles_out, ctx->ltiles.p, (size_t)n * ctx->T * 4 },
+		{ dist_out, ctx->ldist.p, (size_t)n * ctx->T * 4 },
+		{ fullpath_cap ? fullpath_buf : nullptr, ctx->fp_buf.p, (size_t)n * fullpath_cap * 4 },
+		{ fullpath_len, ctx->fp_len.p, (size_t)n * 4 },
+		{ full_distance, ctx->fp_dist.p, (size_t)n * 4 },
+		{ agg3, ctx->agg.p, 12 },
+	};
+	return d2h_results(ctx, out, 6);
 }
 
 extern "C" int mtd_waypoints_layers_dev(mtd_ctx *ctx, uint32_t **d_tiles, uint32_t **d_dist)

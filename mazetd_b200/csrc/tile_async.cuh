@@ -126,6 +126,7 @@ namespace mtd
 		int nb_rule;         // 1: an item does not start while a neighbour tile is in flight or pending with a smaller key
 		uint32_t nb_margin;  // ... smaller by more than this
 		int depth;           // mailboxes per worker in use: 1 or 2
+		int workers;         // worker warps the scheduler hands items to (<= ASYNC_WORKERS; the rest sleep)
 		unsigned long long time_limit_ns;
 	};
 
@@ -773,8 +774,8 @@ namespace mtd
 			uint32_t idle_w = 0, half_w = 0;
 			{
 				const uint32_t b0 = (busy_slots >> (2u * (lane & 15u))) & 3u;
-				idle_w = __ballot_sync(0xFFFFFFFFu, lane < ASYNC_WORKERS && b0 == 0u);
-				half_w = __ballot_sync(0xFFFFFFFFu, lane < ASYNC_WORKERS && (b0 == 1u || b0 == 2u) && A.depth > 1);
+				idle_w = __ballot_sync(0xFFFFFFFFu, lane < (uint32_t)A.workers && b0 == 0u);
+				half_w = __ballot_sync(0xFFFFFFFFu, lane < (uint32_t)A.workers && (b0 == 1u || b0 == 2u) && A.depth > 1);
 			}
 			__syncwarp();
 			uint32_t nasg = 0;

@@ -19,10 +19,11 @@ dt = torch.empty((n, W * H), dtype=torch.int32, device=dev)
 dd = torch.empty((n, W * H), dtype=torch.int32, device=dev)
 ctx.debug_set(ctx.DEBUG_BIG_TMA, tma)
 import os
-nb = int(os.environ.get('MTD_NB', '0'))
-depth = int(os.environ.get('MTD_DEPTH', '1'))
+nb = int(os.environ.get('MTD_NB', '-1'))
+depth = int(os.environ.get('MTD_DEPTH', '2'))
 ctx.debug_set(ctx.DEBUG_ASYNC_NB_RULE, nb)
 ctx.debug_set(ctx.DEBUG_ASYNC_DEPTH, depth)
+ctx.debug_set(ctx.DEBUG_ASYNC_WORKERS, int(os.environ.get('MTD_WORKERS', '16')))
 for delta in deltas:
     ctx.debug_set(ctx.DEBUG_ASYNC_DELTA, delta)
     for it in range(2):
@@ -32,4 +33,4 @@ for delta in deltas:
             ctx.directions_update_dev(srcs[:nsrc], dt.data_ptr(), dd.data_ptr())
         ctx.synchronize()
         relax, _ = ctx.profile_read(ctx.K_BIG_RELAX)
-    print(json.dumps(dict(cfg=cfg, delta=delta, nb=nb, depth=depth, relax_ms=round(relax, 3), **ctx.big_stats())), flush=True)
+    print(json.dumps(dict(cfg=cfg, delta=delta, nb=nb, depth=depth, workers=int(os.environ.get('MTD_WORKERS', '16')), relax_ms=round(relax, 3), **ctx.big_stats())), flush=True)
