@@ -207,6 +207,19 @@ typedef struct mtd_mapgen_params
 int mtd_mapgen_batch(mtd_ctx *ctx, const mtd_mapgen_params *p, uint64_t s1, uint64_t s2, int32_t first, int32_t nmaps, int16_t *elev, uint16_t *flags, uint32_t *wp_tiles, uint32_t *tiles, uint32_t *dist, uint32_t *fullpath, uint32_t *fullpath_len, uint32_t *full_distance, uint32_t *agg);
 /* same with DEVICE output pointers (all required except tiles/dist/fullpath, which may be NULL); asynchronous */
 int mtd_mapgen_batch_dev(mtd_ctx *ctx, const mtd_mapgen_params *p, uint64_t s1, uint64_t s2, int32_t first, int32_t nmaps, int16_t *d_elev, uint16_t *d_flags, uint32_t *d_wp_tiles, uint32_t *d_tiles, uint32_t *d_dist, uint32_t *d_fullpath, uint32_t *d_fullpath_len, uint32_t *d_full_distance, uint32_t *d_agg);
+
+/* Allocation-free variant. NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Waypoints::update + full-path walks of `nmaps` maps that are already on the device: d_elev / d_flags [nmaps][W*H],
+ * d_wp_tiles [nmaps][n] in, d_fullpath_len / d_full_distance [nmaps][n] and d_agg [nmaps][3] out (device pointers, all
+ * required). The kernel's scratch -- the distance and next-hop layers its walker warps chase, and its map counter -- is a
+ * fixed array inside the library image (MTD_NOALLOC_SCRATCH_BYTES, held by every GPU that loads the library until exit):
+ * the call makes no cudaMalloc / cudaFree and no allocating library call. Limit: 256 + nmaps * n * W * H * 8 bytes must fit the
+ * array (e.g. 12 maps of 101 x 101 with 4 waypoints), otherwise MTD_ERR_CAPACITY. Asynchronous on the context's stream like
+ * the other _dev calls (kernel status through mtd_synchronize). Every call, from any context, shares the one array per GPU:
+ * calls that overlap on a GPU race; the array keeps the last call's layers (its control words are cleared by each call). */
+#define MTD_NOALLOC_SCRATCH_BYTES (4u << 20)
+int mtd_waypoints_paths_noalloc(mtd_ctx *ctx, int32_t W, int32_t H, int32_t nmaps, int32_t n, const int16_t *d_elev, const uint16_t *d_flags, const uint32_t *d_wp_tiles, uint32_t *d_fullpath_len, uint32_t *d_full_distance, uint32_t *d_agg);
 /* newGrid after the elevation sampling (sources/map/grid.cpp:160-196): biome flags, maxSlope / radius invalidation,
  * fillUnreachable (largest 4-connected component, first-discovered wins ties), findBorder, Mana -- on the CALLER's
  * int16 elevations [nmaps][T] (host), flags out [nmaps][T] (host). Uses W, H, ox, oy, radius of *p. This is the part of

@@ -26,6 +26,7 @@ EXPORTS = [
     "mtd_monsters_positions_dev", "mtd_monsters_positions", "mtd_monster_spawn",
     "mtd_monsters_dots_upload", "mtd_monsters_dots_tick_dev", "mtd_monsters_dots_tick", "mtd_monsters_dots_download",
     "mtd_monsters_class_upload", "mtd_towers_upload", "mtd_towers_attack_dev", "mtd_towers_download", "mtd_waypoints_layers_refresh",
+    "mtd_waypoints_paths_noalloc",
 ]
 
 
@@ -91,6 +92,7 @@ def load():
     L.mtd_mapgen_batch.argtypes = [vp, C.POINTER(MapgenParams), u64, u64, i32, i32] + [vp] * 9
     L.mtd_mapgen_batch_dev.argtypes = [vp, C.POINTER(MapgenParams), u64, u64, i32, i32] + [vp] * 9
     L.mtd_grid_from_elevations.argtypes = [vp, C.POINTER(MapgenParams), i32, vp, vp]
+    L.mtd_waypoints_paths_noalloc.argtypes = [vp, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp]
     L.mtd_sdf_lattice.argtypes = [vp, u64, u64, i32, i32, i32, i32, vp, vp, vp, vp, vp]
     L.mtd_elevation_samples.argtypes = [vp, u64, u64, vp, i32, vp]
     L.mtd_monsters_upload.argtypes = [vp, i32] + [vp] * 10
@@ -368,6 +370,12 @@ class Context:
         """ptrs: dict of raw device pointers (ints) for elev, flags, wp_tiles, tiles, dist, fullpath, fullpath_len, full_distance, agg"""
         p = MapgenParams(W, H, ox, oy, radius, nwp, cap)
         self._ck(self.L.mtd_mapgen_batch_dev(self.h, C.byref(p), s1, s2, first, nmaps, *[_p(ptrs.get(k)) for k in ("elev", "flags", "wp_tiles", "tiles", "dist", "fullpath", "fullpath_len", "full_distance", "agg")]))
+
+    NOALLOC_SCRATCH_BYTES = 4 << 20
+
+    def waypoints_paths_noalloc(self, W, H, nmaps, n, d_elev, d_flags, d_wp_tiles, d_fullpath_len, d_full_distance, d_agg):
+        """mtd_waypoints_paths_noalloc: raw device pointers (ints) in and out; asynchronous; allocates nothing"""
+        self._ck(self.L.mtd_waypoints_paths_noalloc(self.h, W, H, nmaps, n, _p(d_elev), _p(d_flags), _p(d_wp_tiles), _p(d_fullpath_len), _p(d_full_distance), _p(d_agg)))
 
     def grid_from_elevations(self, elev, W=101, H=101, ox=50, oy=50, radius=45):
         """newGrid after the elevation sampling on the caller's int16 elevations [nmaps][T] -> flags [nmaps][T]"""

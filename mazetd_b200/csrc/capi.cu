@@ -2915,3 +2915,111 @@ extern "C" int mtd_waypoints_layers_refresh(mtd_ctx *ctx)
 	ctx->inc_layers_ok = ctx->inc_n == ctx->nlayers && !ctx->h_blocking.empty();
 	return MTD_OK;
 }
+
+// =====================================================================================================
+// Allocation-free variant (no counterpart in the reference)
+// =====================================================================================================
+// Full-path lengths / distances / aggregates of a few resident maps, with the kernel's scratch -- the distance and
+// next-hop layers the walker warps chase, and the map counter -- in a fixed array that is part of the library image
+// instead of cudaMalloc'ed buffers. Every GPU that loads the library holds MTD_NOALLOC_SCRATCH_BYTES for it until exit.
+// All calls share the array: calls that overlap on one GPU (two streams, two contexts) race.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[MTD_NOALLOC_SCRATCH_BYTES];
+
+namespace
+{
+	constexpr int NOALLOC_MAX_DEVICES = 64;
+	constexpr size_t NOALLOC_HEAD = 256; // control words in front of the layers (word 0: the kernel's map counter)
+	std::mutex g_noalloc_mu;
+	unsigned char *g_noalloc_ptr[NOALLOC_MAX_DEVICES]; // device address of g_noalloc_scratch, per device (the symbol's name is only a host-side handle)
+	bool g_noalloc_cfg[NOALLOC_MAX_DEVICES];           // the kernel was opted in to its shared memory size on that device
+
+	// once per device, with that device current (the caller holds a DeviceGuard)
+	int noalloc_setup(mtd_ctx *ctx, unsigned char **scratch)
+	{
+		if (ctx->device < 0 || ctx->device >= NOALLOC_MAX_DEVICES)
+			return fail(ctx, MTD_ERR_CAPACITY, "device ordinal %d beyond the %d the allocation-free entry point keeps state for", ctx->device, NOALLOC_MAX_DEVICES);
+		std::lock_guard<std::mutex> lk(g_noalloc_mu);
+		if (!g_noalloc_ptr[ctx->device])
+		{
+			void *p = nullptr;
+			const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+			if (e != cudaSuccess || !p)
+			{
+				(void)cudaGetLastError();
+				return fail(ctx, MTD_ERR_CUDA, "cudaGetSymbolAddress(scratch) failed: %s", cudaGetErrorString(e));
+			}
+			g_noalloc_ptr[ctx->device] = (unsigned char *)p;
+		}
+		if (!g_noalloc_cfg[ctx->device])
+		{
+			const cudaError_t e = cudaFuncSetAttribute((const void *)k_waypoints_small<SMALL_GROUP_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MAX_SMEM);
+			if (e != cudaSuccess)
+			{
+				(void)cudaGetLastError();
+				return fail(ctx, MTD_ERR_CUDA, "kernel configuration failed: %s", cudaGetErrorString(e));
+			}
+			g_noalloc_cfg[ctx->device] = true;
+		}
+		*scratch = g_noalloc_ptr[ctx->device];
+		return MTD_OK;
+	}
+}
+
+extern "C" int mtd_waypoints_paths_noalloc(mtd_ctx *ctx, int32_t W, int32_t H, int32_t nmaps, int32_t n, const int16_t *d_elev, const uint16_t *d_flags, const uint32_t *d_wp_tiles, uint32_t *d_fullpath_len, uint32_t *d_full_distance, uint32_t *d_agg)
+{
+	if (!ctx)
+		return MTD_ERR_ARG;
+	std::lock_guard<std::mutex> lk(ctx->mu);
+	DeviceGuard g(ctx->device);
+	if (W < 1 || H < 1 || nmaps < 0 || n < 1 || n > FIND_MAXN)
+		return fail(ctx, MTD_ERR_ARG, "bad shape: W, H >= 1, nmaps >= 0, 1 <= n <= %d waypoints", FIND_MAXN);
+	if (nmaps == 0)
+		return MTD_OK;
+	if (!d_elev || !d_flags || !d_wp_tiles || !d_fullpath_len || !d_full_distance || !d_agg)
+		return fail(ctx, MTD_ERR_ARG, "every input and output pointer is required");
+	const int R = small_resident(W, H, n);
+	if (R < 1)
+		return fail(ctx, MTD_ERR_CAPACITY, "a %d x %d map does not fit the one-CTA path", W, H);
+	const size_t T = (size_t)W * H;
+	const size_t layers = (size_t)nmaps * n * T; // words per array (distances, next hops)
+	const size_t need = NOALLOC_HEAD + layers * 8;
+	if (need > (size_t)MTD_NOALLOC_SCRATCH_BYTES)
+		return fail(ctx, MTD_ERR_CAPACITY, "nmaps * n * W * H * 8 + %zu = %zu bytes of layers exceed the fixed scratch of %zu bytes (MTD_NOALLOC_SCRATCH_BYTES): at most %zu tiles x layers per call",
+					NOALLOC_HEAD, need, (size_t)MTD_NOALLOC_SCRATCH_BYTES, ((size_t)MTD_NOALLOC_SCRATCH_BYTES - NOALLOC_HEAD) / 8);
+	unsigned char *scratch = nullptr;
+	const int rc = noalloc_setup(ctx, &scratch);
+	if (rc)
+		return rc;
+
+	constexpr int GW = SMALL_GROUP_WARPS;
+	WaypointsSmallParams P;
+	memset(&P, 0, sizeof(P));
+	P.W = W;
+	P.H = H;
+	P.n = n;
+	P.R = R;
+	P.nmaps = nmaps;
+	P.nsrc = 1;
+	P.elev = d_elev;
+	P.flags = d_flags;
+	P.wp = d_wp_tiles;
+	P.extra_blocked = MTD_M;
+	P.inc_tile = MTD_M;
+	P.dist = (uint32_t *)(scratch + NOALLOC_HEAD);
+	P.tiles = P.dist + layers;
+	P.fullpath_len = d_fullpath_len;
+	P.full_distance = d_full_distance;
+	P.agg = d_agg;
+	P.status = ctx->d_status.p; // allocated by mtd_create; read by mtd_synchronize
+	P.map_counter = (uint32_t *)scratch;
+	P.smem_budget = (uint32_t)MAX_SMEM;
+	P.walker = 1; // the walker warps chase the layers in the scratch
+	const SmallLayout L = small_layout(W, H, R, P.smem_budget, 0, GW);
+	// the array keeps the previous call's contents: the map counter must start at zero; the layers are written before they are read
+	CU(cudaMemsetAsync(scratch, 0, NOALLOC_HEAD, ctx->stream));
+	const int per_sm = (size_t)L.total * 2 + 2048 <= MAX_SMEM ? 2 : 1;
+	const int blocks = nmaps < ctx->sms * per_sm ? nmaps : ctx->sms * per_sm;
+	k_waypoints_small<GW><<<blocks, SMALL_BLOCK, L.total, ctx->stream>>>(P);
+	LAUNCHED();
+	return MTD_OK;
+}
