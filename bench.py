@@ -495,9 +495,10 @@ def leg_c4(ctx, dev, stream, rank, world, args):
         med = float(np.median(ms))
         peak, src = hbm_peak()
         ach = Wb * Hb * 12 / (med * 1e-3) / 1e9
+        bs = st.ctx.big_stats()
         out.update(partition=f"{world} row stripes (cuts on 64-row tile boundaries), boundary rows and keys stored into the neighbour's memory by the relaxation kernel (CUDA IPC over NVLink)",
-                   ms=med, ms_all=ms, value=Wb * Hb / (med * 1e-3), unit="tile relaxations/s", global_rounds=int(rounds[0]),
-                   roofline={"bound": "hbm", "kernel": "k_tile_rounds (peer-coupled)", "achieved": ach, "peak": peak * world, "unit": "GB/s", "frac": ach / (peak * world), "traffic": None, "peak_source": src + f" x {world} GPUs"})
+                   ms=med, ms_all=ms, value=Wb * Hb / (med * 1e-3), unit="tile relaxations/s", global_rounds=int(rounds[0]), tile_visits_rank0=bs["visits"],
+                   roofline={"bound": "hbm", "kernel": ("k_tile_async" if bs["dataflow"] else "k_tile_rounds") + " (peer-coupled)", "achieved": ach, "peak": peak * world, "unit": "GB/s", "frac": ach / (peak * world), "traffic": None, "peak_source": src + f" x {world} GPUs"})
         if g is not None:
             import torch.distributed as dist
 

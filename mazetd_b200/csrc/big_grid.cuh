@@ -89,7 +89,12 @@ namespace mtd
 	constexpr int PEER_EPOCH = 13;    // local: phases this rank has been through since the block was created
 	constexpr int PEER_SLOT_A = 16;   // [16] phase tag of rank j ("everything I wrote into your block this round has landed")
 	constexpr int PEER_SLOT_B = 32;   // [16] x 64 bit: smallest key << 32 | queue length (24 bits) << 8 | phase tag (8 bits) of rank j
-	constexpr int PEER_CTL_WORDS = 64;
+	// peer-coupled DATAFLOW kernel (k_tile_async with ctl0 != null): no rounds, so instead of the two phases above
+	constexpr int PEER_AREQ = 64;     // written by rank 0 into every block: number of the termination wave it is collecting
+	constexpr int PEER_ASTOP = 65;    // written by rank 0 into every block: the run is over
+	constexpr int PEER_AWM = 80;      // [16] smallest pending key of rank j (written by rank j into every block): the priority window is global
+	constexpr int PEER_AREPLY = 96;   // [16] x 64 bit, read in rank 0's block: wave tag (8) | idle (1) | border offers made (27) | border offers consumed (28) of rank j
+	constexpr int PEER_CTL_WORDS = 128;
 
 	// ---- edge weights -------------------------------------------------------------------------------
 	__global__ void k_edge_weights(int W, int Hl, const int16_t *__restrict__ elev, const int16_t *__restrict__ elev_below /* row after the stripe or null */, const uint16_t *__restrict__ flags, uint32_t *__restrict__ wpack, uint8_t *__restrict__ blocked)

@@ -622,7 +622,9 @@ namespace
 				   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 	}
 
-	int run_async(mtd_ctx *ctx, BigParams P, size_t nitems)
+	// peer = true: peer-coupled row stripes (P.ctl0 set). The kernel is only queued: the ranks enter, exchange border offers
+	// and detect the end of the run on the device; the caller waits in mtd_stripe_peer_finish.
+	int run_async(mtd_ctx *ctx, BigParams P, size_t nitems, bool peer = false)
 	{
 		const size_t smem = async_smem_bytes<BIG_TS>();
 		const int threads = (ASYNC_WORKERS + 1) * 32;
@@ -631,7 +633,15 @@ namespace
 			return MTD_ERR_CUDA;
 		if (per_sm < 1)
 			return fail(ctx, MTD_ERR_CUDA, "the dataflow relaxation kernel does not fit an SM");
-		const int ctas = ctx->sms;
+		int ctas = ctx->sms;
+		if (peer && P.soft_grid)
+		{
+			// several stripes share this GPU (tests): every stripe's kernel must be resident at once, one CTA per SM
+			const int share = ctx->sms / (ctx->peer_world > 0 ? ctx->peer_world : 1);
+			ctas = ctx->peer_ctas < share ? ctx->peer_ctas : share;
+			if (ctas < 1)
+				return fail(ctx, MTD_ERR_CAPACITY, "more stripes than SMs on one GPU");
+		}
 		uint32_t cap = 64;
 		while ((size_t)cap < (nitems + ctas - 1) / ctas + 64)
 			cap <<= 1;
@@ -658,21 +668,33 @@ namespace
 		A.nb_margin = ctx->async_nb_margin;
 		A.depth = ctx->async_depth;
 		A.workers = ctx->async_workers;
-		A.time_limit_ns = 20000000000ull; // an update that takes 20 s is reported, not waited for
+		A.time_limit_ns = peer ? 8000000000ull : 20000000000ull; // an update that takes this long is reported, not waited for
 		P.tile_delta = ctx->async_delta;
 		// frames staged by TMA: one tensor map over the labels of all layers, one over the packed weights
 		alignas(64) CUtensorMap tm_dist, tm_w;
 		memset(&tm_dist, 0, sizeof(tm_dist));
 		memset(&tm_w, 0, sizeof(tm_w));
-		A.use_tma = ctx->big_tma && P.aligned16 && frame_tensor_map(&tm_dist, P.dist, P.W, P.y1 - P.y0, P.nlayers, P.layer_stride) && frame_tensor_map(&tm_w, P.wpack, P.W, P.y1 - P.y0, 0, 0) ? 1 : 0;
+		A.use_tma = !peer && ctx->big_tma && P.aligned16 && frame_tensor_map(&tm_dist, P.dist, P.W, P.y1 - P.y0, P.nlayers, P.layer_stride) && frame_tensor_map(&tm_w, P.wpack, P.W, P.y1 - P.y0, 0, 0) ? 1 : 0;
 		ctx->last_tma = A.use_tma != 0;
+		if (peer) // stripe_prepare seeded the round-based work-lists, which also posts keys: the dataflow kernel starts from "nothing pending"
+			CU(cudaMemsetAsync(ctx->tilekey.p, 0xFF, nitems * 4, ctx->stream));
 		k_async_seed<BIG_TS><<<(P.nlayers * P.nsrc + 127) / 128, 128, 0, ctx->stream>>>(P, A);
 		LAUNCHED();
 		void *args[] = { (void *)&P, (void *)&A, (void *)&tm_dist, (void *)&tm_w };
 		{
 			ProfScope prof(ctx, MTD_K_BIG_RELAX);
-			CU(cudaLaunchCooperativeKernel((const void *)k_tile_async<BIG_TS>, dim3((unsigned)ctas), dim3((unsigned)threads), args, smem, ctx->stream));
+			if (peer && P.soft_grid)
+				k_tile_async<BIG_TS><<<dim3((unsigned)ctas), dim3((unsigned)threads), smem, ctx->stream>>>(P, A, tm_dist, tm_w);
+			else
+				CU(cudaLaunchCooperativeKernel((const void *)k_tile_async<BIG_TS>, dim3((unsigned)ctas), dim3((unsigned)threads), args, smem, ctx->stream));
 			LAUNCHED();
+		}
+		if (peer)
+		{
+			ctx->hflags->round_out[1] = 0u; // no rounds in this mode
+			CU(cudaMemcpyAsync(ctx->hflags->async_ctl, ctx->a_ctl.p, 4 * 4, cudaMemcpyDeviceToHost, ctx->stream));
+			ctx->last_async = true;
+			return MTD_OK;
 		}
 		CU(cudaMemcpyAsync(ctx->hflags->async_ctl, ctx->a_ctl.p, 4 * 4, cudaMemcpyDeviceToHost, ctx->stream));
 		CU(cudaStreamSynchronize(ctx->stream));
@@ -1806,9 +1828,16 @@ extern "C" int mtd_stripe_peer_launch_dev(mtd_ctx *ctx, const uint32_t *sources,
 	if (rc)
 		return rc;
 	const BigParams P = stripe_params(ctx);
-	int round = 0;
-	uint32_t pending = 0;
-	rc = run_rounds(ctx, P, round, 0, pending); // returns once the kernel is queued: the ranks stop together on the device
+	const size_t nitems = (size_t)ctx->tilesX * ctx->tilesY;
+	if (ctx->big_async && async_fits(ctx, nitems) && (!P.soft_grid || ctx->sms / ctx->peer_world >= 1))
+		rc = run_async(ctx, P, nitems, true); // dataflow kernel: border offers and termination go rank to rank, no rounds
+	else
+	{
+		int round = 0;
+		uint32_t pending = 0;
+		rc = run_rounds(ctx, P, round, 0, pending); // returns once the kernel is queued: the ranks stop together on the device
+		ctx->last_async = false;
+	}
 	if (rc)
 		return rc;
 	{
@@ -1832,6 +1861,8 @@ extern "C" int mtd_stripe_peer_finish(mtd_ctx *ctx, uint32_t *rounds_out)
 	DeviceGuard g(ctx->device);
 	const int rc = sync_and_status(ctx);
 	ctx->last_rounds = ctx->hflags->round_out[1];
+	if (ctx->last_async)
+		ctx->last_visits = ctx->hflags->async_ctl[ACTL_VISITS];
 	if (rounds_out)
 		*rounds_out = ctx->last_rounds;
 	if (rc == MTD_ERR_STATE && ctx->peer_root && ctx->peer_blk.p)

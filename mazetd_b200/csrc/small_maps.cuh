@@ -37,7 +37,8 @@ namespace mtd
 		return (size_t)T * 4 + (size_t)((T + 1) & ~1) * 2 * 2 + 128 * sizeof(float2) + 64;
 	}
 
-	__global__ void __launch_bounds__(512, 1) k_mapgen_grid(const MapgenGridParams P)
+	// (512, 2): two CTAs per SM hide each other's latency in the label-propagation passes; 64 registers is what that allows
+	__global__ void __launch_bounds__(512, 2) k_mapgen_grid(const MapgenGridParams P)
 	{
 		extern __shared__ __align__(16) unsigned char smem_raw[];
 		const int W = P.W, H = P.H, T = W * H;

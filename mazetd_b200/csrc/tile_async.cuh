@@ -38,6 +38,11 @@ namespace mtd
 	constexpr int ACTL_ABORT = 1;       // a scheduler hit the time limit
 	constexpr int ACTL_VISITS = 2;      // statistics
 	constexpr int ACTL_IDLE_POLLS = 3;
+	// peer-coupled stripes
+	constexpr int ACTL_STOP = 4; // set by CTA 0's scheduler when rank 0 announced the end of the run
+	constexpr int ACTL_SENT = 5; // offers to a neighbour rank that made its border tile pending
+	constexpr int ACTL_RECV = 6; // such offers from the neighbour ranks taken over by this rank's schedulers
+	constexpr int ACTL_GO = 7;   // set by CTA 0's scheduler once every rank has entered the run and the initial halo rows have landed
 	constexpr int ACTL_WORDS = 32;
 
 	// A worker's frame: the WarpFrame layout (34 rows of 40 words, grid column gx0 + rx at word rx + 3) with both arrays on
@@ -161,12 +166,21 @@ namespace mtd
 		const int layer = s / P.nsrc;
 		const uint32_t src = P.sources[s];
 		const int x = (int)(src % (uint32_t)P.W), y = (int)(src / (uint32_t)P.W);
-		if (y < P.y0 || y >= P.y1)
+		int ty;
+		if (y >= P.y0 && y < P.y1)
+		{
+			P.dist[(size_t)layer * P.layer_stride + (size_t)(y - P.y0) * P.W + x] = 0u;
+			ty = (y - P.y0) / TS;
+		}
+		else if (y == P.y0 - 1)
+			ty = 0; // row stripes: a source on the neighbour's boundary row takes its first hop into my border tile (the visit finds it in the source list)
+		else if (y == P.y1)
+			ty = P.tilesY - 1;
+		else
 			return;
-		P.dist[(size_t)layer * P.layer_stride + (size_t)(y - P.y0) * P.W + x] = 0u;
 		atomicAdd(A.ctl + ACTL_OUTSTANDING, 1u);
 		__threadfence();
-		if (!async_offer(P, A, layer, x / TS, (y - P.y0) / TS, 0u))
+		if (!async_offer(P, A, layer, x / TS, ty, 0u))
 			atomicSub(A.ctl + ACTL_OUTSTANDING, 1u); // several sources in one tile: one item
 	}
 
@@ -640,6 +654,41 @@ namespace mtd
 				MTD_ATICK(1);
 				uint32_t k[4];
 				warp_visit<TS>(P, S, layer, tx, ty, lane, lt, k, guard, A.use_tma ? &tm_dist : nullptr, A.use_tma ? &tm_w : nullptr, tma_phase, slot[mine ^ 1] MTD_ATIMING_PASS);
+				if (P.ctl0)
+				{
+					// row stripes: the tile above / below a border tile belongs to a neighbour rank. Its copy of my boundary row is
+					// in ITS memory: store the row there (NVLink), then post the key in its array of border offers; one of its
+					// schedulers takes it from there. Done BEFORE my own item is given up below: an offer that made the
+					// neighbour's tile pending is counted in ctl[SENT] while this rank still counts as busy (termination, see the
+					// scheduler of CTA 0).
+					const int Hl = P.y1 - P.y0;
+					const int brow = min(TS + 1, Hl - (ty * TS - 1));
+					const int gx = tx * TS + (int)lane;
+					const bool up = ty == 0 && P.peer_up_act && k[0] != MTD_INF, down = ty == P.tilesY - 1 && P.peer_down_act && k[1] != MTD_INF;
+					if (up && gx < P.W)
+						P.peer_up_halo[gx] = S.d[1 * WT::PITCH + 4 + (int)lane];
+					if (down && gx < P.W)
+						P.peer_down_halo[gx] = S.d[(brow - 1) * WT::PITCH + 4 + (int)lane];
+					if (up || down)
+					{
+						__threadfence_system(); // every lane: its part of the row is ordered before the offer
+						__syncwarp();
+						if (lane == 0)
+						{
+							uint32_t made = 0;
+							if (up && atomicMin_system(P.peer_up_act + tx, k[0]) == MTD_INF)
+								made++;
+							if (down && atomicMin_system(P.peer_down_act + tx, k[1]) == MTD_INF)
+								made++;
+							if (made)
+							{
+								atomicAdd(A.ctl + ACTL_SENT, made);
+								__threadfence(); // counted before this visit's own count is given up
+							}
+						}
+						__syncwarp();
+					}
+				}
 				// offers to the four neighbours. The items they may create are counted BEFORE the offers are made (the
 				// count of pending + in-flight items is never behind, so it cannot read zero early); mine is given up with them.
 				const uint32_t kk = lane == 0 ? k[0] : lane == 1 ? k[1] : lane == 2 ? k[2] : k[3];
@@ -688,6 +737,67 @@ namespace mtd
 		unsigned long long *ring = A.inbox + (size_t)me * cap;
 		uint32_t head = 0, pn = 0, polls = 0;
 		uint32_t fill = 0; // lane w < WORKERS: which of worker w's two mailboxes is filled next (the worker empties them in the same order)
+		// ---- peer-coupled stripes: entering the run ----
+		const bool peer = P.ctl0 != nullptr;
+		bool peer_dead = false;
+		uint32_t wave = 1, replied = 0, wm_sent = MTD_INF; // CTA 0, lane 0: termination wave being collected (rank 0) / answered, watermark last published
+		unsigned long long prev_reply[PEER_MAX_WORLD];
+		bool have_prev = false;
+		if (peer)
+		{
+			if (me == 0)
+			{
+				if (lane == 0)
+				{
+					// my words of the protocol start clean (rank 0 writes AREQ / ASTOP, the ranks write AWM and -- into rank 0's block --
+					// AREPLY only after the barriers below)
+					P.ctl[PEER_AREQ] = 0u;
+					P.ctl[PEER_ASTOP] = 0u;
+					for (int j = 0; j < PEER_MAX_WORLD; j++)
+					{
+						P.ctl[PEER_AWM + j] = MTD_INF;
+						reinterpret_cast<unsigned long long *>(P.ctl + PEER_AREPLY)[j] = 0ull;
+					}
+					uint32_t epoch = P.ctl[PEER_EPOCH];
+					// every rank has entered this run (nobody still reads the halo copies of the previous one) ...
+					bool ok = peer_arrive_wait(P, epoch, peer_dead, P.soft_grid ? 4000000000ull : 20000000000ull);
+					P.ctl[PEER_EPOCH] = epoch;
+					if (!ok)
+						atomicOr(P.status, 8); // ST_PEER_TIMEOUT
+				}
+				__syncwarp();
+				// ... my boundary rows as initialised (m, parked blocked tiles and sources 0) go to the neighbours ...
+				const int Hl = P.y1 - P.y0;
+				for (int x = (int)lane; x < P.W; x += 32)
+				{
+					if (P.peer_up_halo)
+						P.peer_up_halo[x] = __ldcg(P.dist + x);
+					if (P.peer_down_halo)
+						P.peer_down_halo[x] = __ldcg(P.dist + (size_t)(Hl - 1) * P.W + x);
+				}
+				__threadfence_system();
+				__syncwarp();
+				if (lane == 0)
+				{
+					// ... and have landed everywhere before any rank reads its copies
+					uint32_t epoch = P.ctl[PEER_EPOCH];
+					if (!peer_arrive_wait(P, epoch, peer_dead))
+						atomicOr(P.status, 8);
+					P.ctl[PEER_EPOCH] = epoch;
+					if (peer_dead)
+						atomicExch(A.ctl + ACTL_ABORT, 1u);
+					__threadfence();
+					atomicExch(A.ctl + ACTL_GO, 1u);
+				}
+				__syncwarp();
+			}
+			else
+			{
+				while (__ldcg(A.ctl + ACTL_GO) == 0u)
+					__nanosleep(500);
+				fence_gpu();
+			}
+		}
 		const unsigned long long t0 = global_timer_ns();
 		bool stop = false;
 		while (!stop)
@@ -699,10 +809,43 @@ namespace mtd
 			const unsigned long long e = __ldcg(ring + ((head + lane) & A.cap_mask));
 			const uint32_t outstanding = __ldcg(A.ctl + ACTL_OUTSTANDING);
 			const uint32_t aborted = __ldcg(A.ctl + ACTL_ABORT);
+			const uint32_t stopped = peer ? __ldcg(A.ctl + ACTL_STOP) : 0u;
 			uint32_t others = MTD_INF;
 			for (int c = (int)lane; c < A.ctas; c += 32)
 				if (c != me)
 					others = min(others, __ldcg(A.ctamin + c));
+			uint32_t others_local = others; // CTA 0 publishes this rank's own position
+			if (peer && (int)lane < P.world && (int)lane != P.rank)
+				others = min(others, ld_sys(P.ctl + PEER_AWM + lane)); // the other ranks' wavefront positions
+			if (peer)
+			{
+				// border offers of the neighbour ranks to the border tiles this CTA owns: taken over and made as local offers
+				// (counted first, like every offer; RECV after the count: a rank that reports "nothing outstanding" together with
+				// a RECV that includes an offer has really finished with it)
+				for (int side = 0; side < 2; side++)
+				{
+					uint32_t *act = side == 0 ? P.act_up : P.act_down;
+					if (!act)
+						continue;
+					const int ty = side == 0 ? 0 : P.tilesY - 1;
+					const int first = (int)(((uint32_t)me + (uint32_t)A.ctas * (uint32_t)(ASYNC_KX * ty) - (uint32_t)(ASYNC_KX * ty)) % (uint32_t)A.ctas); // tx with (tx + KX * ty) % ctas == me
+					for (int tx = first + (int)lane * A.ctas; tx < P.tilesX; tx += 32 * A.ctas)
+					{
+						if (ld_sys(act + tx) == MTD_INF)
+							continue;
+						const uint32_t bk = atomicExch(act + tx, MTD_INF);
+						if (bk == MTD_INF)
+							continue;
+						atomicAdd(A.ctl + ACTL_OUTSTANDING, 1u);
+						__threadfence();
+						atomicAdd(A.ctl + ACTL_RECV, 1u);
+						__threadfence_system(); // the neighbour stored its row before the key: what a worker stages from here on includes it
+						if (!async_offer(P, A, 0, tx, ty, bk))
+							atomicSub(A.ctl + ACTL_OUTSTANDING, 1u);
+					}
+				}
+				__syncwarp();
+			}
 			uint32_t mymin = MTD_INF;
 			for (uint32_t i = lane; i < pn; i += 32)
 			{
@@ -769,6 +912,83 @@ namespace mtd
 			if (lane == 0)
 				__stcg(A.ctamin + me, cmin);
 			const uint32_t wm = min(cmin, warp_redux_min(others));
+			if (peer && me == 0)
+			{
+				const uint32_t rank_min = min(cmin, warp_redux_min(others_local));
+				if (lane == 0)
+				{
+					// this rank's wavefront position, for the priority windows of the others
+					if (rank_min != wm_sent)
+					{
+						for (int j = 0; j < P.world; j++)
+							if (j != P.rank)
+								st_sys(P.peers[j] + PEER_AWM + P.rank, rank_min);
+						wm_sent = rank_min;
+					}
+					// ---- termination (no rounds, no global count): rank 0 collects waves of snapshots. A snapshot of a rank =
+					// (nothing outstanding?, border offers made, border offers consumed), read in the order consumed ->
+					// outstanding -> made with fences in between, which errs towards "not finished" (see the worker and the
+					// take-over above). Two CONSECUTIVE waves -- the second requested after the first was complete -- with
+					// identical snapshots, every rank idle and made == consumed in total, describe one instant at which nothing
+					// was pending, in flight or on its way between ranks: the counters only grow, so a rank whose snapshot did
+					// not change was idle the whole time between its two snapshots, and all these intervals contain the moment
+					// the second wave was requested.
+					const uint32_t req = ld_sys(P.ctl + PEER_AREQ);
+					if (req != replied)
+					{
+						const uint32_t rcv = __ldcg(A.ctl + ACTL_RECV);
+						__threadfence();
+						const uint32_t out = __ldcg(A.ctl + ACTL_OUTSTANDING);
+						__threadfence();
+						const uint32_t snt = __ldcg(A.ctl + ACTL_SENT);
+						const unsigned long long word = ((unsigned long long)(req & 0xFFu) << 56) | ((unsigned long long)(out == 0u ? 1u : 0u) << 55) | ((unsigned long long)(snt & 0x7FFFFFFu) << 28) | (unsigned long long)(rcv & 0xFFFFFFFu);
+						st_sys64(reinterpret_cast<unsigned long long *>(P.peers[0] + PEER_AREPLY) + P.rank, word);
+						replied = req;
+					}
+					if (P.rank == 0 && !stopped)
+					{
+						if (ld_sys(P.ctl + PEER_AREQ) != wave)
+						{
+							for (int j = 0; j < P.world; j++)
+								st_sys(P.peers[j] + PEER_AREQ, wave);
+						}
+						else
+						{
+							bool complete = true, quiet = true, same = have_prev;
+							uint32_t ssum = 0, rsum = 0;
+							unsigned long long cur[PEER_MAX_WORLD];
+							for (int j = 0; j < P.world; j++)
+							{
+								const unsigned long long w = ld_sys64(reinterpret_cast<const unsigned long long *>(P.ctl + PEER_AREPLY) + j);
+								cur[j] = w & 0x00FFFFFFFFFFFFFFull;
+								complete = complete && (uint32_t)(w >> 56) == (wave & 0xFFu);
+								quiet = quiet && ((w >> 55) & 1ull);
+								ssum += (uint32_t)(w >> 28) & 0x7FFFFFFu;
+								rsum += (uint32_t)w & 0xFFFFFFFu;
+								same = same && cur[j] == prev_reply[j];
+							}
+							if (complete)
+							{
+								quiet = quiet && ((ssum - rsum) & 0x7FFFFFFu) == 0u;
+								if (quiet && same)
+								{
+									for (int j = 0; j < P.world; j++)
+										st_sys(P.peers[j] + PEER_ASTOP, 1u);
+								}
+								for (int j = 0; j < P.world; j++)
+									prev_reply[j] = cur[j];
+								have_prev = quiet;
+								wave++;
+								if ((wave & 0xFFu) == 0u)
+									wave++; // tag 0 is "no reply yet"
+							}
+						}
+					}
+					if (ld_sys(P.ctl + PEER_ASTOP) != 0u)
+						atomicExch(A.ctl + ACTL_STOP, 1u);
+				}
+				__syncwarp();
+			}
 			const uint32_t kthr = wm > MTD_INF - P.tile_delta ? MTD_INF : wm + P.tile_delta;
 			// workers that can take an item: first the ones with nothing to do, then the ones that have no NEXT item yet
 			uint32_t idle_w = 0, half_w = 0;
@@ -882,7 +1102,7 @@ namespace mtd
 				atomicAdd(&g_async_timing[13], (unsigned long long)(pn + nasg));
 			}
 #endif
-			if (aborted || outstanding == 0u)
+			if (aborted || (peer ? stopped != 0u : outstanding == 0u))
 				stop = true;
 			else if (global_timer_ns() - t0 > A.time_limit_ns)
 			{

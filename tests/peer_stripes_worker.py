@@ -36,9 +36,14 @@ def main():
         ya, yb = shard.stripe_halo_rows(y0, y1, H)
         st = striped.GpuStripe(local, W, H, y0, y1, elev.reshape(H, W)[ya:yb], flags.reshape(H, W)[ya:yb], srcs)
         striped.connect_peers(st, rank, world)
-        for rep in range(2):  # the second run reuses the peer blocks (barrier epochs carry on)
+        for rep in range(4):  # reps 0, 1: dataflow kernel (the default), 2, 3: round-based kernel; later runs reuse the peer blocks
+            st.ctx.debug_set(st.ctx.DEBUG_BIG_ASYNC, 1 if rep < 2 else 0)
             tiles, d, rounds = striped.solve_peer(st)
-            to, do = oracle.directions_update(W, H, elev, flags, srcs)
+            if st.ctx.big_stats()["dataflow"] != (rep < 2):
+                print(f"rank {rank} case {ci} rep {rep}: wrong kernel ran", flush=True)
+                bad += 1
+            if rep == 0:
+                to, do = oracle.directions_update(W, H, elev, flags, srcs)
             mine_d = d.cpu().numpy().view(np.uint32).reshape(-1)
             mine_t = tiles.cpu().numpy().view(np.uint32).reshape(-1)
             ok = np.array_equal(mine_d, do[y0 * W:y1 * W]) and np.array_equal(mine_t, to[y0 * W:y1 * W])

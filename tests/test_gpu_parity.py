@@ -704,7 +704,9 @@ def _overlap_probe():
     w0, h0 = 64, 64
     e0, f0 = synth.random_grid(w0, h0, seed_k=1, wall_pct=10)
     warm = striped.GpuStripe(0, w0, h0, 0, h0, e0, f0, synth.pick_open_tiles(f0, 1, 1))
-    striped.solve_peer_local([warm])
+    for dataflow in (1, 0):  # both relaxation kernels of the peer-coupled mode
+        warm.ctx.debug_set(warm.ctx.DEBUG_BIG_ASYNC, dataflow)
+        striped.solve_peer_local([warm])
     warm.close()
     W, H = 64, 128
     e, f = synth.random_grid(W, H, seed_k=2, wall_pct=10)
@@ -725,9 +727,17 @@ def _overlap_probe():
     return _OVERLAP[0]
 
 
-def _peer_striped_on_one_gpu(W, H, cuts, elev, flags, srcs, repeat=1):
-    """stripes as contexts of this process whose kernels run side by side on the one GPU (64 CTAs each) and write into
-    each other's peer blocks. Skipped only if the overlap probe says the box serialises the kernels."""
+@pytest.fixture(params=["dataflow", "rounds"])
+def peer_kernel(request):
+    """the two relaxation kernels of the peer-coupled stripes: k_tile_async (default: border offers and termination waves go
+    rank to rank, no rounds) and k_tile_rounds (device-side round barriers)"""
+    return request.param
+
+
+def _peer_striped_on_one_gpu(W, H, cuts, elev, flags, srcs, repeat=1, kernel="dataflow"):
+    """stripes as contexts of this process whose kernels run side by side on the one GPU and write into each other's peer
+    blocks. Skipped only if the overlap probe says the box serialises the kernels. Returns rounds = None for the dataflow
+    kernel (after checking that it really ran)."""
     from mazetd_b200 import shard, striped
 
     if not _overlap_probe():
@@ -736,11 +746,16 @@ def _peer_striped_on_one_gpu(W, H, cuts, elev, flags, srcs, repeat=1):
     for y0, y1 in zip(cuts[:-1], cuts[1:]):
         ya, yb = shard.stripe_halo_rows(y0, y1, H)
         stripes.append(striped.GpuStripe(0, W, H, y0, y1, elev.reshape(H, W)[ya:yb], flags.reshape(H, W)[ya:yb], srcs))
+        stripes[-1].ctx.debug_set(capi.Context.DEBUG_BIG_ASYNC, 1 if kernel == "dataflow" else 0)
     try:
         for _ in range(repeat):
             results, rounds = striped.solve_peer_local(stripes, ctas=64)
     except capi.MtdError:
         raise  # the probe showed that the kernels overlap: a barrier timeout here is a failure of the protocol, not a skip
+    ran_dataflow = [s.ctx.big_stats()["dataflow"] for s in stripes]
+    assert all(ran_dataflow) if kernel == "dataflow" else not any(ran_dataflow)
+    if kernel == "dataflow":
+        rounds = None
     tiles = np.concatenate([t.cpu().numpy().view(np.uint32).reshape(-1) for t, _ in results])
     d = np.concatenate([x.cpu().numpy().view(np.uint32).reshape(-1) for _, x in results])
     for s in stripes:
@@ -755,21 +770,21 @@ def _peer_striped_on_one_gpu(W, H, cuts, elev, flags, srcs, repeat=1):
     (256, 256, [0, 1, 255, 256], 2, 20),     # one-row stripes at both ends
     (1024, 1024, [0, 256, 512, 768, 1024], 16, 30),
 ])
-def test_peer_coupled_stripes_side_by_side_on_one_gpu(oracle, W, H, cuts, nsrc, pct):
+def test_peer_coupled_stripes_side_by_side_on_one_gpu(oracle, peer_kernel, W, H, cuts, nsrc, pct):
     elev, flags = synth.random_grid(W, H, seed_k=W + len(cuts), wall_pct=pct)
     srcs = synth.pick_open_tiles(flags, nsrc, 2)
-    tiles, d, rounds = _peer_striped_on_one_gpu(W, H, cuts, elev, flags, srcs, repeat=2)  # the second run reuses the peer blocks
+    tiles, d, rounds = _peer_striped_on_one_gpu(W, H, cuts, elev, flags, srcs, repeat=2, kernel=peer_kernel)  # the second run reuses the peer blocks
     to, do = oracle.directions_update(W, H, elev, flags, srcs)
     assert np.array_equal(d, do), diff_report(d, do, W)
     assert np.array_equal(tiles, to), diff_report(tiles, to, W)
-    assert rounds >= 1
+    assert rounds is None or rounds >= 1
 
 
-def test_peer_coupled_stripes_maze_and_sources_on_cut_rows(oracle):
+def test_peer_coupled_stripes_maze_and_sources_on_cut_rows(oracle, peer_kernel):
     W, H = 320, 256
     elev, flags = synth.maze_grid(W, H, seed_k=4)
     srcs = synth.pick_open_tiles(flags, 1, 1)
-    tiles, d, _ = _peer_striped_on_one_gpu(W, H, [0, 64, 128, 192, 256], elev, flags, srcs)
+    tiles, d, _ = _peer_striped_on_one_gpu(W, H, [0, 64, 128, 192, 256], elev, flags, srcs, kernel=peer_kernel)
     to, do = oracle.directions_update(W, H, elev, flags, srcs)
     assert np.array_equal(d, do), diff_report(d, do, W)
     assert np.array_equal(tiles, to), diff_report(tiles, to, W)
@@ -779,13 +794,13 @@ def test_peer_coupled_stripes_maze_and_sources_on_cut_rows(oracle):
     srcs = np.array([63 * W + 10, 64 * W + 100, 127 * W + 191, 128 * W + 0], np.uint32)
     flags[srcs] &= ~np.uint16(synth.FLAG_BUILDING | 1)
     flags[srcs[1]] |= synth.FLAG_BUILDING  # a blocked source still expands (paths.cpp:63-67)
-    tiles, d, _ = _peer_striped_on_one_gpu(W, H, [0, 64, 128, 192], elev, flags, srcs)
+    tiles, d, _ = _peer_striped_on_one_gpu(W, H, [0, 64, 128, 192], elev, flags, srcs, kernel=peer_kernel)
     to, do = oracle.directions_update(W, H, elev, flags, srcs)
     assert np.array_equal(d, do), diff_report(d, do, W)
     assert np.array_equal(tiles, to), diff_report(tiles, to, W)
 
 
-def test_peer_coupled_protocol_with_a_single_rank(oracle):
+def test_peer_coupled_protocol_with_a_single_rank(oracle, peer_kernel):
     """world size 1: no neighbour to write to, but the update still runs through the peer-coupled round protocol (barrier
     epochs, totals in the rank's own block, termination on the global queue length), twice on the same peer block"""
     from mazetd_b200 import striped
@@ -794,6 +809,7 @@ def test_peer_coupled_protocol_with_a_single_rank(oracle):
     elev, flags = synth.random_grid(W, H, seed_k=12, wall_pct=30)
     srcs = synth.pick_open_tiles(flags, 3, 5)
     st = striped.GpuStripe(0, W, H, 0, H, elev, flags, srcs)
+    st.ctx.debug_set(st.ctx.DEBUG_BIG_ASYNC, 1 if peer_kernel == "dataflow" else 0)
     st.ctx.stripe_peer_connect(0, 1, [st.ctx.stripe_peer_export()])
     to, do = oracle.directions_update(W, H, elev, flags, srcs)
     for _ in range(2):
@@ -802,7 +818,8 @@ def test_peer_coupled_protocol_with_a_single_rank(oracle):
         tiles = tiles.cpu().numpy().view(np.uint32).reshape(-1)
         assert np.array_equal(d, do), diff_report(d, do, W)
         assert np.array_equal(tiles, to), diff_report(tiles, to, W)
-        assert rounds >= 1
+        assert st.ctx.big_stats()["dataflow"] == (peer_kernel == "dataflow")
+        assert rounds >= 1 or peer_kernel == "dataflow"
     st.close()
 
 
