@@ -508,7 +508,10 @@ def leg_c4(ctx, dev, stream, rank, world, args):
             tot_d = sum(int(p[0].item()) for p in parts) & 0xFFFFFFFFFFFFFFFF
             tot_t = sum(int(p[1].item()) for p in parts) & 0xFFFFFFFFFFFFFFFF
             # per-rank sums were masked to 63 bits: compare modulo 2^63
-            ok = (tot_d & 0x7FFFFFFFFFFFFFFF) == (int(g["C4_dist_sum"]) & 0x7FFFFFFFFFFFFFFF) and (tot_t & 0x7FFFFFFFFFFFFFFF) == (int(g["C4_tiles_sum"]) & 0x7FFFFFFFFFFFFFFF)
+            ok_d = (tot_d & 0x7FFFFFFFFFFFFFFF) == (int(g["C4_dist_sum"]) & 0x7FFFFFFFFFFFFFFF)
+            ok_t = (tot_t & 0x7FFFFFFFFFFFFFFF) == (int(g["C4_tiles_sum"]) & 0x7FFFFFFFFFFFFFFF)
+            ok = ok_d and ok_t
+            out["parity_detail"] = {"distances": bool(ok_d), "next_hops": bool(ok_t)}
             out["parity"] = "golden-ok" if ok else "GOLDEN-MISMATCH"
             out["peer_parity"] = "PEER-OK" if ok else "PEER-MISMATCH"
         st.close()

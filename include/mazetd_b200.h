@@ -148,11 +148,14 @@ int mtd_stripe_finalize_dev(mtd_ctx *ctx, uint32_t *d_tiles);
 int mtd_stripe_round_budget(mtd_ctx *ctx, int32_t rounds);
 int mtd_stripe_pending(mtd_ctx *ctx, uint32_t *items_out);
 
-/* Peer-coupled stripes: the same Directions::update (paths.cpp:24-78) with the ranks advancing round by round inside ONE
- * kernel run per rank instead of through host-driven sweeps. A border tile stores its boundary row straight into the
- * neighbour rank's halo copy over NVLink and posts the offered key there; between rounds every rank stores a phase tag,
- * its queue length and its smallest key into its slot of EVERY rank's block and waits on its own block for the others,
- * so all ranks follow the same wavefront position and stop in the same round.
+/* Peer-coupled stripes: the same Directions::update (paths.cpp:24-78) as ONE kernel run per rank instead of host-driven
+ * sweeps. A border tile stores its boundary row straight into the neighbour rank's halo copy over NVLink and posts the
+ * offered key there. Two relaxation kernels (MTD_DEBUG_BIG_ASYNC, same result):
+ *   dataflow (default)  no rounds: the neighbour's owner CTA takes the posted key over as a local offer; rank 0 collects
+ *                       waves of (idle?, border offers made, border offers consumed) snapshots from all ranks and ends the run
+ *                       after two identical quiet waves; every rank publishes its wavefront position for a global priority window
+ *   rounds              between rounds every rank stores a phase tag, its queue length and its smallest key into its slot of
+ *                       EVERY rank's block and waits on its own block for the others, so all ranks stop in the same round
  *   export         creates this rank's peer block (after mtd_stripe_upload*) and returns its CUDA IPC handle (64 bytes)
  *   connect        maps the blocks of all other ranks from `handles` ([world][64], gathered by the caller; world <= 16)
  *   launch_dev     queues initialisation, the relaxation kernel and the next-hop pass on the context's stream and returns;

@@ -664,16 +664,20 @@ namespace mtd
 					const int Hl = P.y1 - P.y0;
 					const int brow = min(TS + 1, Hl - (ty * TS - 1));
 					const int gx = tx * TS + (int)lane;
-					const bool up = ty == 0 && P.peer_up_act && k[0] != MTD_INF, down = ty == P.tilesY - 1 && P.peer_down_act && k[1] != MTD_INF;
-					if (up && gx < P.W)
+					// The row goes out after EVERY visit of a border tile, offer or not: the neighbour's next-hop pass breaks ties
+					// between optimal predecessors on both sides of the cut by (label, tile), so its copy must end up exact even
+					// where my label only equals what it already has (found at 8 ranks: profiles/r03i_*).
+					const bool up_row = ty == 0 && P.peer_up_act, down_row = ty == P.tilesY - 1 && P.peer_down_act;
+					const bool up = up_row && k[0] != MTD_INF, down = down_row && k[1] != MTD_INF;
+					if (up_row && gx < P.W)
 						P.peer_up_halo[gx] = S.d[1 * WT::PITCH + 4 + (int)lane];
-					if (down && gx < P.W)
+					if (down_row && gx < P.W)
 						P.peer_down_halo[gx] = S.d[(brow - 1) * WT::PITCH + 4 + (int)lane];
-					if (up || down)
+					if (up_row || down_row)
 					{
-						__threadfence_system(); // every lane: its part of the row is ordered before the offer
+						__threadfence_system(); // every lane: its part of the row has landed before the offer, and before this rank can count as idle
 						__syncwarp();
-						if (lane == 0)
+						if (lane == 0 && (up || down))
 						{
 							uint32_t made = 0;
 							if (up && atomicMin_system(P.peer_up_act + tx, k[0]) == MTD_INF)

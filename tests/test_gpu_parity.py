@@ -800,6 +800,21 @@ def test_peer_coupled_stripes_maze_and_sources_on_cut_rows(oracle, peer_kernel):
     assert np.array_equal(tiles, to), diff_report(tiles, to, W)
 
 
+def test_peer_coupled_stripes_ties_across_the_cuts(oracle, peer_kernel):
+    """flat terrain: every edge weighs 255, so most tiles have several optimal predecessors and the next hop is decided by
+    the tie-break (smallest label, then smallest tile id: paths.cpp:16-17, 69) -- across a cut that needs the neighbour's
+    boundary row to be exact even where it never improved anything on this side (found at 8 ranks, profiles/r03i_*)"""
+    W, H = 256, 256
+    _, flags = synth.random_grid(W, H, seed_k=31, wall_pct=15)
+    elev = np.zeros(W * H, np.int16)
+    srcs = synth.pick_open_tiles(flags, 3, 7)
+    to, do = oracle.directions_update(W, H, elev, flags, srcs)
+    for cuts in ([0, 64, 128, 192, 256], [0, 100, 256]):
+        tiles, d, _ = _peer_striped_on_one_gpu(W, H, cuts, elev, flags, srcs, kernel=peer_kernel)
+        assert np.array_equal(d, do), diff_report(d, do, W)
+        assert np.array_equal(tiles, to), diff_report(tiles, to, W)
+
+
 def test_peer_coupled_protocol_with_a_single_rank(oracle, peer_kernel):
     """world size 1: no neighbour to write to, but the update still runs through the peer-coupled round protocol (barrier
     epochs, totals in the rank's own block, termination on the global queue length), twice on the same peer block"""

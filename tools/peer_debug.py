@@ -23,8 +23,12 @@ for y0, y1 in zip(cuts[:-1], cuts[1:]):
 for rep in range(3):
     results, rounds = striped.solve_peer_local(stripes, ctas=64)
     d = np.concatenate([x.cpu().numpy().view(np.uint32).reshape(-1) for _, x in results])
+    t = np.concatenate([x.cpu().numpy().view(np.uint32).reshape(-1) for x, _ in results])
+    badt = np.nonzero(t != to)[0]
+    if len(badt):
+        print("rep", rep, "NEXT-HOP mismatches", len(badt), "rows", sorted(set((badt // W).tolist()))[:20])
     bad = np.nonzero(d != do)[0]
-    print("rep", rep, "mismatches", len(bad), "visits", [s.ctx.big_stats() for s in stripes])
+    print("rep", rep, "mismatches", len(bad), "next-hop mismatches", len(badt), "visits", [s.ctx.big_stats() for s in stripes])
     if len(bad):
         ys, xs = bad // W, bad % W
         print("  y range", ys.min(), ys.max(), "x range", xs.min(), xs.max(), "got INF:", int((d[bad] == 0xFFFFFFFF).sum()), "got smaller:", int((d[bad] < do[bad]).sum()), "got larger finite:", int(((d[bad] > do[bad]) & (d[bad] != 0xFFFFFFFF)).sum()))
