@@ -86,6 +86,7 @@ enum
 	MTD_DEBUG_FUSED_MAPGEN = 11, /* mtd_mapgen_batch with waypoints: 1 (default) = the generator runs inside the waypoints kernel (the next map's elevations are computed while the current map is relaxed), 0 = generator kernel, then waypoints kernel. Same result */
 	MTD_DEBUG_GEN_WARPS = 12,  /* fused generator: how many of the warps without a layer compute the next map's elevations during the relaxation (0 = all warps, after it). Performance only */
 	MTD_DEBUG_ASYNC_WORKERS = 13, /* dataflow scheduler: worker warps per SM that are handed items (1..16). Performance only */
+	MTD_DEBUG_ASYNC_LATE_LOOKS = 14, /* dataflow scheduler: how often a visit re-reads its apron from global memory after converging and goes on if a neighbour lowered it meanwhile (0..4, default 1). Performance only */
 	MTD_DEBUG_BIG_TMA = 7,     /* dataflow scheduler: 1 (default) = tile frames staged by 2-D bulk tensor copies (TMA), 0 = cp.async rows. Same result */
 	MTD_DEBUG_ASYNC_DELTA = 6, /* priority window (label units) of the dataflow scheduler. Performance only */
 	MTD_DEBUG_TILE_DELTA = 4   /* large grids: width (label units) of the window of tile offers visited per round; 2^32-1 = visit everything (no priority). Performance only: any value gives the same result */

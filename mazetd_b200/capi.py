@@ -164,6 +164,7 @@ class Context:
     DEBUG_FUSED_MAPGEN = 11
     DEBUG_GEN_WARPS = 12
     DEBUG_ASYNC_WORKERS = 13
+    DEBUG_ASYNC_LATE_LOOKS = 14
     DEBUG_ASYNC_NB_RULE = 8
     DEBUG_ASYNC_DEPTH = 9
 

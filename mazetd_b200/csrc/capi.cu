@@ -131,6 +131,7 @@ struct mtd_ctx
 	DevBuf<unsigned long long> a_inbox;
 	DevBuf<uint32_t> a_tail, a_ctamin, a_ctl, a_fly;
 	int async_workers = ASYNC_WORKERS; // worker warps per SM in use
+	int async_late_looks = 1;          // a visit re-reads its apron once after converging
 	int async_nb_rule = 0, async_depth = 2; // measured (profiles/r02g_*): the neighbour rule halves the visits but not the time; two mailboxes: 14.5 -> 13.0 ms on C4
 	uint32_t async_nb_margin = 0; // dataflow scheduler of k_tile_async: inbox rings, ring tails, per-CTA smallest keys, control words
 	bool big_async = true;         // large grids: k_tile_async (no global rounds); false = k_tile_rounds (A/B and multi-stripe contexts)
@@ -668,6 +669,7 @@ namespace
 		A.nb_margin = ctx->async_nb_margin;
 		A.depth = ctx->async_depth;
 		A.workers = ctx->async_workers;
+		A.late_looks = ctx->async_late_looks;
 		A.time_limit_ns = peer ? 8000000000ull : 20000000000ull; // an update that takes this long is reported, not waited for
 		P.tile_delta = ctx->async_delta;
 		// frames staged by TMA: one tensor map over the labels of all layers, one over the packed weights
@@ -1300,6 +1302,9 @@ extern "C" int mtd_debug_set(mtd_ctx *ctx, int key, int64_t value)
 	case MTD_DEBUG_ASYNC_NB_RULE:
 		ctx->async_nb_rule = value >= 0 ? 1 : 0; // value = margin (label units); negative = rule off
 		ctx->async_nb_margin = value >= 0 ? (uint32_t)value : 0u;
+		return MTD_OK;
+	case MTD_DEBUG_ASYNC_LATE_LOOKS:
+		ctx->async_late_looks = value < 0 ? 0 : value > 4 ? 4 : (int)value;
 		return MTD_OK;
 	case MTD_DEBUG_ASYNC_WORKERS:
 		ctx->async_workers = value < 1 ? 1 : value > ASYNC_WORKERS ? ASYNC_WORKERS : (int)value;

@@ -132,6 +132,7 @@ namespace mtd
 		uint32_t nb_margin;  // ... smaller by more than this
 		int depth;           // mailboxes per worker in use: 1 or 2
 		int workers;         // worker warps the scheduler hands items to (<= ASYNC_WORKERS; the rest sleep)
+		int late_looks;      // how often a visit re-reads its apron from global memory after converging (0 = never)
 		unsigned long long time_limit_ns;
 	};
 
@@ -189,7 +190,7 @@ namespace mtd
 	// Returns in k[4] (warp-uniform) the smallest label on offer to the tile above / below / left / right (MTD_INF: none).
 	// Same arithmetic as the visit inside k_tile_rounds; `guard` is raised when a label gets close to the uint32 wrap.
 	template<int TS, class WT>
-	__device__ __forceinline__ void warp_visit(const BigParams &P, WT &S, int layer, int tx, int ty, uint32_t lane, uint32_t lt, uint32_t (&k)[4], bool &guard, const CUtensorMap *tm_dist, const CUtensorMap *tm_w, uint32_t &tma_phase, uint32_t next_item MTD_ATIMING_ARGS)
+	__device__ __forceinline__ void warp_visit(const BigParams &P, WT &S, int layer, int tx, int ty, uint32_t lane, uint32_t lt, uint32_t (&k)[4], bool &guard, const CUtensorMap *tm_dist, const CUtensorMap *tm_w, uint32_t &tma_phase, uint32_t next_item, int late_looks MTD_ATIMING_ARGS)
 	{
 		constexpr int RW = WT::RW, PITCH = WT::PITCH, QCAP = WT::QCAP;
 		const int W = P.W;
@@ -428,7 +429,10 @@ namespace mtd
 		// per-lane output count instead of five ballots, and the threshold advances by one bucket per step (jumping ahead
 		// only when a step settled nothing) instead of tracking the exact minimum.
 		const uint32_t spare = (lane + 1u) * (uint32_t)PITCH + ((lane >> 2) % 6u < 3u ? (lane >> 2) % 6u : 34u + (lane >> 2) % 6u); // words 0..2 / 37..39 of frame row lane + 1
-		uint32_t nq = tail, par = 0;
+		uint32_t par = 0;
+		for (int look = 0;; look++)
+		{
+		uint32_t nq = tail;
 		bool overflow = false;
 		uint32_t thr = dmin == MTD_INF ? MTD_INF : dmin + BIG_DELTA;
 		while (nq != 0u)
@@ -535,6 +539,82 @@ namespace mtd
 			}
 		}
 		__syncwarp();
+		if (look >= late_looks)
+			break;
+		// ---- a late look at the apron ----
+		// Offers from several neighbours reach a tile within one visit time (the wavefront passes); whatever arrived while
+		// this visit was running would otherwise wait for it to end and cost a second full visit -- on the chain of dependent
+		// visits that bounds the update that is a wait plus a visit per tile hop. The neighbours write
+		// their interiors back before they offer, so their border cells are re-read from global memory here (one L2 round
+		// trip), and cells that dropped below what this visit was seeded with seed the engine once more. The pending item
+		// such an offer created is still visited later (the accounting stays as it is) and finds nothing to do.
+		{
+			wq = S.q[par];
+			tail = 0;
+			my_min = MTD_INF;
+			const int i = (int)lane;
+			const int gxi = gx0 + 1 + i, lyi = ly0 + 1 + i;
+			uint32_t an[4] = { 0u, 0u, 0u, 0u };
+			if (gxi < W)
+			{
+				if (ly0 >= 0)
+					an[0] = __ldcg(ldist + (size_t)ly0 * W + gxi);
+				else if (ly0 == -1 && P.up_row)
+					an[0] = __ldcg(P.up_row + gxi);
+				const int lyb = ly0 + brow;
+				if (lyb < Hl)
+					an[1] = __ldcg(ldist + (size_t)lyb * W + gxi);
+				else if (lyb == Hl && P.down_row)
+					an[1] = __ldcg(P.down_row + gxi);
+			}
+			if (1 + i < brow)
+			{
+				if (gx0 >= 0)
+					an[2] = __ldcg(ldist + (size_t)lyi * W + gx0);
+				if (gx0 + TS + 1 < W)
+					an[3] = __ldcg(ldist + (size_t)lyi * W + gx0 + TS + 1);
+			}
+#pragma unroll
+			for (int side = 0; side < 4; side++)
+			{
+				uint32_t a, v, wsel;
+				if (side == 0)
+				{
+					a = (uint32_t)(0 * PITCH + 4 + i);
+					v = a + PITCH;
+					wsel = S.w[a] >> 16;
+				}
+				else if (side == 1)
+				{
+					a = (uint32_t)(brow * PITCH + 4 + i);
+					v = a - PITCH;
+					wsel = S.w[v] >> 16;
+				}
+				else if (side == 2)
+				{
+					a = (uint32_t)((1 + i) * PITCH + 3);
+					v = a + 1u;
+					wsel = S.w[a] & 0xFFFFu;
+				}
+				else
+				{
+					a = (uint32_t)((1 + i) * PITCH + 4 + TS);
+					v = a - 1u;
+					wsel = S.w[v] & 0xFFFFu;
+				}
+				const uint32_t da = an[side];
+				const bool row_exists = side < 2 || 1 + i < brow;
+				const bool lower = row_exists && da != 0u && da != MTD_INF && da < ap_old[side]; // a parked cell (0) stays parked: blocked tiles never change
+				relax_into(lower, v, da + MIN_EDGE + wsel);
+				if (lower)
+					ap_old[side] = da;
+			}
+			dmin = warp_redux_min(my_min);
+			__syncwarp();
+			if (tail == 0u)
+				break;
+		}
+		}
 
 		MTD_ATICK(4);
 		// ---- write back the interior ----
@@ -653,7 +733,7 @@ namespace mtd
 				const int tx = (int)(tile % (uint32_t)P.tilesX), ty = (int)(tile / (uint32_t)P.tilesX);
 				MTD_ATICK(1);
 				uint32_t k[4];
-				warp_visit<TS>(P, S, layer, tx, ty, lane, lt, k, guard, A.use_tma ? &tm_dist : nullptr, A.use_tma ? &tm_w : nullptr, tma_phase, slot[mine ^ 1] MTD_ATIMING_PASS);
+				warp_visit<TS>(P, S, layer, tx, ty, lane, lt, k, guard, A.use_tma ? &tm_dist : nullptr, A.use_tma ? &tm_w : nullptr, tma_phase, slot[mine ^ 1], A.late_looks MTD_ATIMING_PASS);
 				if (P.ctl0)
 				{
 					// row stripes: the tile above / below a border tile belongs to a neighbour rank. Its copy of my boundary row is
