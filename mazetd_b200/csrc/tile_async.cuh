@@ -430,7 +430,7 @@ namespace mtd
 		// only when a step settled nothing) instead of tracking the exact minimum.
 		const uint32_t spare = (lane + 1u) * (uint32_t)PITCH + ((lane >> 2) % 6u < 3u ? (lane >> 2) % 6u : 34u + (lane >> 2) % 6u); // words 0..2 / 37..39 of frame row lane + 1
 		uint32_t par = 0;
-		for (int look = 0;; look++)
+		auto engine = [&]()
 		{
 		uint32_t nq = tail;
 		bool overflow = false;
@@ -539,8 +539,8 @@ namespace mtd
 			}
 		}
 		__syncwarp();
-		if (look >= late_looks)
-			break;
+		};
+		engine();
 		// ---- a late look at the apron ----
 		// Offers from several neighbours reach a tile within one visit time (the wavefront passes); whatever arrived while
 		// this visit was running would otherwise wait for it to end and cost a second full visit -- on the chain of dependent
@@ -548,6 +548,7 @@ namespace mtd
 		// their interiors back before they offer, so their border cells are re-read from global memory here (one L2 round
 		// trip), and cells that dropped below what this visit was seeded with seed the engine once more. The pending item
 		// such an offer created is still visited later (the accounting stays as it is) and finds nothing to do.
+		for (int look = 0; look < late_looks; look++)
 		{
 			wq = S.q[par];
 			tail = 0;
@@ -613,7 +614,7 @@ namespace mtd
 			__syncwarp();
 			if (tail == 0u)
 				break;
-		}
+			engine();
 		}
 
 		MTD_ATICK(4);

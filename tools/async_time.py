@@ -25,7 +25,10 @@ ctx.debug_set(ctx.DEBUG_ASYNC_NB_RULE, nb)
 ctx.debug_set(ctx.DEBUG_ASYNC_DEPTH, depth)
 ctx.debug_set(ctx.DEBUG_ASYNC_WORKERS, int(os.environ.get('MTD_WORKERS', '16')))
 looks = int(os.environ.get('MTD_LOOKS', '1'))
-ctx.debug_set(ctx.DEBUG_ASYNC_LATE_LOOKS, looks)
+try:
+    ctx.debug_set(ctx.DEBUG_ASYNC_LATE_LOOKS, looks)
+except Exception:
+    looks = -1  # a library built before the knob existed
 for delta in deltas:
     ctx.debug_set(ctx.DEBUG_ASYNC_DELTA, delta)
     for it in range(2):
