@@ -321,8 +321,14 @@ def _timed_reps(fn, reps, warm, stream, world, dev):
     return ms
 
 
-def _big_roofline(ctx, algo_bytes, update_ms, reps):
+def _big_roofline(ctx, algo_bytes, update_ms, reps, cfg=None):
     from mazetd_b200 import capi
+
+    traffic = None
+    try:  # DRAM bytes of the relaxation kernel from the committed ncu capture of this configuration (full size only)
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(f"k_tile_async_{cfg}_dram_bytes_per_launch") if cfg else None
+    except Exception:
+        pass
 
     peak, src = hbm_peak()
     relax_ms, relax_n = ctx.profile_read(capi.Context.K_BIG_RELAX)
@@ -332,7 +338,8 @@ def _big_roofline(ctx, algo_bytes, update_ms, reps):
     achieved = algo_bytes / (update_ms * 1e-3) / 1e9
     return {
         "bound": "hbm", "kernel": "k_tile_async" if st["dataflow"] else "k_tile_rounds", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-        "traffic": None, "peak_source": src, "algorithmic_bytes_per_update": algo_bytes,
+        "traffic": traffic if st["dataflow"] else None, "traffic_note": "relaxation kernel only, one launch (profiles/traffic.json)" if traffic and st["dataflow"] else None,
+        "peak_source": src, "algorithmic_bytes_per_update": algo_bytes,
         "note": "achieved = W*H*(4 + 8*layers) bytes of the WHOLE update / its device time (init + relaxation + next-hop pass), the conservative reading of SURVEY.md 8d",
         "kernel_avg_ms": relax_ms / max(relax_n, 1), "kernel_share_of_update": (relax_ms / max(relax_n, 1)) / update_ms if update_ms > 0 else None,
         "next_hop_pass_avg_ms": dir_ms / max(dir_n, 1), "init_avg_ms": prep_ms / max(reps, 1),
@@ -372,7 +379,7 @@ def leg_c5(ctx, dev, stream, rank, world, args):
         "workload": "C5: 8 waypoint layers (distance + direction) on one 4096x4096 grid, 30 % walls, weights 255..570", "grid": [Wb, Hb], "layers": L, "n_gpus": world,
         "partition": "layers round-robin over the ranks, grid replicated, no collective" if world > 1 else "one GPU",
         "ms": med, "ms_all": ms, "value": Wb * Hb * L / (med * 1e-3), "unit": "tile relaxations/s",
-        "roofline": _big_roofline(ctx, Wb * Hb * (4 * world + 8 * L), med, reps),
+        "roofline": _big_roofline(ctx, Wb * Hb * (4 * world + 8 * L), med, reps, "C5" if (Wb, L, world) == (4096, 8, 1) else None),
     }
     ctx.profile_enable(False)
     g = _golden_big()
@@ -451,7 +458,7 @@ def leg_c4(ctx, dev, stream, rank, world, args):
             ctx.profile_read(k)
         ms = _timed_reps(run, reps, 0, stream, world, dev)
         med = float(np.median(ms))
-        out.update(partition="one GPU", ms=med, ms_all=ms, value=Wb * Hb / (med * 1e-3), unit="tile relaxations/s", roofline=_big_roofline(ctx, Wb * Hb * 12, med, reps))
+        out.update(partition="one GPU", ms=med, ms_all=ms, value=Wb * Hb / (med * 1e-3), unit="tile relaxations/s", roofline=_big_roofline(ctx, Wb * Hb * 12, med, reps, "C4" if Wb == 16384 else None))
         ctx.profile_enable(False)
         if g is not None:
             out["parity"] = "golden-ok" if _sum64(dd) == int(g["C4_dist_sum"]) and _sum64(dt) == int(g["C4_tiles_sum"]) else "GOLDEN-MISMATCH"

@@ -331,15 +331,58 @@ namespace mtd
 	// The same pass, four tiles of one row per thread (W % 4 == 0, 16-byte aligned bases): the own row, the rows above and
 	// below and the two weight rows move as 16-byte vectors, so the kernel issues a quarter of the load instructions and
 	// streams at HBM speed instead of queueing in the load/store unit.
-	__global__ void k_big_finalize4(int W, int Hl, int y0, int H, uint32_t *__restrict__ dist_base, size_t layer_stride, const uint32_t *__restrict__ wpack, const uint8_t *__restrict__ blocked, const uint32_t *__restrict__ sources_base, int nsrc, const uint32_t *__restrict__ up_row, const uint32_t *__restrict__ up_wpack, const uint32_t *__restrict__ down_row, uint32_t *__restrict__ tiles_base, size_t tiles_stride)
+	// The next-hop pass of k_big_finalize for widths that are a multiple of 4, four tiles of a row per thread, with the labels and
+	// weights of a TW x TH block of cells (plus one row above / below and one quad left / right) staged in shared memory by
+	// 16-byte loads: every label is read from global memory once instead of three times (own row, as "down" of the row
+	// above, as "up" of the row below), the loads of a thread are independent of each other, and a quad with parked cells
+	// goes back as one 16-byte store. HBM-bound streaming: 4 B labels + 4 B weights +
+	// 1 B blocked in, 4 B next hops + (most quads) 4 B labels out per tile.
+	constexpr int FIN_TW = 256, FIN_TH = 16;
+	__global__ void __launch_bounds__(256) k_big_finalize_tiled(int W, int Hl, int y0, int H, uint32_t *__restrict__ dist_base, size_t layer_stride, const uint32_t *__restrict__ wpack, const uint8_t *__restrict__ blocked, const uint32_t *__restrict__ sources_base, int nsrc, const uint32_t *__restrict__ up_row, const uint32_t *__restrict__ up_wpack, const uint32_t *__restrict__ down_row, uint32_t *__restrict__ tiles_base, size_t tiles_stride, int ntx)
 	{
+		constexpr int QD = FIN_TW / 4 + 2, QW = FIN_TW / 4 + 1;
+		__shared__ uint4 sd[FIN_TH + 2][QD]; // labels: row r = local row ly0 - 1 + r, column c = the quad at x0 - 4 + 4 c
+		__shared__ uint4 sw[FIN_TH + 1][QW]; // packed weights: row r = local row ly0 - 1 + r, column c = the quad at x0 - 4 + 4 c
 		__shared__ uint32_t filter[64];
 		const int layer = blockIdx.y;
 		uint32_t *dist = dist_base + (size_t)layer * layer_stride;
 		uint32_t *tiles = tiles_base ? tiles_base + (size_t)layer * tiles_stride : nullptr;
 		const uint32_t *sources = sources_base + (size_t)layer * nsrc;
+		const int x0 = (int)(blockIdx.x % (unsigned)ntx) * FIN_TW, ly0 = (int)(blockIdx.x / (unsigned)ntx) * FIN_TH;
+		const uint4 inf4 = make_uint4(MTD_INF, MTD_INF, MTD_INF, MTD_INF);
+		const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
 		for (int i = threadIdx.x; i < 64; i += blockDim.x)
 			filter[i] = 0u;
+		for (int idx = threadIdx.x; idx < (FIN_TH + 2) * QD; idx += blockDim.x)
+		{
+			const int r = idx / QD, c = idx - r * QD;
+			const int ly = ly0 - 1 + r, x = x0 - 4 + 4 * c, gy = ly + y0;
+			uint4 v = inf4; // outside the grid: no predecessor there
+			if (x >= 0 && x < W && gy >= 0 && gy < H)
+			{
+				if (ly >= 0 && ly < Hl)
+					v = *reinterpret_cast<const uint4 *>(dist + (size_t)ly * W + x);
+				else if (ly == -1 && up_row)
+					v = *reinterpret_cast<const uint4 *>(up_row + x);
+				else if (ly == Hl && down_row)
+					v = *reinterpret_cast<const uint4 *>(down_row + x);
+			}
+			sd[r][c] = v;
+		}
+		for (int idx = threadIdx.x; idx < (FIN_TH + 1) * QW; idx += blockDim.x)
+		{
+			const int r = idx / QW, c = idx - r * QW;
+			const int ly = ly0 - 1 + r, x = x0 - 4 + 4 * c;
+			uint4 v = zero4;
+			if (x >= 0 && x < W && ly + y0 >= 0)
+			{
+				if (ly >= 0 && ly < Hl)
+					v = *reinterpret_cast<const uint4 *>(wpack + (size_t)ly * W + x);
+				else if (ly == -1 && up_row && up_wpack)
+					v = *reinterpret_cast<const uint4 *>(up_wpack + x);
+			}
+			sw[r][c] = v;
+		}
 		__syncthreads();
 		for (int s = threadIdx.x; s < nsrc; s += blockDim.x)
 		{
@@ -357,18 +400,15 @@ namespace mtd
 					return true;
 			return false;
 		};
-		const int QW = W >> 2;
-		const size_t total = (size_t)QW * Hl;
-		const uint4 inf4 = make_uint4(MTD_INF, MTD_INF, MTD_INF, MTD_INF);
-		const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
-		for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += (size_t)gridDim.x * blockDim.x)
+		for (int idx = threadIdx.x; idx < FIN_TH * (FIN_TW / 4); idx += blockDim.x)
 		{
-			const int x = (int)(q % (size_t)QW) << 2;
-			const int ly = (int)(q / (size_t)QW);
-			const int gy = ly + y0;
+			const int r = idx / (FIN_TW / 4), c = idx - r * (FIN_TW / 4);
+			const int ly = ly0 + r, x = x0 + 4 * c;
+			if (ly >= Hl || x >= W)
+				continue;
 			const size_t i = (size_t)ly * W + x;
-			const uint32_t g = (uint32_t)((size_t)gy * W + x);
-			const uint4 dq = *reinterpret_cast<const uint4 *>(dist + i);
+			const uint32_t g = (uint32_t)((size_t)(ly + y0) * W + x);
+			const uint4 dq = sd[r + 1][c + 1];
 			uint32_t dv[4] = { dq.x, dq.y, dq.z, dq.w };
 			uint32_t best[4] = { MTD_INF, MTD_INF, MTD_INF, MTD_INF };
 			bool any_zero = false, any_live = false;
@@ -378,48 +418,14 @@ namespace mtd
 				any_zero |= dv[j] == 0u;
 				any_live |= dv[j] != 0u && dv[j] != MTD_INF;
 			}
-			if (any_zero)
-			{
-				// source (keeps 0, no next hop: paths.cpp:49) or parked blocked tile (never relaxed: paths.cpp:65-67)
-				const uchar4 bq = *reinterpret_cast<const uchar4 *>(blocked + i);
-				const uint8_t b[4] = { bq.x, bq.y, bq.z, bq.w };
-#pragma unroll
-				for (int j = 0; j < 4; j++)
-					if (dv[j] == 0u && b[j] && !is_source(g + (uint32_t)j))
-						dist[i + j] = MTD_INF;
-			}
 			if (any_live && tiles)
 			{
-				uint4 du4 = inf4, dd4 = inf4, wu4 = zero4;
-				if (gy > 0)
-				{
-					if (ly > 0)
-					{
-						du4 = *reinterpret_cast<const uint4 *>(dist + i - W);
-						wu4 = *reinterpret_cast<const uint4 *>(wpack + i - W);
-					}
-					else if (up_row)
-					{
-						du4 = *reinterpret_cast<const uint4 *>(up_row + x);
-						if (up_wpack)
-							wu4 = *reinterpret_cast<const uint4 *>(up_wpack + x);
-					}
-				}
-				if (gy < H - 1)
-				{
-					if (ly < Hl - 1)
-						dd4 = *reinterpret_cast<const uint4 *>(dist + i + W);
-					else if (down_row)
-						dd4 = *reinterpret_cast<const uint4 *>(down_row + x);
-				}
-				const uint4 wq = *reinterpret_cast<const uint4 *>(wpack + i);
+				const uint4 du4 = sd[r][c + 1], dd4 = sd[r + 2][c + 1], wu4 = sw[r][c + 1], wq = sw[r + 1][c + 1];
 				const uint32_t wp[4] = { wq.x, wq.y, wq.z, wq.w };
 				const uint32_t du[4] = { du4.x, du4.y, du4.z, du4.w };
 				const uint32_t dd[4] = { dd4.x, dd4.y, dd4.z, dd4.w };
 				const uint32_t wu[4] = { wu4.x, wu4.y, wu4.z, wu4.w };
-				const uint32_t dleft = x > 0 ? dist[i - 1] : MTD_INF;
-				const uint32_t wleft = x > 0 ? wpack[i - 1] & 0xFFFFu : 0u;
-				const uint32_t dright = x + 4 < W ? dist[i + 4] : MTD_INF;
+				const uint32_t dleft = sd[r + 1][c].w, wleft = sw[r + 1][c].w & 0xFFFFu, dright = sd[r + 1][c + 2].x;
 #pragma unroll
 				for (int j = 0; j < 4; j++)
 				{
@@ -442,10 +448,28 @@ namespace mtd
 					cand(dd[j], wp[j] >> 16, g + (uint32_t)j + (uint32_t)W);
 				}
 			}
+			if (any_zero)
+			{
+				// source (keeps 0, no next hop: paths.cpp:49) or parked blocked tile (never relaxed: paths.cpp:65-67). Blocks
+				// that read these cells as neighbours meanwhile treat 0 (of a tile that is no source) and m alike.
+				const uchar4 bq = *reinterpret_cast<const uchar4 *>(blocked + i);
+				const uint8_t b[4] = { bq.x, bq.y, bq.z, bq.w };
+				bool changed = false;
+#pragma unroll
+				for (int j = 0; j < 4; j++)
+					if (dv[j] == 0u && b[j] && !is_source(g + (uint32_t)j))
+					{
+						dv[j] = MTD_INF;
+						changed = true;
+					}
+				if (changed)
+					*reinterpret_cast<uint4 *>(dist + i) = make_uint4(dv[0], dv[1], dv[2], dv[3]);
+			}
 			if (tiles)
 				__stcs(reinterpret_cast<uint4 *>(tiles + i), make_uint4(best[0], best[1], best[2], best[3]));
 		}
 	}
+
 }
 
 #include "tile_warp.cuh"

@@ -466,10 +466,17 @@ namespace
 		return per_sm;
 	}
 
-	// k_big_finalize4 moves rows as 16-byte vectors: the width and every base it touches must allow that
+	// k_big_finalize_tiled moves rows as 16-byte vectors: the width and every base it touches must allow that
 	bool finalize_vec_ok(mtd_ctx *ctx, const void *d_dist, const void *d_tiles)
 	{
 		return ctx->W % 4 == 0 && ctx->W >= 4 && (((uintptr_t)d_dist | (uintptr_t)d_tiles) & 15u) == 0;
+	}
+
+	// next-hop pass over rows [0, Hl) of `nlayers` layers, labels and weights staged through shared memory (needs finalize_vec_ok)
+	void launch_finalize_tiled(mtd_ctx *ctx, int W, int Hl, int y0, int H, uint32_t *d_dist, size_t stride, int nsrc, int nlayers, const uint32_t *up_row, const uint32_t *up_wpack, const uint32_t *down_row, uint32_t *d_tiles)
+	{
+		const int ntx = (W + FIN_TW - 1) / FIN_TW, nty = (Hl + FIN_TH - 1) / FIN_TH;
+		k_big_finalize_tiled<<<dim3((unsigned)(ntx * nty), (unsigned)nlayers), 256, 0, ctx->stream>>>(W, Hl, y0, H, d_dist, stride, ctx->wpack.p, ctx->blocked.p, ctx->sources.p, nsrc, up_row, up_wpack, down_row, d_tiles, stride, ntx);
 	}
 
 	// ---- small path launcher -------------------------------------------------------------------------
@@ -844,8 +851,7 @@ namespace
 			ProfScope prof(ctx, MTD_K_BIG_DIRECTIONS);
 			if (finalize_vec_ok(ctx, d_dist, d_tiles))
 			{
-				dim3 grid((unsigned)grid_blocks(ctx, ctx->T / 4, 256, nlayers > 4 ? 2 : 8), (unsigned)nlayers);
-				k_big_finalize4<<<grid, 256, 0, ctx->stream>>>(ctx->W, ctx->H, 0, ctx->H, d_dist, ctx->T, ctx->wpack.p, ctx->blocked.p, ctx->sources.p, nsrc, nullptr, nullptr, nullptr, d_tiles, ctx->T);
+				launch_finalize_tiled(ctx, ctx->W, ctx->H, 0, ctx->H, d_dist, ctx->T, nsrc, nlayers, nullptr, nullptr, nullptr, d_tiles);
 			}
 			else
 			{
@@ -1694,7 +1700,7 @@ extern "C" int mtd_stripe_finalize_dev(mtd_ctx *ctx, uint32_t *d_tiles)
 	{
 		ProfScope prof(ctx, MTD_K_BIG_DIRECTIONS);
 		if (finalize_vec_ok(ctx, ctx->stripe_dist, d_tiles))
-			k_big_finalize4<<<dim3((unsigned)grid_blocks(ctx, ctx->T / 4, 256, 8), 1u), 256, 0, ctx->stream>>>(ctx->W, ctx->H, ctx->sy0, ctx->sH, ctx->stripe_dist, ctx->T, ctx->wpack.p, ctx->blocked.p, ctx->sources.p, ctx->stripe_nsrc, P.up_row, P.up_wpack, P.down_row, d_tiles, ctx->T);
+			launch_finalize_tiled(ctx, ctx->W, ctx->H, ctx->sy0, ctx->sH, ctx->stripe_dist, ctx->T, ctx->stripe_nsrc, 1, P.up_row, P.up_wpack, P.down_row, d_tiles);
 		else
 			k_big_finalize<<<dim3((unsigned)grid_blocks(ctx, ctx->T, 256, 8), 1u), 256, 0, ctx->stream>>>(ctx->W, ctx->H, ctx->sy0, ctx->sH, ctx->stripe_dist, ctx->T, ctx->wpack.p, ctx->blocked.p, ctx->sources.p, ctx->stripe_nsrc, P.up_row, P.up_wpack, P.down_row, d_tiles, ctx->T);
 		LAUNCHED();
@@ -1848,7 +1854,7 @@ extern "C" int mtd_stripe_peer_launch_dev(mtd_ctx *ctx, const uint32_t *sources,
 	{
 		ProfScope prof(ctx, MTD_K_BIG_DIRECTIONS);
 		if (finalize_vec_ok(ctx, d_dist, d_tiles))
-			k_big_finalize4<<<dim3((unsigned)grid_blocks(ctx, ctx->T / 4, 256, 8), 1u), 256, 0, ctx->stream>>>(ctx->W, ctx->H, ctx->sy0, ctx->sH, d_dist, ctx->T, ctx->wpack.p, ctx->blocked.p, ctx->sources.p, nsrc, P.up_row, P.up_wpack, P.down_row, d_tiles, ctx->T);
+			launch_finalize_tiled(ctx, ctx->W, ctx->H, ctx->sy0, ctx->sH, d_dist, ctx->T, nsrc, 1, P.up_row, P.up_wpack, P.down_row, d_tiles);
 		else
 			k_big_finalize<<<dim3((unsigned)grid_blocks(ctx, ctx->T, 256, 8), 1u), 256, 0, ctx->stream>>>(ctx->W, ctx->H, ctx->sy0, ctx->sH, d_dist, ctx->T, ctx->wpack.p, ctx->blocked.p, ctx->sources.p, nsrc, P.up_row, P.up_wpack, P.down_row, d_tiles, ctx->T);
 		LAUNCHED();
