@@ -83,36 +83,23 @@ namespace mtd
 			i = (int)((uint32_t)i * (uint32_t)PRIME_X);
 			j = (int)((uint32_t)j * (uint32_t)PRIME_Y);
 
-			float n0 = 0, n1 = 0, n2 = 0;
-
+			// The three corner terms are evaluated without branches: a corner whose falloff is not positive contributes a zero
+			// (the reference skips it and adds its initial 0). The zero may come out negative here (0 * negative gradient);
+			// that cannot reach a result bit: a zero term changes no non-zero sum, and an all-zero sum is only used through
+			// |n| * -2 + 1, which is 1 for either sign.
 			const float a = __fsub_rn(__fsub_rn(0.5f, __fmul_rn(x0, x0)), __fmul_rn(y0, y0));
-			if (a > 0)
-				n0 = pow4_times(a, grad_coord(table, seed, i, j, x0, y0));
+			const float n0 = pow4_times(a > 0 ? a : 0.0f, grad_coord(table, seed, i, j, x0, y0));
 
 			const float c = __fadd_rn(__fmul_rn(C1, t), __fadd_rn(C2, a));
-			if (c > 0)
-			{
-				const float x2 = __fadd_rn(x0, G22M1);
-				const float y2 = __fadd_rn(y0, G22M1);
-				n2 = pow4_times(c, grad_coord(table, seed, (int)((uint32_t)i + (uint32_t)PRIME_X), (int)((uint32_t)j + (uint32_t)PRIME_Y), x2, y2));
-			}
+			const float x2 = __fadd_rn(x0, G22M1);
+			const float y2 = __fadd_rn(y0, G22M1);
+			const float n2 = pow4_times(c > 0 ? c : 0.0f, grad_coord(table, seed, (int)((uint32_t)i + (uint32_t)PRIME_X), (int)((uint32_t)j + (uint32_t)PRIME_Y), x2, y2));
 
-			if (y0 > x0)
-			{
-				const float x1 = __fadd_rn(x0, G2);
-				const float y1 = __fadd_rn(y0, G2M1);
-				const float b = __fsub_rn(__fsub_rn(0.5f, __fmul_rn(x1, x1)), __fmul_rn(y1, y1));
-				if (b > 0)
-					n1 = pow4_times(b, grad_coord(table, seed, i, (int)((uint32_t)j + (uint32_t)PRIME_Y), x1, y1));
-			}
-			else
-			{
-				const float x1 = __fadd_rn(x0, G2M1);
-				const float y1 = __fadd_rn(y0, G2);
-				const float b = __fsub_rn(__fsub_rn(0.5f, __fmul_rn(x1, x1)), __fmul_rn(y1, y1));
-				if (b > 0)
-					n1 = pow4_times(b, grad_coord(table, seed, (int)((uint32_t)i + (uint32_t)PRIME_X), j, x1, y1));
-			}
+			const bool up = y0 > x0;
+			const float x1 = __fadd_rn(x0, up ? G2 : G2M1);
+			const float y1 = __fadd_rn(y0, up ? G2M1 : G2);
+			const float b = __fsub_rn(__fsub_rn(0.5f, __fmul_rn(x1, x1)), __fmul_rn(y1, y1));
+			const float n1 = pow4_times(b > 0 ? b : 0.0f, grad_coord(table, seed, up ? i : (int)((uint32_t)i + (uint32_t)PRIME_X), up ? (int)((uint32_t)j + (uint32_t)PRIME_Y) : j, x1, y1));
 
 			return __fmul_rn(__fadd_rn(__fadd_rn(n0, n1), n2), 99.83685446303647f);
 		}
