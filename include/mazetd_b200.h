@@ -87,6 +87,7 @@ enum
 	MTD_DEBUG_GEN_WARPS = 12,  /* fused generator: how many of the warps without a layer compute the next map's elevations during the relaxation (0 = all warps, after it). Performance only */
 	MTD_DEBUG_ASYNC_WORKERS = 13, /* dataflow scheduler: worker warps per SM that are handed items (1..16). Performance only */
 	MTD_DEBUG_ASYNC_LATE_LOOKS = 14, /* dataflow scheduler: how often a visit re-reads its apron from global memory after converging and goes on if a neighbour lowered it meanwhile (0..4, default 1). Performance only */
+	MTD_DEBUG_ASYNC_CONT = 15, /* dataflow scheduler: 1 (default) = a revisit of a tile goes to the worker that visited it last (queued behind the running visit, or to that worker if idle) and continues on the frame it left instead of staging it again. Same result */
 	MTD_DEBUG_BIG_TMA = 7,     /* dataflow scheduler: 1 (default) = tile frames staged by 2-D bulk tensor copies (TMA), 0 = cp.async rows. Same result */
 	MTD_DEBUG_ASYNC_DELTA = 6, /* priority window (label units) of the dataflow scheduler. Performance only */
 	MTD_DEBUG_TILE_DELTA = 4   /* large grids: width (label units) of the window of tile offers visited per round; 2^32-1 = visit everything (no priority). Performance only: any value gives the same result */

@@ -165,6 +165,7 @@ class Context:
     DEBUG_GEN_WARPS = 12
     DEBUG_ASYNC_WORKERS = 13
     DEBUG_ASYNC_LATE_LOOKS = 14
+    DEBUG_ASYNC_CONT = 15
     DEBUG_ASYNC_NB_RULE = 8
     DEBUG_ASYNC_DEPTH = 9
 

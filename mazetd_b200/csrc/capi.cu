@@ -132,6 +132,7 @@ struct mtd_ctx
 	DevBuf<uint32_t> a_tail, a_ctamin, a_ctl, a_fly;
 	int async_workers = ASYNC_WORKERS; // worker warps per SM in use
 	int async_late_looks = 1;          // a visit re-reads its apron once after converging
+	int async_cont = 0;                // 1: revisits continue on the frame of the worker that visited the tile last (measured: no gain, r03x)
 	int async_nb_rule = 0, async_depth = 2; // measured (profiles/r02g_*): the neighbour rule halves the visits but not the time; two mailboxes: 14.5 -> 13.0 ms on C4
 	uint32_t async_nb_margin = 0; // dataflow scheduler of k_tile_async: inbox rings, ring tails, per-CTA smallest keys, control words
 	bool big_async = true;         // large grids: k_tile_async (no global rounds); false = k_tile_rounds (A/B and multi-stripe contexts)
@@ -677,6 +678,7 @@ namespace
 		A.depth = ctx->async_depth;
 		A.workers = ctx->async_workers;
 		A.late_looks = ctx->async_late_looks;
+		A.cont = ctx->async_cont;
 		A.time_limit_ns = peer ? 8000000000ull : 20000000000ull; // an update that takes this long is reported, not waited for
 		P.tile_delta = ctx->async_delta;
 		// frames staged by TMA: one tensor map over the labels of all layers, one over the packed weights
@@ -724,6 +726,23 @@ namespace
 			unsigned long long x[4], zx[4] = { 0 };
 			cudaMemcpyFromSymbol(x, g_async_sched_extra, sizeof(x));
 			cudaMemcpyToSymbol(g_async_sched_extra, zx, sizeof(zx));
+			{
+				uint32_t dm = 0, zero = 0;
+				cudaMemcpyFromSymbol(&dm, g_async_depth_max, 4);
+				cudaMemcpyToSymbol(g_async_depth_max, &zero, 4);
+				cudaMemset(nullptr, 0, 0);
+				void *dp = nullptr;
+				cudaGetSymbolAddress(&dp, g_async_depth);
+				cudaMemset(dp, 0, sizeof(uint32_t) << 20);
+				uint32_t sm = 0;
+				cudaMemcpyFromSymbol(&sm, g_async_sdepth_max, 4);
+				cudaMemcpyToSymbol(g_async_sdepth_max, &zero, 4);
+				cudaGetSymbolAddress(&dp, g_async_sdepth);
+				cudaMemset(dp, 0, sizeof(uint32_t) << 20);
+				cudaGetSymbolAddress(&dp, g_async_sdepth_off);
+				cudaMemset(dp, 0, sizeof(uint32_t) << 20);
+				printf("ASYNCCHAIN longest chain of dependent visits = %u (offers only), %u (counting the previous visit of the same tile as a predecessor)\n", dm, sm);
+			}
 			printf("ASYNCSCHED2 per iteration: handed out %.2f | pending left: runnable but no free mailbox here %.2f, tile in flight %.2f, beyond the window %.2f\n", t[9] ? (double)x[1] / t[9] : 0.0, t[9] ? (double)t[14] / t[9] : 0.0,
 				   t[9] ? (double)x[0] / t[9] : 0.0, t[9] ? (double)t[15] / t[9] : 0.0);
 			printf("ASYNCSCHED iterations=%llu (%.2f us each at %d schedulers over the kernel) | per iteration: idle workers seen %.2f, left idle %.2f (held back by the window %.2f), pending entries %.1f\n", t[9], 0.0, ctas, t[9] ? (double)t[10] / t[9] : 0.0,
@@ -1308,6 +1327,9 @@ extern "C" int mtd_debug_set(mtd_ctx *ctx, int key, int64_t value)
 	case MTD_DEBUG_ASYNC_NB_RULE:
 		ctx->async_nb_rule = value >= 0 ? 1 : 0; // value = margin (label units); negative = rule off
 		ctx->async_nb_margin = value >= 0 ? (uint32_t)value : 0u;
+		return MTD_OK;
+	case MTD_DEBUG_ASYNC_CONT:
+		ctx->async_cont = value != 0;
 		return MTD_OK;
 	case MTD_DEBUG_ASYNC_LATE_LOOKS:
 		ctx->async_late_looks = value < 0 ? 0 : value > 4 ? 4 : (int)value;

@@ -33,6 +33,7 @@ namespace mtd
 	constexpr int ASYNC_KX = 12;          // owner = (tx + KX * ty + KL * layer) mod CTAs: a 12 x 12 block of tiles has 144 different owners
 	constexpr int ASYNC_KL = 53;
 	constexpr uint32_t SLOT_IDLE = 0xFFFFFFFFu, SLOT_EXIT = 0xFFFFFFFEu;
+	constexpr uint32_t SLOT_CONT = 0x80000000u; // mailbox flag: the worker's frame still holds this item from its last visit (items are < 2^31)
 	// control words (AsyncCtl::ctl)
 	constexpr int ACTL_OUTSTANDING = 0; // items pending or in flight
 	constexpr int ACTL_ABORT = 1;       // a scheduler hit the time limit
@@ -92,6 +93,13 @@ namespace mtd
 	// 0 wait for work, 1 consume key, 2 stage, 3 seed, 4 engine, 5 write back + offers computed, 6 offers sent + finish, 7 engine steps, 8 cells popped
 	__device__ unsigned long long g_async_timing[16];
 	__device__ unsigned long long g_async_sched_extra[4];
+	// developer probe: length of the longest chain of dependent visits (a visit's depth = 1 + the largest depth among the
+	// visits whose offers it was made pending by), and when the deepest visit ended
+	__device__ uint32_t g_async_depth[1u << 20];
+	__device__ uint32_t g_async_depth_max;
+	__device__ uint32_t g_async_sdepth[1u << 20]; // ... counting the previous visit of the same tile as a predecessor too
+	__device__ uint32_t g_async_sdepth_off[1u << 20];
+	__device__ uint32_t g_async_sdepth_max;
 #define MTD_ATICK(k)                                     \
 	do                                                   \
 	{                                                    \
@@ -133,6 +141,7 @@ namespace mtd
 		int depth;           // mailboxes per worker in use: 1 or 2
 		int workers;         // worker warps the scheduler hands items to (<= ASYNC_WORKERS; the rest sleep)
 		int late_looks;      // how often a visit re-reads its apron from global memory after converging (0 = never)
+		int cont;            // 1: a revisit goes to the worker that visited the item last and continues on the frame it left (no staging)
 		unsigned long long time_limit_ns;
 	};
 
@@ -190,7 +199,7 @@ namespace mtd
 	// Returns in k[4] (warp-uniform) the smallest label on offer to the tile above / below / left / right (MTD_INF: none).
 	// Same arithmetic as the visit inside k_tile_rounds; `guard` is raised when a label gets close to the uint32 wrap.
 	template<int TS, class WT>
-	__device__ __forceinline__ void warp_visit(const BigParams &P, WT &S, int layer, int tx, int ty, uint32_t lane, uint32_t lt, uint32_t (&k)[4], bool &guard, const CUtensorMap *tm_dist, const CUtensorMap *tm_w, uint32_t &tma_phase, uint32_t next_item, int late_looks MTD_ATIMING_ARGS)
+	__device__ __forceinline__ void warp_visit(const BigParams &P, WT &S, int layer, int tx, int ty, uint32_t lane, uint32_t lt, uint32_t (&k)[4], bool &guard, const CUtensorMap *tm_dist, const CUtensorMap *tm_w, uint32_t &tma_phase, uint32_t next_item, int late_looks, bool cont MTD_ATIMING_ARGS)
 	{
 		constexpr int RW = WT::RW, PITCH = WT::PITCH, QCAP = WT::QCAP;
 		const int W = P.W;
@@ -206,7 +215,12 @@ namespace mtd
 		const bool interior = P.aligned16 && ly0 >= 0 && ly0 + RW <= Hl && gx0 >= 0 && gx0 + RW <= W;
 		const bool interior_wb = P.aligned16 && ly0 + 1 + TS <= Hl && gx0 + 1 + TS <= W;
 
-		// ---- stage ----
+		// the layer's first 32 sources, requested before the frame so that the list's L2 round trip hides behind the staging
+		// (read twice below: r03w showed 7k cycles in the seed phase, two dependent global loads of it)
+		const uint32_t src0 = (int)lane < P.nsrc ? __ldg(lsrc + lane) : 0u;
+		// ---- stage ---- (not when the frame is still the one this worker left after its last visit of this very item)
+		if (!cont)
+		{
 		if (use_tma)
 		{
 			// two boxes of 40 x 34 words (labels of this layer, packed weights), origin (tile_x0 - 4, tile_y0 - 1); what lies
@@ -289,6 +303,7 @@ namespace mtd
 				S.w[ry * PITCH + 3 + rx] = wv;
 			}
 		}
+		}
 		__syncwarp();
 
 		MTD_ATICK(2);
@@ -313,7 +328,10 @@ namespace mtd
 			}
 			tail += __popc(bal);
 		};
-		uint32_t ap_old[4];
+		uint32_t ap_old[4] = { 0u, 0u, 0u, 0u };
+		uint32_t src_sides = 0;
+		if (!cont)
+		{
 #pragma unroll
 		for (int side = 0; side < 4; side++)
 		{
@@ -348,15 +366,29 @@ namespace mtd
 			const bool row_exists = side < 2 || 1 + i < brow;
 			relax_into(row_exists && da != 0u && da != MTD_INF, v, da + MIN_EDGE + wsel);
 		}
-		uint32_t src_sides = 0;
+		// is any source inside this frame (tile or apron)? Most tiles have none: the two passes over the list below, with their
+		// five ballot-and-store rounds per 32 sources, are skipped then
+		bool src_near = false;
 		for (int s0 = 0; s0 < P.nsrc; s0 += 32)
+		{
+			const int s = s0 + (int)lane;
+			bool near = false;
+			if (s < P.nsrc)
+			{
+				const uint32_t src = s0 == 0 ? src0 : lsrc[s];
+				const int rx = (int)(src % (uint32_t)W) - gx0, ry = (int)(src / (uint32_t)W) - P.y0 - ly0;
+				near = rx >= 0 && rx <= TS + 1 && ry >= 0 && ry <= brow;
+			}
+			src_near |= __any_sync(0xFFFFFFFFu, near);
+		}
+		for (int s0 = 0; src_near && s0 < P.nsrc; s0 += 32)
 		{
 			const int s = s0 + (int)lane;
 			bool want = false;
 			uint32_t v = 0, nd = 0;
 			if (s < P.nsrc)
 			{
-				const uint32_t src = lsrc[s];
+				const uint32_t src = s0 == 0 ? src0 : lsrc[s];
 				const int rx = (int)(src % (uint32_t)W) - gx0, ry = (int)(src / (uint32_t)W) - P.y0 - ly0;
 				const bool inx = rx >= 1 && rx <= TS, iny = ry >= 1 && ry < brow;
 				const uint32_t a = (uint32_t)(ry * PITCH + rx + 3);
@@ -396,14 +428,14 @@ namespace mtd
 			S.d[(1 + i) * PITCH + 4 + TS] = 0u;
 		}
 		__syncwarp();
-		for (int s0 = 0; s0 < P.nsrc; s0 += 32)
+		for (int s0 = 0; src_near && s0 < P.nsrc; s0 += 32)
 		{
 			const int s = s0 + (int)lane;
 			bool want = false;
 			uint32_t c = (uint32_t)(PITCH + 4);
 			if (s < P.nsrc)
 			{
-				const uint32_t src = lsrc[s];
+				const uint32_t src = s0 == 0 ? src0 : lsrc[s];
 				const int rx = (int)(src % (uint32_t)W) - gx0, ry = (int)(src / (uint32_t)W) - P.y0 - ly0;
 				want = rx >= 1 && rx <= TS && ry >= 1 && ry < brow;
 				if (want)
@@ -416,6 +448,7 @@ namespace mtd
 			relax_into(want, c - 1u, MIN_EDGE + (S.w[c - 1u] & 0xFFFFu));
 			relax_into(want, c + 1u, MIN_EDGE + (S.w[c] & 0xFFFFu));
 			relax_into(want, c + PITCH, MIN_EDGE + (S.w[c] >> 16));
+		}
 		}
 		uint32_t dmin = warp_redux_min(my_min);
 		__syncwarp();
@@ -540,7 +573,6 @@ namespace mtd
 		}
 		__syncwarp();
 		};
-		engine();
 		// ---- a late look at the apron ----
 		// Offers from several neighbours reach a tile within one visit time (the wavefront passes); whatever arrived while
 		// this visit was running would otherwise wait for it to end and cost a second full visit -- on the chain of dependent
@@ -548,7 +580,7 @@ namespace mtd
 		// their interiors back before they offer, so their border cells are re-read from global memory here (one L2 round
 		// trip), and cells that dropped below what this visit was seeded with seed the engine once more. The pending item
 		// such an offer created is still visited later (the accounting stays as it is) and finds nothing to do.
-		for (int look = 0; look < late_looks; look++)
+		auto apron_look = [&](bool all)
 		{
 			wq = S.q[par];
 			tail = 0;
@@ -605,13 +637,21 @@ namespace mtd
 				}
 				const uint32_t da = an[side];
 				const bool row_exists = side < 2 || 1 + i < brow;
-				const bool lower = row_exists && da != 0u && da != MTD_INF && da < ap_old[side]; // a parked cell (0) stays parked: blocked tiles never change
+				const bool lower = row_exists && da != 0u && da != MTD_INF && (all || da < ap_old[side]); // a parked cell (0) stays parked: blocked tiles never change
 				relax_into(lower, v, da + MIN_EDGE + wsel);
-				if (lower)
+				if (lower || all)
 					ap_old[side] = da;
 			}
 			dmin = warp_redux_min(my_min);
 			__syncwarp();
+		};
+		// continuing on the frame of my last visit: everything the neighbours hold now is a candidate (their offers are why I am here)
+		if (cont)
+			apron_look(true);
+		engine();
+		for (int look = 0; look < late_looks; look++)
+		{
+			apron_look(false);
 			if (tail == 0u)
 				break;
 			engine();
@@ -704,7 +744,7 @@ namespace mtd
 			// ---------------- worker ----------------
 			WT &S = reinterpret_cast<WT *>(smem_async)[warp];
 			bool guard = false;
-			uint32_t visits = 0, tma_phase = 0, take = 0;
+			uint32_t visits = 0, tma_phase = 0, take = 0, last_item = SLOT_IDLE;
 #ifdef MTD_TIMING
 			unsigned long long tacc[16] = { 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0 };
 			long long last__ = clock64();
@@ -728,13 +768,23 @@ namespace mtd
 				it = __shfl_sync(0xFFFFFFFFu, it, 0);
 				if (it == SLOT_EXIT)
 					break;
+				const bool cont = (it & SLOT_CONT) != 0u && (it & ~SLOT_CONT) == last_item; // the scheduler only flags what it gave me last
+				it &= ~SLOT_CONT;
 				MTD_ATICK(0);
 				const int layer = (int)(it / ntiles);
 				const uint32_t tile = it - (uint32_t)layer * ntiles;
 				const int tx = (int)(tile % (uint32_t)P.tilesX), ty = (int)(tile / (uint32_t)P.tilesX);
 				MTD_ATICK(1);
 				uint32_t k[4];
-				warp_visit<TS>(P, S, layer, tx, ty, lane, lt, k, guard, A.use_tma ? &tm_dist : nullptr, A.use_tma ? &tm_w : nullptr, tma_phase, slot[mine ^ 1], A.late_looks MTD_ATIMING_PASS);
+#ifdef MTD_TIMING
+				const uint32_t depth__ = it < (1u << 20) ? atomicExch(&g_async_depth[it], 0u) : 0u;
+				const uint32_t sdepth__ = it < (1u << 20) ? max(atomicExch(&g_async_sdepth_off[it], 0u), g_async_sdepth[it]) : 0u;
+#endif
+				uint32_t nxt = slot[mine ^ 1];
+				if (nxt & SLOT_CONT)
+					nxt = 0xFFFFFFFFu; // nothing to prefetch: a continued visit (or an empty mailbox)
+				warp_visit<TS>(P, S, layer, tx, ty, lane, lt, k, guard, A.use_tma ? &tm_dist : nullptr, A.use_tma ? &tm_w : nullptr, tma_phase, nxt, A.late_looks, cont MTD_ATIMING_PASS);
+				last_item = it;
 				if (P.ctl0)
 				{
 					// row stripes: the tile above / below a border tile belongs to a neighbour rank. Its copy of my boundary row is
@@ -784,6 +834,25 @@ namespace mtd
 				fence_gpu(); // my labels (and the count) are visible before a neighbour can be scheduled
 				__syncwarp();
 				MTD_ATICK(5);
+#ifdef MTD_TIMING
+				if (have)
+				{
+					const int nx__ = lane == 2 ? tx - 1 : lane == 3 ? tx + 1 : tx, ny__ = lane == 0 ? ty - 1 : lane == 1 ? ty + 1 : ty;
+					const uint32_t ni__ = (uint32_t)layer * ntiles + (uint32_t)(ny__ * P.tilesX + nx__);
+					if (ni__ < (1u << 20))
+					{
+						atomicMax(&g_async_depth[ni__], depth__ + 1u);
+						atomicMax(&g_async_sdepth_off[ni__], sdepth__ + 1u);
+					}
+				}
+				if (lane == 0)
+				{
+					atomicMax(&g_async_depth_max, depth__ + 1u);
+					atomicMax(&g_async_sdepth_max, sdepth__ + 1u);
+					if (it < (1u << 20))
+						g_async_sdepth[it] = sdepth__ + 1u;
+				}
+#endif
 				bool made = false;
 				if (have)
 					made = async_offer(P, A, layer, lane == 2 ? tx - 1 : lane == 3 ? tx + 1 : tx, lane == 0 ? ty - 1 : lane == 1 ? ty + 1 : ty, kk);
@@ -822,6 +891,7 @@ namespace mtd
 		unsigned long long *ring = A.inbox + (size_t)me * cap;
 		uint32_t head = 0, pn = 0, polls = 0;
 		uint32_t fill = 0; // lane w < WORKERS: which of worker w's two mailboxes is filled next (the worker empties them in the same order)
+		uint32_t lastw = SLOT_IDLE; // lane w < WORKERS: the item worker w was given last (its frame holds it once it is through its mailboxes)
 		// ---- peer-coupled stripes: entering the run ----
 		const bool peer = P.ctl0 != nullptr;
 		bool peer_dead = false;
@@ -1083,7 +1153,7 @@ namespace mtd
 				half_w = __ballot_sync(0xFFFFFFFFu, lane < (uint32_t)A.workers && (b0 == 1u || b0 == 2u) && A.depth > 1);
 			}
 			__syncwarp();
-			uint32_t nasg = 0;
+			uint32_t nasg = 0, contmask = 0;
 #ifdef MTD_TIMING
 			const uint32_t idle_before__ = (uint32_t)__popc(idle_w);
 			uint32_t blocked__ = 0;
@@ -1107,17 +1177,57 @@ namespace mtd
 						bi = min(bi, i);
 				bi = warp_redux_min(bi);
 				const uint32_t item = Q.pend_item[bi];
-				if (__any_sync(0xFFFFFFFFu, cur == item))
+				// A revisit costs least on the worker whose frame still holds the tile: it skips the staging and only looks at
+				// the apron again. Most revisits are back to back -- offers from several neighbours reach a wavefront tile within
+				// one visit time -- so the item goes into the OTHER mailbox of the worker that is visiting it right now, or, if
+				// that visit is over, to that worker if it is idle.
+				const uint32_t hit = __ballot_sync(0xFFFFFFFFu, cur < SLOT_EXIT && (cur & ~SLOT_CONT) == item);
+				int w = -1;
+				bool as_cont = false;
+				if (hit)
 				{
-					// its tile is being visited (or waits in a mailbox): it stays pending; hidden for this iteration
-					if (lane == 0)
-						Q.pend_key[bi] = MTD_INF;
-					__syncwarp();
-					continue;
+					const int hw = (__ffs(hit) - 1) >> 1;
+					if (A.cont && __popc(hit) == 1 && ((half_w >> hw) & 1u) && __shfl_sync(0xFFFFFFFFu, lastw, hw) == item)
+					{
+						w = hw;
+						as_cont = true;
+						half_w &= ~(1u << hw);
+					}
+					else
+					{
+						// its tile is being visited and cannot be queued behind that visit: it stays pending; hidden for this iteration
+						if (lane == 0)
+							Q.pend_key[bi] = MTD_INF;
+						__syncwarp();
+						continue;
+					}
 				}
-				const int w = idle_w ? __ffs(idle_w) - 1 : __ffs(half_w) - 1;
+				else
+				{
+					const uint32_t warm = A.cont ? __ballot_sync(0xFFFFFFFFu, lane < (uint32_t)A.workers && lastw == item) & idle_w : 0u;
+					if (warm)
+					{
+						w = __ffs(warm) - 1;
+						as_cont = true;
+						idle_w &= ~(1u << w);
+					}
+					else if (idle_w)
+					{
+						w = __ffs(idle_w) - 1;
+						idle_w &= idle_w - 1u;
+					}
+					else
+					{
+						w = __ffs(half_w) - 1;
+						half_w &= half_w - 1u;
+					}
+				}
 				const uint32_t f = __shfl_sync(0xFFFFFFFFu, fill, w);
 				const uint32_t sl = (uint32_t)w * 2u + f;
+				if (lane == (uint32_t)w)
+					lastw = item;
+				if (as_cont)
+					contmask |= 1u << nasg;
 				if (lane == (uint32_t)w)
 					fill ^= 1u;
 				if (lane == sl)
@@ -1132,10 +1242,6 @@ namespace mtd
 				}
 				nasg++;
 				pn--;
-				if (idle_w)
-					idle_w &= idle_w - 1u;
-				else
-					half_w &= half_w - 1u;
 				__syncwarp();
 			}
 			if (nasg)
@@ -1149,7 +1255,7 @@ namespace mtd
 				fence_gpu();
 				__syncwarp();
 				if (lane < nasg)
-					slot[Q.asg_slot[lane]] = Q.asg_item[lane];
+					slot[Q.asg_slot[lane]] = Q.asg_item[lane] | (((contmask >> lane) & 1u) ? SLOT_CONT : 0u);
 				__syncwarp();
 			}
 			polls++;

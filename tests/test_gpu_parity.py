@@ -241,6 +241,17 @@ def test_dataflow_scheduler_really_runs_and_windows_agree(ctx, oracle):
         assert np.array_equal(dist, do), (delta, diff_report(dist, do, W))
         assert np.array_equal(tiles, to), delta
     ctx.debug_set(ctx.DEBUG_ASYNC_DELTA, 65536)
+    # the scheduler's optional forms: no late look at the apron / two of them, revisits continued on the last visitor's frame,
+    # fewer workers, one mailbox per worker -- all performance knobs, the fixpoint is the same
+    for key, value, default in ((ctx.DEBUG_ASYNC_LATE_LOOKS, 0, 1), (ctx.DEBUG_ASYNC_LATE_LOOKS, 2, 1), (ctx.DEBUG_ASYNC_CONT, 1, 0), (ctx.DEBUG_ASYNC_WORKERS, 5, 16), (ctx.DEBUG_ASYNC_DEPTH, 1, 2)):
+        try:
+            ctx.debug_set(key, value)
+            tiles, dist = ctx.directions_update(srcs)
+        finally:
+            ctx.debug_set(key, default)
+        assert ctx.big_stats()["dataflow"]
+        assert np.array_equal(dist, do), (key, value, diff_report(dist, do, W))
+        assert np.array_equal(tiles, to), (key, value)
 
 
 def test_c5_full_size_against_reference_golden_and_oracle(tctx, oracle):

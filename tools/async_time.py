@@ -25,6 +25,11 @@ ctx.debug_set(ctx.DEBUG_ASYNC_NB_RULE, nb)
 ctx.debug_set(ctx.DEBUG_ASYNC_DEPTH, depth)
 ctx.debug_set(ctx.DEBUG_ASYNC_WORKERS, int(os.environ.get('MTD_WORKERS', '16')))
 looks = int(os.environ.get('MTD_LOOKS', '1'))
+contv = int(os.environ.get('MTD_CONT', '1'))
+try:
+    ctx.debug_set(ctx.DEBUG_ASYNC_CONT, contv)
+except Exception:
+    contv = -1
 try:
     ctx.debug_set(ctx.DEBUG_ASYNC_LATE_LOOKS, looks)
 except Exception:
@@ -38,4 +43,4 @@ for delta in deltas:
             ctx.directions_update_dev(srcs[:nsrc], dt.data_ptr(), dd.data_ptr())
         ctx.synchronize()
         relax, _ = ctx.profile_read(ctx.K_BIG_RELAX)
-    print(json.dumps(dict(cfg=cfg, delta=delta, nb=nb, depth=depth, looks=looks, workers=int(os.environ.get('MTD_WORKERS', '16')), relax_ms=round(relax, 3), **ctx.big_stats())), flush=True)
+    print(json.dumps(dict(cfg=cfg, delta=delta, nb=nb, depth=depth, looks=looks, cont=contv, workers=int(os.environ.get('MTD_WORKERS', '16')), relax_ms=round(relax, 3), **ctx.big_stats())), flush=True)
