@@ -743,6 +743,13 @@ namespace
 				cudaMemset(dp, 0, sizeof(uint32_t) << 20);
 				printf("ASYNCCHAIN longest chain of dependent visits = %u (offers only), %u (counting the previous visit of the same tile as a predecessor)\n", dm, sm);
 			}
+			{
+				unsigned long long ph[8], zp[8] = { 0 };
+				cudaMemcpyFromSymbol(ph, g_async_sched_phase, sizeof(ph));
+				cudaMemcpyToSymbol(g_async_sched_phase, zp, sizeof(zp));
+				const double it = t[9] ? (double)t[9] : 1.0;
+				printf("ASYNCSCHEDPHASE cycles per scheduler iteration: loads + key refresh %.0f | drain + mailboxes + ctamin %.0f | hand-out loop %.0f | consume + ring %.0f | loop tail (stop test, sleep) %.0f\n", ph[0] / it, ph[2] / it, ph[3] / it, ph[4] / it, ph[5] / it);
+			}
 			printf("ASYNCSCHED2 per iteration: handed out %.2f | pending left: runnable but no free mailbox here %.2f, tile in flight %.2f, beyond the window %.2f\n", t[9] ? (double)x[1] / t[9] : 0.0, t[9] ? (double)t[14] / t[9] : 0.0,
 				   t[9] ? (double)x[0] / t[9] : 0.0, t[9] ? (double)t[15] / t[9] : 0.0);
 			printf("ASYNCSCHED iterations=%llu (%.2f us each at %d schedulers over the kernel) | per iteration: idle workers seen %.2f, left idle %.2f (held back by the window %.2f), pending entries %.1f\n", t[9], 0.0, ctas, t[9] ? (double)t[10] / t[9] : 0.0,

@@ -93,6 +93,8 @@ namespace mtd
 	// 0 wait for work, 1 consume key, 2 stage, 3 seed, 4 engine, 5 write back + offers computed, 6 offers sent + finish, 7 engine steps, 8 cells popped
 	__device__ unsigned long long g_async_timing[16];
 	__device__ unsigned long long g_async_sched_extra[4];
+	__device__ unsigned long long g_async_sched_phase[8]; // cycles of a scheduler iteration: loads | refresh + drain | bookkeeping | hand-out | consume + ring | tail
+#define MTD_STICK(k) do { if (lane == 0) { const long long n__ = clock64(); sacc__[k] += (unsigned long long)(n__ - slast__); slast__ = n__; } } while (0)
 	// developer probe: length of the longest chain of dependent visits (a visit's depth = 1 + the largest depth among the
 	// visits whose offers it was made pending by), and when the deepest visit ended
 	__device__ uint32_t g_async_depth[1u << 20];
@@ -111,6 +113,7 @@ namespace mtd
 #define MTD_ATIMING_PASS , tacc, last__
 #else
 #define MTD_ATICK(k)
+#define MTD_STICK(k)
 #define MTD_ATIMING_ARGS
 #define MTD_ATIMING_PASS
 #endif
@@ -955,12 +958,17 @@ namespace mtd
 		}
 		const unsigned long long t0 = global_timer_ns();
 		bool stop = false;
+#ifdef MTD_TIMING
+		unsigned long long sacc__[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+		long long slast__ = clock64();
+#endif
 		while (!stop)
 		{
 			// everything the decision needs from global memory is requested at once: ONE L2 round trip per iteration
 			//   * the next 32 inbox entries past `head` (an entry is 0 until its store has landed: no tail needed),
 			//   * the keys of the pending entries (offers only ever lower them),
 			//   * every CTA's smallest key, the count of items alive, the abort flag
+			MTD_STICK(5);
 			const unsigned long long e = __ldcg(ring + ((head + lane) & A.cap_mask));
 			const uint32_t outstanding = __ldcg(A.ctl + ACTL_OUTSTANDING);
 			const uint32_t aborted = __ldcg(A.ctl + ACTL_ABORT);
@@ -1040,6 +1048,7 @@ namespace mtd
 				}
 				Q.pend_key[i] = kk;
 			}
+			MTD_STICK(0);
 			// drain: entries in order up to the first empty one; each comes with the key it was offered at
 			{
 				const uint32_t room = (uint32_t)ASYNC_PCAP - pn;
@@ -1144,6 +1153,7 @@ namespace mtd
 				}
 				__syncwarp();
 			}
+			MTD_STICK(2);
 			const uint32_t kthr = wm > MTD_INF - P.tile_delta ? MTD_INF : wm + P.tile_delta;
 			// workers that can take an item: first the ones with nothing to do, then the ones that have no NEXT item yet
 			uint32_t idle_w = 0, half_w = 0;
@@ -1158,6 +1168,70 @@ namespace mtd
 			const uint32_t idle_before__ = (uint32_t)__popc(idle_w);
 			uint32_t blocked__ = 0;
 #endif
+			// All hand-outs of an iteration in one step, lane i deciding for pending entry i (r03z: the one-at-a-time loop below
+			// took 60 % of a scheduler iteration, ~2k cycles per item). Runnable = inside the window and its tile in no
+			// mailbox. In the latency-bound regime the workers are mostly idle and every runnable entry finds a mailbox;
+			// otherwise the entries with the smallest keys take the free ones. The loop below remains for lists longer than
+			// a warp and for the optional modes.
+			if (!A.cont && pn != 0u && pn <= 32u && (idle_w | half_w) != 0u)
+			{
+				const uint32_t my_key = lane < pn ? Q.pend_key[lane] : MTD_INF;
+				const uint32_t my_item = lane < pn ? Q.pend_item[lane] : 0xFFFFFFFFu;
+				bool inflight = false;
+#pragma unroll 8
+				for (int sl = 0; sl < ASYNC_SLOTS; sl++)
+				{
+					const uint32_t c = __shfl_sync(0xFFFFFFFFu, cur, sl);
+					inflight |= c == my_item; // an idle or exiting mailbox holds no item number
+				}
+				const uint32_t runnable = __ballot_sync(0xFFFFFFFFu, my_key < kthr && !inflight);
+				const uint32_t nrun = (uint32_t)__popc(runnable), nidle = (uint32_t)__popc(idle_w), nfree = nidle + (uint32_t)__popc(half_w);
+				if (nrun != 0u)
+				{
+					// more runnable entries than free mailboxes: the ones with the smallest keys go (rank by (key, lane))
+					uint32_t r = (uint32_t)__popc(runnable & lt);
+					if (nrun > nfree)
+					{
+						r = 0u;
+						for (int o = 0; o < 32; o++)
+						{
+							const uint32_t ok = __shfl_sync(0xFFFFFFFFu, my_key, o);
+							r += ((runnable >> o) & 1u) && (ok < my_key || (ok == my_key && (uint32_t)o < lane)) ? 1u : 0u;
+						}
+					}
+					const bool sel = ((runnable >> lane) & 1u) && r < nfree;
+					const uint32_t nsel = min(nrun, nfree);
+					// the r-th free worker: the idle ones first, then the ones without a next item
+					const uint32_t w = sel ? (r < nidle ? __fns(idle_w, 0u, (int)r + 1) : __fns(half_w, 0u, (int)(r - nidle) + 1)) : 0u;
+					const uint32_t f = __shfl_sync(0xFFFFFFFFu, fill, (int)w);
+					const uint32_t keep = __ballot_sync(0xFFFFFFFFu, lane < pn && !sel);
+					__syncwarp();
+					if (sel)
+					{
+						const uint32_t sl = w * 2u + f;
+						Q.ifkey[sl] = my_key;
+						Q.asg_slot[r] = sl;
+						Q.asg_item[r] = my_item;
+					}
+					else if (lane < pn)
+					{
+						const uint32_t pos = (uint32_t)__popc(keep & lt);
+						Q.pend_item[pos] = my_item;
+						Q.pend_key[pos] = my_key;
+					}
+					// every worker that got an item (one each) moves on to its other mailbox
+					uint32_t got = 0;
+					if (sel)
+						got = 1u << w;
+					got = __reduce_or_sync(0xFFFFFFFFu, got);
+					if ((got >> lane) & 1u)
+						fill ^= 1u;
+					nasg = nsel;
+					pn = (uint32_t)__popc(keep);
+					idle_w = half_w = 0u; // nothing left for the loop below: every runnable entry or every free mailbox is used
+					__syncwarp();
+				}
+			}
 			while ((idle_w | half_w) != 0u && pn != 0u)
 			{
 				uint32_t bk = MTD_INF;
@@ -1244,6 +1318,7 @@ namespace mtd
 				pn--;
 				__syncwarp();
 			}
+			MTD_STICK(3);
 			if (nasg)
 			{
 				// consume the offers of everything handed out (whoever made one wrote its labels first), THEN ring the mailboxes
@@ -1258,6 +1333,7 @@ namespace mtd
 					slot[Q.asg_slot[lane]] = Q.asg_item[lane] | (((contmask >> lane) & 1u) ? SLOT_CONT : 0u);
 				__syncwarp();
 			}
+			MTD_STICK(4);
 			polls++;
 #ifdef MTD_TIMING
 			{
@@ -1320,6 +1396,11 @@ namespace mtd
 				break;
 			__nanosleep(200);
 		}
+#ifdef MTD_TIMING
+		if (lane == 0)
+			for (int q = 0; q < 8; q++)
+				atomicAdd(&g_async_sched_phase[q], sacc__[q]);
+#endif
 		if (lane == 0)
 			atomicAdd(A.ctl + ACTL_IDLE_POLLS, polls);
 	}

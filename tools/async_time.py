@@ -25,7 +25,7 @@ ctx.debug_set(ctx.DEBUG_ASYNC_NB_RULE, nb)
 ctx.debug_set(ctx.DEBUG_ASYNC_DEPTH, depth)
 ctx.debug_set(ctx.DEBUG_ASYNC_WORKERS, int(os.environ.get('MTD_WORKERS', '16')))
 looks = int(os.environ.get('MTD_LOOKS', '1'))
-contv = int(os.environ.get('MTD_CONT', '1'))
+contv = int(os.environ.get('MTD_CONT', '0'))
 try:
     ctx.debug_set(ctx.DEBUG_ASYNC_CONT, contv)
 except Exception:
