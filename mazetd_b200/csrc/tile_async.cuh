@@ -29,6 +29,14 @@
 namespace mtd
 {
 	constexpr int ASYNC_WORKERS = 16;     // worker warps per CTA (one CTA per SM)
+#ifndef MTD_ASYNC_BUCKET
+#define MTD_ASYNC_BUCKET 384u
+#endif
+	// bucket width of the engine inside a visit, in label units (edges weigh 255 .. ~600). While throughput bounded the kernel
+	// 512 .. 4096 were within 2 % of each other (r02a); now that the chain of dependent visits does, narrower buckets -- fewer
+	// cells settled too early and relaxed again -- make a visit shorter: 255 / 384 / 512 / 768 / 1024 / 2048 give 9.08 / 8.20 /
+	// 8.28 / 8.52 / 8.63 / 8.78 ms on C5 and 12.62 / 11.71 / 11.79 / 12.01 / 12.11 / 12.27 ms on C4 (profiles/r04f_*)
+	constexpr uint32_t ASYNC_BUCKET = MTD_ASYNC_BUCKET;
 	constexpr int ASYNC_PCAP = 2048;      // pending items a scheduler can hold (>= items owned by a CTA, checked on the host)
 	constexpr int ASYNC_KX = 12;          // owner = (tx + KX * ty + KL * layer) mod CTAs: a 12 x 12 block of tiles has 144 different owners
 	constexpr int ASYNC_KL = 53;
@@ -470,7 +478,7 @@ namespace mtd
 		{
 		uint32_t nq = tail;
 		bool overflow = false;
-		uint32_t thr = dmin == MTD_INF ? MTD_INF : dmin + BIG_DELTA;
+		uint32_t thr = dmin == MTD_INF ? MTD_INF : dmin + ASYNC_BUCKET;
 		while (nq != 0u)
 		{
 			if (nq > (uint32_t)QCAP)
@@ -533,12 +541,12 @@ namespace mtd
 					wq[p] = (uint16_t)(c + PITCH);
 			}
 			if (__any_sync(0xFFFFFFFFu, settled_any))
-				thr = thr > MTD_INF - BIG_DELTA ? MTD_INF : thr + BIG_DELTA;
+				thr = thr > MTD_INF - ASYNC_BUCKET ? MTD_INF : thr + ASYNC_BUCKET;
 			else
 			{
 				// nothing was below the threshold: jump to the bucket of the smallest pending label
 				const uint32_t km = warp_redux_min(kept_min);
-				thr = km > MTD_INF - BIG_DELTA ? MTD_INF : km + BIG_DELTA;
+				thr = km > MTD_INF - ASYNC_BUCKET ? MTD_INF : km + ASYNC_BUCKET;
 			}
 			nq = tail;
 			par ^= 1u;
